@@ -1,0 +1,182 @@
+/*
+ * ggml_b200.h — the C ABI of the B200-native quantized MUL_MAT / MUL_MAT_ID path.
+ *
+ * This is the drop-in boundary below the ggml backend shell (libggml-b200.so, which implements the
+ * reference's ggml_backend_{reg,device,buffer_type,buffer}_i + ggml_backend_i vtables,
+ * /root/reference/ggml/src/ggml-backend-impl.h:17-230) and above the hand-written sm_100a kernels.
+ * Plain C: POD arguments, raw DEVICE pointers (unless a function says "host"), byte strides, enum
+ * ggml_type values passed as int, cudaStream_t passed inside the opaque context.  No ggml, torch or
+ * C++ types cross it, so the same library is bound by the C++ shell, by ctypes (tests, bench.py) and
+ * by any other FFI.
+ *
+ * Every entry point returns 0 on success or a negative B200_E* code; b200_last_error() gives the text.
+ * There is NO CPU fallback anywhere behind this header: without a CUDA device every compute call
+ * fails with B200_E_CUDA.
+ *
+ * Reference interfaces each entry replaces (file:line under /root/reference):
+ *   b200_quantize_row_q8_1   quantize_row_q8_1_ref            ggml/src/ggml-quants.c:260-293
+ *                            (= quantize_row_q8_1_generic      ggml/src/ggml-cpu/quants.c:49-51,
+ *                             = s390x VXE quantize_row_q8_1    ggml/src/ggml-cpu/arch/s390/quants.c:94-144;
+ *                             CUDA analogue quantize_row_q8_1_cuda ggml/src/ggml-cuda/quantize.cu:369-383)
+ *   b200_mul_mat             ggml_compute_forward_mul_mat      ggml/src/ggml-cpu/ggml-cpu.c:1241-1439
+ *                            (CUDA analogue ggml_cuda_mul_mat  ggml/src/ggml-cuda/ggml-cuda.cu:2537-2620)
+ *   b200_mul_mat_id          ggml_compute_forward_mul_mat_id   ggml/src/ggml-cpu/ggml-cpu.c:1521-1694
+ *                            (CUDA analogue ggml_cuda_mul_mat_id ggml/src/ggml-cuda/ggml-cuda.cu:2622-2778)
+ *   b200_mm_ids              mm_ids_helper                     ggml/src/ggml-cuda/mmid.cu:26-164
+ *   b200_rowsplit_*          ggml_backend_cuda_split_buffer_type + ggml_cuda_op_mul_mat row-split driver
+ *                                                              ggml/src/ggml-cuda/ggml-cuda.cu:855-1144,1801-2119
+ */
+#ifndef GGML_B200_H
+#define GGML_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#  define B200_API
+#else
+#  define B200_API __attribute__((visibility("default")))
+#endif
+
+#define B200_ABI_VERSION 1
+
+/* error codes */
+enum {
+    B200_OK            =  0,
+    B200_E_ARG         = -1,  /* bad argument / unsupported shape, type or stride        */
+    B200_E_CUDA        = -2,  /* a CUDA runtime call failed (text in b200_last_error())  */
+    B200_E_ALLOC       = -3,  /* device or host allocation failed                         */
+    B200_E_UNSUPPORTED = -4,  /* valid ggml op that this path does not implement          */
+    B200_E_NCCL        = -5,  /* NCCL call failed / library unavailable                   */
+};
+
+/* enum ggml_type values this path understands (ggml/include/ggml.h:389-432) */
+enum {
+    B200_TYPE_F32  = 0,
+    B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q8_0 = 8,
+    B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q6_K = 14,
+    B200_TYPE_I32  = 26,
+};
+
+/* A ggml tensor as the kernels see it: ne[] in elements, nb[] in bytes, ne[0] contiguous
+ * (ggml/include/ggml.h:660-700).  `data` is a device pointer. */
+typedef struct b200_tensor {
+    void *  data;
+    int32_t type;
+    int32_t _pad;
+    int64_t ne[4];
+    int64_t nb[4];
+} b200_tensor;
+
+typedef struct b200_ctx b200_ctx;   /* one device + one stream + scratch; not thread-safe, like a ggml_backend_t */
+
+/* ---- library / device ------------------------------------------------------------------------- */
+B200_API int          b200_abi_version(void);
+B200_API const char * b200_last_error(void);               /* thread-local text of the last failure        */
+B200_API int          b200_device_count(void);             /* number of CUDA devices with CC 10.x; 0 if none */
+B200_API int          b200_device_info(int device, char * name, size_t name_len,
+                                       size_t * free_bytes, size_t * total_bytes, int * cc_major, int * cc_minor,
+                                       int * sm_count);
+
+/* block geometry — ggml_blck_size / ggml_type_size / ggml_row_size (ggml/src/ggml.c:1263-1283) */
+B200_API int     b200_blck_size(int type);
+B200_API size_t  b200_type_size(int type);
+B200_API size_t  b200_row_size(int type, int64_t k);
+
+/* ---- context ----------------------------------------------------------------------------------- */
+/* stream == NULL: the context creates and owns a non-blocking stream; otherwise it borrows `stream`
+ * (a cudaStream_t) — this is how PyTorch's current stream is shared. */
+B200_API int   b200_ctx_create(int device, void * stream, b200_ctx ** out);
+B200_API void  b200_ctx_destroy(b200_ctx * ctx);
+B200_API void *b200_ctx_stream(b200_ctx * ctx);
+B200_API int   b200_ctx_synchronize(b200_ctx * ctx);
+/* number of kernels this context has launched since creation (bench.py's gpu_launches) */
+B200_API int64_t b200_ctx_launch_count(const b200_ctx * ctx);
+/* tuning knobs (also read once from the GGML_B200_* environment): name in
+ * {"force_generic","use_tc","max_gemv_cols","pdl"}; returns the previous value or B200_E_ARG */
+B200_API int   b200_ctx_set_option(b200_ctx * ctx, const char * name, int value);
+
+/* ---- (1) activation quantizer ------------------------------------------------------------------- */
+/* x: nrows rows of k f32 (row stride x_row_stride_bytes); y: nrows * (k/32) block_q8_1
+ * {fp16 d; fp16 s; int8 qs[32]} = 36 B each (ggml/src/ggml-common.h:248-259), rows packed.
+ * Bit-exact against quantize_row_q8_1_ref.  k % 32 == 0. */
+B200_API int b200_quantize_row_q8_1(b200_ctx * ctx, const float * x, int64_t x_row_stride_bytes,
+                                    void * y, int64_t k, int64_t nrows);
+
+/* ---- (2)(3) MUL_MAT ----------------------------------------------------------------------------- */
+/* dst[m, n, ne12, ne13] = src0[k, m, ne02, ne03] (Q4_0|Q8_0|Q4_K|Q6_K) x src1[k, n, ne12, ne13] (F32),
+ * broadcast i02 = i12 / (ne12/ne02), i03 = i13 / (ne13/ne03)  (ggml/src/ggml.c:3232-3255).
+ * src0 rows must be whole blocks with nb[0] == type_size; src1 needs nb[0] == 4; dst must be contiguous f32.
+ * n <= 8 per batch runs the GEMV family, larger n the tensor-core GEMM. */
+B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+/* returns 1 if b200_mul_mat accepts this triple, 0 if not (used by supports_op) — no device needed */
+B200_API int b200_mul_mat_supported(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+
+/* ---- (4) MUL_MAT_ID ----------------------------------------------------------------------------- */
+/* as[k, m, n_expert], b[k, n_used|1, n_tokens] F32, ids[n_used, n_tokens] I32 (may be a strided view),
+ * c[m, n_used, n_tokens] F32:  c[:, e, t] = as[:, :, ids[e,t]] . b[:, e % b.ne[1], t]  (ggml/src/ggml.c:3279-3315) */
+B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids,
+                             const b200_tensor * c);
+B200_API int b200_mul_mat_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids,
+                                       const b200_tensor * c);
+
+/* expert gather helper: from ids[n_used, n_tokens] (row stride ids_nb1 bytes) build
+ *   ids_src1[n_used*n_tokens]  : for sorted position p, the flat (token*n_used + slot) pair index
+ *   expert_bounds[n_expert+1]  : sorted positions [bounds[e], bounds[e+1]) belong to expert e
+ * Stable within an expert (token-major order), like mm_ids_helper (ggml/src/ggml-cuda/mmid.cu:26-116). */
+B200_API int b200_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_nb1, int n_expert, int n_used, int64_t n_tokens,
+                         int32_t * ids_src1, int32_t * expert_bounds);
+
+/* ---- host-buffer convenience (the e2e path: H2D + compute + D2H inside the call) ---------------- */
+/* Device-resident weights handle: uploads `nbytes` of quantized rows once. */
+B200_API int  b200_weights_upload(b200_ctx * ctx, int type, const void * host_rows, int64_t k, int64_t m, void ** dev_out);
+B200_API void b200_weights_free(b200_ctx * ctx, void * dev);
+/* y_host[m, n] = W (device, from b200_weights_upload) x x_host[k, n]; copies x H2D and y D2H on the
+ * context's stream and synchronizes.  x_host / y_host should be pinned for full speed. */
+B200_API int  b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, int64_t k,
+                                const float * x_host, int64_t n, float * y_host);
+
+/* ---- raw device memory (used by the backend shell's buffers and by ctypes callers without torch) -- */
+B200_API int  b200_malloc(int device, size_t nbytes, void ** out);
+B200_API int  b200_free(int device, void * ptr);
+B200_API int  b200_memcpy_h2d(b200_ctx * ctx, void * dst_dev, const void * src_host, size_t nbytes);   /* synchronous */
+B200_API int  b200_memcpy_d2h(b200_ctx * ctx, void * dst_host, const void * src_dev, size_t nbytes);   /* synchronous */
+B200_API int  b200_memcpy_d2d(b200_ctx * ctx, void * dst_dev, const void * src_dev, size_t nbytes);    /* synchronous; any two devices */
+B200_API int  b200_memset(b200_ctx * ctx, void * dst_dev, int value, size_t nbytes);                   /* synchronous */
+/* asynchronous on the context's stream; kind: 0 = host->device, 1 = device->host, 2 = device->device */
+B200_API int  b200_memcpy_async(b200_ctx * ctx, void * dst, const void * src, size_t nbytes, int kind);
+
+/* ---- row-split across GPUs (single process, one NCCL communicator per device) -------------------- */
+typedef struct b200_rowsplit b200_rowsplit;
+/* devices[n_dev]; split[n_dev] cumulative-free fractions (NULL = even).  Cut points are rounded down to
+ * `B200_ROWSPLIT_ROUND` rows like get_row_split (ggml/src/ggml-cuda/ggml-cuda.cu:855-881). */
+#define B200_ROWSPLIT_ROUND 128
+B200_API int  b200_rowsplit_create(const int * devices, int n_dev, const float * split, b200_rowsplit ** out);
+B200_API void b200_rowsplit_destroy(b200_rowsplit * rs);
+B200_API int  b200_rowsplit_n_dev(const b200_rowsplit * rs);
+B200_API int  b200_rowsplit_rows(const b200_rowsplit * rs, int64_t m, int idx, int64_t * row_lo, int64_t * row_hi);
+/* scatter host rows of one [k, m] weight matrix to the devices; returns a handle */
+typedef struct b200_split_weights b200_split_weights;
+B200_API int  b200_rowsplit_upload(b200_rowsplit * rs, int type, const void * host_rows, int64_t k, int64_t m,
+                                   b200_split_weights ** out);
+B200_API void b200_rowsplit_weights_free(b200_rowsplit * rs, b200_split_weights * w);
+/* y[m, n] on every device (y_dev[i] is device i's full [m, n] f32 output) = W x x, where x_dev[i] is device i's
+ * replica of x[k, n] f32.  Each device computes its row shard, then an all-gather of the row slices
+ * (NCCL over NVLink, or direct peer stores when `mode` == 1) fills every y_dev[i].  Asynchronous on the
+ * per-device streams; b200_rowsplit_synchronize waits for all. */
+B200_API int  b200_rowsplit_mul_mat(b200_rowsplit * rs, const b200_split_weights * w, float * const * x_dev, int64_t n,
+                                    float * const * y_dev, int mode);
+B200_API int  b200_rowsplit_synchronize(b200_rowsplit * rs);
+B200_API b200_ctx * b200_rowsplit_ctx(b200_rowsplit * rs, int idx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGML_B200_H */

@@ -1,0 +1,467 @@
+// abi.cu — the extern "C" entry points declared in include/ggml_b200.h: context, argument validation and dispatch
+// onto the kernels (quantize.cu, mmvq.cu, mmid.cu, mmq_tc.cu).  No compute happens on the host and there is no CPU
+// fallback: if CUDA is unavailable every call returns B200_E_CUDA.
+#include "mm_problem.cuh"
+#include "quantize.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+// kernels' host launchers (other TUs)
+int    b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles);
+int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles);
+size_t b200_gemv_q4k_smem(int nc, int64_t k);
+int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
+                          int32_t * ids_src1, int32_t * expert_bounds);
+int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
+int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_cols_total);
+
+// ---- errors ---------------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+void b200_set_error(const char * fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" {
+
+int          b200_abi_version(void) { return B200_ABI_VERSION; }
+const char * b200_last_error(void)  { return g_err; }
+
+int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int ok = 0;
+    for (int i = 0; i < n; ++i) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ok++;
+        else break;    // devices are exposed as a dense prefix 0..ok-1
+    }
+    return ok;
+}
+
+int b200_device_info(int device, char * name, size_t name_len, size_t * free_bytes, size_t * total_bytes, int * cc_major,
+                     int * cc_minor, int * sm_count) {
+    cudaDeviceProp prop;
+    B200_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (name && name_len) { strncpy(name, prop.name, name_len - 1); name[name_len - 1] = 0; }
+    if (cc_major) *cc_major = prop.major;
+    if (cc_minor) *cc_minor = prop.minor;
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (free_bytes || total_bytes) {
+        size_t f = 0, t = 0;
+        B200_CUDA_TRY(cudaSetDevice(device));
+        B200_CUDA_TRY(cudaMemGetInfo(&f, &t));
+        if (free_bytes) *free_bytes = f;
+        if (total_bytes) *total_bytes = t;
+    }
+    return B200_OK;
+}
+
+int    b200_blck_size(int type) { return b200_blck(type); }
+size_t b200_type_size(int type) { return (size_t) b200_tsize(type); }
+size_t b200_row_size(int type, int64_t k) {
+    const int b = b200_blck(type);
+    return b ? (size_t) (k / b) * (size_t) b200_tsize(type) : 0;
+}
+
+// ---- context ------------------------------------------------------------------------------------------------------
+static int env_int(const char * name, int dflt) {
+    const char * v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
+    if (!out) { b200_set_error("ctx_create: out is NULL"); return B200_E_ARG; }
+    *out = nullptr;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    b200_ctx * ctx = (b200_ctx *) calloc(1, sizeof(b200_ctx));
+    if (!ctx) { b200_set_error("ctx_create: out of host memory"); return B200_E_ALLOC; }
+    ctx->device = device;
+    cudaDeviceProp prop;
+    cudaError_t err = cudaGetDeviceProperties(&prop, device);
+    if (err != cudaSuccess) { free(ctx); b200_set_error("cudaGetDeviceProperties: %s", cudaGetErrorString(err)); return B200_E_CUDA; }
+    if (prop.major != 10) {
+        free(ctx);
+        b200_set_error("device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
+        return B200_E_UNSUPPORTED;
+    }
+    ctx->sm_count   = prop.multiProcessorCount;
+    ctx->cc_major   = prop.major;
+    ctx->cc_minor   = prop.minor;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    if (stream) {
+        ctx->stream = (cudaStream_t) stream;
+    } else {
+        err = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+        if (err != cudaSuccess) { free(ctx); b200_set_error("cudaStreamCreate: %s", cudaGetErrorString(err)); return B200_E_CUDA; }
+        ctx->owns_stream = true;
+    }
+    ctx->force_generic = env_int("GGML_B200_FORCE_GENERIC", 0);
+    ctx->use_tc        = env_int("GGML_B200_USE_TC", 1);
+    ctx->max_gemv_cols = env_int("GGML_B200_MAX_GEMV_COLS", 8);
+    ctx->pdl           = env_int("GGML_B200_PDL", 1);
+    ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
+    if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
+    if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
+    *out = ctx;
+    return B200_OK;
+}
+
+void b200_ctx_destroy(b200_ctx * ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->dev_x) cudaFree(ctx->dev_x);
+    if (ctx->dev_y) cudaFree(ctx->dev_y);
+    if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
+    free(ctx);
+}
+
+void *  b200_ctx_stream(b200_ctx * ctx) { return ctx ? (void *) ctx->stream : nullptr; }
+int64_t b200_ctx_launch_count(const b200_ctx * ctx) { return ctx ? ctx->launches : 0; }
+
+int b200_ctx_synchronize(b200_ctx * ctx) {
+    if (!ctx) { b200_set_error("ctx is NULL"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
+    if (!ctx || !name) return B200_E_ARG;
+    int * slot = nullptr;
+    if      (!strcmp(name, "force_generic")) slot = &ctx->force_generic;
+    else if (!strcmp(name, "use_tc"))        slot = &ctx->use_tc;
+    else if (!strcmp(name, "max_gemv_cols")) slot = &ctx->max_gemv_cols;
+    else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
+    else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
+    if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
+    const int prev = *slot;
+    *slot = value;
+    if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
+    if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
+    return prev;
+}
+
+}  // extern "C"
+
+int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes) {
+    if (nbytes <= ctx->ws_size) return B200_OK;
+    // the scratch may still be read by kernels in flight on this stream
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (ctx->ws) { cudaFree(ctx->ws); ctx->ws = nullptr; ctx->ws_size = 0; }
+    const size_t want = (nbytes + (size_t) (1 << 20) - 1) & ~((size_t) (1 << 20) - 1);
+    cudaError_t err = cudaMalloc(&ctx->ws, want);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        b200_set_error("scratch allocation of %zu B failed: %s", want, cudaGetErrorString(err));
+        return B200_E_ALLOC;
+    }
+    ctx->ws_size = want;
+    return B200_OK;
+}
+
+// ---- validation -----------------------------------------------------------------------------------------------------
+static bool is_weight_type(int t) {
+    return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K;
+}
+
+static bool f32_contiguous(const b200_tensor * t) {
+    return t->nb[0] == 4 && t->nb[1] == t->ne[0] * 4 && t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
+}
+
+static const char * check_mul_mat(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    if (!a || !b || !d) return "NULL tensor";
+    if (!is_weight_type(a->type)) return "src0 type is not Q4_0/Q8_0/Q4_K/Q6_K";
+    if (b->type != B200_TYPE_F32 || d->type != B200_TYPE_F32) return "src1/dst must be F32";
+    const int64_t k = a->ne[0];
+    if (k <= 0 || k % b200_blck(a->type) != 0) return "ne00 is not a whole number of blocks";
+    if (b->ne[0] != k) return "src1->ne[0] != src0->ne[0]";
+    if (d->ne[0] != a->ne[1] || d->ne[1] != b->ne[1] || d->ne[2] != b->ne[2] || d->ne[3] != b->ne[3]) return "dst shape mismatch";
+    if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] != 0 || b->ne[3] % a->ne[3] != 0) return "batch dims do not broadcast";
+    if (a->nb[0] != (int64_t) b200_tsize(a->type)) return "src0 is transposed/permuted in dim 0";
+    if (a->nb[1] % 2 != 0 || a->nb[2] % 2 != 0 || a->nb[3] % 2 != 0) return "src0 strides not 2-byte aligned";
+    if (b->nb[0] != 4) return "src1 is not contiguous in dim 0";
+    if (b->nb[1] % 4 != 0 || b->nb[2] % 4 != 0 || b->nb[3] % 4 != 0) return "src1 strides not 4-byte aligned";
+    if (!f32_contiguous(d)) return "dst is not contiguous";
+    if (k > (int64_t) 1 << 24) return "k too large";
+    return nullptr;
+}
+
+static const char * check_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * c) {
+    if (!as || !b || !ids || !c) return "NULL tensor";
+    if (!is_weight_type(as->type)) return "as type is not Q4_0/Q8_0/Q4_K/Q6_K";
+    if (b->type != B200_TYPE_F32 || c->type != B200_TYPE_F32 || ids->type != B200_TYPE_I32) return "b/c must be F32 and ids I32";
+    const int64_t k = as->ne[0];
+    if (k <= 0 || k % b200_blck(as->type) != 0) return "ne00 is not a whole number of blocks";
+    if (as->ne[3] != 1 || b->ne[3] != 1 || c->ne[3] != 1 || ids->ne[2] != 1 || ids->ne[3] != 1) return "4-D MUL_MAT_ID";
+    if (b->ne[0] != k) return "b->ne[0] != as->ne[0]";
+    const int64_t n_used = ids->ne[0], n_tokens = ids->ne[1];
+    if (b->ne[2] != n_tokens) return "b->ne[2] != n_tokens";
+    if (b->ne[1] <= 0 || n_used % b->ne[1] != 0) return "n_used is not a multiple of b->ne[1]";   // ggml.c:3305
+    if (c->ne[0] != as->ne[1] || c->ne[1] != n_used || c->ne[2] != n_tokens) return "c shape mismatch";
+    if (as->nb[0] != (int64_t) b200_tsize(as->type) || as->nb[1] % 2 != 0 || as->nb[2] % 2 != 0) return "as strides";
+    if (b->nb[0] != 4 || b->nb[1] % 4 != 0 || b->nb[2] % 4 != 0) return "b strides";
+    if (ids->nb[0] != 4 || ids->nb[1] % 4 != 0) return "ids strides";
+    if (!f32_contiguous(c)) return "c is not contiguous";
+    if (n_used > 1024 || as->ne[2] > 65535) return "too many experts";
+    return nullptr;
+}
+
+static bool aligned16(const void * p, int64_t a, int64_t b, int64_t c) {
+    return (((uintptr_t) p | (uintptr_t) a | (uintptr_t) b | (uintptr_t) c) & 15) == 0;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// quantize src1 [k, ne1, ne2, ne3] into planes inside the scratch (after `reserve_extra` bytes kept for the caller)
+static int quantize_into_ws(b200_ctx * ctx, const b200_tensor * b, size_t extra, q8_planes * out, uint8_t ** extra_ptr) {
+    const int64_t k = b->ne[0];
+    const int64_t ncols = b->ne[1] * b->ne[2] * b->ne[3];
+    const size_t qs_bytes = align_up((size_t) ncols * k, 256);
+    const size_t ds_bytes = align_up((size_t) ncols * (k / 32) * sizeof(half2), 256);
+    const int rc = b200_ctx_reserve(ctx, qs_bytes + ds_bytes + align_up(extra, 256) + 256);
+    if (rc) return rc;
+    uint8_t * base = (uint8_t *) ctx->ws;
+    int8_t * qs = (int8_t *) base;
+    half2 *  ds = (half2 *) (base + qs_bytes);
+    if (extra_ptr) *extra_ptr = base + qs_bytes + ds_bytes;
+    out->qs = qs; out->ds = ds; out->k = k;
+    return b200_launch_quantize_planes(ctx, (const float *) b->data, k, b->ne[1], b->ne[2], b->ne[3], b->nb[1], b->nb[2], b->nb[3], qs, ds);
+}
+
+extern "C" {
+
+// ---- (1) ----------------------------------------------------------------------------------------------------------
+int b200_quantize_row_q8_1(b200_ctx * ctx, const float * x, int64_t x_row_stride_bytes, void * y, int64_t k, int64_t nrows) {
+    if (!ctx || !x || !y) { b200_set_error("quantize_row_q8_1: NULL argument"); return B200_E_ARG; }
+    if (x_row_stride_bytes % 4 != 0) { b200_set_error("quantize_row_q8_1: row stride must be a multiple of 4"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    return b200_launch_quantize_aos(ctx, x, k, nrows, 1, 1, x_row_stride_bytes, x_row_stride_bytes * nrows, x_row_stride_bytes * nrows, y);
+}
+
+// ---- (2)(3) -------------------------------------------------------------------------------------------------------
+int b200_mul_mat_supported(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    if (check_mul_mat(a, b, d)) return 0;
+    const int64_t batches = b->ne[2] * b->ne[3];
+    const int64_t tiles   = batches * ((b->ne[1] + 7) / 8);
+    return tiles <= 65535 ? 1 : 0;
+}
+
+int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    if (!ctx) { b200_set_error("mul_mat: ctx is NULL"); return B200_E_ARG; }
+    if (const char * why = check_mul_mat(a, b, d)) { b200_set_error("mul_mat: %s", why); return B200_E_ARG; }
+    const int64_t k = a->ne[0], m = a->ne[1], n = b->ne[1];
+    const int64_t batches = b->ne[2] * b->ne[3];
+    if (m == 0 || n == 0 || batches == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+
+    mm_problem P = {};
+    P.W = (const uint8_t *) a->data; P.nb01 = a->nb[1]; P.nb02 = a->nb[2]; P.nb03 = a->nb[3];
+    P.m = m; P.k = k;
+    P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = b->nb[3];
+    P.ne11 = n; P.ne12 = b->ne[2]; P.ne13 = b->ne[3];
+    P.r2 = b->ne[2] / a->ne[2]; P.r3 = b->ne[3] / a->ne[3];
+    P.Y = (float *) d->data;
+    P.mode = MM_PLAIN;
+
+    if (n <= ctx->max_gemv_cols) {
+        if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
+            aligned16(a->data, a->nb[1], a->nb[2], a->nb[3]) && aligned16(b->data, b->nb[1], b->nb[2], b->nb[3]) &&
+            b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
+            return b200_launch_gemv_q4k(ctx, P, (int) n, batches);
+        }
+        int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
+        if (rc) return rc;
+        return b200_launch_gemv_generic(ctx, a->type, P, (int) n, batches);
+    }
+
+    int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
+    if (rc) return rc;
+    if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
+        return b200_launch_gemm_tc(ctx, a->type, P, n * batches);
+    }
+    const int64_t tiles = batches * ((n + 7) / 8);
+    return b200_launch_gemv_generic(ctx, a->type, P, 8, tiles);
+}
+
+// ---- (4) ----------------------------------------------------------------------------------------------------------
+int b200_mul_mat_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * c) {
+    return check_mul_mat_id(as, b, ids, c) ? 0 : 1;
+}
+
+int b200_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_nb1, int n_expert, int n_used, int64_t n_tokens,
+                int32_t * ids_src1, int32_t * expert_bounds) {
+    if (!ctx || !ids || !ids_src1 || !expert_bounds || ids_nb1 % 4 != 0) { b200_set_error("mm_ids: bad argument"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    return b200_launch_mm_ids(ctx, ids, ids_nb1 / 4, n_expert, n_used, n_tokens, ids_src1, expert_bounds);
+}
+
+int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * c) {
+    if (!ctx) { b200_set_error("mul_mat_id: ctx is NULL"); return B200_E_ARG; }
+    if (const char * why = check_mul_mat_id(as, b, ids, c)) { b200_set_error("mul_mat_id: %s", why); return B200_E_ARG; }
+    const int64_t k = as->ne[0], m = as->ne[1];
+    const int     n_expert = (int) as->ne[2];
+    const int     n_used   = (int) ids->ne[0];
+    const int64_t n_tokens = ids->ne[1];
+    const int64_t n_pairs  = n_tokens * n_used;
+    if (m == 0 || n_pairs == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+
+    mm_problem P = {};
+    P.W = (const uint8_t *) as->data; P.nb01 = as->nb[1]; P.nb02 = as->nb[2]; P.nb03 = 0;
+    P.m = m; P.k = k;
+    P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = 0;
+    P.ne11 = b->ne[1]; P.ne12 = n_tokens; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+    P.Y = (float *) c->data;
+    P.ids = (const int32_t *) ids->data; P.ids_stride = ids->nb[1] / 4;
+    P.n_used = n_used; P.n_expert = n_expert;
+
+    if (n_tokens <= ctx->max_gemv_cols && n_pairs <= 65535) {
+        // decode: every (token, slot) pair is a GEMV against the expert the kernel looks up itself
+        P.mode = MM_ID_PAIRS;
+        if (as->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant &&
+            aligned16(as->data, as->nb[1], as->nb[2], 0) && aligned16(b->data, b->nb[1], b->nb[2], 0) &&
+            b200_gemv_q4k_smem(1, k) <= ctx->smem_optin) {
+            return b200_launch_gemv_q4k(ctx, P, 1, n_pairs);
+        }
+        int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
+        if (rc) return rc;
+        return b200_launch_gemv_generic(ctx, as->type, P, 1, n_pairs);
+    }
+
+    // prefill: gather the pairs by expert on the device, then column tiles that never straddle two experts
+    uint8_t * extra = nullptr;
+    const size_t extra_bytes = (size_t) (n_pairs + n_expert + 1) * sizeof(int32_t);
+    int rc = quantize_into_ws(ctx, b, extra_bytes, &P.act, &extra);
+    if (rc) return rc;
+    int32_t * ids_src1 = (int32_t *) extra;
+    int32_t * bounds   = ids_src1 + n_pairs;
+    rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
+    if (rc) return rc;
+    P.mode = MM_ID_SORTED; P.ids_src1 = ids_src1; P.expert_bounds = bounds;
+    if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, as->type, P)) {
+        return b200_launch_gemm_tc(ctx, as->type, P, n_pairs);
+    }
+    const int64_t tiles = (n_pairs + 7) / 8 + n_expert;
+    if (tiles > 65535) { b200_set_error("mul_mat_id: too many column tiles"); return B200_E_UNSUPPORTED; }
+    return b200_launch_gemv_generic(ctx, as->type, P, 8, tiles);
+}
+
+// ---- raw memory -----------------------------------------------------------------------------------------------------
+int b200_malloc(int device, size_t nbytes, void ** out) {
+    if (!out) return B200_E_ARG;
+    *out = nullptr;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    cudaError_t err = cudaMalloc(out, nbytes);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        b200_set_error("cudaMalloc(%zu) on device %d: %s", nbytes, device, cudaGetErrorString(err));
+        return B200_E_ALLOC;
+    }
+    return B200_OK;
+}
+
+int b200_free(int device, void * ptr) {
+    if (!ptr) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    B200_CUDA_TRY(cudaFree(ptr));
+    return B200_OK;
+}
+
+int b200_memcpy_h2d(b200_ctx * ctx, void * dst_dev, const void * src_host, size_t nbytes) {
+    if (!ctx) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaMemcpyAsync(dst_dev, src_host, nbytes, cudaMemcpyHostToDevice, ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_memcpy_d2h(b200_ctx * ctx, void * dst_host, const void * src_dev, size_t nbytes) {
+    if (!ctx) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaMemcpyAsync(dst_host, src_dev, nbytes, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_memcpy_d2d(b200_ctx * ctx, void * dst_dev, const void * src_dev, size_t nbytes) {
+    if (!ctx) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaMemcpyAsync(dst_dev, src_dev, nbytes, cudaMemcpyDefault, ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_memset(b200_ctx * ctx, void * dst_dev, int value, size_t nbytes) {
+    if (!ctx) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaMemsetAsync(dst_dev, value, nbytes, ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+int b200_memcpy_async(b200_ctx * ctx, void * dst, const void * src, size_t nbytes, int kind) {
+    if (!ctx || kind < 0 || kind > 2) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const cudaMemcpyKind kk = kind == 0 ? cudaMemcpyHostToDevice : kind == 1 ? cudaMemcpyDeviceToHost : cudaMemcpyDefault;
+    B200_CUDA_TRY(cudaMemcpyAsync(dst, src, nbytes, kk, ctx->stream));
+    return B200_OK;
+}
+
+// ---- host-buffer convenience ------------------------------------------------------------------------------------------
+int b200_weights_upload(b200_ctx * ctx, int type, const void * host_rows, int64_t k, int64_t m, void ** dev_out) {
+    if (!ctx || !host_rows || !dev_out || !is_weight_type(type) || k % b200_blck(type) != 0) {
+        b200_set_error("weights_upload: bad argument");
+        return B200_E_ARG;
+    }
+    const size_t nbytes = b200_row_size(type, k) * (size_t) m;
+    int rc = b200_malloc(ctx->device, nbytes + 512, dev_out);
+    if (rc) return rc;
+    rc = b200_memcpy_h2d(ctx, *dev_out, host_rows, nbytes);
+    if (rc) { b200_free(ctx->device, *dev_out); *dev_out = nullptr; }
+    return rc;
+}
+
+void b200_weights_free(b200_ctx * ctx, void * dev) { if (ctx) b200_free(ctx->device, dev); }
+
+static int grow(b200_ctx * ctx, void ** buf, size_t * have, size_t want) {
+    if (want <= *have) return B200_OK;
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
+    cudaError_t err = cudaMalloc(buf, want);
+    if (err != cudaSuccess) { cudaGetLastError(); b200_set_error("staging allocation failed: %s", cudaGetErrorString(err)); return B200_E_ALLOC; }
+    *have = want;
+    return B200_OK;
+}
+
+int b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, int64_t k, const float * x_host, int64_t n,
+                      float * y_host) {
+    if (!ctx || !w_dev || !x_host || !y_host || !is_weight_type(type)) { b200_set_error("mul_mat_host: bad argument"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const size_t xb = (size_t) k * n * 4, yb = (size_t) m * n * 4;
+    int rc = grow(ctx, &ctx->dev_x, &ctx->dev_x_size, xb); if (rc) return rc;
+    rc     = grow(ctx, &ctx->dev_y, &ctx->dev_y_size, yb); if (rc) return rc;
+    B200_CUDA_TRY(cudaMemcpyAsync(ctx->dev_x, x_host, xb, cudaMemcpyHostToDevice, ctx->stream));
+    b200_tensor a = {}, b = {}, d = {};
+    a.data = (void *) w_dev; a.type = type; a.ne[0] = k; a.ne[1] = m; a.ne[2] = a.ne[3] = 1;
+    a.nb[0] = (int64_t) b200_tsize(type); a.nb[1] = (int64_t) b200_row_size(type, k); a.nb[2] = a.nb[3] = a.nb[1] * m;
+    b.data = ctx->dev_x; b.type = B200_TYPE_F32; b.ne[0] = k; b.ne[1] = n; b.ne[2] = b.ne[3] = 1;
+    b.nb[0] = 4; b.nb[1] = k * 4; b.nb[2] = b.nb[3] = k * 4 * n;
+    d.data = ctx->dev_y; d.type = B200_TYPE_F32; d.ne[0] = m; d.ne[1] = n; d.ne[2] = d.ne[3] = 1;
+    d.nb[0] = 4; d.nb[1] = m * 4; d.nb[2] = d.nb[3] = m * 4 * n;
+    rc = b200_mul_mat(ctx, &a, &b, &d);
+    if (rc) return rc;
+    B200_CUDA_TRY(cudaMemcpyAsync(y_host, ctx->dev_y, yb, cudaMemcpyDeviceToHost, ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,126 @@
+// common.cuh — shared device/host helpers for the B200 quantized MUL_MAT path.
+//
+// Block layouts are the reference's on-disk / in-memory formats and are parsed bit-for-bit
+// (/root/reference/ggml/src/ggml-common.h:184-366):
+//   block_q4_0 {fp16 d; u8 qs[16]}                                   18 B / 32 weights
+//   block_q8_0 {fp16 d; i8 qs[32]}                                   34 B / 32
+//   block_q8_1 {fp16 d; fp16 s; i8 qs[32]}                           36 B / 32   (activations)
+//   block_q4_K {fp16 d; fp16 dmin; u8 scales[12]; u8 qs[128]}       144 B / 256
+//   block_q6_K {u8 ql[128]; u8 qh[64]; i8 scales[16]; fp16 d}       210 B / 256
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/ggml_b200.h"
+
+#define B200_WARP 32
+
+// ---- block geometry -----------------------------------------------------------------------------
+#define QK_SMALL 32
+#define QK_K     256
+#define SZ_Q4_0  18
+#define SZ_Q8_0  34
+#define SZ_Q8_1  36
+#define SZ_Q4_K  144
+#define SZ_Q6_K  210
+
+__host__ __device__ constexpr int b200_blck(int type) {
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K) ? QK_K
+         : (type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q8_1) ? QK_SMALL
+         : (type == B200_TYPE_F32 || type == B200_TYPE_I32) ? 1 : 0;
+}
+__host__ __device__ constexpr int b200_tsize(int type) {
+    return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : type == B200_TYPE_Q8_1 ? SZ_Q8_1
+         : type == B200_TYPE_Q4_K ? SZ_Q4_K : type == B200_TYPE_Q6_K ? SZ_Q6_K
+         : (type == B200_TYPE_F32 || type == B200_TYPE_I32) ? 4 : 0;
+}
+
+// ---- internal activation format ("q8 planes") -----------------------------------------------------
+// The GEMV / GEMM kernels consume activations quantized exactly like block_q8_1 (same d, s, qs values as
+// quantize_row_q8_1_ref) but stored as two planes so that 16-byte chunks of qs are 16-byte aligned:
+//   qs : int8  [ncols][k]       (column stride k bytes)
+//   ds : half2 [ncols][k/32]    (d, s) per 32-block
+struct q8_planes {
+    const int8_t * qs;
+    const half2 *  ds;
+    int64_t        k;
+};
+
+// ---- host-side error plumbing ---------------------------------------------------------------------
+void b200_set_error(const char * fmt, ...);
+#define B200_CUDA_TRY(expr)                                                                          \
+    do {                                                                                             \
+        cudaError_t err__ = (expr);                                                                  \
+        if (err__ != cudaSuccess) {                                                                  \
+            b200_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__), __FILE__, __LINE__); \
+            return B200_E_CUDA;                                                                      \
+        }                                                                                            \
+    } while (0)
+
+// ---- context (definition shared by the TUs; opaque to callers) -------------------------------------
+struct b200_ctx {
+    int          device;
+    cudaStream_t stream;
+    bool         owns_stream;
+    int          sm_count;
+    int          cc_major, cc_minor;
+    size_t       smem_optin;      // max dynamic shared memory per block
+    // grow-only scratch (activation planes, ids helper arrays, split-K partials)
+    void *       ws;
+    size_t       ws_size;
+    // pinned staging for the host-buffer convenience path
+    void *       dev_x;   size_t dev_x_size;
+    void *       dev_y;   size_t dev_y_size;
+    int64_t      launches;
+    // options
+    int          force_generic;   // 1: never use the specialised GEMV kernels
+    int          use_tc;          // 1: n > max_gemv_cols goes to the tcgen05 GEMM (when the shape allows)
+    int          max_gemv_cols;   // columns per batch handled by the GEMV family (<= 8)
+    int          pdl;             // programmatic dependent launch for back-to-back GEMVs
+    int          fuse_quant;      // 1: GEMV quantizes activations in its prologue (no separate launch)
+};
+
+int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes);   // ensures ctx->ws_size >= nbytes
+
+// ---- device helpers ---------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// 32-bit load from a 2-byte aligned address (fields of block_q4_0/q8_0/q6_K are only 2-byte aligned)
+__device__ __forceinline__ uint32_t ld_b2(const uint8_t * p) {
+    const uint16_t * q = reinterpret_cast<const uint16_t *>(p);
+    return (uint32_t) __ldg(q) | ((uint32_t) __ldg(q + 1) << 16);
+}
+__device__ __forceinline__ float ld_half(const uint8_t * p) {
+    return __half2float(__ushort_as_half(__ldg(reinterpret_cast<const uint16_t *>(p))));
+}
+
+// streaming 128-bit load that does not allocate in L1 (weights are read exactly once)
+__device__ __forceinline__ uint4 ld_stream_u4(const void * p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+// get_scale_min_k4 (ggml/src/ggml-quants.c:818-825) on the 12 scale bytes held as three little-endian words
+__device__ __forceinline__ void q4k_scale_min(int j, uint32_t s0, uint32_t s1, uint32_t s2, int & sc, int & mn) {
+    if (j < 4) {
+        sc = (s0 >> (8 * j)) & 63;
+        mn = (s1 >> (8 * j)) & 63;
+    } else {
+        const int jj = j - 4;
+        sc = ((s2 >> (8 * jj)) & 0xF)       | (((s0 >> (8 * jj + 6)) & 3) << 4);
+        mn = ((s2 >> (8 * jj + 4)) & 0xF)   | (((s1 >> (8 * jj + 6)) & 3) << 4);
+    }
+}
+
+// position (in 16-byte chunks) of activation chunk t inside the swizzled shared-memory copy of one column:
+// chunks {4g+h} and {4g+h+2} of consecutive superblocks land in distinct 16-byte bank groups
+__device__ __forceinline__ int act_swz(int t) { return t ^ (((t >> 3) & 1) << 1); }

@@ -1,0 +1,372 @@
+// mmvq.cu — the decode path: memory-bound GEMV family for 1..8 activation columns.
+//
+// Replaces the hot loop of ggml_compute_forward_mul_mat[_id] (/root/reference/ggml/src/ggml-cpu/ggml-cpu.c:1151-1239,
+// 1443-1511) — vec_dot(W row, quantized X column) for every (row, column) — with integer dot products against
+// Q8_1-quantized activations (same d/qs as quantize_row_q8_1_ref).  The per-block algebra is
+//   Q4_0: d * (d8 * sum((nib)*q8) - 8 * s8)                      (block_q4_0, ggml-common.h:184-189)
+//   Q8_0: d * d8 * sum(q*q8)                                       (block_q8_0, :241-246)
+//   Q4_K: d * sc_j * d8 * sum(nib*q8) - dmin * m_j * d8 * sum(q8)  (block_q4_K, :317-328; scales ggml-quants.c:818-825)
+//   Q6_K: d * d8 * (sc_2j * sum_lo((q-32)*q8) + sc_2j+1 * sum_hi)  (block_q6_K, :352-358; layout ggml-quants.c:1877-1906)
+//
+// Two kernels:
+//   gemv_generic  — any of the four types, any strides / batch / MUL_MAT_ID mode, activations pre-quantized into
+//                   global planes.  One warp per weight row, one 32-weight unit per lane per step.
+//   gemv_q4k      — the Q4_K fast path: persistent CTAs (one per SM), activations quantized IN the prologue into
+//                   swizzled shared memory (no separate launch, no q8 round trip through HBM), weights streamed with
+//                   coalesced 128-bit no-allocate loads (8 lanes per 144-byte superblock), d/dmin/6-bit scales applied
+//                   in registers, warp-shuffle reduction.
+#include "mm_problem.cuh"
+#include "quantize.cuh"
+
+// ------------------------------------------------------------------------------------------------------------------
+// generic kernel
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct act_unit {      // one 32-value activation block of one column
+    int   a[8];
+    float d, s;
+};
+
+__device__ __forceinline__ act_unit load_act(const q8_planes & A, int64_t col, int64_t ib) {
+    act_unit u;
+    const uint4 * q = reinterpret_cast<const uint4 *>(A.qs + col * A.k + ib * 32);
+    const uint4 q0 = __ldg(q), q1 = __ldg(q + 1);
+    u.a[0] = q0.x; u.a[1] = q0.y; u.a[2] = q0.z; u.a[3] = q0.w;
+    u.a[4] = q1.x; u.a[5] = q1.y; u.a[6] = q1.z; u.a[7] = q1.w;
+    const float2 ds = __half22float2(__ldg(A.ds + col * (A.k >> 5) + ib));
+    u.d = ds.x; u.s = ds.y;
+    return u;
+}
+
+// weights of one 32-element unit, unpacked to int8x4 words + the floats needed to scale the integer sums
+template <int TYPE> struct w_unit;
+
+template <> struct w_unit<B200_TYPE_Q4_0> {
+    int lo[4], hi[4]; float d;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint8_t * bp = row + ib * SZ_Q4_0;
+        d = ld_half(bp);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t v = ld_b2(bp + 2 + 4 * i);
+            lo[i] = v & 0x0F0F0F0Fu;
+            hi[i] = (v >> 4) & 0x0F0F0F0Fu;
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sumi = __dp4a(lo[i], u.a[i], sumi); sumi = __dp4a(hi[i], u.a[i + 4], sumi); }
+        return d * (u.d * (float) sumi - 8.0f * u.s);
+    }
+};
+
+template <> struct w_unit<B200_TYPE_Q8_0> {
+    int v[8]; float d;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint8_t * bp = row + ib * SZ_Q8_0;
+        d = ld_half(bp);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = (int) ld_b2(bp + 2 + 4 * i);
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sumi = __dp4a(v[i], u.a[i], sumi);
+        return d * u.d * (float) sumi;
+    }
+};
+
+template <> struct w_unit<B200_TYPE_Q4_K> {
+    int v[8]; float dsc, dmn;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7);
+        const uint32_t * bp = reinterpret_cast<const uint32_t *>(row + sb * SZ_Q4_K);     // 4-byte aligned
+        const float2 dm = __half22float2(*reinterpret_cast<const half2 *>(bp));
+        int sc, mn;
+        q4k_scale_min(j, __ldg(bp + 1), __ldg(bp + 2), __ldg(bp + 3), sc, mn);
+        dsc = dm.x * (float) sc;
+        dmn = dm.y * (float) mn;
+        const uint32_t * q = bp + 4 + 8 * (j >> 1);
+        const int sh = 4 * (j & 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = (__ldg(q + i) >> sh) & 0x0F0F0F0Fu;
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0, sum8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { sumi = __dp4a(v[i], u.a[i], sumi); sum8 = __dp4a(0x01010101, u.a[i], sum8); }
+        return u.d * (dsc * (float) sumi - dmn * (float) sum8);
+    }
+};
+
+template <> struct w_unit<B200_TYPE_Q6_K> {
+    int v[8]; float d0, d1;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7);
+        const int     nh = j >> 2, r = j & 3;
+        const uint8_t * bp = row + sb * SZ_Q6_K;                                            // 2-byte aligned only
+        const uint8_t * ql = bp + nh * 64 + (r & 1) * 32;
+        const uint8_t * qh = bp + 128 + nh * 32;
+        const uint16_t scs = __ldg(reinterpret_cast<const uint16_t *>(bp + 192 + 2 * j));
+        const float d = ld_half(bp + 208);
+        d0 = d * (float) (int8_t) (scs & 0xff);
+        d1 = d * (float) (int8_t) (scs >> 8);
+        const int shl = 4 * (r >> 1), shh = 2 * r;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t l = (ld_b2(ql + 4 * i) >> shl) & 0x0F0F0F0Fu;
+            const uint32_t h = ((ld_b2(qh + 4 * i) >> shh) & 0x03030303u) << 4;
+            v[i] = __vsubss4(l | h, 0x20202020);
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int s0 = 0, s1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { s0 = __dp4a(v[i], u.a[i], s0); s1 = __dp4a(v[i + 4], u.a[i + 4], s1); }
+        return u.d * (d0 * (float) s0 + d1 * (float) s1);
+    }
+};
+
+constexpr int GENERIC_WARPS = 4;
+
+template <int TYPE, int NC>
+__global__ void __launch_bounds__(GENERIC_WARPS * 32)
+gemv_generic(const mm_problem P) {
+    mm_cols<NC> C;
+    if (!mm_resolve<NC>(P, blockIdx.y, C)) return;
+    const int     lane = threadIdx.x & 31;
+    const int64_t row  = (int64_t) blockIdx.x * GENERIC_WARPS + (threadIdx.x >> 5);
+    if (row >= P.m) return;                                   // whole warp leaves together
+    const uint8_t * wrow = C.W + row * P.nb01;
+    const int64_t   nu   = P.k >> 5;
+    float acc[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) acc[c] = 0.0f;
+    for (int64_t ib = lane; ib < nu; ib += 32) {
+        w_unit<TYPE> w;
+        w.load(wrow, ib);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const act_unit u = load_act(P.act, C.plane_col[c], ib);
+            acc[c] += w.dot(u);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+        const float s = warp_sum(acc[c]);
+        if (lane == 0 && c < C.nc) C.y[c][row] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Q4_K fast path
+// ------------------------------------------------------------------------------------------------------------------
+// Shared memory per CTA: NC columns of { int8 qs[k] in swizzled 16-byte chunks ; float2 (d, d*sum) [k/32] }.
+// A lane's task = (superblock sb, 16-byte qs chunk c in 0..7): chunk c holds bytes [16h, 16h+16) of 64-group g = c/2
+// (h = c%2) => low nibbles are elements [16h,16h+16) of sub-block 2g, high nibbles the same elements of sub-block 2g+1
+// (dequantize_row_q4_K, ggml/src/ggml-quants.c:1467-1489).  8 consecutive lanes cover one superblock, a warp covers 4
+// superblocks = 576 contiguous bytes per step with two LDG.128 per lane (header + chunk).
+template <int NC>
+__device__ __forceinline__ void q4k_task(const uint4 hdr, const uint4 q, const int sb, const int c, const int8_t * s_qs,
+                                         const float2 * s_ds, const int k, float (&acc)[NC]) {
+    const int g = c >> 1, h = c & 1;
+    int sc0, mn0, sc1, mn1;
+    q4k_scale_min(2 * g,     hdr.y, hdr.z, hdr.w, sc0, mn0);
+    q4k_scale_min(2 * g + 1, hdr.y, hdr.z, hdr.w, sc1, mn1);
+    const float2 dm  = __half22float2(*reinterpret_cast<const half2 *>(&hdr.x));
+    const float dsc0 = dm.x * (float) sc0, dsc1 = dm.x * (float) sc1;
+    // the min term covers the whole 32-block: only the h == 0 lane of each pair subtracts it
+    const float dmn0 = h == 0 ? dm.y * (float) mn0 : 0.0f;
+    const float dmn1 = h == 0 ? dm.y * (float) mn1 : 0.0f;
+    const int lo0 = q.x & 0x0F0F0F0F, lo1 = q.y & 0x0F0F0F0F, lo2 = q.z & 0x0F0F0F0F, lo3 = q.w & 0x0F0F0F0F;
+    const int hi0 = (q.x >> 4) & 0x0F0F0F0F, hi1 = (q.y >> 4) & 0x0F0F0F0F, hi2 = (q.z >> 4) & 0x0F0F0F0F, hi3 = (q.w >> 4) & 0x0F0F0F0F;
+    const int ib0 = sb * 8 + 2 * g;            // activation block of sub-block 2g; 2g+1 is the next one
+    const int t0  = ib0 * 2 + h;               // 16-byte chunk index inside the column
+    const int p0  = act_swz(t0), p1 = act_swz(t0 + 2);
+#pragma unroll
+    for (int col = 0; col < NC; ++col) {
+        const uint4 * cq = reinterpret_cast<const uint4 *>(s_qs + (size_t) col * k);
+        const uint4 a0 = cq[p0], a1 = cq[p1];
+        const float2 e0 = s_ds[col * (k >> 5) + ib0], e1 = s_ds[col * (k >> 5) + ib0 + 1];
+        int s0 = __dp4a(lo0, (int) a0.x, 0); s0 = __dp4a(lo1, (int) a0.y, s0); s0 = __dp4a(lo2, (int) a0.z, s0); s0 = __dp4a(lo3, (int) a0.w, s0);
+        int s1 = __dp4a(hi0, (int) a1.x, 0); s1 = __dp4a(hi1, (int) a1.y, s1); s1 = __dp4a(hi2, (int) a1.z, s1); s1 = __dp4a(hi3, (int) a1.w, s1);
+        float r = acc[col];
+        r = fmaf(dsc0 * e0.x, (float) s0, r);
+        r = fmaf(dsc1 * e1.x, (float) s1, r);
+        r = fmaf(-dmn0, e0.y, r);
+        r = fmaf(-dmn1, e1.y, r);
+        acc[col] = r;
+    }
+}
+
+template <int NC, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32, 1)
+gemv_q4k(const mm_problem P) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int k   = (int) P.k;
+    const int nbk = k >> 5;
+    int8_t * s_qs = reinterpret_cast<int8_t *>(smem);
+    float2 * s_ds = reinterpret_cast<float2 *>(smem + (size_t) NC * k);
+
+    // the previous kernel in the stream may have produced X or the ids (no-op unless launched with the PDL attribute)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    mm_cols<NC> C;
+    if (!mm_resolve<NC>(P, blockIdx.y, C)) return;             // block-uniform
+
+    // ---- prologue: quantize the NC activation columns into shared memory (bit-exact Q8_1 values) ----
+    {
+        const int sub    = threadIdx.x & 7;
+        const int total  = NC * nbk;
+        const int groups = NWARPS * 4;
+        const int rounds = (total + groups - 1) / groups;
+        int blk = threadIdx.x >> 3;
+        for (int it = 0; it < rounds; ++it, blk += groups) {
+            const bool ok  = blk < total;
+            const int  b   = ok ? blk : total - 1;
+            const int  col = b / nbk;
+            const int  ib  = b - col * nbk;
+            const float * xc = C.x[0];
+#pragma unroll
+            for (int c = 1; c < NC; ++c) if (col == c) xc = C.x[c];
+            const float4 v = __ldg(reinterpret_cast<const float4 *>(xc + ib * 32 + sub * 4));
+            const q8_part qp = quantize_q8_1_part(v);
+            if (ok) {
+                const int t = ib * 2 + (sub >> 2);
+                *reinterpret_cast<uint32_t *>(s_qs + (size_t) col * k + 16 * act_swz(t) + 4 * (sub & 3)) = qp.packed;
+                if (sub == 0) s_ds[col * nbk + ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+            }
+        }
+    }
+    __syncthreads();
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    // ---- main loop: this CTA's contiguous share of the rows, one warp per row ----
+    const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t rlo  = (P.m * (int64_t) blockIdx.x) / gridDim.x;
+    const int64_t rhi  = (P.m * (int64_t) (blockIdx.x + 1)) / gridDim.x;
+    const int     sbl  = lane >> 3, c = lane & 7;
+    const int     nsb  = k >> 8;
+    for (int64_t row = rlo + warp; row < rhi; row += NWARPS) {
+        const uint8_t * wrow = C.W + row * P.nb01;
+        float acc[NC];
+#pragma unroll
+        for (int col = 0; col < NC; ++col) acc[col] = 0.0f;
+        // 4 steps (16 superblocks = k 4096) per batch of loads: 8 x 128-bit loads in flight per lane
+        for (int sb0 = 0; sb0 < nsb; sb0 += 16) {
+            uint4 hdr[4], q[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int sb = sb0 + 4 * u + sbl;
+                if (sb < nsb) {
+                    const uint8_t * bp = wrow + (size_t) sb * SZ_Q4_K;
+                    hdr[u] = ld_stream_u4(bp);
+                    q[u]   = ld_stream_u4(bp + 16 + 16 * c);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int sb = sb0 + 4 * u + sbl;
+                if (sb < nsb) q4k_task<NC>(hdr[u], q[u], sb, c, s_qs, s_ds, k, acc);
+            }
+        }
+#pragma unroll
+        for (int col = 0; col < NC; ++col) {
+            const float s = warp_sum(acc[col]);
+            if (lane == 0 && col < C.nc) C.y[col][row] = s;
+        }
+    }
+}
+
+template <int TYPE>
+int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles) {
+    const dim3 grid((unsigned) ((P.m + GENERIC_WARPS - 1) / GENERIC_WARPS), (unsigned) tiles);
+    const dim3 block(GENERIC_WARPS * 32);
+    switch (nc) {
+        case 1: gemv_generic<TYPE, 1><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 2: gemv_generic<TYPE, 2><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 3: gemv_generic<TYPE, 3><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 4: gemv_generic<TYPE, 4><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 5: gemv_generic<TYPE, 5><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 6: gemv_generic<TYPE, 6><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 7: gemv_generic<TYPE, 7><<<grid, block, 0, ctx->stream>>>(P); break;
+        case 8: gemv_generic<TYPE, 8><<<grid, block, 0, ctx->stream>>>(P); break;
+        default: b200_set_error("gemv_generic: nc=%d out of range", nc); return B200_E_ARG;
+    }
+    ctx->launches++;
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+template <int NC, int NWARPS>
+int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem) {
+    auto kern = gemv_q4k<NC, NWARPS>;
+    static bool attr_done[16] = {};            // per device
+    if (!attr_done[ctx->device & 15]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
+        attr_done[ctx->device & 15] = true;
+    }
+    // persistent: the SMs are shared evenly by the tiles (batches / (token, slot) pairs)
+    int64_t ctas = ctx->sm_count / tiles;
+    if (ctas < 1) ctas = 1;
+    const int64_t max_useful = (P.m + NWARPS - 1) / NWARPS;
+    if (ctas > max_useful) ctas = max_useful;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) ctas, (unsigned) tiles);
+    cfg.blockDim         = dim3(NWARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, P));
+    ctx->launches++;
+    return B200_OK;
+}
+
+}  // namespace
+
+// ---- host entry points used by mul_mat.cu -------------------------------------------------------------------------
+
+// pre-quantized activations in P.act; nc = columns per tile (1..8); tiles = gridDim.y
+int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles) {
+    if (tiles <= 0 || P.m <= 0) return B200_OK;
+    if (tiles > 65535) { b200_set_error("gemv: %lld column tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
+    switch (type) {
+        case B200_TYPE_Q4_0: return launch_generic_t<B200_TYPE_Q4_0>(ctx, P, nc, tiles);
+        case B200_TYPE_Q8_0: return launch_generic_t<B200_TYPE_Q8_0>(ctx, P, nc, tiles);
+        case B200_TYPE_Q4_K: return launch_generic_t<B200_TYPE_Q4_K>(ctx, P, nc, tiles);
+        case B200_TYPE_Q6_K: return launch_generic_t<B200_TYPE_Q6_K>(ctx, P, nc, tiles);
+    }
+    b200_set_error("gemv: unsupported weight type %d", type);
+    return B200_E_UNSUPPORTED;
+}
+
+// shared memory the fused Q4_K kernel needs for nc columns of k values
+size_t b200_gemv_q4k_smem(int nc, int64_t k) { return (size_t) nc * (size_t) (k + k / 4); }
+
+// f32 activations in P.X (quantized in the kernel prologue); nc = columns of every tile (exact, 1..8)
+int b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles) {
+    if (tiles <= 0 || P.m <= 0) return B200_OK;
+    if (tiles > 65535) { b200_set_error("gemv_q4k: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
+    const size_t smem = b200_gemv_q4k_smem(nc, P.k);
+    if (smem > ctx->smem_optin) { b200_set_error("gemv_q4k: %zu B of shared memory needed", smem); return B200_E_ARG; }
+    switch (nc) {
+        case 1: return launch_q4k_t<1, 32>(ctx, P, tiles, smem);
+        case 2: return launch_q4k_t<2, 32>(ctx, P, tiles, smem);
+        case 3: return launch_q4k_t<3, 16>(ctx, P, tiles, smem);
+        case 4: return launch_q4k_t<4, 16>(ctx, P, tiles, smem);
+        case 5: return launch_q4k_t<5, 16>(ctx, P, tiles, smem);
+        case 6: return launch_q4k_t<6, 16>(ctx, P, tiles, smem);
+        case 7: return launch_q4k_t<7, 16>(ctx, P, tiles, smem);
+        case 8: return launch_q4k_t<8, 16>(ctx, P, tiles, smem);
+    }
+    b200_set_error("gemv_q4k: nc=%d out of range", nc);
+    return B200_E_ARG;
+}
