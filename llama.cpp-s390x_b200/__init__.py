@@ -1,0 +1,18 @@
+"""llama.cpp-s390x_b200 — host-side mirror (Python) of the B200 quantized MUL_MAT / MUL_MAT_ID path.
+
+The product is the native code next to this file:
+  libggml_b200_kernels.so  C ABI (include/ggml_b200.h) over hand-written sm_100a CUDA kernels
+  libggml-b200.so          ggml backend plug-in (GGML_BACKEND_PATH) for unmodified llama.cpp / test-backend-ops
+
+This package only binds the C ABI with ctypes so tests and bench.py can drive it with torch tensors as device
+memory.  There is no fallback of any kind: if the library or a B200 is missing, calls raise.
+
+The directory name is not a Python identifier; load it with `load_package()` from tests/conftest.py / bench.py or
+    importlib.util.spec_from_file_location("llama_cpp_s390x_b200", ".../llama.cpp-s390x_b200/__init__.py",
+                                           submodule_search_locations=[...])
+"""
+from .binding import (  # noqa: F401
+    B200Error, Context, F32, I32, Q4_0, Q4_K, Q6_K, Q8_0, Q8_1, WEIGHT_TYPES, blck_size, build_native, lib, lib_path,
+    row_size, type_size,
+)
+from .ops import mm_ids, mul_mat, mul_mat_id, quantize_row_q8_1  # noqa: F401

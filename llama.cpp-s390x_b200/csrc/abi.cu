@@ -17,6 +17,8 @@ int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_strid
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_cols_total);
+int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
+                       int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
 
 // ---- errors ---------------------------------------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -256,7 +258,16 @@ int b200_mul_mat_supported(const b200_tensor * a, const b200_tensor * b, const b
 }
 
 int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    return b200_mul_mat_ex(ctx, a, b, d, 0, nullptr, 0, 0);
+}
+
+}  // extern "C"
+
+// MUL_MAT with the row-split all-gather fused into the store: results also go to peer_Y[p][col*peer_m + peer_row0 + row]
+int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
+                    int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0) {
     if (!ctx) { b200_set_error("mul_mat: ctx is NULL"); return B200_E_ARG; }
+    if (n_peers < 0 || n_peers > B200_MAX_PEERS) { b200_set_error("mul_mat: n_peers out of range"); return B200_E_ARG; }
     if (const char * why = check_mul_mat(a, b, d)) { b200_set_error("mul_mat: %s", why); return B200_E_ARG; }
     const int64_t k = a->ne[0], m = a->ne[1], n = b->ne[1];
     const int64_t batches = b->ne[2] * b->ne[3];
@@ -271,6 +282,8 @@ int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, c
     P.r2 = b->ne[2] / a->ne[2]; P.r3 = b->ne[3] / a->ne[3];
     P.Y = (float *) d->data;
     P.mode = MM_PLAIN;
+    P.n_peers = n_peers; P.peer_m = peer_m; P.peer_row0 = peer_row0;
+    for (int p = 0; p < n_peers; ++p) P.peer_Y[p] = peer_Y[p];
 
     if (n <= ctx->max_gemv_cols) {
         if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
@@ -285,12 +298,14 @@ int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, c
 
     int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
     if (rc) return rc;
-    if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
+    if (n_peers == 0 && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
         return b200_launch_gemm_tc(ctx, a->type, P, n * batches);
     }
     const int64_t tiles = batches * ((n + 7) / 8);
     return b200_launch_gemv_generic(ctx, a->type, P, 8, tiles);
 }
+
+extern "C" {
 
 // ---- (4) ----------------------------------------------------------------------------------------------------------
 int b200_mul_mat_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * c) {

@@ -17,6 +17,7 @@
 #include "../../include/ggml_b200.h"
 
 #define B200_WARP 32
+#define B200_MAX_PEERS 8
 
 // ---- block geometry -----------------------------------------------------------------------------
 #define QK_SMALL 32

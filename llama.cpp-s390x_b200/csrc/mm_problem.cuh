@@ -31,7 +31,23 @@ struct mm_problem {
     int            n_expert;
     const int32_t *ids_src1;     // MM_ID_SORTED: sorted position -> pair index (token * n_used + slot)
     const int32_t *expert_bounds;// MM_ID_SORTED: [n_expert + 1]
+    // row-split all-gather fused into the epilogue: besides Y, every result is also stored into the full-height output
+    // of each peer GPU through NVLink peer mappings: peer_Y[p][col * peer_m + peer_row0 + row]   (MM_PLAIN only)
+    int     n_peers;
+    float * peer_Y[8];
+    int64_t peer_m, peer_row0;
 };
+
+
+
+// store one result (row, plane-order column index `ycol` = (Y column pointer - P.Y) / m) locally and to the peers
+__device__ __forceinline__ void mm_store(const mm_problem & P, float * ycol_ptr, const int64_t row, const float v) {
+    ycol_ptr[row] = v;
+    if (P.n_peers > 0) {
+        const int64_t col = (ycol_ptr - P.Y) / P.m;
+        for (int p = 0; p < P.n_peers; ++p) P.peer_Y[p][col * P.peer_m + P.peer_row0 + row] = v;
+    }
+}
 
 // What one CTA works on: a weight matrix and up to NC columns (plane column index + output pointer each).
 template <int NC>

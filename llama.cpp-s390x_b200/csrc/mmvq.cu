@@ -158,7 +158,7 @@ gemv_generic(const mm_problem P) {
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
         const float s = warp_sum(acc[c]);
-        if (lane == 0 && c < C.nc) C.y[c][row] = s;
+        if (lane == 0 && c < C.nc) mm_store(P, C.y[c], row, s);
     }
 }
 
@@ -277,7 +277,7 @@ gemv_q4k(const mm_problem P) {
 #pragma unroll
         for (int col = 0; col < NC; ++col) {
             const float s = warp_sum(acc[col]);
-            if (lane == 0 && col < C.nc) C.y[col][row] = s;
+            if (lane == 0 && col < C.nc) mm_store(P, C.y[col], row, s);
         }
     }
 }

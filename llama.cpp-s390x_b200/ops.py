@@ -1,0 +1,111 @@
+"""The reference's operator interface for this path, on torch CUDA tensors (device memory only; no arithmetic here).
+
+Names, argument meaning and error behaviour follow ggml:
+  quantize_row_q8_1(x)            quantize_row_q8_1_ref          ggml/src/ggml-quants.c:260-293
+  mul_mat(type, W, x)             ggml_mul_mat   (ggml.c:3240-3255) / ggml_compute_forward_mul_mat    (ggml-cpu.c:1241-1439)
+  mul_mat_id(type, as, b, ids)    ggml_mul_mat_id(ggml.c:3291-3315) / ggml_compute_forward_mul_mat_id (ggml-cpu.c:1521-1694)
+Shapes are written torch-style (outermost first), i.e. reversed ggml `ne`: a ggml tensor [k, n, ne2, ne3] is a torch tensor
+of shape (ne3, ne2, n, k).  Weight tensors are uint8 with the last dim = ggml_row_size(type, k) bytes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+from .binding import F32, I32, Context, Tensor, blck_size, check, lib, row_size, type_size
+
+
+def _desc(t, ggml_type: int, k_elems: int | None = None) -> Tensor:
+    """b200_tensor for a torch tensor of up to 4 dims.  For quantized weights pass k_elems (elements per row)."""
+    import torch
+    assert t.is_cuda, "device tensors only"
+    d = Tensor()
+    d.data = t.data_ptr()
+    d.type = ggml_type
+    shape = list(t.shape)
+    strides = [s * t.element_size() for s in t.stride()]
+    while len(shape) < 4:
+        shape.insert(0, 1)
+        strides.insert(0, strides[0] * shape[1] if strides else t.element_size())
+    # torch (ne3, ne2, ne1, ne0) -> ggml ne[0..3]
+    for i in range(4):
+        d.ne[i] = shape[3 - i]
+        d.nb[i] = strides[3 - i]
+    if k_elems is not None:
+        assert t.dtype == torch.uint8 and t.stride(-1) == 1
+        assert shape[3] == row_size(ggml_type, k_elems), "last dim must be ggml_row_size(type, k)"
+        d.ne[0] = k_elems
+        d.nb[0] = type_size(ggml_type)
+    return d
+
+
+def quantize_row_q8_1(ctx: Context, x):
+    """x: f32 (nrows, k) with contiguous rows -> uint8 (nrows, k/32*36) of block_q8_1"""
+    import torch
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    nrows, k = x.shape
+    if k % 32 != 0:
+        raise ValueError("k must be a multiple of 32 (QK8_1)")
+    y = torch.empty((nrows, k // 32 * 36), dtype=torch.uint8, device=x.device)
+    check(lib().b200_quantize_row_q8_1(ctx.handle, x.data_ptr(), x.stride(0) * 4, y.data_ptr(), k, nrows), "b200_quantize_row_q8_1")
+    return y
+
+
+def mul_mat(ctx: Context, wtype: int, w, x, out=None):
+    """w: uint8 ([ne03, ne02,] m, row_size); x: f32 ([ne13, ne12,] n, k) -> f32 ([ne13, ne12,] n, m)"""
+    import torch
+    k = x.shape[-1]
+    if k % blck_size(wtype) != 0:
+        raise ValueError("k is not a whole number of blocks")
+    a = _desc(w, wtype, k_elems=k)
+    b = _desc(x, F32)
+    m = w.shape[-2]
+    if out is None:
+        out = torch.empty(tuple(x.shape[:-1]) + (m,), dtype=torch.float32, device=x.device)
+    d = _desc(out, F32)
+    check(lib().b200_mul_mat(ctx.handle, C.byref(a), C.byref(b), C.byref(d)), "b200_mul_mat")
+    return out
+
+
+def mul_mat_supported(wtype: int, w, x) -> bool:
+    import torch
+    a = _desc(w, wtype, k_elems=x.shape[-1])
+    b = _desc(x, F32)
+    out = torch.empty(tuple(x.shape[:-1]) + (w.shape[-2],), dtype=torch.float32, device="meta")
+    d = Tensor()
+    d.type = F32
+    shape = [1] * (4 - out.dim()) + list(out.shape)
+    nb = 4
+    for i in range(4):
+        d.ne[i] = shape[3 - i]
+        d.nb[i] = nb
+        nb *= shape[3 - i]
+    return bool(lib().b200_mul_mat_supported(C.byref(a), C.byref(b), C.byref(d)))
+
+
+def mul_mat_id(ctx: Context, wtype: int, as_, b, ids, out=None):
+    """as_: uint8 (n_expert, m, row_size); b: f32 (n_tokens, b_ne1, k); ids: int32 (n_tokens, n_used), rows may be strided
+    -> f32 (n_tokens, n_used, m)"""
+    import torch
+    assert as_.dim() == 3 and b.dim() == 3 and ids.dim() == 2 and ids.dtype == torch.int32
+    k = b.shape[-1]
+    a = _desc(as_, wtype, k_elems=k)
+    bd = _desc(b, F32)
+    idd = _desc(ids, I32)
+    n_tokens, n_used = ids.shape
+    m = as_.shape[-2]
+    if out is None:
+        out = torch.empty((n_tokens, n_used, m), dtype=torch.float32, device=b.device)
+    cd = _desc(out, F32)
+    check(lib().b200_mul_mat_id(ctx.handle, C.byref(a), C.byref(bd), C.byref(idd), C.byref(cd)), "b200_mul_mat_id")
+    return out
+
+
+def mm_ids(ctx: Context, ids, n_expert: int):
+    """expert gather: ids int32 (n_tokens, n_used) -> (ids_src1 int32 [n_pairs], expert_bounds int32 [n_expert+1])"""
+    import torch
+    n_tokens, n_used = ids.shape
+    src1 = torch.full((n_tokens * n_used,), -1, dtype=torch.int32, device=ids.device)
+    bounds = torch.zeros((n_expert + 1,), dtype=torch.int32, device=ids.device)
+    check(lib().b200_mm_ids(ctx.handle, ids.data_ptr(), ids.stride(0) * 4, n_expert, n_used, n_tokens, src1.data_ptr(), bounds.data_ptr()),
+          "b200_mm_ids")
+    return src1, bounds

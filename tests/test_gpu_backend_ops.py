@@ -1,0 +1,46 @@
+"""GPU conformance (-m gpu): the reference's own UNMODIFIED harness, tests/test-backend-ops.cpp (compiled from
+/root/reference into oracle/_ref by oracle/Makefile), run against our backend plug-in loaded through GGML_BACKEND_PATH
+(ggml/src/ggml-backend-reg.cpp:581-585).  It compares every MUL_MAT / MUL_MAT_ID case our supports_op() accepts with the
+reference CPU backend (NMSE <= 5e-4) and checks the sentinels around every tensor for out-of-bounds writes."""
+import re
+import subprocess
+from pathlib import Path
+
+import pytest
+
+from oracle import refenv
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+PLUGIN = ROOT / "llama.cpp-s390x_b200" / "libggml-b200.so"
+HARNESS = refenv.REF_DIR / "test-backend-ops"
+
+
+def run_harness(*args, timeout=900):
+    if not HARNESS.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/test-backend-ops or libggml-b200.so not built (needs /root/reference at build time)")
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN)})
+    p = subprocess.run([str(HARNESS), *args], env=env, capture_output=True, text=True, timeout=timeout)
+    out = re.sub(r"\x1b\[[0-9;]*m", "", p.stdout + p.stderr)
+    return p.returncode, out
+
+
+@pytest.mark.parametrize("op", ["MUL_MAT", "MUL_MAT_ID"])
+def test_backend_ops(op):
+    rc, out = run_harness("test", "-b", "B2000", "-o", op)
+    tail = "\n".join(out.splitlines()[-25:])
+    assert "Backend B2000" in out, tail                     # the plug-in was loaded and selected
+    m = re.search(r"(\d+)/(\d+) tests passed", out)
+    assert m, tail
+    passed, total = int(m.group(1)), int(m.group(2))
+    assert rc == 0 and passed == total and total > 0, tail
+    # every case of the four weight types with F32 activations must have RUN (not "not supported")
+    ran = [l for l in out.splitlines() if re.search(r"type_a=(q4_0|q8_0|q4_K|q6_K),type_b=f32", l) and l.rstrip().endswith("OK")]
+    assert len(ran) >= (20 if op == "MUL_MAT" else 20), f"only {len(ran)} quantized cases ran\n{tail}"
+    failed = [l for l in out.splitlines() if "FAIL" in l]
+    assert not failed, failed[:5]
+
+
+def test_backend_ops_support_listing():
+    rc, out = run_harness("support", "-b", "B2000", "-o", "MUL_MAT")
+    assert rc == 0 and "B2000" in out
