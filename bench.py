@@ -1,0 +1,367 @@
+#!/usr/bin/env python3
+"""bench.py — BASELINE.json's metric on its configuration: Q4_K GEMV HBM GB/s (and matmul-only tok/s) over one decode step
+of Llama-3-8B shapes on B200.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--no-graph] [--shapes]
+
+A "step" is one pass of the hot path over one decoded token: the 225 quantized MUL_MATs of a Llama-3-8B forward at n=1
+(32 layers x {wq, wk, wv, wo, gate, up, down} + output head), pure Q4_K, 4.22 GB of distinct weights — far more than the
+126 MB L2, so every step streams from HBM (no flush needed; stated in config.l2).  Weights are synthetic random VALID
+blocks, activations N(0,1); both are resident in HBM before the timed region.  `value` = algorithmic bytes / time with
+bytes = m*k*4.5/8 + k*4 + m*4 per matmul.  `e2e` is the same metric through the C ABI's host-buffer call
+(b200_mul_mat_host): per matmul, x is copied from pinned host memory, y is copied back, inside the timed region — which is
+exactly how a MUL_MAT-only ggml backend is driven by llama.cpp's scheduler.
+
+N > 1 (torchrun, one process per GPU): the same step with every weight matrix row-split over the ranks and an NCCL
+all-gather of the output row slices after each matmul (strong scaling: total work is fixed).
+
+--impl reference times the reference's own ggml-cpu MUL_MAT (oracle/_ref, compiled from /root/reference; falls back to the
+C restatement in oracle/ if it did not travel) on the host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+Q4_K = 12
+METRIC = "q4_k_gemv_hbm_gbps_llama3_8b_decode"
+UNIT = "GB/s"
+
+# (name, m, k, count per step)
+LLAMA3_8B = [
+    ("wq", 4096, 4096, 32), ("wk", 1024, 4096, 32), ("wv", 1024, 4096, 32), ("wo", 4096, 4096, 32),
+    ("ffn_gate", 14336, 4096, 32), ("ffn_up", 14336, 4096, 32), ("ffn_down", 4096, 14336, 32),
+    ("output", 128256, 4096, 1),
+]
+
+
+def algo_bytes(m, k, n=1):
+    return m * k * 4.5 / 8 + n * k * 4 + m * n * 4
+
+
+STEP_BYTES = sum(algo_bytes(m, k) * c for _, m, k, c in LLAMA3_8B)
+STEP_MATMULS = sum(c for *_, c in LLAMA3_8B)
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region"""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.25)
+            self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = max([int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def device_random_q4k(torch, m, k, gen):
+    """m rows of valid random Q4_K blocks generated ON the device (setup, not timed)"""
+    nb = k // 256
+    raw = torch.randint(0, 256, (m, nb, 144), dtype=torch.uint8, device="cuda", generator=gen)
+    d = (torch.rand((m, nb), device="cuda", generator=gen) * 0.75 + 0.25) * (0.02 / (15 * 63))
+    dmin = (torch.rand((m, nb), device="cuda", generator=gen) * 0.75 + 0.25) * (0.02 / 63)
+    hdr = torch.stack([d, dmin], -1).to(torch.float16).view(torch.uint8).reshape(m, nb, 4)
+    raw[:, :, 0:4] = hdr
+    return raw.reshape(m, nb * 144)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    from __graft_entry__ import load_package
+    pkg = load_package()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    stream = torch.cuda.Stream()
+    ctx = pkg.Context(local, stream=stream.cuda_stream)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(1234 + rank)
+
+    # ---- the workload, resident in HBM ------------------------------------------------------------------------------------
+    ops = []   # (W shard uint8 [rows, rs], x f32 [1, k], y_full f32 [1, m], y_shard)
+    xs = {}
+    for name, m, k, count in LLAMA3_8B:
+        assert m % world == 0
+        rows = m // world
+        if k not in xs:
+            xg = torch.Generator(device="cuda"); xg.manual_seed(4321 + k)          # same activations on every rank
+            xs[k] = torch.randn((1, k), device="cuda", generator=xg)
+        for _ in range(count):
+            W = device_random_q4k(torch, rows, k, gen)
+            y = torch.empty((1, m), device="cuda")
+            ys = y if world == 1 else torch.empty((1, rows), device="cuda")
+            ops.append((W, xs[k], y, ys))
+    # interleave like a real forward: layer by layer
+    per_layer = [[o for o in ops[i * 32:(i + 1) * 32]] for i in range(7)]
+    order = [per_layer[j][l] for l in range(32) for j in range(7)] + [ops[-1]]
+
+    def step():
+        for W, x, y, ys in order:
+            pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
+            if world > 1:
+                dist.all_gather_into_tensor(y.view(-1), ys.view(-1))
+
+    launches0 = ctx.launches
+    with torch.cuda.stream(stream):
+        step()                                               # allocations, function attributes
+        stream.synchronize()
+        launches_per_step = ctx.launches - launches0
+        graph = None
+        if not args.no_graph:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream):
+                step()
+        run = graph.replay if graph is not None else step
+        for _ in range(args.warmup):
+            run()
+        stream.synchronize()
+
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(args.steps):
+            run()
+        ev1.record(stream)
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = STEP_BYTES / (ms_step * 1e-3) / 1e9
+
+    # ---- e2e: host buffers through b200_mul_mat_host (N == 1 semantics on every rank's shard) ---------------------------------
+    e2e = None
+    shapes = None
+    if world == 1:
+        import ctypes as C
+        L = pkg.lib()
+        hctx = pkg.Context(local)                             # own stream
+        kmax, mmax = max(k for _, _, k, _ in LLAMA3_8B), max(m for _, m, _, _ in LLAMA3_8B)
+        xh = torch.randn((1, kmax)).pin_memory()
+        yh = torch.empty((1, mmax)).pin_memory()
+
+        def host_step():
+            for W, x, y, ys in order:
+                rc = L.b200_mul_mat_host(hctx.handle, Q4_K, W.data_ptr(), W.shape[0], x.shape[1], xh.data_ptr(), 1, yh.data_ptr())
+                if rc:
+                    raise pkg.B200Error(L.b200_last_error().decode())
+        host_step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2e_steps = max(1, min(args.steps, 10))
+        for _ in range(e2e_steps):
+            host_step()
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        e2e = {"value": round(STEP_BYTES / (e2e_ms * 1e-3) / 1e9, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 4),
+               "tok_per_s": round(1e3 / e2e_ms, 2),
+               "h2d_bytes_per_step": int(sum(k * 4 * c for _, _, k, c in LLAMA3_8B)),
+               "d2h_bytes_per_step": int(sum(m * 4 * c for _, m, _, c in LLAMA3_8B)),
+               "api": "b200_mul_mat_host (C ABI, pinned host x -> H2D -> GEMV -> D2H y, per matmul)"}
+        if args.shapes:
+            shapes = per_shape(torch, pkg, ctx, stream, ops)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        out = {
+            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "int8 dot (dp4a) x fp32 scales; Q4_K weights, Q8_1 activations", "data": "synthetic",
+            "config": {"workload": "Llama-3-8B Q4_K decode step: 225 MUL_MATs at n=1 (k=4096, m=4096/1024/14336/128256; m=4096,k=14336)",
+                       "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
+                       "l2": "inputs larger than L2: 4.22 GB of distinct weights per step vs 126 MB L2, no flush needed",
+                       "launch": "CUDA graph replay" if graph is not None else "eager launches through the C ABI",
+                       "parallelism": "1 GPU" if world == 1 else f"row-split x{world} + NCCL all-gather per matmul"},
+            "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
+            "gpu_launches": int(launches_per_step * args.steps),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": round(value / world, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(value / world / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "kernel": "gemv_q4k<1,32> (all 225 launches of the step)",
+                         "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / STEP_MATMULS / world)},
+        }
+        if e2e:
+            out["e2e"] = e2e
+        if shapes:
+            out["shapes"] = shapes
+        if world == 1:
+            out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def per_shape(torch, pkg, ctx, stream, ops):
+    """GB/s of each distinct shape, rotating over its 32 distinct copies (> L2 except wk/wv: 32 x 2.4 MB, flagged)"""
+    res = {}
+    idx = 0
+    for name, m, k, count in LLAMA3_8B:
+        group = ops[idx: idx + count]
+        idx += count
+        iters = 64 if count > 1 else 8
+        with torch.cuda.stream(stream):
+            for W, x, y, ys in group[:2]:
+                pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                for i in range(iters):
+                    W, x, y, ys = group[i % count]
+                    pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
+            g.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(5):
+                g.replay()
+            e1.record(stream)
+            stream.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (5 * iters)
+        res[name] = {"m": m, "k": k, "us": round(us, 3), "gbps": round(algo_bytes(m, k) / us / 1e3, 1),
+                     "distinct_mb": round(count * m * k * 4.5 / 8 / 1e6, 1)}
+    return res
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+def cpu_baseline(seconds=16.0, threads=0):
+    """the reference's ggml-cpu MUL_MAT on the host cores: every distinct shape of the step timed for a bounded number of
+    iterations over enough distinct weight copies to defeat the LLC, extrapolated to the 225 matmuls of one step"""
+    import numpy as np
+
+    from oracle import refenv
+    from tests.util import random_blocks
+    cores = threads or os.cpu_count() or 1
+    R = refenv.load_ref()
+    rng = np.random.default_rng(0)
+    shapes = sorted({(m, k) for _, m, k, _ in LLAMA3_8B})
+    counts = {s: sum(c for _, m, k, c in LLAMA3_8B if (m, k) == s) for s in shapes}
+    if R is not None and not threads:
+        # ggml's spinning threadpool collapses when the host has fewer free cores than it reports (shared boxes): use the
+        # thread count that is actually fastest on this host, and report it
+        Wp = random_blocks(Q4_K, 4096, 4096, rng)
+        best = None
+        cand = sorted({cores, max(1, cores // 2), max(1, cores // 4), max(1, cores // 8), 1}, reverse=True)
+        for c in cand:
+            tsec = R.ref_time_mul_mat(Q4_K, refenv.ptr(Wp), 4096, 1, 4096, 16, 48, c)
+            if tsec > 0 and (best is None or tsec < best[0]):
+                best = (tsec, c)
+        cores = best[1]
+    budget = seconds / len(shapes)
+    step_s = 0.0
+    detail = {}
+    for (m, k) in shapes:
+        W = random_blocks(Q4_K, m, k, rng)
+        wbytes = W.nbytes
+        n_mats = max(1, min(16, int(256e6 // wbytes)))
+        if R is not None:
+            probe = R.ref_time_mul_mat(Q4_K, refenv.ptr(W), m, 1, k, n_mats, 3, cores)
+            iters = max(3, min(4000, int(budget / max(probe, 1e-6))))
+            sec = R.ref_time_mul_mat(Q4_K, refenv.ptr(W), m, 1, k, n_mats, iters, cores)
+            kind = "reference"
+        else:
+            O = refenv.load_oracle()
+            X = rng.standard_normal((1, k)).astype(np.float32)
+            Y = np.zeros((1, m), np.float32)
+            t0 = time.perf_counter()
+            iters = 0
+            while time.perf_counter() - t0 < budget:
+                O.orc_mul_mat(Q4_K, refenv.ptr(W), refenv.ptr(X), refenv.ptr(Y), m, 1, k, 1, 1, 1, 1, cores)
+                iters += 1
+            sec = (time.perf_counter() - t0) / iters
+            kind = "port"
+        detail[f"{m}x{k}"] = {"us": round(sec * 1e6, 1), "iters": iters, "n_mats": n_mats}
+        step_s += sec * counts[(m, k)]
+    return {"value": round(STEP_BYTES / step_s / 1e9, 3), "unit": UNIT, "cores": cores, "kind": kind,
+            "ms_per_step": round(step_s * 1e3, 3), "tok_per_s": round(1.0 / step_s, 3),
+            "sample": f"each of the {len(shapes)} distinct shapes timed ~{budget:.1f} s back to back over up to 16 distinct weight copies "
+                      f"(> LLC), extrapolated to the {STEP_MATMULS} matmuls of one step; generic/x86 ggml-cpu (the fork's s390x VXE "
+                      f"kernels cannot run here)",
+            "shapes": detail}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_baseline(seconds=max(8.0, min(60.0, 6.0 * (args.steps + args.warmup))))
+    out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", args.gpus)),
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "int8 dot x fp32 scales (ggml-cpu Q4_K x Q8_K)", "data": "synthetic",
+           "config": {"workload": "Llama-3-8B Q4_K decode step: 225 MUL_MATs at n=1 (bounded per-shape sample, extrapolated)"},
+           "cpu_baseline": cb,
+           "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
+    ap.add_argument("--cpu-seconds", type=float, default=16.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -152,33 +152,41 @@ SHIM_API int ref_mul_mat_id(int wtype, const void * as, const float * b, const i
     return 0;
 }
 
-// Time MUL_MAT on the reference CPU backend: weights stay resident, `iters` back-to-back graph computes of
-// `n_mats` distinct weight matrices (cycled, so the working set can exceed the LLC).  Returns seconds per
-// single matmul (mean), or <0 on error.  Used by bench.py's cpu_baseline / --impl reference arm.
+// Time MUL_MAT on the reference CPU backend the way the reference's own perf harness does (tests/test-backend-ops.cpp:
+// 1455-1583, eval_perf): ONE graph holding `iters` MUL_MAT nodes, so the threadpool start-up is paid once per graph and
+// not per matmul.  The nodes cycle over `n_mats` distinct weight matrices so the working set can exceed the LLC.
+// Returns seconds per single matmul (mean), or <0 on error.  Used by bench.py's cpu_baseline / --impl reference arm.
 SHIM_API double ref_time_mul_mat(int wtype, const void * W_one, int64_t m, int64_t n, int64_t k, int n_mats,
                                  int iters, int n_threads) {
-    cpu_graph g;
-    if (!g.init(n_threads)) return -1.0;
-    std::vector<ggml_tensor *> as(n_mats), cs(n_mats);
-    ggml_tensor * b = ggml_new_tensor_2d(g.ctx, GGML_TYPE_F32, k, n);
-    std::vector<ggml_cgraph *> gfs(n_mats);
-    for (int i = 0; i < n_mats; i++) {
-        as[i]  = ggml_new_tensor_2d(g.ctx, (ggml_type) wtype, k, m);
-        cs[i]  = ggml_mul_mat(g.ctx, as[i], b);
-        gfs[i] = ggml_new_graph_custom(g.ctx, 16, false);
-        ggml_build_forward_expand(gfs[i], cs[i]);
+    if (iters < 1 || n_mats < 1) return -1.0;
+    ggml_init_params ip = { ggml_tensor_overhead() * (size_t) (n_mats + 2 * iters + 16) + ggml_graph_overhead_custom(iters + 16, false),
+                            nullptr, true };
+    ggml_context * ctx = ggml_init(ip);
+    ggml_backend_t backend = ggml_backend_cpu_init();
+    if (!ctx || !backend) return -1.0;
+    if (n_threads > 0) ggml_backend_cpu_set_n_threads(backend, n_threads);
+    std::vector<ggml_tensor *> as(n_mats);
+    ggml_tensor * b = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, k, n);
+    for (int i = 0; i < n_mats; i++) as[i] = ggml_new_tensor_2d(ctx, (ggml_type) wtype, k, m);
+    ggml_cgraph * gf = ggml_new_graph_custom(ctx, iters + 16, false);
+    ggml_cgraph * gw = ggml_new_graph_custom(ctx, 16, false);
+    for (int i = 0; i < iters; i++) ggml_build_forward_expand(gf, ggml_mul_mat(ctx, as[i % n_mats], b));
+    ggml_build_forward_expand(gw, ggml_mul_mat(ctx, as[0], b));
+    ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors(ctx, backend);
+    double result = -2.0;
+    if (buf) {
+        for (int i = 0; i < n_mats; i++) ggml_backend_tensor_set(as[i], W_one, 0, ggml_nbytes(as[i]));
+        std::vector<float> x((size_t) k * n);
+        for (size_t i = 0; i < x.size(); i++) x[i] = (float) ((i * 2654435761u) % 2001) / 1000.0f - 1.0f;
+        ggml_backend_tensor_set(b, x.data(), 0, ggml_nbytes(b));
+        ggml_backend_graph_compute(backend, gw);   // warm-up
+        const auto t0 = std::chrono::steady_clock::now();
+        const bool ok = ggml_backend_graph_compute(backend, gf) == GGML_STATUS_SUCCESS;
+        const auto t1 = std::chrono::steady_clock::now();
+        result = ok ? std::chrono::duration<double>(t1 - t0).count() / iters : -3.0;
+        ggml_backend_buffer_free(buf);
     }
-    if (!g.alloc()) return -2.0;
-    for (int i = 0; i < n_mats; i++) ggml_backend_tensor_set(as[i], W_one, 0, ggml_nbytes(as[i]));
-    std::vector<float> x((size_t) k * n);
-    for (size_t i = 0; i < x.size(); i++) x[i] = (float) ((i * 2654435761u) % 2001) / 1000.0f - 1.0f;
-    ggml_backend_tensor_set(b, x.data(), 0, ggml_nbytes(b));
-    // warm-up
-    for (int i = 0; i < n_mats && i < 2; i++) ggml_backend_graph_compute(g.backend, gfs[i]);
-    const auto t0 = std::chrono::steady_clock::now();
-    for (int it = 0; it < iters; it++) {
-        if (ggml_backend_graph_compute(g.backend, gfs[it % n_mats]) != GGML_STATUS_SUCCESS) return -3.0;
-    }
-    const auto t1 = std::chrono::steady_clock::now();
-    return std::chrono::duration<double>(t1 - t0).count() / iters;
+    ggml_backend_free(backend);
+    ggml_free(ctx);
+    return result;
 }
