@@ -104,7 +104,9 @@ class Context:
     def __init__(self, device: int = 0, stream=None):
         if stream == "torch":
             import torch
-            stream = torch.cuda.current_stream(device).cuda_stream
+            # torch's default stream is the legacy NULL stream (handle 0); hand it over as cudaStreamLegacy (0x1),
+            # because a NULL handle asks b200_ctx_create for a private stream
+            stream = torch.cuda.current_stream(device).cuda_stream or 0x1
         self.device = device
         h = C.c_void_p()
         check(lib().b200_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(h)), "b200_ctx_create")

@@ -11,7 +11,7 @@
 
 // kernels' host launchers (other TUs)
 int    b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles);
-int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles);
+int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait);
 size_t b200_gemv_q4k_smem(int nc, int64_t k);
 int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
                           int32_t * ids_src1, int32_t * expert_bounds);
@@ -109,6 +109,9 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->max_gemv_cols = env_int("GGML_B200_MAX_GEMV_COLS", 8);
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
+    ctx->gemv_cfg      = env_int("GGML_B200_GEMV_CFG", 0);
+    ctx->noop          = env_int("GGML_B200_NOOP", 0);
+    ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
     *out = ctx;
@@ -144,6 +147,9 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "max_gemv_cols")) slot = &ctx->max_gemv_cols;
     else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
+    else if (!strcmp(name, "gemv_cfg"))      slot = &ctx->gemv_cfg;
+    else if (!strcmp(name, "noop"))          slot = &ctx->noop;
+    else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
     const int prev = *slot;
     *slot = value;
@@ -217,6 +223,48 @@ static const char * check_mul_mat_id(const b200_tensor * as, const b200_tensor *
     return nullptr;
 }
 
+// ---- in-flight write tracking for the deferred dependency wait of the fused GEMV (mmvq.cu, flags bit 1) -----------------
+// A GEMV launched with the PDL attribute whose inputs are not written by any kernel that may still be running defers its
+// griddepcontrol.wait to just before its first store.  "May still be running" = every kernel launched since (and
+// including) the last one that waited early: an early waiter proves all of ITS predecessors complete, and because every
+// kernel waits before it stores/finishes, completion is transitive.
+static void tensor_extent(const b200_tensor * t, const char ** lo, const char ** hi) {
+    size_t span = (size_t) b200_tsize(t->type);
+    if (b200_blck(t->type) > 1) span = (size_t) t->nb[1];       // quantized rows: one whole row
+    for (int i = (b200_blck(t->type) > 1 ? 1 : 0); i < 4; ++i) span += (size_t) (t->ne[i] > 0 ? t->ne[i] - 1 : 0) * (size_t) t->nb[i];
+    *lo = (const char *) t->data;
+    *hi = *lo + span;
+}
+
+static bool pending_overlaps(const b200_ctx * ctx, const b200_tensor * t) {
+    const char * lo, * hi;
+    tensor_extent(t, &lo, &hi);
+    for (int i = 0; i < ctx->n_pend; ++i) if (lo < ctx->pend_hi[i] && ctx->pend_lo[i] < hi) return true;
+    return false;
+}
+
+// record the output of a kernel about to be launched; `fresh` = this kernel waits early (or is a normal launch), so
+// everything before it is known complete by the time it runs
+static void pending_push(b200_ctx * ctx, const b200_tensor * dst, bool fresh) {
+    if (fresh) ctx->n_pend = 0;
+    const char * lo, * hi;
+    tensor_extent(dst, &lo, &hi);
+    ctx->pend_lo[ctx->n_pend] = lo; ctx->pend_hi[ctx->n_pend] = hi; ctx->n_pend++;
+}
+
+static void pending_reset_range(b200_ctx * ctx, const void * ptr, size_t nbytes) {
+    ctx->n_pend = 1;
+    ctx->pend_lo[0] = (const char *) ptr;
+    ctx->pend_hi[0] = (const char *) ptr + nbytes;
+}
+
+static bool can_defer_wait(b200_ctx * ctx, const b200_tensor * x, const b200_tensor * ids) {
+    if (!ctx->pdl || !ctx->defer_wait || ctx->n_pend >= 16) return false;
+    if (pending_overlaps(ctx, x)) return false;
+    if (ids && pending_overlaps(ctx, ids)) return false;
+    return true;
+}
+
 static bool aligned16(const void * p, int64_t a, int64_t b, int64_t c) {
     return (((uintptr_t) p | (uintptr_t) a | (uintptr_t) b | (uintptr_t) c) & 15) == 0;
 }
@@ -246,6 +294,7 @@ int b200_quantize_row_q8_1(b200_ctx * ctx, const float * x, int64_t x_row_stride
     if (!ctx || !x || !y) { b200_set_error("quantize_row_q8_1: NULL argument"); return B200_E_ARG; }
     if (x_row_stride_bytes % 4 != 0) { b200_set_error("quantize_row_q8_1: row stride must be a multiple of 4"); return B200_E_ARG; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    pending_reset_range(ctx, y, (size_t) nrows * (size_t) (k / 32) * SZ_Q8_1);
     return b200_launch_quantize_aos(ctx, x, k, nrows, 1, 1, x_row_stride_bytes, x_row_stride_bytes * nrows, x_row_stride_bytes * nrows, y);
 }
 
@@ -289,12 +338,16 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
             aligned16(a->data, a->nb[1], a->nb[2], a->nb[3]) && aligned16(b->data, b->nb[1], b->nb[2], b->nb[3]) &&
             b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
-            return b200_launch_gemv_q4k(ctx, P, (int) n, batches);
+            const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
+            pending_push(ctx, d, !late);
+            return b200_launch_gemv_q4k(ctx, P, (int) n, batches, late);
         }
+        pending_push(ctx, d, true);
         int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
         if (rc) return rc;
         return b200_launch_gemv_generic(ctx, a->type, P, (int) n, batches);
     }
+    pending_push(ctx, d, true);
 
     int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
     if (rc) return rc;
@@ -316,6 +369,9 @@ int b200_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_nb1, int n_expe
                 int32_t * ids_src1, int32_t * expert_bounds) {
     if (!ctx || !ids || !ids_src1 || !expert_bounds || ids_nb1 % 4 != 0) { b200_set_error("mm_ids: bad argument"); return B200_E_ARG; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    ctx->n_pend = 2;
+    ctx->pend_lo[0] = (const char *) ids_src1;      ctx->pend_hi[0] = (const char *) (ids_src1 + (size_t) n_tokens * n_used);
+    ctx->pend_lo[1] = (const char *) expert_bounds; ctx->pend_hi[1] = (const char *) (expert_bounds + n_expert + 1);
     return b200_launch_mm_ids(ctx, ids, ids_nb1 / 4, n_expert, n_used, n_tokens, ids_src1, expert_bounds);
 }
 
@@ -345,14 +401,18 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
         if (as->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant &&
             aligned16(as->data, as->nb[1], as->nb[2], 0) && aligned16(b->data, b->nb[1], b->nb[2], 0) &&
             b200_gemv_q4k_smem(1, k) <= ctx->smem_optin) {
-            return b200_launch_gemv_q4k(ctx, P, 1, n_pairs);
+            const bool late = can_defer_wait(ctx, b, ids);
+            pending_push(ctx, c, !late);
+            return b200_launch_gemv_q4k(ctx, P, 1, n_pairs, late);
         }
+        pending_push(ctx, c, true);
         int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
         if (rc) return rc;
         return b200_launch_gemv_generic(ctx, as->type, P, 1, n_pairs);
     }
 
     // prefill: gather the pairs by expert on the device, then column tiles that never straddle two experts
+    pending_push(ctx, c, true);
     uint8_t * extra = nullptr;
     const size_t extra_bytes = (size_t) (n_pairs + n_expert + 1) * sizeof(int32_t);
     int rc = quantize_into_ws(ctx, b, extra_bytes, &P.act, &extra);

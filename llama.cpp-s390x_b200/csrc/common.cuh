@@ -82,6 +82,13 @@ struct b200_ctx {
     int          max_gemv_cols;   // columns per batch handled by the GEMV family (<= 8)
     int          pdl;             // programmatic dependent launch for back-to-back GEMVs
     int          fuse_quant;      // 1: GEMV quantizes activations in its prologue (no separate launch)
+    int          gemv_cfg;        // CTA shape of the n=1 Q4_K GEMV: 0 = 32 warps x 1 CTA/SM, 1 = 16x2, 2 = 8x4, 3 = 16x1
+    // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)
+    const char * pend_lo[16];
+    const char * pend_hi[16];
+    int          n_pend;
+    int          defer_wait;      // 1: allow the deferred dependency wait
+    int          noop;            // debugging: GEMV kernels return immediately (measures the launch floor)
 };
 
 int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes);   // ensures ctx->ws_size >= nbytes
@@ -122,6 +129,6 @@ __device__ __forceinline__ void q4k_scale_min(int j, uint32_t s0, uint32_t s1, u
     }
 }
 
-// position (in 16-byte chunks) of activation chunk t inside the swizzled shared-memory copy of one column:
-// chunks {4g+h} and {4g+h+2} of consecutive superblocks land in distinct 16-byte bank groups
-__device__ __forceinline__ int act_swz(int t) { return t ^ (((t >> 3) & 1) << 1); }
+
+
+

@@ -13,8 +13,8 @@
 //                   global planes.  One warp per weight row, one 32-weight unit per lane per step.
 //   gemv_q4k      — the Q4_K fast path: persistent CTAs (one per SM), activations quantized IN the prologue into
 //                   swizzled shared memory (no separate launch, no q8 round trip through HBM), weights streamed with
-//                   coalesced 128-bit no-allocate loads (8 lanes per 144-byte superblock), d/dmin/6-bit scales applied
-//                   in registers, warp-shuffle reduction.
+//                   coalesced 128-bit no-allocate loads (4 lanes per 144-byte superblock), d/dmin/6-bit scales applied
+//                   in registers, one fragment of software prefetch, warp-shuffle reduction.
 #include "mm_problem.cuh"
 #include "quantize.cuh"
 
@@ -166,57 +166,144 @@ gemv_generic(const mm_problem P) {
 // Q4_K fast path
 // ------------------------------------------------------------------------------------------------------------------
 // Shared memory per CTA: NC columns of { int8 qs[k] in swizzled 16-byte chunks ; float2 (d, d*sum) [k/32] }.
-// A lane's task = (superblock sb, 16-byte qs chunk c in 0..7): chunk c holds bytes [16h, 16h+16) of 64-group g = c/2
-// (h = c%2) => low nibbles are elements [16h,16h+16) of sub-block 2g, high nibbles the same elements of sub-block 2g+1
-// (dequantize_row_q4_K, ggml/src/ggml-quants.c:1467-1489).  8 consecutive lanes cover one superblock, a warp covers 4
-// superblocks = 576 contiguous bytes per step with two LDG.128 per lane (header + chunk).
+//
+// A lane's task = (superblock sb, 64-group g in 0..3): the 32 qs bytes of group g hold sub-block 2g in their low nibbles
+// and sub-block 2g+1 in their high nibbles (dequantize_row_q4_K, ggml/src/ggml-quants.c:1467-1489).  4 consecutive lanes
+// cover one 144-byte superblock (header re-read by the 4 lanes: one sector), a warp covers 8 superblocks = 1152
+// contiguous bytes per step with three LDG.128 per lane.  High nibbles are NOT shifted down: (q & 0xF0F0F0F0) is fed to
+// an unsigned x signed dp4a and the factor 1/16 is folded into the float scale (exact).
+//
+// Activation chunk t (16 int8) of a column lives at 16-byte slot  t ^ (((t>>3)&1)<<1) ^ ((t>>4)&1): for a lane the four
+// chunks of its 64-byte activation group are permuted by a lane-constant x in 0..3, and the 8 lanes of every LDS.128
+// phase hit 8 distinct 16-byte bank groups.
+__device__ __forceinline__ int act_slot(int t) { return t ^ (((t >> 3) & 1) << 1) ^ ((t >> 4) & 1); }
+
+__device__ __forceinline__ int dp4a_us(uint32_t a_unsigned, int b_signed, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_unsigned), "r"(b_signed), "r"(c));
+    return d;
+}
+
+struct q4k_frag { uint4 hdr, q0, q1; };
+
+// whole-row prefetch into L2 (address and size are multiples of 16: a Q4_K row is 144-byte superblocks)
+__device__ __forceinline__ void l2_prefetch(const void * p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void q4k_load(q4k_frag & f, const uint8_t * wrow, const int sb, const int g) {
+    const uint8_t * bp = wrow + (size_t) sb * SZ_Q4_K;
+    f.hdr = ld_stream_u4(bp);
+    f.q0  = ld_stream_u4(bp + 16 + 32 * g);
+    f.q1  = ld_stream_u4(bp + 32 + 32 * g);
+}
+
 template <int NC>
-__device__ __forceinline__ void q4k_task(const uint4 hdr, const uint4 q, const int sb, const int c, const int8_t * s_qs,
+__device__ __forceinline__ void q4k_task(const q4k_frag & f, const int sb, const int g, const int x, const uint8_t * s_qs,
                                          const float2 * s_ds, const int k, float (&acc)[NC]) {
-    const int g = c >> 1, h = c & 1;
-    int sc0, mn0, sc1, mn1;
-    q4k_scale_min(2 * g,     hdr.y, hdr.z, hdr.w, sc0, mn0);
-    q4k_scale_min(2 * g + 1, hdr.y, hdr.z, hdr.w, sc1, mn1);
-    const float2 dm  = __half22float2(*reinterpret_cast<const half2 *>(&hdr.x));
-    const float dsc0 = dm.x * (float) sc0, dsc1 = dm.x * (float) sc1;
-    // the min term covers the whole 32-block: only the h == 0 lane of each pair subtracts it
-    const float dmn0 = h == 0 ? dm.y * (float) mn0 : 0.0f;
-    const float dmn1 = h == 0 ? dm.y * (float) mn1 : 0.0f;
-    const int lo0 = q.x & 0x0F0F0F0F, lo1 = q.y & 0x0F0F0F0F, lo2 = q.z & 0x0F0F0F0F, lo3 = q.w & 0x0F0F0F0F;
-    const int hi0 = (q.x >> 4) & 0x0F0F0F0F, hi1 = (q.y >> 4) & 0x0F0F0F0F, hi2 = (q.z >> 4) & 0x0F0F0F0F, hi3 = (q.w >> 4) & 0x0F0F0F0F;
-    const int ib0 = sb * 8 + 2 * g;            // activation block of sub-block 2g; 2g+1 is the next one
-    const int t0  = ib0 * 2 + h;               // 16-byte chunk index inside the column
-    const int p0  = act_swz(t0), p1 = act_swz(t0 + 2);
+    // (sc, m) of sub-blocks 2g and 2g+1 as byte pairs — get_scale_min_k4, ggml/src/ggml-quants.c:818-825
+    const int sh = 16 * (g & 1);
+    const uint32_t a = f.hdr.y >> sh, b = f.hdr.z >> sh, c = f.hdr.w >> sh;
+    uint32_t scp, mnp;
+    if (g < 2) {
+        scp = a & 0x3f3f;
+        mnp = b & 0x3f3f;
+    } else {
+        scp = (c & 0x0f0f) | ((a & 0xc0c0) >> 2);
+        mnp = ((c >> 4) & 0x0f0f) | ((b & 0xc0c0) >> 2);
+    }
+    const float2 dm  = __half22float2(*reinterpret_cast<const half2 *>(&f.hdr.x));
+    const float dsc0 = dm.x * (float) (scp & 0xff);
+    const float dsc1 = dm.x * (float) (scp >> 8) * 0.0625f;          // high nibbles enter the dot product as 16*q
+    const float dmn0 = dm.y * (float) (mnp & 0xff);
+    const float dmn1 = dm.y * (float) (mnp >> 8);
+    const uint32_t m_lo = 0x0F0F0F0Fu, m_hi = 0xF0F0F0F0u;
+    const int ib0 = sb * 8 + 2 * g;                                   // activation block of sub-block 2g
+    const int off = (sb * 16 + 4 * g) * 16;                           // byte offset of the lane's 64-byte activation group
 #pragma unroll
     for (int col = 0; col < NC; ++col) {
-        const uint4 * cq = reinterpret_cast<const uint4 *>(s_qs + (size_t) col * k);
-        const uint4 a0 = cq[p0], a1 = cq[p1];
-        const float2 e0 = s_ds[col * (k >> 5) + ib0], e1 = s_ds[col * (k >> 5) + ib0 + 1];
-        int s0 = __dp4a(lo0, (int) a0.x, 0); s0 = __dp4a(lo1, (int) a0.y, s0); s0 = __dp4a(lo2, (int) a0.z, s0); s0 = __dp4a(lo3, (int) a0.w, s0);
-        int s1 = __dp4a(hi0, (int) a1.x, 0); s1 = __dp4a(hi1, (int) a1.y, s1); s1 = __dp4a(hi2, (int) a1.z, s1); s1 = __dp4a(hi3, (int) a1.w, s1);
+        const uint8_t * cq = s_qs + (size_t) col * k + off;
+        const uint4 a0 = *reinterpret_cast<const uint4 *>(cq + 16 * (0 ^ x));
+        const uint4 a1 = *reinterpret_cast<const uint4 *>(cq + 16 * (1 ^ x));
+        const uint4 a2 = *reinterpret_cast<const uint4 *>(cq + 16 * (2 ^ x));
+        const uint4 a3 = *reinterpret_cast<const uint4 *>(cq + 16 * (3 ^ x));
+        const float4 e = *reinterpret_cast<const float4 *>(s_ds + col * (k >> 5) + ib0);   // (d, d*sum) of blocks ib0, ib0+1
+        int s0 = __dp4a((int) (f.q0.x & m_lo), (int) a0.x, 0);
+        s0 = __dp4a((int) (f.q0.y & m_lo), (int) a0.y, s0); s0 = __dp4a((int) (f.q0.z & m_lo), (int) a0.z, s0); s0 = __dp4a((int) (f.q0.w & m_lo), (int) a0.w, s0);
+        s0 = __dp4a((int) (f.q1.x & m_lo), (int) a1.x, s0); s0 = __dp4a((int) (f.q1.y & m_lo), (int) a1.y, s0);
+        s0 = __dp4a((int) (f.q1.z & m_lo), (int) a1.z, s0); s0 = __dp4a((int) (f.q1.w & m_lo), (int) a1.w, s0);
+        int s1 = dp4a_us(f.q0.x & m_hi, (int) a2.x, 0);
+        s1 = dp4a_us(f.q0.y & m_hi, (int) a2.y, s1); s1 = dp4a_us(f.q0.z & m_hi, (int) a2.z, s1); s1 = dp4a_us(f.q0.w & m_hi, (int) a2.w, s1);
+        s1 = dp4a_us(f.q1.x & m_hi, (int) a3.x, s1); s1 = dp4a_us(f.q1.y & m_hi, (int) a3.y, s1);
+        s1 = dp4a_us(f.q1.z & m_hi, (int) a3.z, s1); s1 = dp4a_us(f.q1.w & m_hi, (int) a3.w, s1);
         float r = acc[col];
-        r = fmaf(dsc0 * e0.x, (float) s0, r);
-        r = fmaf(dsc1 * e1.x, (float) s1, r);
-        r = fmaf(-dmn0, e0.y, r);
-        r = fmaf(-dmn1, e1.y, r);
+        r = fmaf(dsc0 * e.x, (float) s0, r);
+        r = fmaf(dsc1 * e.z, (float) s1, r);
+        r = fmaf(-dmn0, e.y, r);
+        r = fmaf(-dmn1, e.w, r);
         acc[col] = r;
     }
 }
 
-template <int NC, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32, 1)
-gemv_q4k(const mm_problem P) {
+template <int NC, int NWARPS, int MINB, int NBUF>
+__global__ void __launch_bounds__(NWARPS * 32, MINB)
+gemv_q4k(const mm_problem P, const int flags) {
+    // flags: < 0 launch-floor probe (ctx option "noop"); bit 0 = PDL launch (prefetch weights before the dependency wait);
+    //        bit 1 = X / ids are NOT written by any kernel still in flight (abi.cu tracks that): the wait moves from
+    //        "before reading X" to "before the first store", so this kernel's prologue and streaming overlap the previous
+    //        kernel's tail, while completion stays transitive (nobody finishes before its predecessor).
+    if (flags < 0) return;
+    const int  prefetch_before_wait = flags & 1;
+    const bool late_wait            = (flags & 2) != 0;
     extern __shared__ __align__(16) uint8_t smem[];
     const int k   = (int) P.k;
     const int nbk = k >> 5;
-    int8_t * s_qs = reinterpret_cast<int8_t *>(smem);
-    float2 * s_ds = reinterpret_cast<float2 *>(smem + (size_t) NC * k);
+    const int nsb = k >> 8;
+    uint8_t * s_qs = smem;
+    float2 *  s_ds = reinterpret_cast<float2 *>(smem + (size_t) NC * k);
+
+    const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int     sbl  = lane >> 2, g = lane & 3;
+    const int     x    = ((g >> 1) << 1) ^ (sbl & 1);
+    const int64_t rlo  = (P.m * (int64_t) blockIdx.x) / gridDim.x;
+    const int64_t rhi  = (P.m * (int64_t) (blockIdx.x + 1)) / gridDim.x;
+
+    // Weights are never produced by a kernel of this path, so this warp's first rows are requested before waiting on the
+    // previous kernel (PDL) and before the activation prologue (first fragment into registers).  The main loop keeps the
+    // register pipeline one fragment ahead (load next, then consume current).  NBUF=1 adds a bulk L2 prefetch two rows
+    // ahead; measured slower on B200 (output head 65 us vs 54 us), kept only as a tuning switch.
+    const int nit = (nsb + 7) >> 3;                       // steps per row; (row, it) are warp-uniform, sb differs per lane
+    const uint32_t row_bytes = (uint32_t) nsb * SZ_Q4_K;
+    int64_t  row = rlo + warp;
+    int      it  = 0, sb = sbl;
+    q4k_frag cur;
+    const uint8_t * Wm = nullptr;
+    auto first_loads = [&]() {
+        if (NBUF > 0 && lane == 0) {
+            if (row < rhi)          l2_prefetch(Wm + row * P.nb01, row_bytes);
+            if (row + NWARPS < rhi) l2_prefetch(Wm + (row + NWARPS) * P.nb01, row_bytes);
+        }
+        if (row < rhi && sb < nsb) q4k_load(cur, Wm + row * P.nb01, sb, g);
+    };
+
+    const bool early = prefetch_before_wait && (P.mode == MM_PLAIN || late_wait);
+    mm_cols<NC> C;
+    bool live = true;
+    if (early) {
+        live = mm_resolve<NC>(P, blockIdx.y, C);
+        Wm = C.W;
+        if (live) first_loads();
+    }
 
     // the previous kernel in the stream may have produced X or the ids (no-op unless launched with the PDL attribute)
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-
-    mm_cols<NC> C;
-    if (!mm_resolve<NC>(P, blockIdx.y, C)) return;             // block-uniform
+    if (late_wait) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    else           asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (!early) {
+        live = mm_resolve<NC>(P, blockIdx.y, C);
+        Wm = C.W;
+        if (live) first_loads();
+    }
+    if (!live) return;                                          // block-uniform
 
     // ---- prologue: quantize the NC activation columns into shared memory (bit-exact Q8_1 values) ----
     {
@@ -225,7 +312,7 @@ gemv_q4k(const mm_problem P) {
         const int groups = NWARPS * 4;
         const int rounds = (total + groups - 1) / groups;
         int blk = threadIdx.x >> 3;
-        for (int it = 0; it < rounds; ++it, blk += groups) {
+        for (int r = 0; r < rounds; ++r, blk += groups) {
             const bool ok  = blk < total;
             const int  b   = ok ? blk : total - 1;
             const int  col = b / nbk;
@@ -237,48 +324,41 @@ gemv_q4k(const mm_problem P) {
             const q8_part qp = quantize_q8_1_part(v);
             if (ok) {
                 const int t = ib * 2 + (sub >> 2);
-                *reinterpret_cast<uint32_t *>(s_qs + (size_t) col * k + 16 * act_swz(t) + 4 * (sub & 3)) = qp.packed;
+                *reinterpret_cast<uint32_t *>(s_qs + (size_t) col * k + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
                 if (sub == 0) s_ds[col * nbk + ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
             }
         }
     }
     __syncthreads();
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (!late_wait) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    bool waited = !late_wait;
 
     // ---- main loop: this CTA's contiguous share of the rows, one warp per row ----
-    const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t rlo  = (P.m * (int64_t) blockIdx.x) / gridDim.x;
-    const int64_t rhi  = (P.m * (int64_t) (blockIdx.x + 1)) / gridDim.x;
-    const int     sbl  = lane >> 3, c = lane & 7;
-    const int     nsb  = k >> 8;
-    for (int64_t row = rlo + warp; row < rhi; row += NWARPS) {
-        const uint8_t * wrow = C.W + row * P.nb01;
-        float acc[NC];
+    float acc[NC];
 #pragma unroll
-        for (int col = 0; col < NC; ++col) acc[col] = 0.0f;
-        // 4 steps (16 superblocks = k 4096) per batch of loads: 8 x 128-bit loads in flight per lane
-        for (int sb0 = 0; sb0 < nsb; sb0 += 16) {
-            uint4 hdr[4], q[4];
+    for (int col = 0; col < NC; ++col) acc[col] = 0.0f;
+    while (row < rhi) {
+        int64_t nrow  = row;
+        int     nit_i = it + 1;
+        if (nit_i >= nit) { nrow = row + NWARPS; nit_i = 0; }
+        const int nsbi = nit_i * 8 + sbl;
+        q4k_frag nxt;
+        if (nrow < rhi && nsbi < nsb) q4k_load(nxt, Wm + nrow * P.nb01, nsbi, g);
+        if (NBUF > 0 && it == 0 && lane == 0 && row + 2 * NWARPS < rhi) l2_prefetch(Wm + (row + 2 * NWARPS) * P.nb01, row_bytes);
+        if (sb < nsb) q4k_task<NC>(cur, sb, g, x, s_qs, s_ds, k, acc);
+        if (nrow != row) {
+            if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int sb = sb0 + 4 * u + sbl;
-                if (sb < nsb) {
-                    const uint8_t * bp = wrow + (size_t) sb * SZ_Q4_K;
-                    hdr[u] = ld_stream_u4(bp);
-                    q[u]   = ld_stream_u4(bp + 16 + 16 * c);
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int sb = sb0 + 4 * u + sbl;
-                if (sb < nsb) q4k_task<NC>(hdr[u], q[u], sb, c, s_qs, s_ds, k, acc);
+            for (int col = 0; col < NC; ++col) {
+                const float s = warp_sum(acc[col]);
+                if (lane == 0 && col < C.nc) mm_store(P, C.y[col], row, s);
+                acc[col] = 0.0f;
             }
         }
-#pragma unroll
-        for (int col = 0; col < NC; ++col) {
-            const float s = warp_sum(acc[col]);
-            if (lane == 0 && col < C.nc) mm_store(P, C.y[col], row, s);
-        }
+        cur = nxt;
+        row = nrow;
+        it  = nit_i;
+        sb  = nsbi;
     }
 }
 
@@ -302,16 +382,16 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
     return B200_OK;
 }
 
-template <int NC, int NWARPS>
-int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem) {
-    auto kern = gemv_q4k<NC, NWARPS>;
+template <int NC, int NWARPS, int MINB, int NBUF>
+int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem, bool late_wait) {
+    auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF>;
     static bool attr_done[16] = {};            // per device
     if (!attr_done[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
         attr_done[ctx->device & 15] = true;
     }
     // persistent: the SMs are shared evenly by the tiles (batches / (token, slot) pairs)
-    int64_t ctas = ctx->sm_count / tiles;
+    int64_t ctas = (int64_t) ctx->sm_count * MINB / tiles;
     if (ctas < 1) ctas = 1;
     const int64_t max_useful = (P.m + NWARPS - 1) / NWARPS;
     if (ctas > max_useful) ctas = max_useful;
@@ -325,7 +405,7 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
     cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, P));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, P, ctx->noop ? -1 : (ctx->pdl ? 1 | (late_wait ? 2 : 0) : 0)));
     ctx->launches++;
     return B200_OK;
 }
@@ -352,20 +432,26 @@ int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int
 size_t b200_gemv_q4k_smem(int nc, int64_t k) { return (size_t) nc * (size_t) (k + k / 4); }
 
 // f32 activations in P.X (quantized in the kernel prologue); nc = columns of every tile (exact, 1..8)
-int b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles) {
+int b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait) {
     if (tiles <= 0 || P.m <= 0) return B200_OK;
     if (tiles > 65535) { b200_set_error("gemv_q4k: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
     const size_t smem = b200_gemv_q4k_smem(nc, P.k);
     if (smem > ctx->smem_optin) { b200_set_error("gemv_q4k: %zu B of shared memory needed", smem); return B200_E_ARG; }
+    if (nc == 1) {
+        switch (ctx->gemv_cfg) {
+            case 1:  return launch_q4k_t<1, 16, 2, 0>(ctx, P, tiles, smem, late_wait);
+            case 2:  return launch_q4k_t<1, 32, 1, 1>(ctx, P, tiles, smem, late_wait);      // + bulk L2 row prefetch (measured: slower)
+            default: return launch_q4k_t<1, 32, 1, 0>(ctx, P, tiles, smem, late_wait);
+        }
+    }
     switch (nc) {
-        case 1: return launch_q4k_t<1, 32>(ctx, P, tiles, smem);
-        case 2: return launch_q4k_t<2, 32>(ctx, P, tiles, smem);
-        case 3: return launch_q4k_t<3, 16>(ctx, P, tiles, smem);
-        case 4: return launch_q4k_t<4, 16>(ctx, P, tiles, smem);
-        case 5: return launch_q4k_t<5, 16>(ctx, P, tiles, smem);
-        case 6: return launch_q4k_t<6, 16>(ctx, P, tiles, smem);
-        case 7: return launch_q4k_t<7, 16>(ctx, P, tiles, smem);
-        case 8: return launch_q4k_t<8, 16>(ctx, P, tiles, smem);
+        case 2: return launch_q4k_t<2, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 3: return launch_q4k_t<3, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 4: return launch_q4k_t<4, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 5: return launch_q4k_t<5, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 6: return launch_q4k_t<6, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 7: return launch_q4k_t<7, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
+        case 8: return launch_q4k_t<8, 16, 1, 0>(ctx, P, tiles, smem, late_wait);
     }
     b200_set_error("gemv_q4k: nc=%d out of range", nc);
     return B200_E_ARG;

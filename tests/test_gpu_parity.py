@@ -90,7 +90,7 @@ def test_q4k_fast_kernel_matches_generic_kernel(pkg, gpu_ctx, n):
         slow = pkg.mul_mat(gpu_ctx, refenv.Q4_K, W, X).cpu().numpy()
     finally:
         gpu_ctx.set_option("force_generic", 0)
-    assert nmse(slow, fast) < 1e-9
+    assert nmse(slow, fast) < 1e-6      # the fast path keeps the fp32 d of each activation block, the planes its fp16 rounding
 
 
 @pytest.mark.parametrize("name", list(TYPES))
@@ -205,3 +205,36 @@ def test_llama3_shapes_sampled_rows_and_slices(pkg, gpu_ctx, orc, name, m, k):
     lo, hi = 16000 if m > 20000 else 1024, 16000 + 4096 if m > 20000 else 2048
     ys = pkg.mul_mat(gpu_ctx, t, Wd[lo:hi], Xd[:1])
     assert torch.equal(ys, y1[:, lo:hi])
+
+
+# ---- host-buffer entry (the e2e path) and back-to-back launches ---------------------------------------------------------------
+def test_mul_mat_host_and_back_to_back_dependencies(pkg, gpu_ctx, orc):
+    """(a) b200_mul_mat_host: H2D x, GEMV, D2H y per call with a different x every call; (b) a chain y1 = W1 x, y2 = W2 y1 launched
+    back to back: the second GEMV's input IS the first one's output, so the deferred dependency wait must not be taken"""
+    import ctypes as C
+    import torch
+    L = pkg.lib()
+    rng = np.random.default_rng(77)
+    m, k = 2048, 2048
+    W1, W2 = random_blocks(refenv.Q4_K, m, k, rng), random_blocks(refenv.Q4_K, m, k, rng, scale=2.0)
+    W1d, W2d = dev(W1), dev(W2)
+    hctx = pkg.Context(0)
+    xh = torch.empty((1, k)).pin_memory()
+    yh = torch.empty((1, m)).pin_memory()
+    for i in range(6):
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        xh.copy_(torch.from_numpy(x))
+        rc = L.b200_mul_mat_host(hctx.handle, refenv.Q4_K, W1d.data_ptr(), m, k, xh.data_ptr(), 1, yh.data_ptr())
+        assert rc == 0, L.b200_last_error()
+        assert nmse(oracle_mul_mat(orc, refenv.Q4_K, W1, x), yh.numpy()) <= NMSE_TOL
+    hctx.close()
+    for i in range(4):
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        xd = dev(x)
+        y1 = pkg.mul_mat(gpu_ctx, refenv.Q4_K, W1d, xd)
+        y2 = pkg.mul_mat(gpu_ctx, refenv.Q4_K, W2d, y1)          # depends on the kernel right before it
+        y3 = pkg.mul_mat(gpu_ctx, refenv.Q4_K, W1d, xd)          # independent: may overlap y2's tail
+        w1 = oracle_mul_mat(orc, refenv.Q4_K, W1, x)
+        assert nmse(w1, y1.cpu().numpy()) <= NMSE_TOL
+        assert nmse(oracle_mul_mat(orc, refenv.Q4_K, W2, y1.cpu().numpy()), y2.cpu().numpy()) <= NMSE_TOL
+        assert torch.equal(y1, y3)
