@@ -187,7 +187,7 @@ def run_gpu(args):
     # ---- e2e: host buffers through b200_mul_mat_host (N == 1 semantics on every rank's shard) ---------------------------------
     e2e = None
     shapes = None
-    if world == 1:
+    if world == 1 and not args.no_e2e:
         import ctypes as C
         L = pkg.lib()
         hctx = pkg.Context(local)                             # own stream
@@ -213,8 +213,8 @@ def run_gpu(args):
                "h2d_bytes_per_step": int(sum(k * 4 * c for _, _, k, c in LLAMA3_8B)),
                "d2h_bytes_per_step": int(sum(m * 4 * c for _, m, _, c in LLAMA3_8B)),
                "api": "b200_mul_mat_host (C ABI, pinned host x -> H2D -> GEMV -> D2H y, per matmul)"}
-        if args.shapes:
-            shapes = per_shape(torch, pkg, ctx, stream, ops)
+    if world == 1 and args.shapes:
+        shapes = per_shape(torch, pkg, ctx, stream, ops)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -239,7 +239,7 @@ def run_gpu(args):
             out["e2e"] = e2e
         if shapes:
             out["shapes"] = shapes
-        if world == 1:
+        if world == 1 and args.cpu_seconds > 0:
             out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -354,7 +354,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
-    ap.add_argument("--cpu-seconds", type=float, default=16.0)
+    ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -45,6 +45,7 @@ __device__ __forceinline__ void mm_store(const mm_problem & P, float * ycol_ptr,
     ycol_ptr[row] = v;
     if (P.n_peers > 0) {
         const int64_t col = (ycol_ptr - P.Y) / P.m;
+#pragma unroll 1
         for (int p = 0; p < P.n_peers; ++p) P.peer_Y[p][col * P.peer_m + P.peer_row0 + row] = v;
     }
 }

@@ -393,6 +393,9 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
     // persistent: the SMs are shared evenly by the tiles (batches / (token, slot) pairs)
     int64_t ctas = (int64_t) ctx->sm_count * MINB / tiles;
     if (ctas < 1) ctas = 1;
+    // Small matrices deliberately do NOT spread over every SM: one row per warp is the useful maximum, and the SMs left free
+    // let the next GEMV of the stream start (PDL + deferred wait) while this one is still running — measured 2.4 us per
+    // 1024x4096 matmul with 32 CTAs against 4.1 us with 148.
     const int64_t max_useful = (P.m + NWARPS - 1) / NWARPS;
     if (ctas > max_useful) ctas = max_useful;
     cudaLaunchConfig_t cfg = {};
