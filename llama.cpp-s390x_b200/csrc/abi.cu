@@ -16,7 +16,8 @@ size_t b200_gemv_q4k_smem(int nc, int64_t k);
 int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
-int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_cols_total);
+int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
+size_t b200_gemm_tc_scratch(const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
                        int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
 
@@ -349,11 +350,13 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
     }
     pending_push(ctx, d, true);
 
+    if (n_peers == 0 && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
+        const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(P, n * batches, 0));
+        if (rc) return rc;
+        return b200_launch_gemm_tc(ctx, a->type, P, n * batches, 0);
+    }
     int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
     if (rc) return rc;
-    if (n_peers == 0 && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
-        return b200_launch_gemm_tc(ctx, a->type, P, n * batches);
-    }
     const int64_t tiles = batches * ((n + 7) / 8);
     return b200_launch_gemv_generic(ctx, a->type, P, 8, tiles);
 }
@@ -415,16 +418,25 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
     pending_push(ctx, c, true);
     uint8_t * extra = nullptr;
     const size_t extra_bytes = (size_t) (n_pairs + n_expert + 1) * sizeof(int32_t);
+    P.mode = MM_ID_SORTED;
+    if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, as->type, P)) {
+        // scratch: [ids_src1 | expert_bounds | fp16 activations gathered by expert | per-position scale and dst column]
+        int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(P, n_pairs, extra_bytes));
+        if (rc) return rc;
+        int32_t * ids_src1 = (int32_t *) ctx->ws;
+        int32_t * bounds   = ids_src1 + n_pairs;
+        rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
+        if (rc) return rc;
+        P.ids_src1 = ids_src1; P.expert_bounds = bounds;
+        return b200_launch_gemm_tc(ctx, as->type, P, n_pairs, extra_bytes);
+    }
     int rc = quantize_into_ws(ctx, b, extra_bytes, &P.act, &extra);
     if (rc) return rc;
     int32_t * ids_src1 = (int32_t *) extra;
     int32_t * bounds   = ids_src1 + n_pairs;
     rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
     if (rc) return rc;
-    P.mode = MM_ID_SORTED; P.ids_src1 = ids_src1; P.expert_bounds = bounds;
-    if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, as->type, P)) {
-        return b200_launch_gemm_tc(ctx, as->type, P, n_pairs);
-    }
+    P.ids_src1 = ids_src1; P.expert_bounds = bounds;
     const int64_t tiles = (n_pairs + 7) / 8 + n_expert;
     if (tiles > 65535) { b200_set_error("mul_mat_id: too many column tiles"); return B200_E_UNSUPPORTED; }
     return b200_launch_gemv_generic(ctx, as->type, P, 8, tiles);
