@@ -111,6 +111,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
     ctx->gemv_cfg      = env_int("GGML_B200_GEMV_CFG", 0);
+    ctx->tc_cluster    = env_int("GGML_B200_TC_CLUSTER", 0);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
@@ -149,6 +150,8 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
     else if (!strcmp(name, "gemv_cfg"))      slot = &ctx->gemv_cfg;
+    else if (!strcmp(name, "tc_cluster"))    slot = &ctx->tc_cluster;
+    else if (!strcmp(name, "tc_dbg"))        slot = &ctx->tc_dbg;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }

@@ -27,12 +27,13 @@ constexpr int TC_M        = 128;     // weight rows per CTA (UMMA M)
 constexpr int TC_KS       = 64;      // K elements per stage (one 128-byte swizzled row of fp16)
 constexpr int TC_A_BYTES  = TC_M * 128;
 constexpr int TC_PRODUCER = 256;     // 8 warps: thread -> (row = t & 127, half = t >> 7)
-constexpr int TC_THREADS  = TC_PRODUCER + 64;   // + TMA warp + MMA warp
+constexpr int TC_THREADS  = 512;     // 8 producer warps, TMA warp, MMA warp, 4 epilogue warps, 2 spare (whole warpgroups)
 
 template <int NT> struct tc_cfg {
     static constexpr int STAGES  = NT == 256 ? 4 : 6;
     static constexpr int B_BYTES = NT * 128;
     static constexpr int SMEM    = STAGES * (TC_A_BYTES + B_BYTES) + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
 };
 
 struct tc_args {
@@ -47,6 +48,8 @@ struct tc_args {
     int     mode;
     int     n_expert;
     const int32_t * expert_bounds;
+    int64_t n_tiles;            // row tiles x column tiles (upper bound for MUL_MAT_ID) x batches
+    int     dbg;                // timing experiments only: 1 no weight loads, 2 no convert/STS, 4 no TMA, 8 no MMA, 16 no stores
 };
 
 // ---- activations: f32 -> normalised fp16, K order (0,2,1,3) inside every group of 4 -------------------------------------
@@ -158,10 +161,13 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
             hi[2 * j]     = h2_bits(__hfma2(__hfma2(c, sixteenth, m64), s_hi, nb_hi));
             hi[2 * j + 1] = h2_bits(__hfma2(__hfma2(d, sixteenth, m64), s_hi, nb_hi));
         }
-        out[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]); slot[0] = 2 * h;
-        out[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]); slot[1] = 2 * h + 1;
-        out[2] = make_uint4(hi[0], hi[1], hi[2], hi[3]); slot[2] = 4 + 2 * h;
-        out[3] = make_uint4(hi[4], hi[5], hi[6], hi[7]); slot[3] = 4 + 2 * h + 1;
+        // half 0 stores slots (0,1,4,5), half 1 stores (6,7,2,3): every 8-lane STS phase hits 8 distinct bank groups
+        const uint4 l0 = make_uint4(lo[0], lo[1], lo[2], lo[3]), l1 = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        const uint4 h0 = make_uint4(hi[0], hi[1], hi[2], hi[3]), h1 = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        out[0] = h ? h0 : l0; slot[0] = h ? 6 : 0;
+        out[1] = h ? h1 : l1; slot[1] = h ? 7 : 1;
+        out[2] = h ? l0 : h0; slot[2] = h ? 2 : 4;
+        out[3] = h ? l1 : h1; slot[3] = h ? 3 : 5;
     }
 };
 
@@ -227,6 +233,44 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
 
 
 // ---- the GEMM ---------------------------------------------------------------------------------------------------------
+// Persistent: CTA c works on tiles c, c + gridDim.x, ...  (row tile fastest, so CTAs running together share an activation
+// tile in L2).  16 warps: 0-7 weight producers (4 pairs), 8 TMA, 9 MMA, 10-13 epilogue (one per TMEM lane quadrant).  Two
+// TMEM accumulators, so the epilogue of tile i overlaps the main loop of tile i + 1.
+struct tc_tile {
+    const uint8_t * W;
+    int row0, pos0, nvalid;
+};
+
+__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int64_t T, tc_tile & t) {
+    const int row_tiles = (a.m + TC_M - 1) / TC_M;
+    const int rt = (int) (T % row_tiles);
+    T /= row_tiles;
+    t.row0 = rt * TC_M;
+    t.W = a.W;
+    if (a.mode == MM_PLAIN) {
+        const int col_tiles = (a.n + NT - 1) / NT;
+        const int ct = (int) (T % col_tiles), batch = (int) (T / col_tiles);
+        const int i12 = batch % a.ne12, i13 = batch / a.ne12;
+        t.W += (int64_t) (i12 / a.r2) * a.nb02 + (int64_t) (i13 / a.r3) * a.nb03;
+        t.pos0   = batch * a.n + ct * NT;
+        t.nvalid = min(NT, a.n - ct * NT);
+        return true;
+    }
+    int ct = (int) T, e = 0, lo = 0, hi = 0;
+    for (; e < a.n_expert; ++e) {
+        lo = __ldg(a.expert_bounds + e);
+        hi = __ldg(a.expert_bounds + e + 1);
+        const int nt = (hi - lo + NT - 1) / NT;
+        if (ct < nt) break;
+        ct -= nt;
+    }
+    if (e >= a.n_expert) return false;
+    t.W += (int64_t) e * a.nb02;
+    t.pos0   = lo + ct * NT;
+    t.nvalid = min(NT, hi - t.pos0);
+    return true;
+}
+
 template <int TYPE, int NT>
 __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmB, const tc_args a) {
     using cfg = tc_cfg<NT>;
@@ -235,52 +279,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t base  = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sA    = base;
     const uint32_t sB    = base + STAGES * TC_A_BYTES;
-    const uint32_t sBar  = sB + STAGES * cfg::B_BYTES;          // full[STAGES], empty[STAGES], acc_full, tmem slot
-    const uint32_t bFull = sBar, bEmpty = sBar + 8 * STAGES, bAcc = sBar + 16 * STAGES, sTmem = bAcc + 8;
+    const uint32_t sBar  = sB + STAGES * cfg::B_BYTES;
+    const uint32_t bFull = sBar, bEmpty = sBar + 8 * STAGES, bAccFull = sBar + 16 * STAGES, bAccEmpty = bAccFull + 16, sTmem = bAccEmpty + 16;
     uint8_t * gen_base   = smem_raw + (base - tc::smem_u32(smem_raw));
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-
-    // ---- which tile ------------------------------------------------------------------------------------------------
-    const int row0 = blockIdx.x * TC_M;
-    const uint8_t * W = a.W;
-    int pos0, nvalid;                   // first activation position of the tile, live columns
-    if (a.mode == MM_PLAIN) {
-        const int batch = blockIdx.z;
-        const int i12 = batch % a.ne12, i13 = batch / a.ne12;
-        W += (int64_t) (i12 / a.r2) * a.nb02 + (int64_t) (i13 / a.r3) * a.nb03;
-        const int c0 = blockIdx.y * NT;
-        pos0   = batch * a.n + c0;
-        nvalid = min(NT, a.n - c0);
-    } else {
-        int t = blockIdx.y, e = 0, lo = 0, hi = 0;
-        for (; e < a.n_expert; ++e) {
-            lo = __ldg(a.expert_bounds + e);
-            hi = __ldg(a.expert_bounds + e + 1);
-            const int nt = (hi - lo + NT - 1) / NT;
-            if (t < nt) break;
-            t -= nt;
-        }
-        if (e >= a.n_expert) return;    // uniform for the whole CTA, before any barrier or allocation
-        W += (int64_t) e * a.nb02;
-        pos0   = lo + t * NT;
-        nvalid = min(NT, hi - pos0);
-    }
     const int nk = a.k / TC_KS;
+    const int64_t n_tiles = a.n_tiles;
 
-    // ---- one-time setup ----------------------------------------------------------------------------------------------
     if (warp == 8) {
         if (lane == 0) {
             tc::tma_prefetch_desc(&tmB);
             for (int s = 0; s < STAGES; ++s) {
-                tc::mbar_init(bFull + 8 * s, TC_PRODUCER / 32 + 1);     // 8 producer warps + the TMA thread's expect_tx
-                tc::mbar_init(bEmpty + 8 * s, 1);                       // one tcgen05.commit
+                tc::mbar_init(bFull + 8 * s, 2 + 1);        // the 2 warps of a producer pair + the TMA thread's expect_tx
+                tc::mbar_init(bEmpty + 8 * s, 1);           // one tcgen05.commit
             }
-            tc::mbar_init(bAcc, 1);
+            for (int i = 0; i < 2; ++i) {
+                tc::mbar_init(bAccFull + 8 * i, 1);         // tcgen05.commit after the last K step of a tile
+                tc::mbar_init(bAccEmpty + 8 * i, 4);        // the 4 epilogue warps
+            }
             tc::mbar_fence_init();
         }
         __syncwarp();
-        tc::tmem_alloc(sTmem, NT);
+        tc::tmem_alloc(sTmem, 2 * NT);
     }
     tc::tc_fence_before();
     __syncthreads();
@@ -290,82 +311,149 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
 
     if (warp < 8) {
         // ===== weight producers: raw blocks -> fp16 -> swizzled K-major A tile ==========================================
-        const int r = tid & 127, h = tid >> 7;
-        const int grow = min(row0 + r, a.m - 1);
-        const uint8_t * wrow = W + (int64_t) grow * a.nb01;
-        const uint32_t a_row = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
-        w_frag<TYPE> cur, nxt;
-        cur.load(wrow, 0, h);
-        for (int it = 0; it < nk; ++it) {
-            const int s = it % STAGES;
-            if (it + 1 < nk) nxt.load(wrow, it + 1, h);
-            uint4 out[4]; int slot[4];
-            cur.convert(it, h, out, slot);
-            tc::mbar_wait(bEmpty + 8 * s, ((it / STAGES) & 1) ^ 1);
-            uint8_t * dst = gen_base + s * TC_A_BYTES + a_row;
+        // Warp pair p produces every 4th pipeline stage on its own (64 rows per warp, 4 (row, half) tasks per lane, adjacent
+        // lanes share a row).  The cross-proxy fence drains a thread's outstanding loads, so the loads for the pair's next
+        // stage are issued right after it and have a whole period (4 stage times) to land.
+        const int pair = warp >> 1, h = lane & 1;
+        const int rbase = 64 * (warp & 1) + (lane >> 1);
+        uint32_t a_off[4];
+        int rsw[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4 *>(dst + ((slot[c] ^ (r & 7)) << 4)) = out[c];
+        for (int j = 0; j < 4; ++j) {
+            const int r = rbase + 16 * j;
+            a_off[j] = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
+            rsw[j]   = r & 7;
+        }
+        w_frag<TYPE> f[4];
+        // g = running stage index over all tiles of this CTA; (tile ordinal, k step) = (g / nk, g % nk)
+        int64_t T = blockIdx.x;
+        tc_tile t;
+        while (T < n_tiles && !tc_resolve(a, NT, T, t)) T += gridDim.x;
+        int it = pair;                              // k step of the fragment held in f (tile T)
+        while (T < n_tiles && it >= nk) {           // nk < 4: this pair may have nothing in a tile
+            it -= nk;
+            do { T += gridDim.x; } while (T < n_tiles && !tc_resolve(a, NT, T, t));
+        }
+        int64_t g = 0;                              // stages of earlier tiles
+        int64_t gcur = pair;                        // global stage index of f
+        (void) g;
+        if (T < n_tiles && !(a.dbg & 1)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) f[j].load(t.W + (int64_t) min(t.row0 + rbase + 16 * j, a.m - 1) * a.nb01, it, h);
+        }
+        while (T < n_tiles) {
+            const int s = (int) (gcur % STAGES);
+            tc::mbar_wait(bEmpty + 8 * s, (uint32_t) ((gcur / STAGES) & 1) ^ 1);
+            uint8_t * dst = gen_base + s * TC_A_BYTES;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (a.dbg & 2) break;
+                uint4 out[4]; int slot[4];
+                f[j].convert(it, h, out, slot);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4 *>(dst + a_off[j] + ((slot[c] ^ rsw[j]) << 4)) = out[c];
+            }
             tc::fence_proxy_async();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(bFull + 8 * s);
-            cur = nxt;
-        }
-        // ===== epilogue: TMEM -> registers -> global ======================================================================
-        tc::mbar_wait(bAcc, 0);
-        tc::tc_fence_after();
-        const int q = warp & 3, half = warp >> 2;
-        const int row = row0 + 32 * q + lane;
-#pragma unroll 1
-        for (int c0 = half * (NT / 2); c0 < (half + 1) * (NT / 2); c0 += 32) {
-            if (c0 >= nvalid) break;                                  // warp-uniform
-            uint32_t v[32];
-            tc::tmem_ld32(tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) c0, v);
-            tc::tmem_ld_wait();
+            // advance to this pair's next stage (possibly in a later tile) and start its loads
+            it += 4; gcur += 4;
+            while (T < n_tiles && it >= nk) {
+                it -= nk;
+                do { T += gridDim.x; } while (T < n_tiles && !tc_resolve(a, NT, T, t));
+            }
+            if (T < n_tiles && !(a.dbg & 1)) {
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-                const int p = c0 + c;
-                if (p < nvalid && row < a.m) {
-                    const float sc = __ldg(a.colscale + pos0 + p);
-                    const int64_t yc = a.ycol ? (int64_t) __ldg(a.ycol + pos0 + p) : (int64_t) (pos0 + p);
-                    a.Y[yc * a.m + row] = __uint_as_float(v[c]) * sc;
-                }
+                for (int j = 0; j < 4; ++j) f[j].load(t.W + (int64_t) min(t.row0 + rbase + 16 * j, a.m - 1) * a.nb01, it, h);
             }
         }
-        tc::tc_fence_before();
     } else if (warp == 8) {
         // ===== TMA: activation tiles ========================================================================================
         if (lane == 0) {
-            for (int it = 0; it < nk; ++it) {
-                const int s = it % STAGES;
-                tc::mbar_wait(bEmpty + 8 * s, ((it / STAGES) & 1) ^ 1);
-                tc::mbar_arrive_expect_tx(bFull + 8 * s, cfg::B_BYTES);
-                tc::tma_load_2d(sB + s * cfg::B_BYTES, &tmB, bFull + 8 * s, it * TC_KS, pos0);
+            int64_t gcur = 0;
+            tc_tile t;
+            for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
+                if (!tc_resolve(a, NT, T, t)) continue;
+                for (int it = 0; it < nk; ++it, ++gcur) {
+                    const int s = (int) (gcur % STAGES);
+                    tc::mbar_wait(bEmpty + 8 * s, (uint32_t) ((gcur / STAGES) & 1) ^ 1);
+                    if (a.dbg & 4) { tc::mbar_arrive(bFull + 8 * s); continue; }
+                    tc::mbar_arrive_expect_tx(bFull + 8 * s, cfg::B_BYTES);
+                    tc::tma_load_2d(sB + s * cfg::B_BYTES, &tmB, bFull + 8 * s, it * TC_KS, t.pos0);
+                }
             }
         }
-    } else {
+    } else if (warp == 9) {
         // ===== MMA issue ====================================================================================================
         if (lane == 0) {
             constexpr uint32_t idesc = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, TC_M, NT);
-            for (int it = 0; it < nk; ++it) {
-                const int s = it % STAGES;
-                tc::mbar_wait(bFull + 8 * s, (it / STAGES) & 1);
+            int64_t gcur = 0;
+            int     ti = 0;                          // ordinal of the tile within this CTA
+            tc_tile t;
+            for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
+                if (!tc_resolve(a, NT, T, t)) continue;
+                const int acc = ti & 1;
+                tc::mbar_wait(bAccEmpty + 8 * acc, (uint32_t) ((ti >> 1) & 1) ^ 1);
                 tc::tc_fence_after();
-                const uint64_t da = tc::umma_desc_sw128(sA + s * TC_A_BYTES);
-                const uint64_t db = tc::umma_desc_sw128(sB + s * cfg::B_BYTES);
+                for (int it = 0; it < nk; ++it, ++gcur) {
+                    const int s = (int) (gcur % STAGES);
+                    tc::mbar_wait(bFull + 8 * s, (uint32_t) ((gcur / STAGES) & 1));
+                    tc::tc_fence_after();
+                    const uint64_t da = tc::umma_desc_sw128(sA + s * TC_A_BYTES);
+                    const uint64_t db = tc::umma_desc_sw128(sB + s * cfg::B_BYTES);
 #pragma unroll
-                for (int kk = 0; kk < TC_KS / 16; ++kk) {
-                    tc::umma_f16(tmem, da + 2 * kk, db + 2 * kk, idesc, (it | kk) != 0);
+                    for (int kk = 0; kk < TC_KS / 16; ++kk) {
+                        if (a.dbg & 8) break;
+                        tc::umma_f16(tmem + acc * NT, da + 2 * kk, db + 2 * kk, idesc, (it | kk) != 0);
+                    }
+                    tc::tc_commit(bEmpty + 8 * s);
                 }
-                tc::tc_commit(bEmpty + 8 * s);
+                tc::tc_commit(bAccFull + 8 * acc);
+                ++ti;
             }
-            tc::tc_commit(bAcc);
+        }
+    } else if (warp < 14) {
+        // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
+        const int q = warp & 3;
+        int ti = 0;
+        tc_tile t;
+        for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
+            if (!tc_resolve(a, NT, T, t)) continue;
+            const int acc = ti & 1;
+            tc::mbar_wait(bAccFull + 8 * acc, (uint32_t) ((ti >> 1) & 1));
+            tc::tc_fence_after();
+            const int row = t.row0 + 32 * q + lane;
+#pragma unroll 1
+            for (int c0 = 0; c0 < NT; c0 += 32) {
+                if (c0 >= t.nvalid) break;                            // warp-uniform
+                uint32_t v[32];
+                tc::tmem_ld32(tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) (acc * NT + c0), v);
+                // this lane fetches the scale / destination column of position c0 + lane; shuffles hand them round
+                const int  pl  = t.pos0 + c0 + lane;
+                const bool pok = c0 + lane < t.nvalid;
+                const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
+                const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
+                tc::tmem_ld_wait();
+                if (!(a.dbg & 16)) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
+                        const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
+                        if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
+                    }
+                }
+            }
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
+            ++ti;
         }
     }
     __syncthreads();
     if (warp == 8) {
         __syncwarp();
         tc::tc_fence_after();
-        tc::tmem_dealloc(tmem, NT);
+        tc::tmem_dealloc(tmem, 2 * NT);
     }
 }
 
@@ -387,24 +475,26 @@ encode_tiled_fn get_encode() {
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
 
 template <int TYPE, int NT>
-int launch_one(b200_ctx * ctx, const CUtensorMap & tm, const tc_args & a, dim3 grid) {
+int launch_one(b200_ctx * ctx, const CUtensorMap & tm, const tc_args & a) {
     static bool configured[16] = {};
+    auto kern = mmq_tc_f16_kernel<TYPE, NT>;
     if (!configured[ctx->device & 15]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc_f16_kernel<TYPE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT>::SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT>::SMEM));
         configured[ctx->device & 15] = true;
     }
-    mmq_tc_f16_kernel<TYPE, NT><<<grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tm, a);
+    const unsigned grid = (unsigned) (a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count);
+    kern<<<grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tm, a);
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
 }
 
 template <int NT>
-int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tm, const tc_args & a, dim3 grid) {
+int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
-        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tm, a, grid);
-        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tm, a, grid);
-        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT>(ctx, tm, a, grid);
+        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tm, a);
+        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tm, a);
+        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT>(ctx, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -419,7 +509,6 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (bits & (type == B200_TYPE_Q4_K ? 15 : 3)) return 0;
     if (((uintptr_t) P.X | (uintptr_t) P.nb11 | (uintptr_t) P.nb12 | (uintptr_t) P.nb13) & 15) return 0;
     if (P.mode == MM_ID_PAIRS) return 0;
-    if (P.mode == MM_PLAIN && P.ne12 * P.ne13 > 65535) return 0;
     if (tc_cfg<256>::SMEM > ctx->smem_optin) return 0;
     return 1;
 }
@@ -449,6 +538,7 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
     CUtensorMap tm;
     const cuuint64_t gdim[2]    = {(cuuint64_t) P.k, (cuuint64_t) n_pos};
     const cuuint64_t gstride[1] = {(cuuint64_t) P.k * sizeof(__half)};
+    const int64_t row_tiles = (P.m + TC_M - 1) / TC_M;
     const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) NT};
     const cuuint32_t estr[2]    = {1, 1};
     const CUresult cr = get_encode()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -461,11 +551,11 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
+    a.dbg = ctx->tc_dbg;
 
     const int64_t col_tiles = P.mode == MM_PLAIN ? (n + NT - 1) / NT : (n_pos + NT - 1) / NT + P.n_expert;
-    if (col_tiles > 65535) { b200_set_error("tcgen05 GEMM: too many column tiles"); return B200_E_UNSUPPORTED; }
-    const dim3 grid((unsigned) ((P.m + TC_M - 1) / TC_M), (unsigned) col_tiles, (unsigned) batches);
-    return NT == 128 ? launch_type<128>(ctx, type, tm, a, grid) : launch_type<256>(ctx, type, tm, a, grid);
+    a.n_tiles = row_tiles * col_tiles * batches;
+    return NT == 128 ? launch_type<128>(ctx, type, tm, a) : launch_type<256>(ctx, type, tm, a);
 }
 
 size_t b200_gemm_tc_scratch(const mm_problem & P, int64_t n_pos, size_t ws_used) {

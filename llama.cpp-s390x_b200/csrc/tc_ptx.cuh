@@ -42,6 +42,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void * tmap, uin
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// the same box written into the same smem offset of every CTA in `mask`; each destination's mbarrier gets the bytes
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void * tmap, uint32_t bar, int c0, int c1, uint16_t mask) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const void * tmap) {
     asm volatile("prefetch.tensormap [%0];" :: "l"(tmap) : "memory");
 }
@@ -58,6 +63,15 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {                            // arrives once all prior MMAs retire
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tc_commit_mc(uint32_t bar, uint16_t mask) {             // ... on the barrier of every CTA in `mask`
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
 }
 
 // K-major operand tile in shared memory, 128-byte rows, SWIZZLE_128B, 8-row atoms 1024 B apart (canonical layout
