@@ -3,38 +3,48 @@
 // Replaces, for large n, the reference's per-column vec_dot loop (ggml/src/ggml-cpu/ggml-cpu.c:1151-1439) and plays the
 // role of ggml-cuda's mul_mat_q / cuBLAS branch (ggml/src/ggml-cuda/mmq.cuh:3446-3783, ggml-cuda.cu:1413-1530) — designed
 // from the hardware up, not from those kernels:
-//   * D[128 weight rows x NT activation columns] per CTA, accumulator in TMEM (fp32), one tcgen05.mma per 32 bytes of K;
-//   * the weight tile (A operand) never exists in HBM in expanded form: 8 producer warps stream the raw quant blocks,
-//     dequantise them in registers to fp16 (exact integer -> fp16 conversion by exponent-bias tricks, then ONE rounding
-//     in `q * scale - min`) and store them straight into the 128-byte-swizzled K-major UMMA layout;
+//   * persistent CTAs; D[128 weight rows x NT activation columns] per tile, fp32 accumulator in TMEM, two accumulators so
+//     the epilogue of one tile overlaps the main loop of the next;
+//   * the weight tile (A operand) never exists in HBM in expanded form: TMA streams the RAW quant blocks (a box of
+//     128 rows x 144 bytes) into a shared-memory ring, 8 converter warps dequantise them to fp16 (exact integer -> fp16
+//     conversion by exponent-bias tricks, then ONE rounding in `q * scale - min`) and store them straight into the
+//     128-byte-swizzled K-major UMMA layout;
 //   * the activation tile (B operand) is fetched by TMA from an fp16 copy of src1 that `tc_act_f16_kernel` writes once per
 //     call (per-column power-of-two normalisation so neither overflow nor fp16 underflow can occur; undone exactly in
 //     the epilogue).  Within every 4 consecutive K elements both operands use the order (0,2,1,3), which is what nibble
 //     unpacking produces for free — a dot product does not care;
-//   * one warp issues TMA, one warp issues MMA, 4-stage mbarrier ring; the producer warps double as epilogue warps
-//     (tcgen05.ld -> scale -> coalesced f32 stores, or the MUL_MAT_ID scatter).
+//   * warp roles: 0-7 converters, 8 TMA, 9 MMA issue, 10-13 epilogue (tcgen05.ld -> scale -> coalesced f32 stores, or the
+//     MUL_MAT_ID scatter); three mbarrier rings (raw weights, A tiles, B tiles).
 // Numerics: fp16 operands (2^-12 relative) + fp32 accumulation — closer to the exact product than the reference's own
-// Q8_1 activation quantisation; NMSE vs ggml-cpu ~1e-5, far inside test-backend-ops' 5e-4.
+// Q8_1 activation quantisation; NMSE vs ggml-cpu ~1.5e-5 (that IS the Q8_1 noise), far inside test-backend-ops' 5e-4.
 #include <cuda.h>
 #include <cuda_fp16.h>
+#include <cstdio>
 
 #include "mm_problem.cuh"
 #include "tc_ptx.cuh"
 
 namespace {
 
-constexpr int TC_M        = 128;     // weight rows per CTA (UMMA M)
-constexpr int TC_KS       = 64;      // K elements per stage (one 128-byte swizzled row of fp16)
+constexpr int TC_M        = 128;     // weight rows per CTA tile (UMMA M)
+constexpr int TC_KS       = 64;      // K elements per MMA stage (one 128-byte swizzled row of fp16)
 constexpr int TC_A_BYTES  = TC_M * 128;
-constexpr int TC_PRODUCER = 256;     // 8 warps: thread -> (row = t & 127, half = t >> 7)
-constexpr int TC_THREADS  = 512;     // 8 producer warps, TMA warp, MMA warp, 4 epilogue warps, 2 spare (whole warpgroups)
+constexpr int TC_RAW_ROW  = 144;     // bytes of raw blocks per row and raw slot (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 + pad)
+constexpr int TC_RAW_BYTES = TC_M * TC_RAW_ROW;
+constexpr int TC_THREADS  = 512;     // 8 converter warps, TMA warp, MMA warp, 4 epilogue warps, 2 spare (whole warpgroups)
+constexpr int TC_A_SLOTS  = 3, TC_RAW_SLOTS = 2;
 
 template <int NT> struct tc_cfg {
-    static constexpr int STAGES  = NT == 256 ? 4 : 6;
+    static constexpr int B_SLOTS = NT == 256 ? 4 : 6;
     static constexpr int B_BYTES = NT * 128;
-    static constexpr int SMEM    = STAGES * (TC_A_BYTES + B_BYTES) + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int SMEM    = B_SLOTS * B_BYTES + TC_A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * TC_RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
     static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
+    static_assert(SMEM <= 232448, "exceeds the 227 KB a CTA can opt into");
 };
+
+// K elements covered by one raw slot (144 bytes per row)
+template <int TYPE> struct raw_k          { static constexpr int value = 256; };
+template <> struct raw_k<B200_TYPE_Q8_0>  { static constexpr int value = 128; };
 
 struct tc_args {
     const uint8_t * W;
@@ -42,6 +52,8 @@ struct tc_args {
     int     m, k;
     int     n;                  // activation columns per batch
     int     ne12, r2, r3;       // batch dims (MM_PLAIN)
+    int     ne02;               // weight matrices per ne03 slice
+    int     raw_step;           // 16-bit elements of a weight row per raw slot (row bytes of raw_k K elements / 2)
     float * Y;
     const float *   colscale;   // per activation position: 2^-e that undoes the fp16 normalisation
     const int32_t * ycol;       // per activation position: output column (MUL_MAT_ID scatter); NULL = identity
@@ -49,7 +61,6 @@ struct tc_args {
     int     n_expert;
     const int32_t * expert_bounds;
     int64_t n_tiles;            // row tiles x column tiles (upper bound for MUL_MAT_ID) x batches
-    int     dbg;                // timing experiments only: 1 no weight loads, 2 no convert/STS, 4 no TMA, 8 no MMA, 16 no stores
 };
 
 // ---- activations: f32 -> normalised fp16, K order (0,2,1,3) inside every group of 4 -------------------------------------
@@ -106,15 +117,12 @@ __global__ void __launch_bounds__(256) tc_act_f16_kernel(const mm_problem P, __h
     }
 }
 
-// ---- weight fragments: what one producer thread holds for one stage (64 K elements of its row, its half of them) ----------
-__device__ __forceinline__ uint32_t ld_nc_u32(const void * p) {
-    uint32_t v; asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+// ---- weight fragments: what one converter thread handles for one stage (64 K elements of its row, its half of them) ------
+__device__ __forceinline__ uint32_t lds_u32(const uint32_t a) {
+    uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v;
 }
-__device__ __forceinline__ uint32_t ld_nc_u16(const void * p) {
-    uint16_t v; asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(p)); return v;
-}
-__device__ __forceinline__ uint4 ld_nc_u4(const void * p) {
-    uint4 v; asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p)); return v;
+__device__ __forceinline__ uint4 lds_u4(const uint32_t a) {
+    uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v;
 }
 __device__ __forceinline__ uint32_t h2_bits(const __half2 h) { return *reinterpret_cast<const uint32_t *>(&h); }
 __device__ __forceinline__ __half2  bits_h2(const uint32_t u) { return *reinterpret_cast<const __half2 *>(&u); }
@@ -135,14 +143,14 @@ template <int TYPE> struct w_frag;
 // super-block sb; thread half h owns qs bytes [16h, 16h+16) of the group: low nibbles -> sub-block 2g, high -> 2g+1.
 template <> struct w_frag<B200_TYPE_Q4_K> {
     uint4 hdr, q;
-    __device__ __forceinline__ void load(const uint8_t * row, const int it, const int h) {
-        const uint8_t * sb = row + (int64_t) (it >> 2) * SZ_Q4_K;
-        hdr = ld_nc_u4(sb);
-        q   = ld_nc_u4(sb + 16 + 32 * (it & 3) + 16 * h);
+    // row = shared-memory address of this row's super-block; sub = 64-group inside it
+    __device__ __forceinline__ void load(const uint32_t row, const int sub, const int h) {
+        hdr = lds_u4(row);
+        q   = lds_u4(row + 16 + 32 * sub + 16 * h);
     }
     // 4 chunks of 8 fp16; chunk slot indices within the 128-byte row returned in `slot`
-    __device__ __forceinline__ void convert(const int it, const int h, uint4 (&out)[4], int (&slot)[4]) const {
-        const int g = it & 3;
+    __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+        const int g = sub;
         int sc0, mn0, sc1, mn1;
         q4k_scale_min(2 * g,     hdr.y, hdr.z, hdr.w, sc0, mn0);
         q4k_scale_min(2 * g + 1, hdr.y, hdr.z, hdr.w, sc1, mn1);
@@ -175,11 +183,11 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
 // block 2it+h: low nibbles = elements 0..15, high nibbles = elements 16..31, value (q - 8) * d.
 template <> struct w_frag<B200_TYPE_Q4_0> {
     uint32_t w[5];
-    __device__ __forceinline__ void load(const uint8_t * row, const int it, const int h) {
-        const uint8_t * b = row + (int64_t) (2 * it + h) * SZ_Q4_0 - 2 * h;      // 4-byte aligned (18 * odd - 2)
+    // row = shared-memory address of this row's 8 blocks; sub = pair of blocks inside them
+    __device__ __forceinline__ void load(const uint32_t row, const int sub, const int h) {
+        const uint32_t b = row + (2 * sub + h) * SZ_Q4_0 - 2 * h;              // 4-byte aligned (18 * odd - 2)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) w[j] = ld_nc_u32(b + 4 * j);
-        w[4] = h ? ld_nc_u32(b + 16) : ld_nc_u16(b + 16);
+        for (int j = 0; j < 5; ++j) w[j] = lds_u32(b + 4 * j);
     }
     __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
@@ -205,11 +213,11 @@ template <> struct w_frag<B200_TYPE_Q4_0> {
 // Q8_0 (ggml-common.h:241-246, dequantize_row_q8_0 ggml-quants.c:392-406): thread half h owns block 2it+h, value q * d.
 template <> struct w_frag<B200_TYPE_Q8_0> {
     uint32_t w[9];
-    __device__ __forceinline__ void load(const uint8_t * row, const int it, const int h) {
-        const uint8_t * b = row + (int64_t) (2 * it + h) * SZ_Q8_0 - 2 * h;      // 4-byte aligned (34 * odd - 2)
+    // row = shared-memory address of this row's 4 blocks (+ 8 bytes of padding); sub = pair of blocks inside them
+    __device__ __forceinline__ void load(const uint32_t row, const int sub, const int h) {
+        const uint32_t b = row + (2 * sub + h) * SZ_Q8_0 - 2 * h;              // 4-byte aligned (34 * odd - 2)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) w[j] = ld_nc_u32(b + 4 * j);
-        w[8] = h ? ld_nc_u32(b + 32) : ld_nc_u16(b + 32);
+        for (int j = 0; j < 9; ++j) w[j] = lds_u32(b + 4 * j);
     }
     __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
@@ -234,10 +242,10 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
 
 // ---- the GEMM ---------------------------------------------------------------------------------------------------------
 // Persistent: CTA c works on tiles c, c + gridDim.x, ...  (row tile fastest, so CTAs running together share an activation
-// tile in L2).  16 warps: 0-7 weight producers (4 pairs), 8 TMA, 9 MMA, 10-13 epilogue (one per TMEM lane quadrant).  Two
-// TMEM accumulators, so the epilogue of tile i overlaps the main loop of tile i + 1.
+// tile in L2).  All roles walk the same tile list and the same running stage counter, so ring slots and mbarrier phases
+// carry over from one tile to the next.
 struct tc_tile {
-    const uint8_t * W;
+    int mat;            // weight matrix index (batch / expert) = 3rd TMA coordinate
     int row0, pos0, nvalid;
 };
 
@@ -246,12 +254,11 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
     const int rt = (int) (T % row_tiles);
     T /= row_tiles;
     t.row0 = rt * TC_M;
-    t.W = a.W;
     if (a.mode == MM_PLAIN) {
         const int col_tiles = (a.n + NT - 1) / NT;
         const int ct = (int) (T % col_tiles), batch = (int) (T / col_tiles);
         const int i12 = batch % a.ne12, i13 = batch / a.ne12;
-        t.W += (int64_t) (i12 / a.r2) * a.nb02 + (int64_t) (i13 / a.r3) * a.nb03;
+        t.mat    = (i13 / a.r3) * a.ne02 + i12 / a.r2;
         t.pos0   = batch * a.n + ct * NT;
         t.nvalid = min(NT, a.n - ct * NT);
         return true;
@@ -265,23 +272,34 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
         ct -= nt;
     }
     if (e >= a.n_expert) return false;
-    t.W += (int64_t) e * a.nb02;
+    t.mat    = e;
     t.pos0   = lo + ct * NT;
     t.nvalid = min(NT, hi - t.pos0);
     return true;
 }
 
+#ifdef TC_TRACE_ENABLE     // development aid: per-stage clock64 stamps of CTA 0 (build with -DTC_TRACE_ENABLE, run tools/tc_trace.py)
+__device__ long long g_tc_trace[6][128];
+#define TC_TRACE(role, gg) do { if (blockIdx.x == 0 && (gg) < 128) g_tc_trace[role][gg] = clock64(); } while (0)
+#else
+#define TC_TRACE(role, gg) do { } while (0)
+#endif
+
 template <int TYPE, int NT>
-__global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmB, const tc_args a) {
+__global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmB,
+                                                                   const tc_args a) {
     using cfg = tc_cfg<NT>;
-    constexpr int STAGES = cfg::STAGES;
+    constexpr int BS  = cfg::B_SLOTS, AS = TC_A_SLOTS, RS = TC_RAW_SLOTS;
+    constexpr int SPR = raw_k<TYPE>::value / TC_KS;          // MMA stages per raw slot
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t base  = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t sA    = base;
-    const uint32_t sB    = base + STAGES * TC_A_BYTES;
-    const uint32_t sBar  = sB + STAGES * cfg::B_BYTES;
-    const uint32_t bFull = sBar, bEmpty = sBar + 8 * STAGES, bAccFull = sBar + 16 * STAGES, bAccEmpty = bAccFull + 16, sTmem = bAccEmpty + 16;
-    uint8_t * gen_base   = smem_raw + (base - tc::smem_u32(smem_raw));
+    const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sB   = base;
+    const uint32_t sA   = sB + BS * cfg::B_BYTES;
+    const uint32_t sRaw = sA + AS * TC_A_BYTES;
+    const uint32_t sBar = sRaw + RS * TC_RAW_BYTES;
+    const uint32_t bBFull = sBar, bBEmpty = bBFull + 8 * BS, bAFull = bBEmpty + 8 * BS, bAEmpty = bAFull + 8 * AS;
+    const uint32_t bRFull = bAEmpty + 8 * AS, bREmpty = bRFull + 8 * RS, bAccFull = bREmpty + 8 * RS, bAccEmpty = bAccFull + 16;
+    const uint32_t sTmem  = bAccEmpty + 16;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nk = a.k / TC_KS;
@@ -289,15 +307,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
 
     if (warp == 8) {
         if (lane == 0) {
+            tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
-            for (int s = 0; s < STAGES; ++s) {
-                tc::mbar_init(bFull + 8 * s, 2 + 1);        // the 2 warps of a producer pair + the TMA thread's expect_tx
-                tc::mbar_init(bEmpty + 8 * s, 1);           // one tcgen05.commit
-            }
-            for (int i = 0; i < 2; ++i) {
-                tc::mbar_init(bAccFull + 8 * i, 1);         // tcgen05.commit after the last K step of a tile
-                tc::mbar_init(bAccEmpty + 8 * i, 4);        // the 4 epilogue warps
-            }
+            for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
+            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 8); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 8 converter warps / commit
+            for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 8); }   // expect_tx / 8 converter warps
+            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4); } // commit / 4 epilogue warps
             tc::mbar_fence_init();
         }
         __syncwarp();
@@ -309,118 +324,131 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
 
+    // Ring positions are kept as (slot, phase) pairs advanced by hand: the single-thread roles below are latency chains,
+    // so no divisions and no 64-bit arithmetic inside the stage loops.
     if (warp < 8) {
-        // ===== weight producers: raw blocks -> fp16 -> swizzled K-major A tile ==========================================
-        // Warp pair p produces every 4th pipeline stage on its own (64 rows per warp, 4 (row, half) tasks per lane, adjacent
-        // lanes share a row).  The cross-proxy fence drains a thread's outstanding loads, so the loads for the pair's next
-        // stage are issued right after it and have a whole period (4 stage times) to land.
-        const int pair = warp >> 1, h = lane & 1;
-        const int rbase = 64 * (warp & 1) + (lane >> 1);
-        uint32_t a_off[4];
-        int rsw[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int r = rbase + 16 * j;
-            a_off[j] = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
-            rsw[j]   = r & 7;
-        }
-        w_frag<TYPE> f[4];
-        // g = running stage index over all tiles of this CTA; (tile ordinal, k step) = (g / nk, g % nk)
-        int64_t T = blockIdx.x;
+        // ===== converters: raw blocks (smem) -> fp16 -> swizzled K-major A tile ===========================================
+        // every warp takes 16 rows of every stage; adjacent lanes share a row (its two 32-element halves)
+        const int r = 16 * warp + (lane >> 1), h = lane & 1;
+        const uint32_t raw_row = sRaw + (uint32_t) (r * TC_RAW_ROW);
+        const uint32_t a_row   = sA + (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
+        int as = 0, rs = 0, sub = 0;
+        uint32_t a_ph = 0, r_ph = 0;
+        int tg = 0; (void) tg;
         tc_tile t;
-        while (T < n_tiles && !tc_resolve(a, NT, T, t)) T += gridDim.x;
-        int it = pair;                              // k step of the fragment held in f (tile T)
-        while (T < n_tiles && it >= nk) {           // nk < 4: this pair may have nothing in a tile
-            it -= nk;
-            do { T += gridDim.x; } while (T < n_tiles && !tc_resolve(a, NT, T, t));
-        }
-        int64_t g = 0;                              // stages of earlier tiles
-        int64_t gcur = pair;                        // global stage index of f
-        (void) g;
-        if (T < n_tiles && !(a.dbg & 1)) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) f[j].load(t.W + (int64_t) min(t.row0 + rbase + 16 * j, a.m - 1) * a.nb01, it, h);
-        }
-        while (T < n_tiles) {
-            const int s = (int) (gcur % STAGES);
-            tc::mbar_wait(bEmpty + 8 * s, (uint32_t) ((gcur / STAGES) & 1) ^ 1);
-            uint8_t * dst = gen_base + s * TC_A_BYTES;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (a.dbg & 2) break;
+        for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
+            if (!tc_resolve(a, NT, T, t)) continue;
+            uint32_t skew = 0;                               // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
+            for (int it = 0; it < nk; ++it) {
+                if (sub == 0) tc::mbar_wait(bRFull + 8 * rs, r_ph);
+                w_frag<TYPE> f;
                 uint4 out[4]; int slot[4];
-                f[j].convert(it, h, out, slot);
+                f.load(raw_row + rs * TC_RAW_BYTES + skew, sub, h);
+                f.convert(sub, h, out, slot);
+                tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1);
+                if (tid == 0) TC_TRACE(2, tg);
+                const uint32_t dst = a_row + as * TC_A_BYTES;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4 *>(dst + a_off[j] + ((slot[c] ^ rsw[j]) << 4)) = out[c];
-            }
-            tc::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bFull + 8 * s);
-            // advance to this pair's next stage (possibly in a later tile) and start its loads
-            it += 4; gcur += 4;
-            while (T < n_tiles && it >= nk) {
-                it -= nk;
-                do { T += gridDim.x; } while (T < n_tiles && !tc_resolve(a, NT, T, t));
-            }
-            if (T < n_tiles && !(a.dbg & 1)) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) f[j].load(t.W + (int64_t) min(t.row0 + rbase + 16 * j, a.m - 1) * a.nb01, it, h);
+                for (int c = 0; c < 4; ++c) {
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + ((slot[c] ^ (r & 7)) << 4)),
+                                 "r"(out[c].x), "r"(out[c].y), "r"(out[c].z), "r"(out[c].w) : "memory");
+                }
+                tc::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    tc::mbar_arrive(bAFull + 8 * as);
+                    if (sub == SPR - 1) tc::mbar_arrive(bREmpty + 8 * rs);      // this warp is done reading the raw slot
+                    if (warp == 0) TC_TRACE(3, tg);
+                    if (warp == 7) TC_TRACE(5, tg);
+                }
+                ++tg;
+                if (++as == AS) { as = 0; a_ph ^= 1; }
+                if (++sub == SPR) {
+                    sub = 0;
+                    if (TYPE == B200_TYPE_Q8_0) skew ^= 8u;
+                    if (++rs == RS) { rs = 0; r_ph ^= 1; }
+                }
             }
         }
     } else if (warp == 8) {
-        // ===== TMA: activation tiles ========================================================================================
-        if (lane == 0) {
-            int64_t gcur = 0;
+        // ===== TMA: raw weight blocks and activation tiles (whole warp in step, one elected lane issues) ===================
+        {
+            int bs = 0, rs = 0, sub = 0;
+            uint32_t b_ph = 0, r_ph = 0;
+            int tg = 0; (void) tg;
             tc_tile t;
             for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
                 if (!tc_resolve(a, NT, T, t)) continue;
-                for (int it = 0; it < nk; ++it, ++gcur) {
-                    const int s = (int) (gcur % STAGES);
-                    tc::mbar_wait(bEmpty + 8 * s, (uint32_t) ((gcur / STAGES) & 1) ^ 1);
-                    if (a.dbg & 4) { tc::mbar_arrive(bFull + 8 * s); continue; }
-                    tc::mbar_arrive_expect_tx(bFull + 8 * s, cfg::B_BYTES);
-                    tc::tma_load_2d(sB + s * cfg::B_BYTES, &tmB, bFull + 8 * s, it * TC_KS, t.pos0);
+                int x = 0, odd = 0;                           // position of the next raw slot in the row (16-bit elements)
+                for (int it = 0; it < nk; ++it) {
+                    if (sub == 0) {
+                        tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1);
+                        if (tc::elect_one()) {
+                            tc::mbar_arrive_expect_tx(bRFull + 8 * rs, TC_RAW_BYTES);
+                            tc::tma_load_3d(sRaw + rs * TC_RAW_BYTES, &tmW, bRFull + 8 * rs, x - (TYPE == B200_TYPE_Q8_0 ? 4 * odd : 0), t.row0, t.mat);
+                        }
+                        __syncwarp();
+                        x += a.raw_step; odd ^= 1;
+                    }
+                    tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1);
+                    if (lane == 0) TC_TRACE(4, tg);
+                    ++tg;
+                    if (tc::elect_one()) {
+                        tc::mbar_arrive_expect_tx(bBFull + 8 * bs, cfg::B_BYTES);
+                        tc::tma_load_2d(sB + bs * cfg::B_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0);
+                    }
+                    __syncwarp();
+                    if (++bs == BS) { bs = 0; b_ph ^= 1; }
+                    if (++sub == SPR) { sub = 0; if (++rs == RS) { rs = 0; r_ph ^= 1; } }
                 }
             }
         }
     } else if (warp == 9) {
-        // ===== MMA issue ====================================================================================================
-        if (lane == 0) {
+        // ===== MMA issue (whole warp in step, one elected lane issues) ======================================================
+        {
             constexpr uint32_t idesc = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, TC_M, NT);
-            int64_t gcur = 0;
-            int     ti = 0;                          // ordinal of the tile within this CTA
+            const uint64_t da0 = tc::umma_desc_sw128(sA), db0 = tc::umma_desc_sw128(sB);
+            int as = 0, bs = 0;
+            uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
+            int tg = 0; (void) tg;
             tc_tile t;
             for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
                 if (!tc_resolve(a, NT, T, t)) continue;
-                const int acc = ti & 1;
-                tc::mbar_wait(bAccEmpty + 8 * acc, (uint32_t) ((ti >> 1) & 1) ^ 1);
+                tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
                 tc::tc_fence_after();
-                for (int it = 0; it < nk; ++it, ++gcur) {
-                    const int s = (int) (gcur % STAGES);
-                    tc::mbar_wait(bFull + 8 * s, (uint32_t) ((gcur / STAGES) & 1));
+                const uint32_t d_tmem = tmem + acc * NT;
+                for (int it = 0; it < nk; ++it) {
+                    tc::mbar_wait(bAFull + 8 * as, a_ph);
+                    tc::mbar_wait(bBFull + 8 * bs, b_ph);
+                    if (lane == 0) TC_TRACE(0, tg);
                     tc::tc_fence_after();
-                    const uint64_t da = tc::umma_desc_sw128(sA + s * TC_A_BYTES);
-                    const uint64_t db = tc::umma_desc_sw128(sB + s * cfg::B_BYTES);
+                    const uint64_t da = da0 + (uint64_t) (as * (TC_A_BYTES >> 4));
+                    const uint64_t db = db0 + (uint64_t) (bs * (cfg::B_BYTES >> 4));
+                    if (tc::elect_one()) {
 #pragma unroll
-                    for (int kk = 0; kk < TC_KS / 16; ++kk) {
-                        if (a.dbg & 8) break;
-                        tc::umma_f16(tmem + acc * NT, da + 2 * kk, db + 2 * kk, idesc, (it | kk) != 0);
+                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (it | kk) != 0);
+                        tc::tc_commit(bAEmpty + 8 * as);
+                        tc::tc_commit(bBEmpty + 8 * bs);
                     }
-                    tc::tc_commit(bEmpty + 8 * s);
+                    __syncwarp();
+                    if (lane == 0) TC_TRACE(1, tg);
+                    ++tg;
+                    if (++as == AS) { as = 0; a_ph ^= 1; }
+                    if (++bs == BS) { bs = 0; b_ph ^= 1; }
                 }
-                tc::tc_commit(bAccFull + 8 * acc);
-                ++ti;
+                if (tc::elect_one()) tc::tc_commit(bAccFull + 8 * acc);
+                __syncwarp();
+                acc ^= 1; if (acc == 0) acc_ph ^= 1;
             }
         }
     } else if (warp < 14) {
         // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
         const int q = warp & 3;
-        int ti = 0;
+        uint32_t acc = 0, acc_ph = 0;
         tc_tile t;
         for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
             if (!tc_resolve(a, NT, T, t)) continue;
-            const int acc = ti & 1;
-            tc::mbar_wait(bAccFull + 8 * acc, (uint32_t) ((ti >> 1) & 1));
+            tc::mbar_wait(bAccFull + 8 * acc, acc_ph);
             tc::tc_fence_after();
             const int row = t.row0 + 32 * q + lane;
 #pragma unroll 1
@@ -434,22 +462,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
                 const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
                 tc::tmem_ld_wait();
-                if (!(a.dbg & 16)) {
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
-                        const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
-                        if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
-                    }
+                for (int c = 0; c < 32; ++c) {
+                    const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
+                    const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
+                    if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
                 }
             }
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
-            ++ti;
+            acc ^= 1; if (acc == 0) acc_ph ^= 1;
         }
     }
     __syncthreads();
+#ifdef TC_TRACE_ENABLE
+    if (blockIdx.x == 0 && tid == 0) {
+        const long long t0 = g_tc_trace[0][96];
+        for (int gg = 96; gg < 112; ++gg) {
+            printf("g=%3d mma_ready=%6lld mma_done=%6lld conv_go=%6lld conv_arr0=%6lld conv_arr7=%6lld tma_go=%6lld\n", gg, g_tc_trace[0][gg] - t0,
+                   g_tc_trace[1][gg] - t0, g_tc_trace[2][gg] - t0, g_tc_trace[3][gg] - t0, g_tc_trace[5][gg] - t0, g_tc_trace[4][gg] - t0);
+        }
+    }
+#endif
     if (warp == 8) {
         __syncwarp();
         tc::tc_fence_after();
@@ -475,7 +510,7 @@ encode_tiled_fn get_encode() {
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
 
 template <int TYPE, int NT>
-int launch_one(b200_ctx * ctx, const CUtensorMap & tm, const tc_args & a) {
+int launch_one(b200_ctx * ctx, const CUtensorMap & tmw, const CUtensorMap & tm, const tc_args & a) {
     static bool configured[16] = {};
     auto kern = mmq_tc_f16_kernel<TYPE, NT>;
     if (!configured[ctx->device & 15]) {
@@ -483,18 +518,18 @@ int launch_one(b200_ctx * ctx, const CUtensorMap & tm, const tc_args & a) {
         configured[ctx->device & 15] = true;
     }
     const unsigned grid = (unsigned) (a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count);
-    kern<<<grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tm, a);
+    kern<<<grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw, tm, a);
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
 }
 
 template <int NT>
-int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tm, const tc_args & a) {
+int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tmw, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
-        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tm, a);
-        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tm, a);
-        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT>(ctx, tm, a);
+        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tmw, tm, a);
+        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -504,9 +539,16 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tm, const tc_args 
 
 int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (!tc_type_ok(type) || !get_encode()) return 0;
-    if (P.k % TC_KS != 0 || P.k > (1 << 24) || P.m > (1 << 30)) return 0;
+    const int rawk = type == B200_TYPE_Q8_0 ? raw_k<B200_TYPE_Q8_0>::value : 256;
+    if (P.k % rawk != 0 || P.k > (1 << 24) || P.m > (1 << 30)) return 0;
+    // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
     const uintptr_t bits = (uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03;
-    if (bits & (type == B200_TYPE_Q4_K ? 15 : 3)) return 0;
+    if (bits & 15) return 0;
+    if (P.mode == MM_PLAIN) {
+        const int64_t ne02 = P.ne12 / P.r2, ne03 = P.ne13 / P.r3;
+        if (ne03 > 1 && P.nb03 != P.nb02 * ne02) return 0;
+        if (ne02 * ne03 > 1 && P.nb02 < P.nb01 * P.m) return 0;
+    } else if (P.n_expert > 1 && P.nb02 < P.nb01 * P.m) return 0;
     if (((uintptr_t) P.X | (uintptr_t) P.nb11 | (uintptr_t) P.nb12 | (uintptr_t) P.nb13) & 15) return 0;
     if (P.mode == MM_ID_PAIRS) return 0;
     if (tc_cfg<256>::SMEM > ctx->smem_optin) return 0;
@@ -545,17 +587,32 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_E_CUDA; }
 
+    // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 128 rows x 144 bytes
+    const int64_t ne02 = P.mode == MM_PLAIN ? P.ne12 / P.r2 : P.n_expert;
+    const int64_t nmat = P.mode == MM_PLAIN ? ne02 * (P.ne13 / P.r3) : P.n_expert;
+    CUtensorMap tmw;
+    {
+        const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) P.m, (cuuint64_t) nmat};
+        const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (nmat > 1 ? P.nb02 : P.nb01 * P.m)};
+        const cuuint32_t wbox[3]    = {(cuuint32_t) TC_RAW_ROW / 2, (cuuint32_t) TC_M, 1};
+        const cuuint32_t westr[3]   = {1, 1, 1};
+        const CUresult wr = get_encode()(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) P.W, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (wr != CUDA_SUCCESS) { b200_set_error("cuTensorMapEncodeTiled (weights) failed (%d)", (int) wr); return B200_E_CUDA; }
+    }
+
     tc_args a = {};
+    a.ne02 = (int) ne02;
+    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : TC_RAW_ROW) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
-    a.dbg = ctx->tc_dbg;
 
     const int64_t col_tiles = P.mode == MM_PLAIN ? (n + NT - 1) / NT : (n_pos + NT - 1) / NT + P.n_expert;
     a.n_tiles = row_tiles * col_tiles * batches;
-    return NT == 128 ? launch_type<128>(ctx, type, tm, a) : launch_type<256>(ctx, type, tm, a);
+    return NT == 128 ? launch_type<128>(ctx, type, tmw, tm, a) : launch_type<256>(ctx, type, tmw, tm, a);
 }
 
 size_t b200_gemm_tc_scratch(const mm_problem & P, int64_t n_pos, size_t ws_used) {

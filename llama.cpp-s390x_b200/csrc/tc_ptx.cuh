@@ -26,12 +26,37 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 // A broken pipeline must not hang the GPU box: after ~4 s of polling the kernel traps instead.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+#ifndef TC_SPIN_TEST_WAIT
+#define TC_SPIN_TEST_WAIT 0
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+#if TC_SPIN_TEST_WAIT
+    if (mbar_test_wait(bar, parity)) return;
+    const long long t1 = clock64();
+    while (!mbar_test_wait(bar, parity)) {
+        if (clock64() - t1 > 8000000000LL) __trap();
+    }
+    return;
+#endif
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
         if (clock64() - t0 > 8000000000LL) __trap();
     }
+}
+
+// one lane of a converged warp; the surrounding code stays warp-uniform, so the compiler keeps descriptors, barrier
+// addresses and loop counters in uniform registers instead of broadcasting them lane by lane
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 
 // generic-proxy smem writes -> visible to the async proxy (UMMA / TMA reads)
@@ -41,6 +66,10 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void * tmap, uint32_t bar, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void * tmap, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 // the same box written into the same smem offset of every CTA in `mask`; each destination's mbarrier gets the bytes
 __device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void * tmap, uint32_t bar, int c0, int c1, uint16_t mask) {
