@@ -17,7 +17,7 @@ int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_strid
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
-size_t b200_gemm_tc_scratch(const mm_problem & P, int64_t n_pos, size_t ws_used);
+size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
                        int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
 
@@ -111,7 +111,8 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
     ctx->gemv_cfg      = env_int("GGML_B200_GEMV_CFG", 0);
-    ctx->tc_cluster    = env_int("GGML_B200_TC_CLUSTER", 0);
+    ctx->tc_nt         = env_int("GGML_B200_TC_NT", 0);
+    ctx->tc_split_k   = env_int("GGML_B200_TC_SPLIT_K", 1);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
@@ -150,8 +151,8 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
     else if (!strcmp(name, "gemv_cfg"))      slot = &ctx->gemv_cfg;
-    else if (!strcmp(name, "tc_cluster"))    slot = &ctx->tc_cluster;
-    else if (!strcmp(name, "tc_dbg"))        slot = &ctx->tc_dbg;
+    else if (!strcmp(name, "tc_nt"))         slot = &ctx->tc_nt;
+    else if (!strcmp(name, "tc_split_k"))   slot = &ctx->tc_split_k;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
@@ -354,7 +355,7 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
     pending_push(ctx, d, true);
 
     if (n_peers == 0 && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
-        const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(P, n * batches, 0));
+        const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, n * batches, 0));
         if (rc) return rc;
         return b200_launch_gemm_tc(ctx, a->type, P, n * batches, 0);
     }
@@ -424,7 +425,7 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
     P.mode = MM_ID_SORTED;
     if (ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, as->type, P)) {
         // scratch: [ids_src1 | expert_bounds | fp16 activations gathered by expert | per-position scale and dst column]
-        int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(P, n_pairs, extra_bytes));
+        int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, n_pairs, extra_bytes));
         if (rc) return rc;
         int32_t * ids_src1 = (int32_t *) ctx->ws;
         int32_t * bounds   = ids_src1 + n_pairs;

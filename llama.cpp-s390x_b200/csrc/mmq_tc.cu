@@ -61,6 +61,9 @@ struct tc_args {
     int     n_expert;
     const int32_t * expert_bounds;
     int64_t n_tiles;            // row tiles x column tiles (upper bound for MUL_MAT_ID) x batches
+    int     grid;               // persistent CTAs
+    int     split_k;            // K parts per tile (1, 2 or 4); the parts of a tile are summed in ascending K order
+    int32_t * tile_sync;        //    through these per-(tile, lane quadrant) turnstiles (zeroed per launch)
 };
 
 // ---- activations: f32 -> normalised fp16, K order (0,2,1,3) inside every group of 4 -------------------------------------
@@ -278,6 +281,36 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
     return true;
 }
 
+// What a CTA works on next: a whole tile, or (split K) the K range [k0, k1) of one.
+struct tc_seg {
+    tc_tile t;
+    int64_t T;
+    int k0, k1;             // in 64-wide stages
+    int order, nparts;      // position of this part in the tile's fixed summation order
+};
+
+struct tc_walker {
+    int64_t w;              // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
+
+    __device__ __forceinline__ tc_walker(const tc_args &) { w = blockIdx.x; }
+
+    __device__ __forceinline__ bool next(const tc_args & a, const int NT, tc_seg & s) {
+        const int64_t n_items = a.n_tiles * a.split_k;
+        for (; w < n_items; w += gridDim.x) {
+            const int64_t part = w / a.n_tiles;
+            s.T = w - part * a.n_tiles;
+            if (tc_resolve(a, NT, s.T, s.t)) {
+                const int len = a.k / TC_KS / a.split_k;
+                s.k0 = (int) part * len; s.k1 = s.k0 + len;
+                s.order = (int) part; s.nparts = a.split_k;
+                w += gridDim.x;
+                return true;
+            }
+        }
+        return false;
+    }
+};
+
 #ifdef TC_TRACE_ENABLE     // development aid: per-stage clock64 stamps of CTA 0 (build with -DTC_TRACE_ENABLE, run tools/tc_trace.py)
 __device__ long long g_tc_trace[6][128];
 #define TC_TRACE(role, gg) do { if (blockIdx.x == 0 && (gg) < 128) g_tc_trace[role][gg] = clock64(); } while (0)
@@ -302,8 +335,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t sTmem  = bAccEmpty + 16;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nk = a.k / TC_KS;
-    const int64_t n_tiles = a.n_tiles;
 
     if (warp == 8) {
         if (lane == 0) {
@@ -335,11 +366,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         int as = 0, rs = 0, sub = 0;
         uint32_t a_ph = 0, r_ph = 0;
         int tg = 0; (void) tg;
-        tc_tile t;
-        for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
-            if (!tc_resolve(a, NT, T, t)) continue;
-            uint32_t skew = 0;                               // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
-            for (int it = 0; it < nk; ++it) {
+        tc_walker wk(a);
+        tc_seg sg;
+        while (wk.next(a, NT, sg)) {
+            // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
+            uint32_t skew = TYPE == B200_TYPE_Q8_0 ? 8u * (uint32_t) ((sg.k0 / SPR) & 1) : 0u;
+            for (int it = sg.k0; it < sg.k1; ++it) {
                 if (sub == 0) tc::mbar_wait(bRFull + 8 * rs, r_ph);
                 w_frag<TYPE> f;
                 uint4 out[4]; int slot[4];
@@ -376,11 +408,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             int bs = 0, rs = 0, sub = 0;
             uint32_t b_ph = 0, r_ph = 0;
             int tg = 0; (void) tg;
-            tc_tile t;
-            for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
-                if (!tc_resolve(a, NT, T, t)) continue;
-                int x = 0, odd = 0;                           // position of the next raw slot in the row (16-bit elements)
-                for (int it = 0; it < nk; ++it) {
+            tc_walker wk(a);
+            tc_seg sg;
+            while (wk.next(a, NT, sg)) {
+                const tc_tile & t = sg.t;
+                int x = (sg.k0 / SPR) * a.raw_step, odd = (sg.k0 / SPR) & 1;    // next raw slot in the row (16-bit elements)
+                for (int it = sg.k0; it < sg.k1; ++it) {
                     if (sub == 0) {
                         tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1);
                         if (tc::elect_one()) {
@@ -411,13 +444,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             int as = 0, bs = 0;
             uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
             int tg = 0; (void) tg;
-            tc_tile t;
-            for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
-                if (!tc_resolve(a, NT, T, t)) continue;
+            tc_walker wk(a);
+            tc_seg sg;
+            while (wk.next(a, NT, sg)) {
                 tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
                 tc::tc_fence_after();
                 const uint32_t d_tmem = tmem + acc * NT;
-                for (int it = 0; it < nk; ++it) {
+                for (int it = sg.k0; it < sg.k1; ++it) {
                     tc::mbar_wait(bAFull + 8 * as, a_ph);
                     tc::mbar_wait(bBFull + 8 * bs, b_ph);
                     if (lane == 0) TC_TRACE(0, tg);
@@ -426,7 +459,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     const uint64_t db = db0 + (uint64_t) (bs * (cfg::B_BYTES >> 4));
                     if (tc::elect_one()) {
 #pragma unroll
-                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (it | kk) != 0);
+                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
                         tc::tc_commit(bAEmpty + 8 * as);
                         tc::tc_commit(bBEmpty + 8 * bs);
                     }
@@ -445,12 +478,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
         const int q = warp & 3;
         uint32_t acc = 0, acc_ph = 0;
-        tc_tile t;
-        for (int64_t T = blockIdx.x; T < n_tiles; T += gridDim.x) {
-            if (!tc_resolve(a, NT, T, t)) continue;
+        tc_walker wk(a);
+        tc_seg sg;
+        while (wk.next(a, NT, sg)) {
+            const tc_tile & t = sg.t;
             tc::mbar_wait(bAccFull + 8 * acc, acc_ph);
             tc::tc_fence_after();
             const int row = t.row0 + 32 * q + lane;
+            int32_t * turnstile = sg.nparts > 1 ? a.tile_sync + sg.T * 4 + q : nullptr;
+            if (sg.order > 0) {
+                // split K: wait for the parts that go before this one (rows of this lane quadrant only)
+                if (lane == 0) {
+                    const long long t0 = clock64();
+                    int seen;
+                    do {
+                        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turnstile) : "memory");
+                        if (clock64() - t0 > 8000000000LL) __trap();
+                    } while (seen < sg.order);
+                }
+                __syncwarp();
+            }
 #pragma unroll 1
             for (int c0 = 0; c0 < NT; c0 += 32) {
                 if (c0 >= t.nvalid) break;                            // warp-uniform
@@ -462,16 +509,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
                 const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
                 tc::tmem_ld_wait();
+                if (sg.order == 0) {
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
-                    const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
-                    if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
+                    for (int c = 0; c < 32; ++c) {
+                        const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
+                        const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
+                        if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
+                    }
+                } else {
+                    // add to the earlier parts' sum with fire-and-forget reductions (no load round trip); the turnstile orders
+                    // the parts, so the summation order — hence the result — is fixed
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
+                        const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
+                        if (c0 + c < t.nvalid && row < a.m) {
+                            asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" :: "l"(a.Y + (int64_t) yc * a.m + row), "f"(__uint_as_float(v[c]) * sc) : "memory");
+                        }
+                    }
                 }
             }
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
+            if (turnstile) {
+                __threadfence();
+                __syncwarp();
+                if (lane == 0) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" :: "l"(turnstile) : "memory");
+            }
             acc ^= 1; if (acc == 0) acc_ph ^= 1;
         }
     }
@@ -517,8 +582,7 @@ int launch_one(b200_ctx * ctx, const CUtensorMap & tmw, const CUtensorMap & tm, 
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT>::SMEM));
         configured[ctx->device & 15] = true;
     }
-    const unsigned grid = (unsigned) (a.n_tiles < ctx->sm_count ? a.n_tiles : ctx->sm_count);
-    kern<<<grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw, tm, a);
+    kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw, tm, a);
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
@@ -555,32 +619,55 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     return 1;
 }
 
+struct tc_plan {
+    int     NT;
+    int64_t n, batches, row_tiles, col_tiles, n_tiles;
+    size_t  off_xh, off_sc, off_yc, off_sync, total;
+};
+
+static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) {
+    tc_plan p;
+    p.batches   = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
+    p.n         = P.mode == MM_PLAIN ? P.ne11 : n_pos;
+    p.row_tiles = (P.m + TC_M - 1) / TC_M;
+    p.NT        = p.n <= 128 ? 128 : 256;
+    if (p.NT == 256 && P.mode == MM_PLAIN) {
+        // 128 x 256 tiles move fewer shared-memory bytes per flop (measured ~836 vs ~586 clocks per 64-wide K stage), but
+        // few of them leave SMs idle: take the tile width with the shorter estimated critical path
+        const int64_t t256 = p.row_tiles * ((p.n + 255) / 256) * p.batches, t128 = p.row_tiles * ((p.n + 127) / 128) * p.batches;
+        const int64_t w256 = (t256 + ctx->sm_count - 1) / ctx->sm_count, w128 = (t128 + ctx->sm_count - 1) / ctx->sm_count;
+        if (ctx->tc_nt == 128 || (ctx->tc_nt == 0 && P.k < 8192 && w128 * 586 < w256 * 836)) p.NT = 128;
+    }
+    p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.NT - 1) / p.NT : (n_pos + p.NT - 1) / p.NT + P.n_expert;
+    p.n_tiles   = p.row_tiles * p.col_tiles * p.batches;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    p.off_xh   = (ws_used + 1023) / 1024 * 1024;
+    p.off_sc   = p.off_xh + up((size_t) n_pos * P.k * sizeof(__half));
+    p.off_yc   = p.off_sc + up((size_t) n_pos * 4);
+    p.off_sync = p.off_yc + up((size_t) n_pos * 4);
+    p.total    = p.off_sync + up((size_t) p.n_tiles * 4 * sizeof(int32_t));
+    return p;
+}
+
 // n_pos = number of activation positions (MM_PLAIN: ne11 * batches; MM_ID_SORTED: pairs).  Uses the context scratch
 // AFTER `ws_used` bytes (the caller may keep ids there).
 int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used) {
-    const size_t xh_bytes = (size_t) n_pos * P.k * sizeof(__half);
-    const size_t off_xh   = (ws_used + 1023) / 1024 * 1024;
-    const size_t off_sc   = off_xh + (xh_bytes + 255) / 256 * 256;
-    const size_t off_yc   = off_sc + ((size_t) n_pos * 4 + 255) / 256 * 256;
-    const size_t total    = off_yc + ((size_t) n_pos * 4 + 255) / 256 * 256;
-    if ((size_t) ctx->ws_size < total) { b200_set_error("tcgen05 GEMM: scratch not reserved"); return B200_E_ARG; }
+    const tc_plan pl = make_plan(ctx, P, n_pos, ws_used);
+    if ((size_t) ctx->ws_size < pl.total) { b200_set_error("tcgen05 GEMM: scratch not reserved"); return B200_E_ARG; }
     uint8_t * ws = (uint8_t *) ctx->ws;
-    __half *  Xh = (__half *) (ws + off_xh);
-    float *   sc = (float *) (ws + off_sc);
-    int32_t * yc = (int32_t *) (ws + off_yc);
+    __half *  Xh = (__half *) (ws + pl.off_xh);
+    float *   sc = (float *) (ws + pl.off_sc);
+    int32_t * yc = (int32_t *) (ws + pl.off_yc);
+    const int NT = pl.NT;
+    const int64_t n = pl.n;
 
     tc_act_f16_kernel<<<(unsigned) n_pos, 256, 0, ctx->stream>>>(P, Xh, sc, yc);
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
 
-    const int64_t batches = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
-    const int64_t n       = P.mode == MM_PLAIN ? P.ne11 : n_pos;
-    const int     NT      = n <= 128 ? 128 : 256;
-
     CUtensorMap tm;
     const cuuint64_t gdim[2]    = {(cuuint64_t) P.k, (cuuint64_t) n_pos};
     const cuuint64_t gstride[1] = {(cuuint64_t) P.k * sizeof(__half)};
-    const int64_t row_tiles = (P.m + TC_M - 1) / TC_M;
     const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) NT};
     const cuuint32_t estr[2]    = {1, 1};
     const CUresult cr = get_encode()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -610,13 +697,28 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
 
-    const int64_t col_tiles = P.mode == MM_PLAIN ? (n + NT - 1) / NT : (n_pos + NT - 1) / NT + P.n_expert;
-    a.n_tiles = row_tiles * col_tiles * batches;
+    a.n_tiles = pl.n_tiles;
+    // Scheduling: whole tiles, walked in the same order by all CTAs (they move along K in step and share activation tiles in
+    // L2).  A long-K matrix with few tiles (down projection: 64 tiles for 148 SMs) is split in two along K; the halves run
+    // in the same wave and the second is added to the first through a per-tile turnstile, so the result does not depend
+    // on timing.  (Measured and rejected: stream-K with equal runs per CTA — loses the L2 sharing, no gain.)
+    // ctx->tc_split_k: 0 = never, 1 = auto, 2 / 4 = forced
+    a.split_k = 1;
+    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0) {
+        auto eff = [&](int64_t sk) {
+            const int64_t items = pl.n_tiles * sk, waves = (items + ctx->sm_count - 1) / ctx->sm_count;
+            return (double) items / (double) (waves * ctx->sm_count);
+        };
+        if (ctx->tc_split_k > 1) { if ((P.k / 256) % ctx->tc_split_k == 0) a.split_k = ctx->tc_split_k; }
+        else if ((P.k / 256) % 2 == 0 && P.k >= 8192 && eff(2) > 1.15 * eff(1)) a.split_k = 2;
+    }
+    const int64_t items = pl.n_tiles * a.split_k;
+    a.grid = (int) (items < ctx->sm_count ? items : ctx->sm_count);
+    if (a.split_k > 1) {
+        a.tile_sync = (int32_t *) (ws + pl.off_sync);
+        B200_CUDA_TRY(cudaMemsetAsync(a.tile_sync, 0, (size_t) pl.n_tiles * 4 * sizeof(int32_t), ctx->stream));
+    }
     return NT == 128 ? launch_type<128>(ctx, type, tmw, tm, a) : launch_type<256>(ctx, type, tmw, tm, a);
 }
 
-size_t b200_gemm_tc_scratch(const mm_problem & P, int64_t n_pos, size_t ws_used) {
-    const size_t xh_bytes = (size_t) n_pos * P.k * sizeof(__half);
-    const size_t off_xh   = (ws_used + 1023) / 1024 * 1024;
-    return off_xh + (xh_bytes + 255) / 256 * 256 + 2 * (((size_t) n_pos * 4 + 255) / 256 * 256);
-}
+size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) { return make_plan(ctx, P, n_pos, ws_used).total; }

@@ -130,6 +130,48 @@ def test_gemm_vs_oracle(pkg, gpu_ctx, orc, name, n, m, k):
     assert nmse(want, got) <= NMSE_TOL
 
 
+TC_TYPES = ["q4_K", "q4_0", "q8_0"]     # weight types the tcgen05 path covers (Q6_K stays on the CUDA-core path)
+
+
+@pytest.mark.parametrize("name", TC_TYPES)
+@pytest.mark.parametrize("n,m,k", [(33, 200, 512), (130, 128, 256), (512, 1000, 2048)])
+def test_tc_gemm_close_to_f64_truth_and_to_cuda_core_path(pkg, gpu_ctx, orc, name, n, m, k):
+    """prefill path (tcgen05, fp16 operands / fp32 accumulate) vs (a) the exact product in f64 — fp16 rounding only, so far
+    closer than the Q8_1-quantised reference gets — and (b) our CUDA-core path that follows ggml-cpu's Q8_1 arithmetic"""
+    from tests.util import oracle_mul_mat_f64
+    t = TYPES[name]
+    rng = np.random.default_rng(7 * n + m)
+    W = random_blocks(t, m, k, rng)
+    X = rng.standard_normal((n, k)).astype(np.float32)
+    truth = oracle_mul_mat_f64(orc, t, W, X)
+    Wd, Xd = dev(W), dev(X)
+    gpu_ctx.set_option("use_tc", 1)
+    got = pkg.mul_mat(gpu_ctx, t, Wd, Xd).cpu().numpy()
+    gpu_ctx.set_option("use_tc", 0)
+    core = pkg.mul_mat(gpu_ctx, t, Wd, Xd).cpu().numpy()
+    gpu_ctx.set_option("use_tc", 1)
+    assert nmse(truth, got) <= 1e-6
+    assert nmse(core, got) <= 1e-4 and nmse(oracle_mul_mat(orc, t, W, X), got) <= NMSE_TOL
+
+
+@pytest.mark.parametrize("name", TC_TYPES)
+def test_tc_gemm_llama_shape_linearity_and_tiles(pkg, gpu_ctx, name):
+    """full prefill size (m=4096, k=4096, n=512): column j of the batched result must equal the same column computed in a
+    small batch (tiles / clusters / persistent scheduling cannot leak between columns), and W(2x) = 2 W(x) exactly
+    (power-of-two scaling commutes with every rounding on the path)"""
+    import torch
+    t = TYPES[name]
+    rng = np.random.default_rng(11)
+    W = dev(np.tile(random_blocks(t, 256, 4096, rng), (16, 1)))
+    X = torch.randn((512, 4096), device="cuda")
+    Y = pkg.mul_mat(gpu_ctx, t, W, X)
+    sel = [0, 1, 127, 128, 255, 256, 300, 511, 17, 64, 200, 444, 3, 5, 7, 9]
+    Ys = pkg.mul_mat(gpu_ctx, t, W, X[sel].contiguous())
+    assert torch.equal(Y[sel], Ys)
+    assert torch.equal(pkg.mul_mat(gpu_ctx, t, W, 2.0 * X), 2.0 * Y)
+    assert torch.equal(Y[:, :256], Y[:, 256:512]) and torch.equal(Y[:, :256], Y[:, 3840:])      # W repeats every 256 rows
+
+
 # ---- (4) MUL_MAT_ID --------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", list(TYPES))
 def test_mul_mat_id_golden_strided_ids(pkg, gpu_ctx, name):

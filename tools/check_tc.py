@@ -56,7 +56,8 @@ if not quick:
     print(f"mul_mat_id q4_K 300 tokens: nmse = {nmse(c0, c1):.3e}", flush=True)
 
     # speed
-    for cl in (1,):
+    for cl in ((1, 0),):
+        ctx.set_option("tc_split_k", cl[0]); ctx.set_option("tc_nt", cl[1])
         for name, t in TYPES.items():
             row = []
             for m, k, n in ((4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (128256, 4096, 512)):
@@ -65,9 +66,6 @@ if not quick:
                 Y = torch.empty((n, m), device="cuda")
                 for _ in range(3):
                     pkg.mul_mat(ctx, t, W, X, out=Y)
-                if cl > 1 and m == 4096 and k == 4096:
-                    ctx.set_option("tc_cluster", 1); Y1 = pkg.mul_mat(ctx, t, W, X).cpu().numpy(); ctx.set_option("tc_cluster", cl)
-                    assert np.array_equal(Y1, Y.cpu().numpy()), "cluster multicast changes results"
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 iters = 20 if m < 100000 else 4
                 e0.record()
@@ -76,4 +74,4 @@ if not quick:
                 e1.record(); torch.cuda.synchronize()
                 ms = e0.elapsed_time(e1) / iters
                 row.append(f"{m}x{k}: {ms * 1e3:7.1f}us {2.0 * m * n * k / ms / 1e9:6.0f}TF")
-            print(f"cluster {cl} {name}: " + " | ".join(row), flush=True)
+            print(f"sched {cl} {name}: " + " | ".join(row), flush=True)
