@@ -101,6 +101,66 @@ def device_random_q4k(torch, m, k, gen):
     return raw.reshape(m, nb * 144)
 
 
+def device_random_q8_0(torch, m, k, gen):
+    """m rows of valid random Q8_0 blocks generated ON the device (setup, not timed)"""
+    nb = k // 32
+    raw = torch.randint(0, 256, (m, nb, 34), dtype=torch.uint8, device="cuda", generator=gen)
+    d = (torch.rand((m, nb), device="cuda", generator=gen) * 0.75 + 0.25) * (0.02 / 127)
+    raw[:, :, 0:2] = d.to(torch.float16).view(torch.uint8).reshape(m, nb, 2)
+    return raw.reshape(m, nb * 34)
+
+
+def tensor_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        for key in ("bf16_tflops", "bf16_tfs", "dense_bf16_tflops", "bf16_dense_tflops"):
+            if key in d:
+                return float(d[key]), f"measured (MEASURED_PEAKS.json {key}, cuBLAS bf16)"
+        for key, v in d.items():
+            if "bf16" in key.lower() and isinstance(v, (int, float)):
+                return float(v), f"measured (MEASURED_PEAKS.json {key}, cuBLAS bf16)"
+    return 1600.0, "fallback (B200_PROFILING.md dense bf16)"
+
+
+def prefill_bench(torch, pkg, ctx, stream, n=512):
+    """BASELINE configs[2]: the same 225 matmuls at n = 512 (prefill) through the tcgen05 path, Q8_0 and Q4_K weights.
+    Compute-bound, so each shape is timed on its own (3 distinct weight copies rotating) and the step is the count-weighted
+    sum; reported against the measured dense 16-bit tensor peak because the MMA runs kind::f16 with fp32 accumulation."""
+    gen = torch.Generator(device="cuda"); gen.manual_seed(99)
+    peak, src = tensor_peak()
+    out = {"n_tokens": n, "tensor_peak_tflops": peak, "peak_source": src, "mma": "tcgen05.mma.kind::f16 (fp16 x fp16 -> fp32 in TMEM)"}
+    shapes = {}
+    for (m, k) in sorted({(m, k) for _, m, k, _ in LLAMA3_8B}):
+        shapes[(m, k)] = sum(c for _, mm, kk, c in LLAMA3_8B if (mm, kk) == (m, k))
+    for tname, ttype, make in (("q8_0", 8, device_random_q8_0), ("q4_K", Q4_K, device_random_q4k)):
+        total_ms, flops, per = 0.0, 0.0, {}
+        for (m, k), count in shapes.items():
+            copies = 1 if m > 100000 else 3
+            Ws = [make(torch, m, k, gen) for _ in range(copies)]
+            X = torch.randn((n, k), device="cuda", generator=gen)
+            Y = torch.empty((n, m), device="cuda")
+            iters = 3 if m > 100000 else 12
+            with torch.cuda.stream(stream):
+                for i in range(3):
+                    pkg.mul_mat(ctx, ttype, Ws[i % copies], X, out=Y)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for i in range(iters):
+                    pkg.mul_mat(ctx, ttype, Ws[i % copies], X, out=Y)
+                e1.record(stream)
+                stream.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            per[f"{m}x{k}"] = {"us": round(ms * 1e3, 1), "tflops": round(2.0 * m * n * k / ms / 1e9, 1)}
+            total_ms += ms * count
+            flops += 2.0 * m * n * k * count
+            del Ws, X, Y
+        tf = flops / total_ms / 1e9
+        out[tname] = {"ms_per_step": round(total_ms, 3), "tok_per_s_matmul_only": round(n / total_ms * 1e3, 1), "tflops": round(tf, 1),
+                      "frac_of_tensor_peak": round(tf / peak, 4), "per_shape": per}
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -123,7 +183,25 @@ def run_gpu(args):
     gen.manual_seed(1234 + rank)
 
     # ---- the workload, resident in HBM ------------------------------------------------------------------------------------
-    ops = []   # (W shard uint8 [rows, rs], x f32 [1, k], y_full f32 [1, m], y_shard)
+    # N > 1: row split (BASELINE configs[4] on the configs[1] workload).  Every rank owns m / N rows of every matrix; the
+    # all-gather of the output rows is FUSED into the GEMV: its epilogue stores each result straight into every rank's
+    # full-height output through NVLink peer mappings (torch symmetric memory provides the mapped pointers), and a
+    # symmetric-memory barrier after every matmul makes the gathered vector complete on all ranks before the next one.
+    hdl, ptrs, maxm = None, None, max(m for _, m, _, _ in LLAMA3_8B)
+    if world > 1:
+        import torch.distributed._symmetric_memory as symm_mem
+        ybuf = symm_mem.empty(2 * maxm, dtype=torch.float32, device=torch.device("cuda", local))
+        hdl = symm_mem.rendezvous(ybuf, dist.group.WORLD)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        # correctness of the fused exchange: same matrix on every rank, gathered result == unsplit result, bit for bit
+        cg = torch.Generator(device="cuda"); cg.manual_seed(7)
+        Wc = device_random_q4k(torch, 4096, 4096, cg); xc = torch.randn((1, 4096), device="cuda", generator=cg)
+        full = pkg.mul_mat(ctx, Q4_K, Wc, xc)
+        r = 4096 // world
+        pkg.mul_mat_gather(ctx, Q4_K, Wc[rank * r:(rank + 1) * r].contiguous(), xc, torch.empty((1, r), device="cuda"), ptrs, 4096, rank * r)
+        ctx.synchronize(); hdl.barrier(channel=0); torch.cuda.synchronize()
+        assert torch.equal(ybuf[:4096].view(1, -1), full), "fused row-split all-gather differs from the unsplit result"
+    ops = []   # (W shard uint8 [rows, rs], x f32 [1, k], y_full f32 [1, m], y_shard, full m)
     xs = {}
     for name, m, k, count in LLAMA3_8B:
         assert m % world == 0
@@ -133,18 +211,24 @@ def run_gpu(args):
             xs[k] = torch.randn((1, k), device="cuda", generator=xg)
         for _ in range(count):
             W = device_random_q4k(torch, rows, k, gen)
-            y = torch.empty((1, m), device="cuda")
-            ys = y if world == 1 else torch.empty((1, rows), device="cuda")
-            ops.append((W, xs[k], y, ys))
+            if world == 1:
+                y = torch.empty((1, m), device="cuda")
+                ys = y
+            else:
+                y, ys = None, torch.empty((1, rows), device="cuda")
+            ops.append((W, xs[k], y, ys, m))
     # interleave like a real forward: layer by layer
     per_layer = [[o for o in ops[i * 32:(i + 1) * 32]] for i in range(7)]
     order = [per_layer[j][l] for l in range(32) for j in range(7)] + [ops[-1]]
 
     def step():
-        for W, x, y, ys in order:
-            pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
-            if world > 1:
-                dist.all_gather_into_tensor(y.view(-1), ys.view(-1))
+        for i, (W, x, y, ys, m) in enumerate(order):
+            if world == 1:
+                pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
+            else:
+                slot = (i & 1) * maxm * 4
+                pkg.mul_mat_gather(ctx, Q4_K, W, x, ys, [p + slot for p in ptrs], m, rank * (m // world))
+                hdl.barrier(channel=0)
 
     launches0 = ctx.launches
     with torch.cuda.stream(stream):
@@ -196,7 +280,7 @@ def run_gpu(args):
         yh = torch.empty((1, mmax)).pin_memory()
 
         def host_step():
-            for W, x, y, ys in order:
+            for W, x, y, ys, m in order:
                 rc = L.b200_mul_mat_host(hctx.handle, Q4_K, W.data_ptr(), W.shape[0], x.shape[1], xh.data_ptr(), 1, yh.data_ptr())
                 if rc:
                     raise pkg.B200Error(L.b200_last_error().decode())
@@ -215,6 +299,11 @@ def run_gpu(args):
                "api": "b200_mul_mat_host (C ABI, pinned host x -> H2D -> GEMV -> D2H y, per matmul)"}
     if world == 1 and args.shapes:
         shapes = per_shape(torch, pkg, ctx, stream, ops)
+    prefill = None
+    if world == 1 and not args.no_prefill:
+        del ops, order, per_layer
+        torch.cuda.empty_cache()
+        prefill = prefill_bench(torch, pkg, ctx, stream)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -226,7 +315,8 @@ def run_gpu(args):
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
                        "l2": "inputs larger than L2: 4.22 GB of distinct weights per step vs 126 MB L2, no flush needed",
                        "launch": "CUDA graph replay" if graph is not None else "eager launches through the C ABI",
-                       "parallelism": "1 GPU" if world == 1 else f"row-split x{world} + NCCL all-gather per matmul"},
+                       "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
+                                                                          "memory + symmetric-memory barrier after every matmul"},
             "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
             "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clocks,
@@ -239,6 +329,8 @@ def run_gpu(args):
             out["e2e"] = e2e
         if shapes:
             out["shapes"] = shapes
+        if prefill:
+            out["prefill"] = prefill
         if world == 1 and args.cpu_seconds > 0:
             out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
         print(json.dumps(out), flush=True)
@@ -255,12 +347,12 @@ def per_shape(torch, pkg, ctx, stream, ops):
         idx += count
         iters = 64 if count > 1 else 8
         with torch.cuda.stream(stream):
-            for W, x, y, ys in group[:2]:
+            for W, x, y, ys, _m in group[:2]:
                 pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=stream):
                 for i in range(iters):
-                    W, x, y, ys = group[i % count]
+                    W, x, y, ys, _m = group[i % count]
                     pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
             g.replay()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -356,6 +448,7 @@ def main():
     ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

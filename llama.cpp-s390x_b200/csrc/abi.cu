@@ -533,6 +533,14 @@ static int grow(b200_ctx * ctx, void ** buf, size_t * have, size_t want) {
     return B200_OK;
 }
 
+int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d_shard,
+                        int n_dst, float * const * dst, int64_t dst_m, int64_t dst_row0) {
+    if (!ctx || !b || n_dst < 1 || !dst) { b200_set_error("mul_mat_gather: bad argument"); return B200_E_ARG; }
+    if (b->ne[1] > ctx->max_gemv_cols || b->ne[1] > 8) { b200_set_error("mul_mat_gather: n <= 8 columns only"); return B200_E_UNSUPPORTED; }
+    if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
+    return b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
+}
+
 int b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, int64_t k, const float * x_host, int64_t n,
                       float * y_host) {
     if (!ctx || !w_dev || !x_host || !y_host || !is_weight_type(type)) { b200_set_error("mul_mat_host: bad argument"); return B200_E_ARG; }

@@ -119,6 +119,13 @@ __device__ __forceinline__ uint4 ld_stream_u4(const void * p) {
     return r;
 }
 
+// restores the caller's current device on scope exit (the multi-device entry points switch devices internally)
+struct device_guard {
+    int saved = -1;
+    device_guard()  { if (cudaGetDevice(&saved) != cudaSuccess) saved = -1; }
+    ~device_guard() { if (saved >= 0) cudaSetDevice(saved); }
+};
+
 // get_scale_min_k4 (ggml/src/ggml-quants.c:818-825) on the 12 scale bytes held as three little-endian words
 __device__ __forceinline__ void q4k_scale_min(int j, uint32_t s0, uint32_t s1, uint32_t s2, int & sc, int & mn) {
     if (j < 4) {

@@ -99,6 +99,7 @@ static int ensure(int device, float ** buf, size_t * have, size_t want) {
 extern "C" {
 
 int b200_rowsplit_create(const int * devices, int n_dev, const float * split, b200_rowsplit ** out) {
+    device_guard guard;
     if (!out || !devices || n_dev < 1 || n_dev > B200_MAX_PEERS) { b200_set_error("rowsplit_create: bad arguments"); return B200_E_ARG; }
     *out = nullptr;
     b200_rowsplit * rs = (b200_rowsplit *) calloc(1, sizeof(b200_rowsplit));
@@ -137,6 +138,7 @@ int b200_rowsplit_create(const int * devices, int n_dev, const float * split, b2
 }
 
 void b200_rowsplit_destroy(b200_rowsplit * rs) {
+    device_guard guard;
     if (!rs) return;
     for (int i = 0; i < rs->n_dev; ++i) {
         if (rs->ctx[i]) { cudaSetDevice(rs->dev[i]); cudaDeviceSynchronize(); }
@@ -168,6 +170,7 @@ int b200_rowsplit_rows(const b200_rowsplit * rs, int64_t m, int idx, int64_t * r
 }
 
 int b200_rowsplit_upload(b200_rowsplit * rs, int type, const void * host_rows, int64_t k, int64_t m, b200_split_weights ** out) {
+    device_guard guard;
     if (!rs || !host_rows || !out || b200_blck(type) == 0 || k % b200_blck(type) != 0) { b200_set_error("rowsplit_upload: bad arguments"); return B200_E_ARG; }
     b200_split_weights * w = (b200_split_weights *) calloc(1, sizeof(b200_split_weights));
     if (!w) return B200_E_ALLOC;
@@ -186,18 +189,21 @@ int b200_rowsplit_upload(b200_rowsplit * rs, int type, const void * host_rows, i
 }
 
 void b200_rowsplit_weights_free(b200_rowsplit * rs, b200_split_weights * w) {
+    device_guard guard;
     if (!rs || !w) return;
     for (int i = 0; i < rs->n_dev; ++i) if (w->shard[i]) b200_free(rs->dev[i], w->shard[i]);
     free(w);
 }
 
 int b200_rowsplit_synchronize(b200_rowsplit * rs) {
+    device_guard guard;
     if (!rs) return B200_E_ARG;
     for (int i = 0; i < rs->n_dev; ++i) { int rc = b200_ctx_synchronize(rs->ctx[i]); if (rc) return rc; }
     return B200_OK;
 }
 
 int b200_rowsplit_mul_mat(b200_rowsplit * rs, const b200_split_weights * w, float * const * x_dev, int64_t n, float * const * y_dev, int mode) {
+    device_guard guard;
     if (!rs || !w || !x_dev || !y_dev || n <= 0 || mode < 0 || mode > 2) { b200_set_error("rowsplit_mul_mat: bad arguments"); return B200_E_ARG; }
     const int G = rs->n_dev;
     if (mode == 0 && !rs->nccl_tried) {

@@ -109,3 +109,14 @@ def mm_ids(ctx: Context, ids, n_expert: int):
     check(lib().b200_mm_ids(ctx.handle, ids.data_ptr(), ids.stride(0) * 4, n_expert, n_used, n_tokens, src1.data_ptr(), bounds.data_ptr()),
           "b200_mm_ids")
     return src1, bounds
+
+
+def mul_mat_gather(ctx: Context, wtype: int, w_shard, x, out_shard, dst_ptrs, dst_m: int, dst_row0: int):
+    """row split, one process per GPU: out_shard = w_shard x x, and every result is also stored into the full-height
+    outputs `dst_ptrs` (peer-mapped device pointers, e.g. torch symmetric memory) at rows [dst_row0, dst_row0 + rows)"""
+    a = _desc(w_shard, wtype, k_elems=x.shape[-1])
+    b = _desc(x, F32)
+    d = _desc(out_shard, F32)
+    arr = (C.c_void_p * len(dst_ptrs))(*dst_ptrs)
+    check(lib().b200_mul_mat_gather(ctx.handle, C.byref(a), C.byref(b), C.byref(d), len(dst_ptrs), arr, dst_m, dst_row0), "b200_mul_mat_gather")
+    return out_shard
