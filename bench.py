@@ -185,8 +185,11 @@ def run_gpu(args):
     # ---- the workload, resident in HBM ------------------------------------------------------------------------------------
     # N > 1: row split (BASELINE configs[4] on the configs[1] workload).  Every rank owns m / N rows of every matrix; the
     # all-gather of the output rows is FUSED into the GEMV: its epilogue stores each result straight into every rank's
-    # full-height output through NVLink peer mappings (torch symmetric memory provides the mapped pointers), and a
-    # symmetric-memory barrier after every matmul makes the gathered vector complete on all ranks before the next one.
+    # full-height output through NVLink peer mappings (torch symmetric memory provides the mapped pointers).  Completion per
+    # matmul: a symmetric-memory barrier kernel after every GEMV (default; measured 2.79 ms / step at N = 2), or
+    # --gather-sync flags: the last CTA of a launch publishes its epoch to every rank and the next launch waits for all
+    # ranks' epochs before it reads its activations (b200_gather_sync_init; measured 3.54 ms: one system-scope fence per CTA
+    # costs more than the separate barrier kernel).  Either way the cost is NVLink round trips, ~10 us per matmul.
     hdl, ptrs, maxm = None, None, max(m for _, m, _, _ in LLAMA3_8B)
     if world > 1:
         import torch.distributed._symmetric_memory as symm_mem
@@ -201,6 +204,16 @@ def run_gpu(args):
         pkg.mul_mat_gather(ctx, Q4_K, Wc[rank * r:(rank + 1) * r].contiguous(), xc, torch.empty((1, r), device="cuda"), ptrs, 4096, rank * r)
         ctx.synchronize(); hdl.barrier(channel=0); torch.cuda.synchronize()
         assert torch.equal(ybuf[:4096].view(1, -1), full), "fused row-split all-gather differs from the unsplit result"
+    use_flags = world > 1 and args.gather_sync == "flags"
+    if use_flags:
+        # completion flags (b200_gather_sync_init): one uint32 per source rank, in symmetric memory
+        fbuf = symm_mem.empty(64, dtype=torch.int32, device=torch.device("cuda", local))
+        fbuf.zero_()
+        fhdl = symm_mem.rendezvous(fbuf, dist.group.WORLD)
+        torch.cuda.synchronize(); fhdl.barrier(channel=0); torch.cuda.synchronize()
+        import ctypes as C
+        farr = (C.c_void_p * world)(*[int(p) for p in fhdl.buffer_ptrs])
+        pkg.check(pkg.lib().b200_gather_sync_init(ctx.handle, rank, world, farr), "b200_gather_sync_init")
     ops = []   # (W shard uint8 [rows, rs], x f32 [1, k], y_full f32 [1, m], y_shard, full m)
     xs = {}
     for name, m, k, count in LLAMA3_8B:
@@ -228,7 +241,10 @@ def run_gpu(args):
             else:
                 slot = (i & 1) * maxm * 4
                 pkg.mul_mat_gather(ctx, Q4_K, W, x, ys, [p + slot for p in ptrs], m, rank * (m // world))
-                hdl.barrier(channel=0)
+                if not use_flags:
+                    hdl.barrier(channel=0)    # the gathered vector is complete on every rank before the next matmul
+        if use_flags:
+            hdl.barrier(channel=0)        # the last matmul's gather is complete everywhere before the step counts as done
 
     launches0 = ctx.launches
     with torch.cuda.stream(stream):
@@ -316,7 +332,7 @@ def run_gpu(args):
                        "l2": "inputs larger than L2: 4.22 GB of distinct weights per step vs 126 MB L2, no flush needed",
                        "launch": "CUDA graph replay" if graph is not None else "eager launches through the C ABI",
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
-                                                                          "memory + symmetric-memory barrier after every matmul"},
+                                                                          "memory; completion per matmul: " + ("in-kernel epoch flags" if use_flags else "symmetric-memory barrier")},
             "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
             "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clocks,
@@ -448,6 +464,7 @@ def main():
     ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--gather-sync", default="barrier", choices=["barrier", "flags"], help="N > 1: how a matmul's gather is completed")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

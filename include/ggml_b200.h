@@ -152,6 +152,13 @@ B200_API int  b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, in
 B200_API int  b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d_shard,
                                   int n_dst, float * const * dst, int64_t dst_m, int64_t dst_row0);
 
+/* Completion protocol for b200_mul_mat_gather (replaces a cross-GPU barrier after every matmul): flags[p] is rank p's
+ * array of `world` zero-initialised uint32 in peer-mapped memory.  The last CTA of every gather launch publishes the
+ * launch's epoch into flags[p][rank] for all p; the next gather launch waits, before reading its activations, until all
+ * ranks have published the previous launch.  All ranks must issue the same sequence of gather calls.  world = 0 turns
+ * the protocol off.  (ggml-cuda orders the same dependency with cross-device events, ggml-cuda.cu:2098-2119.) */
+B200_API int  b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags);
+
 /* ---- raw device memory (used by the backend shell's buffers and by ctypes callers without torch) -- */
 B200_API int  b200_malloc(int device, size_t nbytes, void ** out);
 B200_API int  b200_free(int device, void * ptr);

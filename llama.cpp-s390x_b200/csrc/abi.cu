@@ -126,6 +126,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->gs_state) cudaFree(ctx->gs_state);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
@@ -345,8 +346,14 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
             b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
             const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
             pending_push(ctx, d, !late);
+            if (n_peers > 0 && ctx->gs_world > 0) {
+                P.sync_flags = ctx->gs_flags[ctx->gs_rank];
+                for (int p = 0; p < ctx->gs_world; ++p) P.peer_flags[p] = ctx->gs_flags[p];
+                P.sync_state = ctx->gs_state; P.sync_rank = ctx->gs_rank; P.sync_world = ctx->gs_world;
+            }
             return b200_launch_gemv_q4k(ctx, P, (int) n, batches, late);
         }
+        if (n_peers > 0 && ctx->gs_world > 0) { b200_set_error("mul_mat_gather: the completion protocol needs the fused Q4_K GEMV"); return B200_E_UNSUPPORTED; }
         pending_push(ctx, d, true);
         int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
         if (rc) return rc;
@@ -539,6 +546,21 @@ int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor
     if (b->ne[1] > ctx->max_gemv_cols || b->ne[1] > 8) { b200_set_error("mul_mat_gather: n <= 8 columns only"); return B200_E_UNSUPPORTED; }
     if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
     return b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
+}
+
+int b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags) {
+    if (!ctx || world < 0 || world > B200_MAX_PEERS || (world > 0 && (!flags || rank < 0 || rank >= world))) {
+        b200_set_error("gather_sync_init: bad argument"); return B200_E_ARG;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->gs_world = world; ctx->gs_rank = rank;
+    for (int p = 0; p < world; ++p) ctx->gs_flags[p] = flags[p];
+    if (world > 0) {
+        if (!ctx->gs_state) B200_CUDA_TRY(cudaMalloc((void **) &ctx->gs_state, 2 * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMemset(ctx->gs_state, 0, 2 * sizeof(uint32_t)));
+    }
+    return B200_OK;
 }
 
 int b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, int64_t k, const float * x_host, int64_t n,

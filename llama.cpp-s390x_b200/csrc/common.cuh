@@ -83,6 +83,10 @@ struct b200_ctx {
     int          pdl;             // programmatic dependent launch for back-to-back GEMVs
     int          fuse_quant;      // 1: GEMV quantizes activations in its prologue (no separate launch)
     int          tc_split_k;     // tcgen05 GEMM: split long-K matrices with few tiles along K (0 never, 1 auto, 2/4 forced)
+    // fused row-split all-gather, one process per GPU (b200_gather_sync_init)
+    int          gs_rank, gs_world;
+    uint32_t *   gs_flags[8];
+    uint32_t *   gs_state;
     int          tc_nt;           // tcgen05 GEMM tile width override (0 = auto, 128, 256)
     int          gemv_cfg;        // CTA shape of the n=1 Q4_K GEMV: 0 = 32 warps x 1 CTA/SM, 1 = 16x2, 2 = 8x4, 3 = 16x1
     // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)

@@ -36,6 +36,13 @@ struct mm_problem {
     int     n_peers;
     float * peer_Y[8];
     int64_t peer_m, peer_row0;
+    // ... and, with one process per GPU, the completion protocol that replaces a barrier after every matmul: the last CTA
+    // of a launch publishes the launch's epoch number into flag[my rank] of every rank; the next launch, before it reads
+    // its activations, waits until all ranks' flags have reached the epoch of the launch before it (gemv_q4k).
+    uint32_t * sync_flags;        // this rank's flags[world] (peers write them through NVLink)
+    uint32_t * peer_flags[8];     // flag arrays of all ranks, indexed like peer_Y
+    uint32_t * sync_state;        // local: [0] epoch of the last finished launch, [1] CTAs of the current launch that are done
+    int        sync_rank, sync_world;
 };
 
 

@@ -304,6 +304,22 @@ gemv_q4k(const mm_problem P, const int flags) {
         if (live) first_loads();
     }
     if (!live) return;                                          // block-uniform
+    if (P.sync_flags) {
+        // fused row-split all-gather: the activations may derive from the previous matmul's gathered output, which is complete
+        // once every rank has published that launch's epoch (our own previous launch is complete: griddepcontrol.wait)
+        if (threadIdx.x == 0) {
+            const uint32_t e = *reinterpret_cast<volatile uint32_t *>(P.sync_state);
+            const long long t0 = clock64();
+            for (int src = 0; src < P.sync_world; ++src) {
+                uint32_t seen;
+                do {
+                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(P.sync_flags + src) : "memory");
+                    if (clock64() - t0 > 6000000000LL) __trap();        // a lost rank must not hang the others
+                } while ((int32_t) (seen - e) < 0);
+            }
+        }
+        __syncthreads();
+    }
 
     // ---- prologue: quantize the NC activation columns into shared memory (bit-exact Q8_1 values) ----
     {
@@ -359,6 +375,24 @@ gemv_q4k(const mm_problem P, const int flags) {
         row = nrow;
         it  = nit_i;
         sb  = nsbi;
+    }
+    if (P.sync_flags) {
+        // publish: every CTA makes its peer stores visible system-wide, the last one to finish bumps the epoch and writes it
+        // into flag[my rank] of every rank
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();                            // cumulative: covers the stores of the whole CTA (bar.sync above)
+            const unsigned total = gridDim.x * gridDim.y;
+            if (atomicAdd(P.sync_state + 1, 1u) == total - 1) {
+                P.sync_state[1] = 0;
+                const uint32_t e = P.sync_state[0] + 1;
+                P.sync_state[0] = e;
+                __threadfence_system();
+                for (int p = 0; p < P.sync_world; ++p) {
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(P.peer_flags[p] + P.sync_rank), "r"(e) : "memory");
+                }
+            }
+        }
     }
 }
 

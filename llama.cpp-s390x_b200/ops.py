@@ -120,3 +120,15 @@ def mul_mat_gather(ctx: Context, wtype: int, w_shard, x, out_shard, dst_ptrs, ds
     arr = (C.c_void_p * len(dst_ptrs))(*dst_ptrs)
     check(lib().b200_mul_mat_gather(ctx.handle, C.byref(a), C.byref(b), C.byref(d), len(dst_ptrs), arr, dst_m, dst_row0), "b200_mul_mat_gather")
     return out_shard
+
+
+def row_shard(m: int, rank: int, world: int, rounding: int = 128):
+    """(row0, rows) of rank's shard of an m-row weight matrix: even cut points rounded DOWN to `rounding` rows, the last
+    rank takes the remainder — the rule of get_row_split (ggml/src/ggml-cuda/ggml-cuda.cu:855-881) and b200_rowsplit_rows"""
+    def cut(i):
+        if i >= world:
+            return m
+        c = m * i // world
+        return c - c % rounding
+    lo, hi = cut(rank), cut(rank + 1)
+    return lo, hi - lo
