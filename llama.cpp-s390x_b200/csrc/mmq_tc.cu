@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
             for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
-            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 8); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 8 converter warps / commit
+            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) / commit
             for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 8); }   // expect_tx / 8 converter warps
             for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4); } // commit / 4 epilogue warps
             tc::mbar_fence_init();
@@ -359,10 +359,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     // so no divisions and no 64-bit arithmetic inside the stage loops.
     if (warp < 8) {
         // ===== converters: raw blocks (smem) -> fp16 -> swizzled K-major A tile ===========================================
-        // every warp takes 16 rows of every stage; adjacent lanes share a row (its two 32-element halves)
-        const int r = 16 * warp + (lane >> 1), h = lane & 1;
-        const uint32_t raw_row = sRaw + (uint32_t) (r * TC_RAW_ROW);
-        const uint32_t a_row   = sA + (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
+        // Two groups of 4 warps take alternate stages, so two stages are being converted at any time (one stage's
+        // store -> fence -> arrive latency hides behind the other's arithmetic).  A warp owns 32 rows of its stage: every lane
+        // two (row, half) tasks, adjacent lanes sharing a row.
+        const int grp = warp >> 2, h = lane & 1;
+        const int r0 = 32 * (warp & 3) + (lane >> 1), r1 = r0 + 16;
+        const uint32_t raw_row0 = sRaw + (uint32_t) (r0 * TC_RAW_ROW), raw_row1 = sRaw + (uint32_t) (r1 * TC_RAW_ROW);
+        const uint32_t a_row0 = sA + (uint32_t) ((r0 >> 3) * 1024 + (r0 & 7) * 128), a_row1 = sA + (uint32_t) ((r1 >> 3) * 1024 + (r1 & 7) * 128);
+        const int sw = r0 & 7;                                // r1 & 7 is the same
         int as = 0, rs = 0, sub = 0;
         uint32_t a_ph = 0, r_ph = 0;
         int tg = 0; (void) tg;
@@ -372,26 +376,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
             uint32_t skew = TYPE == B200_TYPE_Q8_0 ? 8u * (uint32_t) ((sg.k0 / SPR) & 1) : 0u;
             for (int it = sg.k0; it < sg.k1; ++it) {
-                if (sub == 0) tc::mbar_wait(bRFull + 8 * rs, r_ph);
-                w_frag<TYPE> f;
-                uint4 out[4]; int slot[4];
-                f.load(raw_row + rs * TC_RAW_BYTES + skew, sub, h);
-                f.convert(sub, h, out, slot);
-                tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1);
-                if (tid == 0) TC_TRACE(2, tg);
-                const uint32_t dst = a_row + as * TC_A_BYTES;
+                if ((it & 1) == grp) {                        // segments start at even stages, so parity follows `it`
+                    // first stage of this group in the raw slot: sub == grp (SPR is even)
+                    if (sub == grp) tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
+                    w_frag<TYPE> f0, f1;
+                    uint4 o0[4], o1[4]; int slot[4];
+                    f0.load(raw_row0 + rs * TC_RAW_BYTES + skew, sub, h);
+                    f1.load(raw_row1 + rs * TC_RAW_BYTES + skew, sub, h);
+                    f0.convert(sub, h, o0, slot);
+                    f1.convert(sub, h, o1, slot);
+                    tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
+                    if (tid == 0) TC_TRACE(2, tg);
+                    const uint32_t off = as * TC_A_BYTES;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + ((slot[c] ^ (r & 7)) << 4)),
-                                 "r"(out[c].x), "r"(out[c].y), "r"(out[c].z), "r"(out[c].w) : "memory");
-                }
-                tc::fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) {
-                    tc::mbar_arrive(bAFull + 8 * as);
-                    if (sub == SPR - 1) tc::mbar_arrive(bREmpty + 8 * rs);      // this warp is done reading the raw slot
-                    if (warp == 0) TC_TRACE(3, tg);
-                    if (warp == 7) TC_TRACE(5, tg);
+                    for (int c = 0; c < 4; ++c) {
+                        const uint32_t chunk = (uint32_t) ((slot[c] ^ sw) << 4);
+                        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_row0 + off + chunk),
+                                     "r"(o0[c].x), "r"(o0[c].y), "r"(o0[c].z), "r"(o0[c].w) : "memory");
+                        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_row1 + off + chunk),
+                                     "r"(o1[c].x), "r"(o1[c].y), "r"(o1[c].z), "r"(o1[c].w) : "memory");
+                    }
+                    tc::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tc::mbar_arrive(bAFull + 8 * as);
+                        if (sub == SPR - 2 + grp) tc::mbar_arrive(bREmpty + 8 * rs);    // this warp's last stage in the raw slot
+                        if (warp == 0) TC_TRACE(3, tg);
+                        if (warp == 7) TC_TRACE(5, tg);
+                    }
                 }
                 ++tg;
                 if (++as == AS) { as = 0; a_ph ^= 1; }
@@ -415,7 +427,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 int x = (sg.k0 / SPR) * a.raw_step, odd = (sg.k0 / SPR) & 1;    // next raw slot in the row (16-bit elements)
                 for (int it = sg.k0; it < sg.k1; ++it) {
                     if (sub == 0) {
-                        tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1);
+                        tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1, 100);
                         if (tc::elect_one()) {
                             tc::mbar_arrive_expect_tx(bRFull + 8 * rs, TC_RAW_BYTES);
                             tc::tma_load_3d(sRaw + rs * TC_RAW_BYTES, &tmW, bRFull + 8 * rs, x - (TYPE == B200_TYPE_Q8_0 ? 4 * odd : 0), t.row0, t.mat);
@@ -423,7 +435,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                         __syncwarp();
                         x += a.raw_step; odd ^= 1;
                     }
-                    tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1);
+                    tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
                     if (lane == 0) TC_TRACE(4, tg);
                     ++tg;
                     if (tc::elect_one()) {
@@ -482,7 +494,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         tc_seg sg;
         while (wk.next(a, NT, sg)) {
             const tc_tile & t = sg.t;
-            tc::mbar_wait(bAccFull + 8 * acc, acc_ph);
+            tc::mbar_wait(bAccFull + 8 * acc, acc_ph, 400);
             tc::tc_fence_after();
             const int row = t.row0 + 32 * q + lane;
             int32_t * turnstile = sg.nparts > 1 ? a.tile_sync + sg.T * 4 + q : nullptr;
@@ -543,8 +555,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     __syncthreads();
 #ifdef TC_TRACE_ENABLE
     if (blockIdx.x == 0 && tid == 0) {
-        const long long t0 = g_tc_trace[0][96];
-        for (int gg = 96; gg < 112; ++gg) {
+        const long long t0 = g_tc_trace[0][32];
+        for (int gg = 32; gg < 48; ++gg) {
             printf("g=%3d mma_ready=%6lld mma_done=%6lld conv_go=%6lld conv_arr0=%6lld conv_arr7=%6lld tma_go=%6lld\n", gg, g_tc_trace[0][gg] - t0,
                    g_tc_trace[1][gg] - t0, g_tc_trace[2][gg] - t0, g_tc_trace[3][gg] - t0, g_tc_trace[5][gg] - t0, g_tc_trace[4][gg] - t0);
         }

@@ -26,27 +26,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 // A broken pipeline must not hang the GPU box: after ~4 s of polling the kernel traps instead.
-__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    return ok != 0;
-}
-#ifndef TC_SPIN_TEST_WAIT
-#define TC_SPIN_TEST_WAIT 0
-#endif
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-#if TC_SPIN_TEST_WAIT
-    if (mbar_test_wait(bar, parity)) return;
-    const long long t1 = clock64();
-    while (!mbar_test_wait(bar, parity)) {
-        if (clock64() - t1 > 8000000000LL) __trap();
-    }
-    return;
-#endif
+// `nap` > 0: sleep that many ns between polls.  Roles that wait long (epilogue: a whole tile; TMA: a ring slot) must not spin,
+// their polling would take issue slots from the converter warps on the same scheduler (measured: 810 -> ... clocks / stage).
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned nap = 0) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
+        if (nap) __nanosleep(nap);
         if (clock64() - t0 > 8000000000LL) __trap();
     }
 }
