@@ -143,6 +143,19 @@ B200_API void b200_weights_free(b200_ctx * ctx, void * dev);
 B200_API int  b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, int64_t k,
                                 const float * x_host, int64_t n, float * y_host);
 
+/* The same for many matmuls at once (one decode / prefill step): all uploads, all launches, all downloads on the context's
+ * stream and ONE synchronisation — what ggml_backend_sched does around a graph_compute of several MUL_MAT nodes
+ * (ggml/src/ggml-backend.cpp: copy inputs -> compute -> copy outputs).  Host vectors that follow one another in memory are
+ * moved with a single copy. */
+typedef struct b200_host_mm {
+    int32_t type, _pad;
+    const void *  w_dev;     /* from b200_weights_upload */
+    int64_t       m, k, n;
+    const float * x_host;    /* [k, n] */
+    float *       y_host;    /* [m, n] */
+} b200_host_mm;
+B200_API int  b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs, int n_jobs);
+
 /* ---- row split, one process per GPU -------------------------------------------------------------- */
 /* MUL_MAT on this rank's row shard `a` (rows [dst_row0, dst_row0 + a->ne[1]) of the full matrix) with the all-gather of
  * the output fused into the kernel's stores: every result also goes to dst[p][col * dst_m + dst_row0 + row] for the

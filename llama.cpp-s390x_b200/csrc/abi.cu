@@ -585,4 +585,85 @@ int b200_mul_mat_host(b200_ctx * ctx, int type, const void * w_dev, int64_t m, i
     return B200_OK;
 }
 
+// A whole step's worth of matmuls with host activations / results: uploads (contiguous host ranges merged into one copy),
+// all launches back to back on the context's stream, downloads (merged likewise), ONE synchronisation.  This is what a
+// graph_compute over many MUL_MAT nodes amounts to for the scheduler (ggml-backend.cpp: copy inputs, compute, copy outputs).
+int b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs, int n_jobs) {
+    if (!ctx || (!jobs && n_jobs > 0) || n_jobs < 0) { b200_set_error("mul_mat_host_batch: bad argument"); return B200_E_ARG; }
+    if (n_jobs == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    size_t xb = 0, yb = 0;
+    for (int j = 0; j < n_jobs; ++j) {
+        const b200_host_mm & J = jobs[j];
+        if (!J.w_dev || !J.x_host || !J.y_host || !is_weight_type(J.type) || J.m <= 0 || J.k <= 0 || J.n <= 0) {
+            b200_set_error("mul_mat_host_batch: bad job %d", j); return B200_E_ARG;
+        }
+        xb += align_up((size_t) J.k * J.n * 4, 256);
+        yb += align_up((size_t) J.m * J.n * 4, 256);
+    }
+    int rc = grow(ctx, &ctx->dev_x, &ctx->dev_x_size, xb); if (rc) return rc;
+    rc     = grow(ctx, &ctx->dev_y, &ctx->dev_y_size, yb); if (rc) return rc;
+    char * dx = (char *) ctx->dev_x, * dy = (char *) ctx->dev_y;
+
+    // uploads: merge jobs whose host vectors follow one another in memory (device layout mirrors the host layout then)
+    size_t off = 0;
+    for (int j = 0; j < n_jobs; ) {
+        const char * h0 = (const char *) jobs[j].x_host;
+        size_t run = 0;
+        int e = j;
+        while (e < n_jobs && (const char *) jobs[e].x_host == h0 + run && ((size_t) jobs[e].k * jobs[e].n * 4) % 256 == 0) {
+            run += (size_t) jobs[e].k * jobs[e].n * 4; ++e;
+        }
+        if (e == j) { run = (size_t) jobs[j].k * jobs[j].n * 4; e = j + 1; }
+        B200_CUDA_TRY(cudaMemcpyAsync(dx + off, h0, run, cudaMemcpyHostToDevice, ctx->stream));
+        off += align_up(run, 256);
+        j = e;
+    }
+    // launches
+    size_t xo = 0, yo = 0;
+    for (int j = 0; j < n_jobs; ) {
+        // same run structure as above: inside a merged run the device offsets advance unpadded
+        const char * h0 = (const char *) jobs[j].x_host;
+        size_t run = 0;
+        int e = j;
+        while (e < n_jobs && (const char *) jobs[e].x_host == h0 + run && ((size_t) jobs[e].k * jobs[e].n * 4) % 256 == 0) {
+            run += (size_t) jobs[e].k * jobs[e].n * 4; ++e;
+        }
+        if (e == j) { run = (size_t) jobs[j].k * jobs[j].n * 4; e = j + 1; }
+        size_t in_run = 0;
+        for (int i = j; i < e; ++i) {
+            const b200_host_mm & J = jobs[i];
+            b200_tensor a = {}, b = {}, d = {};
+            a.data = (void *) J.w_dev; a.type = J.type; a.ne[0] = J.k; a.ne[1] = J.m; a.ne[2] = a.ne[3] = 1;
+            a.nb[0] = (int64_t) b200_tsize(J.type); a.nb[1] = (int64_t) b200_row_size(J.type, J.k); a.nb[2] = a.nb[3] = a.nb[1] * J.m;
+            b.data = dx + xo + in_run; b.type = B200_TYPE_F32; b.ne[0] = J.k; b.ne[1] = J.n; b.ne[2] = b.ne[3] = 1;
+            b.nb[0] = 4; b.nb[1] = J.k * 4; b.nb[2] = b.nb[3] = J.k * 4 * J.n;
+            d.data = dy + yo; d.type = B200_TYPE_F32; d.ne[0] = J.m; d.ne[1] = J.n; d.ne[2] = d.ne[3] = 1;
+            d.nb[0] = 4; d.nb[1] = J.m * 4; d.nb[2] = d.nb[3] = J.m * 4 * J.n;
+            rc = b200_mul_mat(ctx, &a, &b, &d);
+            if (rc) return rc;
+            in_run += (size_t) J.k * J.n * 4;
+            yo += align_up((size_t) J.m * J.n * 4, 256);
+        }
+        xo += align_up(run, 256);
+        j = e;
+    }
+    // downloads: merge jobs whose results are adjacent on the host AND on the device (sizes that are multiples of 256 B)
+    yo = 0;
+    for (int j = 0; j < n_jobs; ) {
+        char * h0 = (char *) jobs[j].y_host;
+        size_t run = 0, dev_run = 0;
+        int e = j;
+        while (e < n_jobs && (char *) jobs[e].y_host == h0 + run && run == dev_run) {
+            const size_t sz = (size_t) jobs[e].m * jobs[e].n * 4;
+            run += sz; dev_run += align_up(sz, 256); ++e;
+        }
+        B200_CUDA_TRY(cudaMemcpyAsync(h0, dy + yo, run, cudaMemcpyDeviceToHost, ctx->stream));
+        yo += dev_run;
+        j = e;
+    }
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
 }  // extern "C"

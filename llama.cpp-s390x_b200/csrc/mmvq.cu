@@ -245,7 +245,7 @@ __device__ __forceinline__ void q4k_task(const q4k_frag & f, const int sb, const
     }
 }
 
-template <int NC, int NWARPS, int MINB, int NBUF>
+template <int NC, int NWARPS, int MINB, int NBUF, bool SYNC>
 __global__ void __launch_bounds__(NWARPS * 32, MINB)
 gemv_q4k(const mm_problem P, const int flags) {
     // flags: < 0 launch-floor probe (ctx option "noop"); bit 0 = PDL launch (prefetch weights before the dependency wait);
@@ -304,7 +304,7 @@ gemv_q4k(const mm_problem P, const int flags) {
         if (live) first_loads();
     }
     if (!live) return;                                          // block-uniform
-    if (P.sync_flags) {
+    if (SYNC && P.sync_flags) {
         // fused row-split all-gather: the activations may derive from the previous matmul's gathered output, which is complete
         // once every rank has published that launch's epoch (our own previous launch is complete: griddepcontrol.wait)
         if (threadIdx.x == 0) {
@@ -376,7 +376,7 @@ gemv_q4k(const mm_problem P, const int flags) {
         it  = nit_i;
         sb  = nsbi;
     }
-    if (P.sync_flags) {
+    if (SYNC && P.sync_flags) {
         // publish: every CTA makes its peer stores visible system-wide, the last one to finish bumps the epoch and writes it
         // into flag[my rank] of every rank
         __syncthreads();
@@ -416,9 +416,15 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
     return B200_OK;
 }
 
-template <int NC, int NWARPS, int MINB, int NBUF>
+template <int NC, int NWARPS, int MINB, int NBUF, bool SYNC = false>
 int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem, bool late_wait) {
-    auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF>;
+    if (!SYNC && P.sync_flags) {
+        // the cross-rank completion protocol lives in its own instantiation so that the single-GPU kernel pays nothing for it
+        if (NC == 1 && NWARPS == 32 && MINB == 1 && NBUF == 0) return launch_q4k_t<1, 32, 1, 0, true>(ctx, P, tiles, smem, late_wait);
+        b200_set_error("gemv_q4k: the completion protocol is built for n = 1 with the default CTA shape");
+        return B200_E_UNSUPPORTED;
+    }
+    auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF, SYNC>;
     static bool attr_done[16] = {};            // per device
     if (!attr_done[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));

@@ -280,3 +280,28 @@ def test_mul_mat_host_and_back_to_back_dependencies(pkg, gpu_ctx, orc):
         assert nmse(w1, y1.cpu().numpy()) <= NMSE_TOL
         assert nmse(oracle_mul_mat(orc, refenv.Q4_K, W2, y1.cpu().numpy()), y2.cpu().numpy()) <= NMSE_TOL
         assert torch.equal(y1, y3)
+
+
+def test_mul_mat_host_batch_matches_single_calls(pkg, gpu_ctx):
+    """b200_mul_mat_host_batch: contiguous and scattered host vectors, mixed types and n; identical to b200_mul_mat_host"""
+    import ctypes as C
+    import torch
+    L = pkg.lib()
+    rng = np.random.default_rng(3)
+    specs = [("q4_K", 512, 1024, 1), ("q4_K", 256, 1024, 1), ("q8_0", 128, 512, 2), ("q6_K", 300, 256, 1), ("q4_0", 64, 2048, 9)]
+    xh = torch.randn((sum(k * n for _, _, k, n in specs) + 64,)).pin_memory()
+    yh = torch.zeros((sum(m * n for _, m, _, n in specs) + 64,)).pin_memory()
+    want = torch.zeros_like(yh)
+    jobs = (pkg.HostMM * len(specs))()
+    Ws, xo, yo = [], 0, 0
+    hctx = pkg.Context(0)
+    for j, (name, m, k, n) in enumerate(specs):
+        if j == 3:
+            xo += 16; yo += 16                               # break the contiguity once
+        W = dev(random_blocks(TYPES[name], m, k, rng)); Ws.append(W)
+        jobs[j].type, jobs[j].w_dev, jobs[j].m, jobs[j].k, jobs[j].n = TYPES[name], W.data_ptr(), m, k, n
+        jobs[j].x_host, jobs[j].y_host = xh.data_ptr() + 4 * xo, yh.data_ptr() + 4 * yo
+        pkg.check(L.b200_mul_mat_host(hctx.handle, TYPES[name], W.data_ptr(), m, k, xh.data_ptr() + 4 * xo, n, want.data_ptr() + 4 * yo), "single")
+        xo += k * n; yo += m * n
+    pkg.check(L.b200_mul_mat_host_batch(hctx.handle, jobs, len(specs)), "batch")
+    assert torch.equal(yh, want) and float(yh.abs().max()) > 0
