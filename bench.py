@@ -155,8 +155,30 @@ def prefill_bench(torch, pkg, ctx, stream, n=512):
             total_ms += ms * count
             flops += 2.0 * m * n * k * count
             del Ws, X, Y
-        tf = flops / total_ms / 1e9
-        out[tname] = {"ms_per_step": round(total_ms, 3), "tok_per_s_matmul_only": round(n / total_ms * 1e3, 1), "tflops": round(tf, 1),
+        # the step with wq/wk/wv and ffn_gate/ffn_up fused (b200_mul_mat_multi: one activation conversion, one grid per group)
+        sep = {(m, k): per[f"{m}x{k}"]["us"] * 1e-3 for (m, k) in shapes}
+        fused_ms = total_ms
+        for gname, ms_ in (("qkv", (4096, 1024, 1024)), ("gate_up", (14336, 14336))):
+            k = 4096
+            Ws = [[make(torch, m, k, gen) for m in ms_] for _ in range(3)]
+            X = torch.randn((n, k), device="cuda", generator=gen)
+            Ys = [torch.empty((n, m), device="cuda") for m in ms_]
+            with torch.cuda.stream(stream):
+                for i in range(3):
+                    pkg.mul_mat_multi(ctx, ttype, Ws[i % 3], X, Ys)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for i in range(12):
+                    pkg.mul_mat_multi(ctx, ttype, Ws[i % 3], X, Ys)
+                e1.record(stream)
+                stream.synchronize()
+            ms = e0.elapsed_time(e1) / 12
+            per[gname + "_fused"] = {"us": round(ms * 1e3, 1), "tflops": round(2.0 * sum(ms_) * n * k / ms / 1e9, 1)}
+            fused_ms += 32 * (ms - sum(sep[(m, k)] for m in ms_))
+            del Ws, X, Ys
+        tf = flops / fused_ms / 1e9
+        out[tname] = {"ms_per_step": round(fused_ms, 3), "ms_per_step_unfused": round(total_ms, 3),
+                      "tok_per_s_matmul_only": round(n / fused_ms * 1e3, 1), "tflops": round(tf, 1),
                       "frac_of_tensor_peak": round(tf / peak, 4), "per_shape": per}
     return out
 
@@ -234,7 +256,29 @@ def run_gpu(args):
     per_layer = [[o for o in ops[i * 32:(i + 1) * 32]] for i in range(7)]
     order = [per_layer[j][l] for l in range(32) for j in range(7)] + [ops[-1]]
 
+    # 1 GPU: the matrices that share their activations (wq / wk / wv, ffn_gate / ffn_up) go through b200_mul_mat_multi, one launch
+    # per group — the same 225 matmuls in 129 launches (--no-fuse: one b200_mul_mat each)
+    fuse = world == 1 and not args.no_fuse
+    groups, i = [], 0
+    while i < len(order):
+        g = [order[i]]
+        while fuse and order[i][4][1] in ("wq", "wk", "ffn_gate") and i + 1 < len(order) and order[i + 1][1] is order[i][1] \
+                and order[i + 1][4][1] in ("wk", "wv", "ffn_up"):
+            i += 1
+            g.append(order[i])
+        groups.append(g)
+        i += 1
+
+    n_groups = len(groups)
+
     def step():
+        if fuse:
+            for g in groups:
+                if len(g) == 1:
+                    pkg.mul_mat(ctx, Q4_K, g[0][0], g[0][1], out=g[0][3])
+                else:
+                    pkg.mul_mat_multi(ctx, Q4_K, [o[0] for o in g], g[0][1], [o[3] for o in g])
+            return
         for i, (W, x, y, ys, (m, name)) in enumerate(order):
             if world == 1:
                 pkg.mul_mat(ctx, Q4_K, W, x, out=ys)
@@ -340,7 +384,7 @@ def run_gpu(args):
         shapes = per_shape(torch, pkg, ctx, stream, ops)
     prefill = None
     if world == 1 and not args.no_prefill:
-        del ops, order, per_layer
+        del ops, order, per_layer, groups
         torch.cuda.empty_cache()
         prefill = prefill_bench(torch, pkg, ctx, stream)
 
@@ -353,7 +397,8 @@ def run_gpu(args):
             "config": {"workload": "Llama-3-8B Q4_K decode step: 225 MUL_MATs at n=1 (k=4096, m=4096/1024/14336/128256; m=4096,k=14336)",
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
                        "l2": "inputs larger than L2: 4.22 GB of distinct weights per step vs 126 MB L2, no flush needed",
-                       "launch": "CUDA graph replay" if graph is not None else "eager launches through the C ABI",
+                       "launch": ("CUDA graph replay" if graph is not None else "eager launches through the C ABI") +
+                                 (f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
                                                                           "memory; completion per matmul: " + ("in-kernel epoch flags after every matmul" if use_flags else "symmetric-memory barrier after wv / wo / ffn_up / ffn_down / output (129 per step)")},
             "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
@@ -361,8 +406,8 @@ def run_gpu(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(value / world, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(value / world / peak, 4), "traffic": None, "peak_source": peak_src,
-                         "kernel": "gemv_q4k<1,32> (all 225 launches of the step)",
-                         "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / STEP_MATMULS / world)},
+                         "kernel": f"gemv_q4k<1,32> (all {launches_per_step} launches of the step, {STEP_MATMULS} matmuls)",
+                         "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / launches_per_step / world)},
         }
         if e2e:
             out["e2e"] = e2e
@@ -488,6 +533,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     ap.add_argument("--gather-sync", default="barrier", choices=["barrier", "flags"], help="N > 1: how a matmul's gather is completed")
+    ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -156,6 +156,13 @@ typedef struct b200_host_mm {
 } b200_host_mm;
 B200_API int  b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs, int n_jobs);
 
+/* n_mats (1..3 fused; more are run one by one) weight matrices against the SAME activations `b`: d[j] = a[j] x b.  What a
+ * transformer layer does for the q/k/v projections and for ffn gate/up: the reference issues one MUL_MAT node per matrix
+ * (src/llama-graph.cpp build_attn / build_ffn -> ggml_mul_mat per weight); here matrices of equal type and row length share
+ * one launch — a single activation prologue, one grid — with results bit-identical to n_mats b200_mul_mat calls. */
+B200_API int  b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b,
+                                 const b200_tensor * const * d);
+
 /* ---- row split, one process per GPU -------------------------------------------------------------- */
 /* MUL_MAT on this rank's row shard `a` (rows [dst_row0, dst_row0 + a->ne[1]) of the full matrix) with the all-gather of
  * the output fused into the kernel's stores: every result also goes to dst[p][col * dst_m + dst_row0 + row] for the

@@ -17,6 +17,7 @@ int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_strid
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
+int    b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d);
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
                        int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
@@ -546,6 +547,53 @@ int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor
     if (b->ne[1] > ctx->max_gemv_cols || b->ne[1] > 8) { b200_set_error("mul_mat_gather: n <= 8 columns only"); return B200_E_UNSUPPORTED; }
     if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
     return b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
+}
+
+// Several weight matrices against the same activations (q/k/v projections, gate/up): one launch instead of n_mats.
+int b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d) {
+    if (!ctx || n_mats < 1 || !a || !b || !d) { b200_set_error("mul_mat_multi: bad argument"); return B200_E_ARG; }
+    for (int j = 0; j < n_mats; ++j) {
+        if (const char * why = check_mul_mat(a[j], b, d[j])) { b200_set_error("mul_mat_multi[%d]: %s", j, why); return B200_E_ARG; }
+    }
+    bool fusable = n_mats >= 2 && n_mats <= 3 && !ctx->force_generic && b->ne[2] * b->ne[3] == 1;
+    for (int j = 0; fusable && j < n_mats; ++j) {
+        fusable = a[j]->type == a[0]->type && a[j]->ne[0] == a[0]->ne[0] && a[j]->nb[1] == a[0]->nb[1] && a[j]->ne[2] * a[j]->ne[3] == 1 &&
+                  a[j]->ne[1] > 0 && aligned16(a[j]->data, a[j]->nb[1], 0, 0);
+    }
+    const int64_t k = a[0]->ne[0], n = b->ne[1];
+    if (fusable && n == 1 && a[0]->type == B200_TYPE_Q4_K && ctx->fuse_quant && aligned16(b->data, b->nb[1], 0, 0) &&
+        b200_gemv_q4k_smem(1, k) <= ctx->smem_optin) {
+        B200_CUDA_TRY(cudaSetDevice(ctx->device));
+        mm_problem P = {};
+        P.W = (const uint8_t *) a[0]->data; P.nb01 = a[0]->nb[1]; P.k = k;
+        P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = b->nb[3];
+        P.ne11 = 1; P.ne12 = 1; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+        P.Y = (float *) d[0]->data; P.mode = MM_PLAIN;
+        P.n_mats = n_mats;
+        int64_t start = a[0]->ne[1];
+        P.m_end[0] = start; P.m_end[1] = INT64_MAX;
+        for (int j = 1; j < n_mats; ++j) {
+            P.Wv[j - 1] = (const uint8_t *) a[j]->data - start * P.nb01;
+            P.Yv[j - 1] = (float *) d[j]->data - start;
+            start += a[j]->ne[1];
+            if (j == 1) P.m_end[1] = start;
+        }
+        if (n_mats == 2) { P.Wv[1] = P.Wv[0]; P.Yv[1] = P.Yv[0]; P.m_end[1] = start; }
+        P.m = start;
+        const bool late = ctx->n_pend + n_mats <= 16 && can_defer_wait(ctx, b, nullptr);
+        for (int j = 0; j < n_mats; ++j) pending_push(ctx, d[j], !late && j == 0);
+        return b200_launch_gemv_q4k(ctx, P, 1, 1, late);
+    }
+    if (fusable && n > 8 && ctx->use_tc) {
+        for (int j = 0; j < n_mats; ++j) pending_push(ctx, d[j], j == 0);      // normal launches: everything before is complete
+        const int rc = b200_mul_mat_multi_tc(ctx, n_mats, a, b, d);
+        if (rc != B200_E_UNSUPPORTED) return rc;
+    }
+    for (int j = 0; j < n_mats; ++j) {
+        const int rc = b200_mul_mat(ctx, a[j], b, d[j]);
+        if (rc) return rc;
+    }
+    return B200_OK;
 }
 
 int b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags) {

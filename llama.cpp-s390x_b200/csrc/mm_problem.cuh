@@ -43,6 +43,13 @@ struct mm_problem {
     uint32_t * peer_flags[8];     // flag arrays of all ranks, indexed like peer_Y
     uint32_t * sync_state;        // local: [0] epoch of the last finished launch, [1] CTAs of the current launch that are done
     int        sync_rank, sync_world;
+    // several weight matrices against the SAME activations in one launch (q/k/v, gate/up): rows are numbered through all of
+    // them, m = total; matrix j > 0 starts at row m_end[j-1].  Wv / Yv are "virtual bases" (W_j - start_j * nb01, Y_j - start_j),
+    // so row r of the numbering is addressed as base + r like in the single-matrix case.  MM_PLAIN, n = 1, no batch dims.
+    int             n_mats;
+    int64_t         m_end[2];
+    const uint8_t * Wv[2];
+    float *         Yv[2];
 };
 
 

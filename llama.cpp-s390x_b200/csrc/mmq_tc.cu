@@ -60,6 +60,12 @@ struct tc_args {
     int     mode;
     int     n_expert;
     const int32_t * expert_bounds;
+    // several weight matrices against the same activations (q/k/v, gate/up; MM_PLAIN, no batch dims): row tiles are numbered
+    // through all of them, every matrix padded to whole tiles; matrix j has its own TMA map, height and output
+    int     n_mats;
+    int     rt_end[3];          // cumulative row tiles
+    int     m_j[3];
+    float * Y_j[3];
     int64_t n_tiles;            // row tiles x column tiles (upper bound for MUL_MAT_ID) x batches
     int     grid;               // persistent CTAs
     int     split_k;            // K parts per tile (1, 2 or 4); the parts of a tile are summed in ascending K order
@@ -250,12 +256,21 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
 struct tc_tile {
     int mat;            // weight matrix index (batch / expert) = 3rd TMA coordinate
     int row0, pos0, nvalid;
+    int wsel;           // which weight tensor map (several matrices per launch)
+    int m;              // height of the matrix = column stride of its output
+    float * Y;
 };
 
 __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int64_t T, tc_tile & t) {
-    const int row_tiles = (a.m + TC_M - 1) / TC_M;
-    const int rt = (int) (T % row_tiles);
+    const int row_tiles = a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + TC_M - 1) / TC_M;
+    int rt = (int) (T % row_tiles);
     T /= row_tiles;
+    t.wsel = 0; t.m = a.m; t.Y = a.Y;
+    if (a.n_mats > 1) {
+        const int j = (rt >= a.rt_end[0]) + (rt >= a.rt_end[1]);
+        rt -= j == 0 ? 0 : a.rt_end[j - 1];
+        t.wsel = j; t.m = a.m_j[j]; t.Y = a.Y_j[j];
+    }
     t.row0 = rt * TC_M;
     if (a.mode == MM_PLAIN) {
         const int col_tiles = (a.n + NT - 1) / NT;
@@ -319,7 +334,8 @@ __device__ long long g_tc_trace[6][128];
 #endif
 
 template <int TYPE, int NT>
-__global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmB,
+__global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1,
+                                                                   const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmB,
                                                                    const tc_args a) {
     using cfg = tc_cfg<NT>;
     constexpr int BS  = cfg::B_SLOTS, AS = TC_A_SLOTS, RS = TC_RAW_SLOTS;
@@ -430,7 +446,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                         tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1, 100);
                         if (tc::elect_one()) {
                             tc::mbar_arrive_expect_tx(bRFull + 8 * rs, TC_RAW_BYTES);
-                            tc::tma_load_3d(sRaw + rs * TC_RAW_BYTES, &tmW, bRFull + 8 * rs, x - (TYPE == B200_TYPE_Q8_0 ? 4 * odd : 0), t.row0, t.mat);
+                            const CUtensorMap * tw = t.wsel == 0 ? &tmW : (t.wsel == 1 ? &tmW1 : &tmW2);
+                            tc::tma_load_3d(sRaw + rs * TC_RAW_BYTES, tw, bRFull + 8 * rs, x - (TYPE == B200_TYPE_Q8_0 ? 4 * odd : 0), t.row0, t.mat);
                         }
                         __syncwarp();
                         x += a.raw_step; odd ^= 1;
@@ -526,7 +543,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
                         const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
-                        if (c0 + c < t.nvalid && row < a.m) a.Y[(int64_t) yc * a.m + row] = __uint_as_float(v[c]) * sc;
+                        if (c0 + c < t.nvalid && row < t.m) t.Y[(int64_t) yc * t.m + row] = __uint_as_float(v[c]) * sc;
                     }
                 } else {
                     // add to the earlier parts' sum with fire-and-forget reductions (no load round trip); the turnstile orders
@@ -535,8 +552,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
                         const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
-                        if (c0 + c < t.nvalid && row < a.m) {
-                            asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" :: "l"(a.Y + (int64_t) yc * a.m + row), "f"(__uint_as_float(v[c]) * sc) : "memory");
+                        if (c0 + c < t.nvalid && row < t.m) {
+                            asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" :: "l"(t.Y + (int64_t) yc * t.m + row), "f"(__uint_as_float(v[c]) * sc) : "memory");
                         }
                     }
                 }
@@ -587,21 +604,21 @@ encode_tiled_fn get_encode() {
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
 
 template <int TYPE, int NT>
-int launch_one(b200_ctx * ctx, const CUtensorMap & tmw, const CUtensorMap & tm, const tc_args & a) {
+int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     static bool configured[16] = {};
     auto kern = mmq_tc_f16_kernel<TYPE, NT>;
     if (!configured[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT>::SMEM));
         configured[ctx->device & 15] = true;
     }
-    kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw, tm, a);
+    kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
 }
 
 template <int NT>
-int launch_type(b200_ctx * ctx, int type, const CUtensorMap & tmw, const CUtensorMap & tm, const tc_args & a) {
+int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
         case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tmw, tm, a);
         case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tmw, tm, a);
@@ -661,9 +678,23 @@ static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_p
     return p;
 }
 
+struct tc_multi {            // several matrices per launch: P.m is the padded total height, these are the parts
+    int n_mats;
+    const uint8_t * W[3];
+    int64_t m[3];
+    float * Y[3];
+};
+
+static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M);
+size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
+
 // n_pos = number of activation positions (MM_PLAIN: ne11 * batches; MM_ID_SORTED: pairs).  Uses the context scratch
 // AFTER `ws_used` bytes (the caller may keep ids there).
 int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used) {
+    return launch_gemm_tc_core(ctx, type, P, n_pos, ws_used, nullptr);
+}
+
+static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M) {
     const tc_plan pl = make_plan(ctx, P, n_pos, ws_used);
     if ((size_t) ctx->ws_size < pl.total) { b200_set_error("tcgen05 GEMM: scratch not reserved"); return B200_E_ARG; }
     uint8_t * ws = (uint8_t *) ctx->ws;
@@ -689,13 +720,17 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
     // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 128 rows x 144 bytes
     const int64_t ne02 = P.mode == MM_PLAIN ? P.ne12 / P.r2 : P.n_expert;
     const int64_t nmat = P.mode == MM_PLAIN ? ne02 * (P.ne13 / P.r3) : P.n_expert;
-    CUtensorMap tmw;
-    {
-        const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) P.m, (cuuint64_t) nmat};
-        const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (nmat > 1 ? P.nb02 : P.nb01 * P.m)};
+    CUtensorMap tmw[3];
+    for (int j = 0; j < 3; ++j) {
+        const int jj = M ? (j < M->n_mats ? j : 0) : 0;
+        if (j > 0 && jj == 0) { tmw[j] = tmw[0]; continue; }
+        const void *  base = M ? (const void *) M->W[jj] : (const void *) P.W;
+        const int64_t rows = M ? M->m[jj] : P.m;
+        const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) rows, (cuuint64_t) (M ? 1 : nmat)};
+        const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (!M && nmat > 1 ? P.nb02 : P.nb01 * rows)};
         const cuuint32_t wbox[3]    = {(cuuint32_t) TC_RAW_ROW / 2, (cuuint32_t) TC_M, 1};
         const cuuint32_t westr[3]   = {1, 1, 1};
-        const CUresult wr = get_encode()(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) P.W, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+        const CUresult wr = get_encode()(&tmw[j], CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) base, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (wr != CUDA_SUCCESS) { b200_set_error("cuTensorMapEncodeTiled (weights) failed (%d)", (int) wr); return B200_E_CUDA; }
     }
@@ -708,6 +743,15 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
+    a.n_mats = M ? M->n_mats : 1;
+    if (M) {
+        int rt = 0;
+        for (int j = 0; j < 3; ++j) {
+            const int jj = j < M->n_mats ? j : M->n_mats - 1;
+            if (j < M->n_mats) rt += (int) ((M->m[j] + TC_M - 1) / TC_M);
+            a.rt_end[j] = rt; a.m_j[j] = (int) M->m[jj]; a.Y_j[j] = M->Y[jj];
+        }
+    }
 
     a.n_tiles = pl.n_tiles;
     // Scheduling: whole tiles, walked in the same order by all CTAs (they move along K in step and share activation tiles in
@@ -731,6 +775,29 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
         B200_CUDA_TRY(cudaMemsetAsync(a.tile_sync, 0, (size_t) pl.n_tiles * 4 * sizeof(int32_t), ctx->stream));
     }
     return NT == 128 ? launch_type<128>(ctx, type, tmw, tm, a) : launch_type<256>(ctx, type, tmw, tm, a);
+}
+
+// several weight matrices x the same activations (caller checked: same type / k / row size, MM_PLAIN without batch dims)
+int b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d) {
+    mm_problem P = {};
+    P.W = (const uint8_t *) a[0]->data; P.nb01 = a[0]->nb[1]; P.nb02 = a[0]->nb[1] * a[0]->ne[1]; P.nb03 = P.nb02;
+    P.k = a[0]->ne[0];
+    P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = b->nb[3];
+    P.ne11 = b->ne[1]; P.ne12 = 1; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+    P.Y = (float *) d[0]->data; P.mode = MM_PLAIN;
+    tc_multi M = {};
+    M.n_mats = n_mats;
+    int64_t padded = 0;
+    for (int j = 0; j < n_mats; ++j) {
+        M.W[j] = (const uint8_t *) a[j]->data; M.m[j] = a[j]->ne[1]; M.Y[j] = (float *) d[j]->data;
+        padded += (a[j]->ne[1] + TC_M - 1) / TC_M * TC_M;
+    }
+    P.m = padded;
+    if (!b200_tc_supported(ctx, a[0]->type, P)) return B200_E_UNSUPPORTED;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, b->ne[1], 0));
+    if (rc) return rc;
+    return launch_gemm_tc_core(ctx, a[0]->type, P, b->ne[1], 0, &M);
 }
 
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) { return make_plan(ctx, P, n_pos, ws_used).total; }

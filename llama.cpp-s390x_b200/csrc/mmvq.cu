@@ -245,9 +245,11 @@ __device__ __forceinline__ void q4k_task(const q4k_frag & f, const int sb, const
     }
 }
 
-template <int NC, int NWARPS, int MINB, int NBUF, bool SYNC>
+// VARIANT: 0 = plain, 1 = cross-rank completion protocol (row split, one process per GPU), 2 = several matrices per launch
+template <int NC, int NWARPS, int MINB, int NBUF, int VARIANT>
 __global__ void __launch_bounds__(NWARPS * 32, MINB)
 gemv_q4k(const mm_problem P, const int flags) {
+    constexpr bool SYNC = VARIANT == 1, MULTI = VARIANT == 2;
     // flags: < 0 launch-floor probe (ctx option "noop"); bit 0 = PDL launch (prefetch weights before the dependency wait);
     //        bit 1 = X / ids are NOT written by any kernel still in flight (abi.cu tracks that): the wait moves from
     //        "before reading X" to "before the first store", so this kernel's prologue and streaming overlap the previous
@@ -278,12 +280,17 @@ gemv_q4k(const mm_problem P, const int flags) {
     int      it  = 0, sb = sbl;
     q4k_frag cur;
     const uint8_t * Wm = nullptr;
+    auto wrow = [&](const int64_t r) -> const uint8_t * {
+        const uint8_t * base = Wm;
+        if (MULTI) base = r < P.m_end[0] ? Wm : (r < P.m_end[1] ? P.Wv[0] : P.Wv[1]);
+        return base + r * P.nb01;
+    };
     auto first_loads = [&]() {
         if (NBUF > 0 && lane == 0) {
-            if (row < rhi)          l2_prefetch(Wm + row * P.nb01, row_bytes);
-            if (row + NWARPS < rhi) l2_prefetch(Wm + (row + NWARPS) * P.nb01, row_bytes);
+            if (row < rhi)          l2_prefetch(wrow(row), row_bytes);
+            if (row + NWARPS < rhi) l2_prefetch(wrow(row + NWARPS), row_bytes);
         }
-        if (row < rhi && sb < nsb) q4k_load(cur, Wm + row * P.nb01, sb, g);
+        if (row < rhi && sb < nsb) q4k_load(cur, wrow(row), sb, g);
     };
 
     const bool early = prefetch_before_wait && (P.mode == MM_PLAIN || late_wait);
@@ -359,15 +366,19 @@ gemv_q4k(const mm_problem P, const int flags) {
         if (nit_i >= nit) { nrow = row + NWARPS; nit_i = 0; }
         const int nsbi = nit_i * 8 + sbl;
         q4k_frag nxt;
-        if (nrow < rhi && nsbi < nsb) q4k_load(nxt, Wm + nrow * P.nb01, nsbi, g);
-        if (NBUF > 0 && it == 0 && lane == 0 && row + 2 * NWARPS < rhi) l2_prefetch(Wm + (row + 2 * NWARPS) * P.nb01, row_bytes);
+        if (nrow < rhi && nsbi < nsb) q4k_load(nxt, wrow(nrow), nsbi, g);
+        if (NBUF > 0 && it == 0 && lane == 0 && row + 2 * NWARPS < rhi) l2_prefetch(wrow(row + 2 * NWARPS), row_bytes);
         if (sb < nsb) q4k_task<NC>(cur, sb, g, x, s_qs, s_ds, k, acc);
         if (nrow != row) {
             if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
 #pragma unroll
             for (int col = 0; col < NC; ++col) {
                 const float s = warp_sum(acc[col]);
-                if (lane == 0 && col < C.nc) mm_store(P, C.y[col], row, s);
+                if (MULTI) {
+                    if (lane == 0) (row < P.m_end[0] ? C.y[0] : (row < P.m_end[1] ? P.Yv[0] : P.Yv[1]))[row] = s;
+                } else if (lane == 0 && col < C.nc) {
+                    mm_store(P, C.y[col], row, s);
+                }
                 acc[col] = 0.0f;
             }
         }
@@ -416,15 +427,18 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
     return B200_OK;
 }
 
-template <int NC, int NWARPS, int MINB, int NBUF, bool SYNC = false>
+template <int NC, int NWARPS, int MINB, int NBUF, int VARIANT = 0>
 int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem, bool late_wait) {
-    if (!SYNC && P.sync_flags) {
-        // the cross-rank completion protocol lives in its own instantiation so that the single-GPU kernel pays nothing for it
-        if (NC == 1 && NWARPS == 32 && MINB == 1 && NBUF == 0) return launch_q4k_t<1, 32, 1, 0, true>(ctx, P, tiles, smem, late_wait);
-        b200_set_error("gemv_q4k: the completion protocol is built for n = 1 with the default CTA shape");
+    if (VARIANT == 0 && (P.sync_flags || P.n_mats > 1)) {
+        // the cross-rank completion protocol and the several-matrices form live in their own instantiations so that the plain
+        // kernel pays nothing for them
+        if (NC == 1 && NWARPS == 32 && MINB == 1 && NBUF == 0 && !(P.sync_flags && P.n_mats > 1)) {
+            return P.sync_flags ? launch_q4k_t<1, 32, 1, 0, 1>(ctx, P, tiles, smem, late_wait) : launch_q4k_t<1, 32, 1, 0, 2>(ctx, P, tiles, smem, late_wait);
+        }
+        b200_set_error("gemv_q4k: this variant is built for n = 1 with the default CTA shape");
         return B200_E_UNSUPPORTED;
     }
-    auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF, SYNC>;
+    auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF, VARIANT>;
     static bool attr_done[16] = {};            // per device
     if (!attr_done[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));

@@ -66,6 +66,22 @@ def mul_mat(ctx: Context, wtype: int, w, x, out=None):
     return out
 
 
+def mul_mat_multi(ctx: Context, wtype: int, ws, x, outs=None):
+    """outs[j] = ws[j] x x for several weight matrices sharing the activations (q/k/v, gate/up) — one launch when fusable"""
+    import torch
+    k = x.shape[-1]
+    if outs is None:
+        outs = [torch.empty(tuple(x.shape[:-1]) + (w.shape[-2],), dtype=torch.float32, device=x.device) for w in ws]
+    a = [_desc(w, wtype, k_elems=k) for w in ws]
+    d = [_desc(o, F32) for o in outs]
+    b = _desc(x, F32)
+    T = C.POINTER(Tensor)
+    ap = (T * len(ws))(*[C.pointer(t) for t in a])
+    dp = (T * len(ws))(*[C.pointer(t) for t in d])
+    check(lib().b200_mul_mat_multi(ctx.handle, len(ws), ap, C.byref(b), dp), "b200_mul_mat_multi")
+    return outs
+
+
 def mul_mat_supported(wtype: int, w, x) -> bool:
     import torch
     a = _desc(w, wtype, k_elems=x.shape[-1])

@@ -305,3 +305,54 @@ def test_mul_mat_host_batch_matches_single_calls(pkg, gpu_ctx):
         xo += k * n; yo += m * n
     pkg.check(L.b200_mul_mat_host_batch(hctx.handle, jobs, len(specs)), "batch")
     assert torch.equal(yh, want) and float(yh.abs().max()) > 0
+
+
+@pytest.mark.parametrize("name,ms,k,n", [
+    ("q4_K", (512, 128, 128), 1024, 1),        # fused GEMV, q/k/v shaped
+    ("q4_K", (1792, 1792), 512, 1),            # fused GEMV, gate/up shaped
+    ("q4_K", (300, 77), 256, 1),               # ragged heights
+    ("q4_K", (512, 128, 128), 1024, 40),       # tcgen05, three matrices
+    ("q4_K", (300, 77), 512, 33),              # tcgen05, ragged heights (row tiles padded per matrix)
+    ("q8_0", (256, 384), 512, 200),            # tcgen05, Q8_0
+    ("q4_0", (128, 640, 64), 256, 129),        # tcgen05, Q4_0
+    ("q6_K", (128, 64), 256, 1),               # not fusable: runs one by one
+    ("q4_K", (128, 64), 256, 4),               # not fusable (n in 2..8): runs one by one
+    ("q4_K", (64, 64, 64, 64), 256, 1),        # more than three matrices: runs one by one
+])
+def test_mul_mat_multi_equals_separate_calls(pkg, gpu_ctx, name, ms, k, n):
+    """b200_mul_mat_multi: several matrices x the same activations == the same b200_mul_mat calls, bit for bit"""
+    import torch
+    rng = np.random.default_rng(11)
+    t = TYPES[name]
+    Ws = [dev(random_blocks(t, m, k, rng)) for m in ms]
+    x = dev(rng.standard_normal((n, k)).astype(np.float32))
+    want = [pkg.mul_mat(gpu_ctx, t, W, x) for W in Ws]
+    outs = [torch.full((n, m), float("nan"), dtype=torch.float32, device="cuda") for m in ms]
+    pkg.mul_mat_multi(gpu_ctx, t, Ws, x, outs)
+    gpu_ctx.synchronize()
+    for w, o in zip(want, outs):
+        assert torch.equal(w, o)
+
+
+def test_mul_mat_multi_chain_orders_dependent_launches(pkg, gpu_ctx):
+    """fused launches in a dependency chain (x -> [a, b] -> a feeds the next pair ...) give the same as single calls"""
+    import torch
+    rng = np.random.default_rng(12)
+    k = 512
+    Ws = [dev(random_blocks(TYPES["q4_K"], k, k, rng)) for _ in range(6)]
+    x0 = dev(rng.standard_normal((1, k)).astype(np.float32))
+
+    def run(fused):
+        x, outs = x0, []
+        for i in range(0, 6, 2):
+            if fused:
+                a, b = pkg.mul_mat_multi(gpu_ctx, TYPES["q4_K"], Ws[i:i + 2], x)
+            else:
+                a, b = pkg.mul_mat(gpu_ctx, TYPES["q4_K"], Ws[i], x), pkg.mul_mat(gpu_ctx, TYPES["q4_K"], Ws[i + 1], x)
+            outs += [a, b]
+            x = a * 0.05
+        gpu_ctx.synchronize()
+        return outs
+
+    for w, o in zip(run(False), run(True)):
+        assert torch.isfinite(w).all() and torch.equal(w, o)
