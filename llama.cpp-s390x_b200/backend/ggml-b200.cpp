@@ -45,6 +45,7 @@ struct b200_backend_ctx {
     int         device;
     std::string name;
     b200_ctx *  ctx;
+    long        n_graphs = 0, n_mul_mat = 0, n_mul_mat_id = 0, n_fused_groups = 0;      // GGML_B200_STATS=1 prints them on free
 };
 
 struct b200_buffer_ctx {
@@ -184,6 +185,10 @@ const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ct
 
 void backend_free(ggml_backend_t backend) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
+    if (const char * e = getenv("GGML_B200_STATS"); e && *e == '1') {
+        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld\n", bctx->n_graphs, bctx->n_mul_mat,
+                bctx->n_mul_mat_id, bctx->n_fused_groups);
+    }
     b200_ctx_destroy(bctx->ctx);
     delete bctx;
     delete backend;
@@ -207,6 +212,7 @@ bool is_view_op(ggml_op op) {
 
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
+    bctx->n_graphs++;
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
         if (ggml_is_empty(node) || is_view_op(node->op)) continue;
@@ -214,12 +220,38 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
         int rc;
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
-                const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), d = to_b200(node);
-                rc = b200_mul_mat(bctx->ctx, &a, &b, &d);
+                // the MUL_MAT nodes that follow and read the same activations (wq / wk / wv, ffn_gate / ffn_up in a llama graph)
+                // run in the same launch (b200_mul_mat_multi); they are independent: their weights are not results of the group
+                ggml_tensor * group[3] = {node, nullptr, nullptr};
+                int n_group = 1, last = i;
+                for (int j = i + 1; j < cgraph->n_nodes && n_group < 3; ++j) {
+                    ggml_tensor * nx = cgraph->nodes[j];
+                    if (ggml_is_empty(nx) || is_view_op(nx->op)) continue;
+                    if (nx->op != GGML_OP_MUL_MAT || nx->src[1] != node->src[1] || (nx->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) break;
+                    bool independent = true;
+                    for (int g = 0; g < n_group; ++g) independent = independent && nx->src[0] != group[g] && nx->src[0]->view_src != group[g];
+                    if (!independent) break;
+                    group[n_group++] = nx;
+                    last = j;
+                }
+                bctx->n_mul_mat += n_group;
+                bctx->n_fused_groups += n_group > 1;
+                if (n_group == 1) {
+                    const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), d = to_b200(node);
+                    rc = b200_mul_mat(bctx->ctx, &a, &b, &d);
+                } else {
+                    b200_tensor a[3], d[3];
+                    const b200_tensor * ap[3], * dp[3];
+                    for (int g = 0; g < n_group; ++g) { a[g] = to_b200(group[g]->src[0]); d[g] = to_b200(group[g]); ap[g] = &a[g]; dp[g] = &d[g]; }
+                    const b200_tensor b = to_b200(node->src[1]);
+                    rc = b200_mul_mat_multi(bctx->ctx, n_group, ap, &b, dp);
+                    i = last;       // view nodes in between need no work
+                }
             } break;
             case GGML_OP_MUL_MAT_ID: {
                 const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), ids = to_b200(node->src[2]), d = to_b200(node);
                 rc = b200_mul_mat_id(bctx->ctx, &a, &b, &ids, &d);
+                bctx->n_mul_mat_id++;
             } break;
             default:
                 GGML_ABORT("ggml-b200: op %s reached graph_compute but supports_op() rejects it", ggml_op_name(node->op));

@@ -44,3 +44,23 @@ def test_backend_ops(op):
 def test_backend_ops_support_listing():
     rc, out = run_harness("support", "-b", "B2000", "-o", "MUL_MAT")
     assert rc == 0 and "B2000" in out
+
+
+GRAPH_CHECK = refenv.REF_DIR / "graph_check"
+
+
+@pytest.mark.parametrize("wtype,n_tokens", [("q4_K", 1), ("q4_K", 5), ("q4_K", 64), ("q8_0", 1), ("q8_0", 48), ("q4_0", 1), ("q4_0", 33), ("q6_K", 1), ("q6_K", 20)])
+def test_layer_graph_through_sched(wtype, n_tokens):
+    """oracle/graph_check.cpp: transformer-layer-shaped graphs scheduled by the reference's ggml_backend_sched over
+    {plug-in, CPU} (all MUL_MATs on the plug-in, everything else on the CPU) == the CPU backend alone; wq/wk/wv and
+    gate/up must have gone through the fused b200_mul_mat_multi path of graph_compute"""
+    if not GRAPH_CHECK.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/graph_check or libggml-b200.so not built (needs /root/reference at build time)")
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN), "GGML_B200_STATS": "1"})
+    p = subprocess.run([str(GRAPH_CHECK), wtype, str(n_tokens), "3"], env=env, capture_output=True, text=True, timeout=300)
+    out = p.stdout + p.stderr
+    assert p.returncode == 0 and "OK" in p.stdout.splitlines()[-1], out[-2000:]
+    m = re.search(r"stats: graphs=(\d+) mul_mat=(\d+) mul_mat_id=(\d+) fused_groups=(\d+)", out)
+    assert m, out[-2000:]
+    # 3 layers x 7 matmuls x 2 passes; two fused groups per layer and pass
+    assert int(m.group(2)) == 3 * 7 * 2 and int(m.group(4)) == 3 * 2 * 2, m.group(0)
