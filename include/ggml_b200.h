@@ -179,6 +179,23 @@ B200_API int  b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b
  * the protocol off.  (ggml-cuda orders the same dependency with cross-device events, ggml-cuda.cu:2098-2119.) */
 B200_API int  b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags);
 
+/* The low-latency ("LL") form of the same exchange for decode (n = 1, Q4_K): the all-gather AND its completion travel in the
+ * data.  Every result is sent as one indivisible 8-byte store {f32 bits, epoch} into an exchange slot on every rank (own
+ * rank included); the receiver — a second small kernel launched by the same call — polls its local slot until every entry
+ * carries the epoch and writes plain full-height f32 vectors.  No fence, no flag, no barrier kernel, no NCCL call: the
+ * cost per matmul is one NVLink store latency.  (The reference's row split instead issues per-device peer copies and
+ * cross-device events per matmul, ggml/src/ggml-cuda/ggml-cuda.cu:2030-2119.)
+ *
+ * b200_gather_ll_init: bufs[p] = rank p's exchange buffer, peer-mapped (CUDA IPC / symmetric memory), zero-initialised,
+ *   2 * slot_entries * 8 bytes (two slots used alternately).  world = 0 turns it off.
+ * b200_mul_mat_gather_ll: n_mats (1..3) row shards a[j] = rows [row0[j], row0[j] + a[j]->ne[1]) of matrices that share the
+ *   activations b (one f32 column); d_full[j] = this rank's full-height f32 result vector of matrix j, complete (all ranks'
+ *   rows) when the call's work is done on the stream.  All ranks issue the same sequence of calls; the sum of the full
+ *   heights of one call must fit a slot.  d_full must not overlap b. */
+B200_API int  b200_gather_ll_init(b200_ctx * ctx, int rank, int world, void * const * bufs, int64_t slot_entries);
+B200_API int  b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const * a_shard, const b200_tensor * b,
+                                     const b200_tensor * const * d_full, const int64_t * row0);
+
 /* ---- raw device memory (used by the backend shell's buffers and by ctypes callers without torch) -- */
 B200_API int  b200_malloc(int device, size_t nbytes, void ** out);
 B200_API int  b200_free(int device, void * ptr);

@@ -17,6 +17,7 @@ int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_strid
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
+int    b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * slot, uint32_t epoch, int n_mats, const int64_t * m_full, float * const * Y);
 int    b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d);
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
@@ -594,6 +595,82 @@ int b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor * const * a
         if (rc) return rc;
     }
     return B200_OK;
+}
+
+// ---- row split, LL exchange ------------------------------------------------------------------------------------------
+int b200_gather_ll_init(b200_ctx * ctx, int rank, int world, void * const * bufs, int64_t slot_entries) {
+    if (!ctx || world < 0 || world > B200_MAX_PEERS || (world > 0 && (!bufs || rank < 0 || rank >= world || slot_entries < 1))) {
+        b200_set_error("gather_ll_init: bad argument"); return B200_E_ARG;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->ll_world = world; ctx->ll_rank = rank; ctx->ll_cap = slot_entries; ctx->ll_epoch = 0;
+    for (int p = 0; p < world; ++p) {
+        if (((uintptr_t) bufs[p]) & 7) { b200_set_error("gather_ll_init: buffers must be 8-byte aligned"); ctx->ll_world = 0; return B200_E_ARG; }
+        ctx->ll_bufs[p] = (uint2 *) bufs[p];
+    }
+    return B200_OK;
+}
+
+int b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d_full,
+                           const int64_t * row0) {
+    if (!ctx || n_mats < 1 || n_mats > 3 || !a || !b || !d_full || !row0) { b200_set_error("mul_mat_gather_ll: bad argument"); return B200_E_ARG; }
+    if (ctx->ll_world < 1) { b200_set_error("mul_mat_gather_ll: b200_gather_ll_init was not called"); return B200_E_ARG; }
+    const int64_t k = a[0]->ne[0];
+    if (b->type != B200_TYPE_F32 || b->ne[0] != k || b->ne[1] != 1 || b->ne[2] * b->ne[3] != 1 || b->nb[0] != 4 || !b->data) {
+        b200_set_error("mul_mat_gather_ll: activations must be one contiguous f32 column of k values"); return B200_E_UNSUPPORTED;
+    }
+    int64_t total_full = 0, shard_rows = 0;
+    const char * xlo, * xhi;
+    tensor_extent(b, &xlo, &xhi);
+    for (int j = 0; j < n_mats; ++j) {
+        const b200_tensor * A = a[j], * D = d_full[j];
+        if (!A || !D || !A->data || !D->data) { b200_set_error("mul_mat_gather_ll[%d]: null tensor", j); return B200_E_ARG; }
+        if (A->type != B200_TYPE_Q4_K || A->ne[0] != k || k % 256 != 0 || A->ne[2] * A->ne[3] != 1 || A->nb[1] != a[0]->nb[1] || A->ne[1] < 1 ||
+            !aligned16(A->data, A->nb[1], 0, 0)) {
+            b200_set_error("mul_mat_gather_ll[%d]: Q4_K shards of equal row length, 16-byte aligned, no batch dims", j); return B200_E_UNSUPPORTED;
+        }
+        if (D->type != B200_TYPE_F32 || D->nb[0] != 4 || D->ne[1] * D->ne[2] * D->ne[3] != 1 || row0[j] < 0 || row0[j] + A->ne[1] > D->ne[0]) {
+            b200_set_error("mul_mat_gather_ll[%d]: d_full must be one contiguous f32 column that holds rows [row0, row0 + shard rows)", j); return B200_E_ARG;
+        }
+        const char * lo, * hi;
+        tensor_extent(D, &lo, &hi);
+        if (lo < xhi && xlo < hi) { b200_set_error("mul_mat_gather_ll[%d]: d_full overlaps the activations", j); return B200_E_ARG; }
+        total_full += D->ne[0]; shard_rows += A->ne[1];
+    }
+    if (total_full > ctx->ll_cap) { b200_set_error("mul_mat_gather_ll: %lld results exceed the exchange slot (%lld)", (long long) total_full, (long long) ctx->ll_cap); return B200_E_ARG; }
+    if (!ctx->fuse_quant || !aligned16(b->data, 0, 0, 0) || b200_gemv_q4k_smem(1, k) > ctx->smem_optin) {
+        b200_set_error("mul_mat_gather_ll: needs the fused Q4_K GEMV (k = %lld)", (long long) k); return B200_E_UNSUPPORTED;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const uint32_t epoch = ++ctx->ll_epoch;
+    const int64_t  slot  = (int64_t) (epoch & 1) * ctx->ll_cap;
+
+    mm_problem P = {};
+    P.W = (const uint8_t *) a[0]->data; P.nb01 = a[0]->nb[1]; P.k = k;
+    P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = b->nb[3];
+    P.ne11 = 1; P.ne12 = 1; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+    P.Y = (float *) d_full[0]->data; P.mode = MM_PLAIN;
+    P.n_mats = n_mats; P.m = shard_rows;
+    P.m_end[0] = P.m_end[1] = INT64_MAX;
+    // rows are numbered through the shards; entry of (matrix j, full row r) in the exchange slot = (sum of full heights before j) + r
+    int64_t start = 0, full_before = 0, m_full[3] = {0, 0, 0};
+    float * Y[3] = {nullptr, nullptr, nullptr};
+    for (int j = 0; j < n_mats; ++j) {
+        if (j > 0) { P.Wv[j - 1] = (const uint8_t *) a[j]->data - start * P.nb01; P.m_end[j - 1] = start; }
+        P.ll_off[j] = full_before + row0[j] - start;
+        start += a[j]->ne[1]; full_before += d_full[j]->ne[0];
+        m_full[j] = d_full[j]->ne[0]; Y[j] = (float *) d_full[j]->data;
+    }
+    // (boundaries of absent matrices stay at INT64_MAX, so their Wv / ll_off entries are never selected)
+    P.ll_world = ctx->ll_world; P.ll_epoch = epoch;
+    for (int p = 0; p < ctx->ll_world; ++p) P.ll_dst[p] = ctx->ll_bufs[p] + slot;
+    // the GEMV waits for everything before it at its start (no deferred wait): the receiver below may become resident while the
+    // GEMV runs and writes d_full as soon as the values arrive, which must not overtake older readers of d_full
+    for (int j = 0; j < n_mats; ++j) pending_push(ctx, d_full[j], j == 0);
+    int rc = b200_launch_gemv_q4k(ctx, P, 1, 1, false);
+    if (rc) return rc;
+    return b200_launch_ll_unpack(ctx, ctx->ll_bufs[ctx->ll_rank] + slot, epoch, n_mats, m_full, Y);
 }
 
 int b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags) {

@@ -87,6 +87,11 @@ struct b200_ctx {
     int          gs_rank, gs_world;
     uint32_t *   gs_flags[8];
     uint32_t *   gs_state;
+    // LL exchange (b200_gather_ll_init): every rank's exchange buffer (2 slots of ll_cap entries), epoch of the last launch
+    int          ll_rank, ll_world;
+    uint2 *      ll_bufs[8];
+    int64_t      ll_cap;
+    uint32_t     ll_epoch;
     int          tc_nt;           // tcgen05 GEMM tile width override (0 = auto, 128, 256)
     int          gemv_cfg;        // CTA shape of the n=1 Q4_K GEMV: 0 = 32 warps x 1 CTA/SM, 1 = 16x2, 2 = 8x4, 3 = 16x1
     // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)

@@ -50,6 +50,14 @@ struct mm_problem {
     int64_t         m_end[2];
     const uint8_t * Wv[2];
     float *         Yv[2];
+    // row split with the "LL" exchange (one process per GPU, n = 1): instead of plain stores + a completion protocol, every
+    // result travels as ONE 8-byte store {value bits, epoch} into slot (ll_off[matrix] + row) of every rank's exchange buffer
+    // (ll_dst[p], peer-mapped, own rank included).  An 8-byte store is indivisible, so the arrival of the epoch IS the
+    // arrival of the value: no fences, no flags, no barrier — the receiver polls the slot (ll_unpack_kernel).
+    int        ll_world;
+    uint2 *    ll_dst[8];
+    int64_t    ll_off[3];
+    uint32_t   ll_epoch;
 };
 
 

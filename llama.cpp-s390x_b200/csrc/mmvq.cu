@@ -245,11 +245,12 @@ __device__ __forceinline__ void q4k_task(const q4k_frag & f, const int sb, const
     }
 }
 
-// VARIANT: 0 = plain, 1 = cross-rank completion protocol (row split, one process per GPU), 2 = several matrices per launch
+// VARIANT: 0 = plain, 1 = cross-rank completion protocol (row split, one process per GPU), 2 = several matrices per launch,
+//          3 = several matrices per launch + LL exchange of the results with all ranks (row split, one process per GPU)
 template <int NC, int NWARPS, int MINB, int NBUF, int VARIANT>
 __global__ void __launch_bounds__(NWARPS * 32, MINB)
 gemv_q4k(const mm_problem P, const int flags) {
-    constexpr bool SYNC = VARIANT == 1, MULTI = VARIANT == 2;
+    constexpr bool SYNC = VARIANT == 1, LL = VARIANT == 3, MULTI = VARIANT == 2 || LL;
     // flags: < 0 launch-floor probe (ctx option "noop"); bit 0 = PDL launch (prefetch weights before the dependency wait);
     //        bit 1 = X / ids are NOT written by any kernel still in flight (abi.cu tracks that): the wait moves from
     //        "before reading X" to "before the first store", so this kernel's prologue and streaming overlap the previous
@@ -374,7 +375,15 @@ gemv_q4k(const mm_problem P, const int flags) {
 #pragma unroll
             for (int col = 0; col < NC; ++col) {
                 const float s = warp_sum(acc[col]);
-                if (MULTI) {
+                if (LL) {
+                    if (lane == 0) {
+                        const int64_t slot = row + (row < P.m_end[0] ? P.ll_off[0] : (row < P.m_end[1] ? P.ll_off[1] : P.ll_off[2]));
+#pragma unroll 1
+                        for (int p = 0; p < P.ll_world; ++p) {
+                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" :: "l"(P.ll_dst[p] + slot), "r"(__float_as_uint(s)), "r"(P.ll_epoch) : "memory");
+                        }
+                    }
+                } else if (MULTI) {
                     if (lane == 0) (row < P.m_end[0] ? C.y[0] : (row < P.m_end[1] ? P.Yv[0] : P.Yv[1]))[row] = s;
                 } else if (lane == 0 && col < C.nc) {
                     mm_store(P, C.y[col], row, s);
@@ -427,11 +436,40 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
     return B200_OK;
 }
 
+// receiver side of the LL exchange: wait until every entry of the slot carries `epoch`, then store the values as plain f32
+// vectors (one per matrix of the fused launch).  A rank that never delivers must not hang the others: trap after ~3 s.
+struct ll_unpack_args {
+    const uint2 * slot;
+    uint32_t      epoch;
+    int64_t       total, end[2];      // entries; matrix boundaries
+    float *       Yv[3];              // virtual bases: entry i of matrix j is stored to Yv[j][i]
+};
+
+__global__ void __launch_bounds__(256)
+ll_unpack_kernel(const ll_unpack_args a) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.total) return;
+    uint32_t v, e;
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(a.slot + i) : "memory");
+    if (e != a.epoch) {
+        const long long t0 = clock64();
+        do {
+            __nanosleep(64);
+            asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(a.slot + i) : "memory");
+            if (clock64() - t0 > 6000000000LL) __trap();
+        } while (e != a.epoch);
+    }
+    (i < a.end[0] ? a.Yv[0] : (i < a.end[1] ? a.Yv[1] : a.Yv[2]))[i] = __uint_as_float(v);
+}
+
 template <int NC, int NWARPS, int MINB, int NBUF, int VARIANT = 0>
 int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t smem, bool late_wait) {
-    if (VARIANT == 0 && (P.sync_flags || P.n_mats > 1)) {
+    if (VARIANT == 0 && (P.sync_flags || P.n_mats > 1 || P.ll_world > 0)) {
         // the cross-rank completion protocol and the several-matrices form live in their own instantiations so that the plain
         // kernel pays nothing for them
+        if (NC == 1 && NWARPS == 32 && MINB == 1 && NBUF == 0 && P.ll_world > 0 && !P.sync_flags) {
+            return launch_q4k_t<1, 32, 1, 0, 3>(ctx, P, tiles, smem, late_wait);
+        }
         if (NC == 1 && NWARPS == 32 && MINB == 1 && NBUF == 0 && !(P.sync_flags && P.n_mats > 1)) {
             return P.sync_flags ? launch_q4k_t<1, 32, 1, 0, 1>(ctx, P, tiles, smem, late_wait) : launch_q4k_t<1, 32, 1, 0, 2>(ctx, P, tiles, smem, late_wait);
         }
@@ -483,6 +521,32 @@ int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int
     }
     b200_set_error("gemv: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
+}
+
+// LL exchange, receiver side: entries [0, total) of `slot` -> n_mats plain vectors of m_full[j] floats
+int b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * slot, uint32_t epoch, int n_mats, const int64_t * m_full, float * const * Y) {
+    ll_unpack_args a = {};
+    a.slot = slot; a.epoch = epoch;
+    int64_t start = 0;
+    for (int j = 0; j < 3; ++j) {
+        const int jj = j < n_mats ? j : n_mats - 1;
+        if (j < n_mats) { a.Yv[j] = Y[j] - start; start += m_full[j]; } else a.Yv[j] = a.Yv[jj];
+        if (j < 2) a.end[j] = j < n_mats ? start : INT64_MAX;
+    }
+    a.total = start;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim  = dim3((unsigned) ((a.total + 255) / 256));
+    cfg.blockDim = dim3(256);
+    cfg.stream   = ctx->stream;
+    // programmatic launch: the receiver may become resident while the GEMV that feeds it is still running (it only polls)
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, ll_unpack_kernel, a));
+    ctx->launches++;
+    return B200_OK;
 }
 
 // shared memory the fused Q4_K kernel needs for nc columns of k values

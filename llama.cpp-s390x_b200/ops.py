@@ -138,6 +138,28 @@ def mul_mat_gather(ctx: Context, wtype: int, w_shard, x, out_shard, dst_ptrs, ds
     return out_shard
 
 
+def gather_ll_init(ctx: Context, rank: int, world: int, buf_ptrs, slot_entries: int):
+    """LL exchange: buf_ptrs[p] = rank p's zeroed, peer-mapped buffer of 2 * slot_entries * 8 bytes"""
+    arr = (C.c_void_p * max(1, len(buf_ptrs)))(*buf_ptrs)
+    check(lib().b200_gather_ll_init(ctx.handle, rank, world, arr, slot_entries), "b200_gather_ll_init")
+
+
+def mul_mat_gather_ll(ctx: Context, wtype: int, w_shards, x, outs_full, row0s):
+    """row split, decode: outs_full[j] (full height, local) = all ranks' rows of matrix j x x; w_shards[j] = this rank's rows
+    [row0s[j], row0s[j] + rows) — one GEMV launch + one receiver launch, no barrier"""
+    k = x.shape[-1]
+    a = [_desc(w, wtype, k_elems=k) for w in w_shards]
+    d = [_desc(o, F32) for o in outs_full]
+    b = _desc(x, F32)
+    T = C.POINTER(Tensor)
+    n = len(w_shards)
+    ap = (T * n)(*[C.pointer(t) for t in a])
+    dp = (T * n)(*[C.pointer(t) for t in d])
+    r0 = (C.c_int64 * n)(*row0s)
+    check(lib().b200_mul_mat_gather_ll(ctx.handle, n, ap, C.byref(b), dp, r0), "b200_mul_mat_gather_ll")
+    return outs_full
+
+
 def row_shard(m: int, rank: int, world: int, rounding: int = 128):
     """(row0, rows) of rank's shard of an m-row weight matrix: even cut points rounded DOWN to `rounding` rows, the last
     rank takes the remainder — the rule of get_row_split (ggml/src/ggml-cuda/ggml-cuda.cu:855-881) and b200_rowsplit_rows"""

@@ -356,3 +356,29 @@ def test_mul_mat_multi_chain_orders_dependent_launches(pkg, gpu_ctx):
 
     for w, o in zip(run(False), run(True)):
         assert torch.isfinite(w).all() and torch.equal(w, o)
+
+
+def test_gather_ll_world1_equals_mul_mat(pkg):
+    """the LL exchange with a world of one rank (the GEMV sends {value, epoch} to its own slot, the receiver unpacks): equal to
+    b200_mul_mat, over several launches (the two slots alternate) and 1..3 matrices per launch"""
+    import torch
+    rng = np.random.default_rng(21)
+    ctx = pkg.Context(0, stream="torch")
+    k, cap = 1024, 4096
+    buf = torch.zeros((2 * cap, 2), dtype=torch.int32, device="cuda")
+    pkg.gather_ll_init(ctx, 0, 1, [buf.data_ptr()], cap)
+    x = dev(rng.standard_normal((1, k)).astype(np.float32))
+    for ms in [(512,), (512, 128, 128), (1792, 1792), (300, 77), (4096,), (640, 64, 1)]:
+        Ws = [dev(random_blocks(TYPES["q4_K"], m, k, rng)) for m in ms]
+        want = [pkg.mul_mat(ctx, TYPES["q4_K"], W, x) for W in Ws]
+        outs = [torch.full((1, m), float("nan"), dtype=torch.float32, device="cuda") for m in ms]
+        pkg.mul_mat_gather_ll(ctx, TYPES["q4_K"], Ws, x, outs, [0] * len(ms))
+        ctx.synchronize()
+        for w, o in zip(want, outs):
+            assert torch.equal(w, o)
+        x = (outs[0][:, :1] * 0 + x)              # next round's activations depend on this round's result
+    # too many results for a slot, overlapping output: refused
+    with pytest.raises(pkg.B200Error):
+        pkg.mul_mat_gather_ll(ctx, TYPES["q4_K"], [dev(random_blocks(TYPES["q4_K"], cap + 256, k, rng))], x,
+                              [torch.empty((1, cap + 256), device="cuda")], [0])
+    ctx.close()

@@ -73,3 +73,57 @@ def test_rowsplit_cut_points(pkg, rs):
         assert lo.value == prev and (hi.value % 128 == 0 or i == n_dev - 1)
         prev = hi.value
     assert prev == 128256
+
+
+def test_gather_ll_two_ranks_in_one_process(pkg):
+    """b200_mul_mat_gather_ll between two GPUs (two contexts of one process, peer-mapped exchange buffers): each rank's
+    full-height results == the unsplit single-GPU results, bit for bit, over several dependent launches"""
+    import torch
+    if _n_gpus() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    if not (torch.cuda.can_device_access_peer(0, 1) and torch.cuda.can_device_access_peer(1, 0)):
+        pytest.skip("no peer access between GPU 0 and 1")
+    q4k = TYPES["q4_K"]
+    rng = np.random.default_rng(5)
+    k, cap, world = 2048, 8192, 2
+    # make torch enable peer access in both directions (cudaMalloc'ed blocks become peer-mapped)
+    torch.zeros(8, device="cuda:0").to("cuda:1"); torch.zeros(8, device="cuda:1").to("cuda:0")
+    bufs = [torch.zeros((2 * cap, 2), dtype=torch.int32, device=f"cuda:{r}") for r in range(world)]
+    ctxs = []
+    for r in range(world):
+        with torch.cuda.device(r):
+            ctxs.append(pkg.Context(r, stream="torch"))
+    for r in range(world):
+        torch.cuda.synchronize(r)
+        pkg.gather_ll_init(ctxs[r], r, world, [b.data_ptr() for b in bufs], cap)
+    x_np = rng.standard_normal((1, k)).astype(np.float32)
+    xs = [torch.from_numpy(x_np).to(f"cuda:{r}") for r in range(world)]
+    for ms in [(2048,), (2048, 512, 512), (3584, 3584), (2048,), (256, 128)]:
+        W_np = [random_blocks(q4k, m, k, rng) for m in ms]
+        with torch.cuda.device(0):
+            want = [pkg.mul_mat(ctxs[0], q4k, torch.from_numpy(W).to("cuda:0"), xs[0]) for W in W_np]
+        # all allocations and uploads first: nothing but the launches may happen while a receiver is polling for its peer
+        prep = []
+        for r in range(world):
+            shards, row0s = [], []
+            for W, m in zip(W_np, ms):
+                lo, rows = pkg.row_shard(m, r, world)
+                shards.append(torch.from_numpy(W[lo:lo + rows]).to(f"cuda:{r}")); row0s.append(lo)
+            o = [torch.full((1, m), float("nan"), dtype=torch.float32, device=f"cuda:{r}") for m in ms]
+            prep.append((shards, row0s, o))
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        outs = []
+        for r in range(world):
+            shards, row0s, o = prep[r]
+            pkg.mul_mat_gather_ll(ctxs[r], q4k, shards, xs[r], o, row0s)           # asynchronous: rank 0's receiver waits for rank 1's GEMV
+            outs.append((o, shards))
+        for r in range(world):
+            ctxs[r].synchronize()
+        for r in range(world):
+            for w, o in zip(want, outs[r][0]):
+                assert torch.equal(w.cpu(), o.cpu())
+        # dependent activations for the next round: x += tiny * first result (same on both ranks)
+        xs = [x + 1e-3 * outs[r][0][0][:, :k] if ms[0] >= k else x for r, x in enumerate(xs)]
+    for c in ctxs:
+        c.close()
