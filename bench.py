@@ -227,6 +227,21 @@ def run_gpu(args):
         ctx.synchronize(); hdl.barrier(channel=0); torch.cuda.synchronize()
         assert torch.equal(ybuf[:4096].view(1, -1), full), "fused row-split all-gather differs from the unsplit result"
     use_flags = world > 1 and args.gather_sync == "flags"
+    use_ll = world > 1 and args.gather_sync == "ll"
+    if use_ll:
+        # LL exchange (b200_gather_ll_init): {value, epoch} in one 8-byte store per result, receiver kernel polls its local slot
+        cap = maxm
+        llbuf = symm_mem.empty(2 * cap * 2, dtype=torch.int32, device=torch.device("cuda", local))
+        llbuf.zero_()
+        lhdl = symm_mem.rendezvous(llbuf, dist.group.WORLD)
+        torch.cuda.synchronize(); lhdl.barrier(channel=0); torch.cuda.synchronize()
+        pkg.gather_ll_init(ctx, rank, world, [int(p) for p in lhdl.buffer_ptrs], cap)
+        # correctness: gathered result == unsplit result, bit for bit, twice (both slots)
+        for _ in range(2):
+            yc = torch.full((1, 4096), float("nan"), device="cuda")
+            pkg.mul_mat_gather_ll(ctx, Q4_K, [Wc[rank * r:(rank + 1) * r].contiguous()], xc, [yc], [rank * r])
+            ctx.synchronize()
+            assert torch.equal(yc, full), "LL row-split exchange differs from the unsplit result"
     if use_flags:
         # completion flags (b200_gather_sync_init): one uint32 per source rank, in symmetric memory
         fbuf = symm_mem.empty(64, dtype=torch.int32, device=torch.device("cuda", local))
@@ -249,6 +264,8 @@ def run_gpu(args):
             if world == 1:
                 y = torch.empty((1, m), device="cuda")
                 ys = y
+            elif use_ll:
+                y, ys = torch.empty((1, m), device="cuda"), None      # full-height local result
             else:
                 y, ys = None, torch.empty((1, rows), device="cuda")
             ops.append((W, xs[k], y, ys, (m, name)))
@@ -258,7 +275,7 @@ def run_gpu(args):
 
     # 1 GPU: the matrices that share their activations (wq / wk / wv, ffn_gate / ffn_up) go through b200_mul_mat_multi, one launch
     # per group — the same 225 matmuls in 129 launches (--no-fuse: one b200_mul_mat each)
-    fuse = world == 1 and not args.no_fuse
+    fuse = (world == 1 or use_ll) and not args.no_fuse
     groups, i = [], 0
     while i < len(order):
         g = [order[i]]
@@ -272,6 +289,10 @@ def run_gpu(args):
     n_groups = len(groups)
 
     def step():
+        if use_ll:
+            for g in groups:
+                pkg.mul_mat_gather_ll(ctx, Q4_K, [o[0] for o in g], g[0][1], [o[2] for o in g], [rank * (o[4][0] // world) for o in g])
+            return
         if fuse:
             for g in groups:
                 if len(g) == 1:
@@ -400,7 +421,8 @@ def run_gpu(args):
                        "launch": ("CUDA graph replay" if graph is not None else "eager launches through the C ABI") +
                                  (f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
-                                                                          "memory; completion per matmul: " + ("in-kernel epoch flags after every matmul" if use_flags else "symmetric-memory barrier after wv / wo / ffn_up / ffn_down / output (129 per step)")},
+                                                                          "memory; completion: " + ("LL exchange: {value, epoch} in one 8-byte store per result, a receiver kernel polls the local slot; no barrier, no NCCL call"
+                                                                          if use_ll else "in-kernel epoch flags after every matmul" if use_flags else "symmetric-memory barrier after wv / wo / ffn_up / ffn_down / output (129 per step)")},
             "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
             "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clocks,
@@ -532,7 +554,7 @@ def main():
     ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
-    ap.add_argument("--gather-sync", default="barrier", choices=["barrier", "flags"], help="N > 1: how a matmul's gather is completed")
+    ap.add_argument("--gather-sync", default="ll", choices=["ll", "barrier", "flags"], help="N > 1: how a matmul's gather is completed")
     ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
     args = ap.parse_args()

@@ -17,7 +17,7 @@ int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_strid
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
-int    b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * slot, uint32_t epoch, int n_mats, const int64_t * m_full, float * const * Y);
+int    b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * buf, int64_t cap, uint32_t * state, int n_mats, const int64_t * m_full, float * const * Y);
 int    b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d);
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
@@ -129,6 +129,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->gs_state) cudaFree(ctx->gs_state);
+    if (ctx->ll_state) cudaFree(ctx->ll_state);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
@@ -604,7 +605,11 @@ int b200_gather_ll_init(b200_ctx * ctx, int rank, int world, void * const * bufs
     }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
-    ctx->ll_world = world; ctx->ll_rank = rank; ctx->ll_cap = slot_entries; ctx->ll_epoch = 0;
+    ctx->ll_world = world; ctx->ll_rank = rank; ctx->ll_cap = slot_entries;
+    if (world > 0) {
+        if (!ctx->ll_state) B200_CUDA_TRY(cudaMalloc((void **) &ctx->ll_state, 2 * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMemset(ctx->ll_state, 0, 2 * sizeof(uint32_t)));
+    }
     for (int p = 0; p < world; ++p) {
         if (((uintptr_t) bufs[p]) & 7) { b200_set_error("gather_ll_init: buffers must be 8-byte aligned"); ctx->ll_world = 0; return B200_E_ARG; }
         ctx->ll_bufs[p] = (uint2 *) bufs[p];
@@ -625,8 +630,9 @@ int b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const
     tensor_extent(b, &xlo, &xhi);
     for (int j = 0; j < n_mats; ++j) {
         const b200_tensor * A = a[j], * D = d_full[j];
-        if (!A || !D || !A->data || !D->data) { b200_set_error("mul_mat_gather_ll[%d]: null tensor", j); return B200_E_ARG; }
-        if (A->type != B200_TYPE_Q4_K || A->ne[0] != k || k % 256 != 0 || A->ne[2] * A->ne[3] != 1 || A->nb[1] != a[0]->nb[1] || A->ne[1] < 1 ||
+        if (!A || !D || (!A->data && A->ne[1] > 0) || !D->data) { b200_set_error("mul_mat_gather_ll[%d]: null tensor", j); return B200_E_ARG; }
+        // (a rank may own no rows of a small matrix: ne[1] == 0)
+        if (A->type != B200_TYPE_Q4_K || A->ne[0] != k || k % 256 != 0 || A->ne[2] * A->ne[3] != 1 || A->nb[1] != a[0]->nb[1] || A->ne[1] < 0 ||
             !aligned16(A->data, A->nb[1], 0, 0)) {
             b200_set_error("mul_mat_gather_ll[%d]: Q4_K shards of equal row length, 16-byte aligned, no batch dims", j); return B200_E_UNSUPPORTED;
         }
@@ -643,9 +649,6 @@ int b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const
         b200_set_error("mul_mat_gather_ll: needs the fused Q4_K GEMV (k = %lld)", (long long) k); return B200_E_UNSUPPORTED;
     }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    const uint32_t epoch = ++ctx->ll_epoch;
-    const int64_t  slot  = (int64_t) (epoch & 1) * ctx->ll_cap;
-
     mm_problem P = {};
     P.W = (const uint8_t *) a[0]->data; P.nb01 = a[0]->nb[1]; P.k = k;
     P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->nb[2]; P.nb13 = b->nb[3];
@@ -663,14 +666,14 @@ int b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const
         m_full[j] = d_full[j]->ne[0]; Y[j] = (float *) d_full[j]->data;
     }
     // (boundaries of absent matrices stay at INT64_MAX, so their Wv / ll_off entries are never selected)
-    P.ll_world = ctx->ll_world; P.ll_epoch = epoch;
-    for (int p = 0; p < ctx->ll_world; ++p) P.ll_dst[p] = ctx->ll_bufs[p] + slot;
+    P.ll_world = ctx->ll_world; P.ll_cap = ctx->ll_cap; P.ll_state = ctx->ll_state;
+    for (int p = 0; p < ctx->ll_world; ++p) P.ll_dst[p] = ctx->ll_bufs[p];
     // the GEMV waits for everything before it at its start (no deferred wait): the receiver below may become resident while the
     // GEMV runs and writes d_full as soon as the values arrive, which must not overtake older readers of d_full
     for (int j = 0; j < n_mats; ++j) pending_push(ctx, d_full[j], j == 0);
     int rc = b200_launch_gemv_q4k(ctx, P, 1, 1, false);
     if (rc) return rc;
-    return b200_launch_ll_unpack(ctx, ctx->ll_bufs[ctx->ll_rank] + slot, epoch, n_mats, m_full, Y);
+    return b200_launch_ll_unpack(ctx, ctx->ll_bufs[ctx->ll_rank], ctx->ll_cap, ctx->ll_state, n_mats, m_full, Y);
 }
 
 int b200_gather_sync_init(b200_ctx * ctx, int rank, int world, uint32_t * const * flags) {

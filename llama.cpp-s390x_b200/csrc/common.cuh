@@ -91,7 +91,7 @@ struct b200_ctx {
     int          ll_rank, ll_world;
     uint2 *      ll_bufs[8];
     int64_t      ll_cap;
-    uint32_t     ll_epoch;
+    uint32_t *   ll_state;       // device: [0] epoch of the last completed exchange, [1] receiver CTAs done
     int          tc_nt;           // tcgen05 GEMM tile width override (0 = auto, 128, 256)
     int          gemv_cfg;        // CTA shape of the n=1 Q4_K GEMV: 0 = 32 warps x 1 CTA/SM, 1 = 16x2, 2 = 8x4, 3 = 16x1
     // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)

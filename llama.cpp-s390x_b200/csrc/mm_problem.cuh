@@ -54,10 +54,13 @@ struct mm_problem {
     // result travels as ONE 8-byte store {value bits, epoch} into slot (ll_off[matrix] + row) of every rank's exchange buffer
     // (ll_dst[p], peer-mapped, own rank included).  An 8-byte store is indivisible, so the arrival of the epoch IS the
     // arrival of the value: no fences, no flags, no barrier — the receiver polls the slot (ll_unpack_kernel).
-    int        ll_world;
-    uint2 *    ll_dst[8];
-    int64_t    ll_off[3];
-    uint32_t   ll_epoch;
+    // The epoch lives in device memory (ll_state[0] = epoch of the last completed exchange; the receiver advances it), so a
+    // CUDA graph that captured these launches uses fresh epochs on every replay.  Slot of epoch e: ll_dst[p] + (e & 1) * ll_cap.
+    int              ll_world;
+    uint2 *          ll_dst[8];
+    int64_t          ll_off[3];
+    int64_t          ll_cap;
+    const uint32_t * ll_state;
 };
 
 

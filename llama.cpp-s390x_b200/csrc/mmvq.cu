@@ -312,6 +312,8 @@ gemv_q4k(const mm_problem P, const int flags) {
         if (live) first_loads();
     }
     if (!live) return;                                          // block-uniform
+    uint32_t ll_e = 0;                                          // this launch's epoch: the last completed one + 1 (needed at the first store)
+    if (LL) { asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ll_e) : "l"(P.ll_state) : "memory"); ll_e += 1; }
     if (SYNC && P.sync_flags) {
         // fused row-split all-gather: the activations may derive from the previous matmul's gathered output, which is complete
         // once every rank has published that launch's epoch (our own previous launch is complete: griddepcontrol.wait)
@@ -377,10 +379,11 @@ gemv_q4k(const mm_problem P, const int flags) {
                 const float s = warp_sum(acc[col]);
                 if (LL) {
                     if (lane == 0) {
-                        const int64_t slot = row + (row < P.m_end[0] ? P.ll_off[0] : (row < P.m_end[1] ? P.ll_off[1] : P.ll_off[2]));
+                        const int64_t slot = row + (row < P.m_end[0] ? P.ll_off[0] : (row < P.m_end[1] ? P.ll_off[1] : P.ll_off[2])) +
+                                             (int64_t) (ll_e & 1) * P.ll_cap;
 #pragma unroll 1
                         for (int p = 0; p < P.ll_world; ++p) {
-                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" :: "l"(P.ll_dst[p] + slot), "r"(__float_as_uint(s)), "r"(P.ll_epoch) : "memory");
+                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" :: "l"(P.ll_dst[p] + slot), "r"(__float_as_uint(s)), "r"(ll_e) : "memory");
                         }
                     }
                 } else if (MULTI) {
@@ -439,27 +442,41 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
 // receiver side of the LL exchange: wait until every entry of the slot carries `epoch`, then store the values as plain f32
 // vectors (one per matrix of the fused launch).  A rank that never delivers must not hang the others: trap after ~3 s.
 struct ll_unpack_args {
-    const uint2 * slot;
-    uint32_t      epoch;
+    const uint2 * buf;                // both slots of this rank's exchange buffer
+    int64_t       cap;
+    uint32_t *    state;              // [0] epoch of the last completed exchange, [1] CTAs of this launch that are done
     int64_t       total, end[2];      // entries; matrix boundaries
     float *       Yv[3];              // virtual bases: entry i of matrix j is stored to Yv[j][i]
 };
 
 __global__ void __launch_bounds__(256)
 ll_unpack_kernel(const ll_unpack_args a) {
+    uint32_t epoch;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(epoch) : "l"(a.state) : "memory");
+    epoch += 1;
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.total) return;
-    uint32_t v, e;
-    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(a.slot + i) : "memory");
-    if (e != a.epoch) {
-        const long long t0 = clock64();
-        do {
-            __nanosleep(64);
-            asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(a.slot + i) : "memory");
-            if (clock64() - t0 > 6000000000LL) __trap();
-        } while (e != a.epoch);
+    if (i < a.total) {
+        const uint2 * src = a.buf + (int64_t) (epoch & 1) * a.cap + i;
+        uint32_t v, e;
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src) : "memory");
+        if (e != epoch) {
+            const long long t0 = clock64();
+            do {
+                __nanosleep(64);
+                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src) : "memory");
+                if (clock64() - t0 > 6000000000LL) __trap();
+            } while (e != epoch);
+        }
+        (i < a.end[0] ? a.Yv[0] : (i < a.end[1] ? a.Yv[1] : a.Yv[2]))[i] = __uint_as_float(v);
     }
-    (i < a.end[0] ? a.Yv[0] : (i < a.end[1] ? a.Yv[1] : a.Yv[2]))[i] = __uint_as_float(v);
+    // the last CTA to finish closes the exchange: every CTA has read the old epoch by then
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(a.state + 1, 1u) == gridDim.x - 1) {
+            a.state[1] = 0;
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(a.state), "r"(epoch) : "memory");
+        }
+    }
 }
 
 template <int NC, int NWARPS, int MINB, int NBUF, int VARIANT = 0>
@@ -524,9 +541,9 @@ int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int
 }
 
 // LL exchange, receiver side: entries [0, total) of `slot` -> n_mats plain vectors of m_full[j] floats
-int b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * slot, uint32_t epoch, int n_mats, const int64_t * m_full, float * const * Y) {
+int b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * buf, int64_t cap, uint32_t * state, int n_mats, const int64_t * m_full, float * const * Y) {
     ll_unpack_args a = {};
-    a.slot = slot; a.epoch = epoch;
+    a.buf = buf; a.cap = cap; a.state = state;
     int64_t start = 0;
     for (int j = 0; j < 3; ++j) {
         const int jj = j < n_mats ? j : n_mats - 1;
