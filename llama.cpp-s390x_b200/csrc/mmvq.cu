@@ -312,8 +312,18 @@ gemv_q4k(const mm_problem P, const int flags) {
         if (live) first_loads();
     }
     if (!live) return;                                          // block-uniform
-    uint32_t ll_e = 0;                                          // this launch's epoch: the last completed one + 1 (needed at the first store)
-    if (LL) { asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ll_e) : "l"(P.ll_state) : "memory"); ll_e += 1; }
+    // LL exchange: this launch's epoch = the last completed one (ll_state[0], advanced by the receiver kernel) + 1.  CTA 0
+    // hands it to this launch's receiver through ll_state[1] — performed (fence) before this CTA's launch_dependents below,
+    // and the receiver cannot become resident before every CTA of this grid has passed that point.
+    uint32_t ll_e = 0;
+    if (LL) {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(ll_e) : "l"(P.ll_state) : "memory");
+        asm volatile("add.u32 %0, %0, 1;" : "+r"(ll_e));       // consumes the load here: it has been performed before the trigger
+        if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(P.ll_state + 1), "r"(ll_e) : "memory");
+            __threadfence();
+        }
+    }
     if (SYNC && P.sync_flags) {
         // fused row-split all-gather: the activations may derive from the previous matmul's gathered output, which is complete
         // once every rank has published that launch's epoch (our own previous launch is complete: griddepcontrol.wait)
@@ -444,38 +454,37 @@ int launch_generic_t(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles
 struct ll_unpack_args {
     const uint2 * buf;                // both slots of this rank's exchange buffer
     int64_t       cap;
-    uint32_t *    state;              // [0] epoch of the last completed exchange, [1] CTAs of this launch that are done
+    uint32_t *    state;              // [0] epoch of the last completed exchange (written here), [1] epoch of the launch in flight (by its GEMV)
     int64_t       total, end[2];      // entries; matrix boundaries
     float *       Yv[3];              // virtual bases: entry i of matrix j is stored to Yv[j][i]
 };
 
 __global__ void __launch_bounds__(256)
 ll_unpack_kernel(const ll_unpack_args a) {
-    uint32_t epoch;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(epoch) : "l"(a.state) : "memory");
-    epoch += 1;
-    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    // let the next kernel of the stream (the next GEMV) become resident and prefetch its weights while this one polls; its
+    // griddepcontrol.wait still returns only when this grid has completed
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int64_t i  = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t ii = i < a.total ? i : 0;
+    // epoch and both candidate slots are requested together (one memory round trip when the values are already there)
+    uint32_t epoch, v0, e0, v1, e1;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(epoch) : "l"(a.state + 1) : "memory");
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v0), "=r"(e0) : "l"(a.buf + ii) : "memory");
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v1), "=r"(e1) : "l"(a.buf + a.cap + ii) : "memory");
+    // the next GEMV reads state[0] only after this whole grid has completed, and this launch's GEMV has read it long ago
+    if (i == 0) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(a.state), "r"(epoch) : "memory");
     if (i < a.total) {
         const uint2 * src = a.buf + (int64_t) (epoch & 1) * a.cap + i;
-        uint32_t v, e;
-        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src) : "memory");
+        uint32_t v = (epoch & 1) ? v1 : v0, e = (epoch & 1) ? e1 : e0;
         if (e != epoch) {
             const long long t0 = clock64();
             do {
-                __nanosleep(64);
+                __nanosleep(32);
                 asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src) : "memory");
                 if (clock64() - t0 > 6000000000LL) __trap();
             } while (e != epoch);
         }
         (i < a.end[0] ? a.Yv[0] : (i < a.end[1] ? a.Yv[1] : a.Yv[2]))[i] = __uint_as_float(v);
-    }
-    // the last CTA to finish closes the exchange: every CTA has read the old epoch by then
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        if (atomicAdd(a.state + 1, 1u) == gridDim.x - 1) {
-            a.state[1] = 0;
-            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(a.state), "r"(epoch) : "memory");
-        }
     }
 }
 
@@ -501,12 +510,12 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
     }
     // persistent: the SMs are shared evenly by the tiles (batches / (token, slot) pairs)
     int64_t ctas = (int64_t) ctx->sm_count * MINB / tiles;
-    if (ctas < 1) ctas = 1;
     // Small matrices deliberately do NOT spread over every SM: one row per warp is the useful maximum, and the SMs left free
     // let the next GEMV of the stream start (PDL + deferred wait) while this one is still running — measured 2.4 us per
     // 1024x4096 matmul with 32 CTAs against 4.1 us with 148.
     const int64_t max_useful = (P.m + NWARPS - 1) / NWARPS;
     if (ctas > max_useful) ctas = max_useful;
+    if (ctas < 1) ctas = 1;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) ctas, (unsigned) tiles);
     cfg.blockDim         = dim3(NWARPS * 32);
@@ -571,7 +580,7 @@ size_t b200_gemv_q4k_smem(int nc, int64_t k) { return (size_t) nc * (size_t) (k 
 
 // f32 activations in P.X (quantized in the kernel prologue); nc = columns of every tile (exact, 1..8)
 int b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait) {
-    if (tiles <= 0 || P.m <= 0) return B200_OK;
+    if (tiles <= 0 || (P.m <= 0 && P.ll_world == 0)) return B200_OK;    // (LL exchange: a rank without rows still announces the epoch)
     if (tiles > 65535) { b200_set_error("gemv_q4k: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
     const size_t smem = b200_gemv_q4k_smem(nc, P.k);
     if (smem > ctx->smem_optin) { b200_set_error("gemv_q4k: %zu B of shared memory needed", smem); return B200_E_ARG; }
