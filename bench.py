@@ -358,18 +358,21 @@ def run_gpu(args):
         import ctypes as C
         L = pkg.lib()
         hctx = pkg.Context(local)                             # own stream
-        # every matmul of the step has its own activation vector and its own result vector in pinned host memory
-        n_x = sum(x.shape[1] for _, x, _, _, _ in order)
+        # every activation vector and every result vector of the step lives in pinned host memory; wq / wk / wv and ffn_gate /
+        # ffn_up read the same vector, as they do in the model (--no-fuse: 225 distinct vectors, one launch per matmul)
+        n_x = sum(g[0][1].shape[1] for g in groups)
         n_y = sum(mn[0] for *_, mn in order)
         xh = torch.randn((n_x,)).pin_memory()
         yh = torch.empty((n_y,)).pin_memory()
         jobs = (pkg.HostMM * len(order))()
-        xo = yo = 0
-        for j, (W, x, y, ys, (m, name)) in enumerate(order):
-            k = x.shape[1]
-            jobs[j].type, jobs[j].w_dev, jobs[j].m, jobs[j].k, jobs[j].n = Q4_K, W.data_ptr(), m, k, 1
-            jobs[j].x_host, jobs[j].y_host = xh.data_ptr() + 4 * xo, yh.data_ptr() + 4 * yo
-            xo += k; yo += m
+        xo = yo = j = 0
+        for g in groups:
+            k = g[0][1].shape[1]
+            for (W, x, y, ys, (m, name)) in g:
+                jobs[j].type, jobs[j].w_dev, jobs[j].m, jobs[j].k, jobs[j].n = Q4_K, W.data_ptr(), m, k, 1
+                jobs[j].x_host, jobs[j].y_host = xh.data_ptr() + 4 * xo, yh.data_ptr() + 4 * yo
+                yo += m; j += 1
+            xo += k
 
         def host_step():                                      # one C-ABI call: uploads, 225 launches, downloads, one sync
             pkg.check(L.b200_mul_mat_host_batch(hctx.handle, jobs, len(order)), "b200_mul_mat_host_batch")
@@ -392,12 +395,16 @@ def run_gpu(args):
         W0, x0 = order[0][0], order[0][1]
         ref0 = pkg.mul_mat(ctx, Q4_K, W0, xh[:x0.shape[1]].view(1, -1).cuda()); ctx.synchronize()
         assert torch.equal(ref0.cpu().view(-1), yh[:W0.shape[0]]), "host-batch result differs from the device-resident result"
+        W1 = order[1][0]                                     # wk of layer 0: same activations, second matrix of the fused launch
+        ref1 = pkg.mul_mat(ctx, Q4_K, W1, xh[:x0.shape[1]].view(1, -1).cuda()); ctx.synchronize()
+        if fuse:
+            assert torch.equal(ref1.cpu().view(-1), yh[W0.shape[0]:W0.shape[0] + W1.shape[0]]), "host-batch (fused) result differs"
         pm_ms = timed(host_step_per_matmul)
         e2e = {"value": round(STEP_BYTES / (e2e_ms * 1e-3) / 1e9, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 4),
                "tok_per_s": round(1e3 / e2e_ms, 2),
                "h2d_bytes_per_step": int(n_x * 4), "d2h_bytes_per_step": int(n_y * 4),
-               "api": "b200_mul_mat_host_batch (C ABI): 225 distinct pinned-host activation vectors -> H2D, 225 launches, "
-                      "225 result vectors -> D2H, one synchronisation per step",
+               "api": f"b200_mul_mat_host_batch (C ABI): {n_groups} distinct pinned-host activation vectors -> H2D, {n_groups} launches "
+                      f"for {STEP_MATMULS} matmuls, {STEP_MATMULS} result vectors -> D2H, one synchronisation per step",
                "per_matmul_sync": {"ms_per_step": round(pm_ms, 4), "tok_per_s": round(1e3 / pm_ms, 2),
                                    "api": "b200_mul_mat_host per matmul (H2D, GEMV, D2H, sync each): a MUL_MAT-only backend "
                                           "with every other op on the CPU"}}

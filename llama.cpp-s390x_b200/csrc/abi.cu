@@ -5,6 +5,7 @@
 #include "quantize.cuh"
 
 #include <cstdarg>
+#include <vector>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -720,74 +721,64 @@ int b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs, int n_job
     if (!ctx || (!jobs && n_jobs > 0) || n_jobs < 0) { b200_set_error("mul_mat_host_batch: bad argument"); return B200_E_ARG; }
     if (n_jobs == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    // device placement.  Jobs that follow one another and read the SAME host activations (wq / wk / wv, ffn_gate / ffn_up of a
+    // decode step) share one uploaded copy — and, below, one launch.
+    std::vector<size_t> xdev((size_t) n_jobs), ydev((size_t) n_jobs);
+    struct span { const char * host; size_t dev, bytes; };
+    std::vector<span> uploads;
     size_t xb = 0, yb = 0;
     for (int j = 0; j < n_jobs; ++j) {
         const b200_host_mm & J = jobs[j];
         if (!J.w_dev || !J.x_host || !J.y_host || !is_weight_type(J.type) || J.m <= 0 || J.k <= 0 || J.n <= 0) {
             b200_set_error("mul_mat_host_batch: bad job %d", j); return B200_E_ARG;
         }
-        xb += align_up((size_t) J.k * J.n * 4, 256);
+        const size_t bytes = (size_t) J.k * J.n * 4;
+        if (j > 0 && J.x_host == jobs[j - 1].x_host && J.k == jobs[j - 1].k && J.n == jobs[j - 1].n) {
+            xdev[j] = xdev[j - 1];
+        } else {
+            xdev[j] = xb;
+            // host vectors that follow one another in memory are moved with a single copy
+            if (!uploads.empty() && uploads.back().host + uploads.back().bytes == (const char *) J.x_host &&
+                uploads.back().dev + uploads.back().bytes == xb) uploads.back().bytes += bytes;
+            else uploads.push_back({(const char *) J.x_host, xb, bytes});
+            xb += align_up(bytes, 256);
+        }
+        ydev[j] = yb;
         yb += align_up((size_t) J.m * J.n * 4, 256);
     }
     int rc = grow(ctx, &ctx->dev_x, &ctx->dev_x_size, xb); if (rc) return rc;
     rc     = grow(ctx, &ctx->dev_y, &ctx->dev_y_size, yb); if (rc) return rc;
     char * dx = (char *) ctx->dev_x, * dy = (char *) ctx->dev_y;
+    for (const span & u : uploads) B200_CUDA_TRY(cudaMemcpyAsync(dx + u.dev, u.host, u.bytes, cudaMemcpyHostToDevice, ctx->stream));
 
-    // uploads: merge jobs whose host vectors follow one another in memory (device layout mirrors the host layout then)
-    size_t off = 0;
-    for (int j = 0; j < n_jobs; ) {
-        const char * h0 = (const char *) jobs[j].x_host;
-        size_t run = 0;
-        int e = j;
-        while (e < n_jobs && (const char *) jobs[e].x_host == h0 + run && ((size_t) jobs[e].k * jobs[e].n * 4) % 256 == 0) {
-            run += (size_t) jobs[e].k * jobs[e].n * 4; ++e;
-        }
-        if (e == j) { run = (size_t) jobs[j].k * jobs[j].n * 4; e = j + 1; }
-        B200_CUDA_TRY(cudaMemcpyAsync(dx + off, h0, run, cudaMemcpyHostToDevice, ctx->stream));
-        off += align_up(run, 256);
-        j = e;
-    }
     // launches
-    size_t xo = 0, yo = 0;
+    auto describe = [&](int i, b200_tensor & a, b200_tensor & b, b200_tensor & d) {
+        const b200_host_mm & J = jobs[i];
+        a = {}; b = {}; d = {};
+        a.data = (void *) J.w_dev; a.type = J.type; a.ne[0] = J.k; a.ne[1] = J.m; a.ne[2] = a.ne[3] = 1;
+        a.nb[0] = (int64_t) b200_tsize(J.type); a.nb[1] = (int64_t) b200_row_size(J.type, J.k); a.nb[2] = a.nb[3] = a.nb[1] * J.m;
+        b.data = dx + xdev[i]; b.type = B200_TYPE_F32; b.ne[0] = J.k; b.ne[1] = J.n; b.ne[2] = b.ne[3] = 1;
+        b.nb[0] = 4; b.nb[1] = J.k * 4; b.nb[2] = b.nb[3] = J.k * 4 * J.n;
+        d.data = dy + ydev[i]; d.type = B200_TYPE_F32; d.ne[0] = J.m; d.ne[1] = J.n; d.ne[2] = d.ne[3] = 1;
+        d.nb[0] = 4; d.nb[1] = J.m * 4; d.nb[2] = d.nb[3] = J.m * 4 * J.n;
+    };
     for (int j = 0; j < n_jobs; ) {
-        // same run structure as above: inside a merged run the device offsets advance unpadded
-        const char * h0 = (const char *) jobs[j].x_host;
-        size_t run = 0;
-        int e = j;
-        while (e < n_jobs && (const char *) jobs[e].x_host == h0 + run && ((size_t) jobs[e].k * jobs[e].n * 4) % 256 == 0) {
-            run += (size_t) jobs[e].k * jobs[e].n * 4; ++e;
-        }
-        if (e == j) { run = (size_t) jobs[j].k * jobs[j].n * 4; e = j + 1; }
-        size_t in_run = 0;
-        for (int i = j; i < e; ++i) {
-            const b200_host_mm & J = jobs[i];
-            b200_tensor a = {}, b = {}, d = {};
-            a.data = (void *) J.w_dev; a.type = J.type; a.ne[0] = J.k; a.ne[1] = J.m; a.ne[2] = a.ne[3] = 1;
-            a.nb[0] = (int64_t) b200_tsize(J.type); a.nb[1] = (int64_t) b200_row_size(J.type, J.k); a.nb[2] = a.nb[3] = a.nb[1] * J.m;
-            b.data = dx + xo + in_run; b.type = B200_TYPE_F32; b.ne[0] = J.k; b.ne[1] = J.n; b.ne[2] = b.ne[3] = 1;
-            b.nb[0] = 4; b.nb[1] = J.k * 4; b.nb[2] = b.nb[3] = J.k * 4 * J.n;
-            d.data = dy + yo; d.type = B200_TYPE_F32; d.ne[0] = J.m; d.ne[1] = J.n; d.ne[2] = d.ne[3] = 1;
-            d.nb[0] = 4; d.nb[1] = J.m * 4; d.nb[2] = d.nb[3] = J.m * 4 * J.n;
-            rc = b200_mul_mat(ctx, &a, &b, &d);
-            if (rc) return rc;
-            in_run += (size_t) J.k * J.n * 4;
-            yo += align_up((size_t) J.m * J.n * 4, 256);
-        }
-        xo += align_up(run, 256);
+        int e = j + 1;
+        while (e < n_jobs && e - j < 3 && xdev[e] == xdev[j] && jobs[e].type == jobs[j].type) ++e;
+        b200_tensor a[3], b[3], d[3];
+        const b200_tensor * ap[3], * dp[3];
+        for (int i = j; i < e; ++i) { describe(i, a[i - j], b[i - j], d[i - j]); ap[i - j] = &a[i - j]; dp[i - j] = &d[i - j]; }
+        rc = e - j == 1 ? b200_mul_mat(ctx, &a[0], &b[0], &d[0]) : b200_mul_mat_multi(ctx, e - j, ap, &b[0], dp);
+        if (rc) return rc;
         j = e;
     }
     // downloads: merge jobs whose results are adjacent on the host AND on the device (sizes that are multiples of 256 B)
-    yo = 0;
     for (int j = 0; j < n_jobs; ) {
         char * h0 = (char *) jobs[j].y_host;
-        size_t run = 0, dev_run = 0;
+        size_t run = 0;
         int e = j;
-        while (e < n_jobs && (char *) jobs[e].y_host == h0 + run && run == dev_run) {
-            const size_t sz = (size_t) jobs[e].m * jobs[e].n * 4;
-            run += sz; dev_run += align_up(sz, 256); ++e;
-        }
-        B200_CUDA_TRY(cudaMemcpyAsync(h0, dy + yo, run, cudaMemcpyDeviceToHost, ctx->stream));
-        yo += dev_run;
+        while (e < n_jobs && (char *) jobs[e].y_host == h0 + run && ydev[e] == ydev[j] + run) { run += (size_t) jobs[e].m * jobs[e].n * 4; ++e; }
+        B200_CUDA_TRY(cudaMemcpyAsync(h0, dy + ydev[j], run, cudaMemcpyDeviceToHost, ctx->stream));
         j = e;
     }
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));

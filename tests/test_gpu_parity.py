@@ -382,3 +382,33 @@ def test_gather_ll_world1_equals_mul_mat(pkg):
         pkg.mul_mat_gather_ll(ctx, TYPES["q4_K"], [dev(random_blocks(TYPES["q4_K"], cap + 256, k, rng))], x,
                               [torch.empty((1, cap + 256), device="cuda")], [0])
     ctx.close()
+
+
+def test_mul_mat_host_batch_shares_uploads_and_launches(pkg, gpu_ctx):
+    """jobs that follow one another with the SAME host activations (q/k/v, gate/up) are uploaded once and fused into one launch;
+    results identical to b200_mul_mat_host per job"""
+    import torch
+    L = pkg.lib()
+    rng = np.random.default_rng(4)
+    k = 1024
+    # (type, m, which x) — x index repeats mark shared activations; a type change or a fourth job must break the group
+    specs = [("q4_K", 512, 0), ("q4_K", 128, 0), ("q4_K", 128, 0), ("q4_K", 512, 1), ("q4_K", 1408, 2), ("q4_K", 1408, 2), ("q8_0", 256, 2),
+             ("q4_K", 64, 3), ("q4_K", 64, 3), ("q4_K", 64, 3), ("q4_K", 64, 3), ("q6_K", 96, 4), ("q6_K", 96, 4)]
+    xh = torch.randn((5, k)).pin_memory()
+    yh = torch.zeros((sum(m for _, m, _ in specs),)).pin_memory()
+    want = torch.zeros_like(yh)
+    jobs = (pkg.HostMM * len(specs))()
+    hctx = pkg.Context(0)
+    Ws, yo = [], 0
+    for j, (name, m, xi) in enumerate(specs):
+        W = dev(random_blocks(TYPES[name], m, k, rng)); Ws.append(W)
+        jobs[j].type, jobs[j].w_dev, jobs[j].m, jobs[j].k, jobs[j].n = TYPES[name], W.data_ptr(), m, k, 1
+        jobs[j].x_host, jobs[j].y_host = xh[xi].data_ptr(), yh.data_ptr() + 4 * yo
+        pkg.check(L.b200_mul_mat_host(hctx.handle, TYPES[name], W.data_ptr(), m, k, xh[xi].data_ptr(), 1, want.data_ptr() + 4 * yo), "single")
+        yo += m
+    n0 = hctx.launches
+    pkg.check(L.b200_mul_mat_host_batch(hctx.handle, jobs, len(specs)), "batch")
+    assert torch.equal(yh, want) and float(yh.abs().max()) > 0
+    # Q4_K groups fuse: {0,1,2} {3} {4,5} {6: q8_0} {7,8,9} {10} -> the q8_0 / q6_K jobs go one by one (2 launches each: quantize + GEMV)
+    assert hctx.launches - n0 < 2 * len(specs) - 4
+    hctx.close()
