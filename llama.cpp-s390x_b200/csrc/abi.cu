@@ -110,6 +110,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     }
     ctx->force_generic = env_int("GGML_B200_FORCE_GENERIC", 0);
     ctx->use_tc        = env_int("GGML_B200_USE_TC", 1);
+    ctx->tc_pair       = env_int("GGML_B200_TC_PAIR", 1);
     ctx->max_gemv_cols = env_int("GGML_B200_MAX_GEMV_COLS", 8);
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
@@ -152,6 +153,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     int * slot = nullptr;
     if      (!strcmp(name, "force_generic")) slot = &ctx->force_generic;
     else if (!strcmp(name, "use_tc"))        slot = &ctx->use_tc;
+    else if (!strcmp(name, "tc_pair"))       slot = &ctx->tc_pair;
     else if (!strcmp(name, "max_gemv_cols")) slot = &ctx->max_gemv_cols;
     else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;

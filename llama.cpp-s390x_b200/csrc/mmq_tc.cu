@@ -34,9 +34,12 @@ constexpr int TC_RAW_BYTES = TC_M * TC_RAW_ROW;
 constexpr int TC_THREADS  = 512;     // 8 converter warps, TMA warp, MMA warp, 4 epilogue warps, 2 spare (whole warpgroups)
 constexpr int TC_A_SLOTS  = 3, TC_RAW_SLOTS = 2;
 
-template <int NT> struct tc_cfg {
-    static constexpr int B_SLOTS = NT == 256 ? 4 : 6;
-    static constexpr int B_BYTES = NT * 128;
+// PAIR: two CTAs (one per SM of a TPC) share one 256-row x NT tile: each converts its own 128 rows of A and holds HALF of
+// the activation tile; the tensor cores of both SMs read both halves, so the B traffic per SM (TMA fill + operand read) halves.
+template <int NT, bool PAIR = false> struct tc_cfg {
+    static constexpr int B_ROWS  = PAIR ? NT / 2 : NT;          // activation columns in this CTA's shared memory
+    static constexpr int B_SLOTS = PAIR ? (NT == 256 ? 6 : 8) : (NT == 256 ? 4 : 6);
+    static constexpr int B_BYTES = B_ROWS * 128;
     static constexpr int SMEM    = B_SLOTS * B_BYTES + TC_A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * TC_RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
     static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
     static_assert(SMEM <= 232448, "exceeds the 227 KB a CTA can opt into");
@@ -261,8 +264,9 @@ struct tc_tile {
     float * Y;
 };
 
-__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int64_t T, tc_tile & t) {
-    const int row_tiles = a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + TC_M - 1) / TC_M;
+// tm = weight rows per work tile (128, or 256 for a CTA pair: CTA `rank` of the pair owns rows [128 * rank, 128 * rank + 128) of it)
+__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int64_t T, tc_tile & t, const int tm = TC_M, const int rank = 0) {
+    const int row_tiles = a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + tm - 1) / tm;
     int rt = (int) (T % row_tiles);
     T /= row_tiles;
     t.wsel = 0; t.m = a.m; t.Y = a.Y;
@@ -271,7 +275,7 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
         rt -= j == 0 ? 0 : a.rt_end[j - 1];
         t.wsel = j; t.m = a.m_j[j]; t.Y = a.Y_j[j];
     }
-    t.row0 = rt * TC_M;
+    t.row0 = rt * tm + TC_M * rank;
     if (a.mode == MM_PLAIN) {
         const int col_tiles = (a.n + NT - 1) / NT;
         const int ct = (int) (T % col_tiles), batch = (int) (T / col_tiles);
@@ -306,19 +310,23 @@ struct tc_seg {
 
 struct tc_walker {
     int64_t w;              // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
+    int     stride, tm, rank;
 
-    __device__ __forceinline__ tc_walker(const tc_args &) { w = blockIdx.x; }
+    // pair = false: one CTA per work item; true: the two CTAs of a cluster walk the same items (256-row tiles)
+    __device__ __forceinline__ tc_walker(const tc_args &, const bool pair = false, const int cta_rank = 0) {
+        w = pair ? blockIdx.x >> 1 : blockIdx.x; stride = pair ? gridDim.x >> 1 : gridDim.x; tm = pair ? 2 * TC_M : TC_M; rank = cta_rank;
+    }
 
     __device__ __forceinline__ bool next(const tc_args & a, const int NT, tc_seg & s) {
         const int64_t n_items = a.n_tiles * a.split_k;
-        for (; w < n_items; w += gridDim.x) {
+        for (; w < n_items; w += stride) {
             const int64_t part = w / a.n_tiles;
             s.T = w - part * a.n_tiles;
-            if (tc_resolve(a, NT, s.T, s.t)) {
+            if (tc_resolve(a, NT, s.T, s.t, tm, rank)) {
                 const int len = a.k / TC_KS / a.split_k;
                 s.k0 = (int) part * len; s.k1 = s.k0 + len;
                 s.order = (int) part; s.nparts = a.split_k;
-                w += gridDim.x;
+                w += stride;
                 return true;
             }
         }
@@ -333,11 +341,15 @@ __device__ long long g_tc_trace[6][128];
 #define TC_TRACE(role, gg) do { } while (0)
 #endif
 
-template <int TYPE, int NT>
+template <int TYPE, int NT, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1,
                                                                    const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmB,
                                                                    const tc_args a) {
-    using cfg = tc_cfg<NT>;
+    using cfg = tc_cfg<NT, PAIR>;
+    // CTA pair: rank 0 is the leader — it issues the MMAs, and the barriers "operands ready" (A full, B full) and "accumulator
+    // drained" that gate them live in ITS shared memory; the peer's warps arrive there remotely.  "Slot free" and "accumulator
+    // ready" barriers are per CTA, signalled in both by multicast commits.
+    const uint32_t cta_rank = PAIR ? tc::cluster_ctarank() : 0u;
     constexpr int BS  = cfg::B_SLOTS, AS = TC_A_SLOTS, RS = TC_RAW_SLOTS;
     constexpr int SPR = raw_k<TYPE>::value / TC_KS;          // MMA stages per raw slot
     extern __shared__ uint8_t smem_raw[];
@@ -356,18 +368,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         if (lane == 0) {
             tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
+            constexpr int NC = PAIR ? 2 : 1;     // CTAs whose warps arrive on the leader's barriers
             for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
-            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) / commit
+            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4 * NC); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) per CTA / commit
             for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 8); }   // expect_tx / 8 converter warps
-            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4); } // commit / 4 epilogue warps
+            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4 * NC); } // commit / 4 epilogue warps per CTA
             tc::mbar_fence_init();
         }
         __syncwarp();
-        tc::tmem_alloc(sTmem, 2 * NT);
+        if (PAIR) tc::tmem_alloc2(sTmem, 2 * NT); else tc::tmem_alloc(sTmem, 2 * NT);
     }
     tc::tc_fence_before();
-    __syncthreads();
+    if (PAIR) tc::cluster_sync(); else __syncthreads();
     tc::tc_fence_after();
+    // where this CTA's warps report "A tile written" / "accumulator drained": the leader's barriers
+    const uint32_t rAFull = PAIR ? tc::mapa_u32(bAFull, 0) : bAFull, rAccEmpty = PAIR ? tc::mapa_u32(bAccEmpty, 0) : bAccEmpty;
+    const uint32_t rBFull = PAIR ? tc::mapa_u32(bBFull, 0) : bBFull;
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
 
@@ -386,7 +402,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         int as = 0, rs = 0, sub = 0;
         uint32_t a_ph = 0, r_ph = 0;
         int tg = 0; (void) tg;
-        tc_walker wk(a);
+        tc_walker wk(a, PAIR, cta_rank);
         tc_seg sg;
         while (wk.next(a, NT, sg)) {
             // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
@@ -415,7 +431,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     tc::fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) {
-                        tc::mbar_arrive(bAFull + 8 * as);
+                        if (PAIR) tc::mbar_arrive_cluster(rAFull + 8 * as); else tc::mbar_arrive(bAFull + 8 * as);
                         if (sub == SPR - 2 + grp) tc::mbar_arrive(bREmpty + 8 * rs);    // this warp's last stage in the raw slot
                         if (warp == 0) TC_TRACE(3, tg);
                         if (warp == 7) TC_TRACE(5, tg);
@@ -436,7 +452,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             int bs = 0, rs = 0, sub = 0;
             uint32_t b_ph = 0, r_ph = 0;
             int tg = 0; (void) tg;
-            tc_walker wk(a);
+            tc_walker wk(a, PAIR, cta_rank);
             tc_seg sg;
             while (wk.next(a, NT, sg)) {
                 const tc_tile & t = sg.t;
@@ -456,8 +472,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     if (lane == 0) TC_TRACE(4, tg);
                     ++tg;
                     if (tc::elect_one()) {
-                        tc::mbar_arrive_expect_tx(bBFull + 8 * bs, cfg::B_BYTES);
-                        tc::tma_load_2d(sB + bs * cfg::B_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0);
+                        if (PAIR) {
+                            // both halves of the activation tile report to the leader's barrier (it expects the bytes of both)
+                            if (cta_rank == 0) tc::mbar_arrive_expect_tx(bBFull + 8 * bs, 2 * cfg::B_BYTES);
+                            tc::tma_load_2d_2cta(sB + bs * cfg::B_BYTES, &tmB, rBFull + 8 * bs, it * TC_KS, t.pos0 + (int) cta_rank * cfg::B_ROWS);
+                        } else {
+                            tc::mbar_arrive_expect_tx(bBFull + 8 * bs, cfg::B_BYTES);
+                            tc::tma_load_2d(sB + bs * cfg::B_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0);
+                        }
                     }
                     __syncwarp();
                     if (++bs == BS) { bs = 0; b_ph ^= 1; }
@@ -466,14 +488,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             }
         }
     } else if (warp == 9) {
-        // ===== MMA issue (whole warp in step, one elected lane issues) ======================================================
-        {
-            constexpr uint32_t idesc = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, TC_M, NT);
+        // ===== MMA issue (whole warp in step, one elected lane issues; CTA pair: the leader only) =========================
+        if (!PAIR || cta_rank == 0) {
+            constexpr uint32_t idesc = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, PAIR ? 2 * TC_M : TC_M, NT);
             const uint64_t da0 = tc::umma_desc_sw128(sA), db0 = tc::umma_desc_sw128(sB);
             int as = 0, bs = 0;
             uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
             int tg = 0; (void) tg;
-            tc_walker wk(a);
+            tc_walker wk(a, PAIR, 0);
             tc_seg sg;
             while (wk.next(a, NT, sg)) {
                 tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
@@ -487,10 +509,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     const uint64_t da = da0 + (uint64_t) (as * (TC_A_BYTES >> 4));
                     const uint64_t db = db0 + (uint64_t) (bs * (cfg::B_BYTES >> 4));
                     if (tc::elect_one()) {
+                        if (PAIR) {
 #pragma unroll
-                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
-                        tc::tc_commit(bAEmpty + 8 * as);
-                        tc::tc_commit(bBEmpty + 8 * bs);
+                            for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_2cta(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                            tc::tc_commit2_mc(bAEmpty + 8 * as, 3);
+                            tc::tc_commit2_mc(bBEmpty + 8 * bs, 3);
+                        } else {
+#pragma unroll
+                            for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                            tc::tc_commit(bAEmpty + 8 * as);
+                            tc::tc_commit(bBEmpty + 8 * bs);
+                        }
                     }
                     __syncwarp();
                     if (lane == 0) TC_TRACE(1, tg);
@@ -498,7 +527,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     if (++as == AS) { as = 0; a_ph ^= 1; }
                     if (++bs == BS) { bs = 0; b_ph ^= 1; }
                 }
-                if (tc::elect_one()) tc::tc_commit(bAccFull + 8 * acc);
+                if (tc::elect_one()) { if (PAIR) tc::tc_commit2_mc(bAccFull + 8 * acc, 3); else tc::tc_commit(bAccFull + 8 * acc); }
                 __syncwarp();
                 acc ^= 1; if (acc == 0) acc_ph ^= 1;
             }
@@ -507,7 +536,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
         const int q = warp & 3;
         uint32_t acc = 0, acc_ph = 0;
-        tc_walker wk(a);
+        tc_walker wk(a, PAIR, cta_rank);
         tc_seg sg;
         while (wk.next(a, NT, sg)) {
             const tc_tile & t = sg.t;
@@ -560,7 +589,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             }
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
+            if (lane == 0) { if (PAIR) tc::mbar_arrive_cluster(rAccEmpty + 8 * acc); else tc::mbar_arrive(bAccEmpty + 8 * acc); }
             if (turnstile) {
                 __threadfence();
                 __syncwarp();
@@ -579,10 +608,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         }
     }
 #endif
+    if (PAIR) tc::cluster_sync();            // the peer may still arrive on this CTA's barriers / read its shared memory
     if (warp == 8) {
         __syncwarp();
         tc::tc_fence_after();
-        tc::tmem_dealloc(tmem, 2 * NT);
+        if (PAIR) tc::tmem_dealloc2(tmem, 2 * NT); else tc::tmem_dealloc(tmem, 2 * NT);
     }
 }
 
@@ -603,26 +633,37 @@ encode_tiled_fn get_encode() {
 
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
 
-template <int TYPE, int NT>
+template <int TYPE, int NT, bool PAIR>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     static bool configured[16] = {};
-    auto kern = mmq_tc_f16_kernel<TYPE, NT>;
+    auto kern = mmq_tc_f16_kernel<TYPE, NT, PAIR>;
     if (!configured[ctx->device & 15]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT>::SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT, PAIR>::SMEM));
         configured[ctx->device & 15] = true;
     }
-    kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT>::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
+    if (PAIR) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned) a.grid); cfg.blockDim = dim3(TC_THREADS);
+        cfg.dynamicSmemBytes = tc_cfg<NT, PAIR>::SMEM; cfg.stream = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tmw[0], tmw[1], tmw[2], tm, a));
+    } else {
+        kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT, PAIR>::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
+    }
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
     return B200_OK;
 }
 
-template <int NT>
+template <int NT, bool PAIR>
 int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
-        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT>(ctx, tmw, tm, a);
-        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT>(ctx, tmw, tm, a);
-        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT, PAIR>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -650,6 +691,7 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
 
 struct tc_plan {
     int     NT;
+    bool    pair;        // CTA pairs on 256-row tiles (MM_PLAIN)
     int64_t n, batches, row_tiles, col_tiles, n_tiles;
     size_t  off_xh, off_sc, off_yc, off_sync, total;
 };
@@ -658,13 +700,17 @@ static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_p
     tc_plan p;
     p.batches   = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
     p.n         = P.mode == MM_PLAIN ? P.ne11 : n_pos;
-    p.row_tiles = (P.m + TC_M - 1) / TC_M;
+    // ctx->tc_pair: 0 = never, 1 = when the matrix has enough 256-row tiles (default), 2 = always (MM_PLAIN)
+    p.pair      = P.mode == MM_PLAIN && (ctx->tc_pair == 2 || (ctx->tc_pair == 1 && P.m >= 2048));
+    const int tm = p.pair ? 2 * TC_M : TC_M;
+    const int units = p.pair ? ctx->sm_count / 2 : ctx->sm_count;
+    p.row_tiles = (P.m + tm - 1) / tm;
     p.NT        = p.n <= 128 ? 128 : 256;
     if (p.NT == 256 && P.mode == MM_PLAIN) {
         // 128 x 256 tiles move fewer shared-memory bytes per flop (measured ~836 vs ~586 clocks per 64-wide K stage), but
         // few of them leave SMs idle: take the tile width with the shorter estimated critical path
         const int64_t t256 = p.row_tiles * ((p.n + 255) / 256) * p.batches, t128 = p.row_tiles * ((p.n + 127) / 128) * p.batches;
-        const int64_t w256 = (t256 + ctx->sm_count - 1) / ctx->sm_count, w128 = (t128 + ctx->sm_count - 1) / ctx->sm_count;
+        const int64_t w256 = (t256 + units - 1) / units, w128 = (t128 + units - 1) / units;
         if (ctx->tc_nt == 128 || (ctx->tc_nt == 0 && P.k < 8192 && w128 * 586 < w256 * 836)) p.NT = 128;
     }
     p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.NT - 1) / p.NT : (n_pos + p.NT - 1) / p.NT + P.n_expert;
@@ -708,12 +754,12 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
 
-    CUtensorMap tm;
+    CUtensorMap tmb;
     const cuuint64_t gdim[2]    = {(cuuint64_t) P.k, (cuuint64_t) n_pos};
     const cuuint64_t gstride[1] = {(cuuint64_t) P.k * sizeof(__half)};
-    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) NT};
+    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) (pl.pair ? NT / 2 : NT)};
     const cuuint32_t estr[2]    = {1, 1};
-    const CUresult cr = get_encode()(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUresult cr = get_encode()(&tmb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_E_CUDA; }
 
@@ -744,11 +790,12 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
     a.n_mats = M ? M->n_mats : 1;
+    const int tm = pl.pair ? 2 * TC_M : TC_M;
     if (M) {
         int rt = 0;
         for (int j = 0; j < 3; ++j) {
             const int jj = j < M->n_mats ? j : M->n_mats - 1;
-            if (j < M->n_mats) rt += (int) ((M->m[j] + TC_M - 1) / TC_M);
+            if (j < M->n_mats) rt += (int) ((M->m[j] + tm - 1) / tm);
             a.rt_end[j] = rt; a.m_j[j] = (int) M->m[jj]; a.Y_j[j] = M->Y[jj];
         }
     }
@@ -760,7 +807,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     // on timing.  (Measured and rejected: stream-K with equal runs per CTA — loses the L2 sharing, no gain.)
     // ctx->tc_split_k: 0 = never, 1 = auto, 2 / 4 = forced
     a.split_k = 1;
-    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0) {
+    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0 && !pl.pair) {
         auto eff = [&](int64_t sk) {
             const int64_t items = pl.n_tiles * sk, waves = (items + ctx->sm_count - 1) / ctx->sm_count;
             return (double) items / (double) (waves * ctx->sm_count);
@@ -770,11 +817,13 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     }
     const int64_t items = pl.n_tiles * a.split_k;
     a.grid = (int) (items < ctx->sm_count ? items : ctx->sm_count);
+    if (pl.pair) { const int64_t cl = ctx->sm_count / 2; a.grid = 2 * (int) (items < cl ? items : cl); }
     if (a.split_k > 1) {
         a.tile_sync = (int32_t *) (ws + pl.off_sync);
         B200_CUDA_TRY(cudaMemsetAsync(a.tile_sync, 0, (size_t) pl.n_tiles * 4 * sizeof(int32_t), ctx->stream));
     }
-    return NT == 128 ? launch_type<128>(ctx, type, tmw, tm, a) : launch_type<256>(ctx, type, tmw, tm, a);
+    if (pl.pair) return NT == 128 ? launch_type<128, true>(ctx, type, tmw, tmb, a) : launch_type<256, true>(ctx, type, tmw, tmb, a);
+    return NT == 128 ? launch_type<128, false>(ctx, type, tmw, tmb, a) : launch_type<256, false>(ctx, type, tmw, tmb, a);
 }
 
 // several weight matrices x the same activations (caller checked: same type / k / row size, MM_PLAIN without batch dims)
@@ -790,7 +839,7 @@ int b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const 
     int64_t padded = 0;
     for (int j = 0; j < n_mats; ++j) {
         M.W[j] = (const uint8_t *) a[j]->data; M.m[j] = a[j]->ne[1]; M.Y[j] = (float *) d[j]->data;
-        padded += (a[j]->ne[1] + TC_M - 1) / TC_M * TC_M;
+        padded += (a[j]->ne[1] + 2 * TC_M - 1) / (2 * TC_M) * (2 * TC_M);      // whole 256-row tiles: valid for single CTAs and for pairs
     }
     P.m = padded;
     if (!b200_tc_supported(ctx, a[0]->type, P)) return B200_E_UNSUPPORTED;
