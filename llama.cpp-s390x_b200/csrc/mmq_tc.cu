@@ -696,7 +696,14 @@ struct tc_plan {
     size_t  off_xh, off_sc, off_yc, off_sync, total;
 };
 
-static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) {
+struct tc_multi {            // several matrices per launch: P.m is the padded total height, these are the parts
+    int n_mats;
+    const uint8_t * W[3];
+    int64_t m[3];
+    float * Y[3];
+};
+
+static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M = nullptr) {
     tc_plan p;
     p.batches   = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
     p.n         = P.mode == MM_PLAIN ? P.ne11 : n_pos;
@@ -705,6 +712,10 @@ static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_p
     const int tm = p.pair ? 2 * TC_M : TC_M;
     const int units = p.pair ? ctx->sm_count / 2 : ctx->sm_count;
     p.row_tiles = (P.m + tm - 1) / tm;
+    if (M) {                 // every matrix padded to whole tiles of the height actually used (must match tc_args::rt_end)
+        p.row_tiles = 0;
+        for (int j = 0; j < M->n_mats; ++j) p.row_tiles += (M->m[j] + tm - 1) / tm;
+    }
     p.NT        = p.n <= 128 ? 128 : 256;
     if (p.NT == 256 && P.mode == MM_PLAIN) {
         // 128 x 256 tiles move fewer shared-memory bytes per flop (measured ~836 vs ~586 clocks per 64-wide K stage), but
@@ -724,13 +735,6 @@ static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_p
     return p;
 }
 
-struct tc_multi {            // several matrices per launch: P.m is the padded total height, these are the parts
-    int n_mats;
-    const uint8_t * W[3];
-    int64_t m[3];
-    float * Y[3];
-};
-
 static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M);
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 
@@ -741,7 +745,7 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
 }
 
 static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M) {
-    const tc_plan pl = make_plan(ctx, P, n_pos, ws_used);
+    const tc_plan pl = make_plan(ctx, P, n_pos, ws_used, M);
     if ((size_t) ctx->ws_size < pl.total) { b200_set_error("tcgen05 GEMM: scratch not reserved"); return B200_E_ARG; }
     uint8_t * ws = (uint8_t *) ctx->ws;
     __half *  Xh = (__half *) (ws + pl.off_xh);
