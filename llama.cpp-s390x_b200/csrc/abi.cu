@@ -14,6 +14,8 @@
 int    b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles);
 int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait);
 size_t b200_gemv_q4k_smem(int nc, int64_t k);
+int    b200_gemv_q4k_mma_ok(const b200_ctx * ctx, const mm_problem & P);
+int    b200_launch_gemv_q4k_mma(b200_ctx * ctx, const mm_problem & P, int64_t tiles, bool late_wait, int64_t live_tiles = 0);
 int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
@@ -116,6 +118,9 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
     ctx->gemv_cfg      = env_int("GGML_B200_GEMV_CFG", 0);
     ctx->tc_nt         = env_int("GGML_B200_TC_NT", 0);
+    ctx->use_mma       = env_int("GGML_B200_USE_MMA", 1);
+    ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
+    ctx->mma_ch        = env_int("GGML_B200_MMA_CH", 0);
     ctx->tc_split_k   = env_int("GGML_B200_TC_SPLIT_K", 1);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
@@ -159,6 +164,9 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
     else if (!strcmp(name, "gemv_cfg"))      slot = &ctx->gemv_cfg;
     else if (!strcmp(name, "tc_nt"))         slot = &ctx->tc_nt;
+    else if (!strcmp(name, "use_mma"))       slot = &ctx->use_mma;
+    else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;
+    else if (!strcmp(name, "mma_ch"))        slot = &ctx->mma_ch;
     else if (!strcmp(name, "tc_split_k"))   slot = &ctx->tc_split_k;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
@@ -350,6 +358,15 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
             aligned16(a->data, a->nb[1], a->nb[2], a->nb[3]) && aligned16(b->data, b->nb[1], b->nb[2], b->nb[3]) &&
             b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
+            // 2..8 columns: integer tensor-core GEMV (mmvq_mma.cu), except where the dp4a kernel's smaller fixed cost still wins
+            // (measured, us dp4a / mma: 1024x4096 n=2 2.9 / 4.4, n=4 4.4 / 4.7; 4096x4096 n=2 6.9 / 8.3, n=4 10.5 / 8.8;
+            //  14336x4096 n=2 12.9 / 12.3; everything at n=8 2-3.5x faster on the tensor cores); use_mma = 2 forces it
+            const bool mma_pays = ctx->use_mma == 2 || (n == 2 ? m * k >= (int64_t) 48 << 20 : (n <= 4 ? m * k >= (int64_t) 8 << 20 : true));
+            if (n >= 2 && ctx->use_mma && mma_pays && !(n_peers > 0 && ctx->gs_world > 0) && b200_gemv_q4k_mma_ok(ctx, P)) {
+                const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
+                pending_push(ctx, d, !late);
+                return b200_launch_gemv_q4k_mma(ctx, P, batches, late);
+            }
             const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
             pending_push(ctx, d, !late);
             if (n_peers > 0 && ctx->gs_world > 0) {
@@ -415,6 +432,25 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
     P.ids = (const int32_t *) ids->data; P.ids_stride = ids->nb[1] / 4;
     P.n_used = n_used; P.n_expert = n_expert;
 
+    if (n_tokens >= 2 && n_tokens <= ctx->max_gemv_cols && (n_pairs >= n_expert || ctx->use_mma == 2) && as->type == B200_TYPE_Q4_K &&
+        ctx->use_mma && !ctx->force_generic && ctx->fuse_quant) {
+        // small batches: gather the pairs by expert, then the tensor-core GEMV takes up to 8 pairs of an expert per pass, so an
+        // expert's weights are read once however many of the tokens chose it (the per-pair GEMV below reads them once per pair:
+        // faster per byte, 5.1 vs 4.3 TB/s, so it keeps the batches in which few pairs share an expert)
+        P.mode = MM_ID_SORTED;
+        if (b200_gemv_q4k_mma_ok(ctx, P)) {
+            pending_push(ctx, c, true);
+            const size_t ids_bytes = (size_t) (n_pairs + n_expert + 1) * sizeof(int32_t);
+            int rc = b200_ctx_reserve(ctx, ids_bytes);
+            if (rc) return rc;
+            int32_t * ids_src1 = (int32_t *) ctx->ws;
+            int32_t * bounds   = ids_src1 + n_pairs;
+            rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
+            if (rc) return rc;
+            P.ids_src1 = ids_src1; P.expert_bounds = bounds;
+            return b200_launch_gemv_q4k_mma(ctx, P, (n_pairs + 7) / 8 + n_expert, false, n_pairs < n_expert ? n_pairs : n_expert);
+        }
+    }
     if (n_tokens <= ctx->max_gemv_cols && n_pairs <= 65535) {
         // decode: every (token, slot) pair is a GEMV against the expert the kernel looks up itself
         P.mode = MM_ID_PAIRS;

@@ -100,6 +100,9 @@ struct b200_ctx {
     const char * pend_hi[16];
     int          n_pend;
     int          defer_wait;      // 1: allow the deferred dependency wait
+    int          use_mma;         // 1: Q4_K with 2..8 columns runs the tensor-core GEMV (mmvq_mma.cu) instead of the dp4a one
+    int          mma_ch;          // tensor-core GEMV: super-blocks per ring stage override (0 = auto, 1)
+    int          mma_ks;          // tensor-core GEMV: K slices per row block override (0 = auto; 1, 2, 4, 8, 16)
     int          noop;            // debugging: GEMV kernels return immediately (measures the launch floor)
 };
 

@@ -1,0 +1,435 @@
+// mmvq_mma.cu — the decode path for 2..8 activation columns (and small MUL_MAT_ID batches): Q4_K GEMV on the integer
+// tensor-core path (mma.sync m16n8k32 u8 x s8), still HBM-bound.
+//
+// Why a second kernel: with dp4a every weight nibble costs one integer MAC instruction PER COLUMN, so gemv_q4k<NC> is issue-bound
+// from n = 2 on (measured on the 128256x4096 output head: n = 4 2.65 TB/s, n = 8 1.24 TB/s).  Here one warp instruction
+// multiplies 16 weight rows x 32 K by all 8 columns, and the per-column cost disappears.
+//
+// Algebra = the reference's own K-quant dot product (ggml_vec_dot_q4_K_q8_K, ggml/src/ggml-cpu/quants.c:645-718): activations
+// quantized per 256 values like quantize_row_q8_K_ref (ggml/src/ggml-quants.c:2692-2729: scale 127/amax, round to nearest
+// even, d8 = 1/scale), then per super-block and (row, column)
+//     y += d8 * ( d * sum_j sc_j * sum_{k in j} q_k * q8_k  -  dmin * sum_j m_j * sum_{k in j} q8_k )
+// with everything inside the brackets exact in int32.  sum_{k in j} q*q8 is one MMA; the sum over the mins is a second MMA
+// chain whose A operand is m_j replicated over the sub-block (it accumulates over j inside the tensor core for free).
+//
+// Data movement:
+//   * weights: every warp owns a private ring of shared-memory stages; a stage = CH super-blocks (144 B each) of 16 rows,
+//     filled by ONE TMA tensor copy (a box of 16 rows x CH*144 bytes out of a tensor map over the raw quant blocks, completion
+//     on an mbarrier) issued several stages ahead by one elected lane — deep prefetch without holding the data in registers
+//     (first version: 16 cp.async.bulk row copies per stage; UBLKCP takes uniform registers, so the 16 lanes were
+//     serialised by a software loop: 2.8 TB/s).  The MMA row <-> matrix row assignment is chosen so that the fragment loads
+//     are bank-conflict-free on the dense box (row stride 144 or 288 B).
+//   * activations: quantized once per CTA in the prologue (persistent CTAs) into int8 [8 columns][k + 32] (conflict-free
+//     B-fragment loads) + float d8[k/256][8].
+//   * K order: a dot product does not care about the order of K as long as both operands agree, so lane t of a row group
+//     takes bytes 8t..8t+7 of a 32-byte group as its A fragment (one LDS.64) and the same 8 K positions of its column as B.
+//   * short matrices: the super-blocks of a 16-row block are split over KS warps of the CTA (K slices) and the partial sums
+//     meet in shared memory.
+//   * summation order: a row's K range is ALWAYS cut into 16 leaves (super-block ranges), each leaf is summed front to back,
+//     and the leaves are added along a fixed binary tree.  A warp that owns several leaves walks its subtree with a small
+//     stack, the K slices of different warps are joined along the same tree — so the fp32 result of a row is bit-identical
+//     for every KS, grid size and row sharding (the row-split parity property), and never depends on timing.
+#include <cuda.h>
+#include "mm_problem.cuh"
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int MW        = 16;                  // warps per CTA
+constexpr int RB        = 16;                  // weight rows per warp task (MMA M)
+constexpr int MAX_STAGE = 8;
+constexpr int OFF_BAR   = 64, OFF_PART = 1152, OFF_D = OFF_PART + 2 * MW * 128 * 4;      // shared-memory map (bytes)
+__host__ __device__ constexpr size_t mma_off_q(int64_t k)    { return (size_t) ((OFF_D + (k / 256) * 32 + 127) / 128 * 128); }
+__host__ __device__ constexpr size_t mma_off_ring(int64_t k) { return mma_off_q(k) + (size_t) 8 * (k + 32); }
+constexpr int COL_PAD   = 32;                  // int8 column stride = k + 32
+
+__device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// the same with a zero accumulator input (no registers to clear)
+__device__ __forceinline__ void mma_u8s8_z(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+__device__ __forceinline__ uint2 lds_u2(const uint32_t a) {
+    uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v;
+}
+__device__ __forceinline__ uint4 lds_u4(const uint32_t a) {
+    uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v;
+}
+
+struct mma_args {
+    int ks;            // K slices per row block (1, 2, 4, 8 or 16)
+    int stages;        // ring depth per warp
+    int ch;            // super-blocks per stage (1 or 2)
+    int late;          // X / ids are not written by a kernel that may still run: the dependency wait moves to just before the first
+                       // store, and this kernel's prologue and streaming overlap the previous kernel's tail (see mmvq.cu / abi.cu)
+};
+
+// adds leaf / subtree sum number i (0-based, in order) of a binary summation tree: on return after the last one of a
+// power-of-two sequence, `cur` is the total
+__device__ __forceinline__ void tree_push(float (&st)[4][4], const int i, float (&cur)[4]) {
+    bool active = true;                 // (no early exit: the levels stay statically indexed, i.e. in registers)
+#pragma unroll
+    for (int lvl = 0; lvl < 4; ++lvl) {
+        const bool bit = (i >> lvl) & 1;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (active && bit)  cur[e] = st[lvl][e] + cur[e];
+            if (active && !bit) st[lvl][e] = cur[e];
+        }
+        active = active && bit;
+    }
+}
+
+// walks a warp's (row block, super-block) steps in order: units u = warp, warp + 16, ... of this CTA; unit = (row block, K slice)
+struct step_cursor {
+    int u, sb, sb_end;
+    int64_t rb;
+    __device__ __forceinline__ void seek(const int units, const int ks, const int nsb, const int64_t rb_lo) {
+        // first non-empty unit at or after u
+        for (; u < units; u += MW) {
+            const int q = u / ks, s = u - q * ks;
+            sb = nsb * s / ks; sb_end = nsb * (s + 1) / ks; rb = rb_lo + q;
+            if (sb < sb_end) return;
+        }
+    }
+    __device__ __forceinline__ bool done(const int units) const { return u >= units; }
+    __device__ __forceinline__ void advance(const int ch, const int units, const int ks, const int nsb, const int64_t rb_lo) {
+        sb += ch;
+        if (sb >= sb_end) { u += MW; seek(units, ks, nsb, rb_lo); }
+    }
+};
+
+__global__ void __launch_bounds__(MW * 32, 1)
+gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const mma_args A) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int k = (int) P.k, nsb = k >> 8;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    // shared memory map
+    float **  s_y    = reinterpret_cast<float **>(smem);                              // 8 output column pointers
+    float *   s_part = reinterpret_cast<float *>(smem + OFF_PART);                    // [2][MW][128] K-slice partial sums
+    float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [nsb][8]
+    int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k));               // [8][k + 32]
+    const uint32_t stage_b = (uint32_t) A.ch * RB * SZ_Q4_K;                          // [MW][stages][16 rows][ch * 144]
+    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k) + (uint32_t) (warp * A.stages) * stage_b;
+    const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
+
+    if (tid == 0) tc::tma_prefetch_desc(&tmW);
+    if (lane == 0) {
+        for (int s = 0; s < A.stages; ++s) tc::mbar_init(bar0 + 8 * s, 1);
+        tc::mbar_fence_init();
+    }
+    __syncwarp();
+
+    // this CTA's share of the row blocks (persistent: the activations are quantized once per CTA)
+    const int64_t nrb   = (P.m + RB - 1) / RB;
+    const int64_t rb_lo = nrb * blockIdx.x / gridDim.x, rb_hi = nrb * (blockIdx.x + 1) / gridDim.x;
+    const int     units = (int) (rb_hi - rb_lo) * A.ks;
+    const int     rounds = (units + MW - 1) / MW;
+
+    mm_cols<8> C;
+    bool live = true;
+    // one ring fill: super-blocks [sb, sb + ch) of rows [16 rb, 16 rb + 16) of matrix `mat` (rows / K past the end are zero-filled)
+    int mat = 0;
+    auto fill = [&](const step_cursor & c, const int stage) {
+        const uint32_t bar = bar0 + 8 * stage;
+        if (tc::elect_one()) {
+            tc::mbar_arrive_expect_tx(bar, stage_b);
+            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (SZ_Q4_K / 2), (int) (c.rb * RB), mat);
+        }
+        __syncwarp();
+    };
+    step_cursor pc;                       // producer cursor
+    int p_stage = 0, in_flight = 0;
+    auto start_fills = [&]() {
+        pc.u = warp; pc.seek(units, A.ks, nsb, rb_lo);
+        for (; in_flight < A.stages && !pc.done(units); ++in_flight) {
+            fill(pc, p_stage);
+            if (++p_stage == A.stages) p_stage = 0;
+            pc.advance(A.ch, units, A.ks, nsb, rb_lo);
+        }
+    };
+    auto set_mat = [&]() { mat = P.nb02 > 0 ? (int) ((C.W - P.W) / P.nb02) : 0; };
+
+    // weights are never written by a kernel of this path: in MM_PLAIN the first ring fills go out before the dependency wait
+    if (P.mode == MM_PLAIN) {
+        live = mm_resolve<8>(P, blockIdx.y, C);
+        set_mat();
+        start_fills();
+    }
+    if (A.late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    else        asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (P.mode != MM_PLAIN) {
+        live = mm_resolve<8>(P, blockIdx.y, C);
+        set_mat();
+        if (live) start_fills();
+    }
+    if (!live) return;                    // block-uniform; nothing was issued
+
+    // ---- prologue: the (up to 8) activation columns -> int8 + one scale per 256 values -----------------------------------
+    if (tid < 8) {
+        float * y = C.y[0];
+#pragma unroll
+        for (int c = 1; c < 8; ++c) if (tid == c) y = C.y[c];
+        s_y[tid] = y;
+    }
+    // (column, super-block) tasks: a warp takes 8 at a time and requests all their data before the first reduction, so the
+    // L2 round trips of a warp's tasks overlap instead of adding up (measured: +0.5 us per column before)
+    for (int task0 = warp; task0 < 8 * nsb; task0 += 8 * MW) {
+        float4 v0[8], v1[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int task = task0 + i * MW;
+            const int col = task / nsb, sb = task - col * nsb;
+            v0[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); v1[i] = v0[i];
+            if (task < 8 * nsb && col < C.nc) {
+                const float * xc = C.x[0];
+#pragma unroll
+                for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
+                const float4 * src = reinterpret_cast<const float4 *>(xc + sb * 256 + lane * 8);
+                v0[i] = __ldg(src); v1[i] = __ldg(src + 1);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int task = task0 + i * MW;
+            if (task >= 8 * nsb) break;
+            const int col = task / nsb, sb = task - col * nsb;
+            uint2 packed = make_uint2(0u, 0u);
+            float d8 = 0.0f;
+            float amax = fmaxf(fmaxf(fmaxf(fabsf(v0[i].x), fabsf(v0[i].y)), fmaxf(fabsf(v0[i].z), fabsf(v0[i].w))),
+                               fmaxf(fmaxf(fabsf(v1[i].x), fabsf(v1[i].y)), fmaxf(fabsf(v1[i].z), fabsf(v1[i].w))));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            if (amax > 0.0f) {
+                const float is = __fdiv_rn(127.0f, amax);
+                d8 = __fdiv_rn(1.0f, is);
+                const int q0 = __float2int_rn(__fmul_rn(is, v0[i].x)), q1 = __float2int_rn(__fmul_rn(is, v0[i].y));
+                const int q2 = __float2int_rn(__fmul_rn(is, v0[i].z)), q3 = __float2int_rn(__fmul_rn(is, v0[i].w));
+                const int q4 = __float2int_rn(__fmul_rn(is, v1[i].x)), q5 = __float2int_rn(__fmul_rn(is, v1[i].y));
+                const int q6 = __float2int_rn(__fmul_rn(is, v1[i].z)), q7 = __float2int_rn(__fmul_rn(is, v1[i].w));
+                packed.x = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) | ((uint32_t) (q3 & 0xff) << 24);
+                packed.y = (uint32_t) (q4 & 0xff) | ((uint32_t) (q5 & 0xff) << 8) | ((uint32_t) (q6 & 0xff) << 16) | ((uint32_t) (q7 & 0xff) << 24);
+            }
+            *reinterpret_cast<uint2 *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
+            if (lane == 0) s_d[sb * 8 + col] = d8;
+        }
+    }
+    __syncthreads();
+    if (!A.late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    bool waited = !A.late;
+
+    // ---- main loop -------------------------------------------------------------------------------------------------------
+    const uint32_t bq = tc::smem_u32(s_q) + (uint32_t) g * (uint32_t) (k + COL_PAD) + 8u * t;   // column g, K bytes 8t..8t+7 of a sub-block
+    const uint32_t sd = tc::smem_u32(s_d) + 8u * t;                                            // d8 of columns 2t, 2t+1
+    // MMA row group g <-> rows rho, rho + 8 of the block: on the dense box (row stride 36 or 72 words) the LDS.64 of a
+    // half-warp (4 row groups x 4 lanes x 8 B) must hit 32 distinct banks: stride 72 words = 8 mod 32 works with rho = g,
+    // stride 36 words = 4 mod 32 needs the rows of a half-warp two apart
+    const int      rho   = A.ch == 1 ? 2 * (g & 3) + (g >> 2) : g;
+    const uint32_t rstr  = (uint32_t) A.ch * SZ_Q4_K;
+    const uint32_t r0off = (uint32_t) rho * rstr, r1off = (uint32_t) (rho + 8) * rstr;
+    int      c_stage = 0;
+    uint32_t c_phase = 0;
+    for (int round = 0; round < rounds; ++round) {
+        const int u = round * MW + warp;
+        float accf[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        int64_t rb = 0;
+        int     ksl = 0;
+        if (u < units) {
+            const int q = u / A.ks;
+            ksl = u - q * A.ks;
+            rb  = rb_lo + q;
+            const int lpw = 16 / A.ks;                                  // summation-tree leaves owned by this warp
+            float st[4][4] = {};
+            const int sb_last = nsb * (ksl + 1) / A.ks - 1;             // last super-block of the unit
+            int in_chunk = 0;
+            for (int li = 0; li < lpw; ++li) {
+              const int lf = ksl * lpw + li;
+              float pf[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+              for (int sb = nsb * lf / 16; sb < nsb * (lf + 1) / 16; ++sb) {
+                if (in_chunk == 0) tc::mbar_wait(bar0 + 8 * c_stage, c_phase);
+                const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * SZ_Q4_K;
+                const uint4 h0 = lds_u4(st_a + r0off), h1 = lds_u4(st_a + r1off);
+                // 6-bit scales / mins of the 8 sub-blocks as bytes (get_scale_min_k4, ggml/src/ggml-quants.c:818-825)
+                const uint32_t sc0[2] = {h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | ((h0.y >> 2) & 0x30303030u)};
+                const uint32_t mn0[2] = {h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | ((h0.z >> 2) & 0x30303030u)};
+                const uint32_t sc1[2] = {h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | ((h1.y >> 2) & 0x30303030u)};
+                const uint32_t mn1[2] = {h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | ((h1.z >> 2) & 0x30303030u)};
+                int al[4] = {0, 0, 0, 0}, ah[4] = {0, 0, 0, 0}, cm[4] = {0, 0, 0, 0};
+                const uint32_t bsb = bq + 256u * sb;
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const uint2 w0 = lds_u2(st_a + r0off + 16 + 32 * jj + 8 * t), w1 = lds_u2(st_a + r1off + 16 + 32 * jj + 8 * t);
+#pragma unroll
+                    for (int hi = 0; hi < 2; ++hi) {
+                        const int j = 2 * jj + hi;
+                        const uint2 b = lds_u2(bsb + 32 * j);
+                        const uint32_t mask = hi ? 0xF0F0F0F0u : 0x0F0F0F0Fu;      // high nibbles stay in place: 16 q, undone below
+                        int c[4];
+                        mma_u8s8_z(c, w0.x & mask, w1.x & mask, w0.y & mask, w1.y & mask, b.x, b.y);
+                        const int s0 = (int) __byte_perm(sc0[j >> 2], 0u, 0x4440u + (j & 3));
+                        const int s1 = (int) __byte_perm(sc1[j >> 2], 0u, 0x4440u + (j & 3));
+                        if (hi) { ah[0] += c[0] * s0; ah[1] += c[1] * s0; ah[2] += c[2] * s1; ah[3] += c[3] * s1; }
+                        else    { al[0] += c[0] * s0; al[1] += c[1] * s0; al[2] += c[2] * s1; al[3] += c[3] * s1; }
+                        const uint32_t m0 = __byte_perm(mn0[j >> 2], 0u, 0x1111u * (j & 3));
+                        const uint32_t m1 = __byte_perm(mn1[j >> 2], 0u, 0x1111u * (j & 3));
+                        mma_u8s8(cm, m0, m1, m0, m1, b.x, b.y);
+                    }
+                }
+                const uint2  d8u = lds_u2(sd + 32u * sb);
+                const float  d8a = __uint_as_float(d8u.x), d8b = __uint_as_float(d8u.y);
+                const float2 dm0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));
+                const float2 dm1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
+                pf[0] += d8a * (dm0.x * (float) (al[0] + (ah[0] >> 4)) - dm0.y * (float) cm[0]);
+                pf[1] += d8b * (dm0.x * (float) (al[1] + (ah[1] >> 4)) - dm0.y * (float) cm[1]);
+                pf[2] += d8a * (dm1.x * (float) (al[2] + (ah[2] >> 4)) - dm1.y * (float) cm[2]);
+                pf[3] += d8b * (dm1.x * (float) (al[3] + (ah[3] >> 4)) - dm1.y * (float) cm[3]);
+                if (++in_chunk == A.ch || sb == sb_last) {
+                    // the stage has been read (values are in registers): hand it to the next fill
+                    in_chunk = 0;
+                    __syncwarp();
+                    if (!pc.done(units)) {
+                        fill(pc, c_stage);
+                        pc.advance(A.ch, units, A.ks, nsb, rb_lo);
+                    }
+                    if (++c_stage == A.stages) { c_stage = 0; c_phase ^= 1u; }
+                }
+              }
+              tree_push(st, li, pf);
+              if (li == lpw - 1) { accf[0] = pf[0]; accf[1] = pf[1]; accf[2] = pf[2]; accf[3] = pf[3]; }
+            }
+        }
+        // ---- end of the unit: add the K slices in slice order, store -----------------------------------------------------
+        bool store = u < units;
+        if (A.ks > 1) {
+            float * part = s_part + (round & 1) * MW * 128;
+            *reinterpret_cast<float4 *>(part + warp * 128 + lane * 4) = make_float4(accf[0], accf[1], accf[2], accf[3]);
+            __syncthreads();
+            store = store && ksl == 0;
+            if (store) {
+                float st[4][4] = {};
+                for (int s = 0; s < A.ks; ++s) {               // the slices' subtree sums, joined along the same tree
+                    const float4 o = *reinterpret_cast<const float4 *>(part + (warp + s) * 128 + lane * 4);
+                    accf[0] = o.x; accf[1] = o.y; accf[2] = o.z; accf[3] = o.w;
+                    tree_push(st, s, accf);
+                }
+            }
+        }
+        if (store) {
+            if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
+            const int64_t row0 = rb * RB + rho, row1 = row0 + 8;
+            const int c0 = 2 * t, c1 = c0 + 1;
+            if (c0 < C.nc) {
+                float * y = s_y[c0];
+                if (row0 < P.m) mm_store(P, y, row0, accf[0]);
+                if (row1 < P.m) mm_store(P, y, row1, accf[2]);
+            }
+            if (c1 < C.nc) {
+                float * y = s_y[c1];
+                if (row0 < P.m) mm_store(P, y, row0, accf[1]);
+                if (row1 < P.m) mm_store(P, y, row1, accf[3]);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn mma_get_encode() {
+    static encode_tiled_fn fn = [] {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (encode_tiled_fn) p;
+    }();
+    return fn;
+}
+
+// shared memory for k values per column with `stages` ring slots of `ch` super-blocks per warp
+static size_t mma_smem(int64_t k, int stages, int ch) { return mma_off_ring(k) + (size_t) MW * stages * ch * RB * SZ_Q4_K; }
+
+// number of weight matrices behind P.W (batches / experts), or 0 when they are not equally spaced
+static int64_t mma_nmat(const mm_problem & P) {
+    if (P.mode != MM_PLAIN) return P.n_expert;
+    const int64_t ne02 = P.ne12 / P.r2, ne03 = P.ne13 / P.r3;
+    if (ne03 > 1 && P.nb03 != P.nb02 * ne02) return 0;
+    return ne02 * ne03;
+}
+
+int b200_gemv_q4k_mma_ok(const b200_ctx * ctx, const mm_problem & P) {
+    if (P.k % 256 != 0 || P.k > (1 << 24) || P.m > (1 << 30) || !mma_get_encode()) return 0;
+    if (mma_smem(P.k, 2, 1) > ctx->smem_optin) return 0;
+    // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
+    if (((uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03) & 15) return 0;
+    const int64_t nmat = mma_nmat(P);
+    if (nmat <= 0 || (nmat > 1 && P.nb02 < P.nb01 * P.m)) return 0;
+    if (((uintptr_t) P.X | (uintptr_t) P.nb11 | (uintptr_t) P.nb12 | (uintptr_t) P.nb13) & 15) return 0;
+    return 1;
+}
+
+// f32 activations in P.X (quantized in the kernel prologue); up to 8 columns per tile (MM_PLAIN: ceil(ne11 / 8) tiles per batch)
+// live_tiles: how many of the tiles are expected to have work (MM_ID_SORTED launches an upper bound; 0 = all)
+int b200_launch_gemv_q4k_mma(b200_ctx * ctx, const mm_problem & Pin, int64_t tiles, bool late_wait, int64_t live_tiles) {
+    if (tiles <= 0 || Pin.m <= 0) return B200_OK;
+    if (tiles > 65535) { b200_set_error("gemv_q4k_mma: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
+    mm_problem P = Pin;
+    const int64_t nmat = mma_nmat(P);
+    if (nmat <= 1) P.nb02 = 0;                    // the kernel derives the matrix index from (W of the tile - P.W) / nb02
+    const int nsb = (int) (P.k / 256);
+    // persistent CTAs share the SMs evenly between the tiles; K slices so that every warp of every CTA has work even when the
+    // matrix is short (the result does not depend on the slicing: fixed summation tree)
+    const int64_t nrb = (P.m + RB - 1) / RB;
+    int64_t ctas = ctx->sm_count / (live_tiles > 0 && live_tiles < tiles ? live_tiles : tiles);
+    if (ctas < 1) ctas = 1;
+    int ks = 1;
+    while (ks < MW && 4 * nrb * ks < 3 * ctas * MW && nsb / (2 * ks) >= 1) ks *= 2;      // measured best: the first ks with ~one unit per warp
+    if (ctx->mma_ks > 0) ks = ctx->mma_ks;
+    if (ks != 1 && ks != 2 && ks != 4 && ks != 8 && ks != 16) { b200_set_error("gemv_q4k_mma: K slices must be 1, 2, 4, 8 or 16"); return B200_E_ARG; }
+    mma_args A = {};
+    A.ks = ks;
+    A.late = ctx->pdl && late_wait ? 1 : 0;
+    // super-blocks per stage: 2 when every K slice is a whole number of pairs
+    A.ch = (nsb % (2 * ks) == 0) ? 2 : 1;
+    if (ctx->mma_ch == 1) A.ch = 1;
+    int stages = MAX_STAGE;
+    while (stages > 1 && mma_smem(P.k, stages, A.ch) > ctx->smem_optin) --stages;
+    if (stages < 2 && A.ch == 2) { A.ch = 1; stages = 2; }
+    if (mma_smem(P.k, stages, A.ch) > ctx->smem_optin) { b200_set_error("gemv_q4k_mma: k = %lld needs too much shared memory", (long long) P.k); return B200_E_ARG; }
+    A.stages = stages;
+
+    // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 16 rows x ch super-blocks
+    CUtensorMap tmw;
+    const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) P.m, (cuuint64_t) (nmat > 1 ? nmat : 1)};
+    const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (nmat > 1 ? P.nb02 : P.nb01 * P.m)};
+    const cuuint32_t wbox[3]    = {(cuuint32_t) (A.ch * SZ_Q4_K / 2), (cuuint32_t) RB, 1};
+    const cuuint32_t westr[3]   = {1, 1, 1};
+    const CUresult wr = mma_get_encode()(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) P.W, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (wr != CUDA_SUCCESS) { b200_set_error("gemv_q4k_mma: cuTensorMapEncodeTiled failed (%d)", (int) wr); return B200_E_CUDA; }
+
+    static bool attr_done[16] = {};
+    if (!attr_done[ctx->device & 15]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
+        attr_done[ctx->device & 15] = true;
+    }
+    const int64_t max_useful = (nrb * ks + MW - 1) / MW;
+    if (ctas > max_useful) ctas = max_useful;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) ctas, (unsigned) tiles);
+    cfg.blockDim         = dim3(MW * 32);
+    cfg.dynamicSmemBytes = mma_smem(P.k, stages, A.ch);
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_q4k_mma, tmw, P, A));
+    ctx->launches++;
+    return B200_OK;
+}
