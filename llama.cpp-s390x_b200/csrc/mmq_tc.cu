@@ -36,11 +36,14 @@ constexpr int TC_A_SLOTS  = 3, TC_RAW_SLOTS = 2;
 
 // PAIR: two CTAs (one per SM of a TPC) share one 256-row x NT tile: each converts its own 128 rows of A and holds HALF of
 // the activation tile; the tensor cores of both SMs read both halves, so the B traffic per SM (TMA fill + operand read) halves.
-template <int NT, bool PAIR = false> struct tc_cfg {
+// RAW_ROW: bytes per row and raw slot — 144 (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 blocks + pad) or 224 (Q6_K: one 210-byte
+// super-block + pad; the wider raw ring is paid for with one activation slot)
+template <int NT, bool PAIR = false, int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
     static constexpr int B_ROWS  = PAIR ? NT / 2 : NT;          // activation columns in this CTA's shared memory
-    static constexpr int B_SLOTS = PAIR ? (NT == 256 ? 6 : 8) : (NT == 256 ? 4 : 6);
+    static constexpr int B_SLOTS = (PAIR ? (NT == 256 ? 6 : 8) : (NT == 256 ? 4 : 6)) - (RAW_ROW > TC_RAW_ROW ? 1 : 0);
     static constexpr int B_BYTES = B_ROWS * 128;
-    static constexpr int SMEM    = B_SLOTS * B_BYTES + TC_A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * TC_RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int RAW_BYTES = TC_M * RAW_ROW;
+    static constexpr int SMEM    = B_SLOTS * B_BYTES + TC_A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
     static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
     static_assert(SMEM <= 232448, "exceeds the 227 KB a CTA can opt into");
 };
@@ -48,6 +51,12 @@ template <int NT, bool PAIR = false> struct tc_cfg {
 // K elements covered by one raw slot (144 bytes per row)
 template <int TYPE> struct raw_k          { static constexpr int value = 256; };
 template <> struct raw_k<B200_TYPE_Q8_0>  { static constexpr int value = 128; };
+// bytes by which raw slot i of a row is fetched early so that the TMA source address is 16-byte aligned
+template <int TYPE> __device__ __forceinline__ uint32_t raw_skew(const int i) {
+    return TYPE == B200_TYPE_Q8_0 ? 8u * (uint32_t) (i & 1) : (TYPE == B200_TYPE_Q6_K ? 2u * (uint32_t) (i & 7) : 0u);
+}
+template <int TYPE> struct raw_row        { static constexpr int value = TC_RAW_ROW; };
+template <> struct raw_row<B200_TYPE_Q6_K> { static constexpr int value = 224; };
 
 struct tc_args {
     const uint8_t * W;
@@ -250,6 +259,50 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
         }
     }
 };
+// Q6_K (ggml-common.h:352-358, dequantize_row_q6_K ggml-quants.c:1877-1906): per 128-half n, element l of 32-group r is
+// (nibble r>>1 of ql[64n + 32(r&1) + l]) | (bits 2r, 2r+1 of qh[32n + l]) << 4, value (q - 32) * d * sc[8n + 2r + l/16].
+// Stage `sub` = K [64 sub, 64 sub + 64): half n = sub >> 1; thread half h owns group r = 2 (sub & 1) + h.  A 210-byte
+// super-block is only 2-byte aligned (in global memory and, after the aligned TMA fetch, in its 224-byte shared-memory row).
+template <> struct w_frag<B200_TYPE_Q6_K> {
+    uint4 l0, l1, q0, q1;
+    uint32_t sc, d;
+    // 16 bytes from a 2-byte aligned shared-memory address (the super-block sits `skew` bytes into its 224-byte row)
+    static __device__ __forceinline__ uint4 lds16_b2(const uint32_t addr) {
+        const uint32_t a = addr & ~3u, sh = (addr & 2u) * 8u;
+        const uint32_t w0 = lds_u32(a), w1 = lds_u32(a + 4), w2 = lds_u32(a + 8), w3 = lds_u32(a + 12), w4 = lds_u32(a + 16);
+        return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    }
+    __device__ __forceinline__ void load(const uint32_t row, const int sub, const int h) {
+        const int n = sub >> 1, r = 2 * (sub & 1) + h;
+        l0 = lds16_b2(row + 64 * n + 32 * h);  l1 = lds16_b2(row + 64 * n + 32 * h + 16);
+        q0 = lds16_b2(row + 128 + 32 * n);     q1 = lds16_b2(row + 128 + 32 * n + 16);
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(sc) : "r"(row + 192 + 8 * n + 2 * r));
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(d)  : "r"(row + 208));
+    }
+    __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+        const int r = 2 * (sub & 1) + h, shl = 4 * (sub & 1), shh = 2 * r;
+        const float df = __half2float(__ushort_as_half((unsigned short) d));
+        const __half2 s_a = h2_const(df * (float) (int8_t) (sc & 0xff)), s_b = h2_const(df * (float) (int8_t) (sc >> 8));
+        const __half2 k1056 = h2_const(1056.0f);
+        const uint32_t lw[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+        const uint32_t hw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        uint32_t v[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t q = ((lw[j] >> shl) & 0x0F0F0F0Fu) | (((hw[j] >> shh) & 0x03030303u) << 4);      // 4 x (0..63)
+            const __half2 a = bits_h2(__byte_perm(q, 0x64646464u, 0x4240));     // (1024 + q0, 1024 + q2)
+            const __half2 b = bits_h2(__byte_perm(q, 0x64646464u, 0x4341));     // (1024 + q1, 1024 + q3)
+            const __half2 s = j < 4 ? s_a : s_b;
+            v[2 * j]     = h2_bits(__hmul2(__hsub2(a, k1056), s));
+            v[2 * j + 1] = h2_bits(__hmul2(__hsub2(b, k1056), s));
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            out[c]  = make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+            slot[c] = 4 * h + c;
+        }
+    }
+};
 
 
 // ---- the GEMM ---------------------------------------------------------------------------------------------------------
@@ -345,7 +398,8 @@ template <int TYPE, int NT, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1,
                                                                    const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmB,
                                                                    const tc_args a) {
-    using cfg = tc_cfg<NT, PAIR>;
+    using cfg = tc_cfg<NT, PAIR, raw_row<TYPE>::value>;
+    constexpr int RAW_ROW = raw_row<TYPE>::value, RAW_BYTES = cfg::RAW_BYTES;
     // CTA pair: rank 0 is the leader — it issues the MMAs, and the barriers "operands ready" (A full, B full) and "accumulator
     // drained" that gate them live in ITS shared memory; the peer's warps arrive there remotely.  "Slot free" and "accumulator
     // ready" barriers are per CTA, signalled in both by multicast commits.
@@ -357,7 +411,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t sB   = base;
     const uint32_t sA   = sB + BS * cfg::B_BYTES;
     const uint32_t sRaw = sA + AS * TC_A_BYTES;
-    const uint32_t sBar = sRaw + RS * TC_RAW_BYTES;
+    const uint32_t sBar = sRaw + RS * RAW_BYTES;
     const uint32_t bBFull = sBar, bBEmpty = bBFull + 8 * BS, bAFull = bBEmpty + 8 * BS, bAEmpty = bAFull + 8 * AS;
     const uint32_t bRFull = bAEmpty + 8 * AS, bREmpty = bRFull + 8 * RS, bAccFull = bREmpty + 8 * RS, bAccEmpty = bAccFull + 16;
     const uint32_t sTmem  = bAccEmpty + 16;
@@ -396,7 +450,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         // two (row, half) tasks, adjacent lanes sharing a row.
         const int grp = warp >> 2, h = lane & 1;
         const int r0 = 32 * (warp & 3) + (lane >> 1), r1 = r0 + 16;
-        const uint32_t raw_row0 = sRaw + (uint32_t) (r0 * TC_RAW_ROW), raw_row1 = sRaw + (uint32_t) (r1 * TC_RAW_ROW);
+        const uint32_t raw_row0 = sRaw + (uint32_t) (r0 * RAW_ROW), raw_row1 = sRaw + (uint32_t) (r1 * RAW_ROW);
         const uint32_t a_row0 = sA + (uint32_t) ((r0 >> 3) * 1024 + (r0 & 7) * 128), a_row1 = sA + (uint32_t) ((r1 >> 3) * 1024 + (r1 & 7) * 128);
         const int sw = r0 & 7;                                // r1 & 7 is the same
         int as = 0, rs = 0, sub = 0;
@@ -405,16 +459,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         tc_walker wk(a, PAIR, cta_rank);
         tc_seg sg;
         while (wk.next(a, NT, sg)) {
-            // Q8_0: odd raw slots are fetched 8 bytes early (16-byte TMA alignment)
-            uint32_t skew = TYPE == B200_TYPE_Q8_0 ? 8u * (uint32_t) ((sg.k0 / SPR) & 1) : 0u;
+            // TMA needs 16-byte aligned global addresses: Q8_0's odd raw slots (136-byte steps) are fetched 8 bytes early, Q6_K's
+            // slot i (210-byte steps) 2 (i mod 8) bytes early; the converters skip the skew
+            int sbi = sg.k0 / SPR;
+            uint32_t skew = raw_skew<TYPE>(sbi);
             for (int it = sg.k0; it < sg.k1; ++it) {
                 if ((it & 1) == grp) {                        // segments start at even stages, so parity follows `it`
                     // first stage of this group in the raw slot: sub == grp (SPR is even)
                     if (sub == grp) tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
                     w_frag<TYPE> f0, f1;
                     uint4 o0[4], o1[4]; int slot[4];
-                    f0.load(raw_row0 + rs * TC_RAW_BYTES + skew, sub, h);
-                    f1.load(raw_row1 + rs * TC_RAW_BYTES + skew, sub, h);
+                    f0.load(raw_row0 + rs * RAW_BYTES + skew, sub, h);
+                    f1.load(raw_row1 + rs * RAW_BYTES + skew, sub, h);
                     f0.convert(sub, h, o0, slot);
                     f1.convert(sub, h, o1, slot);
                     tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
@@ -441,7 +497,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 if (++as == AS) { as = 0; a_ph ^= 1; }
                 if (++sub == SPR) {
                     sub = 0;
-                    if (TYPE == B200_TYPE_Q8_0) skew ^= 8u;
+                    skew = raw_skew<TYPE>(++sbi);
                     if (++rs == RS) { rs = 0; r_ph ^= 1; }
                 }
             }
@@ -456,17 +512,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             tc_seg sg;
             while (wk.next(a, NT, sg)) {
                 const tc_tile & t = sg.t;
-                int x = (sg.k0 / SPR) * a.raw_step, odd = (sg.k0 / SPR) & 1;    // next raw slot in the row (16-bit elements)
+                int sbi = sg.k0 / SPR, x = sbi * a.raw_step;                     // next raw slot in the row (16-bit elements)
                 for (int it = sg.k0; it < sg.k1; ++it) {
                     if (sub == 0) {
                         tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1, 100);
                         if (tc::elect_one()) {
-                            tc::mbar_arrive_expect_tx(bRFull + 8 * rs, TC_RAW_BYTES);
+                            tc::mbar_arrive_expect_tx(bRFull + 8 * rs, RAW_BYTES);
                             const CUtensorMap * tw = t.wsel == 0 ? &tmW : (t.wsel == 1 ? &tmW1 : &tmW2);
-                            tc::tma_load_3d(sRaw + rs * TC_RAW_BYTES, tw, bRFull + 8 * rs, x - (TYPE == B200_TYPE_Q8_0 ? 4 * odd : 0), t.row0, t.mat);
+                            tc::tma_load_3d(sRaw + rs * RAW_BYTES, tw, bRFull + 8 * rs, x - (int) (raw_skew<TYPE>(sbi) >> 1), t.row0, t.mat);
                         }
                         __syncwarp();
-                        x += a.raw_step; odd ^= 1;
+                        x += a.raw_step; ++sbi;
                     }
                     tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
                     if (lane == 0) TC_TRACE(4, tg);
@@ -631,27 +687,28 @@ encode_tiled_fn get_encode() {
     return fn;
 }
 
-bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
+bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
 
 template <int TYPE, int NT, bool PAIR>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     static bool configured[16] = {};
     auto kern = mmq_tc_f16_kernel<TYPE, NT, PAIR>;
+    using cfg_t = tc_cfg<NT, PAIR, raw_row<TYPE>::value>;
     if (!configured[ctx->device & 15]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_cfg<NT, PAIR>::SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg_t::SMEM));
         configured[ctx->device & 15] = true;
     }
     if (PAIR) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned) a.grid); cfg.blockDim = dim3(TC_THREADS);
-        cfg.dynamicSmemBytes = tc_cfg<NT, PAIR>::SMEM; cfg.stream = ctx->stream;
+        cfg.dynamicSmemBytes = cfg_t::SMEM; cfg.stream = ctx->stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
         B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tmw[0], tmw[1], tmw[2], tm, a));
     } else {
-        kern<<<(unsigned) a.grid, TC_THREADS, tc_cfg<NT, PAIR>::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
+        kern<<<(unsigned) a.grid, TC_THREADS, cfg_t::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
     }
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
@@ -664,6 +721,7 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtenso
         case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K, NT, PAIR>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -778,7 +836,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
         const int64_t rows = M ? M->m[jj] : P.m;
         const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) rows, (cuuint64_t) (M ? 1 : nmat)};
         const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (!M && nmat > 1 ? P.nb02 : P.nb01 * rows)};
-        const cuuint32_t wbox[3]    = {(cuuint32_t) TC_RAW_ROW / 2, (cuuint32_t) TC_M, 1};
+        const cuuint32_t wbox[3]    = {(cuuint32_t) (type == B200_TYPE_Q6_K ? raw_row<B200_TYPE_Q6_K>::value : TC_RAW_ROW) / 2, (cuuint32_t) TC_M, 1};
         const cuuint32_t westr[3]   = {1, 1, 1};
         const CUresult wr = get_encode()(&tmw[j], CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) base, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -787,7 +845,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
 
     tc_args a = {};
     a.ne02 = (int) ne02;
-    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : TC_RAW_ROW) / 2;
+    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : TC_RAW_ROW)) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;

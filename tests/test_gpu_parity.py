@@ -182,11 +182,11 @@ def test_gemm_vs_oracle(pkg, gpu_ctx, orc, name, n, m, k):
     assert nmse(want, got) <= NMSE_TOL
 
 
-TC_TYPES = ["q4_K", "q4_0", "q8_0"]     # weight types the tcgen05 path covers (Q6_K stays on the CUDA-core path)
+TC_TYPES = ["q4_K", "q4_0", "q8_0", "q6_K"]     # weight types the tcgen05 path covers (Q6_K: rows of a multiple of 2048 values, else CUDA cores)
 
 
 @pytest.mark.parametrize("name", TC_TYPES)
-@pytest.mark.parametrize("n,m,k", [(33, 200, 512), (130, 128, 256), (512, 1000, 2048)])
+@pytest.mark.parametrize("n,m,k", [(33, 200, 512), (130, 128, 256), (512, 1000, 2048), (77, 300, 4096)])
 def test_tc_gemm_close_to_f64_truth_and_to_cuda_core_path(pkg, gpu_ctx, orc, name, n, m, k):
     """prefill path (tcgen05, fp16 operands / fp32 accumulate) vs (a) the exact product in f64 — fp16 rounding only, so far
     closer than the Q8_1-quantised reference gets — and (b) our CUDA-core path that follows ggml-cpu's Q8_1 arithmetic"""

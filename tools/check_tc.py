@@ -9,7 +9,9 @@ from tests.util import nmse, random_blocks
 pkg = load_package()
 ctx = pkg.Context(0, stream="torch")
 rng = np.random.default_rng(1)
-TYPES = {"q4_K": 12, "q8_0": 8, "q4_0": 2}
+TYPES = {"q4_K": 12, "q8_0": 8, "q4_0": 2, "q6_K": 14}
+if "--q6" in sys.argv:
+    TYPES = {"q6_K": 14}
 quick = "--quick" in sys.argv
 
 
@@ -24,7 +26,7 @@ def both(t, W, X):
     return y0.cpu().numpy(), y1.cpu().numpy()
 
 
-cases = [(256, 1024, 64), (128, 256, 9), (200, 512, 130), (4096, 4096, 512)]
+cases = [(256, 1024, 64), (128, 256, 9), (200, 512, 130), (4096, 4096, 512), (300, 2048, 77)]
 if quick:
     cases = cases[:2]
 for name, t in TYPES.items():
