@@ -410,11 +410,18 @@ def run_gpu(args):
                                           "with every other op on the CPU"}}
     if world == 1 and args.shapes:
         shapes = per_shape(torch, pkg, ctx, stream, ops)
+    decode_batch = None
+    if world == 1 and not args.no_extras:
+        decode_batch = decode_batch_bench(torch, pkg, ctx, stream, ops)
     prefill = None
     if world == 1 and not args.no_prefill:
         del ops, order, per_layer, groups
         torch.cuda.empty_cache()
         prefill = prefill_bench(torch, pkg, ctx, stream)
+    moe = None
+    if world == 1 and not args.no_extras:
+        torch.cuda.empty_cache()
+        moe = moe_bench(torch, pkg, ctx, stream)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -442,13 +449,91 @@ def run_gpu(args):
             out["e2e"] = e2e
         if shapes:
             out["shapes"] = shapes
+        if decode_batch:
+            out["decode_batch"] = decode_batch
         if prefill:
             out["prefill"] = prefill
+        if moe:
+            out["moe"] = moe
         if world == 1 and args.cpu_seconds > 0:
             out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):
+    """BASELINE configs[1], n = 2..8: every distinct shape of the step with n activation columns (CUDA graph, rotating over the
+    step's own distinct weight copies), count-weighted into a step.  Bytes = the algorithmic m*k*4.5/8 + n*k*4 + m*n*4."""
+    peak, _ = peaks()
+    res = {"kernel": "gemv_q4k_mma (mma.sync m16n8k32 u8 x s8, TMA-staged weights) where it beats gemv_q4k<n> (dp4a): see abi.cu"}
+    for n in ns:
+        idx, step_us, step_bytes, per = 0, 0.0, 0.0, {}
+        for name, m, k, count in LLAMA3_8B:
+            group = ops[idx: idx + count]
+            idx += count
+            iters = 32 if count > 1 else 4
+            X = torch.randn((n, k), device="cuda")
+            Y = torch.empty((n, m), device="cuda")
+            with torch.cuda.stream(stream):
+                pkg.mul_mat(ctx, Q4_K, group[0][0], X, out=Y)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    for i in range(iters):
+                        pkg.mul_mat(ctx, Q4_K, group[i % count][0], X, out=Y)
+                g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(3):
+                    g.replay()
+                e1.record(stream)
+                stream.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (3 * iters)
+            b = m * k * 4.5 / 8 + n * k * 4 + m * n * 4
+            per[name] = {"us": round(us, 2), "gbps": round(b / us / 1e3, 1)}
+            step_us += us * count
+            step_bytes += b * count
+        res[f"n{n}"] = {"ms_per_step": round(step_us / 1e3, 4), "gbps": round(step_bytes / step_us / 1e3, 1),
+                        "frac_of_hbm_peak": round(step_bytes / step_us / 1e3 / peak, 4), "tok_per_s_matmul_only": round(n * 1e6 / step_us, 1),
+                        "per_shape": per}
+    return res
+
+
+def moe_bench(torch, pkg, ctx, stream):
+    """BASELINE configs[3]: Mixtral-8x7B Q4_K MUL_MAT_ID, top-2 of 8 experts, ffn_gate/up [4096 -> 14336] and ffn_down
+    [14336 -> 4096] at 1, 8 and 512 tokens (ids: distinct experts per token drawn uniformly, seed 99).  Decode sizes are
+    HBM-bound (GB/s over the bytes of the experts touched), 512 tokens is tensor-bound (2*m*k*tokens*2 flops)."""
+    import numpy as np
+    gen = torch.Generator(device="cuda"); gen.manual_seed(7)
+    rng = np.random.default_rng(99)
+    NE, NU = 8, 2
+    out = {"n_expert": NE, "n_used": NU}
+    for label, m, k in (("gate_up", 14336, 4096), ("down", 4096, 14336)):
+        AS = [device_random_q4k(torch, NE * m, k, gen).reshape(NE, m, -1) for _ in range(2)]      # 2 x 264 MB > L2
+        for n_tokens in (1, 8, 512):
+            ids_np = np.stack([rng.permutation(NE)[:NU] for _ in range(n_tokens)]).astype(np.int32)
+            ids = torch.from_numpy(ids_np).cuda()
+            B = torch.randn((n_tokens, 1, k), device="cuda")
+            C_ = torch.empty((n_tokens, NU, m), device="cuda")
+            iters = 8
+            with torch.cuda.stream(stream):
+                pkg.mul_mat_id(ctx, Q4_K, AS[0], B, ids, out=C_)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    for i in range(iters):
+                        pkg.mul_mat_id(ctx, Q4_K, AS[i % 2], B, ids, out=C_)
+                g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream); g.replay(); g.replay(); e1.record(stream)
+                stream.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (2 * iters)
+            touched = int(len(np.unique(ids_np)))
+            out[f"{label}_t{n_tokens}"] = {"us": round(us, 1), "experts_touched": touched,
+                                           "gbps_touched_expert_bytes": round(touched * m * k * 4.5 / 8 / us / 1e3, 1),
+                                           "tflops": round(2.0 * m * k * n_tokens * NU / us / 1e6, 1)}
+        del AS
+        torch.cuda.empty_cache()
+    return out
 
 
 def per_shape(torch, pkg, ctx, stream, ops):
@@ -564,6 +649,7 @@ def main():
     ap.add_argument("--gather-sync", default="ll", choices=["ll", "barrier", "flags"], help="N > 1: how a matmul's gather is completed")
     ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
+    ap.add_argument("--no-extras", action="store_true", help="skip the n=2..8 decode and the MoE (MUL_MAT_ID) sections")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
