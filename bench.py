@@ -46,8 +46,26 @@ def algo_bytes(m, k, n=1):
     return m * k * 4.5 / 8 + n * k * 4 + m * n * 4
 
 
+# BASELINE configs[4]: Llama-3-70B shapes (80 layers, 39.6 GB of Q4_K weights) for the row-split runs (--model 70b)
+LLAMA3_70B = [
+    ("wq", 8192, 8192, 80), ("wk", 1024, 8192, 80), ("wv", 1024, 8192, 80), ("wo", 8192, 8192, 80),
+    ("ffn_gate", 28672, 8192, 80), ("ffn_up", 28672, 8192, 80), ("ffn_down", 8192, 28672, 80),
+    ("output", 128256, 8192, 1),
+]
+MODEL = "Llama-3-8B"
 STEP_BYTES = sum(algo_bytes(m, k) * c for _, m, k, c in LLAMA3_8B)
 STEP_MATMULS = sum(c for *_, c in LLAMA3_8B)
+
+
+def select_model(name):
+    """--model 70b: the same bench over the Llama-3-70B table (the module-level table keeps its historical name)"""
+    global LLAMA3_8B, STEP_BYTES, STEP_MATMULS, METRIC, MODEL
+    if name == "70b":
+        LLAMA3_8B = LLAMA3_70B
+        METRIC = "q4_k_gemv_hbm_gbps_llama3_70b_decode"
+        MODEL = "Llama-3-70B"
+    STEP_BYTES = sum(algo_bytes(m, k) * c for _, m, k, c in LLAMA3_8B)
+    STEP_MATMULS = sum(c for *_, c in LLAMA3_8B)
 
 
 def peaks():
@@ -158,8 +176,10 @@ def prefill_bench(torch, pkg, ctx, stream, n=512):
         # the step with wq/wk/wv and ffn_gate/ffn_up fused (b200_mul_mat_multi: one activation conversion, one grid per group)
         sep = {(m, k): per[f"{m}x{k}"]["us"] * 1e-3 for (m, k) in shapes}
         fused_ms = total_ms
-        for gname, ms_ in (("qkv", (4096, 1024, 1024)), ("gate_up", (14336, 14336))):
-            k = 4096
+        T = {name: (m, k) for name, m, k, _ in LLAMA3_8B}
+        NL = LLAMA3_8B[0][3]
+        for gname, ms_ in (("qkv", (T["wq"][0], T["wk"][0], T["wv"][0])), ("gate_up", (T["ffn_gate"][0], T["ffn_up"][0]))):
+            k = T["wq"][1]
             Ws = [[make(torch, m, k, gen) for m in ms_] for _ in range(3)]
             X = torch.randn((n, k), device="cuda", generator=gen)
             Ys = [torch.empty((n, m), device="cuda") for m in ms_]
@@ -174,7 +194,7 @@ def prefill_bench(torch, pkg, ctx, stream, n=512):
                 stream.synchronize()
             ms = e0.elapsed_time(e1) / 12
             per[gname + "_fused"] = {"us": round(ms * 1e3, 1), "tflops": round(2.0 * sum(ms_) * n * k / ms / 1e9, 1)}
-            fused_ms += 32 * (ms - sum(sep[(m, k)] for m in ms_))
+            fused_ms += NL * (ms - sum(sep[(m, k)] for m in ms_))
             del Ws, X, Ys
         tf = flops / fused_ms / 1e9
         out[tname] = {"ms_per_step": round(fused_ms, 3), "ms_per_step_unfused": round(total_ms, 3),
@@ -270,8 +290,9 @@ def run_gpu(args):
                 y, ys = None, torch.empty((1, rows), device="cuda")
             ops.append((W, xs[k], y, ys, (m, name)))
     # interleave like a real forward: layer by layer
-    per_layer = [[o for o in ops[i * 32:(i + 1) * 32]] for i in range(7)]
-    order = [per_layer[j][l] for l in range(32) for j in range(7)] + [ops[-1]]
+    NL = LLAMA3_8B[0][3]
+    per_layer = [[o for o in ops[i * NL:(i + 1) * NL]] for i in range(7)]
+    order = [per_layer[j][l] for l in range(NL) for j in range(7)] + [ops[-1]]
 
     # 1 GPU: the matrices that share their activations (wq / wk / wv, ffn_gate / ffn_up) go through b200_mul_mat_multi, one launch
     # per group — the same 225 matmuls in 129 launches (--no-fuse: one b200_mul_mat each)
@@ -418,6 +439,11 @@ def run_gpu(args):
         del ops, order, per_layer, groups
         torch.cuda.empty_cache()
         prefill = prefill_bench(torch, pkg, ctx, stream)
+    prefill_rs = None
+    if world > 1 and not args.no_prefill:
+        del ops, order, per_layer, groups
+        torch.cuda.empty_cache()
+        prefill_rs = prefill_rowsplit_bench(torch, dist, pkg, ctx, stream, rank, world, local)
     moe = None
     if world == 1 and not args.no_extras:
         torch.cuda.empty_cache()
@@ -429,9 +455,9 @@ def run_gpu(args):
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
             "vs_baseline": None, "dtype": "int8 dot (dp4a) x fp32 scales; Q4_K weights, Q8_1 activations", "data": "synthetic",
-            "config": {"workload": "Llama-3-8B Q4_K decode step: 225 MUL_MATs at n=1 (k=4096, m=4096/1024/14336/128256; m=4096,k=14336)",
+            "config": {"workload": f"{MODEL} Q4_K decode step: {STEP_MATMULS} MUL_MATs at n=1 (" + ", ".join(sorted({f"{m}x{k}" for _, m, k, _ in LLAMA3_8B})) + ")",
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
-                       "l2": "inputs larger than L2: 4.22 GB of distinct weights per step vs 126 MB L2, no flush needed",
+                       "l2": f"inputs larger than L2: {sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9:.2f} GB of distinct weights per step vs 126 MB L2, no flush needed",
                        "launch": ("CUDA graph replay" if graph is not None else "eager launches through the C ABI") +
                                  (f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
@@ -453,6 +479,8 @@ def run_gpu(args):
             out["decode_batch"] = decode_batch
         if prefill:
             out["prefill"] = prefill
+        if prefill_rs:
+            out["prefill_rowsplit"] = prefill_rs
         if moe:
             out["moe"] = moe
         if world == 1 and args.cpu_seconds > 0:
@@ -497,6 +525,77 @@ def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):
                         "frac_of_hbm_peak": round(step_bytes / step_us / 1e3 / peak, 4), "tok_per_s_matmul_only": round(n * 1e6 / step_us, 1),
                         "per_shape": per}
     return res
+
+
+def prefill_rowsplit_bench(torch, dist, pkg, ctx, stream, rank, world, local, n=512):
+    """BASELINE configs[4] at prefill size: every Q4_K matrix of the model row-split over the ranks, n = 512 tokens.  Product
+    path: the tcgen05 GEMM's epilogue stores its tiles into every rank's full-height output through NVLink peer mappings
+    (b200_mul_mat_gather) + one symmetric-memory barrier.  Baseline beside it: the same GEMM + NCCL all_gather of the shards.
+    Device-timed (CUDA events), max over ranks."""
+    import torch.distributed._symmetric_memory as symm_mem
+    gen = torch.Generator(device="cuda"); gen.manual_seed(555 + rank)
+    shapes = {}
+    for _, m, k, c in LLAMA3_8B:
+        shapes[(m, k)] = shapes.get((m, k), 0) + c
+    maxm = max(m for m, _ in shapes)
+    ybuf = symm_mem.empty(n * maxm, dtype=torch.float32, device=torch.device("cuda", local))
+    hdl = symm_mem.rendezvous(ybuf, dist.group.WORLD)
+    ptrs = [int(p) for p in hdl.buffer_ptrs]
+    out, tot_fused, tot_nccl, flops = {"n_tokens": n}, 0.0, 0.0, 0.0
+    checked = False
+    for (m, k), count in sorted(shapes.items()):
+        rows = m // world
+        W = device_random_q4k(torch, rows, k, gen)
+        xg = torch.Generator(device="cuda"); xg.manual_seed(999 + k)
+        X = torch.randn((n, k), device="cuda", generator=xg)
+        ysh = torch.empty((n, rows), device="cuda")
+        gat = torch.empty((world, n, rows), device="cuda")
+
+        def fused():
+            pkg.mul_mat_gather(ctx, Q4_K, W, X, ysh, ptrs, m, rank * rows)
+            hdl.barrier(channel=0)
+
+        def nccl():
+            pkg.mul_mat(ctx, Q4_K, W, X, out=ysh)
+            dist.all_gather_into_tensor(gat, ysh)
+
+        res = []
+        with torch.cuda.stream(stream):
+            for fn in (fused, nccl):
+                fn(); fn()
+                stream.synchronize(); dist.barrier()
+                iters = 5
+                g = torch.cuda.CUDAGraph()                   # graph replay: the small shapes would otherwise time the host
+                with torch.cuda.graph(g, stream=stream):
+                    for _ in range(iters):
+                        fn()
+                g.replay()
+                stream.synchronize(); dist.barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                g.replay(); g.replay()
+                e1.record(stream)
+                stream.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) * 1e3 / (2 * iters)], device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                res.append(float(t))
+                del g
+            if not checked:
+                # the fused gather == the NCCL gather, bit for bit (every rank's slice, on every rank)
+                fused(); nccl(); stream.synchronize()
+                full = ybuf[: n * m].view(n, m)
+                for r in range(world):
+                    assert torch.equal(full[:, r * rows:(r + 1) * rows], gat[r]), "fused prefill row-split gather differs from NCCL all_gather"
+                checked = True
+        f = 2.0 * m * n * k
+        out[f"{m}x{k}"] = {"fused_us": round(res[0], 1), "nccl_us": round(res[1], 1), "tflops_fused": round(f / res[0] / 1e6, 1)}
+        tot_fused += res[0] * count; tot_nccl += res[1] * count; flops += f * count
+        del W, ysh, gat
+    out["ms_per_step_fused"] = round(tot_fused / 1e3, 3)
+    out["ms_per_step_nccl"] = round(tot_nccl / 1e3, 3)
+    out["tflops_fused_whole_job"] = round(flops / tot_fused / 1e6, 1)
+    out["tok_per_s_matmul_only"] = round(n * 1e6 / tot_fused, 1)
+    return out
 
 
 def moe_bench(torch, pkg, ctx, stream):
@@ -649,9 +748,14 @@ def main():
     ap.add_argument("--gather-sync", default="ll", choices=["ll", "barrier", "flags"], help="N > 1: how a matmul's gather is completed")
     ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
+    ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b: Llama-3-70B shapes (BASELINE configs[4], row split); skips the extra sections")
     ap.add_argument("--no-extras", action="store_true", help="skip the n=2..8 decode and the MoE (MUL_MAT_ID) sections")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    select_model(args.model)
+    if args.model != "8b":
+        args.no_extras = args.no_e2e = True
+        args.cpu_seconds = 0.0
     if args.impl == "reference":
         run_reference(args)
     else:

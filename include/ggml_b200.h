@@ -167,7 +167,8 @@ B200_API int  b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor *
 /* MUL_MAT on this rank's row shard `a` (rows [dst_row0, dst_row0 + a->ne[1]) of the full matrix) with the all-gather of
  * the output fused into the kernel's stores: every result also goes to dst[p][col * dst_m + dst_row0 + row] for the
  * n_dst (<= 8) full-height outputs `dst` — peer-mapped pointers (CUDA IPC / symmetric memory over NVLink), normally one
- * per rank including this one.  n <= 8 columns (decode).  The multi-process counterpart of b200_rowsplit_mul_mat mode 1;
+ * per rank including this one.  n <= 8 columns: GEMV family; n > 8 (prefill): the tcgen05 GEMM's epilogue stores its tiles
+ * to the peers (completion = the caller's barrier; the in-kernel protocols below are for decode).  The multi-process counterpart of b200_rowsplit_mul_mat mode 1;
  * replaces the per-device dst copies of the reference's row-split driver (ggml/src/ggml-cuda/ggml-cuda.cu:2030-2119). */
 B200_API int  b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d_shard,
                                   int n_dst, float * const * dst, int64_t dst_m, int64_t dst_row0);

@@ -358,10 +358,12 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
             aligned16(a->data, a->nb[1], a->nb[2], a->nb[3]) && aligned16(b->data, b->nb[1], b->nb[2], b->nb[3]) &&
             b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
-            // 2..8 columns: integer tensor-core GEMV (mmvq_mma.cu), except where the dp4a kernel's smaller fixed cost still wins
-            // (measured, us dp4a / mma: 1024x4096 n=2 2.9 / 4.4, n=4 4.4 / 4.7; 4096x4096 n=2 6.9 / 8.3, n=4 10.5 / 8.8;
-            //  14336x4096 n=2 12.9 / 12.3; everything at n=8 2-3.5x faster on the tensor cores); use_mma = 2 forces it
-            const bool mma_pays = ctx->use_mma == 2 || (n == 2 ? m * k >= (int64_t) 48 << 20 : (n <= 4 ? m * k >= (int64_t) 8 << 20 : true));
+            // 3..8 columns: integer tensor-core GEMV (mmvq_mma.cu).  n = 2 stays on the dp4a kernel, whose smaller fixed cost wins on
+            // the decoder-layer shapes (us dp4a / mma at n = 2: 1024x4096 2.9 / 4.3, 4096x4096 7.0 / 8.2, 14336x4096 13.0 / 12.3,
+            // output head 75 / 69; at n = 4: 4.5 / 4.6, 10.5 / 8.8, 19.6 / 12.7, 113 / 70; n = 8: 2-3.5x faster everywhere).
+            // The choice must not depend on m: a row shard has to run the same arithmetic as the whole matrix (row split).
+            // use_mma = 2 forces the tensor-core kernel.
+            const bool mma_pays = ctx->use_mma == 2 || n >= 3;
             if (n >= 2 && ctx->use_mma && mma_pays && !(n_peers > 0 && ctx->gs_world > 0) && b200_gemv_q4k_mma_ok(ctx, P)) {
                 const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
                 pending_push(ctx, d, !late);
@@ -383,8 +385,10 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         return b200_launch_gemv_generic(ctx, a->type, P, (int) n, batches);
     }
     pending_push(ctx, d, true);
+    if (n_peers > 0 && ctx->gs_world > 0) { b200_set_error("mul_mat_gather: the in-kernel completion protocol is for n <= 8; use a barrier for prefill"); return B200_E_UNSUPPORTED; }
 
-    if (n_peers == 0 && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
+    if ((n_peers == 0 || batches == 1) && ctx->use_tc && !ctx->force_generic && b200_tc_supported(ctx, a->type, P)) {
+        // (row split: the tcgen05 epilogue stores every tile into all peers' full-height outputs as well)
         const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, n * batches, 0));
         if (rc) return rc;
         return b200_launch_gemm_tc(ctx, a->type, P, n * batches, 0);
@@ -585,7 +589,7 @@ static int grow(b200_ctx * ctx, void ** buf, size_t * have, size_t want) {
 int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d_shard,
                         int n_dst, float * const * dst, int64_t dst_m, int64_t dst_row0) {
     if (!ctx || !b || n_dst < 1 || !dst) { b200_set_error("mul_mat_gather: bad argument"); return B200_E_ARG; }
-    if (b->ne[1] > ctx->max_gemv_cols || b->ne[1] > 8) { b200_set_error("mul_mat_gather: n <= 8 columns only"); return B200_E_UNSUPPORTED; }
+    // n <= 8: GEMV family; n > 8: tcgen05 GEMM (both store to the peers from their epilogues); completion is the caller's barrier
     if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
     return b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
 }

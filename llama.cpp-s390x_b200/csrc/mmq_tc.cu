@@ -82,6 +82,11 @@ struct tc_args {
     int     grid;               // persistent CTAs
     int     split_k;            // K parts per tile (1, 2 or 4); the parts of a tile are summed in ascending K order
     int32_t * tile_sync;        //    through these per-(tile, lane quadrant) turnstiles (zeroed per launch)
+    // row split: the all-gather of the output rows is fused into the epilogue — every result also goes to
+    // peer_Y[p][col * peer_m + peer_row0 + row] of each GPU (peer-mapped pointers, own GPU included if listed)
+    int     n_peers;
+    float * peer_Y[8];
+    int64_t peer_m, peer_row0;
 };
 
 // ---- activations: f32 -> normalised fp16, K order (0,2,1,3) inside every group of 4 -------------------------------------
@@ -628,7 +633,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
                         const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
-                        if (c0 + c < t.nvalid && row < t.m) t.Y[(int64_t) yc * t.m + row] = __uint_as_float(v[c]) * sc;
+                        if (c0 + c < t.nvalid && row < t.m) {
+                            const float r = __uint_as_float(v[c]) * sc;
+                            t.Y[(int64_t) yc * t.m + row] = r;
+                            if (a.n_peers > 0) {
+#pragma unroll 1
+                                for (int p = 0; p < a.n_peers; ++p) a.peer_Y[p][(int64_t) yc * a.peer_m + a.peer_row0 + row] = r;
+                            }
+                        }
                     }
                 } else {
                     // add to the earlier parts' sum with fire-and-forget reductions (no load round trip); the turnstile orders
@@ -869,7 +881,9 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     // on timing.  (Measured and rejected: stream-K with equal runs per CTA — loses the L2 sharing, no gain.)
     // ctx->tc_split_k: 0 = never, 1 = auto, 2 / 4 = forced
     a.split_k = 1;
-    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0 && !pl.pair) {
+    a.n_peers = P.n_peers; a.peer_m = P.peer_m; a.peer_row0 = P.peer_row0;
+    for (int p = 0; p < P.n_peers; ++p) a.peer_Y[p] = P.peer_Y[p];
+    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0 && !pl.pair && P.n_peers == 0) {
         auto eff = [&](int64_t sk) {
             const int64_t items = pl.n_tiles * sk, waves = (items + ctx->sm_count - 1) / ctx->sm_count;
             return (double) items / (double) (waves * ctx->sm_count);

@@ -192,6 +192,8 @@ def test_tc_gemm_close_to_f64_truth_and_to_cuda_core_path(pkg, gpu_ctx, orc, nam
     closer than the Q8_1-quantised reference gets — and (b) our CUDA-core path that follows ggml-cpu's Q8_1 arithmetic"""
     from tests.util import oracle_mul_mat_f64
     t = TYPES[name]
+    if name == "q6_K" and k % 2048:
+        pytest.skip("Q6_K rows of this length are not 16-byte aligned: CUDA-core path (covered by test_gemm_vs_oracle)")
     rng = np.random.default_rng(7 * n + m)
     W = random_blocks(t, m, k, rng)
     X = rng.standard_normal((n, k)).astype(np.float32)
