@@ -581,11 +581,14 @@ def prefill_rowsplit_bench(torch, dist, pkg, ctx, stream, rank, world, local, n=
                 res.append(float(t))
                 del g
             if not checked:
-                # the fused gather == the NCCL gather, bit for bit (every rank's slice, on every rank)
+                # the fused gather == the NCCL gather on every rank, for every rank's slice (to fp32 re-association: the unfused
+                # GEMM may split long K in two, the fused one does not)
                 fused(); nccl(); stream.synchronize()
                 full = ybuf[: n * m].view(n, m)
                 for r in range(world):
-                    assert torch.equal(full[:, r * rows:(r + 1) * rows], gat[r]), "fused prefill row-split gather differs from NCCL all_gather"
+                    a_, b_ = full[:, r * rows:(r + 1) * rows].double(), gat[r].double()
+                    err = float(((a_ - b_) ** 2).sum() / (b_ ** 2).sum().clamp_min(1e-300))
+                    assert err < 1e-10, f"fused prefill row-split gather differs from NCCL all_gather (nmse {err:.3e})"
                 checked = True
         f = 2.0 * m * n * k
         out[f"{m}x{k}"] = {"fused_us": round(res[0], 1), "nccl_us": round(res[1], 1), "tflops_fused": round(f / res[0] / 1e6, 1)}
