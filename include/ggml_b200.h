@@ -100,7 +100,8 @@ B200_API int   b200_ctx_synchronize(b200_ctx * ctx);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 B200_API int64_t b200_ctx_launch_count(const b200_ctx * ctx);
 /* tuning knobs (also read once from the GGML_B200_* environment): name in
- * {"force_generic","use_tc","max_gemv_cols","pdl"}; returns the previous value or B200_E_ARG */
+ * {"force_generic","use_tc","max_gemv_cols","pdl","fuse_quant","defer_wait","gemv_cfg","use_mma","mma_min_n","mma_ks","mma_ch",
+ *  "tc_pair","tc_nt","tc_split_k","noop"}; returns the previous value or B200_E_ARG */
 B200_API int   b200_ctx_set_option(b200_ctx * ctx, const char * name, int value);
 
 /* ---- (1) activation quantizer ------------------------------------------------------------------- */

@@ -14,8 +14,8 @@
 int    b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles);
 int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait);
 size_t b200_gemv_q4k_smem(int nc, int64_t k);
-int    b200_gemv_q4k_mma_ok(const b200_ctx * ctx, const mm_problem & P);
-int    b200_launch_gemv_q4k_mma(b200_ctx * ctx, const mm_problem & P, int64_t tiles, bool late_wait, int64_t live_tiles = 0);
+int    b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P);
+int    b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & P, int64_t tiles, bool late_wait, int64_t live_tiles = 0);
 int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
@@ -121,6 +121,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->use_mma       = env_int("GGML_B200_USE_MMA", 1);
     ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
     ctx->mma_ch        = env_int("GGML_B200_MMA_CH", 0);
+    ctx->mma_min_n     = env_int("GGML_B200_MMA_MIN_N", 1);
     ctx->tc_split_k   = env_int("GGML_B200_TC_SPLIT_K", 1);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
@@ -167,6 +168,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "use_mma"))       slot = &ctx->use_mma;
     else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;
     else if (!strcmp(name, "mma_ch"))        slot = &ctx->mma_ch;
+    else if (!strcmp(name, "mma_min_n"))     slot = &ctx->mma_min_n;
     else if (!strcmp(name, "tc_split_k"))   slot = &ctx->tc_split_k;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
@@ -364,10 +366,10 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
             // The choice must not depend on m: a row shard has to run the same arithmetic as the whole matrix (row split).
             // use_mma = 2 forces the tensor-core kernel.
             const bool mma_pays = ctx->use_mma == 2 || n >= 3;
-            if (n >= 2 && ctx->use_mma && mma_pays && !(n_peers > 0 && ctx->gs_world > 0) && b200_gemv_q4k_mma_ok(ctx, P)) {
+            if (n >= 2 && ctx->use_mma && mma_pays && !(n_peers > 0 && ctx->gs_world > 0) && b200_gemv_mma_ok(ctx, B200_TYPE_Q4_K, P)) {
                 const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
                 pending_push(ctx, d, !late);
-                return b200_launch_gemv_q4k_mma(ctx, P, batches, late);
+                return b200_launch_gemv_mma(ctx, B200_TYPE_Q4_K, P, batches, late);
             }
             const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
             pending_push(ctx, d, !late);
@@ -379,6 +381,13 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
             return b200_launch_gemv_q4k(ctx, P, (int) n, batches, late);
         }
         if (n_peers > 0 && ctx->gs_world > 0) { b200_set_error("mul_mat_gather: the completion protocol needs the fused Q4_K GEMV"); return B200_E_UNSUPPORTED; }
+        // Q8_0 / Q4_0: tensor-core GEMV (mmvq_mma.cu) from ctx->mma_min_n columns on (the choice depends on n only, see above)
+        if ((a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_0) && ctx->use_mma && !ctx->force_generic && ctx->fuse_quant &&
+            n >= ctx->mma_min_n && batches <= 65535 && b200_gemv_mma_ok(ctx, a->type, P)) {
+            const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
+            pending_push(ctx, d, !late);
+            return b200_launch_gemv_mma(ctx, a->type, P, batches, late);
+        }
         pending_push(ctx, d, true);
         int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
         if (rc) return rc;
@@ -442,7 +451,7 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
         // expert's weights are read once however many of the tokens chose it (the per-pair GEMV below reads them once per pair:
         // faster per byte, 5.1 vs 4.3 TB/s, so it keeps the batches in which few pairs share an expert)
         P.mode = MM_ID_SORTED;
-        if (b200_gemv_q4k_mma_ok(ctx, P)) {
+        if (b200_gemv_mma_ok(ctx, B200_TYPE_Q4_K, P)) {
             pending_push(ctx, c, true);
             const size_t ids_bytes = (size_t) (n_pairs + n_expert + 1) * sizeof(int32_t);
             int rc = b200_ctx_reserve(ctx, ids_bytes);
@@ -452,7 +461,7 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
             rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
             if (rc) return rc;
             P.ids_src1 = ids_src1; P.expert_bounds = bounds;
-            return b200_launch_gemv_q4k_mma(ctx, P, (n_pairs + 7) / 8 + n_expert, false, n_pairs < n_expert ? n_pairs : n_expert);
+            return b200_launch_gemv_mma(ctx, B200_TYPE_Q4_K, P, (n_pairs + 7) / 8 + n_expert, false, n_pairs < n_expert ? n_pairs : n_expert);
         }
     }
     if (n_tokens <= ctx->max_gemv_cols && n_pairs <= 65535) {

@@ -39,6 +39,20 @@ __device__ __forceinline__ act_unit load_act(const q8_planes & A, int64_t col, i
     return u;
 }
 
+// N consecutive 32-bit words from a 2-byte aligned address: N + 1 aligned word loads + funnel shifts (the block formats are
+// only 2-byte aligned; two 16-bit loads per word cost twice the load instructions — the generic kernel is issue-bound).
+// Reads up to 2 bytes past the last word when the address is 4-byte aligned (tensor rows are padded, ggml-cuda.cu:802-816 contract).
+template <int N>
+__device__ __forceinline__ void ldw_b2(const uint8_t * p, uint32_t (&out)[N]) {
+    const uint32_t * a  = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t) 3);
+    const uint32_t   sh = ((uint32_t) reinterpret_cast<uintptr_t>(p) & 2u) * 8u;
+    uint32_t w[N + 1];
+#pragma unroll
+    for (int i = 0; i <= N; ++i) w[i] = __ldg(a + i);
+#pragma unroll
+    for (int i = 0; i < N; ++i) out[i] = __funnelshift_r(w[i], w[i + 1], sh);
+}
+
 // weights of one 32-element unit, unpacked to int8x4 words + the floats needed to scale the integer sums
 template <int TYPE> struct w_unit;
 
@@ -47,11 +61,12 @@ template <> struct w_unit<B200_TYPE_Q4_0> {
     __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
         const uint8_t * bp = row + ib * SZ_Q4_0;
         d = ld_half(bp);
+        uint32_t q[4];
+        ldw_b2<4>(bp + 2, q);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint32_t v = ld_b2(bp + 2 + 4 * i);
-            lo[i] = v & 0x0F0F0F0Fu;
-            hi[i] = (v >> 4) & 0x0F0F0F0Fu;
+            lo[i] = q[i] & 0x0F0F0F0Fu;
+            hi[i] = (q[i] >> 4) & 0x0F0F0F0Fu;
         }
     }
     __device__ __forceinline__ float dot(const act_unit & u) const {
@@ -67,8 +82,10 @@ template <> struct w_unit<B200_TYPE_Q8_0> {
     __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
         const uint8_t * bp = row + ib * SZ_Q8_0;
         d = ld_half(bp);
+        uint32_t q[8];
+        ldw_b2<8>(bp + 2, q);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = (int) ld_b2(bp + 2 + 4 * i);
+        for (int i = 0; i < 8; ++i) v[i] = (int) q[i];
     }
     __device__ __forceinline__ float dot(const act_unit & u) const {
         int sumi = 0;
@@ -116,10 +133,13 @@ template <> struct w_unit<B200_TYPE_Q6_K> {
         d0 = d * (float) (int8_t) (scs & 0xff);
         d1 = d * (float) (int8_t) (scs >> 8);
         const int shl = 4 * (r >> 1), shh = 2 * r;
+        uint32_t lw[8], hw[8];
+        ldw_b2<8>(ql, lw);
+        ldw_b2<8>(qh, hw);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const uint32_t l = (ld_b2(ql + 4 * i) >> shl) & 0x0F0F0F0Fu;
-            const uint32_t h = ((ld_b2(qh + 4 * i) >> shh) & 0x03030303u) << 4;
+            const uint32_t l = (lw[i] >> shl) & 0x0F0F0F0Fu;
+            const uint32_t h = ((hw[i] >> shh) & 0x03030303u) << 4;
             v[i] = __vsubss4(l | h, 0x20202020);
         }
     }

@@ -31,6 +31,7 @@
 //     for every KS, grid size and row sharding (the row-split parity property), and never depends on timing.
 #include <cuda.h>
 #include "mm_problem.cuh"
+#include "quantize.cuh"
 #include "tc_ptx.cuh"
 
 namespace {
@@ -38,10 +39,19 @@ namespace {
 constexpr int MW        = 16;                  // warps per CTA
 constexpr int RB        = 16;                  // weight rows per warp task (MMA M)
 constexpr int MAX_STAGE = 8;
-constexpr int OFF_BAR   = 64, OFF_PART = 1152, OFF_D = OFF_PART + 2 * MW * 128 * 4;      // shared-memory map (bytes)
-__host__ __device__ constexpr size_t mma_off_q(int64_t k)    { return (size_t) ((OFF_D + (k / 256) * 32 + 127) / 128 * 128); }
-__host__ __device__ constexpr size_t mma_off_ring(int64_t k) { return mma_off_q(k) + (size_t) 8 * (k + 32); }
 constexpr int COL_PAD   = 32;                  // int8 column stride = k + 32
+constexpr int OFF_BAR   = 64, OFF_PART = 1152, OFF_D = OFF_PART + 2 * MW * 128 * 4;      // shared-memory map (bytes)
+
+// per weight type: bytes of one 256-value step of a row (the TMA box is `ch` of them wide), and how many values share one
+// activation scale (256 like the reference's Q8_K for the K-quants, 32 like its Q8_0 / Q8_1 for the 32-blocks)
+template <int TYPE> struct mma_geo;
+template <> struct mma_geo<B200_TYPE_Q4_K> { static constexpr int STEP_B = SZ_Q4_K,     ACT_BLK = 256; };
+template <> struct mma_geo<B200_TYPE_Q4_0> { static constexpr int STEP_B = 8 * SZ_Q4_0, ACT_BLK = 32;  };    // 144
+template <> struct mma_geo<B200_TYPE_Q8_0> { static constexpr int STEP_B = 8 * SZ_Q8_0, ACT_BLK = 32;  };    // 272
+__host__ __device__ constexpr int mma_step_b(int type)  { return type == B200_TYPE_Q8_0 ? 8 * SZ_Q8_0 : SZ_Q4_K; }
+__host__ __device__ constexpr int mma_act_blk(int type) { return type == B200_TYPE_Q4_K ? 256 : 32; }
+__host__ __device__ constexpr size_t mma_off_q(int64_t k, int type)    { return (size_t) ((OFF_D + (k / mma_act_blk(type)) * 32 + 127) / 128 * 128); }
+__host__ __device__ constexpr size_t mma_off_ring(int64_t k, int type) { return mma_off_q(k, type) + (size_t) 8 * (k + 32); }
 
 __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
@@ -51,6 +61,24 @@ __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, 
 __device__ __forceinline__ void mma_u8s8_z(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
                  : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+__device__ __forceinline__ void mma_s8s8_z(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+__device__ __forceinline__ uint32_t lds_u1(const uint32_t a) {
+    uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v;
+}
+__device__ __forceinline__ float lds_h(const uint32_t a) {           // fp16 scale of a 32-block
+    uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return __half2float(__ushort_as_half(v));
+}
+// 4 / 8 bytes from a shared-memory address that is 2 mod 4 (fields of the 18- and 34-byte blocks)
+__device__ __forceinline__ uint32_t lds4_odd(const uint32_t a) {
+    return __byte_perm(lds_u1(a - 2), lds_u1(a + 2), 0x5432);
+}
+__device__ __forceinline__ uint2 lds8_odd(const uint32_t a) {
+    const uint32_t w0 = lds_u1(a - 2), w1 = lds_u1(a + 2), w2 = lds_u1(a + 6);
+    return make_uint2(__byte_perm(w0, w1, 0x5432), __byte_perm(w1, w2, 0x5432));
 }
 __device__ __forceinline__ uint2 lds_u2(const uint32_t a) {
     uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v;
@@ -102,6 +130,100 @@ struct step_cursor {
     }
 };
 
+// ---- one 256-value step of 16 rows: st_a = the step's bytes of row 0 in the stage, r0off / r1off = offsets of this lane's two
+// rows, bq_sb = this lane's B bytes of the step (column g, + 8 t), sd_sb = activation scales of columns 2t, 2t+1 for the step ----
+template <int TYPE> struct mma_step;
+
+template <> struct mma_step<B200_TYPE_Q4_K> {
+    static __device__ __forceinline__ void run(const uint32_t st_a, const uint32_t r0off, const uint32_t r1off, const int t,
+                                               const uint32_t bq_sb, const uint32_t sd_sb, float (&pf)[4]) {
+                        const uint4 h0 = lds_u4(st_a + r0off), h1 = lds_u4(st_a + r1off);
+                        // 6-bit scales / mins of the 8 sub-blocks as bytes (get_scale_min_k4, ggml/src/ggml-quants.c:818-825)
+                        const uint32_t sc0[2] = {h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | ((h0.y >> 2) & 0x30303030u)};
+                        const uint32_t mn0[2] = {h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | ((h0.z >> 2) & 0x30303030u)};
+                        const uint32_t sc1[2] = {h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | ((h1.y >> 2) & 0x30303030u)};
+                        const uint32_t mn1[2] = {h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | ((h1.z >> 2) & 0x30303030u)};
+                        int al[4] = {0, 0, 0, 0}, ah[4] = {0, 0, 0, 0}, cm[4] = {0, 0, 0, 0};
+                        const uint32_t bsb = bq_sb;
+        #pragma unroll
+                        for (int jj = 0; jj < 4; ++jj) {
+                            const uint2 w0 = lds_u2(st_a + r0off + 16 + 32 * jj + 8 * t), w1 = lds_u2(st_a + r1off + 16 + 32 * jj + 8 * t);
+        #pragma unroll
+                            for (int hi = 0; hi < 2; ++hi) {
+                                const int j = 2 * jj + hi;
+                                const uint2 b = lds_u2(bsb + 32 * j);
+                                const uint32_t mask = hi ? 0xF0F0F0F0u : 0x0F0F0F0Fu;      // high nibbles stay in place: 16 q, undone below
+                                int c[4];
+                                mma_u8s8_z(c, w0.x & mask, w1.x & mask, w0.y & mask, w1.y & mask, b.x, b.y);
+                                const int s0 = (int) __byte_perm(sc0[j >> 2], 0u, 0x4440u + (j & 3));
+                                const int s1 = (int) __byte_perm(sc1[j >> 2], 0u, 0x4440u + (j & 3));
+                                if (hi) { ah[0] += c[0] * s0; ah[1] += c[1] * s0; ah[2] += c[2] * s1; ah[3] += c[3] * s1; }
+                                else    { al[0] += c[0] * s0; al[1] += c[1] * s0; al[2] += c[2] * s1; al[3] += c[3] * s1; }
+                                const uint32_t m0 = __byte_perm(mn0[j >> 2], 0u, 0x1111u * (j & 3));
+                                const uint32_t m1 = __byte_perm(mn1[j >> 2], 0u, 0x1111u * (j & 3));
+                                mma_u8s8(cm, m0, m1, m0, m1, b.x, b.y);
+                            }
+                        }
+                        const uint2  d8u = lds_u2(sd_sb);
+                        const float  d8a = __uint_as_float(d8u.x), d8b = __uint_as_float(d8u.y);
+                        const float2 dm0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));
+                        const float2 dm1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
+                        pf[0] += d8a * (dm0.x * (float) (al[0] + (ah[0] >> 4)) - dm0.y * (float) cm[0]);
+                        pf[1] += d8b * (dm0.x * (float) (al[1] + (ah[1] >> 4)) - dm0.y * (float) cm[1]);
+                        pf[2] += d8a * (dm1.x * (float) (al[2] + (ah[2] >> 4)) - dm1.y * (float) cm[2]);
+                        pf[3] += d8b * (dm1.x * (float) (al[3] + (ah[3] >> 4)) - dm1.y * (float) cm[3]);
+    }
+};
+
+// Q8_0 (block_q8_0, ggml-common.h:241-246): 8 blocks of {fp16 d; int8 qs[32]} per step; block j of a row sits at 34 j (its qs at
+// 34 j + 2: 4-byte aligned for odd j only).  Per block: one s8 x s8 MMA, then y += float(sum) * d_w * d_x like
+// ggml_vec_dot_q8_0_q8_0 (ggml-cpu/quants.c:400-428) with the same per-32 activation scale.
+template <> struct mma_step<B200_TYPE_Q8_0> {
+    static __device__ __forceinline__ void run(const uint32_t st_a, const uint32_t r0off, const uint32_t r1off, const int t,
+                                               const uint32_t bq_sb, const uint32_t sd_sb, float (&pf)[4]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t a0 = st_a + r0off + 34 * j, a1 = st_a + r1off + 34 * j;
+            uint2 w0, w1;
+            if (j & 1) { w0 = make_uint2(lds_u1(a0 + 2 + 8 * t), lds_u1(a0 + 6 + 8 * t)); w1 = make_uint2(lds_u1(a1 + 2 + 8 * t), lds_u1(a1 + 6 + 8 * t)); }
+            else       { w0 = lds8_odd(a0 + 2 + 8 * t); w1 = lds8_odd(a1 + 2 + 8 * t); }
+            const uint2 b = lds_u2(bq_sb + 32 * j);
+            int c[4];
+            mma_s8s8_z(c, w0.x, w1.x, w0.y, w1.y, b.x, b.y);
+            const float dw0 = lds_h(a0), dw1 = lds_h(a1);
+            const uint2 du = lds_u2(sd_sb + 32 * j);
+            const float da = __uint_as_float(du.x), db = __uint_as_float(du.y);
+            pf[0] += (float) c[0] * (dw0 * da); pf[1] += (float) c[1] * (dw0 * db);
+            pf[2] += (float) c[2] * (dw1 * da); pf[3] += (float) c[3] * (dw1 * db);
+        }
+    }
+};
+
+// Q4_0 (block_q4_0, ggml-common.h:184-189): 8 blocks of {fp16 d; u8 qs[16]} per step; byte i of a block holds value i (low nibble)
+// and value i + 16 (high nibble), each minus 8.  Lane t takes bytes 4t..4t+3: values 4t..4t+3 and 16+4t..16+4t+3 — the
+// activations are stored in that order, so B is again one LDS.64.
+template <> struct mma_step<B200_TYPE_Q4_0> {
+    static __device__ __forceinline__ void run(const uint32_t st_a, const uint32_t r0off, const uint32_t r1off, const int t,
+                                               const uint32_t bq_sb, const uint32_t sd_sb, float (&pf)[4]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t a0 = st_a + r0off + 18 * j, a1 = st_a + r1off + 18 * j;
+            const uint32_t w0 = (j & 1) ? lds_u1(a0 + 2 + 4 * t) : lds4_odd(a0 + 2 + 4 * t);
+            const uint32_t w1 = (j & 1) ? lds_u1(a1 + 2 + 4 * t) : lds4_odd(a1 + 2 + 4 * t);
+            const uint2 b = lds_u2(bq_sb + 32 * j);
+            int c[4];
+            mma_s8s8_z(c, __vsub4(w0 & 0x0F0F0F0Fu, 0x08080808u), __vsub4(w1 & 0x0F0F0F0Fu, 0x08080808u),
+                          __vsub4((w0 >> 4) & 0x0F0F0F0Fu, 0x08080808u), __vsub4((w1 >> 4) & 0x0F0F0F0Fu, 0x08080808u), b.x, b.y);
+            const float dw0 = lds_h(a0), dw1 = lds_h(a1);
+            const uint2 du = lds_u2(sd_sb + 32 * j);
+            const float da = __uint_as_float(du.x), db = __uint_as_float(du.y);
+            pf[0] += (float) c[0] * (dw0 * da); pf[1] += (float) c[1] * (dw0 * db);
+            pf[2] += (float) c[2] * (dw1 * da); pf[3] += (float) c[3] * (dw1 * db);
+        }
+    }
+};
+
+template <int TYPE>
 __global__ void __launch_bounds__(MW * 32, 1)
 gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const mma_args A) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -110,10 +232,11 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     // shared memory map
     float **  s_y    = reinterpret_cast<float **>(smem);                              // 8 output column pointers
     float *   s_part = reinterpret_cast<float *>(smem + OFF_PART);                    // [2][MW][128] K-slice partial sums
-    float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [nsb][8]
-    int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k));               // [8][k + 32]
-    const uint32_t stage_b = (uint32_t) A.ch * RB * SZ_Q4_K;                          // [MW][stages][16 rows][ch * 144]
-    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k) + (uint32_t) (warp * A.stages) * stage_b;
+    constexpr int STEP_B = mma_geo<TYPE>::STEP_B, ACT_BLK = mma_geo<TYPE>::ACT_BLK;
+    float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [k / ACT_BLK][8] activation scales
+    int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k, TYPE));         // [8][k + 32]
+    const uint32_t stage_b = (uint32_t) A.ch * RB * STEP_B;                           // [MW][stages][16 rows][ch * STEP_B]
+    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE) + (uint32_t) (warp * A.stages) * stage_b;
     const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
 
     if (tid == 0) tc::tma_prefetch_desc(&tmW);
@@ -137,7 +260,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
         const uint32_t bar = bar0 + 8 * stage;
         if (tc::elect_one()) {
             tc::mbar_arrive_expect_tx(bar, stage_b);
-            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (SZ_Q4_K / 2), (int) (c.rb * RB), mat);
+            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (STEP_B / 2), (int) (c.rb * RB), mat);
         }
         __syncwarp();
     };
@@ -175,46 +298,79 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
         for (int c = 1; c < 8; ++c) if (tid == c) y = C.y[c];
         s_y[tid] = y;
     }
-    // (column, super-block) tasks: a warp takes 8 at a time and requests all their data before the first reduction, so the
-    // L2 round trips of a warp's tasks overlap instead of adding up (measured: +0.5 us per column before)
-    for (int task0 = warp; task0 < 8 * nsb; task0 += 8 * MW) {
-        float4 v0[8], v1[8];
+    if (ACT_BLK == 256) {
+        // (column, super-block) tasks: a warp takes 8 at a time and requests all their data before the first reduction, so the
+        // L2 round trips of a warp's tasks overlap instead of adding up (measured: +0.5 us per column before)
+        for (int task0 = warp; task0 < 8 * nsb; task0 += 8 * MW) {
+            float4 v0[8], v1[8];
+    #pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int task = task0 + i * MW;
+                const int col = task / nsb, sb = task - col * nsb;
+                v0[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); v1[i] = v0[i];
+                if (task < 8 * nsb && col < C.nc) {
+                    const float * xc = C.x[0];
+    #pragma unroll
+                    for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
+                    const float4 * src = reinterpret_cast<const float4 *>(xc + sb * 256 + lane * 8);
+                    v0[i] = __ldg(src); v1[i] = __ldg(src + 1);
+                }
+            }
+    #pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int task = task0 + i * MW;
+                if (task >= 8 * nsb) break;
+                const int col = task / nsb, sb = task - col * nsb;
+                uint2 packed = make_uint2(0u, 0u);
+                float d8 = 0.0f;
+                float amax = fmaxf(fmaxf(fmaxf(fabsf(v0[i].x), fabsf(v0[i].y)), fmaxf(fabsf(v0[i].z), fabsf(v0[i].w))),
+                                   fmaxf(fmaxf(fabsf(v1[i].x), fabsf(v1[i].y)), fmaxf(fabsf(v1[i].z), fabsf(v1[i].w))));
+    #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                if (amax > 0.0f) {
+                    const float is = __fdiv_rn(127.0f, amax);
+                    d8 = __fdiv_rn(1.0f, is);
+                    const int q0 = __float2int_rn(__fmul_rn(is, v0[i].x)), q1 = __float2int_rn(__fmul_rn(is, v0[i].y));
+                    const int q2 = __float2int_rn(__fmul_rn(is, v0[i].z)), q3 = __float2int_rn(__fmul_rn(is, v0[i].w));
+                    const int q4 = __float2int_rn(__fmul_rn(is, v1[i].x)), q5 = __float2int_rn(__fmul_rn(is, v1[i].y));
+                    const int q6 = __float2int_rn(__fmul_rn(is, v1[i].z)), q7 = __float2int_rn(__fmul_rn(is, v1[i].w));
+                    packed.x = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) | ((uint32_t) (q3 & 0xff) << 24);
+                    packed.y = (uint32_t) (q4 & 0xff) | ((uint32_t) (q5 & 0xff) << 8) | ((uint32_t) (q6 & 0xff) << 16) | ((uint32_t) (q7 & 0xff) << 24);
+                }
+                *reinterpret_cast<uint2 *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
+                if (lane == 0) s_d[sb * 8 + col] = d8;
+            }
+        }
+    } else {
+        // per-32 scales, the values of quantize_row_q8_1_ref (ggml-quants.c:260-293): 8 lanes per block, 8 blocks per lane in
+        // flight.  Q4_0 stores the 8 words of a block in the order (0, 4, 1, 5, 2, 6, 3, 7) — what its nibble layout pairs up.
+        const int nbk = k >> 5, total = C.nc * nbk, sub = lane & 7;
+        for (int i = tid; i < (8 - C.nc) * nbk; i += MW * 32) {          // dead columns: scale 0 (their int8 values are never used)
+            const int col = C.nc + i / nbk, ib = i - (i / nbk) * nbk;
+            s_d[ib * 8 + col] = 0.0f;
+        }
+        for (int blk0 = tid >> 3; blk0 < total; blk0 += 8 * MW * 4) {     // warp-uniform trip count: total is a multiple of 8
+            float4 v[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int task = task0 + i * MW;
-            const int col = task / nsb, sb = task - col * nsb;
-            v0[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); v1[i] = v0[i];
-            if (task < 8 * nsb && col < C.nc) {
+            for (int i = 0; i < 8; ++i) {
+                const int blk = blk0 + i * MW * 4, bb = blk < total ? blk : total - 1;
+                const int col = bb / nbk, ib = bb - col * nbk;
                 const float * xc = C.x[0];
 #pragma unroll
                 for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
-                const float4 * src = reinterpret_cast<const float4 *>(xc + sb * 256 + lane * 8);
-                v0[i] = __ldg(src); v1[i] = __ldg(src + 1);
+                v[i] = __ldg(reinterpret_cast<const float4 *>(xc + ib * 32 + sub * 4));
             }
-        }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int task = task0 + i * MW;
-            if (task >= 8 * nsb) break;
-            const int col = task / nsb, sb = task - col * nsb;
-            uint2 packed = make_uint2(0u, 0u);
-            float d8 = 0.0f;
-            float amax = fmaxf(fmaxf(fmaxf(fabsf(v0[i].x), fabsf(v0[i].y)), fmaxf(fabsf(v0[i].z), fabsf(v0[i].w))),
-                               fmaxf(fmaxf(fabsf(v1[i].x), fabsf(v1[i].y)), fmaxf(fabsf(v1[i].z), fabsf(v1[i].w))));
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            if (amax > 0.0f) {
-                const float is = __fdiv_rn(127.0f, amax);
-                d8 = __fdiv_rn(1.0f, is);
-                const int q0 = __float2int_rn(__fmul_rn(is, v0[i].x)), q1 = __float2int_rn(__fmul_rn(is, v0[i].y));
-                const int q2 = __float2int_rn(__fmul_rn(is, v0[i].z)), q3 = __float2int_rn(__fmul_rn(is, v0[i].w));
-                const int q4 = __float2int_rn(__fmul_rn(is, v1[i].x)), q5 = __float2int_rn(__fmul_rn(is, v1[i].y));
-                const int q6 = __float2int_rn(__fmul_rn(is, v1[i].z)), q7 = __float2int_rn(__fmul_rn(is, v1[i].w));
-                packed.x = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) | ((uint32_t) (q3 & 0xff) << 24);
-                packed.y = (uint32_t) (q4 & 0xff) | ((uint32_t) (q5 & 0xff) << 8) | ((uint32_t) (q6 & 0xff) << 16) | ((uint32_t) (q7 & 0xff) << 24);
+            for (int i = 0; i < 8; ++i) {
+                const int blk = blk0 + i * MW * 4, bb = blk < total ? blk : total - 1;
+                const int col = bb / nbk, ib = bb - col * nbk;
+                const q8_part qp = quantize_q8_1_part(v[i]);
+                if (blk < total) {
+                    const int w = TYPE == B200_TYPE_Q4_0 ? (sub < 4 ? 2 * sub : 2 * (sub - 4) + 1) : sub;
+                    *reinterpret_cast<uint32_t *>(s_q + (size_t) col * (k + COL_PAD) + ib * 32 + 4 * w) = qp.packed;
+                    if (sub == 0) s_d[ib * 8 + col] = qp.d;
+                }
             }
-            *reinterpret_cast<uint2 *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
-            if (lane == 0) s_d[sb * 8 + col] = d8;
         }
     }
     __syncthreads();
@@ -228,7 +384,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     // half-warp (4 row groups x 4 lanes x 8 B) must hit 32 distinct banks: stride 72 words = 8 mod 32 works with rho = g,
     // stride 36 words = 4 mod 32 needs the rows of a half-warp two apart
     const int      rho   = A.ch == 1 ? 2 * (g & 3) + (g >> 2) : g;
-    const uint32_t rstr  = (uint32_t) A.ch * SZ_Q4_K;
+    const uint32_t rstr  = (uint32_t) A.ch * STEP_B;
     const uint32_t r0off = (uint32_t) rho * rstr, r1off = (uint32_t) (rho + 8) * rstr;
     int      c_stage = 0;
     uint32_t c_phase = 0;
@@ -250,42 +406,8 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
               float pf[4] = {0.0f, 0.0f, 0.0f, 0.0f};
               for (int sb = nsb * lf / 16; sb < nsb * (lf + 1) / 16; ++sb) {
                 if (in_chunk == 0) tc::mbar_wait(bar0 + 8 * c_stage, c_phase);
-                const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * SZ_Q4_K;
-                const uint4 h0 = lds_u4(st_a + r0off), h1 = lds_u4(st_a + r1off);
-                // 6-bit scales / mins of the 8 sub-blocks as bytes (get_scale_min_k4, ggml/src/ggml-quants.c:818-825)
-                const uint32_t sc0[2] = {h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | ((h0.y >> 2) & 0x30303030u)};
-                const uint32_t mn0[2] = {h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | ((h0.z >> 2) & 0x30303030u)};
-                const uint32_t sc1[2] = {h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | ((h1.y >> 2) & 0x30303030u)};
-                const uint32_t mn1[2] = {h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | ((h1.z >> 2) & 0x30303030u)};
-                int al[4] = {0, 0, 0, 0}, ah[4] = {0, 0, 0, 0}, cm[4] = {0, 0, 0, 0};
-                const uint32_t bsb = bq + 256u * sb;
-#pragma unroll
-                for (int jj = 0; jj < 4; ++jj) {
-                    const uint2 w0 = lds_u2(st_a + r0off + 16 + 32 * jj + 8 * t), w1 = lds_u2(st_a + r1off + 16 + 32 * jj + 8 * t);
-#pragma unroll
-                    for (int hi = 0; hi < 2; ++hi) {
-                        const int j = 2 * jj + hi;
-                        const uint2 b = lds_u2(bsb + 32 * j);
-                        const uint32_t mask = hi ? 0xF0F0F0F0u : 0x0F0F0F0Fu;      // high nibbles stay in place: 16 q, undone below
-                        int c[4];
-                        mma_u8s8_z(c, w0.x & mask, w1.x & mask, w0.y & mask, w1.y & mask, b.x, b.y);
-                        const int s0 = (int) __byte_perm(sc0[j >> 2], 0u, 0x4440u + (j & 3));
-                        const int s1 = (int) __byte_perm(sc1[j >> 2], 0u, 0x4440u + (j & 3));
-                        if (hi) { ah[0] += c[0] * s0; ah[1] += c[1] * s0; ah[2] += c[2] * s1; ah[3] += c[3] * s1; }
-                        else    { al[0] += c[0] * s0; al[1] += c[1] * s0; al[2] += c[2] * s1; al[3] += c[3] * s1; }
-                        const uint32_t m0 = __byte_perm(mn0[j >> 2], 0u, 0x1111u * (j & 3));
-                        const uint32_t m1 = __byte_perm(mn1[j >> 2], 0u, 0x1111u * (j & 3));
-                        mma_u8s8(cm, m0, m1, m0, m1, b.x, b.y);
-                    }
-                }
-                const uint2  d8u = lds_u2(sd + 32u * sb);
-                const float  d8a = __uint_as_float(d8u.x), d8b = __uint_as_float(d8u.y);
-                const float2 dm0 = __half22float2(*reinterpret_cast<const __half2 *>(&h0.x));
-                const float2 dm1 = __half22float2(*reinterpret_cast<const __half2 *>(&h1.x));
-                pf[0] += d8a * (dm0.x * (float) (al[0] + (ah[0] >> 4)) - dm0.y * (float) cm[0]);
-                pf[1] += d8b * (dm0.x * (float) (al[1] + (ah[1] >> 4)) - dm0.y * (float) cm[1]);
-                pf[2] += d8a * (dm1.x * (float) (al[2] + (ah[2] >> 4)) - dm1.y * (float) cm[2]);
-                pf[3] += d8b * (dm1.x * (float) (al[3] + (ah[3] >> 4)) - dm1.y * (float) cm[3]);
+                const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * STEP_B;
+                mma_step<TYPE>::run(st_a, r0off, r1off, t, bq + 256u * sb, sd + (uint32_t) (256 / ACT_BLK) * 32u * sb, pf);
                 if (++in_chunk == A.ch || sb == sb_last) {
                     // the stage has been read (values are in registers): hand it to the next fill
                     in_chunk = 0;
@@ -350,8 +472,8 @@ static encode_tiled_fn mma_get_encode() {
     return fn;
 }
 
-// shared memory for k values per column with `stages` ring slots of `ch` super-blocks per warp
-static size_t mma_smem(int64_t k, int stages, int ch) { return mma_off_ring(k) + (size_t) MW * stages * ch * RB * SZ_Q4_K; }
+// shared memory for k values per column with `stages` ring slots of `ch` steps per warp
+static size_t mma_smem(int type, int64_t k, int stages, int ch) { return mma_off_ring(k, type) + (size_t) MW * stages * ch * RB * mma_step_b(type); }
 
 // number of weight matrices behind P.W (batches / experts), or 0 when they are not equally spaced
 static int64_t mma_nmat(const mm_problem & P) {
@@ -361,9 +483,11 @@ static int64_t mma_nmat(const mm_problem & P) {
     return ne02 * ne03;
 }
 
-int b200_gemv_q4k_mma_ok(const b200_ctx * ctx, const mm_problem & P) {
-    if (P.k % 256 != 0 || P.k > (1 << 24) || P.m > (1 << 30) || !mma_get_encode()) return 0;
-    if (mma_smem(P.k, 2, 1) > ctx->smem_optin) return 0;
+static bool mma_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
+
+int b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P) {
+    if (!mma_type_ok(type) || P.k % 256 != 0 || P.k > (1 << 24) || P.m > (1 << 30) || !mma_get_encode()) return 0;
+    if (mma_smem(type, P.k, 2, 1) > ctx->smem_optin) return 0;
     // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
     if (((uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03) & 15) return 0;
     const int64_t nmat = mma_nmat(P);
@@ -372,11 +496,22 @@ int b200_gemv_q4k_mma_ok(const b200_ctx * ctx, const mm_problem & P) {
     return 1;
 }
 
+template <int TYPE>
+static int mma_launch_t(b200_ctx * ctx, const cudaLaunchConfig_t & cfg, const CUtensorMap & tmw, const mm_problem & P, const mma_args & A) {
+    static bool attr_done[16] = {};
+    if (!attr_done[ctx->device & 15]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_mma<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
+        attr_done[ctx->device & 15] = true;
+    }
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_q4k_mma<TYPE>, tmw, P, A));
+    return B200_OK;
+}
+
 // f32 activations in P.X (quantized in the kernel prologue); up to 8 columns per tile (MM_PLAIN: ceil(ne11 / 8) tiles per batch)
 // live_tiles: how many of the tiles are expected to have work (MM_ID_SORTED launches an upper bound; 0 = all)
-int b200_launch_gemv_q4k_mma(b200_ctx * ctx, const mm_problem & Pin, int64_t tiles, bool late_wait, int64_t live_tiles) {
+int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64_t tiles, bool late_wait, int64_t live_tiles) {
     if (tiles <= 0 || Pin.m <= 0) return B200_OK;
-    if (tiles > 65535) { b200_set_error("gemv_q4k_mma: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
+    if (tiles > 65535) { b200_set_error("gemv_mma: %lld tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }
     mm_problem P = Pin;
     const int64_t nmat = mma_nmat(P);
     if (nmat <= 1) P.nb02 = 0;                    // the kernel derives the matrix index from (W of the tile - P.W) / nb02
@@ -389,47 +524,49 @@ int b200_launch_gemv_q4k_mma(b200_ctx * ctx, const mm_problem & Pin, int64_t til
     int ks = 1;
     while (ks < MW && 4 * nrb * ks < 3 * ctas * MW && nsb / (2 * ks) >= 1) ks *= 2;      // measured best: the first ks with ~one unit per warp
     if (ctx->mma_ks > 0) ks = ctx->mma_ks;
-    if (ks != 1 && ks != 2 && ks != 4 && ks != 8 && ks != 16) { b200_set_error("gemv_q4k_mma: K slices must be 1, 2, 4, 8 or 16"); return B200_E_ARG; }
+    if (ks != 1 && ks != 2 && ks != 4 && ks != 8 && ks != 16) { b200_set_error("gemv_mma: K slices must be 1, 2, 4, 8 or 16"); return B200_E_ARG; }
     mma_args A = {};
     A.ks = ks;
     A.late = ctx->pdl && late_wait ? 1 : 0;
-    // super-blocks per stage: 2 when every K slice is a whole number of pairs
-    A.ch = (nsb % (2 * ks) == 0) ? 2 : 1;
+    // steps per stage: 2 when every K slice is a whole number of pairs (the 272-byte Q8_0 step exceeds the 256-element box: 1)
+    const int step_b = mma_step_b(type);
+    A.ch = (nsb % (2 * ks) == 0 && step_b * 2 / 2 <= 256) ? 2 : 1;
     if (ctx->mma_ch == 1) A.ch = 1;
     int stages = MAX_STAGE;
-    while (stages > 1 && mma_smem(P.k, stages, A.ch) > ctx->smem_optin) --stages;
+    while (stages > 1 && mma_smem(type, P.k, stages, A.ch) > ctx->smem_optin) --stages;
     if (stages < 2 && A.ch == 2) { A.ch = 1; stages = 2; }
-    if (mma_smem(P.k, stages, A.ch) > ctx->smem_optin) { b200_set_error("gemv_q4k_mma: k = %lld needs too much shared memory", (long long) P.k); return B200_E_ARG; }
+    if (mma_smem(type, P.k, stages, A.ch) > ctx->smem_optin) { b200_set_error("gemv_mma: k = %lld needs too much shared memory", (long long) P.k); return B200_E_ARG; }
     A.stages = stages;
 
-    // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 16 rows x ch super-blocks
+    // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 16 rows x ch steps
     CUtensorMap tmw;
     const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) P.m, (cuuint64_t) (nmat > 1 ? nmat : 1)};
     const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (nmat > 1 ? P.nb02 : P.nb01 * P.m)};
-    const cuuint32_t wbox[3]    = {(cuuint32_t) (A.ch * SZ_Q4_K / 2), (cuuint32_t) RB, 1};
+    const cuuint32_t wbox[3]    = {(cuuint32_t) (A.ch * step_b / 2), (cuuint32_t) RB, 1};
     const cuuint32_t westr[3]   = {1, 1, 1};
     const CUresult wr = mma_get_encode()(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) P.W, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (wr != CUDA_SUCCESS) { b200_set_error("gemv_q4k_mma: cuTensorMapEncodeTiled failed (%d)", (int) wr); return B200_E_CUDA; }
+    if (wr != CUDA_SUCCESS) { b200_set_error("gemv_mma: cuTensorMapEncodeTiled failed (%d)", (int) wr); return B200_E_CUDA; }
 
-    static bool attr_done[16] = {};
-    if (!attr_done[ctx->device & 15]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
-        attr_done[ctx->device & 15] = true;
-    }
     const int64_t max_useful = (nrb * ks + MW - 1) / MW;
     if (ctas > max_useful) ctas = max_useful;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) ctas, (unsigned) tiles);
     cfg.blockDim         = dim3(MW * 32);
-    cfg.dynamicSmemBytes = mma_smem(P.k, stages, A.ch);
+    cfg.dynamicSmemBytes = mma_smem(type, P.k, stages, A.ch);
     cfg.stream           = ctx->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
     cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_q4k_mma, tmw, P, A));
-    ctx->launches++;
-    return B200_OK;
+    int rc = B200_E_UNSUPPORTED;
+    switch (type) {
+        case B200_TYPE_Q4_K: rc = mma_launch_t<B200_TYPE_Q4_K>(ctx, cfg, tmw, P, A); break;
+        case B200_TYPE_Q4_0: rc = mma_launch_t<B200_TYPE_Q4_0>(ctx, cfg, tmw, P, A); break;
+        case B200_TYPE_Q8_0: rc = mma_launch_t<B200_TYPE_Q8_0>(ctx, cfg, tmw, P, A); break;
+        default: b200_set_error("gemv_mma: unsupported weight type %d", type);
+    }
+    if (rc == B200_OK) ctx->launches++;
+    return rc;
 }

@@ -127,6 +127,38 @@ def test_q4k_tensor_core_gemv(pkg, gpu_ctx, orc, n, shape):
     assert nmse(oracle_mul_mat_f64(orc, refenv.Q4_K, W, X), got) <= NMSE_TOL
 
 
+@pytest.mark.parametrize("name", ["q8_0", "q4_0"])
+@pytest.mark.parametrize("n", [1, 3, 8])
+@pytest.mark.parametrize("shape", [(96, 512), (257, 4096), (1030, 2048)])
+def test_tensor_core_gemv_32_blocks(pkg, gpu_ctx, orc, name, n, shape):
+    """mmvq_mma.cu for the 32-value block types (per-32 activation scales = the Q8_1 values): against the oracle, against the
+    CUDA-core kernel that follows the same algebra (fp32 re-association only), and invariant under K slicing / row sharding"""
+    import torch
+    m, k = shape
+    t = TYPES[name]
+    rng = np.random.default_rng(zlib.crc32(repr(("mma32", name, n, shape)).encode()))
+    W = random_blocks(t, m, k, rng)
+    X = rng.standard_normal((n, k)).astype(np.float32)
+    Wd, Xd = dev(W), dev(X)
+    gpu_ctx.set_option("mma_min_n", 1)
+    try:
+        got = pkg.mul_mat(gpu_ctx, t, Wd, Xd)
+        for ks in (1, 4, 16):
+            gpu_ctx.set_option("mma_ks", ks)
+            assert torch.equal(got, pkg.mul_mat(gpu_ctx, t, Wd, Xd)), ks
+        gpu_ctx.set_option("mma_ks", 0)
+        lo, hi = m // 3, m // 3 + max(1, m // 2)
+        assert torch.equal(pkg.mul_mat(gpu_ctx, t, Wd[lo:hi].contiguous(), Xd), got[:, lo:hi])
+        gpu_ctx.set_option("use_mma", 0)
+        core = pkg.mul_mat(gpu_ctx, t, Wd, Xd).cpu().numpy()
+    finally:
+        gpu_ctx.set_option("use_mma", 1); gpu_ctx.set_option("mma_ks", 0); gpu_ctx.set_option("mma_min_n", 1)
+    got = got.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert nmse(core, got) < 1e-6           # same integers, fp32 d of the activation blocks vs their fp16 rounding in the planes
+    assert nmse(oracle_mul_mat(orc, t, W, X), got) <= NMSE_TOL
+
+
 def test_q4k_tensor_core_gemv_batches_and_zero_columns(pkg, gpu_ctx, orc):
     """batch dims with broadcast (several weight matrices behind one tensor map) and an all-zero activation column"""
     rng = np.random.default_rng(77)
