@@ -381,8 +381,8 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
             return b200_launch_gemv_q4k(ctx, P, (int) n, batches, late);
         }
         if (n_peers > 0 && ctx->gs_world > 0) { b200_set_error("mul_mat_gather: the completion protocol needs the fused Q4_K GEMV"); return B200_E_UNSUPPORTED; }
-        // Q8_0 / Q4_0: tensor-core GEMV (mmvq_mma.cu) from ctx->mma_min_n columns on (the choice depends on n only, see above)
-        if ((a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_0) && ctx->use_mma && !ctx->force_generic && ctx->fuse_quant &&
+        // Q8_0 / Q4_0 / Q6_K: tensor-core GEMV (mmvq_mma.cu) from ctx->mma_min_n columns on (the choice depends on n only, see above)
+        if ((a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_0 || a->type == B200_TYPE_Q6_K) && ctx->use_mma && !ctx->force_generic && ctx->fuse_quant &&
             n >= ctx->mma_min_n && batches <= 65535 && b200_gemv_mma_ok(ctx, a->type, P)) {
             const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
             pending_push(ctx, d, !late);

@@ -45,11 +45,14 @@ constexpr int OFF_BAR   = 64, OFF_PART = 1152, OFF_D = OFF_PART + 2 * MW * 128 *
 // per weight type: bytes of one 256-value step of a row (the TMA box is `ch` of them wide), and how many values share one
 // activation scale (256 like the reference's Q8_K for the K-quants, 32 like its Q8_0 / Q8_1 for the 32-blocks)
 template <int TYPE> struct mma_geo;
-template <> struct mma_geo<B200_TYPE_Q4_K> { static constexpr int STEP_B = SZ_Q4_K,     ACT_BLK = 256; };
-template <> struct mma_geo<B200_TYPE_Q4_0> { static constexpr int STEP_B = 8 * SZ_Q4_0, ACT_BLK = 32;  };    // 144
-template <> struct mma_geo<B200_TYPE_Q8_0> { static constexpr int STEP_B = 8 * SZ_Q8_0, ACT_BLK = 32;  };    // 272
-__host__ __device__ constexpr int mma_step_b(int type)  { return type == B200_TYPE_Q8_0 ? 8 * SZ_Q8_0 : SZ_Q4_K; }
-__host__ __device__ constexpr int mma_act_blk(int type) { return type == B200_TYPE_Q4_K ? 256 : 32; }
+// (STEP_B = bytes of a step in global memory, BOX_B = bytes of its TMA box / shared-memory row: Q6_K's 210-byte super-blocks are
+//  fetched from the 16-byte boundary below them, 2 (sb mod 8) bytes early, in a 224-byte box)
+template <> struct mma_geo<B200_TYPE_Q4_K> { static constexpr int STEP_B = SZ_Q4_K,     BOX_B = SZ_Q4_K,     ACT_BLK = 256; };
+template <> struct mma_geo<B200_TYPE_Q4_0> { static constexpr int STEP_B = 8 * SZ_Q4_0, BOX_B = 8 * SZ_Q4_0, ACT_BLK = 32;  };    // 144
+template <> struct mma_geo<B200_TYPE_Q8_0> { static constexpr int STEP_B = 8 * SZ_Q8_0, BOX_B = 8 * SZ_Q8_0, ACT_BLK = 32;  };    // 272
+template <> struct mma_geo<B200_TYPE_Q6_K> { static constexpr int STEP_B = SZ_Q6_K,     BOX_B = 224,         ACT_BLK = 256; };
+__host__ __device__ constexpr int mma_step_b(int type)  { return type == B200_TYPE_Q8_0 ? 8 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? 224 : SZ_Q4_K); }   // box bytes
+__host__ __device__ constexpr int mma_act_blk(int type) { return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K) ? 256 : 32; }
 __host__ __device__ constexpr size_t mma_off_q(int64_t k, int type)    { return (size_t) ((OFF_D + (k / mma_act_blk(type)) * 32 + 127) / 128 * 128); }
 __host__ __device__ constexpr size_t mma_off_ring(int64_t k, int type) { return mma_off_q(k, type) + (size_t) 8 * (k + 32); }
 
@@ -65,6 +68,17 @@ __device__ __forceinline__ void mma_u8s8_z(int (&c)[4], uint32_t a0, uint32_t a1
 __device__ __forceinline__ void mma_s8s8_z(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%10, %10, %10, %10};"
                  : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+__device__ __forceinline__ void mma16_s8s8_z(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%7, %7, %7, %7};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]) : "r"(a0), "r"(a1), "r"(b0), "r"(0));
+}
+// sign-extended byte of x: SEL0 selects byte b (selector b + (8 | b) * 0x1110), `next` = 1 takes byte b + 1 instead
+template <int SEL0> __device__ __forceinline__ int sext_byte(const uint32_t x, const int next) {
+    int r;
+    if (next) asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0), "n"(SEL0 + 0x1111));
+    else      asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(0), "n"(SEL0));
+    return r;
 }
 __device__ __forceinline__ uint32_t lds_u1(const uint32_t a) {
     uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v;
@@ -223,6 +237,68 @@ template <> struct mma_step<B200_TYPE_Q4_0> {
     }
 };
 
+// Q6_K (block_q6_K, ggml-common.h:352-358; layout dequantize_row_q6_K, ggml-quants.c:1877-1906): value l of 32-group r of half n is
+// (nibble r>>1 of ql[64n + 32(r&1) + l]) | (bits 2r, 2r+1 of qh[32n + l]) << 4, minus 32, times the int8 scale sc[8n + 2r + l/16].
+// One s8 x s8 MMA (K = 16) per scale group; sum_j sc_j * (group sum) stays in int32 like ggml_vec_dot_q6_K_q8_K
+// (ggml-cpu/quants.c:800-853).  Lane t takes bytes 4t..4t+3 of every 16-byte run; the activations of a 32-group are stored in the
+// word order (0, 4, 1, 5, 2, 6, 3, 7), so B for the two scale groups of (n, r) is one LDS.64.  The super-block is only 2-byte
+// aligned in its shared-memory row: ODD = its address is 2 mod 4 (every field offset used here is a multiple of 4).
+template <> struct mma_step<B200_TYPE_Q6_K> {
+    template <bool ODD> static __device__ __forceinline__ uint32_t ld(const uint32_t a) { return ODD ? lds4_odd(a) : lds_u1(a); }
+    template <int R> static __device__ __forceinline__ uint32_t q6(const uint32_t la, const uint32_t lb, const uint32_t h) {
+        const uint32_t lo = R == 0 ? la : (R == 1 ? lb : (R == 2 ? la >> 4 : lb >> 4));
+        const uint32_t hi = R == 0 ? h << 4 : (R == 1 ? h << 2 : (R == 2 ? h : h >> 2));
+        return __vsub4((lo & 0x0F0F0F0Fu) | (hi & 0x30303030u), 0x20202020u);
+    }
+    template <bool ODD, int R>
+    static __device__ __forceinline__ void group(const uint32_t (&la0)[2], const uint32_t (&lb0)[2], const uint32_t (&h0)[2], const uint32_t (&la1)[2],
+                                                 const uint32_t (&lb1)[2], const uint32_t (&h1)[2], const uint32_t (&scw0)[4], const uint32_t (&scw1)[4],
+                                                 const int n, const uint32_t bq_sb, int (&acc)[4]) {
+        const uint2 b = lds_u2(bq_sb + 128 * n + 32 * R);
+#pragma unroll
+        for (int is = 0; is < 2; ++is) {
+            const int j = 8 * n + 2 * R + is;
+            int c[4];
+            mma16_s8s8_z(c, q6<R>(la0[is], lb0[is], h0[is]), q6<R>(la1[is], lb1[is], h1[is]), is ? b.y : b.x);
+            // sign-extended byte j & 3 (prmt with the sign-replicate bit; the __byte_perm intrinsic drops that bit)
+            const int s0 = sext_byte<0x8880 + 0x1110 * (R & 1) * 2 + (R & 1) * 2>(scw0[j >> 2], is);
+            const int s1 = sext_byte<0x8880 + 0x1110 * (R & 1) * 2 + (R & 1) * 2>(scw1[j >> 2], is);
+            acc[0] += c[0] * s0; acc[1] += c[1] * s0; acc[2] += c[2] * s1; acc[3] += c[3] * s1;
+        }
+    }
+    template <bool ODD>
+    static __device__ __forceinline__ void run_t(const uint32_t R0, const uint32_t R1, const int t, const uint32_t bq_sb, const uint32_t sd_sb, float (&pf)[4]) {
+        uint32_t scw0[4], scw1[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { scw0[i] = ld<ODD>(R0 + 192 + 4 * i); scw1[i] = ld<ODD>(R1 + 192 + 4 * i); }
+        int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+            uint32_t la0[2], lb0[2], h0[2], la1[2], lb1[2], h1[2];
+#pragma unroll
+            for (int is = 0; is < 2; ++is) {
+                la0[is] = ld<ODD>(R0 + 64 * n + 16 * is + 4 * t);      la1[is] = ld<ODD>(R1 + 64 * n + 16 * is + 4 * t);
+                lb0[is] = ld<ODD>(R0 + 64 * n + 32 + 16 * is + 4 * t); lb1[is] = ld<ODD>(R1 + 64 * n + 32 + 16 * is + 4 * t);
+                h0[is]  = ld<ODD>(R0 + 128 + 32 * n + 16 * is + 4 * t); h1[is] = ld<ODD>(R1 + 128 + 32 * n + 16 * is + 4 * t);
+            }
+            group<ODD, 0>(la0, lb0, h0, la1, lb1, h1, scw0, scw1, n, bq_sb, acc);
+            group<ODD, 1>(la0, lb0, h0, la1, lb1, h1, scw0, scw1, n, bq_sb, acc);
+            group<ODD, 2>(la0, lb0, h0, la1, lb1, h1, scw0, scw1, n, bq_sb, acc);
+            group<ODD, 3>(la0, lb0, h0, la1, lb1, h1, scw0, scw1, n, bq_sb, acc);
+        }
+        const float d0 = lds_h(R0 + 208), d1 = lds_h(R1 + 208);
+        const uint2 du = lds_u2(sd_sb);
+        const float da = __uint_as_float(du.x), db = __uint_as_float(du.y);
+        pf[0] += da * (d0 * (float) acc[0]); pf[1] += db * (d0 * (float) acc[1]);
+        pf[2] += da * (d1 * (float) acc[2]); pf[3] += db * (d1 * (float) acc[3]);
+    }
+    static __device__ __forceinline__ void run(const uint32_t st_a, const uint32_t r0off, const uint32_t r1off, const int t,
+                                               const uint32_t bq_sb, const uint32_t sd_sb, float (&pf)[4]) {
+        if (st_a & 2u) run_t<true>(st_a + r0off, st_a + r1off, t, bq_sb, sd_sb, pf);       // warp-uniform
+        else           run_t<false>(st_a + r0off, st_a + r1off, t, bq_sb, sd_sb, pf);
+    }
+};
+
 template <int TYPE>
 __global__ void __launch_bounds__(MW * 32, 1)
 gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const mma_args A) {
@@ -232,10 +308,10 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     // shared memory map
     float **  s_y    = reinterpret_cast<float **>(smem);                              // 8 output column pointers
     float *   s_part = reinterpret_cast<float *>(smem + OFF_PART);                    // [2][MW][128] K-slice partial sums
-    constexpr int STEP_B = mma_geo<TYPE>::STEP_B, ACT_BLK = mma_geo<TYPE>::ACT_BLK;
+    constexpr int STEP_B = mma_geo<TYPE>::STEP_B, BOX_B = mma_geo<TYPE>::BOX_B, ACT_BLK = mma_geo<TYPE>::ACT_BLK;
     float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [k / ACT_BLK][8] activation scales
     int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k, TYPE));         // [8][k + 32]
-    const uint32_t stage_b = (uint32_t) A.ch * RB * STEP_B;                           // [MW][stages][16 rows][ch * STEP_B]
+    const uint32_t stage_b = (uint32_t) A.ch * RB * BOX_B;                            // [MW][stages][16 rows][ch * BOX_B]
     const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE) + (uint32_t) (warp * A.stages) * stage_b;
     const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
 
@@ -260,7 +336,8 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
         const uint32_t bar = bar0 + 8 * stage;
         if (tc::elect_one()) {
             tc::mbar_arrive_expect_tx(bar, stage_b);
-            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (STEP_B / 2), (int) (c.rb * RB), mat);
+            // (Q6_K: the box starts at the 16-byte boundary below the super-block, 2 (sb mod 8) bytes = (sb mod 8) elements early)
+            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (STEP_B / 2) - (TYPE == B200_TYPE_Q6_K ? (c.sb & 7) : 0), (int) (c.rb * RB), mat);
         }
         __syncwarp();
     };
@@ -337,7 +414,14 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
                     packed.x = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) | ((uint32_t) (q3 & 0xff) << 24);
                     packed.y = (uint32_t) (q4 & 0xff) | ((uint32_t) (q5 & 0xff) << 8) | ((uint32_t) (q6 & 0xff) << 16) | ((uint32_t) (q7 & 0xff) << 24);
                 }
+                if (TYPE == B200_TYPE_Q6_K) {
+                // words (2 lane, 2 lane + 1) of the super-block; inside their 32-group the word order is (0, 4, 1, 5, 2, 6, 3, 7)
+                const int w0 = 2 * (lane & 3), p0 = w0 < 4 ? 2 * w0 : 2 * (w0 - 4) + 1;       // w0 + 1 lands at p0 + 2
+                uint32_t * blk = reinterpret_cast<uint32_t *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + (lane >> 2) * 32);
+                blk[p0] = packed.x; blk[p0 + 2] = packed.y;
+            } else {
                 *reinterpret_cast<uint2 *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
+            }
                 if (lane == 0) s_d[sb * 8 + col] = d8;
             }
         }
@@ -384,7 +468,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     // half-warp (4 row groups x 4 lanes x 8 B) must hit 32 distinct banks: stride 72 words = 8 mod 32 works with rho = g,
     // stride 36 words = 4 mod 32 needs the rows of a half-warp two apart
     const int      rho   = A.ch == 1 ? 2 * (g & 3) + (g >> 2) : g;
-    const uint32_t rstr  = (uint32_t) A.ch * STEP_B;
+    const uint32_t rstr  = (uint32_t) A.ch * BOX_B;
     const uint32_t r0off = (uint32_t) rho * rstr, r1off = (uint32_t) (rho + 8) * rstr;
     int      c_stage = 0;
     uint32_t c_phase = 0;
@@ -406,7 +490,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
               float pf[4] = {0.0f, 0.0f, 0.0f, 0.0f};
               for (int sb = nsb * lf / 16; sb < nsb * (lf + 1) / 16; ++sb) {
                 if (in_chunk == 0) tc::mbar_wait(bar0 + 8 * c_stage, c_phase);
-                const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * STEP_B;
+                const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * BOX_B + (TYPE == B200_TYPE_Q6_K ? 2u * (sb & 7) : 0u);
                 mma_step<TYPE>::run(st_a, r0off, r1off, t, bq + 256u * sb, sd + (uint32_t) (256 / ACT_BLK) * 32u * sb, pf);
                 if (++in_chunk == A.ch || sb == sb_last) {
                     // the stage has been read (values are in registers): hand it to the next fill
@@ -483,7 +567,7 @@ static int64_t mma_nmat(const mm_problem & P) {
     return ne02 * ne03;
 }
 
-static bool mma_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0; }
+static bool mma_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
 
 int b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (!mma_type_ok(type) || P.k % 256 != 0 || P.k > (1 << 24) || P.m > (1 << 30) || !mma_get_encode()) return 0;
@@ -530,7 +614,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
     A.late = ctx->pdl && late_wait ? 1 : 0;
     // steps per stage: 2 when every K slice is a whole number of pairs (the 272-byte Q8_0 step exceeds the 256-element box: 1)
     const int step_b = mma_step_b(type);
-    A.ch = (nsb % (2 * ks) == 0 && step_b * 2 / 2 <= 256) ? 2 : 1;
+    A.ch = (nsb % (2 * ks) == 0 && step_b <= 256 && type != B200_TYPE_Q6_K) ? 2 : 1;
     if (ctx->mma_ch == 1) A.ch = 1;
     int stages = MAX_STAGE;
     while (stages > 1 && mma_smem(type, P.k, stages, A.ch) > ctx->smem_optin) --stages;
@@ -565,6 +649,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
         case B200_TYPE_Q4_K: rc = mma_launch_t<B200_TYPE_Q4_K>(ctx, cfg, tmw, P, A); break;
         case B200_TYPE_Q4_0: rc = mma_launch_t<B200_TYPE_Q4_0>(ctx, cfg, tmw, P, A); break;
         case B200_TYPE_Q8_0: rc = mma_launch_t<B200_TYPE_Q8_0>(ctx, cfg, tmw, P, A); break;
+        case B200_TYPE_Q6_K: rc = mma_launch_t<B200_TYPE_Q6_K>(ctx, cfg, tmw, P, A); break;
         default: b200_set_error("gemv_mma: unsupported weight type %d", type);
     }
     if (rc == B200_OK) ctx->launches++;

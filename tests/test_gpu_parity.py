@@ -96,35 +96,37 @@ def test_q4k_fast_kernel_matches_generic_kernel(pkg, gpu_ctx, n):
     assert nmse(slow, fast) < (1e-6 if n == 1 else 3e-4)
 
 
-@pytest.mark.parametrize("n", [2, 3, 5, 8])
+@pytest.mark.parametrize("name", ["q4_K", "q6_K"])
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 8])
 @pytest.mark.parametrize("shape", [(96, 512), (257, 4096), (64, 14336), (4099, 2048)])
-def test_q4k_tensor_core_gemv(pkg, gpu_ctx, orc, n, shape):
+def test_k_quant_tensor_core_gemv(pkg, gpu_ctx, orc, name, n, shape):
     """mmvq_mma.cu (forced): against the oracle and the f64 truth; the result is bit-identical for every K slicing, ring
     geometry and row sharding (fixed summation tree) — the property the row-split path relies on"""
     import torch
     m, k = shape
-    rng = np.random.default_rng(zlib.crc32(repr(("mma", n, shape)).encode()))
-    W = random_blocks(refenv.Q4_K, m, k, rng)
+    t = TYPES[name]
+    rng = np.random.default_rng(zlib.crc32(repr(("mma", name, n, shape)).encode()))
+    W = random_blocks(t, m, k, rng)
     X = rng.standard_normal((n, k)).astype(np.float32)
     Wd, Xd = dev(W), dev(X)
     gpu_ctx.set_option("use_mma", 2)
     try:
-        got = pkg.mul_mat(gpu_ctx, refenv.Q4_K, Wd, Xd)
+        got = pkg.mul_mat(gpu_ctx, t, Wd, Xd)
         for ks in (1, 2, 4, 8, 16):
             gpu_ctx.set_option("mma_ks", ks)
-            assert torch.equal(got, pkg.mul_mat(gpu_ctx, refenv.Q4_K, Wd, Xd)), ks
+            assert torch.equal(got, pkg.mul_mat(gpu_ctx, t, Wd, Xd)), ks
         gpu_ctx.set_option("mma_ks", 0)
         gpu_ctx.set_option("mma_ch", 1)
-        assert torch.equal(got, pkg.mul_mat(gpu_ctx, refenv.Q4_K, Wd, Xd))
+        assert torch.equal(got, pkg.mul_mat(gpu_ctx, t, Wd, Xd))
         gpu_ctx.set_option("mma_ch", 0)
         lo, hi = m // 3, m // 3 + max(1, m // 2)
-        assert torch.equal(pkg.mul_mat(gpu_ctx, refenv.Q4_K, Wd[lo:hi].contiguous(), Xd), got[:, lo:hi])
+        assert torch.equal(pkg.mul_mat(gpu_ctx, t, Wd[lo:hi].contiguous(), Xd), got[:, lo:hi])
     finally:
         gpu_ctx.set_option("use_mma", 1); gpu_ctx.set_option("mma_ks", 0); gpu_ctx.set_option("mma_ch", 0)
     got = got.cpu().numpy()
     assert np.isfinite(got).all()
-    assert nmse(oracle_mul_mat(orc, refenv.Q4_K, W, X), got) <= NMSE_TOL
-    assert nmse(oracle_mul_mat_f64(orc, refenv.Q4_K, W, X), got) <= NMSE_TOL
+    assert nmse(oracle_mul_mat(orc, t, W, X), got) <= NMSE_TOL
+    assert nmse(oracle_mul_mat_f64(orc, t, W, X), got) <= NMSE_TOL
 
 
 @pytest.mark.parametrize("name", ["q8_0", "q4_0"])
