@@ -54,7 +54,7 @@ template <> struct mma_geo<B200_TYPE_Q6_K> { static constexpr int STEP_B = SZ_Q6
 __host__ __device__ constexpr int mma_step_b(int type)  { return type == B200_TYPE_Q8_0 ? 8 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? 224 : SZ_Q4_K); }   // box bytes
 __host__ __device__ constexpr int mma_act_blk(int type) { return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K) ? 256 : 32; }
 __host__ __device__ constexpr size_t mma_off_q(int64_t k, int type)    { return (size_t) ((OFF_D + (k / mma_act_blk(type)) * 32 + 127) / 128 * 128); }
-__host__ __device__ constexpr size_t mma_off_ring(int64_t k, int type) { return mma_off_q(k, type) + (size_t) 8 * (k + 32); }
+__host__ __device__ constexpr size_t mma_off_ring(int64_t k, int type, int ncol) { return (mma_off_q(k, type) + (size_t) ncol * (k + 32) + 127) / 128 * 128; }
 
 __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
@@ -105,6 +105,7 @@ struct mma_args {
     int ks;            // K slices per row block (1, 2, 4, 8 or 16)
     int stages;        // ring depth per warp
     int ch;            // super-blocks per stage (1 or 2)
+    int ncol;          // activation columns held in shared memory (1..8): long rows only fit with fewer than 8
     int late;          // X / ids are not written by a kernel that may still run: the dependency wait moves to just before the first
                        // store, and this kernel's prologue and streaming overlap the previous kernel's tail (see mmvq.cu / abi.cu)
 };
@@ -312,7 +313,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [k / ACT_BLK][8] activation scales
     int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k, TYPE));         // [8][k + 32]
     const uint32_t stage_b = (uint32_t) A.ch * RB * BOX_B;                            // [MW][stages][16 rows][ch * BOX_B]
-    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE) + (uint32_t) (warp * A.stages) * stage_b;
+    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE, A.ncol) + (uint32_t) (warp * A.stages) * stage_b;
     const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
 
     if (tid == 0) tc::tma_prefetch_desc(&tmW);
@@ -378,14 +379,14 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     if (ACT_BLK == 256) {
         // (column, super-block) tasks: a warp takes 8 at a time and requests all their data before the first reduction, so the
         // L2 round trips of a warp's tasks overlap instead of adding up (measured: +0.5 us per column before)
-        for (int task0 = warp; task0 < 8 * nsb; task0 += 8 * MW) {
+        for (int task0 = warp; task0 < A.ncol * nsb; task0 += 8 * MW) {
             float4 v0[8], v1[8];
     #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int task = task0 + i * MW;
                 const int col = task / nsb, sb = task - col * nsb;
                 v0[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); v1[i] = v0[i];
-                if (task < 8 * nsb && col < C.nc) {
+                if (task < A.ncol * nsb && col < C.nc) {
                     const float * xc = C.x[0];
     #pragma unroll
                     for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
@@ -396,7 +397,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int task = task0 + i * MW;
-                if (task >= 8 * nsb) break;
+                if (task >= A.ncol * nsb) break;
                 const int col = task / nsb, sb = task - col * nsb;
                 uint2 packed = make_uint2(0u, 0u);
                 float d8 = 0.0f;
@@ -462,7 +463,8 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
     bool waited = !A.late;
 
     // ---- main loop -------------------------------------------------------------------------------------------------------
-    const uint32_t bq = tc::smem_u32(s_q) + (uint32_t) g * (uint32_t) (k + COL_PAD) + 8u * t;   // column g, K bytes 8t..8t+7 of a sub-block
+    // (lanes of columns that are not held re-read the last one; those results are never stored)
+    const uint32_t bq = tc::smem_u32(s_q) + (uint32_t) (g < A.ncol ? g : A.ncol - 1) * (uint32_t) (k + COL_PAD) + 8u * t;   // column g, K bytes 8t..8t+7 of a sub-block
     const uint32_t sd = tc::smem_u32(s_d) + 8u * t;                                            // d8 of columns 2t, 2t+1
     // MMA row group g <-> rows rho, rho + 8 of the block: on the dense box (row stride 36 or 72 words) the LDS.64 of a
     // half-warp (4 row groups x 4 lanes x 8 B) must hit 32 distinct banks: stride 72 words = 8 mod 32 works with rho = g,
@@ -557,7 +559,7 @@ static encode_tiled_fn mma_get_encode() {
 }
 
 // shared memory for k values per column with `stages` ring slots of `ch` steps per warp
-static size_t mma_smem(int type, int64_t k, int stages, int ch) { return mma_off_ring(k, type) + (size_t) MW * stages * ch * RB * mma_step_b(type); }
+static size_t mma_smem(int type, int64_t k, int stages, int ch, int ncol) { return mma_off_ring(k, type, ncol) + (size_t) MW * stages * ch * RB * mma_step_b(type); }
 
 // number of weight matrices behind P.W (batches / experts), or 0 when they are not equally spaced
 static int64_t mma_nmat(const mm_problem & P) {
@@ -569,9 +571,12 @@ static int64_t mma_nmat(const mm_problem & P) {
 
 static bool mma_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
 
+// activation columns a tile can have: MUL_MAT n (<= 8), MUL_MAT_ID up to 8 pairs of an expert
+static int mma_ncol(const mm_problem & P) { return P.mode == MM_PLAIN ? (int) (P.ne11 < 8 ? P.ne11 : 8) : 8; }
+
 int b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (!mma_type_ok(type) || P.k % 256 != 0 || P.k > (1 << 24) || P.m > (1 << 30) || !mma_get_encode()) return 0;
-    if (mma_smem(type, P.k, 2, 1) > ctx->smem_optin) return 0;
+    if (mma_smem(type, P.k, 2, 1, mma_ncol(P)) > ctx->smem_optin) return 0;
     // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
     if (((uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03) & 15) return 0;
     const int64_t nmat = mma_nmat(P);
@@ -616,10 +621,11 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
     const int step_b = mma_step_b(type);
     A.ch = (nsb % (2 * ks) == 0 && step_b <= 256 && type != B200_TYPE_Q6_K) ? 2 : 1;
     if (ctx->mma_ch == 1) A.ch = 1;
+    A.ncol = mma_ncol(P);
     int stages = MAX_STAGE;
-    while (stages > 1 && mma_smem(type, P.k, stages, A.ch) > ctx->smem_optin) --stages;
+    while (stages > 1 && mma_smem(type, P.k, stages, A.ch, A.ncol) > ctx->smem_optin) --stages;
     if (stages < 2 && A.ch == 2) { A.ch = 1; stages = 2; }
-    if (mma_smem(type, P.k, stages, A.ch) > ctx->smem_optin) { b200_set_error("gemv_mma: k = %lld needs too much shared memory", (long long) P.k); return B200_E_ARG; }
+    if (mma_smem(type, P.k, stages, A.ch, A.ncol) > ctx->smem_optin) { b200_set_error("gemv_mma: k = %lld needs too much shared memory", (long long) P.k); return B200_E_ARG; }
     A.stages = stages;
 
     // raw weight blocks: [nmat][m][row bytes] seen as 16-bit elements, box = 16 rows x ch steps
@@ -637,7 +643,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim          = dim3((unsigned) ctas, (unsigned) tiles);
     cfg.blockDim         = dim3(MW * 32);
-    cfg.dynamicSmemBytes = mma_smem(type, P.k, stages, A.ch);
+    cfg.dynamicSmemBytes = mma_smem(type, P.k, stages, A.ch, A.ncol);
     cfg.stream           = ctx->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
