@@ -76,6 +76,18 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def measured_traffic(launches_per_step, world):
+    """dram__bytes_read + dram__bytes_write per launch (average over the step's launches) from the committed ncu launch list of
+    this command — only when the run has the same shape of step as the profiled one, else null"""
+    p = ROOT / "profiles" / "r01_traffic.json"
+    if world != 1 or not p.exists():
+        return None
+    d = json.loads(p.read_text())
+    if d.get("workload") != MODEL or d.get("launches_per_step") != launches_per_step:
+        return None
+    return d["dram_bytes_per_launch_avg"]
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region"""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
@@ -467,7 +479,7 @@ def run_gpu(args):
             "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(value / world, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(value / world / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "frac": round(value / world / peak, 4), "traffic": measured_traffic(launches_per_step, world), "peak_source": peak_src,
                          "kernel": f"gemv_q4k<1,32> (all {launches_per_step} launches of the step, {STEP_MATMULS} matmuls)",
                          "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / launches_per_step / world)},
         }
