@@ -43,7 +43,10 @@ template <int NT, bool PAIR = false, int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
     static constexpr int B_SLOTS = (PAIR ? (NT == 256 ? 6 : 8) : (NT == 256 ? 4 : 6)) - (RAW_ROW > TC_RAW_ROW ? 1 : 0);
     static constexpr int B_BYTES = B_ROWS * 128;
     static constexpr int RAW_BYTES = TC_M * RAW_ROW;
-    static constexpr int SMEM    = B_SLOTS * B_BYTES + TC_A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    // CTA pair: the halved activation tile pays for a deeper A ring — "A tile ready" now waits for the converters of two SMs and a
+    // remote arrive, which 3 slots (2 MMA stages of slack) do not cover
+    static constexpr int A_SLOTS = PAIR ? (RAW_ROW > TC_RAW_ROW ? 4 : 5) : TC_A_SLOTS;
+    static constexpr int SMEM    = B_SLOTS * B_BYTES + A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
     static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
     static_assert(SMEM <= 232448, "exceeds the 227 KB a CTA can opt into");
 };
@@ -409,7 +412,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     // drained" that gate them live in ITS shared memory; the peer's warps arrive there remotely.  "Slot free" and "accumulator
     // ready" barriers are per CTA, signalled in both by multicast commits.
     const uint32_t cta_rank = PAIR ? tc::cluster_ctarank() : 0u;
-    constexpr int BS  = cfg::B_SLOTS, AS = TC_A_SLOTS, RS = TC_RAW_SLOTS;
+    constexpr int BS  = cfg::B_SLOTS, AS = cfg::A_SLOTS, RS = TC_RAW_SLOTS;
     constexpr int SPR = raw_k<TYPE>::value / TC_KS;          // MMA stages per raw slot
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
