@@ -122,6 +122,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
     ctx->mma_ch        = env_int("GGML_B200_MMA_CH", 0);
     ctx->mma_min_n     = env_int("GGML_B200_MMA_MIN_N", 1);
+    ctx->mma_prequant  = env_int("GGML_B200_MMA_PREQUANT", 1);
     ctx->tc_split_k   = env_int("GGML_B200_TC_SPLIT_K", 1);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
@@ -169,6 +170,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;
     else if (!strcmp(name, "mma_ch"))        slot = &ctx->mma_ch;
     else if (!strcmp(name, "mma_min_n"))     slot = &ctx->mma_min_n;
+    else if (!strcmp(name, "mma_prequant"))  slot = &ctx->mma_prequant;
     else if (!strcmp(name, "tc_split_k"))   slot = &ctx->tc_split_k;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
@@ -360,12 +362,11 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         if (a->type == B200_TYPE_Q4_K && !ctx->force_generic && ctx->fuse_quant && batches <= 65535 &&
             aligned16(a->data, a->nb[1], a->nb[2], a->nb[3]) && aligned16(b->data, b->nb[1], b->nb[2], b->nb[3]) &&
             b200_gemv_q4k_smem((int) n, k) <= ctx->smem_optin) {
-            // 3..8 columns: integer tensor-core GEMV (mmvq_mma.cu).  n = 2 stays on the dp4a kernel, whose smaller fixed cost wins on
-            // the decoder-layer shapes (us dp4a / mma at n = 2: 1024x4096 2.9 / 4.3, 4096x4096 7.0 / 8.2, 14336x4096 13.0 / 12.3,
-            // output head 75 / 69; at n = 4: 4.5 / 4.6, 10.5 / 8.8, 19.6 / 12.7, 113 / 70; n = 8: 2-3.5x faster everywhere).
-            // The choice must not depend on m: a row shard has to run the same arithmetic as the whole matrix (row split).
-            // use_mma = 2 forces the tensor-core kernel.
-            const bool mma_pays = ctx->use_mma == 2 || n >= 3;
+            // 2..8 columns: integer tensor-core GEMV (mmvq_mma.cu).  Measured (us dp4a / mma, CUDA graph, rotating weights): n = 2:
+            // 1024x4096 2.9 / 3.3, 4096x4096 7.0 / 6.3, 14336x4096 12.8 / 10.4, output head 74.5 / 63.6; n = 8: 8.3 / 4.6, 20.0 / 8.7,
+            // 39.7 / 12.7, 241 / 66.5.  The choice must not depend on m: a row shard has to run the same arithmetic as the whole
+            // matrix (row split).  use_mma = 0 keeps the dp4a kernel.
+            const bool mma_pays = n >= 2;
             if (n >= 2 && ctx->use_mma && mma_pays && !(n_peers > 0 && ctx->gs_world > 0) && b200_gemv_mma_ok(ctx, B200_TYPE_Q4_K, P)) {
                 const bool late = n_peers == 0 && can_defer_wait(ctx, b, nullptr);
                 pending_push(ctx, d, !late);

@@ -101,6 +101,7 @@ struct b200_ctx {
     int          n_pend;
     int          defer_wait;      // 1: allow the deferred dependency wait
     int          use_mma;         // 1: Q4_K with 2..8 columns runs the tensor-core GEMV (mmvq_mma.cu) instead of the dp4a one
+    int          mma_prequant;    // tensor-core GEMV: 1 = activations quantized once per call by a small kernel, 0 = in every CTA's prologue
     int          mma_min_n;       // Q8_0 / Q4_0: columns from which the tensor-core GEMV replaces gemv_generic
     int          mma_ch;          // tensor-core GEMV: super-blocks per ring stage override (0 = auto, 1)
     int          mma_ks;          // tensor-core GEMV: K slices per row block override (0 = auto; 1, 2, 4, 8, 16)

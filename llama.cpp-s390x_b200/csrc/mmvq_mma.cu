@@ -30,6 +30,7 @@
 //     stack, the K slices of different warps are joined along the same tree — so the fp32 result of a row is bit-identical
 //     for every KS, grid size and row sharding (the row-split parity property), and never depends on timing.
 #include <cuda.h>
+#include <cstdio>
 #include "mm_problem.cuh"
 #include "quantize.cuh"
 #include "tc_ptx.cuh"
@@ -101,11 +102,20 @@ __device__ __forceinline__ uint4 lds_u4(const uint32_t a) {
     uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v;
 }
 
+// 1-D bulk copy global -> shared, bytes reported to an mbarrier (both addresses and the size are multiples of 16)
+__device__ __forceinline__ void bulk_g2s(const uint32_t dst, const void * src, const uint32_t bytes, const uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
 struct mma_args {
     int ks;            // K slices per row block (1, 2, 4, 8 or 16)
+    int ks_log2;
     int stages;        // ring depth per warp
     int ch;            // super-blocks per stage (1 or 2)
     int ncol;          // activation columns held in shared memory (1..8): long rows only fit with fewer than 8
+    const uint8_t * img;   // quantized activations prepared by mma_quant_kernel (the shared-memory bytes [OFF_D, ring) verbatim), or NULL:
+                           // every CTA quantizes for itself in its prologue
     int late;          // X / ids are not written by a kernel that may still run: the dependency wait moves to just before the first
                        // store, and this kernel's prologue and streaming overlap the previous kernel's tail (see mmvq.cu / abi.cu)
 };
@@ -130,18 +140,19 @@ __device__ __forceinline__ void tree_push(float (&st)[4][4], const int i, float 
 struct step_cursor {
     int u, sb, sb_end;
     int64_t rb;
-    __device__ __forceinline__ void seek(const int units, const int ks, const int nsb, const int64_t rb_lo) {
+    // (ks is a power of two and passed as its log2: integer divisions are slow enough to show up in a 5 us kernel)
+    __device__ __forceinline__ void seek(const int units, const int ksl2, const int nsb, const int64_t rb_lo) {
         // first non-empty unit at or after u
         for (; u < units; u += MW) {
-            const int q = u / ks, s = u - q * ks;
-            sb = nsb * s / ks; sb_end = nsb * (s + 1) / ks; rb = rb_lo + q;
+            const int q = u >> ksl2, s = u - (q << ksl2);
+            sb = (nsb * s) >> ksl2; sb_end = (nsb * (s + 1)) >> ksl2; rb = rb_lo + q;
             if (sb < sb_end) return;
         }
     }
     __device__ __forceinline__ bool done(const int units) const { return u >= units; }
-    __device__ __forceinline__ void advance(const int ch, const int units, const int ks, const int nsb, const int64_t rb_lo) {
+    __device__ __forceinline__ void advance(const int ch, const int units, const int ksl2, const int nsb, const int64_t rb_lo) {
         sb += ch;
-        if (sb >= sb_end) { u += MW; seek(units, ks, nsb, rb_lo); }
+        if (sb >= sb_end) { u += MW; seek(units, ksl2, nsb, rb_lo); }
     }
 };
 
@@ -300,104 +311,37 @@ template <> struct mma_step<B200_TYPE_Q6_K> {
     }
 };
 
+// ---- activation quantization: the columns x[0..nc) -> int8 image q [ncol][k + 32] + scales d [k / ACT_BLK][8] ----------------
+// Runs either as the GEMV's prologue (every CTA for itself, q / d in shared memory) or once per call in its own small kernel
+// that writes the same image to global memory, from where the GEMV CTAs fetch it with one bulk copy (mma_quant_kernel).
+// wid / nw: index and number of the warps sharing the work.
 template <int TYPE>
-__global__ void __launch_bounds__(MW * 32, 1)
-gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const mma_args A) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    const int k = (int) P.k, nsb = k >> 8;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    // shared memory map
-    float **  s_y    = reinterpret_cast<float **>(smem);                              // 8 output column pointers
-    float *   s_part = reinterpret_cast<float *>(smem + OFF_PART);                    // [2][MW][128] K-slice partial sums
-    constexpr int STEP_B = mma_geo<TYPE>::STEP_B, BOX_B = mma_geo<TYPE>::BOX_B, ACT_BLK = mma_geo<TYPE>::ACT_BLK;
-    float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [k / ACT_BLK][8] activation scales
-    int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k, TYPE));         // [8][k + 32]
-    const uint32_t stage_b = (uint32_t) A.ch * RB * BOX_B;                            // [MW][stages][16 rows][ch * BOX_B]
-    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE, A.ncol) + (uint32_t) (warp * A.stages) * stage_b;
-    const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
-
-    if (tid == 0) tc::tma_prefetch_desc(&tmW);
-    if (lane == 0) {
-        for (int s = 0; s < A.stages; ++s) tc::mbar_init(bar0 + 8 * s, 1);
-        tc::mbar_fence_init();
-    }
-    __syncwarp();
-
-    // this CTA's share of the row blocks (persistent: the activations are quantized once per CTA)
-    const int64_t nrb   = (P.m + RB - 1) / RB;
-    const int64_t rb_lo = nrb * blockIdx.x / gridDim.x, rb_hi = nrb * (blockIdx.x + 1) / gridDim.x;
-    const int     units = (int) (rb_hi - rb_lo) * A.ks;
-    const int     rounds = (units + MW - 1) / MW;
-
-    mm_cols<8> C;
-    bool live = true;
-    // one ring fill: super-blocks [sb, sb + ch) of rows [16 rb, 16 rb + 16) of matrix `mat` (rows / K past the end are zero-filled)
-    int mat = 0;
-    auto fill = [&](const step_cursor & c, const int stage) {
-        const uint32_t bar = bar0 + 8 * stage;
-        if (tc::elect_one()) {
-            tc::mbar_arrive_expect_tx(bar, stage_b);
-            // (Q6_K: the box starts at the 16-byte boundary below the super-block, 2 (sb mod 8) bytes = (sb mod 8) elements early)
-            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (STEP_B / 2) - (TYPE == B200_TYPE_Q6_K ? (c.sb & 7) : 0), (int) (c.rb * RB), mat);
-        }
-        __syncwarp();
-    };
-    step_cursor pc;                       // producer cursor
-    int p_stage = 0, in_flight = 0;
-    auto start_fills = [&]() {
-        pc.u = warp; pc.seek(units, A.ks, nsb, rb_lo);
-        for (; in_flight < A.stages && !pc.done(units); ++in_flight) {
-            fill(pc, p_stage);
-            if (++p_stage == A.stages) p_stage = 0;
-            pc.advance(A.ch, units, A.ks, nsb, rb_lo);
-        }
-    };
-    auto set_mat = [&]() { mat = P.nb02 > 0 ? (int) ((C.W - P.W) / P.nb02) : 0; };
-
-    // weights are never written by a kernel of this path: in MM_PLAIN the first ring fills go out before the dependency wait
-    if (P.mode == MM_PLAIN) {
-        live = mm_resolve<8>(P, blockIdx.y, C);
-        set_mat();
-        start_fills();
-    }
-    if (A.late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    else        asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (P.mode != MM_PLAIN) {
-        live = mm_resolve<8>(P, blockIdx.y, C);
-        set_mat();
-        if (live) start_fills();
-    }
-    if (!live) return;                    // block-uniform; nothing was issued
-
-    // ---- prologue: the (up to 8) activation columns -> int8 + one scale per 256 values -----------------------------------
-    if (tid < 8) {
-        float * y = C.y[0];
-#pragma unroll
-        for (int c = 1; c < 8; ++c) if (tid == c) y = C.y[c];
-        s_y[tid] = y;
-    }
+__device__ __forceinline__ void mma_quantize(const float * const (&x)[8], const int nc, const int ncol, const int k, int8_t * q, float * d,
+                                             const int wid, const int nw, const int lane) {
+    constexpr int ACT_BLK = mma_geo<TYPE>::ACT_BLK;
+    const int nsb = k >> 8;
     if (ACT_BLK == 256) {
         // (column, super-block) tasks: a warp takes 8 at a time and requests all their data before the first reduction, so the
         // L2 round trips of a warp's tasks overlap instead of adding up (measured: +0.5 us per column before)
-        for (int task0 = warp; task0 < A.ncol * nsb; task0 += 8 * MW) {
+        for (int task0 = wid; task0 < ncol * nsb; task0 += 8 * nw) {
             float4 v0[8], v1[8];
     #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int task = task0 + i * MW;
+                const int task = task0 + i * nw;
                 const int col = task / nsb, sb = task - col * nsb;
                 v0[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); v1[i] = v0[i];
-                if (task < A.ncol * nsb && col < C.nc) {
-                    const float * xc = C.x[0];
+                if (task < ncol * nsb && col < nc) {
+                    const float * xc = x[0];
     #pragma unroll
-                    for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
+                    for (int c = 1; c < 8; ++c) if (col == c) xc = x[c];
                     const float4 * src = reinterpret_cast<const float4 *>(xc + sb * 256 + lane * 8);
                     v0[i] = __ldg(src); v1[i] = __ldg(src + 1);
                 }
             }
     #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int task = task0 + i * MW;
-                if (task >= A.ncol * nsb) break;
+                const int task = task0 + i * nw;
+                if (task >= ncol * nsb) break;
                 const int col = task / nsb, sb = task - col * nsb;
                 uint2 packed = make_uint2(0u, 0u);
                 float d8 = 0.0f;
@@ -418,47 +362,183 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
                 if (TYPE == B200_TYPE_Q6_K) {
                 // words (2 lane, 2 lane + 1) of the super-block; inside their 32-group the word order is (0, 4, 1, 5, 2, 6, 3, 7)
                 const int w0 = 2 * (lane & 3), p0 = w0 < 4 ? 2 * w0 : 2 * (w0 - 4) + 1;       // w0 + 1 lands at p0 + 2
-                uint32_t * blk = reinterpret_cast<uint32_t *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + (lane >> 2) * 32);
+                uint32_t * blk = reinterpret_cast<uint32_t *>(q + (size_t) col * (k + COL_PAD) + sb * 256 + (lane >> 2) * 32);
                 blk[p0] = packed.x; blk[p0 + 2] = packed.y;
             } else {
-                *reinterpret_cast<uint2 *>(s_q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
+                *reinterpret_cast<uint2 *>(q + (size_t) col * (k + COL_PAD) + sb * 256 + lane * 8) = packed;
             }
-                if (lane == 0) s_d[sb * 8 + col] = d8;
+                if (lane == 0) d[sb * 8 + col] = d8;
             }
         }
     } else {
         // per-32 scales, the values of quantize_row_q8_1_ref (ggml-quants.c:260-293): 8 lanes per block, 8 blocks per lane in
         // flight.  Q4_0 stores the 8 words of a block in the order (0, 4, 1, 5, 2, 6, 3, 7) — what its nibble layout pairs up.
-        const int nbk = k >> 5, total = C.nc * nbk, sub = lane & 7;
-        for (int i = tid; i < (8 - C.nc) * nbk; i += MW * 32) {          // dead columns: scale 0 (their int8 values are never used)
-            const int col = C.nc + i / nbk, ib = i - (i / nbk) * nbk;
-            s_d[ib * 8 + col] = 0.0f;
+        const int nbk = k >> 5, total = nc * nbk, sub = lane & 7;
+        for (int i = wid * 32 + lane; i < (8 - nc) * nbk; i += nw * 32) {          // dead columns: scale 0 (their int8 values are never used)
+            const int col = nc + i / nbk, ib = i - (i / nbk) * nbk;
+            d[ib * 8 + col] = 0.0f;
         }
-        for (int blk0 = tid >> 3; blk0 < total; blk0 += 8 * MW * 4) {     // warp-uniform trip count: total is a multiple of 8
+        for (int blk0 = wid * 4 + (lane >> 3); blk0 < total; blk0 += 8 * nw * 4) {     // warp-uniform trip count: total is a multiple of 8
             float4 v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int blk = blk0 + i * MW * 4, bb = blk < total ? blk : total - 1;
+                const int blk = blk0 + i * nw * 4, bb = blk < total ? blk : total - 1;
                 const int col = bb / nbk, ib = bb - col * nbk;
-                const float * xc = C.x[0];
+                const float * xc = x[0];
 #pragma unroll
-                for (int c = 1; c < 8; ++c) if (col == c) xc = C.x[c];
+                for (int c = 1; c < 8; ++c) if (col == c) xc = x[c];
                 v[i] = __ldg(reinterpret_cast<const float4 *>(xc + ib * 32 + sub * 4));
             }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int blk = blk0 + i * MW * 4, bb = blk < total ? blk : total - 1;
+                const int blk = blk0 + i * nw * 4, bb = blk < total ? blk : total - 1;
                 const int col = bb / nbk, ib = bb - col * nbk;
                 const q8_part qp = quantize_q8_1_part(v[i]);
                 if (blk < total) {
                     const int w = TYPE == B200_TYPE_Q4_0 ? (sub < 4 ? 2 * sub : 2 * (sub - 4) + 1) : sub;
-                    *reinterpret_cast<uint32_t *>(s_q + (size_t) col * (k + COL_PAD) + ib * 32 + 4 * w) = qp.packed;
-                    if (sub == 0) s_d[ib * 8 + col] = qp.d;
+                    *reinterpret_cast<uint32_t *>(q + (size_t) col * (k + COL_PAD) + ib * 32 + 4 * w) = qp.packed;
+                    if (sub == 0) d[ib * 8 + col] = qp.d;
                 }
             }
         }
     }
+}
+
+// the activations of one MUL_MAT call (<= 8 columns, no batch dims), quantized ONCE for all CTAs of the GEMV that follows
+template <int TYPE>
+__global__ void __launch_bounds__(256) mma_quant_kernel(const mm_problem P, const int ncol, uint8_t * img) {
+    // X may be produced by the previous kernel of the stream, and the previous GEMV may still be fetching the image this kernel
+    // rewrites: wait for it; the GEMV that consumes the image may be launched meanwhile (it waits for this grid before it reads)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int k = (int) P.k, nc = (int) P.ne11;
+    const float * xs[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) xs[c] = reinterpret_cast<const float *>(reinterpret_cast<const char *>(P.X) + (c < nc ? c : 0) * P.nb11);
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+    mma_quantize<TYPE>(xs, nc, ncol, k, reinterpret_cast<int8_t *>(img + (mma_off_q(k, TYPE) - OFF_D)), reinterpret_cast<float *>(img),
+                       gtid >> 5, (int) (gridDim.x * blockDim.x) >> 5, threadIdx.x & 31);
+}
+
+#ifdef MMA_TRACE_ENABLE      // development aid: phase time stamps of CTA 0 / warp 0 (build with -DMMA_TRACE_ENABLE)
+#define MMA_TRACE(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tr_[i] = t_; } } while (0)
+#else
+#define MMA_TRACE(i) do { } while (0)
+#endif
+
+template <int TYPE>
+__global__ void __launch_bounds__(MW * 32, 1)
+gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const mma_args A) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int k = (int) P.k, nsb = k >> 8;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+#ifdef MMA_TRACE_ENABLE
+    unsigned long long tr_[8] = {};
+#endif
+    MMA_TRACE(0);
+    // shared memory map
+    float **  s_y    = reinterpret_cast<float **>(smem);                              // 8 output column pointers
+    float *   s_part = reinterpret_cast<float *>(smem + OFF_PART);                    // [2][MW][128] K-slice partial sums
+    constexpr int STEP_B = mma_geo<TYPE>::STEP_B, BOX_B = mma_geo<TYPE>::BOX_B, ACT_BLK = mma_geo<TYPE>::ACT_BLK;
+    float *   s_d    = reinterpret_cast<float *>(smem + OFF_D);                       // [k / ACT_BLK][8] activation scales
+    int8_t *  s_q    = reinterpret_cast<int8_t *>(smem + mma_off_q(k, TYPE));         // [8][k + 32]
+    const uint32_t stage_b = (uint32_t) A.ch * RB * BOX_B;                            // [MW][stages][16 rows][ch * BOX_B]
+    const uint32_t ring0 = tc::smem_u32(smem) + (uint32_t) mma_off_ring(k, TYPE, A.ncol) + (uint32_t) (warp * A.stages) * stage_b;
+    const uint32_t bar0  = tc::smem_u32(smem) + OFF_BAR + (uint32_t) warp * MAX_STAGE * 8;
+
+    const uint32_t barI = tc::smem_u32(smem) + OFF_BAR + MW * MAX_STAGE * 8;     // completion of the activation image copy
+    if (tid == 0) { tc::tma_prefetch_desc(&tmW); tc::mbar_init(barI, 1); }
+    if (lane == 0) {
+        for (int s = 0; s < A.stages; ++s) tc::mbar_init(bar0 + 8 * s, 1);
+        tc::mbar_fence_init();
+    }
+    __syncwarp();
+
+    // this CTA's share of the row blocks (persistent: the activations are quantized once per CTA)
+    const uint32_t nrb32 = (uint32_t) ((P.m + RB - 1) >> 4);                       // m <= 2^30: 32-bit arithmetic, no 64-bit divisions
+    const int64_t  rb_lo = nrb32 < (1u << 20) ? (int64_t) (nrb32 * blockIdx.x / gridDim.x) : (int64_t) nrb32 * blockIdx.x / gridDim.x;
+    const int64_t  rb_hi = nrb32 < (1u << 20) ? (int64_t) (nrb32 * (blockIdx.x + 1) / gridDim.x) : (int64_t) nrb32 * (blockIdx.x + 1) / gridDim.x;
+    const int     units = (int) (rb_hi - rb_lo) * A.ks;
+    const int     rounds = (units + MW - 1) / MW;
+
+    mm_cols<8> C;
+    bool live = true;
+    // one ring fill: super-blocks [sb, sb + ch) of rows [16 rb, 16 rb + 16) of matrix `mat` (rows / K past the end are zero-filled)
+    int mat = 0;
+    auto fill = [&](const step_cursor & c, const int stage) {
+        const uint32_t bar = bar0 + 8 * stage;
+        if (tc::elect_one()) {
+            tc::mbar_arrive_expect_tx(bar, stage_b);
+            // (Q6_K: the box starts at the 16-byte boundary below the super-block, 2 (sb mod 8) bytes = (sb mod 8) elements early)
+            tc::tma_load_3d(ring0 + stage * stage_b, &tmW, bar, c.sb * (STEP_B / 2) - (TYPE == B200_TYPE_Q6_K ? (c.sb & 7) : 0), (int) (c.rb * RB), mat);
+        }
+        __syncwarp();
+    };
+    step_cursor pc;                       // producer cursor
+    int p_stage = 0, in_flight = 0;
+    auto start_fills = [&]() {
+        pc.u = warp; pc.seek(units, A.ks_log2, nsb, rb_lo);
+        for (; in_flight < A.stages && !pc.done(units); ++in_flight) {
+            fill(pc, p_stage);
+            if (++p_stage == A.stages) p_stage = 0;
+            pc.advance(A.ch, units, A.ks_log2, nsb, rb_lo);
+        }
+    };
+    auto set_mat = [&]() { mat = P.nb02 > 0 ? (int) ((C.W - P.W) / P.nb02) : 0; };
+
+    // weights are never written by a kernel of this path: in MM_PLAIN the first ring fills go out before the dependency wait
+    if (P.mode == MM_PLAIN) {
+        if (gridDim.y == 1) {               // one matrix, <= 8 columns: nothing to resolve (mm_resolve costs several 64-bit divisions)
+            C.W = P.W; C.nc = (int) P.ne11;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int cc = c < C.nc ? c : 0;
+                C.plane_col[c] = cc;
+                C.x[c] = reinterpret_cast<const float *>(reinterpret_cast<const char *>(P.X) + cc * P.nb11);
+                C.y[c] = P.Y + cc * P.m;
+            }
+        } else {
+            live = mm_resolve<8>(P, blockIdx.y, C);
+        }
+        set_mat();
+        start_fills();
+    }
+    MMA_TRACE(1);
+    if (A.late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    else        asm volatile("griddepcontrol.wait;" ::: "memory");
+    MMA_TRACE(2);
+    if (P.mode != MM_PLAIN) {
+        live = mm_resolve<8>(P, blockIdx.y, C);
+        set_mat();
+        if (live) start_fills();
+    }
+    if (!live) return;                    // block-uniform; nothing was issued
+
+    // ---- prologue: the (up to 8) activation columns -> int8 + one scale per 256 values -----------------------------------
+    if (tid < 8) {
+        float * y = C.y[0];
+#pragma unroll
+        for (int c = 1; c < 8; ++c) if (tid == c) y = C.y[c];
+        s_y[tid] = y;
+    }
+    if (A.img) {
+        // quantized once by mma_quant_kernel (complete: the dependency wait above was not deferred): one bulk copy per CTA
+        const uint32_t bytes = (uint32_t) (mma_off_ring(k, TYPE, A.ncol) - OFF_D);
+        if (tid == 0) {
+            tc::mbar_arrive_expect_tx(barI, bytes);
+            bulk_g2s(tc::smem_u32(smem) + OFF_D, A.img, bytes, barI);
+        }
+        __syncthreads();                     // barI's initialisation is visible to everybody
+        tc::mbar_wait(barI, 0);
+    } else {
+        const float * xs[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) xs[c] = C.x[c];
+        mma_quantize<TYPE>(xs, C.nc, A.ncol, k, s_q, s_d, warp, MW, lane);
+    }
+    MMA_TRACE(3);
     __syncthreads();
+    MMA_TRACE(4);
     if (!A.late) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     bool waited = !A.late;
 
@@ -480,17 +560,17 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
         int64_t rb = 0;
         int     ksl = 0;
         if (u < units) {
-            const int q = u / A.ks;
-            ksl = u - q * A.ks;
+            const int q = u >> A.ks_log2;
+            ksl = u - (q << A.ks_log2);
             rb  = rb_lo + q;
-            const int lpw = 16 / A.ks;                                  // summation-tree leaves owned by this warp
+            const int lpw = 16 >> A.ks_log2;                                  // summation-tree leaves owned by this warp
             float st[4][4] = {};
-            const int sb_last = nsb * (ksl + 1) / A.ks - 1;             // last super-block of the unit
+            const int sb_last = ((nsb * (ksl + 1)) >> A.ks_log2) - 1;             // last super-block of the unit
             int in_chunk = 0;
             for (int li = 0; li < lpw; ++li) {
               const int lf = ksl * lpw + li;
               float pf[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-              for (int sb = nsb * lf / 16; sb < nsb * (lf + 1) / 16; ++sb) {
+              for (int sb = (nsb * lf) >> 4; sb < (nsb * (lf + 1)) >> 4; ++sb) {
                 if (in_chunk == 0) tc::mbar_wait(bar0 + 8 * c_stage, c_phase);
                 const uint32_t st_a = ring0 + c_stage * stage_b + in_chunk * BOX_B + (TYPE == B200_TYPE_Q6_K ? 2u * (sb & 7) : 0u);
                 mma_step<TYPE>::run(st_a, r0off, r1off, t, bq + 256u * sb, sd + (uint32_t) (256 / ACT_BLK) * 32u * sb, pf);
@@ -500,7 +580,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
                     __syncwarp();
                     if (!pc.done(units)) {
                         fill(pc, c_stage);
-                        pc.advance(A.ch, units, A.ks, nsb, rb_lo);
+                        pc.advance(A.ch, units, A.ks_log2, nsb, rb_lo);
                     }
                     if (++c_stage == A.stages) { c_stage = 0; c_phase ^= 1u; }
                 }
@@ -509,6 +589,7 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
               if (li == lpw - 1) { accf[0] = pf[0]; accf[1] = pf[1]; accf[2] = pf[2]; accf[3] = pf[3]; }
             }
         }
+        if (round == 0) MMA_TRACE(5);
         // ---- end of the unit: add the K slices in slice order, store -----------------------------------------------------
         bool store = u < units;
         if (A.ks > 1) {
@@ -541,6 +622,12 @@ gemv_q4k_mma(const __grid_constant__ CUtensorMap tmW, const mm_problem P, const 
             }
         }
     }
+    MMA_TRACE(6);
+#ifdef MMA_TRACE_ENABLE
+    if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0)
+        printf("mma trace (ns from start): fills issued %llu, dependency wait done %llu, prologue done %llu, after barrier %llu, first unit done %llu, end %llu  (grid %u, ks %d, stages %d, ch %d)\n",
+               tr_[1] - tr_[0], tr_[2] - tr_[0], tr_[3] - tr_[0], tr_[4] - tr_[0], tr_[5] - tr_[0], tr_[6] - tr_[0], gridDim.x, A.ks, A.stages, A.ch);
+#endif
 }
 
 }  // namespace
@@ -586,6 +673,20 @@ int b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P) {
 }
 
 template <int TYPE>
+static int mma_quant_launch_t(b200_ctx * ctx, const mm_problem & P, int ncol, uint8_t * img) {
+    const int64_t warps = mma_geo<TYPE>::ACT_BLK == 256 ? (int64_t) ncol * (P.k / 256) : (P.ne11 * (P.k / 32) + 3) / 4;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) ((warps + 7) / 8)); cfg.blockDim = dim3(256); cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mma_quant_kernel<TYPE>, P, ncol, img));
+    ctx->launches++;
+    return B200_OK;
+}
+
+template <int TYPE>
 static int mma_launch_t(b200_ctx * ctx, const cudaLaunchConfig_t & cfg, const CUtensorMap & tmw, const mm_problem & P, const mma_args & A) {
     static bool attr_done[16] = {};
     if (!attr_done[ctx->device & 15]) {
@@ -616,6 +717,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
     if (ks != 1 && ks != 2 && ks != 4 && ks != 8 && ks != 16) { b200_set_error("gemv_mma: K slices must be 1, 2, 4, 8 or 16"); return B200_E_ARG; }
     mma_args A = {};
     A.ks = ks;
+    A.ks_log2 = ks == 1 ? 0 : ks == 2 ? 1 : ks == 4 ? 2 : ks == 8 ? 3 : 4;
     A.late = ctx->pdl && late_wait ? 1 : 0;
     // steps per stage: 2 when every K slice is a whole number of pairs (the 272-byte Q8_0 step exceeds the 256-element box: 1)
     const int step_b = mma_step_b(type);
@@ -638,6 +740,33 @@ int b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & Pin, int64
                                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (wr != CUDA_SUCCESS) { b200_set_error("gemv_mma: cuTensorMapEncodeTiled failed (%d)", (int) wr); return B200_E_CUDA; }
 
+    // one MUL_MAT without batch dims: quantize the activations once in a small kernel instead of in every CTA's prologue (measured
+    // per CTA: 3.4 us at n = 1, 7 us at n = 8 for k = 4096 — more than the streaming of a decoder-layer matrix)
+    // Only when the activations are still being produced (no deferred wait possible): otherwise the CTA prologue overlaps the
+    // previous kernel's tail and costs nothing (mma_prequant: 0 never, 1 when dependent, 2 always).
+    // Measured on dependent chains of 4096x4096 matmuls (tools/gemv_chain.py, us per matmul, in-CTA / once): n = 8 Q8_0 13.7 / 10.7,
+    // Q4_0 13.2 / 10.3, Q4_K 9.4 / 8.2, Q6_K 11.4 / 10.2; n <= 4: equal or worse (the extra kernel boundary costs what it saves).
+    const bool pre_possible = ctx->mma_prequant > 0 && (ctx->mma_prequant == 2 || P.ne11 >= 5) && P.mode == MM_PLAIN && tiles == 1 && ctx->pdl;
+    if (pre_possible) {
+        // reserved whether or not this particular launch uses it: a later launch of the same shape may sit inside a stream capture,
+        // where the scratch cannot grow
+        const int rc = b200_ctx_reserve(ctx, mma_off_ring(P.k, type, A.ncol) - OFF_D);
+        if (rc) return rc;
+    }
+    if (pre_possible && (ctx->mma_prequant == 2 || !late_wait)) {
+        int rc = B200_OK;
+        uint8_t * img = (uint8_t *) ctx->ws;
+        switch (type) {
+            case B200_TYPE_Q4_K: rc = mma_quant_launch_t<B200_TYPE_Q4_K>(ctx, P, A.ncol, img); break;
+            case B200_TYPE_Q4_0: rc = mma_quant_launch_t<B200_TYPE_Q4_0>(ctx, P, A.ncol, img); break;
+            case B200_TYPE_Q8_0: rc = mma_quant_launch_t<B200_TYPE_Q8_0>(ctx, P, A.ncol, img); break;
+            case B200_TYPE_Q6_K: rc = mma_quant_launch_t<B200_TYPE_Q6_K>(ctx, P, A.ncol, img); break;
+            default: rc = B200_E_UNSUPPORTED;
+        }
+        if (rc) return rc;
+        A.img  = img;
+        A.late = 0;                       // the image must be complete before the CTAs fetch it
+    }
     const int64_t max_useful = (nrb * ks + MW - 1) / MW;
     if (ctas > max_useful) ctas = max_useful;
     cudaLaunchConfig_t cfg = {};
