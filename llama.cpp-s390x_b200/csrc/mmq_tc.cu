@@ -96,6 +96,12 @@ struct tc_args {
 // one CTA per activation position p (plain: column i11 of batch; MUL_MAT_ID: sorted position -> pair -> (token, slot))
 __global__ void __launch_bounds__(256) tc_act_f16_kernel(const mm_problem P, __half * __restrict__ Xh, float * __restrict__ colscale,
                                                          int32_t * __restrict__ ycol) {
+    // programmatic dependent launch (ctx option tc_pdl): this grid may start while the previous kernel of the stream (normally the
+    // previous GEMM, which still reads the fp16 scratch this kernel rewrites, and may be producing X) is finishing — wait for it
+    // here; the GEMM that consumes this kernel's output may be launched right away (it sets up barriers / TMEM, then waits for
+    // this grid).  Both instructions are no-ops in a launch without the attribute.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int64_t p = blockIdx.x;
     const float * x;
     if (P.mode == MM_PLAIN) {
@@ -448,6 +454,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t rBFull = PAIR ? tc::mapa_u32(bBFull, 0) : bBFull;
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
+    // everything above overlapped the activation-conversion kernel when launched with the PDL attribute; its output is needed from here on
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     // Ring positions are kept as (slot, phase) pairs advanced by hand: the single-thread roles below are latency chains,
     // so no divisions and no 64-bit arithmetic inside the stage loops.
@@ -713,17 +722,24 @@ int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, 
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg_t::SMEM));
         configured[ctx->device & 15] = true;
     }
-    if (PAIR) {
+    {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned) a.grid); cfg.blockDim = dim3(TC_THREADS);
         cfg.dynamicSmemBytes = cfg_t::SMEM; cfg.stream = ctx->stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr; cfg.numAttrs = 1;
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (PAIR) {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        if (ctx->pdl && ctx->tc_pdl && a.split_k == 1) {      // (split K: a memset sits between the two kernels, nothing to overlap)
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
+        cfg.attrs = attr; cfg.numAttrs = na;
         B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tmw[0], tmw[1], tmw[2], tm, a));
-    } else {
-        kern<<<(unsigned) a.grid, TC_THREADS, cfg_t::SMEM, ctx->stream>>>(tmw[0], tmw[1], tmw[2], tm, a);
     }
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;
@@ -827,8 +843,15 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     const int NT = pl.NT;
     const int64_t n = pl.n;
 
-    tc_act_f16_kernel<<<(unsigned) n_pos, 256, 0, ctx->stream>>>(P, Xh, sc, yc);
-    B200_CUDA_TRY(cudaGetLastError());
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned) n_pos); cfg.blockDim = dim3(256); cfg.stream = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = (ctx->pdl && ctx->tc_pdl) ? 1 : 0;
+        B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, tc_act_f16_kernel, P, Xh, sc, yc));
+    }
     ctx->launches++;
 
     CUtensorMap tmb;

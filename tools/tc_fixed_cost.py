@@ -10,13 +10,13 @@ pkg = load_package()
 stream = torch.cuda.Stream()
 ctx = pkg.Context(0, stream=stream.cuda_stream)
 rng = np.random.default_rng(0)
-for opts in ({}, {"tc_split_k": 2}, {"tc_split_k": 4}, {"tc_nt": 256}, {"tc_nt": 256, "tc_split_k": 2}):
-    for k_, v in {"tc_split_k": 1, "tc_nt": 0}.items():
+for opts in ({}, {"tc_pdl": 1}, {}, {"tc_pdl": 1}, {"tc_split_k": 2}, {"tc_nt": 256}):
+    for k_, v in {"tc_split_k": 1, "tc_nt": 0, "tc_pdl": 0}.items():
         ctx.set_option(k_, v)
     for k_, v in opts.items():
         ctx.set_option(k_, v)
     row = []
-    for m, k, n in ((4096, 256, 512), (4096, 1024, 512), (1024, 4096, 512), (4096, 4096, 512), (14336, 4096, 512)):
+    for m, k, n in ((4096, 256, 512), (1024, 4096, 512), (4096, 4096, 512), (14336, 4096, 512), (28672, 4096, 512), (128256, 4096, 512)):
         W = torch.from_numpy(random_blocks(12, 256, k, rng)).cuda().repeat((m + 255) // 256, 1)[:m].contiguous()
         X = torch.randn((n, k), device="cuda"); Y = torch.empty((n, m), device="cuda")
         with torch.cuda.stream(stream):
