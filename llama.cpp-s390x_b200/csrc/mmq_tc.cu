@@ -640,7 +640,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
                 const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
                 tc::tmem_ld_wait();
-                if (sg.order == 0) {
+                if (sg.order == 0 && a.n_peers == 0) {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
+                        const int32_t yc = __shfl_sync(0xffffffffu, my_yc, c);
+                        if (c0 + c < t.nvalid && row < t.m) t.Y[(int64_t) yc * t.m + row] = __uint_as_float(v[c]) * sc;
+                    }
+                } else if (sg.order == 0) {
+                    // row split: the same tile also goes to every rank's full-height output (its own loop: the plain epilogue above
+                    // must not carry the peer branch — measured +10 % on shapes whose last wave exposes the epilogue)
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
@@ -648,10 +657,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                         if (c0 + c < t.nvalid && row < t.m) {
                             const float r = __uint_as_float(v[c]) * sc;
                             t.Y[(int64_t) yc * t.m + row] = r;
-                            if (a.n_peers > 0) {
 #pragma unroll 1
-                                for (int p = 0; p < a.n_peers; ++p) a.peer_Y[p][(int64_t) yc * a.peer_m + a.peer_row0 + row] = r;
-                            }
+                            for (int p = 0; p < a.n_peers; ++p) a.peer_Y[p][(int64_t) yc * a.peer_m + a.peer_row0 + row] = r;
                         }
                     }
                 } else {
