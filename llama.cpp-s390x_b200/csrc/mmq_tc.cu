@@ -332,8 +332,10 @@ struct tc_tile {
 };
 
 // tm = weight rows per work tile (128, or 256 for a CTA pair: CTA `rank` of the pair owns rows [128 * rank, 128 * rank + 128) of it)
-__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int64_t T, tc_tile & t, const int tm = TC_M, const int rank = 0) {
-    const int row_tiles = a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + tm - 1) / tm;
+// (32-bit arithmetic throughout: the host refuses launches with 2^31 or more work items, and 64-bit divisions here sat in front of
+//  the first TMA of every CTA — 1.4 us of a 11 us launch in the phase trace)
+__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, uint32_t T, tc_tile & t, const int tm = TC_M, const int rank = 0) {
+    const uint32_t row_tiles = (uint32_t) (a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + tm - 1) / tm);
     int rt = (int) (T % row_tiles);
     T /= row_tiles;
     t.wsel = 0; t.m = a.m; t.Y = a.Y;
@@ -344,10 +346,15 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
     }
     t.row0 = rt * tm + TC_M * rank;
     if (a.mode == MM_PLAIN) {
-        const int col_tiles = (a.n + NT - 1) / NT;
-        const int ct = (int) (T % col_tiles), batch = (int) (T / col_tiles);
-        const int i12 = batch % a.ne12, i13 = batch / a.ne12;
-        t.mat    = (i13 / a.r3) * a.ne02 + i12 / a.r2;
+        const uint32_t col_tiles = (uint32_t) ((a.n + NT - 1) / NT);
+        int ct, batch;
+        if (col_tiles == 1) { ct = 0; batch = (int) T; } else { ct = (int) (T % col_tiles); batch = (int) (T / col_tiles); }
+        int i12 = 0, i13 = 0;
+        t.mat = 0;
+        if (batch > 0 || a.ne12 > 1) {                   // (a plain 2-D matmul has nothing to divide)
+            i12 = (int) ((uint32_t) batch % (uint32_t) a.ne12); i13 = (int) ((uint32_t) batch / (uint32_t) a.ne12);
+            t.mat = (int) ((uint32_t) i13 / (uint32_t) a.r3) * a.ne02 + (int) ((uint32_t) i12 / (uint32_t) a.r2);
+        }
         t.pos0   = batch * a.n + ct * NT;
         t.nvalid = min(NT, a.n - ct * NT);
         return true;
@@ -370,14 +377,14 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, int6
 // What a CTA works on next: a whole tile, or (split K) the K range [k0, k1) of one.
 struct tc_seg {
     tc_tile t;
-    int64_t T;
+    uint32_t T;
     int k0, k1;             // in 64-wide stages
     int order, nparts;      // position of this part in the tile's fixed summation order
 };
 
 struct tc_walker {
-    int64_t w;              // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
-    int     stride, tm, rank;
+    uint32_t w;             // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
+    int      stride, tm, rank;
 
     // pair = false: one CTA per work item; true: the two CTAs of a cluster walk the same items (256-row tiles)
     __device__ __forceinline__ tc_walker(const tc_args &, const bool pair = false, const int cta_rank = 0) {
@@ -385,10 +392,10 @@ struct tc_walker {
     }
 
     __device__ __forceinline__ bool next(const tc_args & a, const int NT, tc_seg & s) {
-        const int64_t n_items = a.n_tiles * a.split_k;
+        const uint32_t n_tiles = (uint32_t) a.n_tiles, n_items = n_tiles * (uint32_t) a.split_k;
         for (; w < n_items; w += stride) {
-            const int64_t part = w / a.n_tiles;
-            s.T = w - part * a.n_tiles;
+            const uint32_t part = a.split_k == 1 ? 0u : w / n_tiles;
+            s.T = w - part * n_tiles;
             if (tc_resolve(a, NT, s.T, s.t, tm, rank)) {
                 const int len = a.k / TC_KS / a.split_k;
                 s.k0 = (int) part * len; s.k1 = s.k0 + len;
@@ -404,8 +411,11 @@ struct tc_walker {
 #ifdef TC_TRACE_ENABLE     // development aid: per-stage clock64 stamps of CTA 0 (build with -DTC_TRACE_ENABLE, run tools/tc_trace.py)
 __device__ long long g_tc_trace[6][128];
 #define TC_TRACE(role, gg) do { if (blockIdx.x == 0 && (gg) < 128) g_tc_trace[role][gg] = clock64(); } while (0)
+__device__ unsigned long long g_tc_phase[8];          // %globaltimer stamps of CTA 0: where a short GEMM spends its fixed cost
+#define TC_PHASE(i, once) do { if (blockIdx.x == 0 && (once)) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_tc_phase[i] = t_; } } while (0)
 #else
 #define TC_TRACE(role, gg) do { } while (0)
+#define TC_PHASE(i, once) do { } while (0)
 #endif
 
 template <int TYPE, int NT, bool PAIR>
@@ -431,6 +441,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t sTmem  = bAccEmpty + 16;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    TC_PHASE(0, tid == 0);
 
     if (warp == 8) {
         if (lane == 0) {
@@ -454,6 +465,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t rBFull = PAIR ? tc::mapa_u32(bBFull, 0) : bBFull;
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
+    TC_PHASE(1, tid == 0);
     // everything above overlapped the activation-conversion kernel when launched with the PDL attribute; its output is needed from here on
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -484,6 +496,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 if ((it & 1) == grp) {                        // segments start at even stages, so parity follows `it`
                     // first stage of this group in the raw slot: sub == grp (SPR is even)
                     if (sub == grp) tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
+                    TC_PHASE(3, tid == 0 && tg == 0);
                     w_frag<TYPE> f0, f1;
                     uint4 o0[4], o1[4]; int slot[4];
                     f0.load(raw_row0 + rs * RAW_BYTES + skew, sub, h);
@@ -536,6 +549,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                         if (tc::elect_one()) {
                             tc::mbar_arrive_expect_tx(bRFull + 8 * rs, RAW_BYTES);
                             const CUtensorMap * tw = t.wsel == 0 ? &tmW : (t.wsel == 1 ? &tmW1 : &tmW2);
+                            TC_PHASE(2, tg == 0);
                             tc::tma_load_3d(sRaw + rs * RAW_BYTES, tw, bRFull + 8 * rs, x - (int) (raw_skew<TYPE>(sbi) >> 1), t.row0, t.mat);
                         }
                         __syncwarp();
@@ -578,6 +592,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     tc::mbar_wait(bAFull + 8 * as, a_ph);
                     tc::mbar_wait(bBFull + 8 * bs, b_ph);
                     if (lane == 0) TC_TRACE(0, tg);
+                    TC_PHASE(4, lane == 0 && tg == 0);
                     tc::tc_fence_after();
                     const uint64_t da = da0 + (uint64_t) (as * (TC_A_BYTES >> 4));
                     const uint64_t db = db0 + (uint64_t) (bs * (cfg::B_BYTES >> 4));
@@ -614,6 +629,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         while (wk.next(a, NT, sg)) {
             const tc_tile & t = sg.t;
             tc::mbar_wait(bAccFull + 8 * acc, acc_ph, 400);
+            TC_PHASE(5, warp == 10 && lane == 0 && g_tc_phase[5] < g_tc_phase[0]);
             tc::tc_fence_after();
             const int row = t.row0 + 32 * q + lane;
             int32_t * turnstile = sg.nparts > 1 ? a.tile_sync + sg.T * 4 + q : nullptr;
@@ -674,6 +690,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     }
                 }
             }
+            TC_PHASE(6, warp == 10 && lane == 0 && g_tc_phase[6] < g_tc_phase[0]);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) { if (PAIR) tc::mbar_arrive_cluster(rAccEmpty + 8 * acc); else tc::mbar_arrive(bAccEmpty + 8 * acc); }
@@ -686,8 +703,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         }
     }
     __syncthreads();
+    TC_PHASE(7, tid == 0);
 #ifdef TC_TRACE_ENABLE
     if (blockIdx.x == 0 && tid == 0) {
+        printf("tc phases (ns from entry): set-up done %llu, first weight TMA issued %llu, first raw slot full %llu, first MMA ready %llu, first accumulator full %llu, "
+               "first tile stored %llu, all roles done %llu\n", g_tc_phase[1] - g_tc_phase[0], g_tc_phase[2] - g_tc_phase[0], g_tc_phase[3] - g_tc_phase[0],
+               g_tc_phase[4] - g_tc_phase[0], g_tc_phase[5] - g_tc_phase[0], g_tc_phase[6] - g_tc_phase[0], g_tc_phase[7] - g_tc_phase[0]);
         const long long t0 = g_tc_trace[0][32];
         for (int gg = 32; gg < 48; ++gg) {
             printf("g=%3d mma_ready=%6lld mma_done=%6lld conv_go=%6lld conv_arr0=%6lld conv_arr7=%6lld tma_go=%6lld\n", gg, g_tc_trace[0][gg] - t0,
@@ -907,6 +928,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
         }
     }
 
+    if (pl.n_tiles * 4 >= ((int64_t) 1 << 31)) { b200_set_error("tcgen05 GEMM: too many tiles"); return B200_E_UNSUPPORTED; }
     a.n_tiles = pl.n_tiles;
     // Scheduling: whole tiles, walked in the same order by all CTAs (they move along K in step and share activation tiles in
     // L2).  A long-K matrix with few tiles (down projection: 64 tiles for 148 SMs) is split in two along K; the halves run
