@@ -117,7 +117,18 @@ __global__ void __launch_bounds__(256) tc_act_f16_kernel(const mm_problem P, __h
     }
     const int k4 = (int) (P.k / 4);
     float amax = 0.0f;
-    for (int i = threadIdx.x; i < k4; i += 256) {
+    // the first 8 float4 of every thread (all of a column up to k = 8192) stay in registers between the two passes: all loads
+    // of a thread are in flight together and the second pass does not go back to L2
+    constexpr int KEEP = 8;
+    float4 keep[KEEP];
+#pragma unroll
+    for (int j = 0; j < KEEP; ++j) {
+        const int i = threadIdx.x + 256 * j;
+        keep[j] = i < k4 ? __ldg(reinterpret_cast<const float4 *>(x) + i) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+#pragma unroll
+    for (int j = 0; j < KEEP; ++j) amax = fmaxf(amax, fmaxf(fmaxf(fabsf(keep[j].x), fabsf(keep[j].y)), fmaxf(fabsf(keep[j].z), fabsf(keep[j].w))));
+    for (int i = threadIdx.x + 256 * KEEP; i < k4; i += 256) {
         const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
         amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
     }
@@ -141,15 +152,20 @@ __global__ void __launch_bounds__(256) tc_act_f16_kernel(const mm_problem P, __h
     }
     if (threadIdx.x == 0) colscale[p] = down;
     uint2 * out = reinterpret_cast<uint2 *>(Xh + p * P.k);
-    for (int i = threadIdx.x; i < k4; i += 256) {
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
+    auto emit = [&](const int i, const float4 v) {
         const __half2 a = __floats2half2_rn(v.x * up, v.z * up);      // order (0, 2, 1, 3)
         const __half2 b = __floats2half2_rn(v.y * up, v.w * up);
         uint2 o;
         o.x = *reinterpret_cast<const uint32_t *>(&a);
         o.y = *reinterpret_cast<const uint32_t *>(&b);
         out[i] = o;
+    };
+#pragma unroll
+    for (int j = 0; j < KEEP; ++j) {
+        const int i = threadIdx.x + 256 * j;
+        if (i < k4) emit(i, keep[j]);
     }
+    for (int i = threadIdx.x + 256 * KEEP; i < k4; i += 256) emit(i, __ldg(reinterpret_cast<const float4 *>(x) + i));
 }
 
 // ---- weight fragments: what one converter thread handles for one stage (64 K elements of its row, its half of them) ------
@@ -656,7 +672,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
                 const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
                 tc::tmem_ld_wait();
-                if (sg.order == 0 && a.n_peers == 0) {
+                if (sg.order == 0 && a.n_peers == 0 && a.ycol == nullptr) {
+                    // MUL_MAT: output column = activation position, one running pointer instead of a second shuffle per column
+                    float * yp = t.Y + (int64_t) (t.pos0 + c0) * t.m + row;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        const float sc = __shfl_sync(0xffffffffu, my_sc, c);
+                        if (c0 + c < t.nvalid && row < t.m) yp[(int64_t) c * t.m] = __uint_as_float(v[c]) * sc;
+                    }
+                } else if (sg.order == 0 && a.n_peers == 0) {
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
