@@ -672,15 +672,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const float   my_sc = pok ? __ldg(a.colscale + pl) : 0.0f;
                 const int32_t my_yc = pok ? (a.ycol ? __ldg(a.ycol + pl) : pl) : 0;
                 tc::tmem_ld_wait();
-                if (sg.order == 0 && a.n_peers == 0 && a.ycol == nullptr) {
-                    // MUL_MAT: output column = activation position, one running pointer instead of a second shuffle per column
-                    float * yp = t.Y + (int64_t) (t.pos0 + c0) * t.m + row;
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        const float sc = __shfl_sync(0xffffffffu, my_sc, c);
-                        if (c0 + c < t.nvalid && row < t.m) yp[(int64_t) c * t.m] = __uint_as_float(v[c]) * sc;
-                    }
-                } else if (sg.order == 0 && a.n_peers == 0) {
+                if (sg.order == 0 && a.n_peers == 0) {
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
                         const float   sc = __shfl_sync(0xffffffffu, my_sc, c);
