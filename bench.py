@@ -612,6 +612,8 @@ def prefill_rowsplit_bench(torch, dist, pkg, ctx, stream, rank, world, local, n=
                     err = float(((a_ - b_) ** 2).sum() / (b_ ** 2).sum().clamp_min(1e-300))
                     assert err < 1e-10, f"fused prefill row-split gather differs from NCCL all_gather (nmse {err:.3e})"
                 checked = True
+                # nobody may start the next shape (whose fused kernel rewrites every rank's gathered buffer) before all have compared
+                torch.cuda.synchronize(); dist.barrier()
         f = 2.0 * m * n * k
         out[f"{m}x{k}"] = {"fused_us": round(res[0], 1), "nccl_us": round(res[1], 1), "tflops_fused": round(f / res[0] / 1e6, 1)}
         tot_fused += res[0] * count; tot_nccl += res[1] * count; flops += f * count

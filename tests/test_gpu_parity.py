@@ -500,3 +500,27 @@ def test_mul_mat_host_batch_shares_uploads_and_launches(pkg, gpu_ctx):
     # Q4_K groups fuse: {0,1,2} {3} {4,5} {6: q8_0} {7,8,9} {10} -> the q8_0 / q6_K jobs go one by one (2 launches each: quantize + GEMV)
     assert hctx.launches - n0 < 2 * len(specs) - 4
     hctx.close()
+
+
+@pytest.mark.parametrize("m_full,k,n,world", [(1024, 8192, 512, 8), (1024, 1024, 40, 2), (768, 2048, 300, 3)])
+def test_mul_mat_gather_prefill_peer_stores_on_one_gpu(pkg, gpu_ctx, m_full, k, n, world):
+    """row split at prefill size, all `world` ranks emulated on one GPU: every rank's tcgen05 epilogue stores its tiles into all
+    `world` full-height outputs (b200_mul_mat_gather, n > 8) — each of them must equal the unsplit product (to fp32 re-association:
+    the unsplit GEMM may split long K)"""
+    import torch
+    rng = np.random.default_rng(m_full + k + n)
+    t = TYPES["q4_K"]
+    W = dev(random_blocks(t, m_full, k, rng))
+    X = dev(rng.standard_normal((n, k)).astype(np.float32))
+    want = pkg.mul_mat(gpu_ctx, t, W, X)
+    fulls = [torch.full((n, m_full), float("nan"), device="cuda") for _ in range(world)]
+    rows = m_full // world
+    for r in range(world):
+        shard = W[r * rows:(r + 1) * rows].contiguous()
+        ysh = torch.empty((n, rows), device="cuda")
+        pkg.mul_mat_gather(gpu_ctx, t, shard, X, ysh, [f.data_ptr() for f in fulls], m_full, r * rows)
+        gpu_ctx.synchronize()
+        assert nmse(want[:, r * rows:(r + 1) * rows].cpu().numpy(), ysh.cpu().numpy()) < 1e-10
+    for f in fulls:
+        assert torch.isfinite(f).all()
+        assert nmse(want.cpu().numpy(), f.cpu().numpy()) < 1e-10
