@@ -855,7 +855,8 @@ static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_p
         // few of them leave SMs idle: take the tile width with the shorter estimated critical path
         const int64_t t256 = p.row_tiles * ((p.n + 255) / 256) * p.batches, t128 = p.row_tiles * ((p.n + 127) / 128) * p.batches;
         const int64_t w256 = (t256 + units - 1) / units, w128 = (t128 + units - 1) / units;
-        if (ctx->tc_nt == 128 || (ctx->tc_nt == 0 && P.k < 8192 && w128 * 586 < w256 * 836)) p.NT = 128;
+        // (long K normally prefers 256-wide tiles + split K; the fused row-split epilogue cannot split K, so it takes narrow tiles)
+        if (ctx->tc_nt == 128 || (ctx->tc_nt == 0 && (P.k < 8192 || P.n_peers > 0) && w128 * 586 < w256 * 836)) p.NT = 128;
     }
     p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.NT - 1) / p.NT : (n_pos + p.NT - 1) / p.NT + P.n_expert;
     p.n_tiles   = p.row_tiles * p.col_tiles * p.batches;
