@@ -118,6 +118,8 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
     ctx->gemv_cfg      = env_int("GGML_B200_GEMV_CFG", 0);
     ctx->tc_nt         = env_int("GGML_B200_TC_NT", 0);
+    ctx->gemv_rpw      = env_int("GGML_B200_GEMV_RPW", 1);
+    ctx->gemv_rpw_max_m = env_int("GGML_B200_GEMV_RPW_MAX_M", 4096);
     ctx->tc_pdl        = env_int("GGML_B200_TC_PDL", 0);
     ctx->use_mma       = env_int("GGML_B200_USE_MMA", 1);
     ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
@@ -167,6 +169,8 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
     else if (!strcmp(name, "gemv_cfg"))      slot = &ctx->gemv_cfg;
     else if (!strcmp(name, "tc_nt"))         slot = &ctx->tc_nt;
+    else if (!strcmp(name, "gemv_rpw"))      slot = &ctx->gemv_rpw;
+    else if (!strcmp(name, "gemv_rpw_max_m")) slot = &ctx->gemv_rpw_max_m;
     else if (!strcmp(name, "tc_pdl"))        slot = &ctx->tc_pdl;
     else if (!strcmp(name, "use_mma"))       slot = &ctx->use_mma;
     else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;

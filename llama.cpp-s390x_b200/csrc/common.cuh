@@ -95,6 +95,8 @@ struct b200_ctx {
     int64_t      ll_cap;
     uint32_t *   ll_state;       // device: [0] epoch of the last completed exchange, [1] receiver CTAs done
     int          tc_nt;           // tcgen05 GEMM tile width override (0 = auto, 128, 256)
+    int          gemv_rpw_max_m;  // auto rows-per-warp: largest m that gets two rows per warp
+    int          gemv_rpw;        // n=1 Q4_K GEMV: rows per warp below which a matrix does not get more CTAs (1 = default)
     int          gemv_cfg;        // CTA shape of the n=1 Q4_K GEMV: 0 = 32 warps x 1 CTA/SM, 1 = 16x2, 2 = 8x4, 3 = 16x1
     // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)
     const char * pend_lo[16];

@@ -553,7 +553,12 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
     // Small matrices deliberately do NOT spread over every SM: one row per warp is the useful maximum, and the SMs left free
     // let the next GEMV of the stream start (PDL + deferred wait) while this one is still running — measured 2.4 us per
     // 1024x4096 matmul with 32 CTAs against 4.1 us with 148.
-    const int64_t max_useful = (P.m + NWARPS - 1) / NWARPS;
+    // rows per warp that count as "useful" (tuning switch gemv_rpw, default 1; 0 = two rows per warp for 2048 <= m <= gemv_rpw_max_m).
+    // Two rows per warp look better shape by shape (same shape back to back in a graph: 4096x4096 3.92 -> 3.31 us, 4096x14336
+    // 8.91 -> 8.25 us) but make the real step SLOWER (1.110 -> 1.200 ms): half the CTAs live twice as long and delay the large
+    // kernel that follows.  Per-shape timings are not additive; the step is what counts.
+    const int64_t rpw = ctx->gemv_rpw >= 1 ? ctx->gemv_rpw : (P.m >= 2048 && P.m <= ctx->gemv_rpw_max_m ? 2 : 1);
+    const int64_t max_useful = (P.m + NWARPS * rpw - 1) / (NWARPS * rpw);
     if (ctas > max_useful) ctas = max_useful;
     if (ctas < 1) ctas = 1;
     cudaLaunchConfig_t cfg = {};
