@@ -120,6 +120,18 @@ B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * src0, const b200_t
 /* returns 1 if b200_mul_mat accepts this triple, 0 if not (used by supports_op) — no device needed */
 B200_API int b200_mul_mat_supported(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
 
+/* ---- MUL_MAT without any allocation ---------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, shape rules and results
+ * contract as b200_mul_mat, computed by the pre-quantized GEMV route (Q8_1 activation planes -> one integer-dot GEMV), with
+ * the planes in a file-scope static __device__ array of B200_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds
+ * until exit.  Calls no cudaMalloc / cudaFree / allocating library routine.  Limit: the planes of src1,
+ * ncols * k + ncols * (k/32) * 4 bytes (each term rounded up to 256; ncols = ne1 * ne2 * ne3 of src1), must fit the array,
+ * else B200_E_ARG — use b200_mul_mat for bigger activations.  Every call on a device shares the one array (it keeps the last
+ * call's contents; every entry read is rewritten first, nothing needs clearing): calls that overlap on the GPU race. */
+#define B200_NOALLOC_SCRATCH_BYTES (1u << 20)
+B200_API int b200_mul_mat_noalloc(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+
 /* ---- (4) MUL_MAT_ID ----------------------------------------------------------------------------- */
 /* as[k, m, n_expert], b[k, n_used|1, n_tokens] F32, ids[n_used, n_tokens] I32 (may be a strided view),
  * c[m, n_used, n_tokens] F32:  c[:, e, t] = as[:, :, ids[e,t]] . b[:, e % b.ne[1], t]  (ggml/src/ggml.c:3279-3315) */

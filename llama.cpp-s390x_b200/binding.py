@@ -16,6 +16,7 @@ EXPORTS = [
     "b200_abi_version", "b200_last_error", "b200_device_count", "b200_device_info", "b200_blck_size", "b200_type_size",
     "b200_row_size", "b200_ctx_create", "b200_ctx_destroy", "b200_ctx_stream", "b200_ctx_synchronize",
     "b200_ctx_launch_count", "b200_ctx_set_option", "b200_quantize_row_q8_1", "b200_mul_mat", "b200_mul_mat_supported",
+    "b200_mul_mat_noalloc",
     "b200_mul_mat_id", "b200_mul_mat_id_supported", "b200_mm_ids", "b200_weights_upload", "b200_weights_free",
     "b200_mul_mat_host", "b200_mul_mat_host_batch", "b200_mul_mat_gather", "b200_gather_sync_init", "b200_mul_mat_multi", "b200_gather_ll_init", "b200_mul_mat_gather_ll", "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
     "b200_memset", "b200_memcpy_async", "b200_rowsplit_create", "b200_rowsplit_destroy", "b200_rowsplit_n_dev",
@@ -71,6 +72,7 @@ def lib() -> C.CDLL:
     sig("b200_ctx_launch_count", i64, [vp]); sig("b200_ctx_set_option", i32, [vp, C.c_char_p, i32])
     sig("b200_quantize_row_q8_1", i32, [vp, vp, i64, vp, i64, i64])
     sig("b200_mul_mat", i32, [vp, T, T, T]); sig("b200_mul_mat_supported", i32, [T, T, T])
+    sig("b200_mul_mat_noalloc", i32, [vp, T, T, T])
     sig("b200_mul_mat_id", i32, [vp, T, T, T, T]); sig("b200_mul_mat_id_supported", i32, [T, T, T, T])
     sig("b200_mm_ids", i32, [vp, vp, i64, i32, i32, i64, vp, vp])
     sig("b200_weights_upload", i32, [vp, i32, vp, i64, i64, C.POINTER(vp)]); sig("b200_weights_free", None, [vp, vp])

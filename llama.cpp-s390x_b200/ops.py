@@ -66,6 +66,16 @@ def mul_mat(ctx: Context, wtype: int, w, x, out=None):
     return out
 
 
+def mul_mat_noalloc(ctx: Context, wtype: int, w, x, out):
+    """b200_mul_mat_noalloc: same contract as mul_mat, the caller passes `out`; nothing is allocated inside the call (the
+    activation planes live in the library's static device scratch, B200_NOALLOC_SCRATCH_BYTES)"""
+    a = _desc(w, wtype, k_elems=x.shape[-1])
+    b = _desc(x, F32)
+    d = _desc(out, F32)
+    check(lib().b200_mul_mat_noalloc(ctx.handle, C.byref(a), C.byref(b), C.byref(d)), "b200_mul_mat_noalloc")
+    return out
+
+
 def mul_mat_multi(ctx: Context, wtype: int, ws, x, outs=None):
     """outs[j] = ws[j] x x for several weight matrices sharing the activations (q/k/v, gate/up) — one launch when fusable"""
     import torch
