@@ -101,7 +101,7 @@ B200_API int   b200_ctx_synchronize(b200_ctx * ctx);
 B200_API int64_t b200_ctx_launch_count(const b200_ctx * ctx);
 /* tuning knobs (also read once from the GGML_B200_* environment): name in
  * {"force_generic","use_tc","max_gemv_cols","pdl","fuse_quant","defer_wait","gemv_cfg","use_mma","mma_min_n","mma_ks","mma_ch",
- *  "tc_pair","tc_nt","tc_split_k","noop"}; returns the previous value or B200_E_ARG */
+ *  "tc_pair","tc_nt","tc_split_k","noop","use_stream","stream_min_jobs","stream_stages"}; returns the previous value or B200_E_ARG */
 B200_API int   b200_ctx_set_option(b200_ctx * ctx, const char * name, int value);
 
 /* ---- (1) activation quantizer ------------------------------------------------------------------- */
@@ -174,6 +174,17 @@ B200_API int  b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs,
  * (src/llama-graph.cpp build_attn / build_ffn -> ggml_mul_mat per weight); here matrices of equal type and row length share
  * one launch — a single activation prologue, one grid — with results bit-identical to n_mats b200_mul_mat calls. */
 B200_API int  b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b,
+                                 const b200_tensor * const * d);
+
+/* A list of MUL_MATs in one call, executed as if in list order (a later job may read what an earlier one wrote): what
+ * ggml_backend_graph_compute hands a backend when a cgraph holds several MUL_MAT nodes (ggml/src/ggml-backend.cpp:444-448;
+ * test-backend-ops' perf mode builds such graphs, tests/test-backend-ops.cpp:1455-1583) and what the reference's CUDA backend
+ * replays as one CUDA graph (ggml/src/ggml-cuda/ggml-cuda.cu:4457-4490).  Runs of Q4_K matmuls with one activation column go
+ * through ONE persistent launch: a grid of one CTA per SM walks the list with per-warp shared-memory rings fed by bulk async
+ * copies, so the weight stream does not drain between matrices; consecutive jobs with the same src1 share one quantized
+ * copy of it; dependencies between jobs are found from the tensors' address ranges and waited for inside the kernel.
+ * Results are bit-identical to n_jobs b200_mul_mat calls.  Everything else in the list runs as b200_mul_mat[_multi]. */
+B200_API int  b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
                                  const b200_tensor * const * d);
 
 /* ---- row split, one process per GPU -------------------------------------------------------------- */

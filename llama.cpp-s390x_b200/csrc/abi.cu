@@ -3,6 +3,7 @@
 // fallback: if CUDA is unavailable every call returns B200_E_CUDA.
 #include "mm_problem.cuh"
 #include "quantize.cuh"
+#include "stream_jobs.cuh"
 
 #include <cstdarg>
 #include <vector>
@@ -129,6 +130,9 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->tc_split_k   = env_int("GGML_B200_TC_SPLIT_K", 1);
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
+    ctx->use_stream    = env_int("GGML_B200_USE_STREAM", 1);
+    ctx->stream_min_jobs = env_int("GGML_B200_STREAM_MIN_JOBS", 2);
+    ctx->stream_stages = env_int("GGML_B200_STREAM_STAGES", 0);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
     *out = ctx;
@@ -142,6 +146,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->ws) cudaFree(ctx->ws);
     if (ctx->gs_state) cudaFree(ctx->gs_state);
     if (ctx->ll_state) cudaFree(ctx->ll_state);
+    if (ctx->sq_done) cudaFree(ctx->sq_done);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
@@ -180,6 +185,9 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "tc_split_k"))   slot = &ctx->tc_split_k;
     else if (!strcmp(name, "noop"))          slot = &ctx->noop;
     else if (!strcmp(name, "defer_wait"))    slot = &ctx->defer_wait;
+    else if (!strcmp(name, "use_stream"))    slot = &ctx->use_stream;
+    else if (!strcmp(name, "stream_min_jobs")) slot = &ctx->stream_min_jobs;
+    else if (!strcmp(name, "stream_stages")) slot = &ctx->stream_stages;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
     const int prev = *slot;
     *slot = value;
@@ -673,6 +681,108 @@ int b200_mul_mat_multi(b200_ctx * ctx, int n_mats, const b200_tensor * const * a
     for (int j = 0; j < n_mats; ++j) {
         const int rc = b200_mul_mat(ctx, a[j], b, d[j]);
         if (rc) return rc;
+    }
+    return B200_OK;
+}
+
+// ---- a list of matmuls in one call: what graph_compute sees when a cgraph holds several MUL_MAT nodes ---------------------------
+// Runs of Q4_K n = 1 matmuls go through ONE persistent launch (mmvq_stream.cu); the job table, its activation groups and the
+// dependencies between its jobs are resolved here, on the host, from the tensors' address ranges.
+static bool stream_job_ok(const b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    return a->type == B200_TYPE_Q4_K && b->ne[1] == 1 && b->ne[2] * b->ne[3] == 1 && a->ne[2] * a->ne[3] == 1 &&
+           a->ne[0] % 256 == 0 && a->ne[0] / 256 <= 65535 && a->ne[1] >= 1 && a->ne[1] < ((int64_t) 1 << 31) && a->nb[1] < ((int64_t) 1 << 32) &&
+           aligned16(a->data, a->nb[1], 0, 0) && aligned16(b->data, 0, 0, 0) && ((uintptr_t) d->data & 3) == 0 &&
+           b200_gemv_stream_stages(ctx, a->ne[0]) >= 2;
+}
+
+static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, const b200_tensor * const * b, const b200_tensor * const * d) {
+    if (!ctx->sq_done) {
+        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_done, (SQ_MAX_JOBS + 1) * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_done, 0, (SQ_MAX_JOBS + 1) * sizeof(uint32_t), ctx->stream));
+    }
+    static thread_local sq_params P;                        // 24 KB: not on the stack of every caller
+    memset(&P, 0, offsetof(sq_params, jobs));
+    P.n_jobs = n; P.done = ctx->sq_done;
+    const uint32_t G = (uint32_t) ctx->sm_count;
+    std::vector<const char *> xlo((size_t) n), xhi((size_t) n), ylo((size_t) n), yhi((size_t) n);
+    int group = -1, group_first = 0, group_size = 0;
+    const char * xbox_lo = nullptr, * xbox_hi = nullptr, * ybox_lo = nullptr, * ybox_hi = nullptr;
+    for (int j = 0; j < n; ++j) {
+        sq_job & J = P.jobs[j];
+        J.W = (const uint8_t *) a[j]->data; J.X = (const float *) b[j]->data; J.Y = (float *) d[j]->data;
+        J.nb01 = (uint32_t) a[j]->nb[1]; J.m = (uint32_t) a[j]->ne[1];
+        J.base = J.m / G; J.rem = J.m % G;
+        J.nsb = (uint16_t) (a[j]->ne[0] / 256);
+        J.dep = -1; J.flags = 0;
+        if (a[j]->ne[0] > P.kmax) P.kmax = (int) a[j]->ne[0];
+        xlo[j] = (const char *) J.X; xhi[j] = xlo[j] + 4 * a[j]->ne[0];
+        ylo[j] = (const char *) J.Y; yhi[j] = ylo[j] + 4 * a[j]->ne[1];
+        if (xlo[j] < yhi[j] && ylo[j] < xhi[j]) { b200_set_error("mul_mat_batch[%d]: dst overlaps src1", j); return B200_E_ARG; }
+        // the LAST earlier job this one must come after: it wrote what this one reads (RAW) or writes (WAW), or read what this one
+        // writes (WAR).  Completion is counted cumulatively (all jobs <= dep are complete), so the last one is enough.
+        int dep = -1;
+        // (bounding boxes of everything earlier: the usual list has no overlaps at all and skips the scan)
+        const bool maybe = (xlo[j] < ybox_hi && ybox_lo < xhi[j]) || (ylo[j] < ybox_hi && ybox_lo < yhi[j]) || (ylo[j] < xbox_hi && xbox_lo < yhi[j]);
+        for (int i = maybe ? j - 1 : -1; i >= 0; --i) {
+            const bool raw = xlo[j] < yhi[i] && ylo[i] < xhi[j];
+            const bool waw = ylo[j] < yhi[i] && ylo[i] < yhi[j];
+            const bool war = ylo[j] < xhi[i] && xlo[i] < yhi[j];
+            if (raw || waw || war) { dep = i; break; }
+        }
+        if (j == 0 || xlo[j] < xbox_lo) xbox_lo = xlo[j];
+        if (j == 0 || xhi[j] > xbox_hi) xbox_hi = xhi[j];
+        if (j == 0 || ylo[j] < ybox_lo) ybox_lo = ylo[j];
+        if (j == 0 || yhi[j] > ybox_hi) ybox_hi = yhi[j];
+        const bool join = j > 0 && J.X == P.jobs[j - 1].X && J.nsb == P.jobs[j - 1].nsb && group_size < SQ_MAX_GROUP && dep < group_first;
+        if (join) {
+            group_size++;
+            if (dep > P.jobs[group_first].dep) P.jobs[group_first].dep = (int16_t) dep;
+        } else {
+            group++; group_first = j; group_size = 1;
+            J.dep = (int16_t) dep;
+        }
+        J.xg = (uint16_t) group;
+    }
+    P.n_groups = group + 1;
+    for (int j = 0; j < n; ++j) {
+        if (P.jobs[j].dep >= 0 && !(P.jobs[P.jobs[j].dep].flags & 1)) { P.jobs[P.jobs[j].dep].flags |= 1; P.n_flagged++; }
+    }
+    // everything before this launch is complete when its CTAs pass griddepcontrol.wait (no deferred wait here)
+    ctx->n_pend = 0;
+    return b200_launch_gemv_stream(ctx, P);
+}
+
+extern "C" int b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
+                                  const b200_tensor * const * d) {
+    if (!ctx || n_jobs < 0 || (n_jobs > 0 && (!a || !b || !d))) { b200_set_error("mul_mat_batch: bad argument"); return B200_E_ARG; }
+    for (int j = 0; j < n_jobs; ++j) {
+        if (const char * why = check_mul_mat(a[j], b[j], d[j])) { b200_set_error("mul_mat_batch[%d]: %s", j, why); return B200_E_ARG; }
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    for (int j = 0; j < n_jobs; ) {
+        // a run of jobs the persistent kernel takes
+        int e = j;
+        if (ctx->use_stream && !ctx->force_generic && ctx->fuse_quant) {
+            int64_t kmax = 0;
+            while (e < n_jobs && e - j < SQ_MAX_JOBS && a[e]->ne[1] > 0 && stream_job_ok(ctx, a[e], b[e], d[e])) {
+                const int64_t k2 = a[e]->ne[0] > kmax ? a[e]->ne[0] : kmax;
+                if (b200_gemv_stream_stages(ctx, k2) < 2) break;
+                kmax = k2; ++e;
+            }
+        }
+        if (e - j >= (ctx->stream_min_jobs > 1 ? ctx->stream_min_jobs : 1)) {
+            const int rc = stream_run(ctx, e - j, a + j, b + j, d + j);
+            if (rc) return rc;
+            j = e;
+            continue;
+        }
+        // otherwise: the matrices that share their activations in one launch (q / k / v, gate / up), everything else one by one
+        e = j + 1;
+        while (e < n_jobs && e - j < 3 && b[e]->data == b[j]->data && b[e]->ne[1] == b[j]->ne[1] && b[e]->nb[1] == b[j]->nb[1] &&
+               b[e]->ne[2] * b[e]->ne[3] == 1 && b[j]->ne[2] * b[j]->ne[3] == 1 && a[e]->type == a[j]->type && a[e]->ne[0] == a[j]->ne[0]) ++e;
+        const int rc = e - j == 1 ? b200_mul_mat(ctx, a[j], b[j], d[j]) : b200_mul_mat_multi(ctx, e - j, a + j, b[j], d + j);
+        if (rc) return rc;
+        j = e;
     }
     return B200_OK;
 }

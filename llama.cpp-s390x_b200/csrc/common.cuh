@@ -109,6 +109,11 @@ struct b200_ctx {
     int          mma_ch;          // tensor-core GEMV: super-blocks per ring stage override (0 = auto, 1)
     int          mma_ks;          // tensor-core GEMV: K slices per row block override (0 = auto; 1, 2, 4, 8, 16)
     int          noop;            // debugging: GEMV kernels return immediately (measures the launch floor)
+    // persistent job-table GEMV (mmvq_stream.cu, b200_mul_mat_batch)
+    int          use_stream;      // 1: runs of Q4_K n = 1 matmuls of a batch go through one persistent launch
+    int          stream_min_jobs; // shortest run that takes the persistent kernel
+    int          stream_stages;   // ring slots per warp override (0 = auto)
+    uint32_t *   sq_done;         // device: [SQ_MAX_JOBS + 1] completion counters + ticket, zero between launches
 };
 
 int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes);   // ensures ctx->ws_size >= nbytes

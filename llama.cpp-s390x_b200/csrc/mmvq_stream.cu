@@ -1,0 +1,408 @@
+// mmvq_stream.cu — the decode path as ONE persistent kernel per list of matmuls ("job table").
+//
+// Why: a decoder-layer GEMV at n = 1 streams 2-33 MB, i.e. 0.4-5 us of HBM time; launched one kernel per matmul, every one of them
+// pays launch -> resolve -> first DRAM round trip -> activation prologue -> tail (measured ~3.6 us of fixed cost per launch, 0.58 of
+// the HBM roofline over a Llama-3-8B step).  Here a single grid of one CTA per SM walks the whole list:
+//   * every consumer warp owns a private ring of shared-memory slots that an elected lane keeps filled with bulk async copies
+//     (cp.async.bulk global -> shared, mbarrier complete_tx) of its NEXT row-pair chunks — across matrix boundaries, so the
+//     weight stream never drains between matmuls and up to ~190 KB per SM stay in flight;
+//   * four quantizer warps turn the activation vector of the NEXT group of matmuls into Q8_1 values (bit-exact with
+//     quantize_row_q8_1_ref, same code as everywhere in this library) in a second shared-memory buffer while the consumers are
+//     still on the current one (full / empty mbarriers);
+//   * a matmul whose activations are produced by an earlier matmul of the same list waits on a per-job completion counter in
+//     global memory (all CTAs done with that job) — only the quantizer warps wait, the weight rings keep filling.
+// The arithmetic per row is the one of gemv_q4k (mmvq.cu): same lane mapping, same operation order, same warp reduction, so the
+// results are BIT-IDENTICAL to b200_mul_mat and independent of how rows are distributed over CTAs and warps.
+//
+// Reference behaviour replaced: the vec_dot loop of ggml_compute_forward_mul_mat (/root/reference/ggml/src/ggml-cpu/ggml-cpu.c:1241-1439)
+// with ggml_vec_dot_q4_K_q8_K's block algebra (ggml/src/ggml-cpu/quants.c:645-718), for all MUL_MAT nodes of a graph at once.
+#include "stream_jobs.cuh"
+#include "quantize.cuh"
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int SQ_NCW      = 28;                        // consumer warps
+constexpr int SQ_NQW      = 4;                         // quantizer warps
+constexpr int SQ_THREADS  = (SQ_NCW + SQ_NQW) * 32;
+constexpr int SQ_CHUNK_SB = 8;                         // super-blocks of one row per chunk (one per 4 lanes)
+constexpr int SQ_CHUNK_B  = SQ_CHUNK_SB * SZ_Q4_K;     // 1152
+constexpr int SQ_SLOT_B   = 2 * SQ_CHUNK_B;            // a ring slot: the same chunk of two consecutive rows
+constexpr int SQ_MAX_S    = 4;
+constexpr int SQ_NCNT     = 256;                       // CTA-level row counters, indexed by job % SQ_NCNT (see SQ_MAX_GROUP)
+
+// shared memory: [barriers | slot meta | row counters | x buffer 0 | x buffer 1 | rings]
+constexpr int OFF_FULL  = 0;                                         // [SQ_NCW][SQ_MAX_S] u64
+constexpr int OFF_XFULL = OFF_FULL + SQ_NCW * SQ_MAX_S * 8;          // [2] u64
+constexpr int OFF_XEMPTY = OFF_XFULL + 16;                           // [2] u64
+constexpr int OFF_META  = OFF_XEMPTY + 16;                           // [SQ_NCW][SQ_MAX_S] uint2
+constexpr int OFF_CNT   = OFF_META + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NCNT] u32
+constexpr int OFF_X     = (OFF_CNT + SQ_NCNT * 4 + 127) / 128 * 128;
+
+__host__ __device__ constexpr int sq_xbytes(int kmax) { return kmax + kmax / 4; }
+__host__ __device__ constexpr int sq_ring_off(int kmax) { return (OFF_X + 2 * sq_xbytes(kmax) + 127) / 128 * 128; }
+__host__ __device__ constexpr size_t sq_smem(int kmax, int stages) { return (size_t) sq_ring_off(kmax) + (size_t) SQ_NCW * stages * SQ_SLOT_B; }
+
+__device__ __forceinline__ int act_slot(int t) { return t ^ (((t >> 3) & 1) << 1) ^ ((t >> 4) & 1); }     // as in mmvq.cu
+
+__device__ __forceinline__ int dp4a_us(uint32_t a_unsigned, int b_signed, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_unsigned), "r"(b_signed), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+    return r;
+}
+__device__ __forceinline__ float4 ld_cg_f4(const float * p) {        // L2-coherent: X may have been written by other SMs during this launch
+    float4 r;
+    asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+struct act_frag { uint4 a0, a1, a2, a3; float4 e; };
+
+// one lane's share of one super-block of one row: 64 weights (sub-blocks 2g, 2g+1) — the operation sequence of q4k_task (mmvq.cu)
+__device__ __forceinline__ float q4k_dot(const uint4 hdr, const uint4 q0, const uint4 q1, const int g, const act_frag & A, float r) {
+    const int sh = 16 * (g & 1);
+    const uint32_t a = hdr.y >> sh, b = hdr.z >> sh, c = hdr.w >> sh;
+    uint32_t scp, mnp;
+    if (g < 2) {
+        scp = a & 0x3f3f;
+        mnp = b & 0x3f3f;
+    } else {
+        scp = (c & 0x0f0f) | ((a & 0xc0c0) >> 2);
+        mnp = ((c >> 4) & 0x0f0f) | ((b & 0xc0c0) >> 2);
+    }
+    const float2 dm  = __half22float2(*reinterpret_cast<const half2 *>(&hdr.x));
+    const float dsc0 = dm.x * (float) (scp & 0xff);
+    const float dsc1 = dm.x * (float) (scp >> 8) * 0.0625f;          // high nibbles enter the dot product as 16*q
+    const float dmn0 = dm.y * (float) (mnp & 0xff);
+    const float dmn1 = dm.y * (float) (mnp >> 8);
+    const uint32_t m_lo = 0x0F0F0F0Fu, m_hi = 0xF0F0F0F0u;
+    int s0 = __dp4a((int) (q0.x & m_lo), (int) A.a0.x, 0);
+    s0 = __dp4a((int) (q0.y & m_lo), (int) A.a0.y, s0); s0 = __dp4a((int) (q0.z & m_lo), (int) A.a0.z, s0); s0 = __dp4a((int) (q0.w & m_lo), (int) A.a0.w, s0);
+    s0 = __dp4a((int) (q1.x & m_lo), (int) A.a1.x, s0); s0 = __dp4a((int) (q1.y & m_lo), (int) A.a1.y, s0);
+    s0 = __dp4a((int) (q1.z & m_lo), (int) A.a1.z, s0); s0 = __dp4a((int) (q1.w & m_lo), (int) A.a1.w, s0);
+    int s1 = dp4a_us(q0.x & m_hi, (int) A.a2.x, 0);
+    s1 = dp4a_us(q0.y & m_hi, (int) A.a2.y, s1); s1 = dp4a_us(q0.z & m_hi, (int) A.a2.z, s1); s1 = dp4a_us(q0.w & m_hi, (int) A.a2.w, s1);
+    s1 = dp4a_us(q1.x & m_hi, (int) A.a3.x, s1); s1 = dp4a_us(q1.y & m_hi, (int) A.a3.y, s1);
+    s1 = dp4a_us(q1.z & m_hi, (int) A.a3.z, s1); s1 = dp4a_us(q1.w & m_hi, (int) A.a3.w, s1);
+    r = fmaf(dsc0 * A.e.x, (float) s0, r);
+    r = fmaf(dsc1 * A.e.z, (float) s1, r);
+    r = fmaf(-dmn0, A.e.y, r);
+    r = fmaf(-dmn1, A.e.w, r);
+    return r;
+}
+
+// the sequence of (job, row pair, chunk) steps of one consumer warp
+struct sq_cursor {
+    int      j;          // current job; == n_jobs: exhausted
+    uint32_t row;        // first row of the current pair
+    uint32_t rhi;        // end of this CTA's rows of job j
+    int      c, nch;     // next chunk, chunks per row
+    uint32_t rot;        // pairs of the CTA dealt so far, mod SQ_NCW: pair p of job j goes to warp (rot + p) % SQ_NCW
+};
+
+__device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
+    const uint32_t b = blockIdx.x;
+    while (cu.j < P.n_jobs) {
+        const sq_job & J = P.jobs[cu.j];
+        const uint32_t cnt    = J.base + (b < J.rem ? 1u : 0u);
+        const uint32_t npairs = (cnt + 1) >> 1;
+        const uint32_t pos    = warp >= cu.rot ? warp - cu.rot : warp + SQ_NCW - cu.rot;
+        if (pos < npairs) {
+            const uint32_t rlo = b * J.base + (b < J.rem ? b : J.rem);
+            cu.row = rlo + 2 * pos;
+            cu.rhi = rlo + cnt;
+            cu.c   = 0;
+            cu.nch = (J.nsb + SQ_CHUNK_SB - 1) / SQ_CHUNK_SB;
+            return;
+        }
+        cu.rot = (cu.rot + npairs) % SQ_NCW;
+        cu.j++;
+    }
+}
+
+__device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
+    if (++cu.c < cu.nch) return;
+    cu.c = 0;
+    cu.row += 2 * SQ_NCW;
+    if (cu.row < cu.rhi) return;
+    const sq_job & J = P.jobs[cu.j];
+    const uint32_t cnt = J.base + (blockIdx.x < J.rem ? 1u : 0u);
+    cu.rot = (cu.rot + ((cnt + 1) >> 1)) % SQ_NCW;
+    cu.j++;
+    sq_seek(P, cu, warp);
+}
+
+__global__ void __launch_bounds__(SQ_THREADS, 1)
+gemv_q4k_stream(const __grid_constant__ sq_params P) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t sbase = tc::smem_u32(smem);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = P.stages;
+    const int xbytes = sq_xbytes(P.kmax);
+
+    if (tid == 0) {
+        for (int i = 0; i < SQ_NCW * SQ_MAX_S; ++i) tc::mbar_init(sbase + OFF_FULL + 8 * i, 1);
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(sbase + OFF_XFULL + 8 * i, SQ_NQW * 32);
+            tc::mbar_init(sbase + OFF_XEMPTY + 8 * i, SQ_NCW);
+        }
+        tc::mbar_fence_init();
+    }
+    if (tid < SQ_NCNT) reinterpret_cast<uint32_t *>(smem + OFF_CNT)[tid] = 0;
+    __syncthreads();
+
+    if (warp < SQ_NCW) {
+        // ================================================= consumer warp ================================================
+        const uint32_t bar0  = sbase + OFF_FULL + (uint32_t) warp * SQ_MAX_S * 8;
+        const uint32_t meta0 = sbase + OFF_META + (uint32_t) warp * SQ_MAX_S * 8;
+        const uint32_t ring0 = sbase + (uint32_t) sq_ring_off(P.kmax) + (uint32_t) (warp * S) * SQ_SLOT_B;
+        const int sbl = lane >> 2, g = lane & 3;
+        const int xsw = ((g >> 1) << 1) ^ (sbl & 1);
+        // lane-constant byte offsets: weights inside a chunk, activations inside a chunk's 8 super-blocks
+        const uint32_t w_off = (uint32_t) sbl * SZ_Q4_K;
+        const uint32_t q_off = w_off + 16 + 32 * g;
+        const uint32_t a_off = (uint32_t) (sbl * 16 + 4 * g) * 16;
+        const uint32_t e_off = (uint32_t) P.kmax + (uint32_t) (sbl * 8 + 2 * g) * 8;
+
+        sq_cursor pc;                                     // producer cursor: S steps ahead of the consumer
+        pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0;
+        sq_seek(P, pc, (uint32_t) warp);
+        auto fill = [&](const int slot) {
+            const sq_job & J = P.jobs[pc.j];
+            const int      left  = (int) J.nsb - pc.c * SQ_CHUNK_SB;
+            const uint32_t bytes = (uint32_t) (left < SQ_CHUNK_SB ? left : SQ_CHUNK_SB) * SZ_Q4_K;
+            const bool     two   = pc.row + 1 < pc.rhi;
+            const bool     last  = pc.c + 1 == pc.nch;
+            const uint8_t * src  = J.W + (size_t) pc.row * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
+            const uint32_t dst   = ring0 + (uint32_t) slot * SQ_SLOT_B;
+            const uint32_t bar   = bar0 + 8 * slot;
+            if (tc::elect_one()) {
+                const uint32_t m1 = (uint32_t) pc.j | ((uint32_t) pc.c << 16) | (two ? 1u << 30 : 0u) | (last ? 1u << 31 : 0u);
+                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(meta0 + 8 * slot), "r"(pc.row), "r"(m1) : "memory");
+                tc::mbar_arrive_expect_tx(bar, two ? 2 * bytes : bytes);
+                bulk_g2s(dst, src, bytes, bar);
+                if (two) bulk_g2s(dst + SQ_CHUNK_B, src + J.nb01, bytes, bar);
+            }
+            __syncwarp();
+            sq_advance(P, pc, (uint32_t) warp);
+        };
+        int produced = 0, consumed = 0;
+        // weights are never written by a kernel of this path: the rings are filled before the dependency wait
+        for (int s = 0; s < S && pc.j < P.n_jobs; ++s) { fill(s); produced++; }
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+        int   slot = 0;
+        uint32_t phase = 0;
+        int   cur_g = -1;
+        float accA = 0.0f, accB = 0.0f;
+        uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
+        // move on to activation group `want`: hand the buffers of finished groups back, wait for the new one
+        auto enter_group = [&](const int want) {
+            while (cur_g < want) {
+                if (cur_g >= 0) {
+                    __syncwarp();                            // every lane has finished reading the old buffer
+                    if (lane == 0) tc::mbar_arrive(sbase + OFF_XEMPTY + 8 * (cur_g & 1));
+                }
+                cur_g++;
+                if (cur_g < P.n_groups) tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), (uint32_t) (cur_g >> 1) & 1u, 20);
+            }
+        };
+        // Completion accounting (only when a later group of the list waits for an earlier job): a warp "passes" job j once all
+        // its rows of the jobs <= j are stored — it walks the list in order — and checks in on a CTA counter; the CTA reports job
+        // j as done when its 28 consumer warps and its quantizers (which have then read the job's activations) have checked in.
+        // done[j] == grid therefore means: every row of every job <= j is stored, and nobody will read their activations again.
+        // The check-in comes BEFORE the wait for the next group's activations, which may be what is waiting for it.
+        int passed = 0;
+        auto pass_jobs = [&](const int upto) {
+            if (P.n_flagged && lane == 0) {
+                for (int jj = passed; jj < upto; ++jj) {
+                    if (!(P.jobs[jj].flags & 1)) continue;
+                    __threadfence();
+                    if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
+                        cnt[jj & (SQ_NCNT - 1)] = 0;
+                        __threadfence();
+                        atomicAdd(P.done + jj, 1u);
+                    }
+                }
+            }
+            passed = upto;
+        };
+        while (consumed < produced) {
+            uint32_t row, m1;                                 // (the slot's description was written when its fill was issued)
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(row), "=r"(m1) : "r"(meta0 + 8 * slot) : "memory");
+            const int  j    = (int) (m1 & 0xffffu);
+            const int  c    = (int) ((m1 >> 16) & 0x3fffu);
+            const bool two  = (m1 >> 30) & 1u;
+            const bool last = (m1 >> 31) & 1u;
+            const sq_job & J = P.jobs[j];
+            if (j > passed) pass_jobs(j);
+            if ((int) J.xg != cur_g) enter_group((int) J.xg);
+            tc::mbar_wait(bar0 + 8 * slot, phase);
+            const int sb = c * SQ_CHUNK_SB + sbl;
+            if (sb < (int) J.nsb) {
+                const uint32_t xb = sbase + OFF_X + (uint32_t) (cur_g & 1) * (uint32_t) xbytes;
+                const uint32_t ab = xb + (uint32_t) c * (SQ_CHUNK_SB * 256) + a_off;
+                act_frag A;
+                A.a0 = lds128(ab + 16 * (0 ^ xsw));
+                A.a1 = lds128(ab + 16 * (1 ^ xsw));
+                A.a2 = lds128(ab + 16 * (2 ^ xsw));
+                A.a3 = lds128(ab + 16 * (3 ^ xsw));
+                const uint4 ev = lds128(xb + (uint32_t) c * (SQ_CHUNK_SB * 64) + e_off);
+                A.e = make_float4(__uint_as_float(ev.x), __uint_as_float(ev.y), __uint_as_float(ev.z), __uint_as_float(ev.w));
+                const uint32_t ws = ring0 + (uint32_t) slot * SQ_SLOT_B;
+                {
+                    const uint4 hdr = lds128(ws + w_off), q0 = lds128(ws + q_off), q1 = lds128(ws + q_off + 16);
+                    accA = q4k_dot(hdr, q0, q1, g, A, accA);
+                }
+                if (two) {
+                    const uint4 hdr = lds128(ws + SQ_CHUNK_B + w_off), q0 = lds128(ws + SQ_CHUNK_B + q_off), q1 = lds128(ws + SQ_CHUNK_B + q_off + 16);
+                    accB = q4k_dot(hdr, q0, q1, g, A, accB);
+                }
+            }
+            if (last) {
+                const float sA = warp_sum(accA);
+                const float sB = warp_sum(accB);
+                if (lane == 0) {
+                    J.Y[row] = sA;
+                    if (two) J.Y[row + 1] = sB;
+                }
+                accA = 0.0f; accB = 0.0f;
+            }
+            // the slot has been read (values are in registers): refill it with the step S ahead
+            __syncwarp();
+            if (pc.j < P.n_jobs) { fill(slot); produced++; }
+            consumed++;
+            if (++slot == S) { slot = 0; phase ^= 1u; }
+        }
+        pass_jobs(P.n_jobs);
+        enter_group(P.n_groups);                              // pass the remaining groups so that the quantizers can finish
+    } else {
+        // ================================================= quantizer warps ==============================================
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        const int qt  = tid - SQ_NCW * 32;                    // 0 .. 127
+        const int sub = qt & 7;
+        int jq = 0;
+        for (int gidx = 0; gidx < P.n_groups; ++gidx) {
+            while (jq < P.n_jobs && (int) P.jobs[jq].xg < gidx) jq++;
+            const sq_job & J = P.jobs[jq];
+            const int b = gidx & 1;
+            if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, (uint32_t) ((gidx >> 1) - 1) & 1u, 20);
+            if (J.dep >= 0) {
+                // every CTA has finished job `dep` (rows stored, its activations read)
+                const uint32_t * flag = P.done + J.dep;
+                uint32_t seen;
+                const long long t0 = clock64();
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+                    if (seen >= gridDim.x) break;
+                    __nanosleep(20);
+                    if (clock64() - t0 > 8000000000LL) __trap();      // a broken dependency must not hang the box
+                } while (true);
+            }
+            uint8_t * s_qs = smem + OFF_X + (size_t) b * xbytes;
+            float2 *  s_ds = reinterpret_cast<float2 *>(s_qs + P.kmax);
+            const int nbk = (int) J.nsb * 8;
+            const float * x = J.X;
+            constexpr int QG = SQ_NQW * 4;                    // 32-value blocks per round
+            for (int ib0 = 0; ib0 < nbk; ib0 += 4 * QG) {
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int ib = ib0 + u * QG + (qt >> 3);
+                    v[u] = ld_cg_f4(x + (ib < nbk ? ib : nbk - 1) * 32 + sub * 4);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int ib = ib0 + u * QG + (qt >> 3);
+                    const q8_part qp = quantize_q8_1_part(v[u]);
+                    if (ib < nbk) {
+                        const int t = ib * 2 + (sub >> 2);
+                        *reinterpret_cast<uint32_t *>(s_qs + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
+                        if (sub == 0) s_ds[ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+                    }
+                }
+            }
+            tc::mbar_arrive(sbase + OFF_XFULL + 8 * b);
+            // the quantizers' check-in for the flagged jobs of this group: their activations have been read by this CTA
+            if (P.n_flagged) {
+                bool any = false;
+                for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) any = any || (P.jobs[jj].flags & 1);
+                if (any) {
+                    asm volatile("bar.sync 1, %0;" :: "n"(SQ_NQW * 32) : "memory");       // all 128 quantizer threads have their values
+                    if (qt == 0) {
+                        uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
+                        for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) {
+                            if (!(P.jobs[jj].flags & 1)) continue;
+                            if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
+                                cnt[jj & (SQ_NCNT - 1)] = 0;
+                                __threadfence();
+                                atomicAdd(P.done + jj, 1u);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    if (P.n_flagged) {
+        // the last CTA to finish leaves the counters at zero for the next launch (nobody polls them any more)
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            if (atomicAdd(P.done + SQ_MAX_JOBS, 1u) == gridDim.x - 1) {
+                for (int j = 0; j < P.n_jobs; ++j) P.done[j] = 0;
+                P.done[SQ_MAX_JOBS] = 0;
+            }
+        }
+    }
+}
+
+}  // namespace
+
+int b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax) {
+    if (kmax <= 0 || kmax % 256 != 0 || kmax > (1 << 20)) return 0;
+    for (int s = SQ_MAX_S; s >= 2; --s) {
+        if (sq_smem((int) kmax, s) <= ctx->smem_optin) return s > 3 ? 3 : s;     // (3 slots = 6.9 KB per warp already cover the latency)
+    }
+    return 0;
+}
+
+int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
+    if (P.n_jobs <= 0) return B200_OK;
+    if (P.n_jobs > SQ_MAX_JOBS || P.n_groups < 1 || P.n_groups > P.n_jobs) { b200_set_error("gemv_stream: bad job table"); return B200_E_ARG; }
+    P.stages = ctx->stream_stages > 0 ? ctx->stream_stages : b200_gemv_stream_stages(ctx, P.kmax);
+    if (P.stages < 2 || P.stages > SQ_MAX_S || sq_smem(P.kmax, P.stages) > ctx->smem_optin) {
+        b200_set_error("gemv_stream: k = %d does not fit the shared-memory rings", P.kmax); return B200_E_UNSUPPORTED;
+    }
+    const size_t smem = sq_smem(P.kmax, P.stages);
+    static bool attr_done[16] = {};            // per device
+    if (!attr_done[ctx->device & 15]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
+        attr_done[ctx->device & 15] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim          = dim3((unsigned) ctx->sm_count);
+    cfg.blockDim         = dim3(SQ_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream           = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs    = attr;
+    cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_q4k_stream, P));
+    ctx->launches++;
+    return B200_OK;
+}

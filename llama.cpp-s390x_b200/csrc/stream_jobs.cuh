@@ -1,0 +1,41 @@
+// stream_jobs.cuh — the job table of the persistent decode GEMV (mmvq_stream.cu), shared with its host-side builder (abi.cu).
+//
+// One launch = one list of Q4_K n = 1 MUL_MATs executed "as if in list order": what ggml_backend_graph_compute hands a backend
+// when a cgraph holds several MUL_MAT nodes (/root/reference/ggml/src/ggml-backend.cpp:444-448 -> graph_compute; the perf mode
+// of test-backend-ops builds exactly such graphs, tests/test-backend-ops.cpp:1455-1583) and what the reference's CUDA backend
+// turns into ONE CUDA-graph launch (ggml/src/ggml-cuda/ggml-cuda.cu:4457-4490).  Here the list is a kernel PARAMETER
+// (__grid_constant__, <= 32 KB), so a launch needs no table upload and is capturable as is.
+#pragma once
+#include "common.cuh"
+
+#define SQ_MAX_JOBS    512      // per launch (longer lists are cut into several launches)
+#define SQ_MAX_GROUP   64       // jobs that may share one quantized activation vector (bounds the live window of the CTA counters)
+
+struct sq_job {
+    const uint8_t * W;          // first row of the [m, k] Q4_K matrix (or row shard), 16-byte aligned
+    const float *   X;          // k f32, 16-byte aligned
+    float *         Y;          // m f32
+    uint32_t nb01;              // row stride in bytes (multiple of 16)
+    uint32_t m;
+    uint32_t base, rem;         // m / grid, m % grid: CTA b owns rows [b * base + min(b, rem), ... + base + (b < rem))
+    uint16_t nsb;               // k / 256
+    uint16_t xg;                // index of the job's activation group (consecutive jobs with the same X share one quantized copy)
+    int16_t  dep;               // first job of a group: index of the LAST earlier job of this launch whose completion the group
+                                // has to wait for (its output overlaps this group's X or Y, or this group's Y overlaps its X); -1 = none
+    uint16_t flags;             // bit 0: a later group waits for this job -> completion is counted in done[job]
+};
+
+struct sq_params {
+    int        n_jobs, n_groups;
+    int        kmax;            // largest k of the launch: an activation buffer holds kmax int8 + kmax / 32 float2
+    int        stages;          // ring slots per warp (2..4)
+    int        n_flagged;       // jobs with flags & 1 (0: the kernel touches neither `done` nor the ticket)
+    int        _pad;
+    uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j) + [SQ_MAX_JOBS] = ticket; all zero between launches
+    sq_job     jobs[SQ_MAX_JOBS];
+};
+
+// host launcher (mmvq_stream.cu); P.jobs[0 .. n_jobs) filled, groups / deps / flags resolved by the caller
+int    b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P);
+// ring slots per warp that fit next to two activation buffers of kmax values (0: does not fit)
+int    b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax);

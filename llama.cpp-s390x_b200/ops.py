@@ -92,6 +92,35 @@ def mul_mat_multi(ctx: Context, wtype: int, ws, x, outs=None):
     return outs
 
 
+class MatmulBatch:
+    """A prepared list of matmuls for b200_mul_mat_batch: d[i] = ws[i] x xs[i], executed as if in list order.  The descriptor
+    arrays are built once, run() is one C-ABI call (what the backend shell does for the MUL_MAT nodes of a cgraph)."""
+
+    def __init__(self, wtype: int, ws, xs, outs):
+        self.keep = (ws, xs, outs)
+        n = len(ws)
+        self.a = [_desc(w, wtype, k_elems=x.shape[-1]) for w, x in zip(ws, xs)]
+        self.b = [_desc(x, F32) for x in xs]
+        self.d = [_desc(o, F32) for o in outs]
+        T = C.POINTER(Tensor)
+        self.ap = (T * n)(*[C.pointer(t) for t in self.a])
+        self.bp = (T * n)(*[C.pointer(t) for t in self.b])
+        self.dp = (T * n)(*[C.pointer(t) for t in self.d])
+        self.n = n
+
+    def run(self, ctx: Context):
+        check(lib().b200_mul_mat_batch(ctx.handle, self.n, self.ap, self.bp, self.dp), "b200_mul_mat_batch")
+        return self.keep[2]
+
+
+def mul_mat_batch(ctx: Context, wtype: int, ws, xs, outs=None):
+    """outs[i] = ws[i] x xs[i] for a list of matmuls, in list order, through one C-ABI call"""
+    import torch
+    if outs is None:
+        outs = [torch.empty(tuple(x.shape[:-1]) + (w.shape[-2],), dtype=torch.float32, device=x.device) for w, x in zip(ws, xs)]
+    return MatmulBatch(wtype, ws, xs, outs).run(ctx)
+
+
 def mul_mat_supported(wtype: int, w, x) -> bool:
     import torch
     a = _desc(w, wtype, k_elems=x.shape[-1])
