@@ -79,13 +79,16 @@ def peaks():
 def measured_traffic(launches_per_step, world):
     """dram__bytes_read + dram__bytes_write per launch (average over the step's launches) from the committed ncu launch list of
     this command — only when the run has the same shape of step as the profiled one, else null"""
-    p = ROOT / "profiles" / "r01_traffic.json"
-    if world != 1 or not p.exists():
+    if world != 1:
         return None
-    d = json.loads(p.read_text())
-    if d.get("workload") != MODEL or d.get("launches_per_step") != launches_per_step:
-        return None
-    return d["dram_bytes_per_launch_avg"]
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        p = ROOT / "profiles" / name
+        if not p.exists():
+            continue
+        d = json.loads(p.read_text())
+        if d.get("workload") == MODEL and d.get("launches_per_step") == launches_per_step:
+            return d["dram_bytes_per_launch_avg"]
+    return None
 
 
 class ClockSampler:
@@ -330,8 +333,14 @@ def run_gpu(args):
         i += 1
 
     n_groups = len(groups)
+    use_stream = world == 1 and not args.no_stream
+    batch = pkg.MatmulBatch(Q4_K, [o[0] for o in order], [o[1] for o in order], [o[3] for o in order]) if use_stream else None
 
     def step():
+        if use_stream:
+            # ONE C-ABI call for the whole list: the persistent job-table GEMV walks all 225 matmuls in one launch
+            batch.run(ctx)
+            return
         if use_ll:
             for g in groups:
                 pkg.mul_mat_gather_ll(ctx, Q4_K, [o[0] for o in g], g[0][1], [o[2] for o in g], [rank * (o[4][0] // world) for o in g])
@@ -393,6 +402,11 @@ def run_gpu(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = STEP_BYTES / (ms_step * 1e-3) / 1e9
+
+    # ---- the same step as a DEPENDENT chain (every group's activations are an earlier matmul's output, as in the model) -------
+    dependent = None
+    if world == 1 and not args.no_extras:
+        dependent = dependent_chain_bench(torch, pkg, ctx, stream, order, args)
 
     # ---- e2e: host buffers through b200_mul_mat_host (N == 1 semantics on every rank's shard) ---------------------------------
     e2e = None
@@ -481,7 +495,10 @@ def run_gpu(args):
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
                        "l2": f"inputs larger than L2: {sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9:.2f} GB of distinct weights per step vs 126 MB L2, no flush needed",
                        "launch": ("CUDA graph replay" if graph is not None else "eager launches through the C ABI") +
-                                 (f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
+                                 (f"; one b200_mul_mat_batch call = {launches_per_step} persistent job-table launch(es) for {STEP_MATMULS} matmuls "
+                                  f"({n_groups} activation groups)" if use_stream else
+                                  f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
+                       "activations": "independent: every matmul reads a fixed resident vector (see dependent_chain for the step wired like the model)",
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
                                                                           "memory; completion: " + ("LL exchange: {value, epoch} in one 8-byte store per result, a receiver kernel polls the local slot; no barrier, no NCCL call"
                                                                           if use_ll else "in-kernel epoch flags after every matmul" if use_flags else "symmetric-memory barrier after wv / wo / ffn_up / ffn_down / output (129 per step)")},
@@ -490,9 +507,12 @@ def run_gpu(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(value / world, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(value / world / peak, 4), "traffic": measured_traffic(launches_per_step, world), "peak_source": peak_src,
-                         "kernel": f"gemv_q4k<1,32> (all {launches_per_step} launches of the step, {STEP_MATMULS} matmuls)",
+                         "kernel": (f"gemv_q4k_stream (persistent job table: {launches_per_step} launch(es) per step, {STEP_MATMULS} matmuls)" if use_stream
+                                    else f"gemv_q4k<1,32> (all {launches_per_step} launches of the step, {STEP_MATMULS} matmuls)"),
                          "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / launches_per_step / world)},
         }
+        if dependent:
+            out["dependent_chain"] = dependent
         if e2e:
             out["e2e"] = e2e
         if shapes:
@@ -510,6 +530,76 @@ def run_gpu(args):
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def dependent_chain_bench(torch, pkg, ctx, stream, order, args):
+    """The step wired like the model: q/k/v read the layer input, wo reads q, gate/up read wo's output, down reads gate's output and
+    writes the next layer's input, the head reads the last one — 129 dependent groups.  Timed (CUDA graph) through
+    b200_mul_mat_batch (one persistent launch, in-kernel completion counters) and through one launch per group with every
+    kernel waiting for its predecessor before it reads its activations (b200_mul_mat / _multi with defer_wait = 0)."""
+    names = {"wq": 0, "wk": 1, "wv": 2, "wo": 3, "ffn_gate": 4, "ffn_up": 5, "ffn_down": 6}
+    dims = {name: (m, k) for name, m, k, _ in LLAMA3_8B}
+    hid, ffn = dims["wq"][1], dims["ffn_gate"][0]
+    gen = torch.Generator(device="cuda"); gen.manual_seed(77)
+    h0 = torch.randn((1, hid), device="cuda", generator=gen)
+    q, h1 = torch.empty((1, dims["wq"][0]), device="cuda"), torch.empty((1, dims["wo"][0]), device="cuda")
+    kk, v = torch.empty((1, dims["wk"][0]), device="cuda"), torch.empty((1, dims["wv"][0]), device="cuda")
+    g, u = torch.empty((1, ffn), device="cuda"), torch.empty((1, ffn), device="cuda")
+    logits = torch.empty((1, dims["output"][0]), device="cuda")
+    wire = {"wq": (h0, q), "wk": (h0, kk), "wv": (h0, v), "wo": (q, h1), "ffn_gate": (h1, g), "ffn_up": (h1, u), "ffn_down": (g, h0),
+            "output": (h0, logits)}
+    ws = [o[0] for o in order]
+    xs = [wire[o[4][1]][0] for o in order]
+    ys = [wire[o[4][1]][1] for o in order]
+    batch = pkg.MatmulBatch(Q4_K, ws, xs, ys)
+
+    def per_launch():
+        i = 0
+        while i < len(order):
+            j = i + 1
+            while j < len(order) and j - i < 3 and xs[j] is xs[i] and order[j][4][1] in ("wk", "wv", "ffn_up"):
+                j += 1
+            if j - i == 1:
+                pkg.mul_mat(ctx, Q4_K, ws[i], xs[i], out=ys[i])
+            else:
+                pkg.mul_mat_multi(ctx, Q4_K, ws[i:j], xs[i], ys[i:j])
+            i = j
+
+    res = {}
+    h_init = h0.clone()
+    finals = {}
+    with torch.cuda.stream(stream):
+        for label, fn in (("stream", lambda: batch.run(ctx)), ("per_launch", per_launch)):
+            prev = ctx.set_option("defer_wait", 0) if label == "per_launch" else None
+            h0.copy_(h_init)
+            fn()
+            stream.synchronize()
+            finals[label] = logits.clone()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=stream):
+                fn()
+            for _ in range(3):
+                gr.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            iters = max(5, min(args.steps, 20))
+            e0.record(stream)
+            for _ in range(iters):
+                gr.replay()
+            e1.record(stream)
+            stream.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            res[label] = {"ms_per_step": round(ms, 4), "gbps": round(STEP_BYTES / ms / 1e6, 1), "tok_per_s_matmul_only": round(1e3 / ms, 1)}
+            if prev is not None:
+                ctx.set_option("defer_wait", prev)
+            del gr
+    # both ways compute the same chain, bit for bit (NaN-safe comparison of the raw words)
+    assert torch.equal(finals["stream"].view(torch.int32), finals["per_launch"].view(torch.int32)), "dependent chain: stream != per-launch result"
+    peak, _ = peaks()
+    for label in res:
+        res[label]["frac_of_hbm_peak"] = round(res[label]["gbps"] / peak, 4)
+    res["note"] = ("129 dependent groups per step; 'stream' = one b200_mul_mat_batch launch with in-kernel completion counters, 'per_launch' = "
+                   "129 launches, each waiting for its predecessor before reading its activations (defer_wait = 0)")
+    return res
 
 
 def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):
@@ -773,6 +863,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     ap.add_argument("--gather-sync", default="ll", choices=["ll", "barrier", "flags"], help="N > 1: how a matmul's gather is completed")
+    ap.add_argument("--no-stream", action="store_true", help="N = 1: one launch per activation group (round-1 path) instead of b200_mul_mat_batch")
     ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")
     ap.add_argument("--model", default="8b", choices=["8b", "70b"], help="70b: Llama-3-70B shapes (BASELINE configs[4], row split); skips the extra sections")

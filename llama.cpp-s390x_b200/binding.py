@@ -41,7 +41,9 @@ class Tensor(C.Structure):
 
 
 def lib_path() -> Path:
-    return HERE / "libggml_b200_kernels.so"
+    import os
+    alt = os.environ.get("GGML_B200_KERNELS_SO")          # experiments: a differently configured build of the same library
+    return Path(alt) if alt else HERE / "libggml_b200_kernels.so"
 
 
 def build_native() -> None:

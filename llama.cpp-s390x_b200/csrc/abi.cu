@@ -133,6 +133,8 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->use_stream    = env_int("GGML_B200_USE_STREAM", 1);
     ctx->stream_min_jobs = env_int("GGML_B200_STREAM_MIN_JOBS", 2);
     ctx->stream_stages = env_int("GGML_B200_STREAM_STAGES", 0);
+    ctx->stream_ll     = env_int("GGML_B200_STREAM_LL", 1);
+    ctx->stream_pair_min = env_int("GGML_B200_STREAM_PAIR_MIN", 0);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
     *out = ctx;
@@ -147,6 +149,8 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->gs_state) cudaFree(ctx->gs_state);
     if (ctx->ll_state) cudaFree(ctx->ll_state);
     if (ctx->sq_done) cudaFree(ctx->sq_done);
+    if (ctx->sq_ll) cudaFree(ctx->sq_ll);
+    if (ctx->sq_trace) cudaFree(ctx->sq_trace);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
@@ -188,6 +192,9 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "use_stream"))    slot = &ctx->use_stream;
     else if (!strcmp(name, "stream_min_jobs")) slot = &ctx->stream_min_jobs;
     else if (!strcmp(name, "stream_stages")) slot = &ctx->stream_stages;
+    else if (!strcmp(name, "stream_ll"))     slot = &ctx->stream_ll;
+    else if (!strcmp(name, "stream_trace"))  slot = &ctx->stream_trace;
+    else if (!strcmp(name, "stream_pair_min")) slot = &ctx->stream_pair_min;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
     const int prev = *slot;
     *slot = value;
@@ -697,49 +704,68 @@ static bool stream_job_ok(const b200_ctx * ctx, const b200_tensor * a, const b20
 
 static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, const b200_tensor * const * b, const b200_tensor * const * d) {
     if (!ctx->sq_done) {
-        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_done, (SQ_MAX_JOBS + 1) * sizeof(uint32_t)));
-        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_done, 0, (SQ_MAX_JOBS + 1) * sizeof(uint32_t), ctx->stream));
+        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_done, (SQ_MAX_JOBS + 2) * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_done, 0, (SQ_MAX_JOBS + 2) * sizeof(uint32_t), ctx->stream));
     }
-    static thread_local sq_params P;                        // 24 KB: not on the stack of every caller
+    static thread_local sq_params P;                        // ~26 KB: not on the stack of every caller
     memset(&P, 0, offsetof(sq_params, jobs));
-    P.n_jobs = n; P.done = ctx->sq_done;
+    P.n_jobs = n; P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
     const uint32_t G = (uint32_t) ctx->sm_count;
     std::vector<const char *> xlo((size_t) n), xhi((size_t) n), ylo((size_t) n), yhi((size_t) n);
+    std::vector<int> xsrc((size_t) n, -1);                  // job whose exchange entries job j reads instead of X
     int group = -1, group_first = 0, group_size = 0;
     const char * xbox_lo = nullptr, * xbox_hi = nullptr, * ybox_lo = nullptr, * ybox_hi = nullptr;
+    size_t ll_entries = 0;
     for (int j = 0; j < n; ++j) {
         sq_job & J = P.jobs[j];
+        const uint32_t m = (uint32_t) a[j]->ne[1];
         J.W = (const uint8_t *) a[j]->data; J.X = (const float *) b[j]->data; J.Y = (float *) d[j]->data;
-        J.nb01 = (uint32_t) a[j]->nb[1]; J.m = (uint32_t) a[j]->ne[1];
-        J.base = J.m / G; J.rem = J.m % G;
+        J.nb01 = (uint32_t) a[j]->nb[1];
+        J.base = m / G; J.rem = (uint16_t) (m % G);
         J.nsb = (uint16_t) (a[j]->ne[0] / 256);
-        J.dep = -1; J.flags = 0;
+        J.dep = -1; J.xsrc = -1; J.flags = 0; J.ll_off = SQ_NO_LL;
         if (a[j]->ne[0] > P.kmax) P.kmax = (int) a[j]->ne[0];
         xlo[j] = (const char *) J.X; xhi[j] = xlo[j] + 4 * a[j]->ne[0];
         ylo[j] = (const char *) J.Y; yhi[j] = ylo[j] + 4 * a[j]->ne[1];
         if (xlo[j] < yhi[j] && ylo[j] < xhi[j]) { b200_set_error("mul_mat_batch[%d]: dst overlaps src1", j); return B200_E_ARG; }
-        // the LAST earlier job this one must come after: it wrote what this one reads (RAW) or writes (WAW), or read what this one
-        // writes (WAR).  Completion is counted cumulatively (all jobs <= dep are complete), so the last one is enough.
-        int dep = -1;
+        // Hazards against earlier jobs of the list, latest first:
+        //  * X is EXACTLY the output of the latest job that wrote into X's range: the dependency travels in the data — that job
+        //    also writes {value, epoch} words into the exchange buffer and this group polls them (no counters on that path);
+        //  * anything else — X partly written by an earlier job, WAW on Y, WAR against a job that reads the plain tensor — waits
+        //    for a completion counter.  Completion is cumulative (every job <= dep is complete), so the LAST such job is enough.
+        int dep = -1, src = -1;
+        bool raw_open = true;
         // (bounding boxes of everything earlier: the usual list has no overlaps at all and skips the scan)
-        const bool maybe = (xlo[j] < ybox_hi && ybox_lo < xhi[j]) || (ylo[j] < ybox_hi && ybox_lo < yhi[j]) || (ylo[j] < xbox_hi && xbox_lo < yhi[j]);
-        for (int i = maybe ? j - 1 : -1; i >= 0; --i) {
-            const bool raw = xlo[j] < yhi[i] && ylo[i] < xhi[j];
-            const bool waw = ylo[j] < yhi[i] && ylo[i] < yhi[j];
-            const bool war = ylo[j] < xhi[i] && xlo[i] < yhi[j];
-            if (raw || waw || war) { dep = i; break; }
+        const bool maybe = j > 0 && ((xlo[j] < ybox_hi && ybox_lo < xhi[j]) || (ylo[j] < ybox_hi && ybox_lo < yhi[j]) || (ylo[j] < xbox_hi && xbox_lo < yhi[j]));
+        for (int i = maybe ? j - 1 : -1; i >= 0 && (dep < 0 || raw_open); --i) {
+            bool hazard = false;
+            if (raw_open && xlo[j] < yhi[i] && ylo[i] < xhi[j]) {
+                raw_open = false;                              // older writers of this range are superseded, or covered by the cumulative counter
+                if (ylo[i] == xlo[j] && yhi[i] == xhi[j] && ctx->stream_ll) src = i; else hazard = true;
+            }
+            if (ylo[j] < yhi[i] && ylo[i] < yhi[j]) hazard = true;                                   // WAW
+            if (xsrc[i] < 0 && ylo[j] < xhi[i] && xlo[i] < yhi[j]) hazard = true;                      // WAR (job i reads the tensor itself)
+            if (hazard && dep < 0) dep = i;
         }
+        xsrc[j] = src;
         if (j == 0 || xlo[j] < xbox_lo) xbox_lo = xlo[j];
         if (j == 0 || xhi[j] > xbox_hi) xbox_hi = xhi[j];
         if (j == 0 || ylo[j] < ybox_lo) ybox_lo = ylo[j];
         if (j == 0 || yhi[j] > ybox_hi) ybox_hi = yhi[j];
-        const bool join = j > 0 && J.X == P.jobs[j - 1].X && J.nsb == P.jobs[j - 1].nsb && group_size < SQ_MAX_GROUP && dep < group_first;
+        const bool join = j > 0 && J.X == P.jobs[j - 1].X && J.nsb == P.jobs[j - 1].nsb && group_size < SQ_MAX_GROUP && dep < group_first &&
+                          src == xsrc[group_first];
         if (join) {
             group_size++;
             if (dep > P.jobs[group_first].dep) P.jobs[group_first].dep = (int16_t) dep;
         } else {
             group++; group_first = j; group_size = 1;
-            J.dep = (int16_t) dep;
+            J.dep = (int16_t) dep; J.xsrc = (int16_t) src;
+            P.gfirst[group] = (uint16_t) j;
+            if (src >= 0 && P.jobs[src].ll_off == SQ_NO_LL) {
+                P.jobs[src].ll_off = (uint32_t) ll_entries;
+                ll_entries += ((size_t) a[src]->ne[1] + 3) & ~(size_t) 3;
+                P.n_ll++;
+            }
         }
         J.xg = (uint16_t) group;
     }
@@ -747,9 +773,32 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
     for (int j = 0; j < n; ++j) {
         if (P.jobs[j].dep >= 0 && !(P.jobs[P.jobs[j].dep].flags & 1)) { P.jobs[P.jobs[j].dep].flags |= 1; P.n_flagged++; }
     }
+    if (ll_entries > ctx->sq_ll_cap) {
+        // grow-only; like the scratch of the other paths this needs one un-captured call before a CUDA-graph capture
+        B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        if (ctx->sq_ll) { cudaFree(ctx->sq_ll); ctx->sq_ll = nullptr; ctx->sq_ll_cap = 0; }
+        const size_t want = ll_entries < ((size_t) 1 << 20) ? ((size_t) 1 << 20) : ll_entries;
+        if (cudaMalloc((void **) &ctx->sq_ll, want * 8) != cudaSuccess) { cudaGetLastError(); b200_set_error("mul_mat_batch: exchange buffer allocation failed"); return B200_E_ALLOC; }
+        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_ll, 0, want * 8, ctx->stream));
+        ctx->sq_ll_cap = want;
+    }
+    P.ll = ctx->sq_ll;
+    if (ctx->stream_trace) {
+        if (!ctx->sq_trace) B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_trace, (2 * SQ_MAX_JOBS * 4 + 128 * 32 * 5) * sizeof(unsigned long long)));
+        P.trace = ctx->sq_trace;
+    }
     // everything before this launch is complete when its CTAs pass griddepcontrol.wait (no deferred wait here)
     ctx->n_pend = 0;
     return b200_launch_gemv_stream(ctx, P);
+}
+
+// debugging aid, deliberately not in ggml_b200.h: copies the coordinator time stamps of the last traced launch (tools/stream_trace.py)
+extern "C" __attribute__((visibility("default"))) int b200_dbg_stream_trace(b200_ctx * ctx, unsigned long long * out, int n_words) {
+    if (!ctx || !ctx->sq_trace || !out || n_words > 2 * SQ_MAX_JOBS * 4 + 128 * 32 * 5) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    B200_CUDA_TRY(cudaMemcpy(out, ctx->sq_trace, (size_t) n_words * 8, cudaMemcpyDeviceToHost));
+    return B200_OK;
 }
 
 extern "C" int b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
@@ -950,15 +999,13 @@ int b200_mul_mat_host_batch(b200_ctx * ctx, const b200_host_mm * jobs, int n_job
         d.data = dy + ydev[i]; d.type = B200_TYPE_F32; d.ne[0] = J.m; d.ne[1] = J.n; d.ne[2] = d.ne[3] = 1;
         d.nb[0] = 4; d.nb[1] = J.m * 4; d.nb[2] = d.nb[3] = J.m * 4 * J.n;
     };
-    for (int j = 0; j < n_jobs; ) {
-        int e = j + 1;
-        while (e < n_jobs && e - j < 3 && xdev[e] == xdev[j] && jobs[e].type == jobs[j].type) ++e;
-        b200_tensor a[3], b[3], d[3];
-        const b200_tensor * ap[3], * dp[3];
-        for (int i = j; i < e; ++i) { describe(i, a[i - j], b[i - j], d[i - j]); ap[i - j] = &a[i - j]; dp[i - j] = &d[i - j]; }
-        rc = e - j == 1 ? b200_mul_mat(ctx, &a[0], &b[0], &d[0]) : b200_mul_mat_multi(ctx, e - j, ap, &b[0], dp);
+    {
+        // the whole list in one b200_mul_mat_batch: runs of Q4_K n = 1 jobs become one persistent launch, the rest is grouped there
+        std::vector<b200_tensor> ta((size_t) n_jobs), tb((size_t) n_jobs), td((size_t) n_jobs);
+        std::vector<const b200_tensor *> pa((size_t) n_jobs), pb((size_t) n_jobs), pd((size_t) n_jobs);
+        for (int i = 0; i < n_jobs; ++i) { describe(i, ta[i], tb[i], td[i]); pa[i] = &ta[i]; pb[i] = &tb[i]; pd[i] = &td[i]; }
+        rc = b200_mul_mat_batch(ctx, n_jobs, pa.data(), pb.data(), pd.data());
         if (rc) return rc;
-        j = e;
     }
     // downloads: merge jobs whose results are adjacent on the host AND on the device (sizes that are multiples of 256 B)
     for (int j = 0; j < n_jobs; ) {

@@ -22,7 +22,10 @@
 
 namespace {
 
-constexpr int SQ_NCW      = 28;                        // consumer warps
+#ifndef SQ_NCW_CFG
+#define SQ_NCW_CFG 28
+#endif
+constexpr int SQ_NCW      = SQ_NCW_CFG;                // consumer warps
 constexpr int SQ_NQW      = 4;                         // quantizer warps
 constexpr int SQ_THREADS  = (SQ_NCW + SQ_NQW) * 32;
 constexpr int SQ_CHUNK_SB = 8;                         // super-blocks of one row per chunk (one per 4 lanes)
@@ -35,7 +38,10 @@ constexpr int SQ_NCNT     = 256;                       // CTA-level row counters
 constexpr int OFF_FULL  = 0;                                         // [SQ_NCW][SQ_MAX_S] u64
 constexpr int OFF_XFULL = OFF_FULL + SQ_NCW * SQ_MAX_S * 8;          // [2] u64
 constexpr int OFF_XEMPTY = OFF_XFULL + 16;                           // [2] u64
-constexpr int OFF_META  = OFF_XEMPTY + 16;                           // [SQ_NCW][SQ_MAX_S] uint2
+constexpr int OFF_XOPEN = OFF_XEMPTY + 16;                           // [2] u64
+constexpr int OFF_CLAIM = OFF_XOPEN + 16;                            // [2] u32 unit counters, [2] = this launch's epoch
+constexpr int OFF_PROG  = OFF_CLAIM + 16;                            // [32] u32: jobs passed by consumer warp w (see pass_jobs)
+constexpr int OFF_META  = OFF_PROG + 128;                            // [SQ_NCW][SQ_MAX_S] uint2
 constexpr int OFF_CNT   = OFF_META + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NCNT] u32
 constexpr int OFF_X     = (OFF_CNT + SQ_NCNT * 4 + 127) / 128 * 128;
 
@@ -101,13 +107,108 @@ __device__ __forceinline__ float q4k_dot(const uint4 hdr, const uint4 q0, const 
     return r;
 }
 
-// the sequence of (job, row pair, chunk) steps of one consumer warp
+// Quantization of a group's activations is split into units of 16 blocks (512 values) that ANY warp of the CTA may claim: the
+// four quantizer warps work ahead of the consumers; a consumer warp that arrives at a group whose activations are not ready
+// yet (a dependent chain: everybody waits for the same vector) takes units too instead of idling.
+// Units are small — 4 blocks (one 32-value block per 8 lanes) for vectors up to 4096 values, 8 blocks beyond — because a unit is
+// one long dependency chain (load, 3 + 3 shuffles, two IEEE divisions, 4 roundings): with 16-block units a 4096-vector took 2 us
+// however many warps were idle (traced), with 4-block units all 32 warps of the CTA run one chain each.
+__device__ __forceinline__ int sq_unit_blocks(const int nbk) { return nbk <= 128 ? 4 : 8; }
+
+__device__ __forceinline__ void mbar_complete_tx(uint32_t bar, uint32_t n) {
+    asm volatile("mbarrier.complete_tx.relaxed.cta.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(n) : "memory");
+}
+
+// four consecutive activations: from the tensor, or from the exchange entries of the job that produces them — polled until every
+// word carries this launch's epoch (the arrival of the word IS the arrival of the value: one 8-byte access, no flag, no fence)
+__device__ __forceinline__ float4 sq_load_x4(const float * x, const unsigned long long * ll, const uint32_t epoch, const int idx) {
+    if (!ll) return ld_cg_f4(x + idx);
+    const unsigned long long * p = ll + idx;
+    unsigned long long w0, w1, w2, w3;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+        asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(p + 2) : "memory");
+        if ((uint32_t) (w0 >> 32) == epoch && (uint32_t) (w1 >> 32) == epoch && (uint32_t) (w2 >> 32) == epoch && (uint32_t) (w3 >> 32) == epoch) break;
+        __nanosleep(100);
+        if (clock64() - t0 > 8000000000LL) __trap();          // a producer that never delivers must not hang the box
+    }
+    return make_float4(__uint_as_float((uint32_t) w0), __uint_as_float((uint32_t) w1), __uint_as_float((uint32_t) w2), __uint_as_float((uint32_t) w3));
+}
+
+// whole warp: quantize blocks [4 NR unit, 4 NR (unit + 1)) of x (nbk blocks) into the swizzled buffer (bit-exact Q8_1 values)
+template <int NR>
+__device__ __forceinline__ void sq_quantize_unit(const float * x, const unsigned long long * ll, const uint32_t epoch, const int nbk, const int unit,
+                                                 uint8_t * s_qs, float2 * s_ds, const int lane) {
+    const int sub = lane & 7;
+    float4 v[NR];
+#pragma unroll
+    for (int u = 0; u < NR; ++u) {
+        const int ib = unit * (4 * NR) + u * 4 + (lane >> 3);
+        v[u] = sq_load_x4(x, ll, epoch, (ib < nbk ? ib : nbk - 1) * 32 + sub * 4);
+    }
+#pragma unroll
+    for (int u = 0; u < NR; ++u) {
+        const int ib = unit * (4 * NR) + u * 4 + (lane >> 3);
+        const q8_part qp = quantize_q8_1_part(v[u]);
+        if (ib < nbk) {
+            const int t = ib * 2 + (sub >> 2);
+            *reinterpret_cast<uint32_t *>(s_qs + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
+            if (sub == 0) s_ds[ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+        }
+    }
+}
+
+// whole warp: take units of group g until none is left (the group must be open: xopen waited for)
+__device__ __forceinline__ void sq_claim_units(const sq_params & P, const int g, uint8_t * smem, const uint32_t sbase, const int xbytes, const int lane,
+                                               const uint32_t epoch) {
+    const int b = g & 1;
+    const sq_job & J = P.jobs[P.gfirst[g]];
+    const unsigned long long * ll = J.xsrc >= 0 ? P.ll + P.jobs[J.xsrc].ll_off : nullptr;
+    const int nbk = (int) J.nsb * 8;
+    const int ub  = sq_unit_blocks(nbk);
+    const int nunits = (nbk + ub - 1) / ub;
+    uint32_t * claim = reinterpret_cast<uint32_t *>(smem + OFF_CLAIM) + b;
+    uint8_t * s_qs = smem + OFF_X + (size_t) b * xbytes;
+    float2 *  s_ds = reinterpret_cast<float2 *>(s_qs + P.kmax);
+    while (true) {
+        uint32_t u = 0;
+        if (lane == 0) u = atomicAdd(claim, 1u);
+        u = __shfl_sync(0xffffffffu, u, 0);
+        if ((int) u >= nunits) break;
+        if (ub == 4) sq_quantize_unit<1>(J.X, ll, epoch, nbk, (int) u, s_qs, s_ds, lane);
+        else         sq_quantize_unit<2>(J.X, ll, epoch, nbk, (int) u, s_qs, s_ds, lane);
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();                            // the unit's values before its completion count
+            mbar_complete_tx(sbase + OFF_XFULL + 8 * b, 1);
+        }
+    }
+}
+
+// this launch's epoch: launches that use the exchange buffer are counted in done[SQ_MAX_JOBS + 1] (advanced by the last CTA to
+// finish; read after griddepcontrol.wait, i.e. after the previous launch has completed)
+__device__ __forceinline__ uint32_t sq_epoch(const sq_params & P) {
+    uint32_t e = 0;
+    if (P.n_ll) {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(P.done + SQ_MAX_JOBS + 1) : "memory");
+        e += 1;
+    }
+    return e;
+}
+
+// the sequence of (job, row pair, chunk) steps of one consumer warp.  Rows are walked in PAIRS (the activations are fetched once
+// for two rows).  pair_min (ctx option stream_pair_min, default 0) > 0 hands out single rows when a CTA owns at most that many rows
+// of a job, so that more warps work on a small matrix; measured SLOWER on B200 (Llama-3-8B step 0.78 -> 1.06 ms independent,
+// 1.67 -> 2.0 ms as a dependent chain): the kernel is instruction-issue-bound and a single-row step carries the same ring and
+// cursor overhead as a pair step.
 struct sq_cursor {
     int      j;          // current job; == n_jobs: exhausted
-    uint32_t row;        // first row of the current pair
+    uint32_t row;        // first row of the current step
     uint32_t rhi;        // end of this CTA's rows of job j
     int      c, nch;     // next chunk, chunks per row
-    uint32_t rot;        // pairs of the CTA dealt so far, mod SQ_NCW: pair p of job j goes to warp (rot + p) % SQ_NCW
+    uint32_t rot;        // steps' worth of rows of the CTA dealt so far, mod SQ_NCW: unit p of job j goes to warp (rot + p) % SQ_NCW
+    uint32_t stride;     // rows per step of job j in this CTA (1 or 2)
 };
 
 __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
@@ -115,17 +216,19 @@ __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, con
     while (cu.j < P.n_jobs) {
         const sq_job & J = P.jobs[cu.j];
         const uint32_t cnt    = J.base + (b < J.rem ? 1u : 0u);
-        const uint32_t npairs = (cnt + 1) >> 1;
+        const uint32_t stride = cnt > (uint32_t) P.pair_min ? 2u : 1u;
+        const uint32_t nunits = (cnt + stride - 1) / stride;
         const uint32_t pos    = warp >= cu.rot ? warp - cu.rot : warp + SQ_NCW - cu.rot;
-        if (pos < npairs) {
+        if (pos < nunits) {
             const uint32_t rlo = b * J.base + (b < J.rem ? b : J.rem);
-            cu.row = rlo + 2 * pos;
+            cu.row = rlo + stride * pos;
             cu.rhi = rlo + cnt;
             cu.c   = 0;
             cu.nch = (J.nsb + SQ_CHUNK_SB - 1) / SQ_CHUNK_SB;
+            cu.stride = stride;
             return;
         }
-        cu.rot = (cu.rot + npairs) % SQ_NCW;
+        cu.rot = (cu.rot + nunits) % SQ_NCW;
         cu.j++;
     }
 }
@@ -133,11 +236,11 @@ __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, con
 __device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
     if (++cu.c < cu.nch) return;
     cu.c = 0;
-    cu.row += 2 * SQ_NCW;
+    cu.row += cu.stride * SQ_NCW;
     if (cu.row < cu.rhi) return;
     const sq_job & J = P.jobs[cu.j];
     const uint32_t cnt = J.base + (blockIdx.x < J.rem ? 1u : 0u);
-    cu.rot = (cu.rot + ((cnt + 1) >> 1)) % SQ_NCW;
+    cu.rot = (cu.rot + (cnt + cu.stride - 1) / cu.stride) % SQ_NCW;
     cu.j++;
     sq_seek(P, cu, warp);
 }
@@ -153,12 +256,16 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
     if (tid == 0) {
         for (int i = 0; i < SQ_NCW * SQ_MAX_S; ++i) tc::mbar_init(sbase + OFF_FULL + 8 * i, 1);
         for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(sbase + OFF_XFULL + 8 * i, SQ_NQW * 32);
+            tc::mbar_init(sbase + OFF_XFULL + 8 * i, 1);          // one arrival (the coordinator's expect_tx) + one tx per unit
             tc::mbar_init(sbase + OFF_XEMPTY + 8 * i, SQ_NCW);
+            tc::mbar_init(sbase + OFF_XOPEN + 8 * i, 1);
         }
         tc::mbar_fence_init();
     }
     if (tid < SQ_NCNT) reinterpret_cast<uint32_t *>(smem + OFF_CNT)[tid] = 0;
+    if (tid < 32) reinterpret_cast<uint32_t *>(smem + OFF_PROG)[tid] = 0;
+    volatile uint32_t * s_epoch = reinterpret_cast<volatile uint32_t *>(smem + OFF_CLAIM) + 2;
+    volatile uint32_t * s_prog  = reinterpret_cast<volatile uint32_t *>(smem + OFF_PROG);
     __syncthreads();
 
     if (warp < SQ_NCW) {
@@ -175,13 +282,13 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         const uint32_t e_off = (uint32_t) P.kmax + (uint32_t) (sbl * 8 + 2 * g) * 8;
 
         sq_cursor pc;                                     // producer cursor: S steps ahead of the consumer
-        pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0;
+        pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0; pc.stride = 1;
         sq_seek(P, pc, (uint32_t) warp);
         auto fill = [&](const int slot) {
             const sq_job & J = P.jobs[pc.j];
             const int      left  = (int) J.nsb - pc.c * SQ_CHUNK_SB;
             const uint32_t bytes = (uint32_t) (left < SQ_CHUNK_SB ? left : SQ_CHUNK_SB) * SZ_Q4_K;
-            const bool     two   = pc.row + 1 < pc.rhi;
+            const bool     two   = pc.stride == 2 && pc.row + 1 < pc.rhi;
             const bool     last  = pc.c + 1 == pc.nch;
             const uint8_t * src  = J.W + (size_t) pc.row * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
             const uint32_t dst   = ring0 + (uint32_t) slot * SQ_SLOT_B;
@@ -215,7 +322,12 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     if (lane == 0) tc::mbar_arrive(sbase + OFF_XEMPTY + 8 * (cur_g & 1));
                 }
                 cur_g++;
-                if (cur_g < P.n_groups) tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), (uint32_t) (cur_g >> 1) & 1u, 20);
+                if (cur_g < P.n_groups) {
+                    const uint32_t par = (uint32_t) (cur_g >> 1) & 1u;
+                    tc::mbar_wait(sbase + OFF_XOPEN + 8 * (cur_g & 1), par, 20);
+                    sq_claim_units(P, cur_g, smem, sbase, xbytes, lane, *s_epoch);          // usually nothing left to take
+                    tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), par, 20);
+                }
             }
         };
         // Completion accounting (only when a later group of the list waits for an earlier job): a warp "passes" job j once all
@@ -228,7 +340,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             if (P.n_flagged && lane == 0) {
                 for (int jj = passed; jj < upto; ++jj) {
                     if (!(P.jobs[jj].flags & 1)) continue;
-                    __threadfence();
+                    __threadfence_block();                    // release at CTA scope; the reporting warp's fence below is cumulative
                     if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
                         cnt[jj & (SQ_NCNT - 1)] = 0;
                         __threadfence();
@@ -237,6 +349,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 }
             }
             passed = upto;
+            if (P.n_ll && lane == 0) s_prog[warp] = (uint32_t) upto;      // (the quantizers open a data-dependent group when all 28 are past its source)
         };
         while (consumed < produced) {
             uint32_t row, m1;                                 // (the slot's description was written when its fill was issued)
@@ -276,6 +389,12 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 if (lane == 0) {
                     J.Y[row] = sA;
                     if (two) J.Y[row + 1] = sB;
+                    if (J.ll_off != SQ_NO_LL) {
+                        unsigned long long * e = P.ll + J.ll_off + row;
+                        const uint32_t epoch = *s_epoch;
+                        asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(e), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sA)) : "memory");
+                        if (two) asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" :: "l"(e + 1), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sB)) : "memory");
+                    }
                 }
                 accA = 0.0f; accB = 0.0f;
             }
@@ -292,77 +411,83 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const int qt  = tid - SQ_NCW * 32;                    // 0 .. 127
-        const int sub = qt & 7;
-        int jq = 0;
+        unsigned long long * tr = nullptr;
+        if (P.trace && qt == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) tr = P.trace + (blockIdx.x == 0 ? 0 : SQ_MAX_JOBS * 4);
+        auto stamp = [&](const int g, const int what) {
+            if (tr) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tr[g * 4 + what] = t; }
+        };
         for (int gidx = 0; gidx < P.n_groups; ++gidx) {
-            while (jq < P.n_jobs && (int) P.jobs[jq].xg < gidx) jq++;
+            const int jq = P.gfirst[gidx];
+            stamp(gidx, 0);
             const sq_job & J = P.jobs[jq];
             const int b = gidx & 1;
-            if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, (uint32_t) ((gidx >> 1) - 1) & 1u, 20);
-            if (J.dep >= 0) {
-                // every CTA has finished job `dep` (rows stored, its activations read)
-                const uint32_t * flag = P.done + J.dep;
-                uint32_t seen;
+            const uint32_t par = (uint32_t) (gidx >> 1) & 1u;
+            if (qt < 32 && J.xsrc >= 0) {
+                // Activations that ARE an earlier job's output are polled in the exchange buffer.  Polling starts when this CTA's own
+                // consumer warps are past that job — the other CTAs finish at about the same time, so few polls fail (polling from
+                // the moment the buffer is free would flood the L2 with failing reads: measured 2.3 ms instead of 1.35 ms per step).
                 const long long t0 = clock64();
-                do {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
-                    if (seen >= gridDim.x) break;
+                while (true) {
+                    const uint32_t mine = lane < SQ_NCW ? s_prog[lane] : 0xffffffffu;
+                    if (__reduce_min_sync(0xffffffffu, mine) > (uint32_t) J.xsrc) break;
                     __nanosleep(20);
-                    if (clock64() - t0 > 8000000000LL) __trap();      // a broken dependency must not hang the box
-                } while (true);
-            }
-            uint8_t * s_qs = smem + OFF_X + (size_t) b * xbytes;
-            float2 *  s_ds = reinterpret_cast<float2 *>(s_qs + P.kmax);
-            const int nbk = (int) J.nsb * 8;
-            const float * x = J.X;
-            constexpr int QG = SQ_NQW * 4;                    // 32-value blocks per round
-            for (int ib0 = 0; ib0 < nbk; ib0 += 4 * QG) {
-                float4 v[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int ib = ib0 + u * QG + (qt >> 3);
-                    v[u] = ld_cg_f4(x + (ib < nbk ? ib : nbk - 1) * 32 + sub * 4);
+                    if (clock64() - t0 > 8000000000LL) __trap();
                 }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int ib = ib0 + u * QG + (qt >> 3);
-                    const q8_part qp = quantize_q8_1_part(v[u]);
-                    if (ib < nbk) {
-                        const int t = ib * 2 + (sub >> 2);
-                        *reinterpret_cast<uint32_t *>(s_qs + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
-                        if (sub == 0) s_ds[ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+            }
+            if (qt == 0) {
+                // the coordinator opens the group: buffer free, dependency complete, unit counter reset
+                if (gidx == 0) *s_epoch = sq_epoch(P);
+                if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, par ^ 1u, 20);
+                if (J.dep >= 0) {
+                    // every CTA has finished job `dep` and everything before it (rows stored, activations read)
+                    const uint32_t * flag = P.done + J.dep;
+                    uint32_t seen;
+                    const long long t0 = clock64();
+                    while (true) {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+                        if (seen >= gridDim.x) break;
+                        if (clock64() - t0 > 8000000000LL) __trap();      // a broken dependency must not hang the box
                     }
                 }
+                stamp(gidx, 1);
+                reinterpret_cast<uint32_t *>(smem + OFF_CLAIM)[b] = 0;
+                const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
+                tc::mbar_arrive_expect_tx(sbase + OFF_XFULL + 8 * b, (uint32_t) ((nbk + ub - 1) / ub));
+                tc::mbar_arrive(sbase + OFF_XOPEN + 8 * b);
             }
-            tc::mbar_arrive(sbase + OFF_XFULL + 8 * b);
+            tc::mbar_wait(sbase + OFF_XOPEN + 8 * b, par, 20);
+            sq_claim_units(P, gidx, smem, sbase, xbytes, lane, *s_epoch);
+            // no quantizer warp is inside this group's claim loop any more when the coordinator goes on (the counter is reused)
+            asm volatile("bar.sync 1, %0;" :: "n"(SQ_NQW * 32) : "memory");
+            stamp(gidx, 2);
+            if (tr) { tc::mbar_wait(sbase + OFF_XFULL + 8 * b, par, 20); stamp(gidx, 3); }
             // the quantizers' check-in for the flagged jobs of this group: their activations have been read by this CTA
-            if (P.n_flagged) {
+            if (P.n_flagged && qt == 0) {
                 bool any = false;
                 for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) any = any || (P.jobs[jj].flags & 1);
                 if (any) {
-                    asm volatile("bar.sync 1, %0;" :: "n"(SQ_NQW * 32) : "memory");       // all 128 quantizer threads have their values
-                    if (qt == 0) {
-                        uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
-                        for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) {
-                            if (!(P.jobs[jj].flags & 1)) continue;
-                            if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
-                                cnt[jj & (SQ_NCNT - 1)] = 0;
-                                __threadfence();
-                                atomicAdd(P.done + jj, 1u);
-                            }
+                    tc::mbar_wait(sbase + OFF_XFULL + 8 * b, par, 20);            // all units, whoever took them
+                    uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
+                    for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) {
+                        if (!(P.jobs[jj].flags & 1)) continue;
+                        if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
+                            cnt[jj & (SQ_NCNT - 1)] = 0;
+                            __threadfence();
+                            atomicAdd(P.done + jj, 1u);
                         }
                     }
                 }
             }
         }
     }
-    if (P.n_flagged) {
-        // the last CTA to finish leaves the counters at zero for the next launch (nobody polls them any more)
+    if (P.n_flagged || P.n_ll) {
+        // the last CTA to finish leaves the counters at zero for the next launch (nobody polls them any more) and counts the launch
         __syncthreads();
         if (tid == 0) {
             __threadfence();
             if (atomicAdd(P.done + SQ_MAX_JOBS, 1u) == gridDim.x - 1) {
-                for (int j = 0; j < P.n_jobs; ++j) P.done[j] = 0;
+                if (P.n_flagged) for (int j = 0; j < P.n_jobs; ++j) P.done[j] = 0;
+                if (P.n_ll) P.done[SQ_MAX_JOBS + 1] += 1;
                 P.done[SQ_MAX_JOBS] = 0;
             }
         }

@@ -11,17 +11,22 @@
 #define SQ_MAX_JOBS    512      // per launch (longer lists are cut into several launches)
 #define SQ_MAX_GROUP   64       // jobs that may share one quantized activation vector (bounds the live window of the CTA counters)
 
-struct sq_job {
+#define SQ_NO_LL 0xffffffffu
+
+struct sq_job {                 // 48 bytes
     const uint8_t * W;          // first row of the [m, k] Q4_K matrix (or row shard), 16-byte aligned
     const float *   X;          // k f32, 16-byte aligned
     float *         Y;          // m f32
     uint32_t nb01;              // row stride in bytes (multiple of 16)
-    uint32_t m;
-    uint32_t base, rem;         // m / grid, m % grid: CTA b owns rows [b * base + min(b, rem), ... + base + (b < rem))
+    uint32_t base;              // m / grid: CTA b owns rows [b * base + min(b, rem), ... + base + (b < rem))
+    uint32_t ll_off;            // SQ_NO_LL, or: every result also goes, as {f32 bits, launch epoch} in one 8-byte word, to entry
+                                // ll_off + row of the exchange buffer — a later group of this launch reads its activations from there
+    uint16_t rem;               // m % grid
     uint16_t nsb;               // k / 256
     uint16_t xg;                // index of the job's activation group (consecutive jobs with the same X share one quantized copy)
     int16_t  dep;               // first job of a group: index of the LAST earlier job of this launch whose completion the group
-                                // has to wait for (its output overlaps this group's X or Y, or this group's Y overlaps its X); -1 = none
+                                // has to wait for (hazards other than "X is exactly an earlier job's output"); -1 = none
+    int16_t  xsrc;              // first job of a group: the earlier job whose exchange entries ARE this group's activations; -1 = read X
     uint16_t flags;             // bit 0: a later group waits for this job -> completion is counted in done[job]
 };
 
@@ -29,9 +34,16 @@ struct sq_params {
     int        n_jobs, n_groups;
     int        kmax;            // largest k of the launch: an activation buffer holds kmax int8 + kmax / 32 float2
     int        stages;          // ring slots per warp (2..4)
-    int        n_flagged;       // jobs with flags & 1 (0: the kernel touches neither `done` nor the ticket)
+    int        n_flagged;       // jobs with flags & 1
+    int        pair_min;        // a CTA with more rows of a job than this walks them in pairs, else one by one
     int        _pad;
-    uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j) + [SQ_MAX_JOBS] = ticket; all zero between launches
+    int        n_ll;            // jobs with an exchange region (0 and n_flagged == 0: the kernel touches no global state)
+    uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j), [SQ_MAX_JOBS] ticket, [SQ_MAX_JOBS + 1] launch
+                                // epoch; counters and ticket are zero between launches, the epoch counts the launches that used it
+    unsigned long long * trace; // debugging (ctx option stream_trace): %globaltimer stamps of the coordinator of CTA 0 and of the last CTA,
+                                // [2][SQ_MAX_JOBS][4] = {group start, opened, own units done, all units done}; NULL = off
+    unsigned long long * ll;    // exchange buffer (entries of 8 bytes: epoch << 32 | f32 bits), zero-initialised
+    uint16_t   gfirst[SQ_MAX_JOBS];   // first job of activation group g
     sq_job     jobs[SQ_MAX_JOBS];
 };
 

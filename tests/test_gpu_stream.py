@@ -61,8 +61,21 @@ def chain(pkg, ctx, ws, x0, bufs):
     return xs, outs
 
 
-def test_batch_dependent_chain_matches_sequential_calls(pkg, gpu_ctx):
-    """every job reads the previous job's output (RAW) and overwrites the buffer the one before read (WAR)"""
+@pytest.mark.parametrize("opts", [{}, {"stream_ll": 0}, {"stream_pair_min": 28}, {"stream_stages": 2}])
+def test_batch_dependent_chain_matches_sequential_calls(pkg, gpu_ctx, opts):
+    """every job reads the previous job's output (RAW) and overwrites the buffer the one before read (WAR); with the dependency
+    carried in the data ({value, epoch} words, default), by completion counters only (stream_ll = 0), with single-row steps and
+    with two ring slots per warp"""
+    import torch
+    prev = {k: gpu_ctx.set_option(k, v) for k, v in opts.items()}
+    try:
+        _chain_case(pkg, gpu_ctx)
+    finally:
+        for k, v in prev.items():
+            gpu_ctx.set_option(k, v)
+
+
+def _chain_case(pkg, gpu_ctx):
     import torch
     rng = np.random.default_rng(12)
     dims = [1024, 2048, 512, 4096, 256, 1024, 1024, 768, 256]           # k_0 = 1024, then m_i = k_{i+1}
