@@ -465,6 +465,15 @@ def run_gpu(args):
                "per_matmul_sync": {"ms_per_step": round(pm_ms, 4), "tok_per_s": round(1e3 / pm_ms, 2),
                                    "api": "b200_mul_mat_host per matmul (H2D, GEMV, D2H, sync each): a MUL_MAT-only backend "
                                           "with every other op on the CPU"}}
+    if e2e is not None:
+        plug = plugin_e2e(args)
+        if plug is not None:
+            # the headline e2e is the one a reference caller gets: the reference's own backend API on the plug-in; the direct C-ABI
+            # figure stays beside it
+            e2e = {"value": round(STEP_BYTES / (plug["ms_per_step"] * 1e-3) / 1e9, 2), "unit": UNIT, "ms_per_step": plug["ms_per_step"],
+                   "tok_per_s": round(1e3 / plug["ms_per_step"], 2), "h2d_bytes_per_step": plug["h2d_bytes_per_step"],
+                   "d2h_bytes_per_step": plug["d2h_bytes_per_step"], "api": plug["api"], "nmse_vs_cpu_backend": plug["nmse_vs_cpu_backend"],
+                   "caps": plug["caps"], "host_memory": plug["host_memory"], "c_abi_host_batch": e2e}
     if world == 1 and args.shapes:
         shapes = per_shape(torch, pkg, ctx, stream, ops)
     decode_batch = None
@@ -600,6 +609,28 @@ def dependent_chain_bench(torch, pkg, ctx, stream, order, args):
     res["note"] = ("129 dependent groups per step; 'stream' = one b200_mul_mat_batch launch with in-kernel completion counters, 'per_launch' = "
                    "129 launches, each waiting for its predecessor before reading its activations (defer_wait = 0)")
     return res
+
+
+def plugin_e2e(args):
+    """e2e through the drop-in boundary itself: oracle/_ref/e2e_plugin (our oracle/e2e_plugin.cpp hosted by the reference's unmodified
+    libggml) drives libggml-b200.so with ggml_backend_tensor_set_async / graph_compute_async / tensor_get_async / synchronize —
+    host buffers in pinned memory, H2D and D2H inside the timed region.  None when the reference libraries did not travel."""
+    from oracle import refenv
+    exe = refenv.REF_DIR / "e2e_plugin"
+    plugin = ROOT / "llama.cpp-s390x_b200" / "libggml-b200.so"
+    if not exe.exists() or not plugin.exists():
+        return None
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(plugin)})
+    try:
+        p = subprocess.run([str(exe), "70b" if MODEL.endswith("70B") else "8b", str(max(5, min(args.steps, 50))), str(max(3, args.warmup))],
+                           env=env, capture_output=True, text=True, timeout=600)
+        if p.returncode != 0:
+            sys.stderr.write("e2e_plugin failed: " + (p.stdout + p.stderr)[-1000:] + "\n")
+            return None
+        return json.loads(p.stdout.strip().splitlines()[-1])
+    except (OSError, ValueError, subprocess.TimeoutExpired) as exc:
+        sys.stderr.write(f"e2e_plugin: {exc}\n")
+        return None
 
 
 def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):

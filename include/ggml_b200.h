@@ -231,6 +231,21 @@ B200_API int  b200_memset(b200_ctx * ctx, void * dst_dev, int value, size_t nbyt
 /* asynchronous on the context's stream; kind: 0 = host->device, 1 = device->host, 2 = device->device */
 B200_API int  b200_memcpy_async(b200_ctx * ctx, void * dst, const void * src, size_t nbytes, int kind);
 
+/* ---- pinned host memory, events ------------------------------------------------------------------- */
+/* Page-locked host memory for the shell's host buffer type (the reference: ggml_cuda_host_malloc + the "CUDA_Host" buffer
+ * type, ggml/src/ggml-cuda/ggml-cuda.cu:1493-1542), which is what makes llama.cpp's asynchronous weight upload and the
+ * scheduler's asynchronous input copies truly asynchronous (src/llama-model-loader.cpp:1461 asks for caps.async &&
+ * caps.host_buffer && caps.events). */
+B200_API int  b200_host_malloc(size_t nbytes, void ** out);
+B200_API int  b200_host_free(void * ptr);
+/* Events on a context's stream (ggml_backend_cuda_event_record / _wait, ggml-cuda.cu:4498-4520; device event_new / _free /
+ * _synchronize, :5430-5460).  An event is created for a device and may be waited for by any context of any device. */
+B200_API int  b200_event_create(int device, void ** event_out);
+B200_API int  b200_event_destroy(int device, void * event);
+B200_API int  b200_event_record(b200_ctx * ctx, void * event);        /* after everything queued on ctx's stream so far      */
+B200_API int  b200_event_wait(b200_ctx * ctx, void * event);          /* ctx's stream waits (device side) for the event      */
+B200_API int  b200_event_synchronize(void * event);                   /* the host waits                                      */
+
 /* ---- row-split across GPUs (single process, one NCCL communicator per device) -------------------- */
 typedef struct b200_rowsplit b200_rowsplit;
 /* devices[n_dev]; split[n_dev] cumulative-free fractions (NULL = even).  Cut points are rounded down to
@@ -251,6 +266,13 @@ B200_API void b200_rowsplit_weights_free(b200_rowsplit * rs, b200_split_weights 
  * per-device streams; b200_rowsplit_synchronize waits for all. */
 B200_API int  b200_rowsplit_mul_mat(b200_rowsplit * rs, const b200_split_weights * w, float * const * x_dev, int64_t n,
                                     float * const * y_dev, int mode);
+/* The split-buffer-type form (what the shell's "ggml_backend_split_buffer_type" needs; reference: ggml_cuda_op_mul_mat's row-split
+ * driver, ggml/src/ggml-cuda/ggml-cuda.cu:1801-2119): src1 [k, n] and dst [m, n] live on ONE device — the one of main_ctx, on whose
+ * stream the op is ordered — and shards[i] holds rows [row_lo[i], row_hi[i]) of the [k, m] weight matrix on rs's device i.  The
+ * other devices fetch src1 over NVLink, run the single-GPU kernel on their shard and store their rows straight into dst (peer
+ * stores from the kernel epilogue); per-row results are bit-identical to the unsplit b200_mul_mat. */
+B200_API int  b200_rowsplit_mul_mat_main(b200_rowsplit * rs, b200_ctx * main_ctx, int type, int64_t k, int64_t m, void * const * shards,
+                                         const int64_t * row_lo, const int64_t * row_hi, const b200_tensor * src1, const b200_tensor * dst);
 B200_API int  b200_rowsplit_synchronize(b200_rowsplit * rs);
 B200_API b200_ctx * b200_rowsplit_ctx(b200_rowsplit * rs, int idx);
 

@@ -22,12 +22,17 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #define GGML_B200_NAME     "B200"
 #define GGML_B200_MAX_DEVS 16
+
+extern "C" {
+GGML_BACKEND_API ggml_backend_reg_t ggml_backend_b200_reg(void);
+}
 
 namespace {
 
@@ -46,6 +51,9 @@ struct b200_backend_ctx {
     std::string name;
     b200_ctx *  ctx;
     long        n_graphs = 0, n_mul_mat = 0, n_mul_mat_id = 0, n_fused_groups = 0;      // GGML_B200_STATS=1 prints them on free
+    void *      copy_event = nullptr;      // orders cpy_tensor_async after this backend's queued work
+    b200_rowsplit * rs = nullptr;          // row-split driver of the split buffer type this backend last computed with
+    const void *    rs_key = nullptr;
 };
 
 struct b200_buffer_ctx {
@@ -179,6 +187,206 @@ const ggml_backend_buffer_type_i k_buft_iface = {
 // context for weight placement probes (ggml-backend.cpp:38-45, llama-model-loader.cpp:919-931)
 bool buft_is_b200(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == buft_get_name; }
 bool buffer_is_b200(ggml_backend_buffer_t buffer) { return buffer && buft_is_b200(buffer->buft); }
+bool buft_is_split(ggml_backend_buffer_type_t buft);
+
+// ---- split buffer type ("ggml_backend_split_buffer_type": llama.cpp -sm row) --------------------------------------------------
+// Replaces ggml_backend_cuda_split_buffer_type (ggml-cuda.cu:855-1144): a weight matrix allocated in this buffer type is cut by
+// rows — cut points round_down(m * cumulative tensor_split, 128), get_row_split :868-881 — and shard i lives on device i.  The
+// buffer's base address is a dummy (get_base :921-926); init_tensor allocates the shards (:928-976), set_tensor scatters host
+// rows (:978-1015), get_tensor gathers them.  MUL_MAT with such a src0 runs on every device at once (b200_rowsplit_mul_mat_main);
+// MUL_MAT_ID with split weights is not supported, like in the reference (:2628).
+// GGML_B200_SPLIT_EMULATE=N (testing): N shards on ONE physical device, so a single-GPU box exercises the whole path.
+struct b200_split_buft_ctx {
+    int         main_device = 0;
+    int         n_shards = 0;
+    int         device[GGML_B200_MAX_DEVS];       // physical device of shard i
+    float       cum[GGML_B200_MAX_DEVS + 1];      // cumulative row fractions
+    std::string name;
+    ggml_backend_buffer_type buft;
+};
+
+struct b200_split_extra {
+    void *  shard[GGML_B200_MAX_DEVS] = {};
+    int64_t lo[GGML_B200_MAX_DEVS] = {}, hi[GGML_B200_MAX_DEVS] = {};
+};
+
+struct b200_split_buffer_ctx {
+    b200_split_buft_ctx * bt;
+    std::vector<b200_split_extra *> extras;
+};
+
+const char * split_buft_get_name(ggml_backend_buffer_type_t buft) { return ((b200_split_buft_ctx *) buft->context)->name.c_str(); }
+bool buft_is_split(ggml_backend_buffer_type_t buft) { return buft && buft->iface.get_name == split_buft_get_name; }
+
+b200_device_ctx * reg_device_ctx(int device) {
+    ggml_backend_reg_t reg = ggml_backend_b200_reg();
+    return (b200_device_ctx *) ggml_backend_reg_dev_get(reg, (size_t) device)->context;
+}
+
+void split_rows(const b200_split_buft_ctx * bt, int64_t m, int i, int64_t * lo, int64_t * hi) {
+    auto cut = [&](int j) -> int64_t {
+        if (j <= 0) return 0;
+        if (j >= bt->n_shards) return m;
+        int64_t r = (int64_t) ((double) m * (double) bt->cum[j]);
+        return r - r % B200_ROWSPLIT_ROUND;
+    };
+    *lo = cut(i); *hi = cut(i + 1);
+}
+
+size_t split_shard_bytes(const ggml_tensor * t, int64_t rows) {
+    size_t size = ggml_row_size(t->type, t->ne[0]) * (size_t) rows;
+    if (t->ne[0] % 512 != 0) size += ggml_row_size(t->type, 512 - t->ne[0] % 512);        // the kernels may over-read the last row in bounds
+    return size;
+}
+
+void split_buffer_free(ggml_backend_buffer_t buffer) {
+    b200_split_buffer_ctx * bc = (b200_split_buffer_ctx *) buffer->context;
+    for (b200_split_extra * e : bc->extras) {
+        for (int i = 0; i < bc->bt->n_shards; ++i) if (e->shard[i]) b200_free(bc->bt->device[i], e->shard[i]);
+        delete e;
+    }
+    delete bc;
+}
+
+void * split_buffer_get_base(ggml_backend_buffer_t) { return (void *) 0x1000; }      // tensors in a split buffer have no single address
+
+ggml_status split_buffer_init_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor) {
+    GGML_ASSERT(tensor->view_src == nullptr);                       // views of split tensors are not supported (ggml-cuda.cu:929)
+    GGML_ASSERT(ggml_is_contiguous(tensor) && tensor->ne[2] * tensor->ne[3] == 1 && "split tensors must be contiguous 2-D matrices");
+    b200_split_buffer_ctx * bc = (b200_split_buffer_ctx *) buffer->context;
+    b200_split_extra * e = new b200_split_extra;
+    bc->extras.push_back(e);
+    for (int i = 0; i < bc->bt->n_shards; ++i) {
+        split_rows(bc->bt, tensor->ne[1], i, &e->lo[i], &e->hi[i]);
+        const int64_t rows = e->hi[i] - e->lo[i];
+        if (rows <= 0) continue;
+        const size_t bytes = split_shard_bytes(tensor, rows);
+        if (b200_malloc(bc->bt->device[i], bytes + 512, &e->shard[i]) != B200_OK) {
+            GGML_LOG_ERROR("ggml-b200: split shard of %s on device %d: %s\n", tensor->name, bc->bt->device[i], b200_last_error());
+            return GGML_STATUS_ALLOC_FAILED;
+        }
+        // the padding past the last row must not hold NaN patterns (it is multiplied by activations that are zero there)
+        const size_t body = ggml_row_size(tensor->type, tensor->ne[0]) * (size_t) rows;
+        check(b200_memset(device_util_ctx(reg_device_ctx(bc->bt->device[i])), (char *) e->shard[i] + body, 0, bytes + 512 - body), "split pad");
+    }
+    tensor->extra = e;
+    return GGML_STATUS_SUCCESS;
+}
+
+void split_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * tensor, const void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "split tensors are set as a whole (ggml-cuda.cu:979-981)");
+    b200_split_buffer_ctx * bc = (b200_split_buffer_ctx *) buffer->context;
+    b200_split_extra * e = (b200_split_extra *) tensor->extra;
+    const size_t rb = ggml_row_size(tensor->type, tensor->ne[0]);
+    for (int i = 0; i < bc->bt->n_shards; ++i) {
+        const int64_t rows = e->hi[i] - e->lo[i];
+        if (rows <= 0) continue;
+        check(b200_memcpy_h2d(device_util_ctx(reg_device_ctx(bc->bt->device[i])), e->shard[i], (const char *) data + rb * e->lo[i], rb * rows), "split set_tensor");
+    }
+}
+
+void split_buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * tensor, void * data, size_t offset, size_t size) {
+    GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor));
+    b200_split_buffer_ctx * bc = (b200_split_buffer_ctx *) buffer->context;
+    const b200_split_extra * e = (const b200_split_extra *) tensor->extra;
+    const size_t rb = ggml_row_size(tensor->type, tensor->ne[0]);
+    for (int i = 0; i < bc->bt->n_shards; ++i) {
+        const int64_t rows = e->hi[i] - e->lo[i];
+        if (rows <= 0) continue;
+        check(b200_memcpy_d2h(device_util_ctx(reg_device_ctx(bc->bt->device[i])), (char *) data + rb * e->lo[i], e->shard[i], rb * rows), "split get_tensor");
+    }
+}
+
+void split_buffer_clear(ggml_backend_buffer_t, uint8_t) {}            // (no-op in the reference too, ggml-cuda.cu:1051-1054)
+
+const ggml_backend_buffer_i k_split_buffer_iface = {
+    /* .free_buffer   = */ split_buffer_free,
+    /* .get_base      = */ split_buffer_get_base,
+    /* .init_tensor   = */ split_buffer_init_tensor,
+    /* .memset_tensor = */ nullptr,
+    /* .set_tensor    = */ split_buffer_set_tensor,
+    /* .get_tensor    = */ split_buffer_get_tensor,
+    /* .set_tensor_2d = */ nullptr,
+    /* .get_tensor_2d = */ nullptr,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ split_buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+ggml_backend_buffer_t split_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    // the shards are allocated tensor by tensor in init_tensor; `size` (the sum of get_alloc_size) is only accounted for
+    return ggml_backend_buffer_init(buft, k_split_buffer_iface, new b200_split_buffer_ctx{(b200_split_buft_ctx *) buft->context, {}}, size);
+}
+
+size_t split_buft_get_alloc_size(ggml_backend_buffer_type_t buft, const ggml_tensor * tensor) {
+    const b200_split_buft_ctx * bt = (const b200_split_buft_ctx *) buft->context;
+    size_t total = 0;
+    for (int i = 0; i < bt->n_shards; ++i) {
+        int64_t lo, hi;
+        split_rows(bt, tensor->ne[1], i, &lo, &hi);
+        if (hi > lo) total += split_shard_bytes(tensor, hi - lo);
+    }
+    return total;
+}
+
+const ggml_backend_buffer_type_i k_split_buft_iface = {
+    /* .get_name       = */ split_buft_get_name,
+    /* .alloc_buffer   = */ split_buft_alloc_buffer,
+    /* .get_alignment  = */ buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ split_buft_get_alloc_size,
+    /* .is_host        = */ buft_is_host,
+};
+
+// the proc address llama.cpp asks for (src/llama-model.cpp:885-897): one buffer type object per (main device, split)
+ggml_backend_buffer_type_t split_buffer_type(int main_device, const float * tensor_split) {
+    static std::mutex mutex;
+    static std::map<std::pair<int, std::vector<float>>, b200_split_buft_ctx *> cache;
+    std::lock_guard<std::mutex> lock(mutex);
+    const int n_phys = (int) ggml_backend_reg_dev_count(ggml_backend_b200_reg());
+    if (n_phys < 1 || main_device < 0 || main_device >= n_phys) return nullptr;
+    int emulate = 0;
+    if (const char * e = getenv("GGML_B200_SPLIT_EMULATE")) emulate = atoi(e);
+    const int n = emulate > 1 ? (emulate < 8 ? emulate : 8) : (n_phys < 8 ? n_phys : 8);
+    std::vector<float> split((size_t) n, 0.0f);
+    bool all_zero = true;
+    for (int i = 0; i < n; ++i) { split[i] = tensor_split ? tensor_split[i] : 0.0f; all_zero = all_zero && split[i] == 0.0f; }
+    if (all_zero) for (int i = 0; i < n; ++i) split[i] = 1.0f;          // (the reference defaults to the devices' memory sizes: equal here)
+    auto key = std::make_pair(main_device, split);
+    auto it = cache.find(key);
+    if (it != cache.end()) return &it->second->buft;
+    b200_split_buft_ctx * bt = new b200_split_buft_ctx;
+    bt->main_device = main_device; bt->n_shards = n;
+    float total = 0.0f, acc = 0.0f;
+    for (int i = 0; i < n; ++i) total += split[i];
+    for (int i = 0; i < n; ++i) { bt->device[i] = emulate > 1 ? main_device : i; bt->cum[i] = acc / total; acc += split[i]; }
+    bt->cum[n] = 1.0f;
+    bt->name = GGML_B200_NAME "_Split";
+    bt->buft = ggml_backend_buffer_type{ k_split_buft_iface, ggml_backend_reg_dev_get(ggml_backend_b200_reg(), (size_t) main_device), bt };
+    cache[key] = bt;
+    return &bt->buft;
+}
+
+// src0 of a MUL_MAT node lives in a split buffer
+bool split_src0(const ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0];
+    return a && a->buffer && buft_is_split(a->buffer->buft);
+}
+
+int split_mul_mat(b200_backend_ctx * bctx, const ggml_tensor * node) {
+    const ggml_tensor * a = node->src[0];
+    const b200_split_buft_ctx * bt = (const b200_split_buft_ctx *) a->buffer->buft->context;
+    const b200_split_extra * e = (const b200_split_extra *) a->extra;
+    if (bctx->rs_key != bt) {
+        if (bctx->rs) { b200_rowsplit_destroy(bctx->rs); bctx->rs = nullptr; }
+        const int rc = b200_rowsplit_create(bt->device, bt->n_shards, nullptr, &bctx->rs);
+        if (rc != B200_OK) return rc;
+        bctx->rs_key = bt;
+    }
+    const b200_tensor b = to_b200(node->src[1]), d = to_b200(node);
+    bctx->n_mul_mat++;
+    return b200_rowsplit_mul_mat_main(bctx->rs, bctx->ctx, (int) a->type, a->ne[0], a->ne[1], e->shard, e->lo, e->hi, &b, &d);
+}
 
 // ---- backend (stream) -------------------------------------------------------------------------------------------------------
 const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ctx *) backend->context)->name.c_str(); }
@@ -189,6 +397,8 @@ void backend_free(ggml_backend_t backend) {
         fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld\n", bctx->n_graphs, bctx->n_mul_mat,
                 bctx->n_mul_mat_id, bctx->n_fused_groups);
     }
+    if (bctx->copy_event) b200_event_destroy(bctx->device, bctx->copy_event);
+    if (bctx->rs) b200_rowsplit_destroy(bctx->rs);
     b200_ctx_destroy(bctx->ctx);
     delete bctx;
     delete backend;
@@ -210,59 +420,91 @@ bool is_view_op(ggml_op op) {
     return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE;
 }
 
+// graph_compute: every maximal run of MUL_MAT nodes (view ops in between need no work) goes to the kernels as ONE list,
+// b200_mul_mat_batch — the list is executed as if in node order (dependencies between its nodes are found from the tensors'
+// address ranges), runs of Q4_K decode matmuls become one persistent launch, nodes that share their activations (wq / wk / wv,
+// ffn_gate / ffn_up of a llama graph) share one quantization of them.  The reference's CUDA backend reaches the same end by
+// capturing the whole cgraph into a CUDA graph (ggml-cuda.cu:4457-4490).
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     bctx->n_graphs++;
+    std::vector<b200_tensor> ta, tb, td;
+    std::vector<const b200_tensor *> pa, pb, pd;
+    auto flush = [&]() -> int {
+        const int n = (int) ta.size();
+        if (n == 0) return B200_OK;
+        pa.resize(n); pb.resize(n); pd.resize(n);
+        for (int j = 0; j < n; ++j) { pa[j] = &ta[j]; pb[j] = &tb[j]; pd[j] = &td[j]; }
+        const int rc = n == 1 ? b200_mul_mat(bctx->ctx, pa[0], pb[0], pd[0]) : b200_mul_mat_batch(bctx->ctx, n, pa.data(), pb.data(), pd.data());
+        bctx->n_mul_mat += n;
+        bctx->n_fused_groups += n > 1;
+        ta.clear(); tb.clear(); td.clear();
+        return rc;
+    };
+    auto failed = [&](int rc, const ggml_tensor * node) -> ggml_status {
+        if (rc == B200_E_ALLOC) return GGML_STATUS_ALLOC_FAILED;
+        GGML_LOG_ERROR("ggml-b200: %s (%s) failed: %s\n", ggml_op_name(node->op), node->name, b200_last_error());
+        return GGML_STATUS_FAILED;
+    };
+    const ggml_tensor * last_mm = nullptr;
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         ggml_tensor * node = cgraph->nodes[i];
         if (ggml_is_empty(node) || is_view_op(node->op)) continue;
         if ((node->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) continue;
-        int rc;
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
-                // the MUL_MAT nodes that follow and read the same activations (wq / wk / wv, ffn_gate / ffn_up in a llama graph)
-                // run in the same launch (b200_mul_mat_multi); they are independent: their weights are not results of the group
-                ggml_tensor * group[3] = {node, nullptr, nullptr};
-                int n_group = 1, last = i;
-                for (int j = i + 1; j < cgraph->n_nodes && n_group < 3; ++j) {
-                    ggml_tensor * nx = cgraph->nodes[j];
-                    if (ggml_is_empty(nx) || is_view_op(nx->op)) continue;
-                    if (nx->op != GGML_OP_MUL_MAT || nx->src[1] != node->src[1] || (nx->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) break;
-                    bool independent = true;
-                    for (int g = 0; g < n_group; ++g) independent = independent && nx->src[0] != group[g] && nx->src[0]->view_src != group[g];
-                    if (!independent) break;
-                    group[n_group++] = nx;
-                    last = j;
+                if (split_src0(node)) {
+                    int rc = flush();
+                    if (rc == B200_OK) rc = split_mul_mat(bctx, node);
+                    if (rc != B200_OK) return failed(rc, node);
+                    break;
                 }
-                bctx->n_mul_mat += n_group;
-                bctx->n_fused_groups += n_group > 1;
-                if (n_group == 1) {
-                    const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), d = to_b200(node);
-                    rc = b200_mul_mat(bctx->ctx, &a, &b, &d);
-                } else {
-                    b200_tensor a[3], d[3];
-                    const b200_tensor * ap[3], * dp[3];
-                    for (int g = 0; g < n_group; ++g) { a[g] = to_b200(group[g]->src[0]); d[g] = to_b200(group[g]); ap[g] = &a[g]; dp[g] = &d[g]; }
-                    const b200_tensor b = to_b200(node->src[1]);
-                    rc = b200_mul_mat_multi(bctx->ctx, n_group, ap, &b, dp);
-                    i = last;       // view nodes in between need no work
-                }
+                ta.push_back(to_b200(node->src[0])); tb.push_back(to_b200(node->src[1])); td.push_back(to_b200(node));
+                last_mm = node;
             } break;
             case GGML_OP_MUL_MAT_ID: {
+                int rc = flush();
+                if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
                 const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), ids = to_b200(node->src[2]), d = to_b200(node);
                 rc = b200_mul_mat_id(bctx->ctx, &a, &b, &ids, &d);
                 bctx->n_mul_mat_id++;
+                if (rc != B200_OK) return failed(rc, node);
             } break;
             default:
                 GGML_ABORT("ggml-b200: op %s reached graph_compute but supports_op() rejects it", ggml_op_name(node->op));
         }
-        if (rc == B200_E_ALLOC) return GGML_STATUS_ALLOC_FAILED;
-        if (rc != B200_OK) {
-            GGML_LOG_ERROR("ggml-b200: %s (%s) failed: %s\n", ggml_op_name(node->op), node->name, b200_last_error());
-            return GGML_STATUS_FAILED;
-        }
     }
+    const int rc = flush();
+    if (rc != B200_OK) return failed(rc, last_mm ? last_mm : cgraph->nodes[0]);
     return GGML_STATUS_SUCCESS;
+}
+
+// ---- events, asynchronous copies (ggml_backend_cuda_event_record / _wait, ggml-cuda.cu:4498-4520; cpy_tensor_async :3177) ----
+void backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    check(b200_event_record(((b200_backend_ctx *) backend->context)->ctx, event->context), "event_record");
+}
+
+void backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    check(b200_event_wait(((b200_backend_ctx *) backend->context)->ctx, event->context), "event_wait");
+}
+
+bool backend_is_b200(ggml_backend_t backend);
+
+// device-to-device copy between two of our backends (any two devices), ordered after the source backend's queued work and
+// executed on the destination backend's stream
+bool backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const ggml_tensor * src, ggml_tensor * dst) {
+    if (!backend_is_b200(backend_src) || !backend_is_b200(backend_dst)) return false;
+    ggml_backend_buffer_t sbuf = src->view_src ? src->view_src->buffer : src->buffer;
+    ggml_backend_buffer_t dbuf = dst->view_src ? dst->view_src->buffer : dst->buffer;
+    if (!buffer_is_b200(sbuf) || !buffer_is_b200(dbuf) || buft_is_split(sbuf->buft) || buft_is_split(dbuf->buft)) return false;
+    b200_backend_ctx * cs = (b200_backend_ctx *) backend_src->context, * cd = (b200_backend_ctx *) backend_dst->context;
+    if (cs != cd) {
+        if (!cs->copy_event) check(b200_event_create(cs->device, &cs->copy_event), "event_create");
+        check(b200_event_record(cs->ctx, cs->copy_event), "event_record");
+        check(b200_event_wait(cd->ctx, cs->copy_event), "event_wait");
+    }
+    check(b200_memcpy_async(cd->ctx, dst->data, src->data, ggml_nbytes(src), 2), "cpy_tensor_async");
+    return true;
 }
 
 const ggml_backend_i k_backend_iface = {
@@ -272,17 +514,19 @@ const ggml_backend_i k_backend_iface = {
     /* .get_tensor_async    = */ backend_get_tensor_async,
     /* .set_tensor_2d_async = */ nullptr,
     /* .get_tensor_2d_async = */ nullptr,
-    /* .cpy_tensor_async    = */ nullptr,
+    /* .cpy_tensor_async    = */ backend_cpy_tensor_async,
     /* .synchronize         = */ backend_synchronize,
     /* .graph_plan_create   = */ nullptr,
     /* .graph_plan_free     = */ nullptr,
     /* .graph_plan_update   = */ nullptr,
     /* .graph_plan_compute  = */ nullptr,
     /* .graph_compute       = */ backend_graph_compute,
-    /* .event_record        = */ nullptr,
-    /* .event_wait          = */ nullptr,
+    /* .event_record        = */ backend_event_record,
+    /* .event_wait          = */ backend_event_wait,
     /* .graph_optimize      = */ nullptr,
 };
+
+bool backend_is_b200(ggml_backend_t backend) { return backend && backend->iface.get_name == backend_get_name; }
 
 ggml_guid_t backend_guid() {
     static ggml_guid guid = { 0xb2, 0x00, 0x51, 0x10, 0x0a, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x01 };
@@ -308,10 +552,10 @@ void device_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
     props->device_id   = nullptr;
     device_get_memory(dev, &props->memory_free, &props->memory_total);
     props->caps = {
-        /* .async                = */ false,
-        /* .host_buffer          = */ false,
+        /* .async                = */ true,       // graph_compute, set/get/cpy_tensor_async only queue work on the backend's stream
+        /* .host_buffer          = */ true,       // pinned host buffer type below
         /* .buffer_from_host_ptr = */ false,
-        /* .events               = */ false,
+        /* .events               = */ true,
     };
 }
 
@@ -338,10 +582,12 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
         case GGML_OP_MUL_MAT: {
             if (!op->src[0] || !op->src[1]) return false;
             const b200_tensor a = to_b200(op->src[0]), b = to_b200(op->src[1]), d = to_b200(op);
+            if (split_src0(op) && (op->src[1]->ne[2] * op->src[1]->ne[3] != 1 || (op->ne[1] > 1 && op->nb[1] != (size_t) op->ne[0] * 4))) return false;
             return b200_mul_mat_supported(&a, &b, &d) != 0;
         }
         case GGML_OP_MUL_MAT_ID: {
             if (!op->src[0] || !op->src[1] || !op->src[2]) return false;
+            if (split_src0(op)) return false;                      // like the reference (ggml-cuda.cu:2628)
             const b200_tensor a = to_b200(op->src[0]), b = to_b200(op->src[1]), ids = to_b200(op->src[2]), d = to_b200(op);
             return b200_mul_mat_id_supported(&a, &b, &ids, &d) != 0;
         }
@@ -351,8 +597,58 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
 }
 
 bool device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    if (buft_is_split(buft)) {
+        // the main device's backend computes with split weights (the other devices take part through the row-split driver)
+        return buft->device == dev;
+    }
     return buft_is_b200(buft) && buft->device == dev;
 }
+
+// ---- pinned host buffer type (ggml_backend_cuda_host_buffer_type, ggml-cuda.cu:1493-1542): plain CPU buffers over page-locked
+// memory, so the scheduler's input copies and llama.cpp's weight upload run asynchronously -------------------------------------
+const char * host_buft_get_name(ggml_backend_buffer_type_t) { return GGML_B200_NAME "_Host"; }
+
+void host_buffer_free(ggml_backend_buffer_t buffer) { b200_host_free(buffer->context); }
+
+ggml_backend_buffer_t host_buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    void * ptr = nullptr;
+    if (b200_host_malloc(size, &ptr) != B200_OK) {
+        return ggml_backend_buft_alloc_buffer(ggml_backend_cpu_buffer_type(), size);      // pageable memory still works, synchronously
+    }
+    ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
+    buffer->buft = buft;
+    buffer->iface.free_buffer = host_buffer_free;
+    return buffer;
+}
+
+ggml_backend_buffer_type_t device_get_host_buffer_type(ggml_backend_dev_t dev) {
+    static ggml_backend_buffer_type host_buft[GGML_B200_MAX_DEVS];
+    static std::once_flag once;
+    std::call_once(once, [] {
+        ggml_backend_buffer_type_t cpu = ggml_backend_cpu_buffer_type();
+        for (auto & b : host_buft) {
+            b.iface = { host_buft_get_name, host_buft_alloc_buffer, cpu->iface.get_alignment, nullptr, cpu->iface.get_alloc_size, cpu->iface.is_host };
+            b.device = nullptr; b.context = nullptr;
+        }
+    });
+    b200_device_ctx * dctx = (b200_device_ctx *) dev->context;
+    host_buft[dctx->device].device = dev;
+    return &host_buft[dctx->device];
+}
+
+// ---- device events (ggml_backend_cuda_device_event_new / _free / _synchronize, ggml-cuda.cu:5430-5460) ------------------------
+ggml_backend_event_t device_event_new(ggml_backend_dev_t dev) {
+    void * ev = nullptr;
+    if (b200_event_create(((b200_device_ctx *) dev->context)->device, &ev) != B200_OK) return nullptr;
+    return new ggml_backend_event{ /* .device = */ dev, /* .context = */ ev };
+}
+
+void device_event_free(ggml_backend_dev_t dev, ggml_backend_event_t event) {
+    b200_event_destroy(((b200_device_ctx *) dev->context)->device, event->context);
+    delete event;
+}
+
+void device_event_synchronize(ggml_backend_dev_t, ggml_backend_event_t event) { check(b200_event_synchronize(event->context), "event_synchronize"); }
 
 const ggml_backend_device_i k_device_iface = {
     /* .get_name             = */ device_get_name,
@@ -362,14 +658,14 @@ const ggml_backend_device_i k_device_iface = {
     /* .get_props            = */ device_get_props,
     /* .init_backend         = */ device_init_backend,
     /* .get_buffer_type      = */ device_get_buffer_type,
-    /* .get_host_buffer_type = */ nullptr,
+    /* .get_host_buffer_type = */ device_get_host_buffer_type,
     /* .buffer_from_host_ptr = */ nullptr,
     /* .supports_op          = */ device_supports_op,
     /* .supports_buft        = */ device_supports_buft,
     /* .offload_op           = */ nullptr,
-    /* .event_new            = */ nullptr,
-    /* .event_free           = */ nullptr,
-    /* .event_synchronize    = */ nullptr,
+    /* .event_new            = */ device_event_new,
+    /* .event_free           = */ device_event_free,
+    /* .event_synchronize    = */ device_event_synchronize,
 };
 
 // ---- registry --------------------------------------------------------------------------------------------------------------
@@ -398,6 +694,7 @@ ggml_backend_feature * get_features(ggml_backend_reg_t) {
 
 void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
+    if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;      // ggml_backend_split_buffer_type_t
     return nullptr;
 }
 
@@ -409,10 +706,6 @@ const ggml_backend_reg_i k_reg_iface = {
 };
 
 }  // namespace
-
-extern "C" {
-GGML_BACKEND_API ggml_backend_reg_t ggml_backend_b200_reg(void);
-}
 
 ggml_backend_reg_t ggml_backend_b200_reg(void) {
     static ggml_backend_reg reg;

@@ -611,6 +611,63 @@ int b200_memcpy_async(b200_ctx * ctx, void * dst, const void * src, size_t nbyte
     return B200_OK;
 }
 
+// ---- pinned host memory and events (what the shell needs to report caps.host_buffer / caps.events / caps.async) --------------
+int b200_host_malloc(size_t nbytes, void ** out) {
+    if (!out) return B200_E_ARG;
+    *out = nullptr;
+    const cudaError_t err = cudaMallocHost(out, nbytes);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        b200_set_error("cudaMallocHost(%zu): %s", nbytes, cudaGetErrorString(err));
+        return B200_E_ALLOC;
+    }
+    return B200_OK;
+}
+
+int b200_host_free(void * ptr) {
+    if (!ptr) return B200_OK;
+    B200_CUDA_TRY(cudaFreeHost(ptr));
+    return B200_OK;
+}
+
+int b200_event_create(int device, void ** out) {
+    if (!out) return B200_E_ARG;
+    *out = nullptr;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    cudaEvent_t ev;
+    B200_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    *out = (void *) ev;
+    return B200_OK;
+}
+
+int b200_event_destroy(int device, void * event) {
+    if (!event) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    B200_CUDA_TRY(cudaEventDestroy((cudaEvent_t) event));
+    return B200_OK;
+}
+
+int b200_event_record(b200_ctx * ctx, void * event) {
+    if (!ctx || !event) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaEventRecord((cudaEvent_t) event, ctx->stream));
+    return B200_OK;
+}
+
+int b200_event_wait(b200_ctx * ctx, void * event) {
+    if (!ctx || !event) return B200_E_ARG;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamWaitEvent(ctx->stream, (cudaEvent_t) event, 0));
+    ctx->n_pend = 16;       // whatever the event orders is not a kernel of this context: the next GEMV waits before it reads
+    return B200_OK;
+}
+
+int b200_event_synchronize(void * event) {
+    if (!event) return B200_E_ARG;
+    B200_CUDA_TRY(cudaEventSynchronize((cudaEvent_t) event));
+    return B200_OK;
+}
+
 // ---- host-buffer convenience ------------------------------------------------------------------------------------------
 int b200_weights_upload(b200_ctx * ctx, int type, const void * host_rows, int64_t k, int64_t m, void ** dev_out) {
     if (!ctx || !host_rows || !dev_out || !is_weight_type(type) || k % b200_blck(type) != 0) {

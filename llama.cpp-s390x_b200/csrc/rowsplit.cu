@@ -71,7 +71,10 @@ struct b200_rowsplit {
     cudaEvent_t ev[B200_MAX_PEERS];
     float *     stage[B200_MAX_PEERS];       // per device: its own shard result [n][rows_i]
     float *     gather[B200_MAX_PEERS];      // per device: concatenation of all shards' blocks (mode 0, n > 1)
-    size_t      stage_size[B200_MAX_PEERS], gather_size[B200_MAX_PEERS];
+    float *     xstage[B200_MAX_PEERS];      // per device: its copy of the main device's activations (b200_rowsplit_mul_mat_main)
+    size_t      stage_size[B200_MAX_PEERS], gather_size[B200_MAX_PEERS], xstage_size[B200_MAX_PEERS];
+    cudaEvent_t ev_main;                     // on the main context's device
+    int         ev_main_dev;
     bool        nccl_tried, nccl_ok;
     nccl_api    nccl;
     nccl_comm_t comm[B200_MAX_PEERS];
@@ -120,7 +123,7 @@ int b200_rowsplit_create(const int * devices, int n_dev, const float * split, b2
     for (int i = 0; i < n_dev; ++i) {
         cudaSetDevice(devices[i]);
         for (int j = 0; j < n_dev; ++j) {
-            if (i == j) continue;
+            if (i == j || devices[i] == devices[j]) continue;      // (one device listed twice: a split emulated on one GPU)
             int can = 0;
             cudaDeviceCanAccessPeer(&can, devices[i], devices[j]);
             if (!can) { b200_set_error("devices %d and %d have no peer access", devices[i], devices[j]); b200_rowsplit_destroy(rs); return B200_E_UNSUPPORTED; }
@@ -145,9 +148,11 @@ void b200_rowsplit_destroy(b200_rowsplit * rs) {
         if (rs->nccl_ok && rs->comm[i]) rs->nccl.CommDestroy(rs->comm[i]);
         if (rs->stage[i]) cudaFree(rs->stage[i]);
         if (rs->gather[i]) cudaFree(rs->gather[i]);
+        if (rs->xstage[i]) cudaFree(rs->xstage[i]);
         if (rs->ev[i]) cudaEventDestroy(rs->ev[i]);
         if (rs->ctx[i]) b200_ctx_destroy(rs->ctx[i]);
     }
+    if (rs->ev_main) { cudaSetDevice(rs->ev_main_dev); cudaEventDestroy(rs->ev_main); }
     free(rs);
 }
 
@@ -296,6 +301,64 @@ int b200_rowsplit_mul_mat(b200_rowsplit * rs, const b200_split_weights * w, floa
         B200_CUDA_TRY(cudaSetDevice(rs->dev[i]));
         for (int j = 0; j < G; ++j) if (j != i) B200_CUDA_TRY(cudaStreamWaitEvent(rs->ctx[i]->stream, rs->ev[j], 0));
     }
+    return B200_OK;
+}
+
+// MUL_MAT whose weights are row-split over the devices while src1 and dst live on ONE device (the contract of the reference's
+// split buffer type: ggml_cuda_op_mul_mat broadcasts src1 from the main device and copies the dst row slices back to it,
+// ggml-cuda.cu:1801-2119).  Ordered on main_ctx's stream: the other devices' streams wait for it, fetch the activations over
+// NVLink, run the single-GPU kernel on their shard — whose epilogue stores the results straight into the main device's dst
+// (peer stores, mm_store) — and main_ctx's stream waits for them.
+int b200_rowsplit_mul_mat_main(b200_rowsplit * rs, b200_ctx * main_ctx, int type, int64_t k, int64_t m, void * const * shards,
+                               const int64_t * row_lo, const int64_t * row_hi, const b200_tensor * src1, const b200_tensor * dst) {
+    device_guard guard;
+    if (!rs || !main_ctx || !shards || !row_lo || !row_hi || !src1 || !dst) { b200_set_error("rowsplit_mul_mat_main: bad arguments"); return B200_E_ARG; }
+    const int64_t n = src1->ne[1];
+    if (src1->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32 || src1->ne[0] != k || src1->nb[0] != 4 || src1->ne[2] * src1->ne[3] != 1 ||
+        dst->ne[0] != m || dst->ne[1] != n || dst->ne[2] * dst->ne[3] != 1 || dst->nb[0] != 4 || (n > 1 && dst->nb[1] != m * 4)) {
+        b200_set_error("rowsplit_mul_mat_main: src1 [k, n] f32 and a contiguous dst [m, n] f32 without batch dims"); return B200_E_UNSUPPORTED;
+    }
+    if (n == 0 || m == 0) return B200_OK;
+    const int G = rs->n_dev;
+    const size_t rb = b200_row_size(type, k);
+    if (!rs->ev_main || rs->ev_main_dev != main_ctx->device) {
+        if (rs->ev_main) { cudaSetDevice(rs->ev_main_dev); cudaEventDestroy(rs->ev_main); rs->ev_main = nullptr; }
+        B200_CUDA_TRY(cudaSetDevice(main_ctx->device));
+        B200_CUDA_TRY(cudaEventCreateWithFlags(&rs->ev_main, cudaEventDisableTiming));
+        rs->ev_main_dev = main_ctx->device;
+    }
+    B200_CUDA_TRY(cudaSetDevice(main_ctx->device));
+    B200_CUDA_TRY(cudaEventRecord(rs->ev_main, main_ctx->stream));
+    float * peer[1] = { (float *) dst->data };
+    for (int i = 0; i < G; ++i) {
+        const int64_t rows = row_hi[i] - row_lo[i];
+        if (rows <= 0) continue;
+        if (!shards[i]) { b200_set_error("rowsplit_mul_mat_main: shard %d is NULL", i); return B200_E_ARG; }
+        b200_ctx * ci = rs->ctx[i];
+        int rc = ensure(rs->dev[i], &rs->stage[i], &rs->stage_size[i], (size_t) rows * n * 4);
+        if (rc) return rc;
+        B200_CUDA_TRY(cudaSetDevice(rs->dev[i]));
+        B200_CUDA_TRY(cudaStreamWaitEvent(ci->stream, rs->ev_main, 0));
+        b200_tensor a = {}, b = *src1, d = {};
+        if (rs->dev[i] != main_ctx->device) {
+            rc = ensure(rs->dev[i], &rs->xstage[i], &rs->xstage_size[i], (size_t) k * n * 4);
+            if (rc) return rc;
+            B200_CUDA_TRY(cudaMemcpy2DAsync(rs->xstage[i], (size_t) k * 4, src1->data, (size_t) (n > 1 ? src1->nb[1] : k * 4), (size_t) k * 4, (size_t) n,
+                                            cudaMemcpyDefault, ci->stream));
+            b.data = rs->xstage[i]; b.nb[1] = k * 4; b.nb[2] = b.nb[3] = k * 4 * n;
+        }
+        a.data = shards[i]; a.type = type; a.ne[0] = k; a.ne[1] = rows; a.ne[2] = a.ne[3] = 1;
+        a.nb[0] = b200_tsize(type); a.nb[1] = (int64_t) rb; a.nb[2] = a.nb[3] = (int64_t) rb * rows;
+        d.data = rs->stage[i]; d.type = B200_TYPE_F32; d.ne[0] = rows; d.ne[1] = n; d.ne[2] = d.ne[3] = 1;
+        d.nb[0] = 4; d.nb[1] = rows * 4; d.nb[2] = d.nb[3] = rows * 4 * n;
+        ci->n_pend = 16;                                   // its activations arrive by a copy / another stream: wait before reading them
+        rc = b200_mul_mat_ex(ci, &a, &b, &d, 1, peer, m, row_lo[i]);
+        if (rc) return rc;
+        B200_CUDA_TRY(cudaEventRecord(rs->ev[i], ci->stream));
+    }
+    B200_CUDA_TRY(cudaSetDevice(main_ctx->device));
+    for (int i = 0; i < G; ++i) if (row_hi[i] > row_lo[i]) B200_CUDA_TRY(cudaStreamWaitEvent(main_ctx->stream, rs->ev[i], 0));
+    main_ctx->n_pend = 16;
     return B200_OK;
 }
 

@@ -64,3 +64,40 @@ def test_layer_graph_through_sched(wtype, n_tokens):
     assert m, out[-2000:]
     # 3 layers x 7 matmuls x 2 passes; two fused groups per layer and pass
     assert int(m.group(2)) == 3 * 7 * 2 and int(m.group(4)) == 3 * 2 * 2, m.group(0)
+
+
+SPLIT_CHECK = refenv.REF_DIR / "split_check"
+
+
+@pytest.mark.parametrize("args,shards", [(("q4_K", "4096", "4096", "1", "0.5"), 2), (("q4_K", "1536", "2048", "4", "0.3"), 3), (("q8_0", "1000", "1024", "5", "0.6"), 2),
+                                         (("q6_K", "1280", "2048", "1", "0.5"), 4), (("q4_0", "2048", "512", "8", "0.5"), 2), (("q4_K", "2048", "4096", "64", "0.4"), 2),
+                                         (("q8_0", "4096", "4096", "512", "0.5"), 2)])
+def test_split_buffer_type(args, shards):
+    """oracle/split_check.cpp: "ggml_backend_split_buffer_type" from the registry (llama.cpp -sm row), weights scattered by
+    set_tensor, MUL_MAT with src1 / dst on the main device == the unsplit result bit for bit and == the CPU backend within
+    NMSE 5e-4; the llama.cpp weight placement probe passes; MUL_MAT_ID with split weights is rejected.  The shards are emulated
+    on the one GPU of the test box (GGML_B200_SPLIT_EMULATE); on a multi-GPU box the same binary runs over real devices."""
+    if not SPLIT_CHECK.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/split_check or libggml-b200.so not built (needs /root/reference at build time)")
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN), "GGML_B200_SPLIT_EMULATE": str(shards)})
+    p = subprocess.run([str(SPLIT_CHECK), *args], env=env, capture_output=True, text=True, timeout=300)
+    out = p.stdout + p.stderr
+    assert p.returncode == 0 and "OK" in p.stdout.splitlines()[-1], out[-2000:]
+    assert "buft=B200_Split" in out and "split==plain:1" in out, out[-2000:]
+
+
+E2E_PLUGIN = refenv.REF_DIR / "e2e_plugin"
+
+
+def test_e2e_through_the_plugin_small():
+    """oracle/e2e_plugin.cpp (bench.py's e2e leg) on a tiny model: set_async -> graph_compute_async -> get_async -> synchronize
+    through libggml-b200.so, pinned host memory from the plug-in's host buffer type, spot check against the CPU backend"""
+    if not E2E_PLUGIN.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/e2e_plugin or libggml-b200.so not built (needs /root/reference at build time)")
+    import json
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN)})
+    p = subprocess.run([str(E2E_PLUGIN), "tiny", "3", "1"], env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+    d = json.loads(p.stdout.strip().splitlines()[-1])
+    assert d["n_matmuls"] == 15 and d["nmse_vs_cpu_backend"] <= 5e-4
+    assert d["caps"] == {"async": 1, "host_buffer": 1, "events": 1} and d["host_memory"] == "B200_Host"
