@@ -273,6 +273,16 @@ def run_gpu(args):
         assert torch.equal(ybuf[:4096].view(1, -1), full), "fused row-split all-gather differs from the unsplit result"
     use_flags = world > 1 and args.gather_sync == "flags"
     use_ll = world > 1 and args.gather_sync == "ll"
+    use_sg = world > 1 and args.gather_sync == "stream"
+    if use_sg:
+        # the persistent job-table kernel with the all-gather folded in (b200_mul_mat_batch_gather): exchange buffers of 2 slots
+        sg_cap = (sum((m + 3) // 4 * 4 for _, m, _, c in LLAMA3_8B for _ in range(c)) + 3) // 4 * 4
+        sgbuf = symm_mem.empty(2 * sg_cap, dtype=torch.int64, device=torch.device("cuda", local))
+        sgbuf.zero_()
+        sghdl = symm_mem.rendezvous(sgbuf, dist.group.WORLD)
+        torch.cuda.synchronize(); sghdl.barrier(channel=0); torch.cuda.synchronize()
+        pkg.stream_comm_init(ctx, rank, world, [int(p) for p in sghdl.buffer_ptrs], sg_cap)
+        torch.cuda.synchronize(); sghdl.barrier(channel=0); torch.cuda.synchronize()
     if use_ll:
         # LL exchange (b200_gather_ll_init): {value, epoch} in one 8-byte store per result, receiver kernel polls its local slot
         cap = maxm
@@ -309,7 +319,7 @@ def run_gpu(args):
             if world == 1:
                 y = torch.empty((1, m), device="cuda")
                 ys = y
-            elif use_ll:
+            elif use_ll or use_sg:
                 y, ys = torch.empty((1, m), device="cuda"), None      # full-height local result
             else:
                 y, ys = None, torch.empty((1, rows), device="cuda")
@@ -335,10 +345,30 @@ def run_gpu(args):
     n_groups = len(groups)
     use_stream = world == 1 and not args.no_stream
     batch = pkg.MatmulBatch(Q4_K, [o[0] for o in order], [o[1] for o in order], [o[3] for o in order]) if use_stream else None
+    if use_sg:
+        batch = pkg.MatmulBatchGather(Q4_K, [o[0] for o in order], [o[1] for o in order], [o[2] for o in order],
+                                      [rank * (o[4][0] // world) for o in order])
+        # every rank's gathered vectors == the unsplit result of the same matrix, bit for bit, for EVERY matmul of the step (each
+        # rank knows only its shard: rank r's rows of its own full-height result must equal b200_mul_mat on its shard, and all ranks
+        # must hold the same full vector — compared through an all_gather of checksums)
+        batch.run(ctx); batch.run(ctx); ctx.synchronize()
+        sums = []
+        for (W, x, y, ys, (m, name)) in order:
+            rows = m // world
+            mine = pkg.mul_mat(ctx, Q4_K, W, x)
+            assert torch.equal(y[:, rank * rows:(rank + 1) * rows], mine), f"row-split list: {name} rows of rank {rank} differ from b200_mul_mat on the shard"
+            sums.append(y.view(torch.int32).to(torch.int64).sum())
+        ctx.synchronize()
+        mine = torch.stack(sums)
+        allv = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allv, mine)
+        for r in range(world):
+            assert torch.equal(allv[r], mine), f"row-split list: rank {r} holds different gathered vectors than rank {rank}"
 
     def step():
-        if use_stream:
-            # ONE C-ABI call for the whole list: the persistent job-table GEMV walks all 225 matmuls in one launch
+        if use_stream or use_sg:
+            # ONE C-ABI call for the whole list: the persistent job-table GEMV walks all 225 matmuls in one launch (N > 1: with the
+            # all-gather of every result folded into the same launch)
             batch.run(ctx)
             return
         if use_ll:
@@ -498,7 +528,7 @@ def run_gpu(args):
         peak, peak_src = peaks()
         out = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 dot (dp4a) x fp32 scales; Q4_K weights, Q8_1 activations", "data": "synthetic",
             "config": {"workload": f"{MODEL} Q4_K decode step: {STEP_MATMULS} MUL_MATs at n=1 (" + ", ".join(sorted({f"{m}x{k}" for _, m, k, _ in LLAMA3_8B})) + ")",
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
@@ -509,7 +539,8 @@ def run_gpu(args):
                                   f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
                        "activations": "independent: every matmul reads a fixed resident vector (see dependent_chain for the step wired like the model)",
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
-                                                                          "memory; completion: " + ("LL exchange: {value, epoch} in one 8-byte store per result, a receiver kernel polls the local slot; no barrier, no NCCL call"
+                                                                          "memory; completion: " + ("b200_mul_mat_batch_gather: ONE persistent launch per step, every result travels as an 8-byte {value, epoch} word to every rank, consumers poll while they quantize; no receiver kernel, no barrier, no NCCL call in the data path"
+                                                                          if use_sg else "LL exchange: {value, epoch} in one 8-byte store per result, a receiver kernel polls the local slot; no barrier, no NCCL call"
                                                                           if use_ll else "in-kernel epoch flags after every matmul" if use_flags else "symmetric-memory barrier after wv / wo / ffn_up / ffn_down / output (129 per step)")},
             "tok_per_s_matmul_only": round(1e3 / ms_step, 2),
             "gpu_launches": int(launches_per_step * args.steps),
@@ -893,7 +924,8 @@ def main():
     ap.add_argument("--shapes", action="store_true", help="also report per-shape GB/s")
     ap.add_argument("--cpu-seconds", type=float, default=16.0, help="CPU baseline sample budget; <= 0 skips it")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
-    ap.add_argument("--gather-sync", default="ll", choices=["ll", "barrier", "flags"], help="N > 1: how a matmul's gather is completed")
+    ap.add_argument("--gather-sync", default="stream", choices=["stream", "ll", "barrier", "flags"],
+                    help="N > 1: stream = one persistent launch per step with the all-gather folded in (default); ll / barrier / flags = the round-1 per-matmul forms")
     ap.add_argument("--no-stream", action="store_true", help="N = 1: one launch per activation group (round-1 path) instead of b200_mul_mat_batch")
     ap.add_argument("--no-fuse", action="store_true", help="one b200_mul_mat per matrix instead of b200_mul_mat_multi for q/k/v and gate/up")
     ap.add_argument("--no-prefill", action="store_true", help="skip the n=512 tcgen05 prefill section")

@@ -221,6 +221,20 @@ B200_API int  b200_gather_ll_init(b200_ctx * ctx, int rank, int world, void * co
 B200_API int  b200_mul_mat_gather_ll(b200_ctx * ctx, int n_mats, const b200_tensor * const * a_shard, const b200_tensor * b,
                                      const b200_tensor * const * d_full, const int64_t * row0);
 
+/* The row split of a whole LIST of matmuls, one process per GPU (decode): the persistent job-table kernel of b200_mul_mat_batch with
+ * the all-gather folded into it.  Every rank passes its row shards a[j] = rows [row0[j], row0[j] + a[j]->ne[1]) and gets the
+ * FULL-height results d_full[j].  Inside the one launch every result travels as one 8-byte {value, epoch} word into the exchange
+ * buffer of every rank (NVLink peer stores, one lane per destination rank); a later job of the list whose src1 IS an earlier job's
+ * full-height output polls those words while it quantizes its activations — there is no receiver kernel, no barrier, no NCCL call
+ * and no kernel boundary between dependent matmuls.  The plain d_full vectors are written at the end of the launch.
+ * b200_stream_comm_init: bufs[p] = rank p's exchange buffer, peer-mapped (CUDA IPC / symmetric memory), zero-initialised,
+ *   2 * slot_entries * 8 bytes (two slots alternate between launches; a rank can be at most one launch ahead of the slowest).
+ * All ranks issue the same sequence of b200_mul_mat_batch_gather calls.  (The reference orders the same exchange with per-matmul
+ * peer copies and cross-device events, ggml/src/ggml-cuda/ggml-cuda.cu:2030-2119.) */
+B200_API int  b200_stream_comm_init(b200_ctx * ctx, int rank, int world, void * const * bufs, int64_t slot_entries);
+B200_API int  b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a_shard, const b200_tensor * const * b,
+                                        const b200_tensor * const * d_full, const int64_t * row0);
+
 /* ---- raw device memory (used by the backend shell's buffers and by ctypes callers without torch) -- */
 B200_API int  b200_malloc(int device, size_t nbytes, void ** out);
 B200_API int  b200_free(int device, void * ptr);

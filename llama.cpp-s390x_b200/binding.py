@@ -18,7 +18,7 @@ EXPORTS = [
     "b200_ctx_launch_count", "b200_ctx_set_option", "b200_quantize_row_q8_1", "b200_mul_mat", "b200_mul_mat_supported",
     "b200_mul_mat_noalloc",
     "b200_mul_mat_id", "b200_mul_mat_id_supported", "b200_mm_ids", "b200_weights_upload", "b200_weights_free",
-    "b200_mul_mat_host", "b200_mul_mat_host_batch", "b200_mul_mat_gather", "b200_gather_sync_init", "b200_mul_mat_multi", "b200_mul_mat_batch", "b200_gather_ll_init", "b200_mul_mat_gather_ll", "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
+    "b200_mul_mat_host", "b200_mul_mat_host_batch", "b200_mul_mat_gather", "b200_gather_sync_init", "b200_mul_mat_multi", "b200_mul_mat_batch", "b200_stream_comm_init", "b200_mul_mat_batch_gather", "b200_gather_ll_init", "b200_mul_mat_gather_ll", "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
     "b200_memset", "b200_memcpy_async", "b200_host_malloc", "b200_host_free", "b200_event_create", "b200_event_destroy",
     "b200_event_record", "b200_event_wait", "b200_event_synchronize", "b200_rowsplit_create", "b200_rowsplit_destroy", "b200_rowsplit_n_dev",
     "b200_rowsplit_rows", "b200_rowsplit_upload", "b200_rowsplit_weights_free", "b200_rowsplit_mul_mat", "b200_rowsplit_mul_mat_main",
@@ -85,6 +85,8 @@ def lib() -> C.CDLL:
     sig("b200_gather_sync_init", i32, [vp, i32, i32, C.POINTER(vp)])
     sig("b200_mul_mat_multi", i32, [vp, i32, C.POINTER(T), T, C.POINTER(T)])
     sig("b200_mul_mat_batch", i32, [vp, i32, C.POINTER(T), C.POINTER(T), C.POINTER(T)])
+    sig("b200_stream_comm_init", i32, [vp, i32, i32, C.POINTER(vp), i64])
+    sig("b200_mul_mat_batch_gather", i32, [vp, i32, C.POINTER(T), C.POINTER(T), C.POINTER(T), C.POINTER(i64)])
     sig("b200_gather_ll_init", i32, [vp, i32, i32, C.POINTER(vp), i64])
     sig("b200_mul_mat_gather_ll", i32, [vp, i32, C.POINTER(T), T, C.POINTER(T), C.POINTER(i64)])
     sig("b200_malloc", i32, [i32, sz, C.POINTER(vp)]); sig("b200_free", i32, [i32, vp])

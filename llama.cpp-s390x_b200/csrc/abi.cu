@@ -134,6 +134,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->stream_min_jobs = env_int("GGML_B200_STREAM_MIN_JOBS", 2);
     ctx->stream_stages = env_int("GGML_B200_STREAM_STAGES", 0);
     ctx->stream_ll     = env_int("GGML_B200_STREAM_LL", 1);
+    ctx->stream_grid   = env_int("GGML_B200_STREAM_GRID", 0);
     ctx->stream_pair_min = env_int("GGML_B200_STREAM_PAIR_MIN", 0);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
@@ -193,6 +194,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "stream_min_jobs")) slot = &ctx->stream_min_jobs;
     else if (!strcmp(name, "stream_stages")) slot = &ctx->stream_stages;
     else if (!strcmp(name, "stream_ll"))     slot = &ctx->stream_ll;
+    else if (!strcmp(name, "stream_grid"))   slot = &ctx->stream_grid;
     else if (!strcmp(name, "stream_trace"))  slot = &ctx->stream_trace;
     else if (!strcmp(name, "stream_pair_min")) slot = &ctx->stream_pair_min;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
@@ -767,7 +769,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
     static thread_local sq_params P;                        // ~26 KB: not on the stack of every caller
     memset(&P, 0, offsetof(sq_params, jobs));
     P.n_jobs = n; P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
-    const uint32_t G = (uint32_t) ctx->sm_count;
+    const uint32_t G = (uint32_t) b200_gemv_stream_grid(ctx);
     std::vector<const char *> xlo((size_t) n), xhi((size_t) n), ylo((size_t) n), yhi((size_t) n);
     std::vector<int> xsrc((size_t) n, -1);                  // job whose exchange entries job j reads instead of X
     int group = -1, group_first = 0, group_size = 0;
@@ -855,6 +857,97 @@ extern "C" __attribute__((visibility("default"))) int b200_dbg_stream_trace(b200
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     B200_CUDA_TRY(cudaMemcpy(out, ctx->sq_trace, (size_t) n_words * 8, cudaMemcpyDeviceToHost));
+    return B200_OK;
+}
+
+// ---- row split of a whole list, one process per GPU ---------------------------------------------------------------------------
+extern "C" int b200_stream_comm_init(b200_ctx * ctx, int rank, int world, void * const * bufs, int64_t slot_entries) {
+    if (!ctx || world < 0 || world > B200_MAX_PEERS || (world > 0 && (!bufs || rank < 0 || rank >= world || slot_entries < 4 || slot_entries % 4 != 0))) {
+        b200_set_error("stream_comm_init: bad argument (slot_entries must be a positive multiple of 4)"); return B200_E_ARG;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->sq_world = world; ctx->sq_rank = rank; ctx->sq_peer_cap = (size_t) slot_entries;
+    for (int p = 0; p < world; ++p) {
+        if (!bufs[p] || ((uintptr_t) bufs[p] & 15)) { b200_set_error("stream_comm_init: buffers must be 16-byte aligned"); ctx->sq_world = 0; return B200_E_ARG; }
+        ctx->sq_peer[p] = (unsigned long long *) bufs[p];
+    }
+    if (!ctx->sq_done) {
+        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_done, (SQ_MAX_JOBS + 2) * sizeof(uint32_t)));
+    }
+    // all ranks start counting their launches from zero together
+    B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_done, 0, (SQ_MAX_JOBS + 2) * sizeof(uint32_t), ctx->stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
+                                         const b200_tensor * const * d_full, const int64_t * row0) {
+    if (!ctx || n_jobs < 0 || (n_jobs > 0 && (!a || !b || !d_full || !row0))) { b200_set_error("mul_mat_batch_gather: bad argument"); return B200_E_ARG; }
+    if (ctx->sq_world < 2) { b200_set_error("mul_mat_batch_gather: b200_stream_comm_init was not called (world >= 2)"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const uint32_t G = (uint32_t) b200_gemv_stream_grid(ctx);
+    static thread_local sq_params P;
+    for (int j0 = 0; j0 < n_jobs; ) {
+        // one launch: up to SQ_MAX_JOBS jobs whose exchange entries fit a slot
+        memset(&P, 0, offsetof(sq_params, jobs));
+        P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
+        P.world = ctx->sq_world; P.rank = ctx->sq_rank; P.ll_cap = ctx->sq_peer_cap;
+        for (int p = 0; p < ctx->sq_world; ++p) P.ll_peer[p] = ctx->sq_peer[p];
+        P.ll = ctx->sq_peer[ctx->sq_rank];
+        size_t entries = 0;
+        int n = 0, group = -1, group_first = 0, group_size = 0;
+        std::vector<int> xsrc;
+        for (int j = j0; j < n_jobs && n < SQ_MAX_JOBS; ++j, ++n) {
+            const b200_tensor * A = a[j], * B = b[j], * D = d_full[j];
+            if (!A || !B || !D || A->type != B200_TYPE_Q4_K || A->ne[0] % 256 != 0 || A->ne[0] / 256 > 65535 || A->ne[2] * A->ne[3] != 1 || A->ne[1] < 0 ||
+                (A->ne[1] > 0 && !aligned16(A->data, A->nb[1], 0, 0)) || A->nb[1] >= ((int64_t) 1 << 32) || A->nb[0] != SZ_Q4_K ||
+                B->type != B200_TYPE_F32 || B->ne[0] != A->ne[0] || B->ne[1] * B->ne[2] * B->ne[3] != 1 || B->nb[0] != 4 || !aligned16(B->data, 0, 0, 0) ||
+                D->type != B200_TYPE_F32 || D->nb[0] != 4 || D->ne[1] * D->ne[2] * D->ne[3] != 1 || row0[j] < 0 || row0[j] + A->ne[1] > D->ne[0] ||
+                D->ne[0] >= ((int64_t) 1 << 31) || b200_gemv_stream_stages(ctx, A->ne[0]) < 2) {
+                b200_set_error("mul_mat_batch_gather[%d]: Q4_K row shards (16-byte aligned rows, k %% 256 == 0) x one f32 column -> one full-height f32 column", j);
+                return B200_E_UNSUPPORTED;
+            }
+            const size_t need = ((size_t) D->ne[0] + 3) & ~(size_t) 3;
+            if (entries + need > ctx->sq_peer_cap) {
+                if (n == 0) { b200_set_error("mul_mat_batch_gather[%d]: %lld results exceed the exchange slot (%zu entries)", j, (long long) D->ne[0], ctx->sq_peer_cap); return B200_E_ARG; }
+                break;
+            }
+            const int64_t kmax2 = A->ne[0] > P.kmax ? A->ne[0] : P.kmax;
+            if (b200_gemv_stream_stages(ctx, kmax2) < 2) break;
+            sq_job & J = P.jobs[n];
+            const uint32_t m = (uint32_t) A->ne[1];
+            J.W = (const uint8_t *) A->data; J.X = (const float *) B->data; J.Y = (float *) D->data;
+            J.nb01 = (uint32_t) A->nb[1]; J.base = m / G; J.rem = (uint16_t) (m % G); J.nsb = (uint16_t) (A->ne[0] / 256);
+            J.row0 = (uint32_t) row0[j]; J.m_full = (uint32_t) D->ne[0];
+            J.dep = -1; J.xsrc = -1; J.flags = 0; J.ll_off = (uint32_t) entries;
+            entries += need;
+            P.kmax = (int) kmax2;
+            // X is exactly the full-height output of an earlier job of this launch: polled in the exchange buffer.  Any other overlap
+            // between X and an earlier output cannot be ordered across ranks inside the launch: the list is cut there.
+            const char * xlo = (const char *) J.X, * xhi = xlo + 4 * A->ne[0];
+            int src = -1; bool cut = false;
+            for (int i = n - 1; i >= 0; --i) {
+                const char * ylo = (const char *) P.jobs[i].Y, * yhi = ylo + 4 * (size_t) P.jobs[i].m_full;
+                if (xlo < yhi && ylo < xhi) { if (ylo == xlo && yhi == xhi) src = i; else cut = true; break; }
+            }
+            if (cut) { if (n == 0) { b200_set_error("mul_mat_batch_gather[%d]: src1 overlaps dst", j); return B200_E_ARG; } entries -= need; break; }
+            {
+                const char * ylo = (const char *) J.Y, * yhi = ylo + 4 * (size_t) J.m_full;
+                if (xlo < yhi && ylo < xhi) { b200_set_error("mul_mat_batch_gather[%d]: dst overlaps src1", j); return B200_E_ARG; }
+            }
+            xsrc.push_back(src);
+            const bool join = n > 0 && J.X == P.jobs[n - 1].X && J.nsb == P.jobs[n - 1].nsb && group_size < SQ_MAX_GROUP && src == xsrc[group_first];
+            if (join) group_size++;
+            else { group++; group_first = n; group_size = 1; J.xsrc = (int16_t) src; P.gfirst[group] = (uint16_t) n; }
+            J.xg = (uint16_t) group;
+        }
+        P.n_jobs = n; P.n_groups = group + 1; P.n_ll = n;
+        ctx->n_pend = 0;
+        const int rc = b200_launch_gemv_stream(ctx, P);
+        if (rc) return rc;
+        j0 += n;
+    }
     return B200_OK;
 }
 

@@ -113,11 +113,16 @@ struct b200_ctx {
     int          use_stream;      // 1: runs of Q4_K n = 1 matmuls of a batch go through one persistent launch
     int          stream_min_jobs; // shortest run that takes the persistent kernel
     int          stream_stages;   // ring slots per warp override (0 = auto)
+    int          stream_grid;     // CTAs of the persistent kernel (0 = one per SM); smaller grids let several launches be co-resident
     int          stream_ll;       // 1: "X is exactly an earlier job's output" travels as {value, epoch} words (0: completion counters only)
     uint32_t *   sq_done;         // device: [SQ_MAX_JOBS + 2] completion counters, ticket, launch epoch
     unsigned long long * sq_ll;   // device: exchange buffer of the in-launch dependencies (8-byte {epoch, value} entries)
     size_t       sq_ll_cap;       // ... its capacity in entries
     int          stream_pair_min; // rows of a job per CTA up to which they are walked one by one instead of in pairs
+    // row split of the persistent kernel, one process per GPU (b200_stream_comm_init)
+    int          sq_world, sq_rank;
+    unsigned long long * sq_peer[8];  // every rank's exchange buffer (peer-mapped), 2 * sq_peer_cap entries
+    size_t       sq_peer_cap;
     int          stream_trace;    // debugging: 1 = record coordinator time stamps (b200_dbg_stream_trace reads them)
     unsigned long long * sq_trace;
 };

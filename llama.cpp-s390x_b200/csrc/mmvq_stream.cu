@@ -20,6 +20,8 @@
 #include "quantize.cuh"
 #include "tc_ptx.cuh"
 
+#include <mutex>
+
 namespace {
 
 #ifndef SQ_NCW_CFG
@@ -127,8 +129,9 @@ __device__ __forceinline__ float4 sq_load_x4(const float * x, const unsigned lon
     unsigned long long w0, w1, w2, w3;
     const long long t0 = clock64();
     while (true) {
-        asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(p + 2) : "memory");
+        // (system scope: with a row split the words are written by other GPUs through NVLink)
+        asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+        asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(p + 2) : "memory");
         if ((uint32_t) (w0 >> 32) == epoch && (uint32_t) (w1 >> 32) == epoch && (uint32_t) (w2 >> 32) == epoch && (uint32_t) (w3 >> 32) == epoch) break;
         __nanosleep(100);
         if (clock64() - t0 > 8000000000LL) __trap();          // a producer that never delivers must not hang the box
@@ -164,7 +167,8 @@ __device__ __forceinline__ void sq_claim_units(const sq_params & P, const int g,
                                                const uint32_t epoch) {
     const int b = g & 1;
     const sq_job & J = P.jobs[P.gfirst[g]];
-    const unsigned long long * ll = J.xsrc >= 0 ? P.ll + P.jobs[J.xsrc].ll_off : nullptr;
+    // (row split: the slot of this launch's epoch parity; entries are indexed by the row of the FULL matrix)
+    const unsigned long long * ll = J.xsrc >= 0 ? P.ll + (P.world > 1 ? (size_t) (epoch & 1u) * P.ll_cap : 0) + P.jobs[J.xsrc].ll_off : nullptr;
     const int nbk = (int) J.nsb * 8;
     const int ub  = sq_unit_blocks(nbk);
     const int nunits = (nbk + ub - 1) / ub;
@@ -245,6 +249,8 @@ __device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, 
     sq_seek(P, cu, warp);
 }
 
+// MULTI: row split over `world` processes (one per GPU), see sq_params::ll_peer
+template <bool MULTI>
 __global__ void __launch_bounds__(SQ_THREADS, 1)
 gemv_q4k_stream(const __grid_constant__ sq_params P) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -386,7 +392,15 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             if (last) {
                 const float sA = warp_sum(accA);
                 const float sB = warp_sum(accB);
-                if (lane == 0) {
+                if (MULTI) {
+                    // lane p delivers to rank p (the butterfly sum left sA / sB in every lane): one NVLink store per rank and row
+                    if (lane < P.world) {
+                        const uint32_t epoch = *s_epoch;
+                        unsigned long long * e = P.ll_peer[lane] + (size_t) (epoch & 1u) * P.ll_cap + J.ll_off + J.row0 + row;
+                        asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sA)) : "memory");
+                        if (two) asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e + 1), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sB)) : "memory");
+                    }
+                } else if (lane == 0) {
                     J.Y[row] = sA;
                     if (two) J.Y[row + 1] = sB;
                     if (J.ll_off != SQ_NO_LL) {
@@ -480,6 +494,29 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             }
         }
     }
+    if (MULTI) {
+        // Row split: the plain full-height result vectors are written from this rank's exchange buffer once the CTA has finished its
+        // own rows — in job order by a fixed thread per entry, so that a vector written by two jobs of the list ends up with the
+        // later one's values; nobody in this launch reads the plain vectors of its own jobs (they are polled in the buffer).
+        __syncthreads();
+        const uint32_t epoch = *s_epoch;
+        const unsigned long long * base = P.ll + (size_t) (epoch & 1u) * P.ll_cap;
+        for (int j = 0; j < P.n_jobs; ++j) {
+            const sq_job & J = P.jobs[j];
+            for (uint32_t i = blockIdx.x * SQ_THREADS + tid; i < J.m_full; i += gridDim.x * SQ_THREADS) {
+                const unsigned long long * p = base + J.ll_off + i;
+                unsigned long long w;
+                const long long t0 = clock64();
+                while (true) {
+                    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+                    if ((uint32_t) (w >> 32) == epoch) break;
+                    __nanosleep(100);
+                    if (clock64() - t0 > 20000000000LL) __trap();     // ~10 s: a rank that never delivers must not hang the others for ever
+                }
+                J.Y[i] = __uint_as_float((uint32_t) w);
+            }
+        }
+    }
     if (P.n_flagged || P.n_ll) {
         // the last CTA to finish leaves the counters at zero for the next launch (nobody polls them any more) and counts the launch
         __syncthreads();
@@ -504,6 +541,10 @@ int b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax) {
     return 0;
 }
 
+int b200_gemv_stream_grid(const b200_ctx * ctx) {
+    return ctx->stream_grid > 0 && ctx->stream_grid < ctx->sm_count ? ctx->stream_grid : ctx->sm_count;
+}
+
 int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
     if (P.n_jobs <= 0) return B200_OK;
     if (P.n_jobs > SQ_MAX_JOBS || P.n_groups < 1 || P.n_groups > P.n_jobs) { b200_set_error("gemv_stream: bad job table"); return B200_E_ARG; }
@@ -512,13 +553,19 @@ int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
         b200_set_error("gemv_stream: k = %d does not fit the shared-memory rings", P.kmax); return B200_E_UNSUPPORTED;
     }
     const size_t smem = sq_smem(P.kmax, P.stages);
-    static bool attr_done[16] = {};            // per device
-    if (!attr_done[ctx->device & 15]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_stream, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
-        attr_done[ctx->device & 15] = true;
+    const bool multi = P.world > 1;
+    auto kern = multi ? gemv_q4k_stream<true> : gemv_q4k_stream<false>;
+    static std::mutex attr_mutex;
+    static bool attr_done[2][64] = {};         // per variant and device
+    {
+        std::lock_guard<std::mutex> lock(attr_mutex);
+        if (!attr_done[multi][ctx->device & 63]) {
+            B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
+            attr_done[multi][ctx->device & 63] = true;
+        }
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) ctx->sm_count);
+    cfg.gridDim          = dim3((unsigned) b200_gemv_stream_grid(ctx));
     cfg.blockDim         = dim3(SQ_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream           = ctx->stream;
@@ -526,8 +573,10 @@ int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
-    cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_q4k_stream, P));
+    // (row split: no early start of the next launch — its CTAs would only sit on SMs that another rank's kernel may need when
+    // several ranks share one GPU in the tests, and a full-size grid leaves no SM free anyway)
+    cfg.numAttrs = ctx->pdl && !multi ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, P));
     ctx->launches++;
     return B200_OK;
 }

@@ -13,12 +13,14 @@
 
 #define SQ_NO_LL 0xffffffffu
 
-struct sq_job {                 // 48 bytes
+struct sq_job {                 // 56 bytes
     const uint8_t * W;          // first row of the [m, k] Q4_K matrix (or row shard), 16-byte aligned
     const float *   X;          // k f32, 16-byte aligned
     float *         Y;          // m f32
     uint32_t nb01;              // row stride in bytes (multiple of 16)
     uint32_t base;              // m / grid: CTA b owns rows [b * base + min(b, rem), ... + base + (b < rem))
+    uint32_t row0;              // row split (world > 1): W holds rows [row0, row0 + m) of a matrix of m_full rows; Y is the FULL-height vector
+    uint32_t m_full;
     uint32_t ll_off;            // SQ_NO_LL, or: every result also goes, as {f32 bits, launch epoch} in one 8-byte word, to entry
                                 // ll_off + row of the exchange buffer — a later group of this launch reads its activations from there
     uint16_t rem;               // m % grid
@@ -43,6 +45,12 @@ struct sq_params {
     unsigned long long * trace; // debugging (ctx option stream_trace): %globaltimer stamps of the coordinator of CTA 0 and of the last CTA,
                                 // [2][SQ_MAX_JOBS][4] = {group start, opened, own units done, all units done}; NULL = off
     unsigned long long * ll;    // exchange buffer (entries of 8 bytes: epoch << 32 | f32 bits), zero-initialised
+    // row split, one process per GPU (b200_mul_mat_batch_gather): every result goes as one {value, epoch} word into the exchange
+    // buffer of EVERY rank (peer-mapped, own rank included), at entry (epoch & 1) * ll_cap + ll_off + row0 + row; the plain Y
+    // vectors are written from the local exchange buffer at the end of the launch
+    int        world, rank;
+    unsigned long long   ll_cap;
+    unsigned long long * ll_peer[8];
     uint16_t   gfirst[SQ_MAX_JOBS];   // first job of activation group g
     sq_job     jobs[SQ_MAX_JOBS];
 };
@@ -51,3 +59,5 @@ struct sq_params {
 int    b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P);
 // ring slots per warp that fit next to two activation buffers of kmax values (0: does not fit)
 int    b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax);
+// CTAs of a launch on this context (the job table's base / rem fields are computed for this grid)
+int    b200_gemv_stream_grid(const b200_ctx * ctx);

@@ -113,6 +113,24 @@ class MatmulBatch:
         return self.keep[2]
 
 
+def stream_comm_init(ctx: Context, rank: int, world: int, buf_ptrs, slot_entries: int):
+    """row split of b200_mul_mat_batch_gather: buf_ptrs[p] = rank p's zeroed, peer-mapped buffer of 2 * slot_entries * 8 bytes"""
+    arr = (C.c_void_p * max(1, len(buf_ptrs)))(*buf_ptrs)
+    check(lib().b200_stream_comm_init(ctx.handle, rank, world, arr, slot_entries), "b200_stream_comm_init")
+
+
+class MatmulBatchGather(MatmulBatch):
+    """b200_mul_mat_batch_gather: ws[i] = this rank's row shard (rows [row0s[i], ...)), outs[i] = the full-height result"""
+
+    def __init__(self, wtype: int, ws, xs, outs, row0s):
+        super().__init__(wtype, ws, xs, outs)
+        self.r0 = (C.c_int64 * self.n)(*row0s)
+
+    def run(self, ctx: Context):
+        check(lib().b200_mul_mat_batch_gather(ctx.handle, self.n, self.ap, self.bp, self.dp, self.r0), "b200_mul_mat_batch_gather")
+        return self.keep[2]
+
+
 def mul_mat_batch(ctx: Context, wtype: int, ws, xs, outs=None):
     """outs[i] = ws[i] x xs[i] for a list of matmuls, in list order, through one C-ABI call"""
     import torch

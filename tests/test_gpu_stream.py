@@ -182,3 +182,62 @@ def test_batch_llama_shapes_sampled_rows_vs_oracle(pkg, gpu_ctx, orc, m, k):
     assert nmse(want, got[:, rows]) <= NMSE_TOL
     assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[0][:, : m // 4])
     assert torch.equal(outs[0], pkg.mul_mat(gpu_ctx, Q4_K, Wd, Xd))
+
+
+@pytest.mark.parametrize("world,slot", [(2, 16384), (4, 16384), (2, 8192)])
+def test_row_split_list_emulated_on_one_gpu(pkg, world, slot):
+    """b200_mul_mat_batch_gather (the persistent kernel with the all-gather folded in) with `world` ranks emulated on ONE GPU:
+    every rank is a context with its own stream, exchange buffer and a reduced grid, so that the world's launches are
+    co-resident and exchange {value, epoch} words with each other exactly as over NVLink.  A dependent chain (q/k/v-style
+    sharing, wo reads q, ...) must give, on every rank, bit for bit what sequential b200_mul_mat calls give on the unsplit
+    matrices — twice in a row (both exchange slots) and a third time (slot reuse).  slot = 8192 entries do not hold the whole
+    list: it is cut into two launches."""
+    import torch
+    rng = np.random.default_rng(21 + world)
+    grid = 148 // world - 2
+    # (name, m, k): wq/wk/wv share x0; wo reads q; gate/up read wo's output; down reads gate's output; head reads down's output
+    dims = [("wq", 1024, 512), ("wk", 256, 512), ("wv", 256, 512), ("wo", 512, 1024), ("gate", 1536, 512), ("up", 1536, 512), ("down", 512, 1536),
+            ("head", 3000, 512)]
+    Ws = {n: q4k(m, k, rng) for n, m, k in dims}
+    x0 = dev((rng.standard_normal((1, 512)) * 30).astype(np.float32))
+    ref_ctx = pkg.Context(0, stream="torch")
+    want = {}
+    want["wq"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["wq"], x0); want["wk"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["wk"], x0); want["wv"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["wv"], x0)
+    want["wo"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["wo"], want["wq"])
+    want["gate"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["gate"], want["wo"]); want["up"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["up"], want["wo"])
+    want["down"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["down"], want["gate"])
+    want["head"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["head"], want["down"])
+    ref_ctx.synchronize()
+
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    ctxs = [pkg.Context(0, stream=s.cuda_stream) for s in streams]
+    bufs = [torch.zeros((2 * slot,), dtype=torch.int64, device="cuda") for _ in range(world)]
+    torch.cuda.synchronize()
+    batches, outs = [], []
+    for r in range(world):
+        ctxs[r].set_option("stream_grid", grid)
+        pkg.stream_comm_init(ctxs[r], r, world, [b.data_ptr() for b in bufs], slot)
+        y = {n: torch.full((1, m), float("nan"), device="cuda") for n, m, k in dims}
+        src = {"wq": x0, "wk": x0, "wv": x0, "wo": y["wq"], "gate": y["wo"], "up": y["wo"], "down": y["gate"], "head": y["down"]}
+        shards, row0s = [], []
+        for n, m, k in dims:
+            lo, rows = pkg.row_shard(m, r, world)
+            shards.append(Ws[n][lo:lo + rows].contiguous() if rows > 0 else Ws[n][0:0])
+            row0s.append(lo)
+        batches.append(pkg.MatmulBatchGather(Q4_K, shards, [src[n] for n, _, _ in dims], [y[n] for n, _, _ in dims], row0s))
+        outs.append(y)
+    for rep in range(3):
+        for r in range(world):
+            for t in outs[r].values():
+                t.fill_(float("nan"))
+        torch.cuda.synchronize()
+        for r in range(world):
+            batches[r].run(ctxs[r])
+        for r in range(world):
+            ctxs[r].synchronize()
+        for r in range(world):
+            for n, _, _ in dims:
+                assert torch.equal(outs[r][n], want[n]), (rep, r, n)
+    for c in ctxs:
+        c.close()
+    ref_ctx.close()
