@@ -352,13 +352,17 @@ def run_gpu(args):
         # rank knows only its shard: rank r's rows of its own full-height result must equal b200_mul_mat on its shard, and all ranks
         # must hold the same full vector — compared through an all_gather of checksums)
         batch.run(ctx); batch.run(ctx); ctx.synchronize()
-        sums = []
-        for (W, x, y, ys, (m, name)) in order:
+        sums, bad = [], []
+        for i, (W, x, y, ys, (m, name)) in enumerate(order):
             rows = m // world
             mine = pkg.mul_mat(ctx, Q4_K, W, x)
-            assert torch.equal(y[:, rank * rows:(rank + 1) * rows], mine), f"row-split list: {name} rows of rank {rank} differ from b200_mul_mat on the shard"
+            ctx.synchronize()
+            got = y[:, rank * rows:(rank + 1) * rows]
+            if not torch.equal(got, mine):
+                idx = (got != mine).nonzero()
+                bad.append((i, name, int(idx.shape[0]), int(torch.isnan(got).sum()), idx[:4, 1].tolist(), got[0, idx[:2, 1]].tolist(), mine[0, idx[:2, 1]].tolist()))
             sums.append(y.view(torch.int32).to(torch.int64).sum())
-        ctx.synchronize()
+        assert not bad, f"row-split list: rows of rank {rank} differ from b200_mul_mat on the shard: {bad[:6]} ({len(bad)} matmuls)"
         mine = torch.stack(sums)
         allv = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(allv, mine)
@@ -535,7 +539,7 @@ def run_gpu(args):
                        "l2": f"inputs larger than L2: {sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9:.2f} GB of distinct weights per step vs 126 MB L2, no flush needed",
                        "launch": ("CUDA graph replay" if graph is not None else "eager launches through the C ABI") +
                                  (f"; one b200_mul_mat_batch call = {launches_per_step} persistent job-table launch(es) for {STEP_MATMULS} matmuls "
-                                  f"({n_groups} activation groups)" if use_stream else
+                                  f"({n_groups} activation groups)" if use_stream or use_sg else
                                   f"; wq/wk/wv and ffn_gate/ffn_up fused by b200_mul_mat_multi ({n_groups} launches for {STEP_MATMULS} matmuls)" if fuse else ""),
                        "activations": "independent: every matmul reads a fixed resident vector (see dependent_chain for the step wired like the model)",
                        "parallelism": "1 GPU" if world == 1 else f"row-split x{world}: all-gather fused into the GEMV stores over NVLink peer "
@@ -547,7 +551,7 @@ def run_gpu(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(value / world, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(value / world / peak, 4), "traffic": measured_traffic(launches_per_step, world), "peak_source": peak_src,
-                         "kernel": (f"gemv_q4k_stream (persistent job table: {launches_per_step} launch(es) per step, {STEP_MATMULS} matmuls)" if use_stream
+                         "kernel": (f"gemv_q4k_stream (persistent job table: {launches_per_step} launch(es) per step, {STEP_MATMULS} matmuls)" if use_stream or use_sg
                                     else f"gemv_q4k<1,32> (all {launches_per_step} launches of the step, {STEP_MATMULS} matmuls)"),
                          "algorithmic_bytes_per_launch_avg": round(STEP_BYTES / launches_per_step / world)},
         }
