@@ -151,6 +151,8 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->ll_state) cudaFree(ctx->ll_state);
     if (ctx->sq_done) cudaFree(ctx->sq_done);
     if (ctx->sq_ll) cudaFree(ctx->sq_ll);
+    if (ctx->sq_img) cudaFree(ctx->sq_img);
+    if (ctx->sq_xflag) cudaFree(ctx->sq_xflag);
     if (ctx->sq_trace) cudaFree(ctx->sq_trace);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
@@ -761,6 +763,29 @@ static bool stream_job_ok(const b200_ctx * ctx, const b200_tensor * a, const b20
            b200_gemv_stream_stages(ctx, a->ne[0]) >= 2;
 }
 
+// image offsets of the launch's activation groups + the buffers behind them (grow-only: like the other scratch, a list needs one
+// un-captured call before it is captured into a CUDA graph)
+static int stream_images(b200_ctx * ctx, sq_params & P) {
+    size_t total = 0;
+    for (int g = 0; g < P.n_groups; ++g) {
+        P.gimg[g] = (uint32_t) total;
+        total += ((size_t) P.jobs[P.gfirst[g]].nsb * 320 + 127) & ~(size_t) 127;       // k int8 + k / 32 float2 = 320 B per super-block
+    }
+    if (total > ctx->sq_img_cap) {
+        B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        if (ctx->sq_img) { cudaFree(ctx->sq_img); ctx->sq_img = nullptr; ctx->sq_img_cap = 0; }
+        const size_t want = total < ((size_t) 4 << 20) ? ((size_t) 4 << 20) : total;
+        if (cudaMalloc((void **) &ctx->sq_img, want) != cudaSuccess) { cudaGetLastError(); b200_set_error("mul_mat_batch: activation image allocation failed"); return B200_E_ALLOC; }
+        ctx->sq_img_cap = want;
+    }
+    if (!ctx->sq_xflag) {
+        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_xflag, (size_t) SQ_MAX_JOBS * 64 * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_xflag, 0, (size_t) SQ_MAX_JOBS * 64 * sizeof(uint32_t), ctx->stream));
+    }
+    P.ximg = ctx->sq_img; P.xflag = ctx->sq_xflag;
+    return B200_OK;
+}
+
 static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, const b200_tensor * const * b, const b200_tensor * const * d) {
     if (!ctx->sq_done) {
         B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_done, (SQ_MAX_JOBS + 2) * sizeof(uint32_t)));
@@ -842,6 +867,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
         ctx->sq_ll_cap = want;
     }
     P.ll = ctx->sq_ll;
+    if (const int rc = stream_images(ctx, P)) return rc;
     if (ctx->stream_trace) {
         if (!ctx->sq_trace) B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_trace, (2 * SQ_MAX_JOBS * 4 + 128 * 32 * 5) * sizeof(unsigned long long)));
         P.trace = ctx->sq_trace;
@@ -943,6 +969,7 @@ extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_
             J.xg = (uint16_t) group;
         }
         P.n_jobs = n; P.n_groups = group + 1; P.n_ll = n;
+        if (const int rc = stream_images(ctx, P)) return rc;
         ctx->n_pend = 0;
         const int rc = b200_launch_gemv_stream(ctx, P);
         if (rc) return rc;

@@ -118,6 +118,9 @@ struct b200_ctx {
     uint32_t *   sq_done;         // device: [SQ_MAX_JOBS + 2] completion counters, ticket, launch epoch
     unsigned long long * sq_ll;   // device: exchange buffer of the in-launch dependencies (8-byte {epoch, value} entries)
     size_t       sq_ll_cap;       // ... its capacity in entries
+    uint8_t *    sq_img;          // device: quantized-activation images of a launch's groups
+    size_t       sq_img_cap;
+    uint32_t *   sq_xflag;        // device: [SQ_MAX_JOBS][64] unit flags
     int          stream_pair_min; // rows of a job per CTA up to which they are walked one by one instead of in pairs
     // row split of the persistent kernel, one process per GPU (b200_stream_comm_init)
     int          sq_world, sq_rank;

@@ -40,10 +40,8 @@ constexpr int SQ_NCNT     = 256;                       // CTA-level row counters
 constexpr int OFF_FULL  = 0;                                         // [SQ_NCW][SQ_MAX_S] u64
 constexpr int OFF_XFULL = OFF_FULL + SQ_NCW * SQ_MAX_S * 8;          // [2] u64
 constexpr int OFF_XEMPTY = OFF_XFULL + 16;                           // [2] u64
-constexpr int OFF_XOPEN = OFF_XEMPTY + 16;                           // [2] u64
-constexpr int OFF_CLAIM = OFF_XOPEN + 16;                            // [2] u32 unit counters, [2] = this launch's epoch
-constexpr int OFF_PROG  = OFF_CLAIM + 16;                            // [32] u32: jobs passed by consumer warp w (see pass_jobs)
-constexpr int OFF_META  = OFF_PROG + 128;                            // [SQ_NCW][SQ_MAX_S] uint2
+constexpr int OFF_EPOCH = OFF_XEMPTY + 16;                           // u32: this launch's epoch (+ pad)
+constexpr int OFF_META  = OFF_EPOCH + 16;                            // [SQ_NCW][SQ_MAX_S] uint2
 constexpr int OFF_CNT   = OFF_META + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NCNT] u32
 constexpr int OFF_X     = (OFF_CNT + SQ_NCNT * 4 + 127) / 128 * 128;
 
@@ -109,17 +107,13 @@ __device__ __forceinline__ float q4k_dot(const uint4 hdr, const uint4 q0, const 
     return r;
 }
 
-// Quantization of a group's activations is split into units of 16 blocks (512 values) that ANY warp of the CTA may claim: the
-// four quantizer warps work ahead of the consumers; a consumer warp that arrives at a group whose activations are not ready
-// yet (a dependent chain: everybody waits for the same vector) takes units too instead of idling.
-// Units are small — 4 blocks (one 32-value block per 8 lanes) for vectors up to 4096 values, 8 blocks beyond — because a unit is
-// one long dependency chain (load, 3 + 3 shuffles, two IEEE divisions, 4 roundings): with 16-block units a 4096-vector took 2 us
-// however many warps were idle (traced), with 4-block units all 32 warps of the CTA run one chain each.
-__device__ __forceinline__ int sq_unit_blocks(const int nbk) { return nbk <= 128 ? 4 : 8; }
-
-__device__ __forceinline__ void mbar_complete_tx(uint32_t bar, uint32_t n) {
-    asm volatile("mbarrier.complete_tx.relaxed.cta.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(n) : "memory");
-}
+// Activation quantization is done ONCE per group for the whole GPU, not once per CTA: the vector is cut into units (4 .. 32
+// blocks of 32 values, at most 64 units), unit u of group g is quantized by a quantizer warp of CTA (37 g + u) mod grid into an
+// IMAGE of the shared-memory layout in global memory (L2-resident: 5-18 KB) and announced by a flag word carrying the launch
+// epoch; every CTA's coordinator warp waits for the group's flags and pulls the image into its activation buffer with two bulk
+// async copies.  (Quantizing in every CTA — 148 times the same work — cost 20 % of the instruction issue of a Llama-3-8B step on
+// one GPU and did not shrink with the row split: 0.53 ms per step at 8 GPUs against 0.08 ms of HBM time.)
+__host__ __device__ __forceinline__ int sq_unit_blocks(const int nbk) { return nbk <= 256 ? 4 : nbk <= 512 ? 8 : nbk <= 1024 ? 16 : 32; }
 
 // four consecutive activations: from the tensor, or from the exchange entries of the job that produces them — polled until every
 // word carries this launch's epoch (the arrival of the word IS the arrival of the value: one 8-byte access, no flag, no fence)
@@ -133,59 +127,36 @@ __device__ __forceinline__ float4 sq_load_x4(const float * x, const unsigned lon
         asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
         asm volatile("ld.relaxed.sys.global.v2.b64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(p + 2) : "memory");
         if ((uint32_t) (w0 >> 32) == epoch && (uint32_t) (w1 >> 32) == epoch && (uint32_t) (w2 >> 32) == epoch && (uint32_t) (w3 >> 32) == epoch) break;
-        __nanosleep(100);
-        if (clock64() - t0 > 8000000000LL) __trap();          // a producer that never delivers must not hang the box
+        __nanosleep(50);
+        if (clock64() - t0 > 20000000000LL) __trap();         // ~10 s: a producer that never delivers must not hang the box for ever
     }
     return make_float4(__uint_as_float((uint32_t) w0), __uint_as_float((uint32_t) w1), __uint_as_float((uint32_t) w2), __uint_as_float((uint32_t) w3));
 }
 
-// whole warp: quantize blocks [4 NR unit, 4 NR (unit + 1)) of x (nbk blocks) into the swizzled buffer (bit-exact Q8_1 values)
-template <int NR>
-__device__ __forceinline__ void sq_quantize_unit(const float * x, const unsigned long long * ll, const uint32_t epoch, const int nbk, const int unit,
-                                                 uint8_t * s_qs, float2 * s_ds, const int lane) {
+// whole warp: quantize blocks [ub unit, ub (unit + 1)) of x (nbk blocks) into the image (bit-exact Q8_1 values, swizzled like the
+// shared-memory buffer: int8 plane of k bytes, then the float2 (d, d * sum) plane)
+__device__ __forceinline__ void sq_produce_unit(const float * x, const unsigned long long * ll, const uint32_t epoch, const int nbk, const int ub,
+                                                const int unit, uint8_t * img, const int lane) {
     const int sub = lane & 7;
-    float4 v[NR];
+    float2 * img_ds = reinterpret_cast<float2 *>(img + (size_t) nbk * 32);
+    for (int r0 = 0; r0 < ub; r0 += 8) {
+        float4 v[2];
 #pragma unroll
-    for (int u = 0; u < NR; ++u) {
-        const int ib = unit * (4 * NR) + u * 4 + (lane >> 3);
-        v[u] = sq_load_x4(x, ll, epoch, (ib < nbk ? ib : nbk - 1) * 32 + sub * 4);
-    }
-#pragma unroll
-    for (int u = 0; u < NR; ++u) {
-        const int ib = unit * (4 * NR) + u * 4 + (lane >> 3);
-        const q8_part qp = quantize_q8_1_part(v[u]);
-        if (ib < nbk) {
-            const int t = ib * 2 + (sub >> 2);
-            *reinterpret_cast<uint32_t *>(s_qs + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
-            if (sub == 0) s_ds[ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+        for (int u = 0; u < 2; ++u) {
+            const int ib = unit * ub + r0 + u * 4 + (lane >> 3);
+            // (blocks past the unit or the vector: re-read the unit's first block instead of somebody else's, the result is dropped)
+            v[u] = sq_load_x4(x, ll, epoch, (ib < nbk && r0 + u * 4 < ub ? ib : unit * ub) * 32 + sub * 4);
         }
-    }
-}
-
-// whole warp: take units of group g until none is left (the group must be open: xopen waited for)
-__device__ __forceinline__ void sq_claim_units(const sq_params & P, const int g, uint8_t * smem, const uint32_t sbase, const int xbytes, const int lane,
-                                               const uint32_t epoch) {
-    const int b = g & 1;
-    const sq_job & J = P.jobs[P.gfirst[g]];
-    // (row split: the slot of this launch's epoch parity; entries are indexed by the row of the FULL matrix)
-    const unsigned long long * ll = J.xsrc >= 0 ? P.ll + (P.world > 1 ? (size_t) (epoch & 1u) * P.ll_cap : 0) + P.jobs[J.xsrc].ll_off : nullptr;
-    const int nbk = (int) J.nsb * 8;
-    const int ub  = sq_unit_blocks(nbk);
-    const int nunits = (nbk + ub - 1) / ub;
-    uint32_t * claim = reinterpret_cast<uint32_t *>(smem + OFF_CLAIM) + b;
-    uint8_t * s_qs = smem + OFF_X + (size_t) b * xbytes;
-    float2 *  s_ds = reinterpret_cast<float2 *>(s_qs + P.kmax);
-    while (true) {
-        uint32_t u = 0;
-        if (lane == 0) u = atomicAdd(claim, 1u);
-        u = __shfl_sync(0xffffffffu, u, 0);
-        if ((int) u >= nunits) break;
-        if (ub == 4) sq_quantize_unit<1>(J.X, ll, epoch, nbk, (int) u, s_qs, s_ds, lane);
-        else         sq_quantize_unit<2>(J.X, ll, epoch, nbk, (int) u, s_qs, s_ds, lane);
-        __syncwarp();
-        if (lane == 0) {
-            __threadfence_block();                            // the unit's values before its completion count
-            mbar_complete_tx(sbase + OFF_XFULL + 8 * b, 1);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int  ib = unit * ub + r0 + u * 4 + (lane >> 3);
+            const bool ok = ib < nbk && r0 + u * 4 < ub;
+            const q8_part qp = quantize_q8_1_part(v[u]);
+            if (ok) {
+                const int t = ib * 2 + (sub >> 2);
+                *reinterpret_cast<uint32_t *>(img + 16 * act_slot(t) + 4 * (sub & 3)) = qp.packed;
+                if (sub == 0) img_ds[ib] = make_float2(qp.d, __fmul_rn((float) qp.sum, qp.d));
+            }
         }
     }
 }
@@ -193,12 +164,9 @@ __device__ __forceinline__ void sq_claim_units(const sq_params & P, const int g,
 // this launch's epoch: launches that use the exchange buffer are counted in done[SQ_MAX_JOBS + 1] (advanced by the last CTA to
 // finish; read after griddepcontrol.wait, i.e. after the previous launch has completed)
 __device__ __forceinline__ uint32_t sq_epoch(const sq_params & P) {
-    uint32_t e = 0;
-    if (P.n_ll) {
-        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(P.done + SQ_MAX_JOBS + 1) : "memory");
-        e += 1;
-    }
-    return e;
+    uint32_t e;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(P.done + SQ_MAX_JOBS + 1) : "memory");
+    return e + 1;
 }
 
 // the sequence of (job, row pair, chunk) steps of one consumer warp.  Rows are walked in PAIRS (the activations are fetched once
@@ -262,16 +230,13 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
     if (tid == 0) {
         for (int i = 0; i < SQ_NCW * SQ_MAX_S; ++i) tc::mbar_init(sbase + OFF_FULL + 8 * i, 1);
         for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(sbase + OFF_XFULL + 8 * i, 1);          // one arrival (the coordinator's expect_tx) + one tx per unit
+            tc::mbar_init(sbase + OFF_XFULL + 8 * i, 1);          // the coordinator's expect_tx + the bytes of the image copies
             tc::mbar_init(sbase + OFF_XEMPTY + 8 * i, SQ_NCW);
-            tc::mbar_init(sbase + OFF_XOPEN + 8 * i, 1);
         }
         tc::mbar_fence_init();
     }
     if (tid < SQ_NCNT) reinterpret_cast<uint32_t *>(smem + OFF_CNT)[tid] = 0;
-    if (tid < 32) reinterpret_cast<uint32_t *>(smem + OFF_PROG)[tid] = 0;
-    volatile uint32_t * s_epoch = reinterpret_cast<volatile uint32_t *>(smem + OFF_CLAIM) + 2;
-    volatile uint32_t * s_prog  = reinterpret_cast<volatile uint32_t *>(smem + OFF_PROG);
+    volatile uint32_t * s_epoch = reinterpret_cast<volatile uint32_t *>(smem + OFF_EPOCH);
     __syncthreads();
 
     if (warp < SQ_NCW) {
@@ -328,17 +293,12 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     if (lane == 0) tc::mbar_arrive(sbase + OFF_XEMPTY + 8 * (cur_g & 1));
                 }
                 cur_g++;
-                if (cur_g < P.n_groups) {
-                    const uint32_t par = (uint32_t) (cur_g >> 1) & 1u;
-                    tc::mbar_wait(sbase + OFF_XOPEN + 8 * (cur_g & 1), par, 20);
-                    sq_claim_units(P, cur_g, smem, sbase, xbytes, lane, *s_epoch);          // usually nothing left to take
-                    tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), par, 20);
-                }
+                if (cur_g < P.n_groups) tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), (uint32_t) (cur_g >> 1) & 1u, 20);
             }
         };
         // Completion accounting (only when a later group of the list waits for an earlier job): a warp "passes" job j once all
         // its rows of the jobs <= j are stored — it walks the list in order — and checks in on a CTA counter; the CTA reports job
-        // j as done when its 28 consumer warps and its quantizers (which have then read the job's activations) have checked in.
+        // j as done when its 28 consumer warps and its coordinator (which has then seen the job's activations quantized) have checked in.
         // done[j] == grid therefore means: every row of every job <= j is stored, and nobody will read their activations again.
         // The check-in comes BEFORE the wait for the next group's activations, which may be what is waiting for it.
         int passed = 0;
@@ -355,7 +315,6 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 }
             }
             passed = upto;
-            if (P.n_ll && lane == 0) s_prog[warp] = (uint32_t) upto;      // (the quantizers open a data-dependent group when all 28 are past its source)
         };
         while (consumed < produced) {
             uint32_t row, m1;                                 // (the slot's description was written when its fill was issued)
@@ -424,63 +383,51 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         // ================================================= quantizer warps ==============================================
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        const int qt  = tid - SQ_NCW * 32;                    // 0 .. 127
-        unsigned long long * tr = nullptr;
-        if (P.trace && qt == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) tr = P.trace + (blockIdx.x == 0 ? 0 : SQ_MAX_JOBS * 4);
-        auto stamp = [&](const int g, const int what) {
-            if (tr) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tr[g * 4 + what] = t; }
-        };
-        for (int gidx = 0; gidx < P.n_groups; ++gidx) {
-            const int jq = P.gfirst[gidx];
-            stamp(gidx, 0);
-            const sq_job & J = P.jobs[jq];
-            const int b = gidx & 1;
-            const uint32_t par = (uint32_t) (gidx >> 1) & 1u;
-            if (qt < 32 && J.xsrc >= 0) {
-                // Activations that ARE an earlier job's output are polled in the exchange buffer.  Polling starts when this CTA's own
-                // consumer warps are past that job — the other CTAs finish at about the same time, so few polls fail (polling from
-                // the moment the buffer is free would flood the L2 with failing reads: measured 2.3 ms instead of 1.35 ms per step).
-                const long long t0 = clock64();
-                while (true) {
-                    const uint32_t mine = lane < SQ_NCW ? s_prog[lane] : 0xffffffffu;
-                    if (__reduce_min_sync(0xffffffffu, mine) > (uint32_t) J.xsrc) break;
-                    __nanosleep(20);
-                    if (clock64() - t0 > 8000000000LL) __trap();
-                }
-            }
-            if (qt == 0) {
-                // the coordinator opens the group: buffer free, dependency complete, unit counter reset
-                if (gidx == 0) *s_epoch = sq_epoch(P);
-                if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, par ^ 1u, 20);
-                if (J.dep >= 0) {
-                    // every CTA has finished job `dep` and everything before it (rows stored, activations read)
-                    const uint32_t * flag = P.done + J.dep;
-                    uint32_t seen;
+        const int qw = warp - SQ_NCW;                         // 0: coordinator of this CTA's activation buffers; 1 .. 3: producers of units
+        const uint32_t epoch = sq_epoch(P);
+        if (qw == 0) {
+            if (lane == 0) *s_epoch = epoch;
+            unsigned long long * tr = nullptr;
+            if (P.trace && lane == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) tr = P.trace + (blockIdx.x == 0 ? 0 : SQ_MAX_JOBS * 4);
+            auto stamp = [&](const int g, const int what) {
+                if (tr) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tr[g * 4 + what] = t; }
+            };
+            for (int gidx = 0; gidx < P.n_groups; ++gidx) {
+                const int jq = P.gfirst[gidx];
+                const sq_job & J = P.jobs[jq];
+                const int b = gidx & 1;
+                const uint32_t par = (uint32_t) (gidx >> 1) & 1u;
+                const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
+                const int nunits = (nbk + ub - 1) / ub;
+                stamp(gidx, 0);
+                // every unit of the group has been announced with this launch's epoch (lane l watches units l and l + 32)
+                {
+                    const uint32_t * f = P.xflag + (size_t) gidx * 64;
                     const long long t0 = clock64();
-                    while (true) {
-                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
-                        if (seen >= gridDim.x) break;
-                        if (clock64() - t0 > 8000000000LL) __trap();      // a broken dependency must not hang the box
+                    for (int u = lane; u < nunits; u += 32) {
+                        uint32_t seen;
+                        while (true) {
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(f + u) : "memory");
+                            if (seen == epoch) break;
+                            __nanosleep(40);
+                            if (clock64() - t0 > 20000000000LL) __trap();
+                        }
                     }
+                    __syncwarp();
                 }
                 stamp(gidx, 1);
-                reinterpret_cast<uint32_t *>(smem + OFF_CLAIM)[b] = 0;
-                const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
-                tc::mbar_arrive_expect_tx(sbase + OFF_XFULL + 8 * b, (uint32_t) ((nbk + ub - 1) / ub));
-                tc::mbar_arrive(sbase + OFF_XOPEN + 8 * b);
-            }
-            tc::mbar_wait(sbase + OFF_XOPEN + 8 * b, par, 20);
-            sq_claim_units(P, gidx, smem, sbase, xbytes, lane, *s_epoch);
-            // no quantizer warp is inside this group's claim loop any more when the coordinator goes on (the counter is reused)
-            asm volatile("bar.sync 1, %0;" :: "n"(SQ_NQW * 32) : "memory");
-            stamp(gidx, 2);
-            if (tr) { tc::mbar_wait(sbase + OFF_XFULL + 8 * b, par, 20); stamp(gidx, 3); }
-            // the quantizers' check-in for the flagged jobs of this group: their activations have been read by this CTA
-            if (P.n_flagged && qt == 0) {
-                bool any = false;
-                for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) any = any || (P.jobs[jj].flags & 1);
-                if (any) {
-                    tc::mbar_wait(sbase + OFF_XFULL + 8 * b, par, 20);            // all units, whoever took them
+                if (lane == 0) {
+                    if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, par ^ 1u, 20);       // the buffer's previous group has been consumed
+                    asm volatile("fence.proxy.async;" ::: "memory");                           // the image was written with ordinary stores
+                    const uint8_t * img = P.ximg + P.gimg[gidx];
+                    const uint32_t xb = sbase + OFF_X + (uint32_t) b * (uint32_t) xbytes, bar = sbase + OFF_XFULL + 8 * b;
+                    tc::mbar_arrive_expect_tx(bar, (uint32_t) nbk * 40u);
+                    bulk_g2s(xb, img, (uint32_t) nbk * 32u, bar);
+                    bulk_g2s(xb + (uint32_t) P.kmax, img + (size_t) nbk * 32, (uint32_t) nbk * 8u, bar);
+                }
+                stamp(gidx, 2);
+                // check-in for the flagged jobs of this group: their activations have been read (quantized) for good
+                if (P.n_flagged && lane == 0) {
                     uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
                     for (int jj = jq; jj < P.n_jobs && (int) P.jobs[jj].xg == gidx; ++jj) {
                         if (!(P.jobs[jj].flags & 1)) continue;
@@ -489,6 +436,43 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                             __threadfence();
                             atomicAdd(P.done + jj, 1u);
                         }
+                    }
+                }
+                if (tr) { tc::mbar_wait(sbase + OFF_XFULL + 8 * b, par, 20); stamp(gidx, 3); }
+                __syncwarp();
+            }
+        } else {
+            // producers: this CTA's share of the units, in group order; warp qw takes the groups g with g % 3 == qw - 1
+            for (int gidx = qw - 1; gidx < P.n_groups; gidx += SQ_NQW - 1) {
+                const sq_job & J = P.jobs[P.gfirst[gidx]];
+                const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
+                const int nunits = (nbk + ub - 1) / ub;
+                const uint32_t first = (blockIdx.x + gridDim.x - (uint32_t) ((37 * gidx) % (int) gridDim.x)) % gridDim.x;    // (37 g + u) % grid == this CTA
+                if ((int) first >= nunits) continue;
+                if (J.dep >= 0) {
+                    // hazards ordered by completion counters: every CTA has finished job `dep` and everything before it
+                    if (lane == 0) {
+                        const uint32_t * flag = P.done + J.dep;
+                        uint32_t seen;
+                        const long long t0 = clock64();
+                        while (true) {
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+                            if (seen >= gridDim.x) break;
+                            __nanosleep(40);
+                            if (clock64() - t0 > 20000000000LL) __trap();
+                        }
+                    }
+                    __syncwarp();
+                }
+                // (row split: the slot of this launch's epoch parity; entries are indexed by the row of the FULL matrix)
+                const unsigned long long * ll = J.xsrc >= 0 ? P.ll + (MULTI ? (size_t) (epoch & 1u) * P.ll_cap : 0) + P.jobs[J.xsrc].ll_off : nullptr;
+                uint8_t * img = P.ximg + P.gimg[gidx];
+                for (int u = (int) first; u < nunits; u += (int) gridDim.x) {
+                    sq_produce_unit(J.X, ll, epoch, nbk, ub, u, img, lane);
+                    __syncwarp();
+                    if (lane == 0) {
+                        __threadfence();                          // the unit's image before its flag
+                        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(P.xflag + (size_t) gidx * 64 + u), "r"(epoch) : "memory");
                     }
                 }
             }
@@ -517,14 +501,14 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             }
         }
     }
-    if (P.n_flagged || P.n_ll) {
+    {
         // the last CTA to finish leaves the counters at zero for the next launch (nobody polls them any more) and counts the launch
         __syncthreads();
         if (tid == 0) {
             __threadfence();
             if (atomicAdd(P.done + SQ_MAX_JOBS, 1u) == gridDim.x - 1) {
                 if (P.n_flagged) for (int j = 0; j < P.n_jobs; ++j) P.done[j] = 0;
-                if (P.n_ll) P.done[SQ_MAX_JOBS + 1] += 1;
+                P.done[SQ_MAX_JOBS + 1] += 1;
                 P.done[SQ_MAX_JOBS] = 0;
             }
         }

@@ -39,11 +39,13 @@ struct sq_params {
     int        n_flagged;       // jobs with flags & 1
     int        pair_min;        // a CTA with more rows of a job than this walks them in pairs, else one by one
     int        _pad;
-    int        n_ll;            // jobs with an exchange region (0 and n_flagged == 0: the kernel touches no global state)
+    int        n_ll;            // jobs with an exchange region
     uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j), [SQ_MAX_JOBS] ticket, [SQ_MAX_JOBS + 1] launch
                                 // epoch; counters and ticket are zero between launches, the epoch counts the launches that used it
     unsigned long long * trace; // debugging (ctx option stream_trace): %globaltimer stamps of the coordinator of CTA 0 and of the last CTA,
                                 // [2][SQ_MAX_JOBS][4] = {group start, opened, own units done, all units done}; NULL = off
+    uint8_t *  ximg;            // quantized-activation images of the launch's groups (gimg[g] = byte offset of group g's image)
+    uint32_t * xflag;           // [SQ_MAX_JOBS][64] unit flags: == launch epoch once unit u of group g is in the image
     unsigned long long * ll;    // exchange buffer (entries of 8 bytes: epoch << 32 | f32 bits), zero-initialised
     // row split, one process per GPU (b200_mul_mat_batch_gather): every result goes as one {value, epoch} word into the exchange
     // buffer of EVERY rank (peer-mapped, own rank included), at entry (epoch & 1) * ll_cap + ll_off + row0 + row; the plain Y
@@ -52,6 +54,7 @@ struct sq_params {
     unsigned long long   ll_cap;
     unsigned long long * ll_peer[8];
     uint16_t   gfirst[SQ_MAX_JOBS];   // first job of activation group g
+    uint32_t   gimg[SQ_MAX_JOBS];     // byte offset of group g's image in ximg
     sq_job     jobs[SQ_MAX_JOBS];
 };
 

@@ -52,14 +52,9 @@ units = buf[2 * 512 * 4: 2 * 512 * 4 + 128 * 32 * 3].reshape(128, 32, 3).astype(
 enter = buf[2 * 512 * 4 + 128 * 32 * 3:].reshape(128, 32, 2).astype(np.int64)
 t0 = tr[0, 0, 0]
 gn = ["qkv", "wo", "gate_up", "down"]
-print(f"mode={mode} stream_ll={ll}  (ns; CTA 0 | last CTA)  group: start opened(+wait) own-units-done all-units-done   group-to-group")
+print(f"mode={mode} stream_ll={ll}  (ns; CTA 0 | last CTA)  group: coordinator start, +flags seen, +copy issued, +image in shared memory   group-to-group")
 for gi in range(n_groups):
     a, b = tr[0, gi], tr[1, gi]
     nxt = tr[0, gi + 1, 3] - a[3] if gi + 1 < n_groups else 0
-    print(f"{gi:3d} {gn[gi % 4]:8s} {a[0]-t0:8d} open+{a[1]-a[0]:6d} units+{a[2]-a[1]:6d} all+{a[3]-a[1]:6d} | last CTA open {b[1]-t0:8d} all+{b[3]-b[1]:6d} | next group's x ready after {nxt:6d}")
+    print(f"{gi:3d} {gn[gi % 4]:8s} {a[0]-t0:8d} flags+{a[1]-a[0]:6d} issue+{a[2]-a[1]:6d} landed+{a[3]-a[2]:6d} | last CTA flags at {b[1]-t0:8d} landed+{b[3]-b[2]:6d} | next group's x ready after {nxt:6d}")
 
-for gi in range(4, 8):
-    o = tr[0, gi, 1]
-    print(f"group {gi} {gn[gi % 4]}: opened at {o - t0}; units (claim, done, warp) relative to open:")
-    print("   ", [(int(units[gi, u, 0] - o), int(units[gi, u, 1] - o), int(units[gi, u, 2])) for u in range(32) if units[gi, u, 0] > 0])
-    print("    consumer warps (wait start, x ready) relative to open:", [(int(enter[gi, w, 0] - o), int(enter[gi, w, 1] - o)) for w in range(28)])
