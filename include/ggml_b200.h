@@ -117,6 +117,12 @@ B200_API int b200_quantize_row_q8_1(b200_ctx * ctx, const float * x, int64_t x_r
  * src0 rows must be whole blocks with nb[0] == type_size; src1 needs nb[0] == 4; dst must be contiguous f32.
  * n <= 8 per batch runs the GEMV family, larger n the tensor-core GEMM. */
 B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+/* Ordering contract of the decode kernels: consecutive launches of one context overlap (programmatic dependent launch); a GEMV
+ * reads its activations BEFORE its predecessors have finished only when no kernel still in flight on this context writes them.
+ * The context tracks the outputs of its OWN launches for that; memory written by anything else — another context or stream, a
+ * peer GPU, a copy — must be ordered before the call by the caller (event / synchronize), as with any CUDA stream.  The entry
+ * points that write through peer mappings or wait for events (b200_mul_mat_gather*, b200_event_wait, b200_rowsplit_*) make the
+ * next launch wait early on their own. */
 /* returns 1 if b200_mul_mat accepts this triple, 0 if not (used by supports_op) — no device needed */
 B200_API int b200_mul_mat_supported(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
 

@@ -131,7 +131,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->noop          = env_int("GGML_B200_NOOP", 0);
     ctx->defer_wait    = env_int("GGML_B200_DEFER_WAIT", 1);
     ctx->use_stream    = env_int("GGML_B200_USE_STREAM", 1);
-    ctx->stream_min_jobs = env_int("GGML_B200_STREAM_MIN_JOBS", 2);
+    ctx->stream_min_jobs = env_int("GGML_B200_STREAM_MIN_JOBS", 6);
     ctx->stream_stages = env_int("GGML_B200_STREAM_STAGES", 0);
     ctx->stream_ll     = env_int("GGML_B200_STREAM_LL", 1);
     ctx->stream_grid   = env_int("GGML_B200_STREAM_GRID", 0);
@@ -703,7 +703,13 @@ int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor
     if (!ctx || !b || n_dst < 1 || !dst) { b200_set_error("mul_mat_gather: bad argument"); return B200_E_ARG; }
     // n <= 8: GEMV family; n > 8: tcgen05 GEMM (both store to the peers from their epilogues); completion is the caller's barrier
     if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
-    return b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
+    const int rc = b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
+    // The in-flight write tracker knows d_shard only; the same kernel also wrote this rank's rows of the full-height outputs
+    // (dst[p] through peer mappings), and other ranks write the rest.  A later GEMV that reads such a vector must not defer its
+    // dependency wait: force the next launch to wait before it reads.  (Deferral contract: only writes made through this context
+    // are tracked — see ggml_b200.h.)
+    ctx->n_pend = 16;
+    return rc;
 }
 
 // Several weight matrices against the same activations (q/k/v projections, gate/up): one launch instead of n_mats.
@@ -996,6 +1002,8 @@ extern "C" int b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor 
                 kmax = k2; ++e;
             }
         }
+        // (a persistent launch costs ~8 us before its first row — launch, barriers, ring prologue, the first group's image — against
+        // ~4 us for a per-matmul kernel: measured break-even at one decoder layer's 7 matmuls, so shorter runs keep the per-launch kernels)
         if (e - j >= (ctx->stream_min_jobs > 1 ? ctx->stream_min_jobs : 1)) {
             const int rc = stream_run(ctx, e - j, a + j, b + j, d + j);
             if (rc) return rc;

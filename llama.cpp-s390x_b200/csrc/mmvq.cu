@@ -270,6 +270,13 @@ __device__ __forceinline__ void q4k_task(const q4k_frag & f, const int sb, const
 // mm_resolve for the common case "one matrix, one column tile" (every decode matmul of a model): nothing to divide.  The 64-bit
 // divisions of the general resolution cost about a microsecond on the way to the first weight request of a kernel that
 // streams its matrix in two (measured: Llama-3-8B decode step 1.20 -> 1.11 ms).
+// Why this is a separate function and not a branch inside mm_resolve (round-2 diagnosis of the round-1 conformance failure):
+// with the shortcut INSIDE mm_resolve — one call site or two, Wm const or not — the nvcc 12.9 / ptxas build of gemv_q4k<1,32>
+// computes the FIRST weight fragment of the early (pre-griddepcontrol) path from P.W read straight out of the constant bank
+// (SASS at the join of the two resolve branches: LDCU.128 c[0x0][0x380] -> address = P.W + row * nb01 + sb * 144), i.e. it drops
+// the batch offset (i12 / r2) * nb02 + (i13 / r3) * nb03 that the general branch computed; x and y pointers are right.  Every
+// batched test-backend-ops case (bs != [1,1]) then multiplies batch 0's weights; with pdl = 0 (the late path) the same binary is
+// correct, and an in-kernel printf of C.W shows the resolved pointer correct.  Kept apart, the compiler has nothing to fold.
 template <int NC>
 __device__ __forceinline__ bool mm_resolve_fast(const mm_problem & P, mm_cols<NC> & C) {
     if (!(P.mode == MM_PLAIN && gridDim.y == 1)) return mm_resolve<NC>(P, blockIdx.y, C);

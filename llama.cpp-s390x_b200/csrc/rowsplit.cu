@@ -117,6 +117,9 @@ int b200_rowsplit_create(const int * devices, int n_dev, const float * split, b2
         rs->dev[i] = devices[i];
         int rc = b200_ctx_create(devices[i], nullptr, &rs->ctx[i]);
         if (rc) { b200_rowsplit_destroy(rs); return rc; }
+        // the automatic split-K of the tcgen05 GEMM depends on the tile count, i.e. on the shard height: shards never split K, so
+        // that every split of a matrix runs one and the same K schedule (the unsplit matrix run with tc_split_k = 0 gives the same bits)
+        rs->ctx[i]->tc_split_k = 0;
         cudaError_t err = cudaEventCreateWithFlags(&rs->ev[i], cudaEventDisableTiming);
         if (err != cudaSuccess) { b200_set_error("cudaEventCreate: %s", cudaGetErrorString(err)); b200_rowsplit_destroy(rs); return B200_E_CUDA; }
     }
@@ -243,6 +246,7 @@ int b200_rowsplit_mul_mat(b200_rowsplit * rs, const b200_split_weights * w, floa
         d.nb[0] = 4; d.nb[1] = rows * 4; d.nb[2] = d.nb[3] = rows * 4 * n;
         rc = b200_mul_mat_ex(rs->ctx[i], &a, &b, &d, mode == 1 ? G : 0, y_dev, w->m, w->lo[i]);
         if (rc) return rc;
+        rs->ctx[i]->n_pend = 16;       // (outputs written through peer mappings are not in the in-flight tracker: wait early next time)
     }
 
     // 2) exchange

@@ -128,7 +128,11 @@ int main(int argc, char ** argv) {
     const std::vector<float> y_plain = run(gpu, ggml_backend_dev_buffer_type(dev), type, m, k, n, wq, x, false);
     const std::vector<float> y_split = run(gpu, sbuft, type, m, k, n, wq, x, true);
 
-    const bool same = memcmp(y_plain.data(), y_split.data(), y_plain.size() * sizeof(float)) == 0;
+    // Same bits: the shards run the per-row arithmetic of the unsplit kernel.  One documented exception: the unsplit tcgen05 GEMM may
+    // split a long K in two when the matrix has few tiles (k >= 8192, n > 8), the shards never do — then the two K halves are
+    // added in a different association and the results agree to fp32 rounding only.
+    const bool may_split_k = n > 8 && k >= 8192;
+    const bool same = may_split_k ? nmse(y_plain, y_split) <= 1e-10 : memcmp(y_plain.data(), y_split.data(), y_plain.size() * sizeof(float)) == 0;
     const double e_plain = nmse(y_cpu, y_plain), e_split = nmse(y_cpu, y_split);
     printf("split_check type=%s m=%lld k=%lld n=%lld buft=%s split==plain:%d nmse_plain=%.3e nmse_split=%.3e\n", argv[1], (long long) m, (long long) k,
            (long long) n, ggml_backend_buft_name(sbuft), (int) same, e_plain, e_split);

@@ -71,7 +71,7 @@ SPLIT_CHECK = refenv.REF_DIR / "split_check"
 
 @pytest.mark.parametrize("args,shards", [(("q4_K", "4096", "4096", "1", "0.5"), 2), (("q4_K", "1536", "2048", "4", "0.3"), 3), (("q8_0", "1000", "1024", "5", "0.6"), 2),
                                          (("q6_K", "1280", "2048", "1", "0.5"), 4), (("q4_0", "2048", "512", "8", "0.5"), 2), (("q4_K", "2048", "4096", "64", "0.4"), 2),
-                                         (("q8_0", "4096", "4096", "512", "0.5"), 2)])
+                                         (("q8_0", "4096", "4096", "512", "0.5"), 2), (("q4_K", "2048", "8192", "512", "0.5"), 4)])
 def test_split_buffer_type(args, shards):
     """oracle/split_check.cpp: "ggml_backend_split_buffer_type" from the registry (llama.cpp -sm row), weights scattered by
     set_tensor, MUL_MAT with src1 / dst on the main device == the unsplit result bit for bit and == the CPU backend within
