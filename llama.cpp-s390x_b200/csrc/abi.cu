@@ -153,6 +153,7 @@ void b200_ctx_destroy(b200_ctx * ctx) {
     if (ctx->sq_ll) cudaFree(ctx->sq_ll);
     if (ctx->sq_img) cudaFree(ctx->sq_img);
     if (ctx->sq_xflag) cudaFree(ctx->sq_xflag);
+    if (ctx->sq_emu) cudaFree(ctx->sq_emu);
     if (ctx->sq_trace) cudaFree(ctx->sq_trace);
     if (ctx->dev_x) cudaFree(ctx->dev_x);
     if (ctx->dev_y) cudaFree(ctx->dev_y);
@@ -913,20 +914,29 @@ extern "C" int b200_stream_comm_init(b200_ctx * ctx, int rank, int world, void *
     return B200_OK;
 }
 
-extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
-                                         const b200_tensor * const * d_full, const int64_t * row0) {
-    if (!ctx || n_jobs < 0 || (n_jobs > 0 && (!a || !b || !d_full || !row0))) { b200_set_error("mul_mat_batch_gather: bad argument"); return B200_E_ARG; }
-    if (ctx->sq_world < 2) { b200_set_error("mul_mat_batch_gather: b200_stream_comm_init was not called (world >= 2)"); return B200_E_ARG; }
+// emu_world > 0 (tests): all ranks inside one launch on this GPU — a[j] are the FULL matrices, every rank r works on rows
+// [r m / world, (r + 1) m / world) and on its own copy of the vectors (emu_stride bytes apart), see gemv_q4k_stream<2>
+static int gather_impl(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b, const b200_tensor * const * d_full,
+                       const int64_t * row0, int emu_world, size_t emu_stride, unsigned long long * emu_ll, size_t emu_cap) {
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    const uint32_t G = (uint32_t) b200_gemv_stream_grid(ctx);
+    const int world = emu_world > 0 ? emu_world : ctx->sq_world;
+    const uint32_t G = emu_world > 0 ? (uint32_t) (ctx->sm_count / emu_world) : (uint32_t) b200_gemv_stream_grid(ctx);
+    const size_t cap = emu_world > 0 ? emu_cap : ctx->sq_peer_cap;
+    // emulation: per-rank counters, flags and images in one zero-initialised block [done | flags | images]
+    const size_t emu_done_b = (size_t) 8 * (SQ_MAX_JOBS + 2) * 4, emu_flag_b = (size_t) 8 * SQ_MAX_JOBS * 64 * 4, emu_img_b = (size_t) 4 << 20;
+    if (emu_world > 0 && !ctx->sq_emu) {
+        B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_emu, emu_done_b + emu_flag_b + 8 * emu_img_b));
+        B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_emu, 0, emu_done_b + emu_flag_b + 8 * emu_img_b, ctx->stream));
+    }
     static thread_local sq_params P;
     for (int j0 = 0; j0 < n_jobs; ) {
         // one launch: up to SQ_MAX_JOBS jobs whose exchange entries fit a slot
         memset(&P, 0, offsetof(sq_params, jobs));
         P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
-        P.world = ctx->sq_world; P.rank = ctx->sq_rank; P.ll_cap = ctx->sq_peer_cap;
-        for (int p = 0; p < ctx->sq_world; ++p) P.ll_peer[p] = ctx->sq_peer[p];
-        P.ll = ctx->sq_peer[ctx->sq_rank];
+        P.world = world; P.rank = emu_world > 0 ? 0 : ctx->sq_rank; P.ll_cap = cap;
+        for (int p = 0; p < world; ++p) P.ll_peer[p] = emu_world > 0 ? emu_ll + (size_t) p * 2 * cap : ctx->sq_peer[p];
+        P.ll = P.ll_peer[P.rank];
+        if (emu_world > 0) { P.emu_stride = emu_stride; P.emu_img_stride = emu_img_b; }
         size_t entries = 0;
         int n = 0, group = -1, group_first = 0, group_size = 0;
         std::vector<int> xsrc;
@@ -935,23 +945,24 @@ extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_
             if (!A || !B || !D || A->type != B200_TYPE_Q4_K || A->ne[0] % 256 != 0 || A->ne[0] / 256 > 65535 || A->ne[2] * A->ne[3] != 1 || A->ne[1] < 0 ||
                 (A->ne[1] > 0 && !aligned16(A->data, A->nb[1], 0, 0)) || A->nb[1] >= ((int64_t) 1 << 32) || A->nb[0] != SZ_Q4_K ||
                 B->type != B200_TYPE_F32 || B->ne[0] != A->ne[0] || B->ne[1] * B->ne[2] * B->ne[3] != 1 || B->nb[0] != 4 || !aligned16(B->data, 0, 0, 0) ||
-                D->type != B200_TYPE_F32 || D->nb[0] != 4 || D->ne[1] * D->ne[2] * D->ne[3] != 1 || row0[j] < 0 || row0[j] + A->ne[1] > D->ne[0] ||
+                D->type != B200_TYPE_F32 || D->nb[0] != 4 || D->ne[1] * D->ne[2] * D->ne[3] != 1 || (emu_world == 0 && (row0[j] < 0 || row0[j] + A->ne[1] > D->ne[0])) ||
                 D->ne[0] >= ((int64_t) 1 << 31) || b200_gemv_stream_stages(ctx, A->ne[0]) < 2) {
                 b200_set_error("mul_mat_batch_gather[%d]: Q4_K row shards (16-byte aligned rows, k %% 256 == 0) x one f32 column -> one full-height f32 column", j);
                 return B200_E_UNSUPPORTED;
             }
             const size_t need = ((size_t) D->ne[0] + 3) & ~(size_t) 3;
-            if (entries + need > ctx->sq_peer_cap) {
-                if (n == 0) { b200_set_error("mul_mat_batch_gather[%d]: %lld results exceed the exchange slot (%zu entries)", j, (long long) D->ne[0], ctx->sq_peer_cap); return B200_E_ARG; }
+            if (entries + need > cap) {
+                if (n == 0) { b200_set_error("mul_mat_batch_gather[%d]: %lld results exceed the exchange slot (%zu entries)", j, (long long) D->ne[0], cap); return B200_E_ARG; }
                 break;
             }
+            if (emu_world > 0 && (A->ne[1] % emu_world != 0 || A->ne[1] != D->ne[0])) { b200_set_error("emulated row split: m must be a multiple of the world size"); return B200_E_ARG; }
             const int64_t kmax2 = A->ne[0] > P.kmax ? A->ne[0] : P.kmax;
             if (b200_gemv_stream_stages(ctx, kmax2) < 2) break;
             sq_job & J = P.jobs[n];
-            const uint32_t m = (uint32_t) A->ne[1];
+            const uint32_t m = (uint32_t) (emu_world > 0 ? A->ne[1] / emu_world : A->ne[1]);
             J.W = (const uint8_t *) A->data; J.X = (const float *) B->data; J.Y = (float *) D->data;
             J.nb01 = (uint32_t) A->nb[1]; J.base = m / G; J.rem = (uint16_t) (m % G); J.nsb = (uint16_t) (A->ne[0] / 256);
-            J.row0 = (uint32_t) row0[j]; J.m_full = (uint32_t) D->ne[0];
+            J.row0 = (uint32_t) (emu_world > 0 ? 0 : row0[j]); J.m_full = (uint32_t) D->ne[0];
             J.dep = -1; J.xsrc = -1; J.flags = 0; J.ll_off = (uint32_t) entries;
             entries += need;
             P.kmax = (int) kmax2;
@@ -976,12 +987,35 @@ extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_
         }
         P.n_jobs = n; P.n_groups = group + 1; P.n_ll = n;
         if (const int rc = stream_images(ctx, P)) return rc;
+        if (emu_world > 0) {
+            if ((size_t) P.gimg[P.n_groups - 1] + (size_t) P.jobs[P.gfirst[P.n_groups - 1]].nsb * 320 > emu_img_b) { b200_set_error("emulated row split: images exceed 4 MB"); return B200_E_ARG; }
+            P.done  = (uint32_t *) ctx->sq_emu;
+            P.xflag = (uint32_t *) ((char *) ctx->sq_emu + emu_done_b);
+            P.ximg  = (uint8_t *) ctx->sq_emu + emu_done_b + emu_flag_b;
+        }
         ctx->n_pend = 0;
         const int rc = b200_launch_gemv_stream(ctx, P);
         if (rc) return rc;
         j0 += n;
     }
     return B200_OK;
+}
+
+extern "C" int b200_mul_mat_batch_gather(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,
+                                         const b200_tensor * const * d_full, const int64_t * row0) {
+    if (!ctx || n_jobs < 0 || (n_jobs > 0 && (!a || !b || !d_full || !row0))) { b200_set_error("mul_mat_batch_gather: bad argument"); return B200_E_ARG; }
+    if (ctx->sq_world < 2) { b200_set_error("mul_mat_batch_gather: b200_stream_comm_init was not called (world >= 2)"); return B200_E_ARG; }
+    return gather_impl(ctx, n_jobs, a, b, d_full, row0, 0, 0, nullptr, 0);
+}
+
+// testing aid, deliberately not in ggml_b200.h: b200_mul_mat_batch_gather with `world` ranks emulated inside ONE cooperative launch
+// on this GPU.  a[j] = the full matrices; b[j] / d_full[j] = rank 0's vectors, rank r's copies lie r * arena_stride bytes further;
+// ll = zero-initialised exchange memory of world * 2 * slot_entries * 8 bytes.
+extern "C" __attribute__((visibility("default"))) int b200_dbg_batch_gather_emulated(b200_ctx * ctx, int world, size_t arena_stride, void * ll, int64_t slot_entries,
+        int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b, const b200_tensor * const * d_full) {
+    if (!ctx || world < 2 || world > B200_MAX_PEERS || !ll || slot_entries < 4 || slot_entries % 4 != 0 || arena_stride % 16 != 0 || arena_stride == 0 ||
+        n_jobs < 0 || (n_jobs > 0 && (!a || !b || !d_full))) { b200_set_error("dbg_batch_gather_emulated: bad argument"); return B200_E_ARG; }
+    return gather_impl(ctx, n_jobs, a, b, d_full, nullptr, world, arena_stride, (unsigned long long *) ll, (size_t) slot_entries);
 }
 
 extern "C" int b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a, const b200_tensor * const * b,

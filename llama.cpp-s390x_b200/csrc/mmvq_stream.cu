@@ -163,9 +163,9 @@ __device__ __forceinline__ void sq_produce_unit(const float * x, const unsigned 
 
 // this launch's epoch: launches that use the exchange buffer are counted in done[SQ_MAX_JOBS + 1] (advanced by the last CTA to
 // finish; read after griddepcontrol.wait, i.e. after the previous launch has completed)
-__device__ __forceinline__ uint32_t sq_epoch(const sq_params & P) {
+__device__ __forceinline__ uint32_t sq_epoch(const uint32_t * done) {
     uint32_t e;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(P.done + SQ_MAX_JOBS + 1) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(e) : "l"(done + SQ_MAX_JOBS + 1) : "memory");
     return e + 1;
 }
 
@@ -183,8 +183,7 @@ struct sq_cursor {
     uint32_t stride;     // rows per step of job j in this CTA (1 or 2)
 };
 
-__device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
-    const uint32_t b = blockIdx.x;
+__device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, const uint32_t warp, const uint32_t b) {
     while (cu.j < P.n_jobs) {
         const sq_job & J = P.jobs[cu.j];
         const uint32_t cnt    = J.base + (b < J.rem ? 1u : 0u);
@@ -205,22 +204,35 @@ __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, con
     }
 }
 
-__device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, const uint32_t warp) {
+__device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, const uint32_t warp, const uint32_t b) {
     if (++cu.c < cu.nch) return;
     cu.c = 0;
     cu.row += cu.stride * SQ_NCW;
     if (cu.row < cu.rhi) return;
     const sq_job & J = P.jobs[cu.j];
-    const uint32_t cnt = J.base + (blockIdx.x < J.rem ? 1u : 0u);
+    const uint32_t cnt = J.base + (b < J.rem ? 1u : 0u);
     cu.rot = (cu.rot + (cnt + cu.stride - 1) / cu.stride) % SQ_NCW;
     cu.j++;
-    sq_seek(P, cu, warp);
+    sq_seek(P, cu, warp, b);
 }
 
-// MULTI: row split over `world` processes (one per GPU), see sq_params::ll_peer
-template <bool MULTI>
+// MODE 0: one GPU.  MODE 1: row split over `world` processes (one per GPU), see sq_params::ll_peer.  MODE 2 (tests): the same row
+// split with ALL ranks inside one launch on one GPU — CTAs [r G, (r + 1) G) are rank r, every rank has its own exchange buffer,
+// images, flags, counters and activation / result arena (rank r's copy of a vector of rank 0 lies emu_stride bytes further) and
+// its shard is rows [r m, (r + 1) m) of the full matrices the job table points to.  One cooperative launch: its blocks wait on
+// one another, which separate launches on one GPU must not do.
+template <int MODE>
 __global__ void __launch_bounds__(SQ_THREADS, 1)
 gemv_q4k_stream(const __grid_constant__ sq_params P) {
+    constexpr bool MULTI = MODE != 0;
+    const uint32_t G   = MODE == 2 ? gridDim.x / (uint32_t) P.world : gridDim.x;       // CTAs of one rank
+    const uint32_t cta = MODE == 2 ? blockIdx.x % G : blockIdx.x;
+    const uint32_t er  = MODE == 2 ? blockIdx.x / G : 0u;                               // emulated rank of this CTA
+    uint32_t * const done  = P.done  + (MODE == 2 ? (size_t) er * (SQ_MAX_JOBS + 2) : 0);
+    uint32_t * const xflag = P.xflag + (MODE == 2 ? (size_t) er * SQ_MAX_JOBS * 64 : 0);
+    uint8_t *  const ximg  = P.ximg  + (MODE == 2 ? (size_t) er * P.emu_img_stride : 0);
+    const unsigned long long * const ll_local = MODE == 2 ? P.ll_peer[er] : P.ll;
+    const size_t arena = MODE == 2 ? (size_t) er * P.emu_stride : 0;                   // bytes between rank 0's and this rank's vectors
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t sbase = tc::smem_u32(smem);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -254,14 +266,14 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
 
         sq_cursor pc;                                     // producer cursor: S steps ahead of the consumer
         pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0; pc.stride = 1;
-        sq_seek(P, pc, (uint32_t) warp);
+        sq_seek(P, pc, (uint32_t) warp, cta);
         auto fill = [&](const int slot) {
             const sq_job & J = P.jobs[pc.j];
             const int      left  = (int) J.nsb - pc.c * SQ_CHUNK_SB;
             const uint32_t bytes = (uint32_t) (left < SQ_CHUNK_SB ? left : SQ_CHUNK_SB) * SZ_Q4_K;
             const bool     two   = pc.stride == 2 && pc.row + 1 < pc.rhi;
             const bool     last  = pc.c + 1 == pc.nch;
-            const uint8_t * src  = J.W + (size_t) pc.row * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
+            const uint8_t * src  = J.W + ((size_t) pc.row + (MODE == 2 ? (size_t) er * (J.base * G + J.rem) : 0)) * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
             const uint32_t dst   = ring0 + (uint32_t) slot * SQ_SLOT_B;
             const uint32_t bar   = bar0 + 8 * slot;
             if (tc::elect_one()) {
@@ -272,7 +284,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 if (two) bulk_g2s(dst + SQ_CHUNK_B, src + J.nb01, bytes, bar);
             }
             __syncwarp();
-            sq_advance(P, pc, (uint32_t) warp);
+            sq_advance(P, pc, (uint32_t) warp, cta);
         };
         int produced = 0, consumed = 0;
         // weights are never written by a kernel of this path: the rings are filled before the dependency wait
@@ -310,7 +322,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
                         cnt[jj & (SQ_NCNT - 1)] = 0;
                         __threadfence();
-                        atomicAdd(P.done + jj, 1u);
+                        atomicAdd(done + jj, 1u);
                     }
                 }
             }
@@ -355,7 +367,8 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     // lane p delivers to rank p (the butterfly sum left sA / sB in every lane): one NVLink store per rank and row
                     if (lane < P.world) {
                         const uint32_t epoch = *s_epoch;
-                        unsigned long long * e = P.ll_peer[lane] + (size_t) (epoch & 1u) * P.ll_cap + J.ll_off + J.row0 + row;
+                        unsigned long long * e = P.ll_peer[lane] + (size_t) (epoch & 1u) * P.ll_cap + J.ll_off + J.row0 + row +
+                                                 (MODE == 2 ? (size_t) er * (J.base * G + J.rem) : 0);
                         asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sA)) : "memory");
                         if (two) asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e + 1), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sB)) : "memory");
                     }
@@ -384,7 +397,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         asm volatile("griddepcontrol.wait;" ::: "memory");
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const int qw = warp - SQ_NCW;                         // 0: coordinator of this CTA's activation buffers; 1 .. 3: producers of units
-        const uint32_t epoch = sq_epoch(P);
+        const uint32_t epoch = sq_epoch(done);
         if (qw == 0) {
             if (lane == 0) *s_epoch = epoch;
             unsigned long long * tr = nullptr;
@@ -402,7 +415,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 stamp(gidx, 0);
                 // every unit of the group has been announced with this launch's epoch (lane l watches units l and l + 32)
                 {
-                    const uint32_t * f = P.xflag + (size_t) gidx * 64;
+                    const uint32_t * f = xflag + (size_t) gidx * 64;
                     const long long t0 = clock64();
                     for (int u = lane; u < nunits; u += 32) {
                         uint32_t seen;
@@ -419,7 +432,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 if (lane == 0) {
                     if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, par ^ 1u, 20);       // the buffer's previous group has been consumed
                     asm volatile("fence.proxy.async;" ::: "memory");                           // the image was written with ordinary stores
-                    const uint8_t * img = P.ximg + P.gimg[gidx];
+                    const uint8_t * img = ximg + P.gimg[gidx];
                     const uint32_t xb = sbase + OFF_X + (uint32_t) b * (uint32_t) xbytes, bar = sbase + OFF_XFULL + 8 * b;
                     tc::mbar_arrive_expect_tx(bar, (uint32_t) nbk * 40u);
                     bulk_g2s(xb, img, (uint32_t) nbk * 32u, bar);
@@ -434,7 +447,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                         if (atomicAdd(cnt + (jj & (SQ_NCNT - 1)), 1u) == (uint32_t) SQ_NCW) {
                             cnt[jj & (SQ_NCNT - 1)] = 0;
                             __threadfence();
-                            atomicAdd(P.done + jj, 1u);
+                            atomicAdd(done + jj, 1u);
                         }
                     }
                 }
@@ -447,17 +460,17 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 const sq_job & J = P.jobs[P.gfirst[gidx]];
                 const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
                 const int nunits = (nbk + ub - 1) / ub;
-                const uint32_t first = (blockIdx.x + gridDim.x - (uint32_t) ((37 * gidx) % (int) gridDim.x)) % gridDim.x;    // (37 g + u) % grid == this CTA
+                const uint32_t first = (cta + G - (uint32_t) ((37 * gidx) % (int) G)) % G;    // (37 g + u) % grid == this CTA
                 if ((int) first >= nunits) continue;
                 if (J.dep >= 0) {
                     // hazards ordered by completion counters: every CTA has finished job `dep` and everything before it
                     if (lane == 0) {
-                        const uint32_t * flag = P.done + J.dep;
+                        const uint32_t * flag = done + J.dep;
                         uint32_t seen;
                         const long long t0 = clock64();
                         while (true) {
                             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
-                            if (seen >= gridDim.x) break;
+                            if (seen >= G) break;
                             __nanosleep(40);
                             if (clock64() - t0 > 20000000000LL) __trap();
                         }
@@ -465,14 +478,15 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     __syncwarp();
                 }
                 // (row split: the slot of this launch's epoch parity; entries are indexed by the row of the FULL matrix)
-                const unsigned long long * ll = J.xsrc >= 0 ? P.ll + (MULTI ? (size_t) (epoch & 1u) * P.ll_cap : 0) + P.jobs[J.xsrc].ll_off : nullptr;
-                uint8_t * img = P.ximg + P.gimg[gidx];
-                for (int u = (int) first; u < nunits; u += (int) gridDim.x) {
-                    sq_produce_unit(J.X, ll, epoch, nbk, ub, u, img, lane);
+                const unsigned long long * ll = J.xsrc >= 0 ? ll_local + (MULTI ? (size_t) (epoch & 1u) * P.ll_cap : 0) + P.jobs[J.xsrc].ll_off : nullptr;
+                uint8_t * img = ximg + P.gimg[gidx];
+                const float * xsrc = reinterpret_cast<const float *>(reinterpret_cast<const char *>(J.X) + arena);
+                for (int u = (int) first; u < nunits; u += (int) G) {
+                    sq_produce_unit(xsrc, ll, epoch, nbk, ub, u, img, lane);
                     __syncwarp();
                     if (lane == 0) {
                         __threadfence();                          // the unit's image before its flag
-                        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(P.xflag + (size_t) gidx * 64 + u), "r"(epoch) : "memory");
+                        asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(xflag + (size_t) gidx * 64 + u), "r"(epoch) : "memory");
                     }
                 }
             }
@@ -484,10 +498,11 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         // later one's values; nobody in this launch reads the plain vectors of its own jobs (they are polled in the buffer).
         __syncthreads();
         const uint32_t epoch = *s_epoch;
-        const unsigned long long * base = P.ll + (size_t) (epoch & 1u) * P.ll_cap;
+        const unsigned long long * base = ll_local + (size_t) (epoch & 1u) * P.ll_cap;
         for (int j = 0; j < P.n_jobs; ++j) {
             const sq_job & J = P.jobs[j];
-            for (uint32_t i = blockIdx.x * SQ_THREADS + tid; i < J.m_full; i += gridDim.x * SQ_THREADS) {
+            float * yj = reinterpret_cast<float *>(reinterpret_cast<char *>(J.Y) + arena);
+            for (uint32_t i = cta * SQ_THREADS + tid; i < J.m_full; i += G * SQ_THREADS) {
                 const unsigned long long * p = base + J.ll_off + i;
                 unsigned long long w;
                 const long long t0 = clock64();
@@ -497,7 +512,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     __nanosleep(100);
                     if (clock64() - t0 > 20000000000LL) __trap();     // ~10 s: a rank that never delivers must not hang the others for ever
                 }
-                J.Y[i] = __uint_as_float((uint32_t) w);
+                yj[i] = __uint_as_float((uint32_t) w);
             }
         }
     }
@@ -506,10 +521,10 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         __syncthreads();
         if (tid == 0) {
             __threadfence();
-            if (atomicAdd(P.done + SQ_MAX_JOBS, 1u) == gridDim.x - 1) {
-                if (P.n_flagged) for (int j = 0; j < P.n_jobs; ++j) P.done[j] = 0;
-                P.done[SQ_MAX_JOBS + 1] += 1;
-                P.done[SQ_MAX_JOBS] = 0;
+            if (atomicAdd(done + SQ_MAX_JOBS, 1u) == G - 1) {
+                if (P.n_flagged) for (int j = 0; j < P.n_jobs; ++j) done[j] = 0;
+                done[SQ_MAX_JOBS + 1] += 1;
+                done[SQ_MAX_JOBS] = 0;
             }
         }
     }
@@ -538,28 +553,30 @@ int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
     }
     const size_t smem = sq_smem(P.kmax, P.stages);
     const bool multi = P.world > 1;
-    auto kern = multi ? gemv_q4k_stream<true> : gemv_q4k_stream<false>;
+    const int  mode  = !multi ? 0 : P.emu_stride ? 2 : 1;
+    auto kern = mode == 0 ? gemv_q4k_stream<0> : mode == 1 ? gemv_q4k_stream<1> : gemv_q4k_stream<2>;
     static std::mutex attr_mutex;
-    static bool attr_done[2][64] = {};         // per variant and device
+    static bool attr_done[3][64] = {};         // per variant and device
     {
         std::lock_guard<std::mutex> lock(attr_mutex);
-        if (!attr_done[multi][ctx->device & 63]) {
+        if (!attr_done[mode][ctx->device & 63]) {
             B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
-            attr_done[multi][ctx->device & 63] = true;
+            attr_done[mode][ctx->device & 63] = true;
         }
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim          = dim3((unsigned) b200_gemv_stream_grid(ctx));
+    cfg.gridDim          = dim3((unsigned) (mode == 2 ? P.world * (ctx->sm_count / P.world) : b200_gemv_stream_grid(ctx)));
     cfg.blockDim         = dim3(SQ_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream           = ctx->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
+    if (mode == 2) { attr[0].id = cudaLaunchAttributeCooperative; attr[0].val.cooperative = 1; }
     cfg.attrs    = attr;
     // (row split: no early start of the next launch — its CTAs would only sit on SMs that another rank's kernel may need when
     // several ranks share one GPU in the tests, and a full-size grid leaves no SM free anyway)
-    cfg.numAttrs = ctx->pdl && !multi ? 1 : 0;
+    cfg.numAttrs = mode == 2 ? 1 : ctx->pdl && !multi ? 1 : 0;
     B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, P));
     ctx->launches++;
     return B200_OK;

@@ -53,6 +53,9 @@ struct sq_params {
     int        world, rank;
     unsigned long long   ll_cap;
     unsigned long long * ll_peer[8];
+    // tests only: all ranks inside one launch on one GPU (gemv_q4k_stream<2>); 0 = off
+    unsigned long long   emu_stride;      // bytes between the activation / result vectors of consecutive ranks
+    unsigned long long   emu_img_stride;  // bytes between the ranks' image buffers
     uint16_t   gfirst[SQ_MAX_JOBS];   // first job of activation group g
     uint32_t   gimg[SQ_MAX_JOBS];     // byte offset of group g's image in ximg
     sq_job     jobs[SQ_MAX_JOBS];

@@ -195,19 +195,23 @@ def test_batch_llama_shapes_sampled_rows_vs_oracle(pkg, gpu_ctx, orc, m, k):
 
 
 @pytest.mark.parametrize("world,slot", [(2, 16384), (4, 16384), (2, 8192)])
-def test_row_split_list_emulated_on_one_gpu(pkg, world, slot):
-    """b200_mul_mat_batch_gather (the persistent kernel with the all-gather folded in) with `world` ranks emulated on ONE GPU:
-    every rank is a context with its own stream, exchange buffer and a reduced grid, so that the world's launches are
-    co-resident and exchange {value, epoch} words with each other exactly as over NVLink.  A dependent chain (q/k/v-style
-    sharing, wo reads q, ...) must give, on every rank, bit for bit what sequential b200_mul_mat calls give on the unsplit
-    matrices — twice in a row (both exchange slots) and a third time (slot reuse).  slot = 8192 entries do not hold the whole
-    list: it is cut into two launches."""
+def test_row_split_list_all_ranks_in_one_launch(pkg, world, slot):
+    """b200_mul_mat_batch_gather (the persistent kernel with the all-gather folded in) with `world` ranks emulated on ONE GPU inside
+    ONE cooperative launch (gemv_q4k_stream<2>: CTAs [r G, (r + 1) G) are rank r; separate launches that wait for one another must
+    not share a GPU).  Every rank has its own exchange buffer, activation images, flags, counters and vectors, works on its row
+    shard and exchanges {value, epoch} words with the others exactly as over NVLink.  A dependent chain (q/k/v-style sharing, wo
+    reads q, ...) must give, on every rank, bit for bit what sequential b200_mul_mat calls give on the unsplit matrices — three
+    times in a row (both exchange slots, then slot reuse).  slot = 8192 entries do not hold the whole list: it is cut into two
+    launches."""
+    import ctypes as C
+
     import torch
+    from llama_cpp_s390x_b200.binding import Tensor
+    from llama_cpp_s390x_b200.ops import _desc
     rng = np.random.default_rng(21 + world)
-    grid = 148 // world - 2
     # (name, m, k): wq/wk/wv share x0; wo reads q; gate/up read wo's output; down reads gate's output; head reads down's output
     dims = [("wq", 1024, 512), ("wk", 256, 512), ("wv", 256, 512), ("wo", 512, 1024), ("gate", 1536, 512), ("up", 1536, 512), ("down", 512, 1536),
-            ("head", 3000, 512)]
+            ("head", 3072, 512)]
     Ws = {n: q4k(m, k, rng) for n, m, k in dims}
     x0 = dev((rng.standard_normal((1, 512)) * 30).astype(np.float32))
     ref_ctx = pkg.Context(0, stream="torch")
@@ -219,35 +223,39 @@ def test_row_split_list_emulated_on_one_gpu(pkg, world, slot):
     want["head"] = pkg.mul_mat(ref_ctx, Q4_K, Ws["head"], want["down"])
     ref_ctx.synchronize()
 
-    streams = [torch.cuda.Stream() for _ in range(world)]
-    ctxs = [pkg.Context(0, stream=s.cuda_stream) for s in streams]
-    bufs = [torch.zeros((2 * slot,), dtype=torch.int64, device="cuda") for _ in range(world)]
+    # one arena per rank: [x0 | y(wq) | y(wk) | ...], every vector 64-float aligned
+    off, o = {}, 512
+    for n, m, k in dims:
+        off[n] = o
+        o += (m + 63) // 64 * 64
+    arena = torch.zeros((world, o), dtype=torch.float32, device="cuda")
+    arena[:, :512] = x0
+
+    def vec(name, length):
+        start = 0 if name == "x0" else off[name]
+        return arena[0, start:start + length].view(1, length)
+
+    src = {"wq": "x0", "wk": "x0", "wv": "x0", "wo": "wq", "gate": "wo", "up": "wo", "down": "gate", "head": "down"}
+    a = [_desc(Ws[n], Q4_K, k_elems=k) for n, m, k in dims]
+    b = [_desc(vec(src[n], k), pkg.F32) for n, m, k in dims]
+    d = [_desc(vec(n, m), pkg.F32) for n, m, k in dims]
+    T = C.POINTER(Tensor)
+    ap, bp, dp = ((T * len(dims))(*[C.pointer(t) for t in arr]) for arr in (a, b, d))
+    ll = torch.zeros((world * 2 * slot,), dtype=torch.int64, device="cuda")
+    stream = torch.cuda.Stream()
+    ctx = pkg.Context(0, stream=stream.cuda_stream)
     torch.cuda.synchronize()
-    batches, outs = [], []
-    for r in range(world):
-        ctxs[r].set_option("stream_grid", grid)
-        pkg.stream_comm_init(ctxs[r], r, world, [b.data_ptr() for b in bufs], slot)
-        y = {n: torch.full((1, m), float("nan"), device="cuda") for n, m, k in dims}
-        src = {"wq": x0, "wk": x0, "wv": x0, "wo": y["wq"], "gate": y["wo"], "up": y["wo"], "down": y["gate"], "head": y["down"]}
-        shards, row0s = [], []
-        for n, m, k in dims:
-            lo, rows = pkg.row_shard(m, r, world)
-            shards.append(Ws[n][lo:lo + rows].contiguous() if rows > 0 else Ws[n][0:0])
-            row0s.append(lo)
-        batches.append(pkg.MatmulBatchGather(Q4_K, shards, [src[n] for n, _, _ in dims], [y[n] for n, _, _ in dims], row0s))
-        outs.append(y)
+    L = pkg.lib()
+    L.b200_dbg_batch_gather_emulated.restype = C.c_int
+    L.b200_dbg_batch_gather_emulated.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p, C.c_int64, C.c_int, C.POINTER(T), C.POINTER(T), C.POINTER(T)]
     for rep in range(3):
-        for r in range(world):
-            for t in outs[r].values():
-                t.fill_(float("nan"))
+        arena[:, 512:] = float("nan")
         torch.cuda.synchronize()
+        pkg.check(L.b200_dbg_batch_gather_emulated(ctx.handle, world, arena.stride(0) * 4, ll.data_ptr(), slot, len(dims), ap, bp, dp), "b200_dbg_batch_gather_emulated")
+        ctx.synchronize()
         for r in range(world):
-            batches[r].run(ctxs[r])
-        for r in range(world):
-            ctxs[r].synchronize()
-        for r in range(world):
-            for n, _, _ in dims:
-                assert torch.equal(outs[r][n], want[n]), (rep, r, n)
-    for c in ctxs:
-        c.close()
+            for n, m, k in dims:
+                got = arena[r, off[n]:off[n] + m].view(1, m)
+                assert torch.equal(got, want[n]), (rep, r, n)
+    ctx.close()
     ref_ctx.close()
