@@ -222,9 +222,14 @@ def prefill_bench(torch, pkg, ctx, stream, n=512):
             fused_ms += NL * (ms - sum(sep[(m, k)] for m in ms_))
             del Ws, X, Ys
         tf = flops / fused_ms / 1e9
+        head = per[f"{max(m for m, _ in shapes)}x{LLAMA3_8B[0][2]}"]
         out[tname] = {"ms_per_step": round(fused_ms, 3), "ms_per_step_unfused": round(total_ms, 3),
                       "tok_per_s_matmul_only": round(n / fused_ms * 1e3, 1), "tflops": round(tf, 1),
-                      "frac_of_tensor_peak": round(tf / peak, 4), "per_shape": per}
+                      "frac_of_tensor_peak": round(tf / peak, 4), "per_shape": per,
+                      "dtype": f"{tname} weights dequantized to fp16 in the producers, activations fp16 (per-column power-of-two normalised), fp32 accumulate in TMEM",
+                      "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(tf / peak, 4),
+                                   "kernel": "mmq_tc_f16_kernel (tcgen05.mma kind::f16) + tc_act_f16_kernel, count-weighted step of per-shape CUDA-graph timings",
+                                   "largest_shape_frac": round(head["tflops"] / peak, 4), "peak_source": src, "traffic": None}}
     return out
 
 
@@ -508,6 +513,8 @@ def run_gpu(args):
                    "tok_per_s": round(1e3 / plug["ms_per_step"], 2), "h2d_bytes_per_step": plug["h2d_bytes_per_step"],
                    "d2h_bytes_per_step": plug["d2h_bytes_per_step"], "api": plug["api"], "nmse_vs_cpu_backend": plug["nmse_vs_cpu_backend"],
                    "caps": plug["caps"], "host_memory": plug["host_memory"], "c_abi_host_batch": e2e}
+    if use_sg and not args.no_e2e:
+        e2e = rowsplit_e2e(torch, dist, pkg, ctx, order, rank, world, args)
     if world == 1 and args.shapes:
         shapes = per_shape(torch, pkg, ctx, stream, ops)
     decode_batch = None
@@ -527,13 +534,23 @@ def run_gpu(args):
     if world == 1 and not args.no_extras:
         torch.cuda.empty_cache()
         moe = moe_bench(torch, pkg, ctx, stream)
+    big = None
+    if MODEL.endswith("8B") and not args.no_extras and (world == 1 or use_sg):
+        # BASELINE configs[4]: the Llama-3-70B Q4_K decode step on the same N GPUs (row split through the same persistent launch)
+        try:
+            del ops, order, per_layer, groups
+        except NameError:
+            pass
+        batch = None
+        torch.cuda.empty_cache()
+        big = llama70b_step(torch, dist if world > 1 else None, pkg, ctx, stream, rank, world, args)
 
     if rank == 0:
         peak, peak_src = peaks()
         out = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int8 dot (dp4a) x fp32 scales; Q4_K weights, Q8_1 activations", "data": "synthetic",
+            "vs_baseline": None, "dtype": "u8 x s8 dp4a into int32 per 32-value block, fp32 block scales (Q4_K weights; activations quantized to the reference's Q8_1 values)", "data": "synthetic",
             "config": {"workload": f"{MODEL} Q4_K decode step: {STEP_MATMULS} MUL_MATs at n=1 (" + ", ".join(sorted({f"{m}x{k}" for _, m, k, _ in LLAMA3_8B})) + ")",
                        "weights_gb": round(sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9, 3),
                        "l2": f"inputs larger than L2: {sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_8B) / 1e9:.2f} GB of distinct weights per step vs 126 MB L2, no flush needed",
@@ -569,6 +586,8 @@ def run_gpu(args):
             out["prefill_rowsplit"] = prefill_rs
         if moe:
             out["moe"] = moe
+        if big:
+            out["llama3_70b"] = big
         if world == 1 and args.cpu_seconds > 0:
             out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
         print(json.dumps(out), flush=True)
@@ -646,6 +665,105 @@ def dependent_chain_bench(torch, pkg, ctx, stream, order, args):
     return res
 
 
+def rowsplit_e2e(torch, dist, pkg, ctx, order, rank, world, args):
+    """e2e at N > 1 through the C ABI: every rank copies the step's activation vectors from pinned host memory (H2D), runs the
+    row-split list (b200_mul_mat_batch_gather: one persistent launch with the all-gather folded in), copies all full-height
+    results back (D2H) and synchronizes — every step, inside the timed region; wall clock, max over ranks"""
+    L = pkg.lib()
+    # activation slots as in the model: wq / wk / wv share one vector, ffn_gate / ffn_up share one
+    share = {"wk": "wq", "wv": "wq", "ffn_up": "ffn_gate"}
+    x_off, y_off, xo, yo, last = [], [], 0, 0, {}
+    for (W, x, y, ys, (m, name)) in order:
+        k = x.shape[1]
+        if name in share and share[name] in last:
+            x_off.append(last[share[name]])
+        else:
+            x_off.append(xo); last[name] = xo; xo += k
+        if name in ("ffn_down", "output"):
+            last = {}
+        y_off.append(yo); yo += m
+    xh = torch.randn((xo,)).pin_memory(); yh = torch.empty((yo,)).pin_memory()
+    Xd = torch.empty((xo,), device="cuda"); Yd = torch.empty((yo,), device="cuda")
+    b = pkg.MatmulBatchGather(Q4_K, [o[0] for o in order], [Xd[x_off[i]:x_off[i] + o[1].shape[1]].view(1, -1) for i, o in enumerate(order)],
+                              [Yd[y_off[i]:y_off[i] + o[4][0]].view(1, -1) for i, o in enumerate(order)], [rank * (o[4][0] // world) for o in order])
+
+    def host_step():
+        pkg.check(L.b200_memcpy_async(ctx.handle, Xd.data_ptr(), xh.data_ptr(), xo * 4, 0), "h2d")
+        b.run(ctx)
+        pkg.check(L.b200_memcpy_async(ctx.handle, yh.data_ptr(), Yd.data_ptr(), yo * 4, 1), "d2h")
+        ctx.synchronize()
+
+    for _ in range(3):
+        host_step()
+    steps = max(3, min(args.steps, 10))
+    dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        host_step()
+    dt = torch.tensor([(time.perf_counter() - t0) * 1e3 / steps], device="cuda")
+    dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    ms = float(dt.item())
+    return {"value": round(STEP_BYTES / (ms * 1e-3) / 1e9, 2), "unit": UNIT, "ms_per_step": round(ms, 4), "tok_per_s": round(1e3 / ms, 2),
+            "h2d_bytes_per_step": int(xo * 4) * world, "d2h_bytes_per_step": int(yo * 4) * world,
+            "api": f"per rank: b200_memcpy_async H2D of the step's activations from pinned host memory, b200_mul_mat_batch_gather ({len(order)} matmuls, "
+                   f"one persistent launch, all-gather folded in), b200_memcpy_async D2H of all full-height results, b200_ctx_synchronize; wall clock, max over {world} ranks"}
+
+
+def llama70b_step(torch, dist, pkg, ctx, stream, rank, world, args):
+    """BASELINE configs[4] beside the headline: one Llama-3-70B Q4_K decode step (561 matmuls, 39.1 GB of weights), every matrix
+    row-split over the N ranks, through the same persistent launch (N = 1: b200_mul_mat_batch)"""
+    gen = torch.Generator(device="cuda"); gen.manual_seed(4242 + rank)
+    NL = LLAMA3_70B[0][3]
+    xs = {}
+    for _, m, k, _ in LLAMA3_70B:
+        if k not in xs:
+            xg = torch.Generator(device="cuda"); xg.manual_seed(99 + k)
+            xs[k] = torch.randn((1, k), device="cuda", generator=xg)
+    layers = [[] for _ in range(NL)]
+    head = None
+    for name, m, k, count in LLAMA3_70B:
+        for l in range(count):
+            item = (device_random_q4k(torch, m // world, k, gen), xs[k], torch.empty((1, m), device="cuda"), m)
+            if count == 1:
+                head = item
+            else:
+                layers[l].append(item)
+    seq = [it for layer in layers for it in layer] + [head]
+    if world == 1:
+        b = pkg.MatmulBatch(Q4_K, [i[0] for i in seq], [i[1] for i in seq], [i[2] for i in seq])
+    else:
+        b = pkg.MatmulBatchGather(Q4_K, [i[0] for i in seq], [i[1] for i in seq], [i[2] for i in seq], [rank * (i[3] // world) for i in seq])
+    with torch.cuda.stream(stream):
+        b.run(ctx); stream.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            b.run(ctx)
+        for _ in range(3):
+            g.replay()
+        stream.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 5
+        e0.record(stream)
+        for _ in range(iters):
+            g.replay()
+        e1.record(stream)
+        stream.synchronize()
+        if dist is not None:
+            dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    nbytes = sum(algo_bytes(m, k) * c for _, m, k, c in LLAMA3_70B)
+    peak, _ = peaks()
+    return {"workload": f"Llama-3-70B Q4_K decode step: {len(seq)} MUL_MATs at n=1, {sum(m * k * 4.5 / 8 * c for _, m, k, c in LLAMA3_70B) / 1e9:.1f} GB of weights, row split x{world}",
+            "ms_per_step": round(ms, 4), "gbps": round(nbytes / ms / 1e6, 1), "tok_per_s_matmul_only": round(1e3 / ms, 2),
+            "frac_of_hbm_peak_per_gpu": round(nbytes / ms / 1e6 / world / peak, 4)}
+
+
 def plugin_e2e(args):
     """e2e through the drop-in boundary itself: oracle/_ref/e2e_plugin (our oracle/e2e_plugin.cpp hosted by the reference's unmodified
     libggml) drives libggml-b200.so with ggml_backend_tensor_set_async / graph_compute_async / tensor_get_async / synchronize —
@@ -699,8 +817,12 @@ def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):
             per[name] = {"us": round(us, 2), "gbps": round(b / us / 1e3, 1)}
             step_us += us * count
             step_bytes += b * count
-        res[f"n{n}"] = {"ms_per_step": round(step_us / 1e3, 4), "gbps": round(step_bytes / step_us / 1e3, 1),
-                        "frac_of_hbm_peak": round(step_bytes / step_us / 1e3 / peak, 4), "tok_per_s_matmul_only": round(n * 1e6 / step_us, 1),
+        g = step_bytes / step_us / 1e3
+        res[f"n{n}"] = {"ms_per_step": round(step_us / 1e3, 4), "gbps": round(g, 1),
+                        "frac_of_hbm_peak": round(g / peak, 4), "tok_per_s_matmul_only": round(n * 1e6 / step_us, 1),
+                        "dtype": "u8 x s8 mma.sync (Q4_K nibbles x activations quantized per 256 values like the reference's Q8_K), int32 sums, fp32 scales",
+                        "roofline": {"bound": "hbm", "achieved": round(g, 1), "peak": peak, "unit": "GB/s", "frac": round(g / peak, 4),
+                                     "kernel": "gemv_q4k_mma<Q4_K> (one launch per matmul, count-weighted step of per-shape CUDA-graph timings)", "traffic": None},
                         "per_shape": per}
     return res
 
@@ -810,9 +932,15 @@ def moe_bench(torch, pkg, ctx, stream):
                 stream.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / (2 * iters)
             touched = int(len(np.unique(ids_np)))
+            gb, tf = touched * m * k * 4.5 / 8 / us / 1e3, 2.0 * m * k * n_tokens * NU / us / 1e6
+            hbm_peak, _ = peaks()
+            tpeak, _ = tensor_peak()
+            rl = ({"bound": "tensor", "achieved": round(tf, 1), "peak": tpeak, "unit": "TFLOP/s", "frac": round(tf / tpeak, 4),
+                   "kernel": "mm_ids_kernel + tc_act_f16_kernel (gather by expert) + mmq_tc_f16_kernel (grouped tcgen05 GEMM)"} if n_tokens > 8 else
+                  {"bound": "hbm", "achieved": round(gb, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(gb / hbm_peak, 4),
+                   "kernel": "gemv_q4k (one GEMV per (token, slot) pair)" if n_tokens == 1 else "mm_ids_kernel + gemv_q4k_mma (pairs gathered by expert)"})
             out[f"{label}_t{n_tokens}"] = {"us": round(us, 1), "experts_touched": touched,
-                                           "gbps_touched_expert_bytes": round(touched * m * k * 4.5 / 8 / us / 1e3, 1),
-                                           "tflops": round(2.0 * m * k * n_tokens * NU / us / 1e6, 1)}
+                                           "gbps_touched_expert_bytes": round(gb, 1), "tflops": round(tf, 1), "roofline": rl}
         del AS
         torch.cuda.empty_cache()
     return out
