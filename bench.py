@@ -632,8 +632,9 @@ def dependent_chain_bench(torch, pkg, ctx, stream, order, args):
     h_init = h0.clone()
     finals = {}
     with torch.cuda.stream(stream):
-        for label, fn in (("stream", lambda: batch.run(ctx)), ("per_launch", per_launch)):
+        for label, fn in (("stream", lambda: batch.run(ctx)), ("per_launch", per_launch), ("batch_default", lambda: batch.run(ctx))):
             prev = ctx.set_option("defer_wait", 0) if label == "per_launch" else None
+            prev_chain = ctx.set_option("stream_chain", 1 if label == "stream" else 0)
             h0.copy_(h_init)
             fn()
             stream.synchronize()
@@ -654,14 +655,18 @@ def dependent_chain_bench(torch, pkg, ctx, stream, order, args):
             res[label] = {"ms_per_step": round(ms, 4), "gbps": round(STEP_BYTES / ms / 1e6, 1), "tok_per_s_matmul_only": round(1e3 / ms, 1)}
             if prev is not None:
                 ctx.set_option("defer_wait", prev)
+            ctx.set_option("stream_chain", prev_chain)
             del gr
     # both ways compute the same chain, bit for bit (NaN-safe comparison of the raw words)
     assert torch.equal(finals["stream"].view(torch.int32), finals["per_launch"].view(torch.int32)), "dependent chain: stream != per-launch result"
     peak, _ = peaks()
     for label in res:
         res[label]["frac_of_hbm_peak"] = round(res[label]["gbps"] / peak, 4)
-    res["note"] = ("129 dependent groups per step; 'stream' = one b200_mul_mat_batch launch with in-kernel completion counters, 'per_launch' = "
-                   "129 launches, each waiting for its predecessor before reading its activations (defer_wait = 0)")
+    assert torch.equal(finals["stream"].view(torch.int32), finals["batch_default"].view(torch.int32)), "dependent chain: batch default != stream result"
+    res["note"] = ("129 dependent groups per step; 'stream' = forced through ONE persistent launch (dependencies travel as {value, epoch} words inside "
+                   "the kernel), 'per_launch' = 129 launches of the per-matmul kernels, each waiting for its predecessor before reading its activations "
+                   "(defer_wait = 0), 'batch_default' = what b200_mul_mat_batch does on its own for such a list (it detects the chain and keeps the "
+                   "per-launch kernels, with the deferred wait wherever the in-flight tracker allows it)")
     return res
 
 

@@ -135,6 +135,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->stream_stages = env_int("GGML_B200_STREAM_STAGES", 0);
     ctx->stream_ll     = env_int("GGML_B200_STREAM_LL", 1);
     ctx->stream_grid   = env_int("GGML_B200_STREAM_GRID", 0);
+    ctx->stream_chain  = env_int("GGML_B200_STREAM_CHAIN", 0);
     ctx->stream_pair_min = env_int("GGML_B200_STREAM_PAIR_MIN", 0);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
@@ -198,6 +199,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "stream_stages")) slot = &ctx->stream_stages;
     else if (!strcmp(name, "stream_ll"))     slot = &ctx->stream_ll;
     else if (!strcmp(name, "stream_grid"))   slot = &ctx->stream_grid;
+    else if (!strcmp(name, "stream_chain"))  slot = &ctx->stream_chain;
     else if (!strcmp(name, "stream_trace"))  slot = &ctx->stream_trace;
     else if (!strcmp(name, "stream_pair_min")) slot = &ctx->stream_pair_min;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
@@ -861,6 +863,14 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
         J.xg = (uint16_t) group;
     }
     P.n_groups = group + 1;
+    // A list that is mostly a dependency CHAIN (every group waits for the one before it) gains nothing from streaming across matrix
+    // boundaries, and a dependency inside the persistent kernel costs more than a kernel boundary (measured on the Llama-3-8B step
+    // wired like the model: 1.64 ms in one launch, 1.20 ms with one PDL launch per group): such lists keep the per-launch kernels.
+    {
+        int waiting = 0;
+        for (int g = 0; g < P.n_groups; ++g) waiting += P.jobs[P.gfirst[g]].dep >= 0 || P.jobs[P.gfirst[g]].xsrc >= 0;
+        if (!ctx->stream_chain && 2 * waiting > P.n_groups) return 1;      // not taken
+    }
     for (int j = 0; j < n; ++j) {
         if (P.jobs[j].dep >= 0 && !(P.jobs[P.jobs[j].dep].flags & 1)) { P.jobs[P.jobs[j].dep].flags |= 1; P.n_flagged++; }
     }
@@ -1040,9 +1050,9 @@ extern "C" int b200_mul_mat_batch(b200_ctx * ctx, int n_jobs, const b200_tensor 
         // ~4 us for a per-matmul kernel: measured break-even at one decoder layer's 7 matmuls, so shorter runs keep the per-launch kernels)
         if (e - j >= (ctx->stream_min_jobs > 1 ? ctx->stream_min_jobs : 1)) {
             const int rc = stream_run(ctx, e - j, a + j, b + j, d + j);
-            if (rc) return rc;
-            j = e;
-            continue;
+            if (rc < 0) return rc;
+            if (rc == 0) { j = e; continue; }
+            // (rc == 1: a dependency chain — the per-launch kernels below take it)
         }
         // otherwise: the matrices that share their activations in one launch (q / k / v, gate / up), everything else one by one
         e = j + 1;

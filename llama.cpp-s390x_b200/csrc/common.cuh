@@ -113,6 +113,7 @@ struct b200_ctx {
     int          use_stream;      // 1: runs of Q4_K n = 1 matmuls of a batch go through one persistent launch
     int          stream_min_jobs; // shortest run that takes the persistent kernel
     int          stream_stages;   // ring slots per warp override (0 = auto)
+    int          stream_chain;    // 1: lists that are mostly a dependency chain also take the persistent kernel (default: per-launch kernels)
     int          stream_grid;     // CTAs of the persistent kernel (0 = one per SM); smaller grids let several launches be co-resident
     int          stream_ll;       // 1: "X is exactly an earlier job's output" travels as {value, epoch} words (0: completion counters only)
     uint32_t *   sq_done;         // device: [SQ_MAX_JOBS + 2] completion counters, ticket, launch epoch

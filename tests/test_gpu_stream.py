@@ -26,8 +26,10 @@ def every_list_takes_the_persistent_kernel(gpu_ctx):
     """b200_mul_mat_batch keeps lists shorter than stream_min_jobs (default 6) on the per-launch kernels; these tests are about the
     persistent kernel, so it takes every list here"""
     prev = gpu_ctx.set_option("stream_min_jobs", 1)
+    prev_chain = gpu_ctx.set_option("stream_chain", 1)        # ... dependency chains included
     yield
     gpu_ctx.set_option("stream_min_jobs", prev)
+    gpu_ctx.set_option("stream_chain", prev_chain)
 
 
 def q4k(m, k, rng):
@@ -153,6 +155,7 @@ def test_batch_under_cuda_graph_replay(pkg, orc):
     stream = torch.cuda.Stream()
     ctx = pkg.Context(0, stream=stream.cuda_stream)
     ctx.set_option("stream_min_jobs", 1)
+    ctx.set_option("stream_chain", 1)
     dims = [2048, 1024, 2048, 1024, 2048]
     ws = [q4k(dims[i + 1], dims[i], rng) for i in range(len(dims) - 1)]
     x0 = dev((rng.standard_normal((1, dims[0])) * 30).astype(np.float32))
