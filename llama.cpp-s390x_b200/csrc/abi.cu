@@ -780,6 +780,25 @@ static int stream_images(b200_ctx * ctx, sq_params & P) {
         P.gimg[g] = (uint32_t) total;
         total += ((size_t) P.jobs[P.gfirst[g]].nsb * 320 + 127) & ~(size_t) 127;       // k int8 + k / 32 float2 = 320 B per super-block
     }
+    // the images' places in the shared-memory ring of 2 x the largest image: bump allocation with wrap-around; a place can be
+    // reused once every consumer warp has finished the groups that lay there
+    {
+        const size_t ring = 2 * ((size_t) P.kmax + (size_t) P.kmax / 4);
+        size_t off = 0;
+        std::vector<int> live;                              // groups whose place has not been handed on, oldest first
+        std::vector<size_t> lo((size_t) P.n_groups), hi((size_t) P.n_groups);
+        for (int g = 0; g < P.n_groups; ++g) {
+            const size_t sz = ((size_t) P.jobs[P.gfirst[g]].nsb * 320 + 127) & ~(size_t) 127;
+            if (off + sz > ring) off = 0;
+            lo[g] = off; hi[g] = off + sz;
+            int wait = -1;
+            std::vector<int> keep;
+            for (int q : live) { if (lo[q] < hi[g] && lo[g] < hi[q]) { if (q > wait) wait = q; } else keep.push_back(q); }
+            live.swap(keep); live.push_back(g);
+            P.gsm[g] = (uint32_t) off; P.gwait[g] = (int16_t) wait;
+            off += sz;
+        }
+    }
     if (total > ctx->sq_img_cap) {
         B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
         if (ctx->sq_img) { cudaFree(ctx->sq_img); ctx->sq_img = nullptr; ctx->sq_img_cap = 0; }

@@ -33,14 +33,15 @@ constexpr int SQ_THREADS  = (SQ_NCW + SQ_NQW) * 32;
 constexpr int SQ_CHUNK_SB = 8;                         // super-blocks of one row per chunk (one per 4 lanes)
 constexpr int SQ_CHUNK_B  = SQ_CHUNK_SB * SZ_Q4_K;     // 1152
 constexpr int SQ_SLOT_B   = 2 * SQ_CHUNK_B;            // a ring slot: the same chunk of two consecutive rows
-constexpr int SQ_MAX_S    = 4;
+constexpr int SQ_MAX_S    = 3;
 constexpr int SQ_NCNT     = 256;                       // CTA-level row counters, indexed by job % SQ_NCNT (see SQ_MAX_GROUP)
 
-// shared memory: [barriers | slot meta | row counters | x buffer 0 | x buffer 1 | rings]
+// shared memory: [barriers | progress words | slot meta | row counters | ring of activation images (2 x the largest image) | weight rings]
 constexpr int OFF_FULL  = 0;                                         // [SQ_NCW][SQ_MAX_S] u64
-constexpr int OFF_XFULL = OFF_FULL + SQ_NCW * SQ_MAX_S * 8;          // [2] u64
-constexpr int OFF_XEMPTY = OFF_XFULL + 16;                           // [2] u64
-constexpr int OFF_EPOCH = OFF_XEMPTY + 16;                           // u32: this launch's epoch (+ pad)
+constexpr int SQ_NXF    = 16;                                        // image barriers: group g completes xfull[g % 16], phase (g / 16) & 1
+constexpr int OFF_XFULL = OFF_FULL + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NXF] u64
+constexpr int OFF_GPROG = OFF_XFULL + SQ_NXF * 8;                    // [32] u32: consumer warp w has finished every group < s_gprog[w]
+constexpr int OFF_EPOCH = OFF_GPROG + 128;                           // u32: this launch's epoch (+ pad)
 constexpr int OFF_META  = OFF_EPOCH + 16;                            // [SQ_NCW][SQ_MAX_S] uint2
 constexpr int OFF_CNT   = OFF_META + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NCNT] u32
 constexpr int OFF_X     = (OFF_CNT + SQ_NCNT * 4 + 127) / 128 * 128;
@@ -237,17 +238,15 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
     const uint32_t sbase = tc::smem_u32(smem);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.stages;
-    const int xbytes = sq_xbytes(P.kmax);
 
     if (tid == 0) {
         for (int i = 0; i < SQ_NCW * SQ_MAX_S; ++i) tc::mbar_init(sbase + OFF_FULL + 8 * i, 1);
-        for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(sbase + OFF_XFULL + 8 * i, 1);          // the coordinator's expect_tx + the bytes of the image copies
-            tc::mbar_init(sbase + OFF_XEMPTY + 8 * i, SQ_NCW);
-        }
+        for (int i = 0; i < SQ_NXF; ++i) tc::mbar_init(sbase + OFF_XFULL + 8 * i, 1);      // the coordinator's expect_tx + the bytes of the image copies
         tc::mbar_fence_init();
     }
     if (tid < SQ_NCNT) reinterpret_cast<uint32_t *>(smem + OFF_CNT)[tid] = 0;
+    if (tid < 32) reinterpret_cast<uint32_t *>(smem + OFF_GPROG)[tid] = 0;
+    volatile uint32_t * s_gprog = reinterpret_cast<volatile uint32_t *>(smem + OFF_GPROG);
     volatile uint32_t * s_epoch = reinterpret_cast<volatile uint32_t *>(smem + OFF_EPOCH);
     __syncthreads();
 
@@ -262,7 +261,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         const uint32_t w_off = (uint32_t) sbl * SZ_Q4_K;
         const uint32_t q_off = w_off + 16 + 32 * g;
         const uint32_t a_off = (uint32_t) (sbl * 16 + 4 * g) * 16;
-        const uint32_t e_off = (uint32_t) P.kmax + (uint32_t) (sbl * 8 + 2 * g) * 8;
+        const uint32_t e_off = (uint32_t) (sbl * 8 + 2 * g) * 8;
 
         sq_cursor pc;                                     // producer cursor: S steps ahead of the consumer
         pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0; pc.stride = 1;
@@ -297,15 +296,18 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         int   cur_g = -1;
         float accA = 0.0f, accB = 0.0f;
         uint32_t * cnt = reinterpret_cast<uint32_t *>(smem + OFF_CNT);
-        // move on to activation group `want`: hand the buffers of finished groups back, wait for the new one
+        // move on to activation group `want`: publish that every earlier group is finished by this warp (its image may be overwritten
+        // once all 28 warps say so), wait for the new group's image (it sits at gsm[g] of the image ring)
+        uint32_t xb = 0;
         auto enter_group = [&](const int want) {
             while (cur_g < want) {
-                if (cur_g >= 0) {
-                    __syncwarp();                            // every lane has finished reading the old buffer
-                    if (lane == 0) tc::mbar_arrive(sbase + OFF_XEMPTY + 8 * (cur_g & 1));
-                }
                 cur_g++;
-                if (cur_g < P.n_groups) tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & 1), (uint32_t) (cur_g >> 1) & 1u, 20);
+                __syncwarp();                                // every lane has finished reading the old image
+                if (lane == 0) s_gprog[warp] = (uint32_t) cur_g;
+                if (cur_g < P.n_groups) {
+                    tc::mbar_wait(sbase + OFF_XFULL + 8 * (cur_g & (SQ_NXF - 1)), (uint32_t) (cur_g / SQ_NXF) & 1u, 20);
+                    xb = sbase + OFF_X + P.gsm[cur_g];
+                }
             }
         };
         // Completion accounting (only when a later group of the list waits for an earlier job): a warp "passes" job j once all
@@ -341,14 +343,13 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             tc::mbar_wait(bar0 + 8 * slot, phase);
             const int sb = c * SQ_CHUNK_SB + sbl;
             if (sb < (int) J.nsb) {
-                const uint32_t xb = sbase + OFF_X + (uint32_t) (cur_g & 1) * (uint32_t) xbytes;
                 const uint32_t ab = xb + (uint32_t) c * (SQ_CHUNK_SB * 256) + a_off;
                 act_frag A;
                 A.a0 = lds128(ab + 16 * (0 ^ xsw));
                 A.a1 = lds128(ab + 16 * (1 ^ xsw));
                 A.a2 = lds128(ab + 16 * (2 ^ xsw));
                 A.a3 = lds128(ab + 16 * (3 ^ xsw));
-                const uint4 ev = lds128(xb + (uint32_t) c * (SQ_CHUNK_SB * 64) + e_off);
+                const uint4 ev = lds128(xb + (uint32_t) J.nsb * 256u + (uint32_t) c * (SQ_CHUNK_SB * 64) + e_off);
                 A.e = make_float4(__uint_as_float(ev.x), __uint_as_float(ev.y), __uint_as_float(ev.z), __uint_as_float(ev.w));
                 const uint32_t ws = ring0 + (uint32_t) slot * SQ_SLOT_B;
                 {
@@ -408,8 +409,8 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             for (int gidx = 0; gidx < P.n_groups; ++gidx) {
                 const int jq = P.gfirst[gidx];
                 const sq_job & J = P.jobs[jq];
-                const int b = gidx & 1;
-                const uint32_t par = (uint32_t) (gidx >> 1) & 1u;
+                const int b = gidx & (SQ_NXF - 1);
+                const uint32_t par = (uint32_t) (gidx / SQ_NXF) & 1u;
                 const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
                 const int nunits = (nbk + ub - 1) / ub;
                 stamp(gidx, 0);
@@ -429,14 +430,26 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     __syncwarp();
                 }
                 stamp(gidx, 1);
+                // the image's place in the ring is free: every consumer warp has finished the groups that lay there (host-computed:
+                // gwait[g] = the latest such group), and the barrier of group g - 16 has been waited for by everybody
+                {
+                    const int need = (int) P.gwait[gidx] > gidx - SQ_NXF ? (int) P.gwait[gidx] : gidx - SQ_NXF;
+                    if (need >= 0) {
+                        const long long t0 = clock64();
+                        while (true) {
+                            const uint32_t mine = lane < SQ_NCW ? s_gprog[lane] : 0xffffffffu;
+                            if (__reduce_min_sync(0xffffffffu, mine) > (uint32_t) need) break;
+                            __nanosleep(20);
+                            if (clock64() - t0 > 20000000000LL) __trap();
+                        }
+                    }
+                }
                 if (lane == 0) {
-                    if (gidx >= 2) tc::mbar_wait(sbase + OFF_XEMPTY + 8 * b, par ^ 1u, 20);       // the buffer's previous group has been consumed
                     asm volatile("fence.proxy.async;" ::: "memory");                           // the image was written with ordinary stores
                     const uint8_t * img = ximg + P.gimg[gidx];
-                    const uint32_t xb = sbase + OFF_X + (uint32_t) b * (uint32_t) xbytes, bar = sbase + OFF_XFULL + 8 * b;
+                    const uint32_t xbuf = sbase + OFF_X + P.gsm[gidx], bar = sbase + OFF_XFULL + 8 * b;
                     tc::mbar_arrive_expect_tx(bar, (uint32_t) nbk * 40u);
-                    bulk_g2s(xb, img, (uint32_t) nbk * 32u, bar);
-                    bulk_g2s(xb + (uint32_t) P.kmax, img + (size_t) nbk * 32, (uint32_t) nbk * 8u, bar);
+                    bulk_g2s(xbuf, img, (uint32_t) nbk * 40u, bar);                            // int8 plane + (d, d * sum) plane, contiguous
                 }
                 stamp(gidx, 2);
                 // check-in for the flagged jobs of this group: their activations have been read (quantized) for good

@@ -8,7 +8,7 @@
 #pragma once
 #include "common.cuh"
 
-#define SQ_MAX_JOBS    512      // per launch (longer lists are cut into several launches)
+#define SQ_MAX_JOBS    448      // per launch (longer lists are cut into several launches; bounded by the 32 KB of kernel parameters)
 #define SQ_MAX_GROUP   64       // jobs that may share one quantized activation vector (bounds the live window of the CTA counters)
 
 #define SQ_NO_LL 0xffffffffu
@@ -58,6 +58,8 @@ struct sq_params {
     unsigned long long   emu_img_stride;  // bytes between the ranks' image buffers
     uint16_t   gfirst[SQ_MAX_JOBS];   // first job of activation group g
     uint32_t   gimg[SQ_MAX_JOBS];     // byte offset of group g's image in ximg
+    uint32_t   gsm[SQ_MAX_JOBS];      // byte offset of group g's image in the shared-memory image ring (2 x the largest image of the launch)
+    int16_t    gwait[SQ_MAX_JOBS];    // the latest earlier group whose image lay in that place (-1: none): it must be finished first
     sq_job     jobs[SQ_MAX_JOBS];
 };
 
