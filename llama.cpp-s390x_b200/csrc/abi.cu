@@ -136,7 +136,6 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->stream_ll     = env_int("GGML_B200_STREAM_LL", 1);
     ctx->stream_grid   = env_int("GGML_B200_STREAM_GRID", 0);
     ctx->stream_chain  = env_int("GGML_B200_STREAM_CHAIN", 0);
-    ctx->stream_pair_min = env_int("GGML_B200_STREAM_PAIR_MIN", 0);
     if (ctx->max_gemv_cols < 1) ctx->max_gemv_cols = 1;
     if (ctx->max_gemv_cols > 8) ctx->max_gemv_cols = 8;
     *out = ctx;
@@ -201,7 +200,6 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "stream_grid"))   slot = &ctx->stream_grid;
     else if (!strcmp(name, "stream_chain"))  slot = &ctx->stream_chain;
     else if (!strcmp(name, "stream_trace"))  slot = &ctx->stream_trace;
-    else if (!strcmp(name, "stream_pair_min")) slot = &ctx->stream_pair_min;
     if (!slot) { b200_set_error("unknown option '%s'", name); return B200_E_ARG; }
     const int prev = *slot;
     *slot = value;
@@ -821,7 +819,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
     }
     static thread_local sq_params P;                        // ~26 KB: not on the stack of every caller
     memset(&P, 0, offsetof(sq_params, jobs));
-    P.n_jobs = n; P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
+    P.n_jobs = n; P.done = ctx->sq_done;
     const uint32_t G = (uint32_t) b200_gemv_stream_grid(ctx);
     std::vector<const char *> xlo((size_t) n), xhi((size_t) n), ylo((size_t) n), yhi((size_t) n);
     std::vector<int> xsrc((size_t) n, -1);                  // job whose exchange entries job j reads instead of X
@@ -833,9 +831,9 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
         const uint32_t m = (uint32_t) a[j]->ne[1];
         J.W = (const uint8_t *) a[j]->data; J.X = (const float *) b[j]->data; J.Y = (float *) d[j]->data;
         J.nb01 = (uint32_t) a[j]->nb[1];
-        J.base = m / G; J.rem = (uint16_t) (m % G);
+        J.base = ((m + 1) / 2) / G; J.rem = (uint16_t) (((m + 1) / 2) % G);          // row pairs
         J.nsb = (uint16_t) (a[j]->ne[0] / 256);
-        J.dep = -1; J.xsrc = -1; J.flags = 0; J.ll_off = SQ_NO_LL;
+        J.dep = -1; J.xsrc = -1; J.flags = (uint16_t) ((m & 1u) << 1); J.ll_off = SQ_NO_LL;
         if (a[j]->ne[0] > P.kmax) P.kmax = (int) a[j]->ne[0];
         xlo[j] = (const char *) J.X; xhi[j] = xlo[j] + 4 * a[j]->ne[0];
         ylo[j] = (const char *) J.Y; yhi[j] = ylo[j] + 4 * a[j]->ne[1];
@@ -961,7 +959,7 @@ static int gather_impl(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a
     for (int j0 = 0; j0 < n_jobs; ) {
         // one launch: up to SQ_MAX_JOBS jobs whose exchange entries fit a slot
         memset(&P, 0, offsetof(sq_params, jobs));
-        P.done = ctx->sq_done; P.pair_min = ctx->stream_pair_min;
+        P.done = ctx->sq_done;
         P.world = world; P.rank = emu_world > 0 ? 0 : ctx->sq_rank; P.ll_cap = cap;
         for (int p = 0; p < world; ++p) P.ll_peer[p] = emu_world > 0 ? emu_ll + (size_t) p * 2 * cap : ctx->sq_peer[p];
         P.ll = P.ll_peer[P.rank];
@@ -990,9 +988,11 @@ static int gather_impl(b200_ctx * ctx, int n_jobs, const b200_tensor * const * a
             sq_job & J = P.jobs[n];
             const uint32_t m = (uint32_t) (emu_world > 0 ? A->ne[1] / emu_world : A->ne[1]);
             J.W = (const uint8_t *) A->data; J.X = (const float *) B->data; J.Y = (float *) D->data;
-            J.nb01 = (uint32_t) A->nb[1]; J.base = m / G; J.rem = (uint16_t) (m % G); J.nsb = (uint16_t) (A->ne[0] / 256);
+            J.nb01 = (uint32_t) A->nb[1]; J.base = ((m + 1) / 2) / G; J.rem = (uint16_t) (((m + 1) / 2) % G); J.nsb = (uint16_t) (A->ne[0] / 256);
             J.row0 = (uint32_t) (emu_world > 0 ? 0 : row0[j]); J.m_full = (uint32_t) D->ne[0];
-            J.dep = -1; J.xsrc = -1; J.flags = 0; J.ll_off = (uint32_t) entries;
+            J.dep = -1; J.xsrc = -1; J.flags = (uint16_t) ((m & 1u) << 1); J.ll_off = (uint32_t) entries;
+            // (the two results of a row pair travel as one aligned 16-byte store: shards start at even rows and, emulated, have an even height)
+            if ((J.row0 & 1u) || (emu_world > 0 && (m & 1u))) { b200_set_error("mul_mat_batch_gather[%d]: row shards must start at an even row", j); return B200_E_UNSUPPORTED; }
             entries += need;
             P.kmax = (int) kmax2;
             // X is exactly the full-height output of an earlier job of this launch: polled in the exchange buffer.  Any other overlap

@@ -123,7 +123,6 @@ struct b200_ctx {
     size_t       sq_img_cap;
     uint32_t *   sq_xflag;        // device: [SQ_MAX_JOBS][64] unit flags
     void *       sq_emu;          // tests: per-rank counters, flags and images of the emulated row split
-    int          stream_pair_min; // rows of a job per CTA up to which they are walked one by one instead of in pairs
     // row split of the persistent kernel, one process per GPU (b200_stream_comm_init)
     int          sq_world, sq_rank;
     unsigned long long * sq_peer[8];  // every rank's exchange buffer (peer-mapped), 2 * sq_peer_cap entries

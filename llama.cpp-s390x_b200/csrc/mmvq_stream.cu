@@ -170,37 +170,36 @@ __device__ __forceinline__ uint32_t sq_epoch(const uint32_t * done) {
     return e + 1;
 }
 
-// the sequence of (job, row pair, chunk) steps of one consumer warp.  Rows are walked in PAIRS (the activations are fetched once
-// for two rows).  pair_min (ctx option stream_pair_min, default 0) > 0 hands out single rows when a CTA owns at most that many rows
-// of a job, so that more warps work on a small matrix; measured SLOWER on B200 (Llama-3-8B step 0.78 -> 1.06 ms independent,
-// 1.67 -> 2.0 ms as a dependent chain): the kernel is instruction-issue-bound and a single-row step carries the same ring and
-// cursor overhead as a pair step.
+// the sequence of (job, row pair, chunk) steps of one consumer warp.  Rows are walked in PAIRS (2 p, 2 p + 1) — the activations are
+// fetched once for two rows and the two results go out as one aligned 16-byte store where they are exchanged — and the PAIRS of a
+// matrix are what is dealt to the CTAs: CTA b owns pairs [b base + min(b, rem), ... + base + (b < rem)); the last pair of a matrix
+// with an odd number of rows holds one row (flags bit 1).  (Single-row steps for matrices with few rows per CTA were measured
+// slower: the kernel is instruction-issue-bound and a single-row step carries the same ring and cursor overhead as a pair step.)
 struct sq_cursor {
     int      j;          // current job; == n_jobs: exhausted
-    uint32_t row;        // first row of the current step
-    uint32_t rhi;        // end of this CTA's rows of job j
+    uint32_t pair;       // current pair
+    uint32_t phi;        // end of this CTA's pairs of job j
     int      c, nch;     // next chunk, chunks per row
-    uint32_t rot;        // steps' worth of rows of the CTA dealt so far, mod SQ_NCW: unit p of job j goes to warp (rot + p) % SQ_NCW
-    uint32_t stride;     // rows per step of job j in this CTA (1 or 2)
+    uint32_t rot;        // pairs of the CTA dealt so far, mod SQ_NCW: pair p of job j goes to warp (rot + p) % SQ_NCW
 };
+
+__device__ __forceinline__ uint32_t sq_pairs(const sq_job & J, const uint32_t G) { return J.base * G + J.rem; }      // pairs of the matrix (shard)
+__device__ __forceinline__ uint32_t sq_rows(const sq_job & J, const uint32_t G) { return 2 * sq_pairs(J, G) - ((J.flags >> 1) & 1u); }
 
 __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, const uint32_t warp, const uint32_t b) {
     while (cu.j < P.n_jobs) {
         const sq_job & J = P.jobs[cu.j];
-        const uint32_t cnt    = J.base + (b < J.rem ? 1u : 0u);
-        const uint32_t stride = cnt > (uint32_t) P.pair_min ? 2u : 1u;
-        const uint32_t nunits = (cnt + stride - 1) / stride;
-        const uint32_t pos    = warp >= cu.rot ? warp - cu.rot : warp + SQ_NCW - cu.rot;
-        if (pos < nunits) {
-            const uint32_t rlo = b * J.base + (b < J.rem ? b : J.rem);
-            cu.row = rlo + stride * pos;
-            cu.rhi = rlo + cnt;
-            cu.c   = 0;
-            cu.nch = (J.nsb + SQ_CHUNK_SB - 1) / SQ_CHUNK_SB;
-            cu.stride = stride;
+        const uint32_t cnt = J.base + (b < J.rem ? 1u : 0u);
+        const uint32_t pos = warp >= cu.rot ? warp - cu.rot : warp + SQ_NCW - cu.rot;
+        if (pos < cnt) {
+            const uint32_t plo = b * J.base + (b < J.rem ? b : J.rem);
+            cu.pair = plo + pos;
+            cu.phi  = plo + cnt;
+            cu.c    = 0;
+            cu.nch  = (J.nsb + SQ_CHUNK_SB - 1) / SQ_CHUNK_SB;
             return;
         }
-        cu.rot = (cu.rot + nunits) % SQ_NCW;
+        cu.rot = (cu.rot + cnt) % SQ_NCW;
         cu.j++;
     }
 }
@@ -208,11 +207,11 @@ __device__ __forceinline__ void sq_seek(const sq_params & P, sq_cursor & cu, con
 __device__ __forceinline__ void sq_advance(const sq_params & P, sq_cursor & cu, const uint32_t warp, const uint32_t b) {
     if (++cu.c < cu.nch) return;
     cu.c = 0;
-    cu.row += cu.stride * SQ_NCW;
-    if (cu.row < cu.rhi) return;
+    cu.pair += SQ_NCW;
+    if (cu.pair < cu.phi) return;
     const sq_job & J = P.jobs[cu.j];
     const uint32_t cnt = J.base + (b < J.rem ? 1u : 0u);
-    cu.rot = (cu.rot + (cnt + cu.stride - 1) / cu.stride) % SQ_NCW;
+    cu.rot = (cu.rot + cnt) % SQ_NCW;
     cu.j++;
     sq_seek(P, cu, warp, b);
 }
@@ -264,20 +263,21 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         const uint32_t e_off = (uint32_t) (sbl * 8 + 2 * g) * 8;
 
         sq_cursor pc;                                     // producer cursor: S steps ahead of the consumer
-        pc.j = 0; pc.row = 0; pc.rhi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0; pc.stride = 1;
+        pc.j = 0; pc.pair = 0; pc.phi = 0; pc.c = 0; pc.nch = 1; pc.rot = 0;
         sq_seek(P, pc, (uint32_t) warp, cta);
         auto fill = [&](const int slot) {
             const sq_job & J = P.jobs[pc.j];
             const int      left  = (int) J.nsb - pc.c * SQ_CHUNK_SB;
             const uint32_t bytes = (uint32_t) (left < SQ_CHUNK_SB ? left : SQ_CHUNK_SB) * SZ_Q4_K;
-            const bool     two   = pc.stride == 2 && pc.row + 1 < pc.rhi;
+            const uint32_t prow  = 2 * pc.pair;
+            const bool     two   = prow + 1 < sq_rows(J, G);
             const bool     last  = pc.c + 1 == pc.nch;
-            const uint8_t * src  = J.W + ((size_t) pc.row + (MODE == 2 ? (size_t) er * (J.base * G + J.rem) : 0)) * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
+            const uint8_t * src  = J.W + ((size_t) prow + (MODE == 2 ? (size_t) er * sq_rows(J, G) : 0)) * J.nb01 + (size_t) pc.c * SQ_CHUNK_B;
             const uint32_t dst   = ring0 + (uint32_t) slot * SQ_SLOT_B;
             const uint32_t bar   = bar0 + 8 * slot;
             if (tc::elect_one()) {
                 const uint32_t m1 = (uint32_t) pc.j | ((uint32_t) pc.c << 16) | (two ? 1u << 30 : 0u) | (last ? 1u << 31 : 0u);
-                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(meta0 + 8 * slot), "r"(pc.row), "r"(m1) : "memory");
+                asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(meta0 + 8 * slot), "r"(prow), "r"(m1) : "memory");
                 tc::mbar_arrive_expect_tx(bar, two ? 2 * bytes : bytes);
                 bulk_g2s(dst, src, bytes, bar);
                 if (two) bulk_g2s(dst + SQ_CHUNK_B, src + J.nb01, bytes, bar);
@@ -368,10 +368,13 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                     // lane p delivers to rank p (the butterfly sum left sA / sB in every lane): one NVLink store per rank and row
                     if (lane < P.world) {
                         const uint32_t epoch = *s_epoch;
+                        // (row is even, row0 and ll_off are even: the pair's two words are one aligned 16-byte store — one NVLink
+                        // packet instead of two; each word is still its own indivisible {value, epoch})
                         unsigned long long * e = P.ll_peer[lane] + (size_t) (epoch & 1u) * P.ll_cap + J.ll_off + J.row0 + row +
-                                                 (MODE == 2 ? (size_t) er * (J.base * G + J.rem) : 0);
-                        asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sA)) : "memory");
-                        if (two) asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e + 1), "l"(((unsigned long long) epoch << 32) | __float_as_uint(sB)) : "memory");
+                                                 (MODE == 2 ? (size_t) er * sq_rows(J, G) : 0);
+                        const unsigned long long wA = ((unsigned long long) epoch << 32) | __float_as_uint(sA), wB = ((unsigned long long) epoch << 32) | __float_as_uint(sB);
+                        if (two) asm volatile("st.relaxed.sys.global.v2.b64 [%0], {%1, %2};" :: "l"(e), "l"(wA), "l"(wB) : "memory");
+                        else     asm volatile("st.relaxed.sys.global.b64 [%0], %1;" :: "l"(e), "l"(wA) : "memory");
                     }
                 } else if (lane == 0) {
                     J.Y[row] = sA;

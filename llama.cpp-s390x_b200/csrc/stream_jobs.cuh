@@ -18,18 +18,18 @@ struct sq_job {                 // 56 bytes
     const float *   X;          // k f32, 16-byte aligned
     float *         Y;          // m f32
     uint32_t nb01;              // row stride in bytes (multiple of 16)
-    uint32_t base;              // m / grid: CTA b owns rows [b * base + min(b, rem), ... + base + (b < rem))
+    uint32_t base;              // row PAIRS / grid: CTA b owns pairs [b * base + min(b, rem), ... + base + (b < rem)); pair p = rows 2p, 2p + 1
     uint32_t row0;              // row split (world > 1): W holds rows [row0, row0 + m) of a matrix of m_full rows; Y is the FULL-height vector
     uint32_t m_full;
     uint32_t ll_off;            // SQ_NO_LL, or: every result also goes, as {f32 bits, launch epoch} in one 8-byte word, to entry
                                 // ll_off + row of the exchange buffer — a later group of this launch reads its activations from there
-    uint16_t rem;               // m % grid
+    uint16_t rem;               // row pairs % grid
     uint16_t nsb;               // k / 256
     uint16_t xg;                // index of the job's activation group (consecutive jobs with the same X share one quantized copy)
     int16_t  dep;               // first job of a group: index of the LAST earlier job of this launch whose completion the group
                                 // has to wait for (hazards other than "X is exactly an earlier job's output"); -1 = none
     int16_t  xsrc;              // first job of a group: the earlier job whose exchange entries ARE this group's activations; -1 = read X
-    uint16_t flags;             // bit 0: a later group waits for this job -> completion is counted in done[job]
+    uint16_t flags;             // bit 0: a later group waits for this job -> completion is counted in done[job]; bit 1: odd number of rows
 };
 
 struct sq_params {
@@ -37,8 +37,7 @@ struct sq_params {
     int        kmax;            // largest k of the launch: an activation buffer holds kmax int8 + kmax / 32 float2
     int        stages;          // ring slots per warp (2..4)
     int        n_flagged;       // jobs with flags & 1
-    int        pair_min;        // a CTA with more rows of a job than this walks them in pairs, else one by one
-    int        _pad;
+    int        _pad[2];
     int        n_ll;            // jobs with an exchange region
     uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j), [SQ_MAX_JOBS] ticket, [SQ_MAX_JOBS + 1] launch
                                 // epoch; counters and ticket are zero between launches, the epoch counts the launches that used it

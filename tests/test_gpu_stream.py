@@ -72,10 +72,10 @@ def chain(pkg, ctx, ws, x0, bufs):
     return xs, outs
 
 
-@pytest.mark.parametrize("opts", [{}, {"stream_ll": 0}, {"stream_pair_min": 28}, {"stream_stages": 2}])
+@pytest.mark.parametrize("opts", [{}, {"stream_ll": 0}, {"stream_stages": 2}])
 def test_batch_dependent_chain_matches_sequential_calls(pkg, gpu_ctx, opts):
     """every job reads the previous job's output (RAW) and overwrites the buffer the one before read (WAR); with the dependency
-    carried in the data ({value, epoch} words, default), by completion counters only (stream_ll = 0), with single-row steps and
+    carried in the data ({value, epoch} words, default), by completion counters only (stream_ll = 0) and
     with two ring slots per warp"""
     import torch
     prev = {k: gpu_ctx.set_option(k, v) for k, v in opts.items()}
