@@ -781,7 +781,9 @@ static int stream_images(b200_ctx * ctx, sq_params & P) {
     // the images' places in the shared-memory ring of 2 x the largest image: bump allocation with wrap-around; a place can be
     // reused once every consumer warp has finished the groups that lay there
     {
-        const size_t ring = 2 * ((size_t) P.kmax + (size_t) P.kmax / 4);
+        P.stages = b200_gemv_stream_stages(ctx, P.kmax);
+        P.xring  = (unsigned) b200_gemv_stream_xring(ctx, P.stages > 0 ? P.stages : 2);
+        const size_t ring = P.xring;
         size_t off = 0;
         std::vector<int> live;                              // groups whose place has not been handed on, oldest first
         std::vector<size_t> lo((size_t) P.n_groups), hi((size_t) P.n_groups);
@@ -903,7 +905,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
     P.ll = ctx->sq_ll;
     if (const int rc = stream_images(ctx, P)) return rc;
     if (ctx->stream_trace) {
-        if (!ctx->sq_trace) B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_trace, (2 * SQ_MAX_JOBS * 4 + 128 * 32 * 5) * sizeof(unsigned long long)));
+        if (!ctx->sq_trace) B200_CUDA_TRY(cudaMalloc((void **) &ctx->sq_trace, 2 * SQ_MAX_JOBS * 4 * sizeof(unsigned long long)));
         P.trace = ctx->sq_trace;
     }
     // everything before this launch is complete when its CTAs pass griddepcontrol.wait (no deferred wait here)
@@ -913,7 +915,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
 
 // debugging aid, deliberately not in ggml_b200.h: copies the coordinator time stamps of the last traced launch (tools/stream_trace.py)
 extern "C" __attribute__((visibility("default"))) int b200_dbg_stream_trace(b200_ctx * ctx, unsigned long long * out, int n_words) {
-    if (!ctx || !ctx->sq_trace || !out || n_words > 2 * SQ_MAX_JOBS * 4 + 128 * 32 * 5) return B200_E_ARG;
+    if (!ctx || !ctx->sq_trace || !out || n_words > 2 * SQ_MAX_JOBS * 4) return B200_E_ARG;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     B200_CUDA_TRY(cudaMemcpy(out, ctx->sq_trace, (size_t) n_words * 8, cudaMemcpyDeviceToHost));

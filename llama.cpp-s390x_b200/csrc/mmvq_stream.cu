@@ -47,8 +47,6 @@ constexpr int OFF_CNT   = OFF_META + SQ_NCW * SQ_MAX_S * 8;          // [SQ_NCNT
 constexpr int OFF_X     = (OFF_CNT + SQ_NCNT * 4 + 127) / 128 * 128;
 
 __host__ __device__ constexpr int sq_xbytes(int kmax) { return kmax + kmax / 4; }
-__host__ __device__ constexpr int sq_ring_off(int kmax) { return (OFF_X + 2 * sq_xbytes(kmax) + 127) / 128 * 128; }
-__host__ __device__ constexpr size_t sq_smem(int kmax, int stages) { return (size_t) sq_ring_off(kmax) + (size_t) SQ_NCW * stages * SQ_SLOT_B; }
 
 __device__ __forceinline__ int act_slot(int t) { return t ^ (((t >> 3) & 1) << 1) ^ ((t >> 4) & 1); }     // as in mmvq.cu
 
@@ -253,7 +251,7 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
         // ================================================= consumer warp ================================================
         const uint32_t bar0  = sbase + OFF_FULL + (uint32_t) warp * SQ_MAX_S * 8;
         const uint32_t meta0 = sbase + OFF_META + (uint32_t) warp * SQ_MAX_S * 8;
-        const uint32_t ring0 = sbase + (uint32_t) sq_ring_off(P.kmax) + (uint32_t) (warp * S) * SQ_SLOT_B;
+        const uint32_t ring0 = sbase + (uint32_t) OFF_X + (uint32_t) P.xring + (uint32_t) (warp * S) * SQ_SLOT_B;
         const int sbl = lane >> 2, g = lane & 3;
         const int xsw = ((g >> 1) << 1) ^ (sbl & 1);
         // lane-constant byte offsets: weights inside a chunk, activations inside a chunk's 8 super-blocks
@@ -409,6 +407,8 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
             auto stamp = [&](const int g, const int what) {
                 if (tr) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tr[g * 4 + what] = t; }
             };
+            int known = 0;                                    // groups [0, known) have all their units in their images
+            const long long t_poll = clock64();
             for (int gidx = 0; gidx < P.n_groups; ++gidx) {
                 const int jq = P.gfirst[gidx];
                 const sq_job & J = P.jobs[jq];
@@ -417,20 +417,33 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
                 const int nbk = (int) J.nsb * 8, ub = sq_unit_blocks(nbk);
                 const int nunits = (nbk + ub - 1) / ub;
                 stamp(gidx, 0);
-                // every unit of the group has been announced with this launch's epoch (lane l watches units l and l + 32)
-                {
-                    const uint32_t * f = xflag + (size_t) gidx * 64;
-                    const long long t0 = clock64();
-                    for (int u = lane; u < nunits; u += 32) {
-                        uint32_t seen;
-                        while (true) {
-                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(f + u) : "memory");
-                            if (seen == epoch) break;
-                            __nanosleep(40);
-                            if (clock64() - t0 > 20000000000LL) __trap();
+                // every unit of the group has been announced with this launch's epoch.  The flags of FOUR groups are fetched per round
+                // trip (lane l watches units l and l + 32 of each): one acquire round trip per group was ~1 us x 129 groups, the
+                // floor of a step whose matrices are small (row shards)
+                while (known <= gidx) {
+                    uint32_t seen[4][2];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int gq = known + q < P.n_groups ? known + q : P.n_groups - 1;
+                        const int nbq = (int) P.jobs[P.gfirst[gq]].nsb * 8, nuq = (nbq + sq_unit_blocks(nbq) - 1) / sq_unit_blocks(nbq);
+                        const uint32_t * f = xflag + (size_t) gq * 64;
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            seen[q][h] = epoch;
+                            if (lane + 32 * h < nuq) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(seen[q][h]) : "l"(f + lane + 32 * h) : "memory");
                         }
                     }
-                    __syncwarp();
+                    uint32_t ok = 0;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) ok |= (seen[q][0] == epoch && seen[q][1] == epoch ? 1u : 0u) << q;
+                    ok = __reduce_and_sync(0xffffffffu, ok);
+                    int adv = 0;
+                    while (adv < 4 && ((ok >> adv) & 1u) && known + adv < P.n_groups) ++adv;
+                    if (adv) { known += adv; __threadfence(); }                  // (relaxed reads + fence = acquire: the images are visible)
+                    else {
+                        __nanosleep(40);
+                        if (clock64() - t_poll > 20000000000LL) __trap();
+                    }
                 }
                 stamp(gidx, 1);
                 // the image's place in the ring is free: every consumer warp has finished the groups that lay there (host-computed:
@@ -548,12 +561,21 @@ gemv_q4k_stream(const __grid_constant__ sq_params P) {
 
 }  // namespace
 
+// Shared-memory split: `stages` weight-ring slots per consumer warp (2: measured as fast as 3 on the full-size step, 0.788 vs 0.792 ms),
+// everything else is the ring of activation images — the deeper it is, the more groups the consumers may be spread over, which is
+// what bounds a step of SMALL matrices (row shards): one warp walks the 7 chunks of a k = 14336 row pair in ~5 us, and with two
+// image places only ~1.5 decoder layers were in flight (0.27 ms for the Llama-3-8B list at 1/8 of its rows, 3x its HBM time).
 int b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax) {
     if (kmax <= 0 || kmax % 256 != 0 || kmax > (1 << 20)) return 0;
-    for (int s = SQ_MAX_S; s >= 2; --s) {
-        if (sq_smem((int) kmax, s) <= ctx->smem_optin) return s > 3 ? 3 : s;     // (3 slots = 6.9 KB per warp already cover the latency)
-    }
-    return 0;
+    const int s = ctx->stream_stages >= 2 && ctx->stream_stages <= SQ_MAX_S ? ctx->stream_stages : 2;
+    const size_t rings = (size_t) SQ_NCW * s * SQ_SLOT_B;
+    if ((size_t) OFF_X + rings + 2 * (size_t) sq_xbytes((int) kmax) + 256 > ctx->smem_optin) return 0;       // at least two images of the longest vector
+    return s;
+}
+
+// bytes of the image ring for `stages` weight-ring slots: all the shared memory that is left (a multiple of 128)
+size_t b200_gemv_stream_xring(const b200_ctx * ctx, int stages) {
+    return (ctx->smem_optin - (size_t) OFF_X - (size_t) SQ_NCW * stages * SQ_SLOT_B) & ~(size_t) 127;
 }
 
 int b200_gemv_stream_grid(const b200_ctx * ctx) {
@@ -563,11 +585,11 @@ int b200_gemv_stream_grid(const b200_ctx * ctx) {
 int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
     if (P.n_jobs <= 0) return B200_OK;
     if (P.n_jobs > SQ_MAX_JOBS || P.n_groups < 1 || P.n_groups > P.n_jobs) { b200_set_error("gemv_stream: bad job table"); return B200_E_ARG; }
-    P.stages = ctx->stream_stages > 0 ? ctx->stream_stages : b200_gemv_stream_stages(ctx, P.kmax);
-    if (P.stages < 2 || P.stages > SQ_MAX_S || sq_smem(P.kmax, P.stages) > ctx->smem_optin) {
+    if (P.stages < 2 || P.stages > SQ_MAX_S || P.xring < 2 * (unsigned) sq_xbytes(P.kmax)) {
         b200_set_error("gemv_stream: k = %d does not fit the shared-memory rings", P.kmax); return B200_E_UNSUPPORTED;
     }
-    const size_t smem = sq_smem(P.kmax, P.stages);
+    const size_t smem = (size_t) OFF_X + P.xring + (size_t) SQ_NCW * P.stages * SQ_SLOT_B;
+    if (smem > ctx->smem_optin) { b200_set_error("gemv_stream: shared-memory budget exceeded"); return B200_E_UNSUPPORTED; }
     const bool multi = P.world > 1;
     const int  mode  = !multi ? 0 : P.emu_stride ? 2 : 1;
     auto kern = mode == 0 ? gemv_q4k_stream<0> : mode == 1 ? gemv_q4k_stream<1> : gemv_q4k_stream<2>;

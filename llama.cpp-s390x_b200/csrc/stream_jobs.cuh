@@ -35,9 +35,10 @@ struct sq_job {                 // 56 bytes
 struct sq_params {
     int        n_jobs, n_groups;
     int        kmax;            // largest k of the launch: an activation buffer holds kmax int8 + kmax / 32 float2
-    int        stages;          // ring slots per warp (2..4)
+    int        stages;          // weight-ring slots per consumer warp (2 or 3)
+    unsigned   xring;           // bytes of the shared-memory ring of activation images
     int        n_flagged;       // jobs with flags & 1
-    int        _pad[2];
+    int        _pad;
     int        n_ll;            // jobs with an exchange region
     uint32_t * done;            // [SQ_MAX_JOBS] completion counters (CTAs done with job j), [SQ_MAX_JOBS] ticket, [SQ_MAX_JOBS + 1] launch
                                 // epoch; counters and ticket are zero between launches, the epoch counts the launches that used it
@@ -64,7 +65,9 @@ struct sq_params {
 
 // host launcher (mmvq_stream.cu); P.jobs[0 .. n_jobs) filled, groups / deps / flags resolved by the caller
 int    b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P);
-// ring slots per warp that fit next to two activation buffers of kmax values (0: does not fit)
+// weight-ring slots per warp for a launch whose longest activation vector has kmax values (0: does not fit), and the bytes of
+// the image ring that go with it
 int    b200_gemv_stream_stages(const b200_ctx * ctx, int64_t kmax);
+size_t b200_gemv_stream_xring(const b200_ctx * ctx, int stages);
 // CTAs of a launch on this context (the job table's base / rem fields are computed for this grid)
 int    b200_gemv_stream_grid(const b200_ctx * ctx);

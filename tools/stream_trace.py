@@ -12,9 +12,11 @@ import bench
 pkg = load_package()
 mode = sys.argv[1] if len(sys.argv) > 1 else "chain"
 ll = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+div = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 stream = torch.cuda.Stream()
 ctx = pkg.Context(0, stream=stream.cuda_stream)
 ctx.set_option("stream_ll", ll)
+ctx.set_option("stream_chain", 1); ctx.set_option("stream_min_jobs", 1)
 gen = torch.Generator(device="cuda"); gen.manual_seed(1)
 NL = 8
 T = {n: (m, k) for n, m, k, _ in bench.LLAMA3_8B}
@@ -28,6 +30,7 @@ ws, xs, ys, names = [], [], [], []
 for l in range(NL):
     for n in ("wq", "wk", "wv", "wo", "ffn_gate", "ffn_up", "ffn_down"):
         m, k = T[n]
+        m //= div
         ws.append(bench.device_random_q4k(torch, m, k, gen))
         if mode == "chain":
             xs.append(wire[n][0]); ys.append(wire[n][1])
@@ -44,12 +47,11 @@ with torch.cuda.stream(stream):
     batch.run(ctx)
     stream.synchronize()
 n_groups = 4 * NL
-buf = np.zeros(2 * 512 * 4 + 128 * 32 * 5, np.uint64)
+MAXJ = 448
+buf = np.zeros(2 * MAXJ * 4, np.uint64)
 rc = pkg.lib().b200_dbg_stream_trace(ctx.handle, buf.ctypes.data_as(C.c_void_p), buf.size)
 assert rc == 0, rc
-tr = buf[:2 * 512 * 4].reshape(2, 512, 4).astype(np.int64)
-units = buf[2 * 512 * 4: 2 * 512 * 4 + 128 * 32 * 3].reshape(128, 32, 3).astype(np.int64)
-enter = buf[2 * 512 * 4 + 128 * 32 * 3:].reshape(128, 32, 2).astype(np.int64)
+tr = buf.reshape(2, MAXJ, 4).astype(np.int64)
 t0 = tr[0, 0, 0]
 gn = ["qkv", "wo", "gate_up", "down"]
 print(f"mode={mode} stream_ll={ll}  (ns; CTA 0 | last CTA)  group: coordinator start, +flags seen, +copy issued, +image in shared memory   group-to-group")
