@@ -162,7 +162,9 @@ def prefill_bench(torch, pkg, ctx, stream, n=512):
     sum; reported against the measured dense 16-bit tensor peak because the MMA runs kind::f16 with fp32 accumulation."""
     gen = torch.Generator(device="cuda"); gen.manual_seed(99)
     peak, src = tensor_peak()
-    out = {"n_tokens": n, "tensor_peak_tflops": peak, "peak_source": src, "mma": "tcgen05.mma.kind::f16 (fp16 x fp16 -> fp32 in TMEM)"}
+    out = {"n_tokens": n, "tensor_peak_tflops": peak, "peak_source": src, "mma": "tcgen05.mma.kind::f16 (fp16 x fp16 -> fp32 in TMEM)",
+           "int8_peak_measured_tops": 4551.0, "f16_issue_peak_measured_tflops": 2124.0,
+           "int8_peak_source": "tools/tc_rate.cu on this pool's B200 (profiles/r02_tc_rate.txt): tcgen05.mma kind::i8 8190 MAC/clk/SM, kind::f16 4095; why the product path is kind::f16: DESIGN.md section 7"}
     shapes = {}
     for (m, k) in sorted({(m, k) for _, m, k, _ in LLAMA3_8B}):
         shapes[(m, k)] = sum(c for _, mm, kk, c in LLAMA3_8B if (mm, kk) == (m, k))
