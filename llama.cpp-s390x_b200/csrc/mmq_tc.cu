@@ -1,24 +1,35 @@
-// mmq_tc.cu — prefill path (n > 8): tensor-core GEMM on tcgen05 with TMEM accumulators.
+// mmq_tc.cu — prefill path (n > 8): tensor-core GEMM on tcgen05 with the accumulators AND the weight operand in tensor memory.
 //
 // Replaces, for large n, the reference's per-column vec_dot loop (ggml/src/ggml-cpu/ggml-cpu.c:1151-1439) and plays the
 // role of ggml-cuda's mul_mat_q / cuBLAS branch (ggml/src/ggml-cuda/mmq.cuh:3446-3783, ggml-cuda.cu:1413-1530) — designed
 // from the hardware up, not from those kernels:
-//   * persistent CTAs; D[128 weight rows x NT activation columns] per tile, fp32 accumulator in TMEM, two accumulators so
-//     the epilogue of one tile overlaps the main loop of the next;
-//   * the weight tile (A operand) never exists in HBM in expanded form: TMA streams the RAW quant blocks (a box of
-//     128 rows x 144 bytes) into a shared-memory ring, 8 converter warps dequantise them to fp16 (exact integer -> fp16
-//     conversion by exponent-bias tricks, then ONE rounding in `q * scale - min`) and store them straight into the
-//     128-byte-swizzled K-major UMMA layout;
-//   * the activation tile (B operand) is fetched by TMA from an fp16 copy of src1 that `tc_act_f16_kernel` writes once per
-//     call (per-column power-of-two normalisation so neither overflow nor fp16 underflow can occur; undone exactly in
-//     the epilogue).  Within every 4 consecutive K elements both operands use the order (0,2,1,3), which is what nibble
-//     unpacking produces for free — a dot product does not care;
-//   * warp roles: 0-7 converters, 8 TMA, 9 MMA issue, 10-13 epilogue (tcgen05.ld -> scale -> coalesced f32 stores, or the
-//     MUL_MAT_ID scatter); three mbarrier rings (raw weights, A tiles, B tiles).
+//   * persistent CTAs; D[128 weight rows x up to 192 activation columns] per tile, fp32 accumulator in TMEM, two accumulators
+//     so the epilogue of one tile overlaps the main loop of the next;
+//   * the weight tile (A operand) never exists in HBM in expanded form, and not in shared memory either: TMA streams the RAW
+//     quant blocks (a box of 128 rows x 144 bytes) into a shared-memory ring, 8 converter warps dequantise them to fp16 (exact
+//     integer -> fp16 conversion by exponent-bias tricks, then ONE rounding in `q * scale - min`) and write them with
+//     tcgen05.st into a 4-stage ring of TENSOR MEMORY columns (thread = tile row = TMEM lane, 32 columns = 64 K elements); the
+//     MMA takes A from there (`tcgen05.mma [d], [a_tmem], b_desc`).  Round 1 kept A in shared memory: 16 KB written + 16 KB read
+//     per 64-K stage out of ~107 KB of shared-memory traffic, which is what bounded that kernel (836 clocks per stage against
+//     512 of MMA time); tools/tc_ts_probe.cu checks the TMEM operand layout and shows the MMA keeps its full rate from it;
+//   * the activation tile (B operand) is fetched by TMA (boxes of 64 columns x 64 K) from an fp16 copy of src1 that
+//     `tc_act_f16_kernel` writes once per call (per-column power-of-two normalisation so neither overflow nor fp16 underflow
+//     can occur; undone exactly in the epilogue).  Within every 4 consecutive K elements both operands use the order
+//     (0,2,1,3), which is what nibble unpacking produces for free — a dot product does not care;
+//   * tiles are as wide as their valid columns: the MMA's N is the tile's column count rounded up to 16 and only the boxes that
+//     hold valid columns are fetched, so a ragged last tile or a MUL_MAT_ID expert with few tokens costs what it uses;
+//   * warp roles: 0-11 converters (three groups of four, a group takes every third stage), 12 activation TMA, 13 MMA issue, 14-17
+//     epilogue (tcgen05.ld -> scale -> coalesced f32 stores, or the MUL_MAT_ID scatter), 18 weight TMA (its own warp: the raw ring
+//     holds 16 stages and must run that far ahead — HBM latency — while the activation ring holds 6; one warp serving both in
+//     program order let the raw blocks arrive late, ncu: 26 % of the converters' time in the raw-slot wait); mbarrier rings:
+//     raw weights, A stages (TMEM), B tiles, accumulators.  The converters are what the stage rate hangs on (ncu source page, profiles/): ~290 instructions
+//     per warp and stage in a mostly serial chain, so the third group is what keeps the A ring ahead of the MMA warp.
 // Numerics: fp16 operands (2^-12 relative) + fp32 accumulation — closer to the exact product than the reference's own
-// Q8_1 activation quantisation; NMSE vs ggml-cpu ~1.5e-5 (that IS the Q8_1 noise), far inside test-backend-ops' 5e-4.
+// Q8_1 activation quantisation; NMSE vs ggml-cpu ~1.5e-5 (that IS the Q8_1 noise), far inside test-backend-ops' 5e-4.  The sum
+// over K of one output element is formed in the same order whatever the tile width, so results do not depend on the tiling.
 #include <cuda.h>
 #include <cuda_fp16.h>
+#include <atomic>
 #include <cstdio>
 
 #include "mm_problem.cuh"
@@ -26,28 +37,29 @@
 
 namespace {
 
-constexpr int TC_M        = 128;     // weight rows per CTA tile (UMMA M)
-constexpr int TC_KS       = 64;      // K elements per MMA stage (one 128-byte swizzled row of fp16)
-constexpr int TC_A_BYTES  = TC_M * 128;
+constexpr int TC_M        = 128;     // weight rows per CTA tile (UMMA M) = TMEM lanes
+constexpr int TC_KS       = 64;      // K elements per MMA stage (one 128-byte swizzled row of fp16 B; 32 TMEM columns of A)
+constexpr int TC_NT_MAX   = 192;     // widest tile: 2 accumulators x 192 columns + the A ring = the 512 TMEM columns
+constexpr int TC_A_SLOTS  = 4;       // A stages in tensor memory
+constexpr int TC_A_COL0   = 2 * TC_NT_MAX;
+constexpr int TC_A_COLS   = TC_KS / 2;
+constexpr int TC_B_BOX    = 64;      // activation columns per TMA box
+constexpr int TC_B_BOX_BYTES = TC_B_BOX * 128;
+constexpr int TC_B_BYTES  = TC_NT_MAX * 128;
 constexpr int TC_RAW_ROW  = 144;     // bytes of raw blocks per row and raw slot (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 + pad)
-constexpr int TC_RAW_BYTES = TC_M * TC_RAW_ROW;
-constexpr int TC_THREADS  = 512;     // 8 converter warps, TMA warp, MMA warp, 4 epilogue warps, 2 spare (whole warpgroups)
-constexpr int TC_A_SLOTS  = 3, TC_RAW_SLOTS = 2;
+constexpr int TC_CONV_GROUPS = 3;    // converter groups of 4 warps (one warp per TMEM lane quadrant); group g takes every 3rd stage
+constexpr int TC_CONV_WARPS  = 4 * TC_CONV_GROUPS;
+constexpr int TC_W_TMA = TC_CONV_WARPS, TC_W_MMA = TC_CONV_WARPS + 1, TC_W_EPI = TC_CONV_WARPS + 2, TC_W_RAW = TC_CONV_WARPS + 6;   // warp roles
+constexpr int TC_THREADS  = 32 * (TC_CONV_WARPS + 7);   // 12 converter warps, activation-TMA warp, MMA warp, 4 epilogue warps, weight-TMA warp
+static_assert(TC_A_COL0 + TC_A_SLOTS * TC_A_COLS <= 512, "accumulators and the A ring must fit the 512 TMEM columns");
 
-// PAIR: two CTAs (one per SM of a TPC) share one 256-row x NT tile: each converts its own 128 rows of A and holds HALF of
-// the activation tile; the tensor cores of both SMs read both halves, so the B traffic per SM (TMA fill + operand read) halves.
 // RAW_ROW: bytes per row and raw slot — 144 (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 blocks + pad) or 224 (Q6_K: one 210-byte
-// super-block + pad; the wider raw ring is paid for with one activation slot)
-template <int NT, bool PAIR = false, int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
-    static constexpr int B_ROWS  = PAIR ? NT / 2 : NT;          // activation columns in this CTA's shared memory
-    static constexpr int B_SLOTS = (PAIR ? (NT == 256 ? 6 : 8) : (NT == 256 ? 4 : 6)) - (RAW_ROW > TC_RAW_ROW ? 1 : 0);
-    static constexpr int B_BYTES = B_ROWS * 128;
+// super-block + pad; the wider raw ring is paid for with one activation slot and one raw slot)
+template <int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
+    static constexpr int B_SLOTS   = RAW_ROW > TC_RAW_ROW ? 5 : 6;
+    static constexpr int RAW_SLOTS = RAW_ROW > TC_RAW_ROW ? 3 : 4;
     static constexpr int RAW_BYTES = TC_M * RAW_ROW;
-    // CTA pair: the halved activation tile pays for a deeper A ring — "A tile ready" now waits for the converters of two SMs and a
-    // remote arrive, which 3 slots (2 MMA stages of slack) do not cover
-    static constexpr int A_SLOTS = PAIR ? (RAW_ROW > TC_RAW_ROW ? 4 : 5) : TC_A_SLOTS;
-    static constexpr int SMEM    = B_SLOTS * B_BYTES + A_SLOTS * TC_A_BYTES + TC_RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
-    static_assert(2 * NT <= 512, "two accumulators must fit the 512 TMEM columns");
+    static constexpr int SMEM      = B_SLOTS * TC_B_BYTES + RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 512 /*barriers*/;
     static_assert(SMEM <= 232448, "exceeds the 227 KB a CTA can opt into");
 };
 
@@ -66,6 +78,8 @@ struct tc_args {
     int64_t nb01, nb02, nb03;
     int     m, k;
     int     n;                  // activation columns per batch
+    int     nt;                 // tile width in columns (64, 128 or 192); the last tile of a row of tiles may be narrower
+    int     col_tiles;          // MM_PLAIN: tiles per batch along n
     int     ne12, r2, r3;       // batch dims (MM_PLAIN)
     int     ne02;               // weight matrices per ne03 slice
     int     raw_step;           // 16-bit elements of a weight row per raw slot (row bytes of raw_k K elements / 2)
@@ -199,6 +213,11 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
         hdr = lds_u4(row);
         q   = lds_u4(row + 16 + 32 * sub + 16 * h);
     }
+    // both halves of a row's stage: one header load (the scale / min work of the two halves is then common code)
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) {
+        f0.hdr = lds_u4(row); f1.hdr = f0.hdr;
+        f0.q = lds_u4(row + 16 + 32 * sub); f1.q = lds_u4(row + 16 + 32 * sub + 16);
+    }
     // 4 chunks of 8 fp16; chunk slot indices within the 128-byte row returned in `slot`
     __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const int g = sub;
@@ -240,6 +259,7 @@ template <> struct w_frag<B200_TYPE_Q4_0> {
 #pragma unroll
         for (int j = 0; j < 5; ++j) w[j] = lds_u32(b + 4 * j);
     }
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
     __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
         const __half2 k1032 = h2_const(1032.0f), sixteenth = h2_const(0.0625f), m72 = h2_const(-72.0f);
@@ -270,6 +290,7 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
 #pragma unroll
         for (int j = 0; j < 9; ++j) w[j] = lds_u32(b + 4 * j);
     }
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
     __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
         const __half2 k1152 = h2_const(1152.0f);
@@ -309,6 +330,7 @@ template <> struct w_frag<B200_TYPE_Q6_K> {
         asm volatile("ld.shared.u16 %0, [%1];" : "=r"(sc) : "r"(row + 192 + 8 * n + 2 * r));
         asm volatile("ld.shared.u16 %0, [%1];" : "=r"(d)  : "r"(row + 208));
     }
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
     __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
         const int r = 2 * (sub & 1) + h, shl = 4 * (sub & 1), shh = 2 * r;
         const float df = __half2float(__ushort_as_half((unsigned short) d));
@@ -336,9 +358,10 @@ template <> struct w_frag<B200_TYPE_Q6_K> {
 
 
 // ---- the GEMM ---------------------------------------------------------------------------------------------------------
-// Persistent: CTA c works on tiles c, c + gridDim.x, ...  (row tile fastest, so CTAs running together share an activation
-// tile in L2).  All roles walk the same tile list and the same running stage counter, so ring slots and mbarrier phases
-// carry over from one tile to the next.
+// Persistent: CTA c works on tiles c, c + gridDim.x, ...  MUL_MAT: column tile fastest — the CTAs that run together then work on
+// the column tiles of the same few row tiles, so a weight tile is read from HBM once and the other readers hit L2 (the fp16
+// activations, a few MB, stay L2-resident anyway).  All roles walk the same tile list and the same running stage counter, so ring
+// slots and mbarrier phases carry over from one tile to the next.
 struct tc_tile {
     int mat;            // weight matrix index (batch / expert) = 3rd TMA coordinate
     int row0, pos0, nvalid;
@@ -347,24 +370,29 @@ struct tc_tile {
     float * Y;
 };
 
-// tm = weight rows per work tile (128, or 256 for a CTA pair: CTA `rank` of the pair owns rows [128 * rank, 128 * rank + 128) of it)
 // (32-bit arithmetic throughout: the host refuses launches with 2^31 or more work items, and 64-bit divisions here sat in front of
 //  the first TMA of every CTA — 1.4 us of a 11 us launch in the phase trace)
-__device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, uint32_t T, tc_tile & t, const int tm = TC_M, const int rank = 0) {
-    const uint32_t row_tiles = (uint32_t) (a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + tm - 1) / tm);
-    int rt = (int) (T % row_tiles);
-    T /= row_tiles;
+__device__ __forceinline__ bool tc_resolve(const tc_args & a, uint32_t T, tc_tile & t) {
+    const uint32_t row_tiles = (uint32_t) (a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + TC_M - 1) / TC_M);
+    const int NT = a.nt;
+    int rt, ct = 0, batch = 0;
+    if (a.mode == MM_PLAIN) {
+        const uint32_t col_tiles = (uint32_t) a.col_tiles;
+        if (col_tiles > 1) { ct = (int) (T % col_tiles); T /= col_tiles; }
+        rt = (int) (T % row_tiles);
+        batch = (int) (T / row_tiles);
+    } else {
+        rt = (int) (T % row_tiles);
+        ct = (int) (T / row_tiles);
+    }
     t.wsel = 0; t.m = a.m; t.Y = a.Y;
     if (a.n_mats > 1) {
         const int j = (rt >= a.rt_end[0]) + (rt >= a.rt_end[1]);
         rt -= j == 0 ? 0 : a.rt_end[j - 1];
         t.wsel = j; t.m = a.m_j[j]; t.Y = a.Y_j[j];
     }
-    t.row0 = rt * tm + TC_M * rank;
+    t.row0 = rt * TC_M;
     if (a.mode == MM_PLAIN) {
-        const uint32_t col_tiles = (uint32_t) ((a.n + NT - 1) / NT);
-        int ct, batch;
-        if (col_tiles == 1) { ct = 0; batch = (int) T; } else { ct = (int) (T % col_tiles); batch = (int) (T / col_tiles); }
         int i12 = 0, i13 = 0;
         t.mat = 0;
         if (batch > 0 || a.ne12 > 1) {                   // (a plain 2-D matmul has nothing to divide)
@@ -375,7 +403,7 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, const int NT, uint
         t.nvalid = min(NT, a.n - ct * NT);
         return true;
     }
-    int ct = (int) T, e = 0, lo = 0, hi = 0;
+    int e = 0, lo = 0, hi = 0;
     for (; e < a.n_expert; ++e) {
         lo = __ldg(a.expert_bounds + e);
         hi = __ldg(a.expert_bounds + e + 1);
@@ -400,19 +428,16 @@ struct tc_seg {
 
 struct tc_walker {
     uint32_t w;             // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
-    int      stride, tm, rank;
+    int      stride;
 
-    // pair = false: one CTA per work item; true: the two CTAs of a cluster walk the same items (256-row tiles)
-    __device__ __forceinline__ tc_walker(const tc_args &, const bool pair = false, const int cta_rank = 0) {
-        w = pair ? blockIdx.x >> 1 : blockIdx.x; stride = pair ? gridDim.x >> 1 : gridDim.x; tm = pair ? 2 * TC_M : TC_M; rank = cta_rank;
-    }
+    __device__ __forceinline__ tc_walker() { w = blockIdx.x; stride = gridDim.x; }
 
-    __device__ __forceinline__ bool next(const tc_args & a, const int NT, tc_seg & s) {
+    __device__ __forceinline__ bool next(const tc_args & a, tc_seg & s) {
         const uint32_t n_tiles = (uint32_t) a.n_tiles, n_items = n_tiles * (uint32_t) a.split_k;
         for (; w < n_items; w += stride) {
             const uint32_t part = a.split_k == 1 ? 0u : w / n_tiles;
             s.T = w - part * n_tiles;
-            if (tc_resolve(a, NT, s.T, s.t, tm, rank)) {
+            if (tc_resolve(a, s.T, s.t)) {
                 const int len = a.k / TC_KS / a.split_k;
                 s.k0 = (int) part * len; s.k1 = s.k0 + len;
                 s.order = (int) part; s.nparts = a.split_k;
@@ -425,7 +450,7 @@ struct tc_walker {
 };
 
 #ifdef TC_TRACE_ENABLE     // development aid: per-stage clock64 stamps of CTA 0 (build with -DTC_TRACE_ENABLE, run tools/tc_trace.py)
-__device__ long long g_tc_trace[6][128];
+__device__ long long g_tc_trace[12][128];
 #define TC_TRACE(role, gg) do { if (blockIdx.x == 0 && (gg) < 128) g_tc_trace[role][gg] = clock64(); } while (0)
 __device__ unsigned long long g_tc_phase[8];          // %globaltimer stamps of CTA 0: where a short GEMM spends its fixed cost
 #define TC_PHASE(i, once) do { if (blockIdx.x == 0 && (once)) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_tc_phase[i] = t_; } } while (0)
@@ -434,23 +459,18 @@ __device__ unsigned long long g_tc_phase[8];          // %globaltimer stamps of 
 #define TC_PHASE(i, once) do { } while (0)
 #endif
 
-template <int TYPE, int NT, bool PAIR>
+template <int TYPE>
 __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1,
                                                                    const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmB,
                                                                    const tc_args a) {
-    using cfg = tc_cfg<NT, PAIR, raw_row<TYPE>::value>;
+    using cfg = tc_cfg<raw_row<TYPE>::value>;
     constexpr int RAW_ROW = raw_row<TYPE>::value, RAW_BYTES = cfg::RAW_BYTES;
-    // CTA pair: rank 0 is the leader — it issues the MMAs, and the barriers "operands ready" (A full, B full) and "accumulator
-    // drained" that gate them live in ITS shared memory; the peer's warps arrive there remotely.  "Slot free" and "accumulator
-    // ready" barriers are per CTA, signalled in both by multicast commits.
-    const uint32_t cta_rank = PAIR ? tc::cluster_ctarank() : 0u;
-    constexpr int BS  = cfg::B_SLOTS, AS = cfg::A_SLOTS, RS = TC_RAW_SLOTS;
+    constexpr int BS  = cfg::B_SLOTS, AS = TC_A_SLOTS, RS = cfg::RAW_SLOTS;
     constexpr int SPR = raw_k<TYPE>::value / TC_KS;          // MMA stages per raw slot
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sB   = base;
-    const uint32_t sA   = sB + BS * cfg::B_BYTES;
-    const uint32_t sRaw = sA + AS * TC_A_BYTES;
+    const uint32_t sRaw = sB + BS * TC_B_BYTES;
     const uint32_t sBar = sRaw + RS * RAW_BYTES;
     const uint32_t bBFull = sBar, bBEmpty = bBFull + 8 * BS, bAFull = bBEmpty + 8 * BS, bAEmpty = bAFull + 8 * AS;
     const uint32_t bRFull = bAEmpty + 8 * AS, bREmpty = bRFull + 8 * RS, bAccFull = bREmpty + 8 * RS, bAccEmpty = bAccFull + 16;
@@ -459,26 +479,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     TC_PHASE(0, tid == 0);
 
-    if (warp == 8) {
+    if (warp == TC_W_TMA) {
         if (lane == 0) {
             tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
-            constexpr int NC = PAIR ? 2 : 1;     // CTAs whose warps arrive on the leader's barriers
             for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
-            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4 * NC); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) per CTA / commit
-            for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 8); }   // expect_tx / 8 converter warps
-            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4 * NC); } // commit / 4 epilogue warps per CTA
+            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) / commit
+            for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 4 * SPR); }   // expect_tx / 4 converter warps per stage of the slot
+            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4); } // commit / 4 epilogue warps
             tc::mbar_fence_init();
         }
         __syncwarp();
-        if (PAIR) tc::tmem_alloc2(sTmem, 2 * NT); else tc::tmem_alloc(sTmem, 2 * NT);
+        tc::tmem_alloc(sTmem, 512);
     }
     tc::tc_fence_before();
-    if (PAIR) tc::cluster_sync(); else __syncthreads();
+    __syncthreads();
     tc::tc_fence_after();
-    // where this CTA's warps report "A tile written" / "accumulator drained": the leader's barriers
-    const uint32_t rAFull = PAIR ? tc::mapa_u32(bAFull, 0) : bAFull, rAccEmpty = PAIR ? tc::mapa_u32(bAccEmpty, 0) : bAccEmpty;
-    const uint32_t rBFull = PAIR ? tc::mapa_u32(bBFull, 0) : bBFull;
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
     TC_PHASE(1, tid == 0);
@@ -488,58 +504,59 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
 
     // Ring positions are kept as (slot, phase) pairs advanced by hand: the single-thread roles below are latency chains,
     // so no divisions and no 64-bit arithmetic inside the stage loops.
-    if (warp < 8) {
-        // ===== converters: raw blocks (smem) -> fp16 -> swizzled K-major A tile ===========================================
-        // Two groups of 4 warps take alternate stages, so two stages are being converted at any time (one stage's
-        // store -> fence -> arrive latency hides behind the other's arithmetic).  A warp owns 32 rows of its stage: every lane
-        // two (row, half) tasks, adjacent lanes sharing a row.
-        const int grp = warp >> 2, h = lane & 1;
-        const int r0 = 32 * (warp & 3) + (lane >> 1), r1 = r0 + 16;
-        const uint32_t raw_row0 = sRaw + (uint32_t) (r0 * RAW_ROW), raw_row1 = sRaw + (uint32_t) (r1 * RAW_ROW);
-        const uint32_t a_row0 = sA + (uint32_t) ((r0 >> 3) * 1024 + (r0 & 7) * 128), a_row1 = sA + (uint32_t) ((r1 >> 3) * 1024 + (r1 & 7) * 128);
-        const int sw = r0 & 7;                                // r1 & 7 is the same
-        int as = 0, rs = 0, sub = 0;
+    if (warp < TC_CONV_WARPS) {
+        // ===== converters: raw blocks (smem) -> fp16 -> A stage in tensor memory =============================================
+        // Three groups of 4 warps take the stages in turn, so three stages are being converted at any time (a stage is a long,
+        // mostly serial instruction chain for one warp).  A warp owns the 32 rows of its TMEM lane quadrant (warp index mod 4); a
+        // thread converts the 64 K elements of ITS row of the stage (two 32-element halves) and writes them as 32 columns.
+        const int grp = warp >> 2, q = warp & 3;
+        const uint32_t raw_row_a = sRaw + (uint32_t) ((32 * q + lane) * RAW_ROW);
+        const uint32_t ta = tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) TC_A_COL0;
+        int as = 0, rs = 0, sub = 0, turn = 0;            // turn: which group the next stage belongs to (runs on across tiles)
         uint32_t a_ph = 0, r_ph = 0;
         int tg = 0; (void) tg;
-        tc_walker wk(a, PAIR, cta_rank);
+        tc_walker wk;
         tc_seg sg;
-        while (wk.next(a, NT, sg)) {
+        while (wk.next(a, sg)) {
             // TMA needs 16-byte aligned global addresses: Q8_0's odd raw slots (136-byte steps) are fetched 8 bytes early, Q6_K's
             // slot i (210-byte steps) 2 (i mod 8) bytes early; the converters skip the skew
             int sbi = sg.k0 / SPR;
             uint32_t skew = raw_skew<TYPE>(sbi);
             for (int it = sg.k0; it < sg.k1; ++it) {
-                if ((it & 1) == grp) {                        // segments start at even stages, so parity follows `it`
-                    // first stage of this group in the raw slot: sub == grp (SPR is even)
-                    if (sub == grp) tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
+                if (turn == grp) {
+                    tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
                     TC_PHASE(3, tid == 0 && tg == 0);
+                    if (tid == 0) TC_TRACE(6, tg);
                     w_frag<TYPE> f0, f1;
-                    uint4 o0[4], o1[4]; int slot[4];
-                    f0.load(raw_row0 + rs * RAW_BYTES + skew, sub, h);
-                    f1.load(raw_row1 + rs * RAW_BYTES + skew, sub, h);
-                    f0.convert(sub, h, o0, slot);
-                    f1.convert(sub, h, o1, slot);
-                    tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
-                    if (tid == 0) TC_TRACE(2, tg);
-                    const uint32_t off = as * TC_A_BYTES;
+                    uint4 o0[4], o1[4]; int s0[4], s1[4];
+                    w_frag<TYPE>::load_row(f0, f1, raw_row_a + rs * RAW_BYTES + skew, sub);
+                    f0.convert(sub, 0, o0, s0);
+                    f1.convert(sub, 1, o1, s1);
+                    // chunk s of the row (K elements 8 s .. 8 s + 7 of the stage) = columns 4 s .. 4 s + 3 (the slots are
+                    // compile-time constants once the half is)
+                    uint32_t v[32];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        const uint32_t chunk = (uint32_t) ((slot[c] ^ sw) << 4);
-                        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_row0 + off + chunk),
-                                     "r"(o0[c].x), "r"(o0[c].y), "r"(o0[c].z), "r"(o0[c].w) : "memory");
-                        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_row1 + off + chunk),
-                                     "r"(o1[c].x), "r"(o1[c].y), "r"(o1[c].z), "r"(o1[c].w) : "memory");
+                        v[4 * s0[c]] = o0[c].x; v[4 * s0[c] + 1] = o0[c].y; v[4 * s0[c] + 2] = o0[c].z; v[4 * s0[c] + 3] = o0[c].w;
+                        v[4 * s1[c]] = o1[c].x; v[4 * s1[c] + 1] = o1[c].y; v[4 * s1[c] + 2] = o1[c].z; v[4 * s1[c] + 3] = o1[c].w;
                     }
-                    tc::fence_proxy_async();
+                    if (tid == 0) TC_TRACE(7, tg);
+                    tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
+                    tc::tc_fence_after();
+                    if (tid == 0) TC_TRACE(2, tg);
+                    tc::tmem_st32(ta + (uint32_t) (as * TC_A_COLS), v);
+                    tc::tmem_st_wait();
+                    tc::tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        if (PAIR) tc::mbar_arrive_cluster(rAFull + 8 * as); else tc::mbar_arrive(bAFull + 8 * as);
-                        if (sub == SPR - 2 + grp) tc::mbar_arrive(bREmpty + 8 * rs);    // this warp's last stage in the raw slot
+                        tc::mbar_arrive(bAFull + 8 * as);
+                        tc::mbar_arrive(bREmpty + 8 * rs);
                         if (warp == 0) TC_TRACE(3, tg);
                         if (warp == 7) TC_TRACE(5, tg);
                     }
                 }
                 ++tg;
+                if (++turn == TC_CONV_GROUPS) turn = 0;
                 if (++as == AS) { as = 0; a_ph ^= 1; }
                 if (++sub == SPR) {
                     sub = 0;
@@ -548,104 +565,109 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 }
             }
         }
-    } else if (warp == 8) {
-        // ===== TMA: raw weight blocks and activation tiles (whole warp in step, one elected lane issues) ===================
-        {
-            int bs = 0, rs = 0, sub = 0;
-            uint32_t b_ph = 0, r_ph = 0;
-            int tg = 0; (void) tg;
-            tc_walker wk(a, PAIR, cta_rank);
-            tc_seg sg;
-            while (wk.next(a, NT, sg)) {
-                const tc_tile & t = sg.t;
-                int sbi = sg.k0 / SPR, x = sbi * a.raw_step;                     // next raw slot in the row (16-bit elements)
-                for (int it = sg.k0; it < sg.k1; ++it) {
-                    if (sub == 0) {
-                        tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1, 100);
-                        if (tc::elect_one()) {
-                            tc::mbar_arrive_expect_tx(bRFull + 8 * rs, RAW_BYTES);
-                            const CUtensorMap * tw = t.wsel == 0 ? &tmW : (t.wsel == 1 ? &tmW1 : &tmW2);
-                            TC_PHASE(2, tg == 0);
-                            tc::tma_load_3d(sRaw + rs * RAW_BYTES, tw, bRFull + 8 * rs, x - (int) (raw_skew<TYPE>(sbi) >> 1), t.row0, t.mat);
-                        }
-                        __syncwarp();
-                        x += a.raw_step; ++sbi;
-                    }
-                    tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
-                    if (lane == 0) TC_TRACE(4, tg);
-                    ++tg;
-                    if (tc::elect_one()) {
-                        if (PAIR) {
-                            // both halves of the activation tile report to the leader's barrier (it expects the bytes of both)
-                            if (cta_rank == 0) tc::mbar_arrive_expect_tx(bBFull + 8 * bs, 2 * cfg::B_BYTES);
-                            tc::tma_load_2d_2cta(sB + bs * cfg::B_BYTES, &tmB, rBFull + 8 * bs, it * TC_KS, t.pos0 + (int) cta_rank * cfg::B_ROWS);
-                        } else {
-                            tc::mbar_arrive_expect_tx(bBFull + 8 * bs, cfg::B_BYTES);
-                            tc::tma_load_2d(sB + bs * cfg::B_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0);
-                        }
-                    }
-                    __syncwarp();
-                    if (++bs == BS) { bs = 0; b_ph ^= 1; }
-                    if (++sub == SPR) { sub = 0; if (++rs == RS) { rs = 0; r_ph ^= 1; } }
+    } else if (warp == TC_W_TMA) {
+        // ===== TMA: activation tiles (whole warp in step, one elected lane issues) =========================================
+        int bs = 0;
+        uint32_t b_ph = 0;
+        int tg = 0; (void) tg;
+        tc_walker wk;
+        tc_seg sg;
+        while (wk.next(a, sg)) {
+            const tc_tile & t = sg.t;
+            const int nbox = (t.nvalid + TC_B_BOX - 1) / TC_B_BOX;            // only the boxes that hold valid columns
+            for (int it = sg.k0; it < sg.k1; ++it) {
+                tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
+                if (lane == 0) TC_TRACE(4, tg);
+                ++tg;
+                if (tc::elect_one()) {
+                    tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (nbox * TC_B_BOX_BYTES));
+                    for (int j = 0; j < nbox; ++j)
+                        tc::tma_load_2d(sB + bs * TC_B_BYTES + j * TC_B_BOX_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0 + j * TC_B_BOX);
                 }
-            }
-        }
-    } else if (warp == 9) {
-        // ===== MMA issue (whole warp in step, one elected lane issues; CTA pair: the leader only) =========================
-        if (!PAIR || cta_rank == 0) {
-            constexpr uint32_t idesc = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, PAIR ? 2 * TC_M : TC_M, NT);
-            const uint64_t da0 = tc::umma_desc_sw128(sA), db0 = tc::umma_desc_sw128(sB);
-            int as = 0, bs = 0;
-            uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
-            int tg = 0; (void) tg;
-            tc_walker wk(a, PAIR, 0);
-            tc_seg sg;
-            while (wk.next(a, NT, sg)) {
-                tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
-                tc::tc_fence_after();
-                const uint32_t d_tmem = tmem + acc * NT;
-                for (int it = sg.k0; it < sg.k1; ++it) {
-                    tc::mbar_wait(bAFull + 8 * as, a_ph);
-                    tc::mbar_wait(bBFull + 8 * bs, b_ph);
-                    if (lane == 0) TC_TRACE(0, tg);
-                    TC_PHASE(4, lane == 0 && tg == 0);
-                    tc::tc_fence_after();
-                    const uint64_t da = da0 + (uint64_t) (as * (TC_A_BYTES >> 4));
-                    const uint64_t db = db0 + (uint64_t) (bs * (cfg::B_BYTES >> 4));
-                    if (tc::elect_one()) {
-                        if (PAIR) {
-#pragma unroll
-                            for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_2cta(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
-                            tc::tc_commit2_mc(bAEmpty + 8 * as, 3);
-                            tc::tc_commit2_mc(bBEmpty + 8 * bs, 3);
-                        } else {
-#pragma unroll
-                            for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
-                            tc::tc_commit(bAEmpty + 8 * as);
-                            tc::tc_commit(bBEmpty + 8 * bs);
-                        }
-                    }
-                    __syncwarp();
-                    if (lane == 0) TC_TRACE(1, tg);
-                    ++tg;
-                    if (++as == AS) { as = 0; a_ph ^= 1; }
-                    if (++bs == BS) { bs = 0; b_ph ^= 1; }
-                }
-                if (tc::elect_one()) { if (PAIR) tc::tc_commit2_mc(bAccFull + 8 * acc, 3); else tc::tc_commit(bAccFull + 8 * acc); }
                 __syncwarp();
-                acc ^= 1; if (acc == 0) acc_ph ^= 1;
+                if (++bs == BS) { bs = 0; b_ph ^= 1; }
             }
         }
-    } else if (warp < 14) {
+    } else if (warp == TC_W_RAW) {
+        // ===== TMA: raw weight blocks, as far ahead as the raw ring allows ==================================================
+        int rs = 0;
+        uint32_t r_ph = 0;
+        int tg = 0; (void) tg;
+        tc_walker wk;
+        tc_seg sg;
+        while (wk.next(a, sg)) {
+            const tc_tile & t = sg.t;
+            const CUtensorMap * tw = t.wsel == 0 ? &tmW : (t.wsel == 1 ? &tmW1 : &tmW2);
+            int sbi = sg.k0 / SPR, x = sbi * a.raw_step;                     // next raw slot in the row (16-bit elements)
+            for (int it = sg.k0; it < sg.k1; it += SPR) {
+                tc::mbar_wait(bREmpty + 8 * rs, r_ph ^ 1, 100);
+                if (tc::elect_one()) {
+                    tc::mbar_arrive_expect_tx(bRFull + 8 * rs, RAW_BYTES);
+                    TC_PHASE(2, tg == 0);
+                    tc::tma_load_3d(sRaw + rs * RAW_BYTES, tw, bRFull + 8 * rs, x - (int) (raw_skew<TYPE>(sbi) >> 1), t.row0, t.mat);
+                }
+                __syncwarp();
+                ++tg;
+                x += a.raw_step; ++sbi;
+                if (++rs == RS) { rs = 0; r_ph ^= 1; }
+            }
+        }
+    } else if (warp == TC_W_MMA) {
+        // ===== MMA issue (whole warp in step, one elected lane issues) ====================================================
+        constexpr uint32_t idesc0 = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, TC_M, 0);
+        const uint64_t db0 = tc::umma_desc_sw128(sB);
+        const uint32_t ta0 = tmem + (uint32_t) TC_A_COL0;
+        int as = 0, bs = 0;
+        uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
+        int tg = 0; (void) tg;
+        tc_walker wk;
+        tc_seg sg;
+        while (wk.next(a, sg)) {
+            tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
+            tc::tc_fence_after();
+            const uint32_t d_tmem = tmem + acc * TC_NT_MAX;
+            const uint32_t idesc = idesc0 | ((uint32_t) ((sg.t.nvalid + 15) >> 4) << 18);      // N = valid columns rounded up to 16 (N >> 3 at bit 17)
+            for (int it = sg.k0; it < sg.k1; ++it) {
+                {   // both operands are normally there: probe the two barriers back to back, wait only for what is missing
+                    const bool okA = tc::mbar_try_wait(bAFull + 8 * as, a_ph), okB = tc::mbar_try_wait(bBFull + 8 * bs, b_ph);
+                    if (!okA) tc::mbar_wait(bAFull + 8 * as, a_ph);
+                    if (!okB) tc::mbar_wait(bBFull + 8 * bs, b_ph);
+                }
+                if (lane == 0) TC_TRACE(0, tg);
+                TC_PHASE(4, lane == 0 && tg == 0);
+                tc::tc_fence_after();
+                if (lane == 0) TC_TRACE(8, tg);
+                const uint32_t da = ta0 + (uint32_t) (as * TC_A_COLS);
+                const uint64_t db = db0 + (uint64_t) (bs * (TC_B_BYTES >> 4));
+                if (tc::elect_one()) {
+                    TC_TRACE(9, tg);
+#pragma unroll
+                    for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                    TC_TRACE(10, tg);
+                    tc::tc_commit(bAEmpty + 8 * as);
+                    tc::tc_commit(bBEmpty + 8 * bs);
+                    TC_TRACE(11, tg);
+                }
+                __syncwarp();
+                if (lane == 0) TC_TRACE(1, tg);
+                ++tg;
+                if (++as == AS) { as = 0; a_ph ^= 1; }
+                if (++bs == BS) { bs = 0; b_ph ^= 1; }
+            }
+            if (tc::elect_one()) tc::tc_commit(bAccFull + 8 * acc);
+            __syncwarp();
+            acc ^= 1; if (acc == 0) acc_ph ^= 1;
+        }
+    } else if (warp < TC_W_RAW) {
         // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
         const int q = warp & 3;
         uint32_t acc = 0, acc_ph = 0;
-        tc_walker wk(a, PAIR, cta_rank);
+        tc_walker wk;
         tc_seg sg;
-        while (wk.next(a, NT, sg)) {
+        while (wk.next(a, sg)) {
             const tc_tile & t = sg.t;
             tc::mbar_wait(bAccFull + 8 * acc, acc_ph, 400);
-            TC_PHASE(5, warp == 10 && lane == 0 && g_tc_phase[5] < g_tc_phase[0]);
+            TC_PHASE(5, warp == TC_W_EPI && lane == 0 && g_tc_phase[5] < g_tc_phase[0]);
             tc::tc_fence_after();
             const int row = t.row0 + 32 * q + lane;
             int32_t * turnstile = sg.nparts > 1 ? a.tile_sync + sg.T * 4 + q : nullptr;
@@ -662,10 +684,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 __syncwarp();
             }
 #pragma unroll 1
-            for (int c0 = 0; c0 < NT; c0 += 32) {
+            for (int c0 = 0; c0 < TC_NT_MAX; c0 += 32) {
                 if (c0 >= t.nvalid) break;                            // warp-uniform
                 uint32_t v[32];
-                tc::tmem_ld32(tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) (acc * NT + c0), v);
+                tc::tmem_ld32(tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) (acc * TC_NT_MAX + c0), v);
                 // this lane fetches the scale / destination column of position c0 + lane; shuffles hand them round
                 const int  pl  = t.pos0 + c0 + lane;
                 const bool pok = c0 + lane < t.nvalid;
@@ -706,10 +728,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     }
                 }
             }
-            TC_PHASE(6, warp == 10 && lane == 0 && g_tc_phase[6] < g_tc_phase[0]);
+            TC_PHASE(6, warp == TC_W_EPI && lane == 0 && g_tc_phase[6] < g_tc_phase[0]);
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) { if (PAIR) tc::mbar_arrive_cluster(rAccEmpty + 8 * acc); else tc::mbar_arrive(bAccEmpty + 8 * acc); }
+            if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
             if (turnstile) {
                 __threadfence();
                 __syncwarp();
@@ -727,16 +749,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                g_tc_phase[4] - g_tc_phase[0], g_tc_phase[5] - g_tc_phase[0], g_tc_phase[6] - g_tc_phase[0], g_tc_phase[7] - g_tc_phase[0]);
         const long long t0 = g_tc_trace[0][32];
         for (int gg = 32; gg < 48; ++gg) {
-            printf("g=%3d mma_ready=%6lld mma_done=%6lld conv_go=%6lld conv_arr0=%6lld conv_arr7=%6lld tma_go=%6lld\n", gg, g_tc_trace[0][gg] - t0,
-                   g_tc_trace[1][gg] - t0, g_tc_trace[2][gg] - t0, g_tc_trace[3][gg] - t0, g_tc_trace[5][gg] - t0, g_tc_trace[4][gg] - t0);
+            printf("g=%3d mma_ready=%6lld fenced=%6lld elected=%6lld mmas_issued=%6lld committed=%6lld mma_done=%6lld | conv_start=%6lld converted=%6lld conv_go=%6lld conv_arr0=%6lld conv_arr7=%6lld tma_go=%6lld\n", gg,
+                   g_tc_trace[0][gg] - t0, g_tc_trace[8][gg] - t0, g_tc_trace[9][gg] - t0, g_tc_trace[10][gg] - t0, g_tc_trace[11][gg] - t0, g_tc_trace[1][gg] - t0,
+                   g_tc_trace[6][gg] - t0, g_tc_trace[7][gg] - t0, g_tc_trace[2][gg] - t0, g_tc_trace[3][gg] - t0, g_tc_trace[5][gg] - t0, g_tc_trace[4][gg] - t0);
         }
     }
 #endif
-    if (PAIR) tc::cluster_sync();            // the peer may still arrive on this CTA's barriers / read its shared memory
-    if (warp == 8) {
+    if (warp == TC_W_TMA) {
         __syncwarp();
         tc::tc_fence_after();
-        if (PAIR) tc::tmem_dealloc2(tmem, 2 * NT); else tc::tmem_dealloc(tmem, 2 * NT);
+        tc::tmem_dealloc(tmem, 512);
     }
 }
 
@@ -757,26 +779,21 @@ encode_tiled_fn get_encode() {
 
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
 
-template <int TYPE, int NT, bool PAIR>
+template <int TYPE>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
-    static bool configured[16] = {};
-    auto kern = mmq_tc_f16_kernel<TYPE, NT, PAIR>;
-    using cfg_t = tc_cfg<NT, PAIR, raw_row<TYPE>::value>;
-    if (!configured[ctx->device & 15]) {
+    static std::atomic<bool> configured[16];
+    auto kern = mmq_tc_f16_kernel<TYPE>;
+    using cfg_t = tc_cfg<raw_row<TYPE>::value>;
+    if (!configured[ctx->device & 15].load(std::memory_order_acquire)) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg_t::SMEM));
-        configured[ctx->device & 15] = true;
+        configured[ctx->device & 15].store(true, std::memory_order_release);
     }
     {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned) a.grid); cfg.blockDim = dim3(TC_THREADS);
         cfg.dynamicSmemBytes = cfg_t::SMEM; cfg.stream = ctx->stream;
-        cudaLaunchAttribute attr[2];
+        cudaLaunchAttribute attr[1];
         int na = 0;
-        if (PAIR) {
-            attr[na].id = cudaLaunchAttributeClusterDimension;
-            attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
-            ++na;
-        }
         if (ctx->pdl && ctx->tc_pdl && a.split_k == 1) {      // (split K: a memset sits between the two kernels, nothing to overlap)
             attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             attr[na].val.programmaticStreamSerializationAllowed = 1;
@@ -790,13 +807,12 @@ int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, 
     return B200_OK;
 }
 
-template <int NT, bool PAIR>
 int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
-        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, NT, PAIR>(ctx, tmw, tm, a);
-        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, NT, PAIR>(ctx, tmw, tm, a);
-        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, NT, PAIR>(ctx, tmw, tm, a);
-        case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K, NT, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0>(ctx, tmw, tm, a);
+        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0>(ctx, tmw, tm, a);
+        case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -818,13 +834,13 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     } else if (P.n_expert > 1 && P.nb02 < P.nb01 * P.m) return 0;
     if (((uintptr_t) P.X | (uintptr_t) P.nb11 | (uintptr_t) P.nb12 | (uintptr_t) P.nb13) & 15) return 0;
     if (P.mode == MM_ID_PAIRS) return 0;
-    if (tc_cfg<256>::SMEM > ctx->smem_optin) return 0;
+    if (tc_cfg<>::SMEM > ctx->smem_optin) return 0;
     return 1;
 }
 
 struct tc_plan {
-    int     NT;
-    bool    pair;        // CTA pairs on 256-row tiles (MM_PLAIN)
+    int     nt;          // tile width
+    int     split_k;
     int64_t n, batches, row_tiles, col_tiles, n_tiles;
     size_t  off_xh, off_sc, off_yc, off_sync, total;
 };
@@ -836,36 +852,84 @@ struct tc_multi {            // several matrices per launch: P.m is the padded t
     float * Y[3];
 };
 
-static tc_plan make_plan(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M = nullptr) {
+// Estimated clocks of one 64-K stage of a tile with w valid columns: the MMA (2 clocks per column of N, N = w rounded up to 16)
+// against the shared-memory traffic at 128 bytes per clock (activation boxes written by TMA + N rows read by the MMA + raw weight
+// blocks written and read once), whichever is longer.
+static double tc_stage_clocks(int64_t w, int raw_stage_bytes) {
+    const double n16 = (double) ((w + 15) / 16 * 16), boxes = (double) ((w + TC_B_BOX - 1) / TC_B_BOX);
+    const double smem = (boxes * TC_B_BOX_BYTES + n16 * 128.0 + 2.0 * raw_stage_bytes) / 128.0;
+    return (2.0 * n16 > smem ? 2.0 * n16 : smem) + 24.0;
+}
+
+// longest chain of stages any CTA walks when the tiles of a MUL_MAT are dealt round robin (column tile fastest)
+static double tc_makespan(int64_t row_tiles, int64_t n, int64_t batches, int nt, int sk, int64_t stages, int sms, int raw_stage_bytes) {
+    const int64_t col_tiles = (n + nt - 1) / nt, n_tiles = row_tiles * col_tiles * batches, items = n_tiles * sk;
+    const int64_t last_w = n - (col_tiles - 1) * nt;
+    const double c_full = tc_stage_clocks(nt, raw_stage_bytes), c_last = tc_stage_clocks(last_w, raw_stage_bytes);
+    const double per_item = (double) (stages / sk) + 24.0;          // + pipeline fill / epilogue hand-over in stage units (measured order of magnitude)
+    const int64_t G = items < sms ? items : sms;
+    if (items > 64 * (int64_t) sms) {                               // many waves: the average is what counts
+        const double avg = (c_full * (col_tiles - 1) + c_last) / (double) col_tiles;
+        return avg * per_item * (double) ((items + G - 1) / G);
+    }
+    double worst = 0.0;
+    for (int64_t c = 0; c < G; ++c) {
+        double t = 0.0;
+        for (int64_t w = c; w < items; w += G) t += ((w % n_tiles) % col_tiles == col_tiles - 1 ? c_last : c_full) * per_item;
+        worst = t > worst ? t : worst;
+    }
+    return worst;
+}
+
+static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M = nullptr) {
     tc_plan p;
     p.batches   = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
     p.n         = P.mode == MM_PLAIN ? P.ne11 : n_pos;
-    // ctx->tc_pair: 0 = never, 1 = when the matrix has enough 256-row tiles (default), 2 = always (MM_PLAIN)
-    p.pair      = P.mode == MM_PLAIN && (ctx->tc_pair == 2 || (ctx->tc_pair == 1 && P.m >= 2048));
-    const int tm = p.pair ? 2 * TC_M : TC_M;
-    const int units = p.pair ? ctx->sm_count / 2 : ctx->sm_count;
-    p.row_tiles = (P.m + tm - 1) / tm;
-    if (M) {                 // every matrix padded to whole tiles of the height actually used (must match tc_args::rt_end)
+    p.row_tiles = (P.m + TC_M - 1) / TC_M;
+    if (M) {                 // every matrix padded to whole tiles (must match tc_args::rt_end)
         p.row_tiles = 0;
-        for (int j = 0; j < M->n_mats; ++j) p.row_tiles += (M->m[j] + tm - 1) / tm;
+        for (int j = 0; j < M->n_mats; ++j) p.row_tiles += (M->m[j] + TC_M - 1) / TC_M;
     }
-    p.NT        = p.n <= 128 ? 128 : 256;
-    if (p.NT == 256 && P.mode == MM_PLAIN) {
-        // 128 x 256 tiles move fewer shared-memory bytes per flop (measured ~836 vs ~586 clocks per 64-wide K stage), but
-        // few of them leave SMs idle: take the tile width with the shorter estimated critical path
-        const int64_t t256 = p.row_tiles * ((p.n + 255) / 256) * p.batches, t128 = p.row_tiles * ((p.n + 127) / 128) * p.batches;
-        const int64_t w256 = (t256 + units - 1) / units, w128 = (t128 + units - 1) / units;
-        // (long K normally prefers 256-wide tiles + split K; the fused row-split epilogue cannot split K, so it takes narrow tiles)
-        if (ctx->tc_nt == 128 || (ctx->tc_nt == 0 && (P.k < 8192 || P.n_peers > 0) && w128 * 586 < w256 * 836)) p.NT = 128;
+    const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : 36));
+    const int forced = ctx->tc_nt >= 192 ? 192 : (ctx->tc_nt >= 128 ? 128 : (ctx->tc_nt > 0 ? 64 : 0));
+    p.split_k = 1;
+    if (P.mode == MM_PLAIN) {
+        // tile width and split K by the estimated critical path.  ctx->tc_split_k: 0 = never, 1 = auto (long K only: the second
+        // half of a tile is added through a turnstile, which pays off when the K loop is long), 2 / 4 = forced
+        const int64_t stages = P.k / TC_KS;
+        double best = 0.0;
+        p.nt = 0;
+        for (const int nt : {192, 128, 64}) {
+            if (forced && nt != forced) continue;
+            if (!forced && nt > 64 && p.n <= nt - 64) continue;      // a narrower width already covers n with one tile
+            for (const int sk : {1, 2, 4}) {
+                if (sk > 1) {
+                    if (ctx->tc_split_k == 0 || P.n_peers > 0 || (P.k / 256) % sk != 0) continue;
+                    if (ctx->tc_split_k == 1 && (sk > 2 || P.k < 8192)) continue;
+                    if (ctx->tc_split_k > 1 && sk != ctx->tc_split_k) continue;
+                } else if (ctx->tc_split_k > 1 && (P.k / 256) % ctx->tc_split_k == 0 && P.n_peers == 0) continue;
+                double t = tc_makespan(p.row_tiles, p.n, p.batches, nt, sk, stages, ctx->sm_count, raw_stage_bytes);
+                if (sk > 1) t *= 1.05;                                // the turnstile and the reductions are not free
+                if (p.nt == 0 || t < best) { best = t; p.nt = nt; p.split_k = sk; }
+            }
+        }
+        if (p.nt == 0) p.nt = forced ? forced : 192;
+    } else {
+        // MUL_MAT_ID: the positions per expert are only known on the device; take the width that holds an average expert's share
+        // with some margin in one tile (a tile costs what its valid columns cost)
+        const int64_t avg = n_pos / (P.n_expert > 0 ? P.n_expert : 1);
+        p.nt = forced ? forced : (avg <= 48 ? 64 : (avg <= 100 ? 128 : 192));
     }
-    p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.NT - 1) / p.NT : (n_pos + p.NT - 1) / p.NT + P.n_expert;
+    p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.nt - 1) / p.nt : (n_pos + p.nt - 1) / p.nt + P.n_expert;
     p.n_tiles   = p.row_tiles * p.col_tiles * p.batches;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     p.off_xh   = (ws_used + 1023) / 1024 * 1024;
     p.off_sc   = p.off_xh + up((size_t) n_pos * P.k * sizeof(__half));
     p.off_yc   = p.off_sc + up((size_t) n_pos * 4);
     p.off_sync = p.off_yc + up((size_t) n_pos * 4);
-    p.total    = p.off_sync + up((size_t) p.n_tiles * 4 * sizeof(int32_t));
+    // (room for the turnstiles of the narrowest tiling: the scratch is reserved before options may change the plan)
+    const int64_t max_tiles = p.row_tiles * (P.mode == MM_PLAIN ? (p.n + 63) / 64 : (n_pos + 63) / 64 + P.n_expert) * p.batches;
+    p.total    = p.off_sync + up((size_t) max_tiles * 4 * sizeof(int32_t));
     return p;
 }
 
@@ -879,13 +943,12 @@ int b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t 
 }
 
 static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used, const tc_multi * M) {
-    const tc_plan pl = make_plan(ctx, P, n_pos, ws_used, M);
+    const tc_plan pl = make_plan(ctx, type, P, n_pos, ws_used, M);
     if ((size_t) ctx->ws_size < pl.total) { b200_set_error("tcgen05 GEMM: scratch not reserved"); return B200_E_ARG; }
     uint8_t * ws = (uint8_t *) ctx->ws;
     __half *  Xh = (__half *) (ws + pl.off_xh);
     float *   sc = (float *) (ws + pl.off_sc);
     int32_t * yc = (int32_t *) (ws + pl.off_yc);
-    const int NT = pl.NT;
     const int64_t n = pl.n;
 
     {
@@ -899,10 +962,11 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     }
     ctx->launches++;
 
+    // fp16 activations: boxes of 64 positions x 64 K (a tile fetches as many as it has valid columns); positions past the end read as zero
     CUtensorMap tmb;
     const cuuint64_t gdim[2]    = {(cuuint64_t) P.k, (cuuint64_t) n_pos};
     const cuuint64_t gstride[1] = {(cuuint64_t) P.k * sizeof(__half)};
-    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) (pl.pair ? NT / 2 : NT)};
+    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) TC_B_BOX};
     const cuuint32_t estr[2]    = {1, 1};
     const CUresult cr = get_encode()(&tmb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -931,47 +995,35 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : TC_RAW_ROW)) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
+    a.nt = pl.nt; a.col_tiles = (int) pl.col_tiles;
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
     a.n_mats = M ? M->n_mats : 1;
-    const int tm = pl.pair ? 2 * TC_M : TC_M;
     if (M) {
         int rt = 0;
         for (int j = 0; j < 3; ++j) {
             const int jj = j < M->n_mats ? j : M->n_mats - 1;
-            if (j < M->n_mats) rt += (int) ((M->m[j] + tm - 1) / tm);
+            if (j < M->n_mats) rt += (int) ((M->m[j] + TC_M - 1) / TC_M);
             a.rt_end[j] = rt; a.m_j[j] = (int) M->m[jj]; a.Y_j[j] = M->Y[jj];
         }
     }
 
     if (pl.n_tiles * 4 >= ((int64_t) 1 << 31)) { b200_set_error("tcgen05 GEMM: too many tiles"); return B200_E_UNSUPPORTED; }
     a.n_tiles = pl.n_tiles;
-    // Scheduling: whole tiles, walked in the same order by all CTAs (they move along K in step and share activation tiles in
-    // L2).  A long-K matrix with few tiles (down projection: 64 tiles for 148 SMs) is split in two along K; the halves run
-    // in the same wave and the second is added to the first through a per-tile turnstile, so the result does not depend
-    // on timing.  (Measured and rejected: stream-K with equal runs per CTA — loses the L2 sharing, no gain.)
-    // ctx->tc_split_k: 0 = never, 1 = auto, 2 / 4 = forced
-    a.split_k = 1;
+    // Scheduling: whole tiles dealt round robin.  A long-K matrix with few tiles (down projection) is split along K; the parts run
+    // in the same wave and the later ones are added to the first through a per-tile turnstile, so the result does not depend
+    // on timing.  (Measured and rejected: stream-K with equal runs per CTA — no gain.)
+    a.split_k = pl.split_k;
     a.n_peers = P.n_peers; a.peer_m = P.peer_m; a.peer_row0 = P.peer_row0;
     for (int p = 0; p < P.n_peers; ++p) a.peer_Y[p] = P.peer_Y[p];
-    if (P.mode == MM_PLAIN && ctx->tc_split_k > 0 && !pl.pair && P.n_peers == 0) {
-        auto eff = [&](int64_t sk) {
-            const int64_t items = pl.n_tiles * sk, waves = (items + ctx->sm_count - 1) / ctx->sm_count;
-            return (double) items / (double) (waves * ctx->sm_count);
-        };
-        if (ctx->tc_split_k > 1) { if ((P.k / 256) % ctx->tc_split_k == 0) a.split_k = ctx->tc_split_k; }
-        else if ((P.k / 256) % 2 == 0 && P.k >= 8192 && eff(2) > 1.15 * eff(1)) a.split_k = 2;
-    }
     const int64_t items = pl.n_tiles * a.split_k;
     a.grid = (int) (items < ctx->sm_count ? items : ctx->sm_count);
-    if (pl.pair) { const int64_t cl = ctx->sm_count / 2; a.grid = 2 * (int) (items < cl ? items : cl); }
     if (a.split_k > 1) {
         a.tile_sync = (int32_t *) (ws + pl.off_sync);
         B200_CUDA_TRY(cudaMemsetAsync(a.tile_sync, 0, (size_t) pl.n_tiles * 4 * sizeof(int32_t), ctx->stream));
     }
-    if (pl.pair) return NT == 128 ? launch_type<128, true>(ctx, type, tmw, tmb, a) : launch_type<256, true>(ctx, type, tmw, tmb, a);
-    return NT == 128 ? launch_type<128, false>(ctx, type, tmw, tmb, a) : launch_type<256, false>(ctx, type, tmw, tmb, a);
+    return launch_type(ctx, type, tmw, tmb, a);
 }
 
 // several weight matrices x the same activations (caller checked: same type / k / row size, MM_PLAIN without batch dims)
@@ -987,7 +1039,7 @@ int b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const 
     int64_t padded = 0;
     for (int j = 0; j < n_mats; ++j) {
         M.W[j] = (const uint8_t *) a[j]->data; M.m[j] = a[j]->ne[1]; M.Y[j] = (float *) d[j]->data;
-        padded += (a[j]->ne[1] + 2 * TC_M - 1) / (2 * TC_M) * (2 * TC_M);      // whole 256-row tiles: valid for single CTAs and for pairs
+        padded += (a[j]->ne[1] + TC_M - 1) / TC_M * TC_M;
     }
     P.m = padded;
     if (!b200_tc_supported(ctx, a[0]->type, P)) return B200_E_UNSUPPORTED;
@@ -997,4 +1049,4 @@ int b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const 
     return launch_gemm_tc_core(ctx, a[0]->type, P, b->ne[1], 0, &M);
 }
 
-size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) { return make_plan(ctx, P, n_pos, ws_used).total; }
+size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used) { return make_plan(ctx, B200_TYPE_Q4_K, P, n_pos, ws_used).total; }
