@@ -52,6 +52,7 @@ constexpr int TC_CONV_WARPS  = 4 * TC_CONV_GROUPS;
 constexpr int TC_W_TMA = TC_CONV_WARPS, TC_W_MMA = TC_CONV_WARPS + 1, TC_W_EPI = TC_CONV_WARPS + 2, TC_W_RAW = TC_CONV_WARPS + 6;   // warp roles
 constexpr int TC_THREADS  = 32 * (TC_CONV_WARPS + 7);   // 12 converter warps, activation-TMA warp, MMA warp, 4 epilogue warps, weight-TMA warp
 static_assert(TC_A_COL0 + TC_A_SLOTS * TC_A_COLS <= 512, "accumulators and the A ring must fit the 512 TMEM columns");
+static_assert((TC_A_SLOTS & (TC_A_SLOTS - 1)) == 0, "A ring slots are taken from the stage counter by masking");
 
 // RAW_ROW: bytes per row and raw slot — 144 (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 blocks + pad) or 224 (Q6_K: one 210-byte
 // super-block + pad; the wider raw ring is paid for with one activation slot and one raw slot)
@@ -83,6 +84,7 @@ struct tc_args {
     int     ne12, r2, r3;       // batch dims (MM_PLAIN)
     int     ne02;               // weight matrices per ne03 slice
     int     raw_step;           // 16-bit elements of a weight row per raw slot (row bytes of raw_k K elements / 2)
+    uint32_t k6400;             // 0x64006400 (see and_or)
     float * Y;
     const float *   colscale;   // per activation position: 2^-e that undoes the fp16 normalisation
     const int32_t * ycol;       // per activation position: output column (MUL_MAT_ID scatter); NULL = identity
@@ -193,13 +195,21 @@ __device__ __forceinline__ uint32_t h2_bits(const __half2 h) { return *reinterpr
 __device__ __forceinline__ __half2  bits_h2(const uint32_t u) { return *reinterpret_cast<const __half2 *>(&u); }
 __device__ __forceinline__ __half2  h2_const(const float v)  { return __float2half2_rn(v); }
 
+// (a & mask) | k in ONE instruction: LOP3 takes a single immediate, so the exponent pattern 0x64006400 has to sit in a register — it
+// is read from the kernel arguments (tc_args::k6400), which keeps ptxas from folding it back into a second immediate and splitting
+// the operation in two (the ALU pipe is what the converters hang on: ncu, 59 % busy at 0.5 instructions / clock)
+__device__ __forceinline__ uint32_t and_or(const uint32_t a, const uint32_t mask, const uint32_t k) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "r"(mask), "r"(k));
+    return r;
+}
 // (b0, b2) and (b1, b3) low nibbles of a word as exact fp16 integers 1024 + q; the high nibbles as 1024 + 16 q
-__device__ __forceinline__ void nib_pairs(const uint32_t w, __half2 & lo02, __half2 & lo13, __half2 & hi02, __half2 & hi13) {
+__device__ __forceinline__ void nib_pairs(const uint32_t w, const uint32_t k6400, __half2 & lo02, __half2 & lo13, __half2 & hi02, __half2 & hi13) {
     const uint32_t s = w >> 8;
-    lo02 = bits_h2((w & 0x000F000Fu) | 0x64006400u);
-    lo13 = bits_h2((s & 0x000F000Fu) | 0x64006400u);
-    hi02 = bits_h2((w & 0x00F000F0u) | 0x64006400u);
-    hi13 = bits_h2((s & 0x00F000F0u) | 0x64006400u);
+    lo02 = bits_h2(and_or(w, 0x000F000Fu, k6400));
+    lo13 = bits_h2(and_or(s, 0x000F000Fu, k6400));
+    hi02 = bits_h2(and_or(w, 0x00F000F0u, k6400));
+    hi13 = bits_h2(and_or(s, 0x00F000F0u, k6400));
 }
 
 template <int TYPE> struct w_frag;
@@ -219,7 +229,7 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
         f0.q = lds_u4(row + 16 + 32 * sub); f1.q = lds_u4(row + 16 + 32 * sub + 16);
     }
     // 4 chunks of 8 fp16; chunk slot indices within the 128-byte row returned in `slot`
-    __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+    __device__ __forceinline__ void convert(const int sub, const int h, const uint32_t k6400, uint4 (&out)[4], int (&slot)[4]) const {
         const int g = sub;
         int sc0, mn0, sc1, mn1;
         q4k_scale_min(2 * g,     hdr.y, hdr.z, hdr.w, sc0, mn0);
@@ -233,7 +243,7 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             __half2 a, b, c, d;
-            nib_pairs(w[j], a, b, c, d);
+            nib_pairs(w[j], k6400, a, b, c, d);
             lo[2 * j]     = h2_bits(__hfma2(__hsub2(a, k1024), s_lo, nb_lo));
             lo[2 * j + 1] = h2_bits(__hfma2(__hsub2(b, k1024), s_lo, nb_lo));
             hi[2 * j]     = h2_bits(__hfma2(__hfma2(c, sixteenth, m64), s_hi, nb_hi));
@@ -260,7 +270,7 @@ template <> struct w_frag<B200_TYPE_Q4_0> {
         for (int j = 0; j < 5; ++j) w[j] = lds_u32(b + 4 * j);
     }
     static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
-    __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+    __device__ __forceinline__ void convert(const int, const int h, const uint32_t k6400, uint4 (&out)[4], int (&slot)[4]) const {
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
         const __half2 k1032 = h2_const(1032.0f), sixteenth = h2_const(0.0625f), m72 = h2_const(-72.0f);
         uint32_t lo[8], hi[8];
@@ -268,7 +278,7 @@ template <> struct w_frag<B200_TYPE_Q4_0> {
         for (int j = 0; j < 4; ++j) {
             const uint32_t qs = h ? w[j + 1] : __funnelshift_r(w[j], w[j + 1], 16);
             __half2 a, b, c, d;
-            nib_pairs(qs, a, b, c, d);
+            nib_pairs(qs, k6400, a, b, c, d);
             lo[2 * j]     = h2_bits(__hmul2(__hsub2(a, k1032), d2));
             lo[2 * j + 1] = h2_bits(__hmul2(__hsub2(b, k1032), d2));
             hi[2 * j]     = h2_bits(__hmul2(__hfma2(c, sixteenth, m72), d2));
@@ -291,7 +301,8 @@ template <> struct w_frag<B200_TYPE_Q8_0> {
         for (int j = 0; j < 9; ++j) w[j] = lds_u32(b + 4 * j);
     }
     static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
-    __device__ __forceinline__ void convert(const int, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+    __device__ __forceinline__ void convert(const int, const int h, const uint32_t k6400, uint4 (&out)[4], int (&slot)[4]) const {
+        (void) k6400;
         const __half2 d2 = __half2half2(__ushort_as_half((unsigned short) (h ? w[0] >> 16 : w[0] & 0xFFFF)));
         const __half2 k1152 = h2_const(1152.0f);
         uint32_t v[16];
@@ -331,7 +342,8 @@ template <> struct w_frag<B200_TYPE_Q6_K> {
         asm volatile("ld.shared.u16 %0, [%1];" : "=r"(d)  : "r"(row + 208));
     }
     static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
-    __device__ __forceinline__ void convert(const int sub, const int h, uint4 (&out)[4], int (&slot)[4]) const {
+    __device__ __forceinline__ void convert(const int sub, const int h, const uint32_t k6400, uint4 (&out)[4], int (&slot)[4]) const {
+        (void) k6400;
         const int r = 2 * (sub & 1) + h, shl = 4 * (sub & 1), shh = 2 * r;
         const float df = __half2float(__ushort_as_half((unsigned short) d));
         const __half2 s_a = h2_const(df * (float) (int8_t) (sc & 0xff)), s_b = h2_const(df * (float) (int8_t) (sc >> 8));
@@ -512,58 +524,61 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         const int grp = warp >> 2, q = warp & 3;
         const uint32_t raw_row_a = sRaw + (uint32_t) ((32 * q + lane) * RAW_ROW);
         const uint32_t ta = tmem + ((uint32_t) (32 * q) << 16) + (uint32_t) TC_A_COL0;
-        int as = 0, rs = 0, sub = 0, turn = 0;            // turn: which group the next stage belongs to (runs on across tiles)
-        uint32_t a_ph = 0, r_ph = 0;
+        // gs: running stage counter of this CTA over all its tiles (every role counts the same stages) — ring slots and phases follow
+        // from it in closed form, and a group only visits its own stages (gs mod 3 == grp).  Segments are whole raw slots (host:
+        // k and the split parts are multiples of 256), so the raw-slot counter is gs / SPR.
+        uint32_t gs = 0, gmod = 0;
+        const uint32_t k6400 = a.k6400;
         int tg = 0; (void) tg;
         tc_walker wk;
         tc_seg sg;
         while (wk.next(a, sg)) {
-            // TMA needs 16-byte aligned global addresses: Q8_0's odd raw slots (136-byte steps) are fetched 8 bytes early, Q6_K's
-            // slot i (210-byte steps) 2 (i mod 8) bytes early; the converters skip the skew
-            int sbi = sg.k0 / SPR;
-            uint32_t skew = raw_skew<TYPE>(sbi);
-            for (int it = sg.k0; it < sg.k1; ++it) {
-                if (turn == grp) {
-                    tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
-                    TC_PHASE(3, tid == 0 && tg == 0);
-                    if (tid == 0) TC_TRACE(6, tg);
-                    w_frag<TYPE> f0, f1;
-                    uint4 o0[4], o1[4]; int s0[4], s1[4];
-                    w_frag<TYPE>::load_row(f0, f1, raw_row_a + rs * RAW_BYTES + skew, sub);
-                    f0.convert(sub, 0, o0, s0);
-                    f1.convert(sub, 1, o1, s1);
-                    // chunk s of the row (K elements 8 s .. 8 s + 7 of the stage) = columns 4 s .. 4 s + 3 (the slots are
-                    // compile-time constants once the half is)
-                    uint32_t v[32];
+            const int nst = sg.k1 - sg.k0;
+            const int first = (int) ((grp + 3u - gmod) % 3u);
+            for (int lt = first; lt < nst; lt += TC_CONV_GROUPS) {
+                const uint32_t g = gs + (uint32_t) lt;
+                const int it = sg.k0 + lt, sub = lt & (SPR - 1), sbi = it / SPR;
+                const int as = (int) (g & (AS - 1));
+                const uint32_t a_ph = (g / AS) & 1u;
+                const uint32_t slotc = g / SPR;
+                const int rs = (int) (slotc % RS);
+                const uint32_t r_ph = (slotc / RS) & 1u;
+                // TMA needs 16-byte aligned global addresses: Q8_0's odd raw slots (136-byte steps) are fetched 8 bytes early, Q6_K's
+                // slot i (210-byte steps) 2 (i mod 8) bytes early; the converters skip the skew
+                const uint32_t skew = raw_skew<TYPE>(sbi);
+                tc::mbar_wait(bRFull + 8 * rs, r_ph, 40);
+                TC_PHASE(3, tid == 0 && g == 0);
+                if (tid == 0) TC_TRACE(6, (int) g);
+                w_frag<TYPE> f0, f1;
+                uint4 o0[4], o1[4]; int s0[4], s1[4];
+                w_frag<TYPE>::load_row(f0, f1, raw_row_a + rs * RAW_BYTES + skew, sub);
+                f0.convert(sub, 0, k6400, o0, s0);
+                f1.convert(sub, 1, k6400, o1, s1);
+                // chunk s of the row (K elements 8 s .. 8 s + 7 of the stage) = columns 4 s .. 4 s + 3 (the slots are
+                // compile-time constants once the half is)
+                uint32_t v[32];
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        v[4 * s0[c]] = o0[c].x; v[4 * s0[c] + 1] = o0[c].y; v[4 * s0[c] + 2] = o0[c].z; v[4 * s0[c] + 3] = o0[c].w;
-                        v[4 * s1[c]] = o1[c].x; v[4 * s1[c] + 1] = o1[c].y; v[4 * s1[c] + 2] = o1[c].z; v[4 * s1[c] + 3] = o1[c].w;
-                    }
-                    if (tid == 0) TC_TRACE(7, tg);
-                    tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
-                    tc::tc_fence_after();
-                    if (tid == 0) TC_TRACE(2, tg);
-                    tc::tmem_st32(ta + (uint32_t) (as * TC_A_COLS), v);
-                    tc::tmem_st_wait();
-                    tc::tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) {
-                        tc::mbar_arrive(bAFull + 8 * as);
-                        tc::mbar_arrive(bREmpty + 8 * rs);
-                        if (warp == 0) TC_TRACE(3, tg);
-                        if (warp == 7) TC_TRACE(5, tg);
-                    }
+                for (int c = 0; c < 4; ++c) {
+                    v[4 * s0[c]] = o0[c].x; v[4 * s0[c] + 1] = o0[c].y; v[4 * s0[c] + 2] = o0[c].z; v[4 * s0[c] + 3] = o0[c].w;
+                    v[4 * s1[c]] = o1[c].x; v[4 * s1[c] + 1] = o1[c].y; v[4 * s1[c] + 2] = o1[c].z; v[4 * s1[c] + 3] = o1[c].w;
                 }
-                ++tg;
-                if (++turn == TC_CONV_GROUPS) turn = 0;
-                if (++as == AS) { as = 0; a_ph ^= 1; }
-                if (++sub == SPR) {
-                    sub = 0;
-                    skew = raw_skew<TYPE>(++sbi);
-                    if (++rs == RS) { rs = 0; r_ph ^= 1; }
+                if (tid == 0) TC_TRACE(7, (int) g);
+                tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
+                tc::tc_fence_after();
+                if (tid == 0) TC_TRACE(2, (int) g);
+                tc::tmem_st32(ta + (uint32_t) (as * TC_A_COLS), v);
+                tc::tmem_st_wait();
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    tc::mbar_arrive(bAFull + 8 * as);
+                    tc::mbar_arrive(bREmpty + 8 * rs);
+                    if (warp == 0) TC_TRACE(3, (int) g);
+                    if (warp == 7) TC_TRACE(5, (int) g);
                 }
             }
+            gs += (uint32_t) nst;
+            gmod = (gmod + (uint32_t) nst) % 3u;
         }
     } else if (warp == TC_W_TMA) {
         // ===== TMA: activation tiles (whole warp in step, one elected lane issues) =========================================
@@ -995,7 +1010,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : TC_RAW_ROW)) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
-    a.nt = pl.nt; a.col_tiles = (int) pl.col_tiles;
+    a.nt = pl.nt; a.col_tiles = (int) pl.col_tiles; a.k6400 = 0x64006400u;
     a.ne12 = (int) P.ne12; a.r2 = (int) P.r2; a.r3 = (int) P.r3;
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
