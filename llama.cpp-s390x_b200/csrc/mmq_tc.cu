@@ -43,8 +43,9 @@ constexpr int TC_NT_MAX   = 192;     // widest tile: 2 accumulators x 192 column
 constexpr int TC_A_SLOTS  = 4;       // A stages in tensor memory
 constexpr int TC_A_COL0   = 2 * TC_NT_MAX;
 constexpr int TC_A_COLS   = TC_KS / 2;
-constexpr int TC_B_BOX    = 64;      // activation columns per TMA box
+constexpr int TC_B_BOX    = 64;      // activation columns per TMA box (CTA pair: 32 — a CTA holds half of the tile's columns)
 constexpr int TC_B_BOX_BYTES = TC_B_BOX * 128;
+constexpr int TC_B_BOX_P  = 32, TC_B_BOX_P_BYTES = TC_B_BOX_P * 128;
 constexpr int TC_B_BYTES  = TC_NT_MAX * 128;
 constexpr int TC_RAW_ROW  = 144;     // bytes of raw blocks per row and raw slot (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 + pad)
 constexpr int TC_CONV_GROUPS = 3;    // converter groups of 4 warps (one warp per TMEM lane quadrant); group g takes every 3rd stage
@@ -384,8 +385,9 @@ struct tc_tile {
 
 // (32-bit arithmetic throughout: the host refuses launches with 2^31 or more work items, and 64-bit divisions here sat in front of
 //  the first TMA of every CTA — 1.4 us of a 11 us launch in the phase trace)
-__device__ __forceinline__ bool tc_resolve(const tc_args & a, uint32_t T, tc_tile & t) {
-    const uint32_t row_tiles = (uint32_t) (a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + TC_M - 1) / TC_M);
+// tm = weight rows per work tile (128, or 256 for a CTA pair: CTA `rank` of the pair owns rows [128 rank, 128 rank + 128) of it)
+__device__ __forceinline__ bool tc_resolve(const tc_args & a, uint32_t T, tc_tile & t, const int tm = TC_M, const int rank = 0) {
+    const uint32_t row_tiles = (uint32_t) (a.n_mats > 1 ? a.rt_end[a.n_mats - 1] : (a.m + tm - 1) / tm);
     const int NT = a.nt;
     int rt, ct = 0, batch = 0;
     if (a.mode == MM_PLAIN) {
@@ -403,7 +405,7 @@ __device__ __forceinline__ bool tc_resolve(const tc_args & a, uint32_t T, tc_til
         rt -= j == 0 ? 0 : a.rt_end[j - 1];
         t.wsel = j; t.m = a.m_j[j]; t.Y = a.Y_j[j];
     }
-    t.row0 = rt * TC_M;
+    t.row0 = rt * tm + TC_M * rank;
     if (a.mode == MM_PLAIN) {
         int i12 = 0, i13 = 0;
         t.mat = 0;
@@ -440,16 +442,19 @@ struct tc_seg {
 
 struct tc_walker {
     uint32_t w;             // next work item: tile = w % n_tiles, K part = w / n_tiles (the parts of a tile run in the same wave)
-    int      stride;
+    int      stride, tm, rank;
 
-    __device__ __forceinline__ tc_walker() { w = blockIdx.x; stride = gridDim.x; }
+    // pair = false: one CTA per work item; true: the two CTAs of a cluster walk the same items (256-row tiles)
+    __device__ __forceinline__ tc_walker(const bool pair = false, const int cta_rank = 0) {
+        w = pair ? blockIdx.x >> 1 : blockIdx.x; stride = pair ? gridDim.x >> 1 : gridDim.x; tm = pair ? 2 * TC_M : TC_M; rank = cta_rank;
+    }
 
     __device__ __forceinline__ bool next(const tc_args & a, tc_seg & s) {
         const uint32_t n_tiles = (uint32_t) a.n_tiles, n_items = n_tiles * (uint32_t) a.split_k;
         for (; w < n_items; w += stride) {
             const uint32_t part = a.split_k == 1 ? 0u : w / n_tiles;
             s.T = w - part * n_tiles;
-            if (tc_resolve(a, s.T, s.t)) {
+            if (tc_resolve(a, s.T, s.t, tm, rank)) {
                 const int len = a.k / TC_KS / a.split_k;
                 s.k0 = (int) part * len; s.k1 = s.k0 + len;
                 s.order = (int) part; s.nparts = a.split_k;
@@ -471,7 +476,12 @@ __device__ unsigned long long g_tc_phase[8];          // %globaltimer stamps of 
 #define TC_PHASE(i, once) do { } while (0)
 #endif
 
-template <int TYPE>
+// PAIR: two CTAs of a cluster (the two SMs of a TPC) share one 256-row tile: each converts its own 128 rows of A into its own tensor
+// memory and fetches HALF of the activation tile; one M = 256 MMA (cta_group::2), issued by the leader (cluster rank 0), reads both
+// halves — the activation bytes an SM pulls through L2 per flop halve, and that traffic is what bounds single-CTA tiles.
+// The barriers "operands ready" (A full, B full) and "accumulator drained" that gate the MMAs live in the LEADER's shared memory, the
+// peer's warps arrive there remotely; "slot free" and "accumulator ready" are per CTA, signalled in both by multicast commits.
+template <int TYPE, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmW1,
                                                                    const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmB,
                                                                    const tc_args a) {
@@ -489,6 +499,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
     const uint32_t sTmem  = bAccEmpty + 16;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t cta_rank = PAIR ? tc::cluster_ctarank() : 0u;
+    constexpr int NC = PAIR ? 2 : 1;     // CTAs whose warps arrive on the leader's barriers
     TC_PHASE(0, tid == 0);
 
     if (warp == TC_W_TMA) {
@@ -496,17 +508,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
             for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
-            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) / commit
+            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4 * NC); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) per CTA / commit
             for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 4 * SPR); }   // expect_tx / 4 converter warps per stage of the slot
-            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4); } // commit / 4 epilogue warps
+            for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4 * NC); } // commit / 4 epilogue warps per CTA
             tc::mbar_fence_init();
         }
         __syncwarp();
-        tc::tmem_alloc(sTmem, 512);
+        if (PAIR) tc::tmem_alloc2(sTmem, 512); else tc::tmem_alloc(sTmem, 512);
     }
     tc::tc_fence_before();
-    __syncthreads();
+    if (PAIR) tc::cluster_sync(); else __syncthreads();
     tc::tc_fence_after();
+    // where this CTA's warps report "A stage written" / "accumulator drained" / "activation bytes landed": the leader's barriers
+    const uint32_t rAFull = PAIR ? tc::mapa_u32(bAFull, 0) : bAFull, rAccEmpty = PAIR ? tc::mapa_u32(bAccEmpty, 0) : bAccEmpty;
+    const uint32_t rBFull = PAIR ? tc::mapa_u32(bBFull, 0) : bBFull;
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(sTmem));
     TC_PHASE(1, tid == 0);
@@ -530,7 +545,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         uint32_t gs = 0, gmod = 0;
         const uint32_t k6400 = a.k6400;
         int tg = 0; (void) tg;
-        tc_walker wk;
+        tc_walker wk(PAIR, (int) cta_rank);
         tc_seg sg;
         while (wk.next(a, sg)) {
             const int nst = sg.k1 - sg.k0;
@@ -571,7 +586,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    tc::mbar_arrive(bAFull + 8 * as);
+                    if (PAIR) tc::mbar_arrive_cluster(rAFull + 8 * as); else tc::mbar_arrive(bAFull + 8 * as);
                     tc::mbar_arrive(bREmpty + 8 * rs);
                     if (warp == 0) TC_TRACE(3, (int) g);
                     if (warp == 7) TC_TRACE(5, (int) g);
@@ -585,19 +600,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         int bs = 0;
         uint32_t b_ph = 0;
         int tg = 0; (void) tg;
-        tc_walker wk;
+        tc_walker wk(PAIR, (int) cta_rank);
         tc_seg sg;
         while (wk.next(a, sg)) {
             const tc_tile & t = sg.t;
-            const int nbox = (t.nvalid + TC_B_BOX - 1) / TC_B_BOX;            // only the boxes that hold valid columns
+            // only the boxes that hold valid columns; CTA pair: this CTA's half of the N = 16-rounded columns, in 32-column boxes
+            const int n16 = (t.nvalid + 15) & ~15, half = n16 >> 1;
+            const int nbox = PAIR ? (half + TC_B_BOX_P - 1) / TC_B_BOX_P : (t.nvalid + TC_B_BOX - 1) / TC_B_BOX;
+            const int col0 = t.pos0 + (PAIR ? (int) cta_rank * half : 0);
             for (int it = sg.k0; it < sg.k1; ++it) {
                 tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
                 if (lane == 0) TC_TRACE(4, tg);
                 ++tg;
                 if (tc::elect_one()) {
-                    tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (nbox * TC_B_BOX_BYTES));
-                    for (int j = 0; j < nbox; ++j)
-                        tc::tma_load_2d(sB + bs * TC_B_BYTES + j * TC_B_BOX_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, t.pos0 + j * TC_B_BOX);
+                    if (PAIR) {
+                        // both halves of the activation tile report to the leader's barrier (it expects the bytes of both)
+                        if (cta_rank == 0) tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (2 * nbox * TC_B_BOX_P_BYTES));
+                        for (int j = 0; j < nbox; ++j)
+                            tc::tma_load_2d_2cta(sB + bs * TC_B_BYTES + j * TC_B_BOX_P_BYTES, &tmB, rBFull + 8 * bs, it * TC_KS, col0 + j * TC_B_BOX_P);
+                    } else {
+                        tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (nbox * TC_B_BOX_BYTES));
+                        for (int j = 0; j < nbox; ++j)
+                            tc::tma_load_2d(sB + bs * TC_B_BYTES + j * TC_B_BOX_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, col0 + j * TC_B_BOX);
+                    }
                 }
                 __syncwarp();
                 if (++bs == BS) { bs = 0; b_ph ^= 1; }
@@ -608,7 +633,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         int rs = 0;
         uint32_t r_ph = 0;
         int tg = 0; (void) tg;
-        tc_walker wk;
+        tc_walker wk(PAIR, (int) cta_rank);
         tc_seg sg;
         while (wk.next(a, sg)) {
             const tc_tile & t = sg.t;
@@ -628,14 +653,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             }
         }
     } else if (warp == TC_W_MMA) {
-        // ===== MMA issue (whole warp in step, one elected lane issues) ====================================================
-        constexpr uint32_t idesc0 = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, TC_M, 0);
+        // ===== MMA issue (whole warp in step, one elected lane issues; CTA pair: the leader only) =========================
+        if (!PAIR || cta_rank == 0) {
+        constexpr uint32_t idesc0 = tc::umma_idesc(/*f32*/ 1, /*f16*/ 0, /*f16*/ 0, PAIR ? 2 * TC_M : TC_M, 0);
         const uint64_t db0 = tc::umma_desc_sw128(sB);
         const uint32_t ta0 = tmem + (uint32_t) TC_A_COL0;
         int as = 0, bs = 0;
         uint32_t a_ph = 0, b_ph = 0, acc = 0, acc_ph = 0;
         int tg = 0; (void) tg;
-        tc_walker wk;
+        tc_walker wk(PAIR, 0);
         tc_seg sg;
         while (wk.next(a, sg)) {
             tc::mbar_wait(bAccEmpty + 8 * acc, acc_ph ^ 1);
@@ -656,11 +682,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 const uint64_t db = db0 + (uint64_t) (bs * (TC_B_BYTES >> 4));
                 if (tc::elect_one()) {
                     TC_TRACE(9, tg);
+                    if (PAIR) {
 #pragma unroll
-                    for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
-                    TC_TRACE(10, tg);
-                    tc::tc_commit(bAEmpty + 8 * as);
-                    tc::tc_commit(bBEmpty + 8 * bs);
+                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts_2cta(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                        TC_TRACE(10, tg);
+                        tc::tc_commit2_mc(bAEmpty + 8 * as, 3);
+                        tc::tc_commit2_mc(bBEmpty + 8 * bs, 3);
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                        TC_TRACE(10, tg);
+                        tc::tc_commit(bAEmpty + 8 * as);
+                        tc::tc_commit(bBEmpty + 8 * bs);
+                    }
                     TC_TRACE(11, tg);
                 }
                 __syncwarp();
@@ -669,15 +703,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 if (++as == AS) { as = 0; a_ph ^= 1; }
                 if (++bs == BS) { bs = 0; b_ph ^= 1; }
             }
-            if (tc::elect_one()) tc::tc_commit(bAccFull + 8 * acc);
+            if (tc::elect_one()) { if (PAIR) tc::tc_commit2_mc(bAccFull + 8 * acc, 3); else tc::tc_commit(bAccFull + 8 * acc); }
             __syncwarp();
             acc ^= 1; if (acc == 0) acc_ph ^= 1;
+        }
         }
     } else if (warp < TC_W_RAW) {
         // ===== epilogue: TMEM -> registers -> global (coalesced along rows; MUL_MAT_ID scatters columns) ===================
         const int q = warp & 3;
         uint32_t acc = 0, acc_ph = 0;
-        tc_walker wk;
+        tc_walker wk(PAIR, (int) cta_rank);
         tc_seg sg;
         while (wk.next(a, sg)) {
             const tc_tile & t = sg.t;
@@ -746,7 +781,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             TC_PHASE(6, warp == TC_W_EPI && lane == 0 && g_tc_phase[6] < g_tc_phase[0]);
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bAccEmpty + 8 * acc);
+            if (lane == 0) { if (PAIR) tc::mbar_arrive_cluster(rAccEmpty + 8 * acc); else tc::mbar_arrive(bAccEmpty + 8 * acc); }
             if (turnstile) {
                 __threadfence();
                 __syncwarp();
@@ -770,10 +805,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         }
     }
 #endif
+    if (PAIR) tc::cluster_sync();            // the peer may still arrive on this CTA's barriers
     if (warp == TC_W_TMA) {
         __syncwarp();
         tc::tc_fence_after();
-        tc::tmem_dealloc(tmem, 512);
+        if (PAIR) tc::tmem_dealloc2(tmem, 512); else tc::tmem_dealloc(tmem, 512);
     }
 }
 
@@ -794,10 +830,10 @@ encode_tiled_fn get_encode() {
 
 bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
 
-template <int TYPE>
+template <int TYPE, bool PAIR>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     static std::atomic<bool> configured[16];
-    auto kern = mmq_tc_f16_kernel<TYPE>;
+    auto kern = mmq_tc_f16_kernel<TYPE, PAIR>;
     using cfg_t = tc_cfg<raw_row<TYPE>::value>;
     if (!configured[ctx->device & 15].load(std::memory_order_acquire)) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, cfg_t::SMEM));
@@ -807,8 +843,13 @@ int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, 
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned) a.grid); cfg.blockDim = dim3(TC_THREADS);
         cfg.dynamicSmemBytes = cfg_t::SMEM; cfg.stream = ctx->stream;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         int na = 0;
+        if (PAIR) {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
         if (ctx->pdl && ctx->tc_pdl && a.split_k == 1) {      // (split K: a memset sits between the two kernels, nothing to overlap)
             attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             attr[na].val.programmaticStreamSerializationAllowed = 1;
@@ -822,12 +863,13 @@ int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, 
     return B200_OK;
 }
 
+template <bool PAIR>
 int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
     switch (type) {
-        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K>(ctx, tmw, tm, a);
-        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0>(ctx, tmw, tm, a);
-        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0>(ctx, tmw, tm, a);
-        case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_K: return launch_one<B200_TYPE_Q4_K, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K, PAIR>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -856,6 +898,7 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
 struct tc_plan {
     int     nt;          // tile width
     int     split_k;
+    bool    pair;        // CTA pairs on 256-row tiles (MM_PLAIN)
     int64_t n, batches, row_tiles, col_tiles, n_tiles;
     size_t  off_xh, off_sc, off_yc, off_sync, total;
 };
@@ -867,23 +910,24 @@ struct tc_multi {            // several matrices per launch: P.m is the padded t
     float * Y[3];
 };
 
-// Estimated clocks of one 64-K stage of a tile with w valid columns: the MMA (2 clocks per column of N, N = w rounded up to 16)
-// against the shared-memory traffic at 128 bytes per clock (activation boxes written by TMA + N rows read by the MMA + raw weight
-// blocks written and read once), whichever is longer.
-static double tc_stage_clocks(int64_t w, int raw_stage_bytes) {
-    const double n16 = (double) ((w + 15) / 16 * 16), boxes = (double) ((w + TC_B_BOX - 1) / TC_B_BOX);
-    const double smem = (boxes * TC_B_BOX_BYTES + n16 * 128.0 + 2.0 * raw_stage_bytes) / 128.0;
-    return (2.0 * n16 > smem ? 2.0 * n16 : smem) + 24.0;
+// Estimated clocks of one 64-K stage of a tile with w valid columns: the MMA (2 clocks per column of N, N = w rounded up to 16, for a
+// single CTA's 128 rows as for a pair's 256) against the bytes one SM pulls through L2 for it — activation boxes + raw weight blocks
+// — at the ~42.6 B/clk an SM gets when all 148 pull (profiles/r02_summary.md), whichever is longer.
+static double tc_stage_clocks(int64_t w, int raw_stage_bytes, bool pair) {
+    const double n16 = (double) ((w + 15) / 16 * 16);
+    const double act = pair ? (double) (((int64_t) n16 / 2 + TC_B_BOX_P - 1) / TC_B_BOX_P) * TC_B_BOX_P_BYTES : (double) ((w + TC_B_BOX - 1) / TC_B_BOX) * TC_B_BOX_BYTES;
+    const double l2 = (act + raw_stage_bytes) / 42.6;
+    return (2.0 * n16 > l2 ? 2.0 * n16 : l2) + 24.0;
 }
 
-// longest chain of stages any CTA walks when the tiles of a MUL_MAT are dealt round robin (column tile fastest)
-static double tc_makespan(int64_t row_tiles, int64_t n, int64_t batches, int nt, int sk, int64_t stages, int sms, int raw_stage_bytes) {
+// longest chain of stages any CTA (or CTA pair) walks when the tiles of a MUL_MAT are dealt round robin (column tile fastest)
+static double tc_makespan(int64_t row_tiles, int64_t n, int64_t batches, int nt, int sk, int64_t stages, int units, int raw_stage_bytes, bool pair) {
     const int64_t col_tiles = (n + nt - 1) / nt, n_tiles = row_tiles * col_tiles * batches, items = n_tiles * sk;
     const int64_t last_w = n - (col_tiles - 1) * nt;
-    const double c_full = tc_stage_clocks(nt, raw_stage_bytes), c_last = tc_stage_clocks(last_w, raw_stage_bytes);
+    const double c_full = tc_stage_clocks(nt, raw_stage_bytes, pair), c_last = tc_stage_clocks(last_w, raw_stage_bytes, pair);
     const double per_item = (double) (stages / sk) + 24.0;          // + pipeline fill / epilogue hand-over in stage units (measured order of magnitude)
-    const int64_t G = items < sms ? items : sms;
-    if (items > 64 * (int64_t) sms) {                               // many waves: the average is what counts
+    const int64_t G = items < units ? items : units;
+    if (items > 64 * (int64_t) units) {                             // many waves: the average is what counts
         const double avg = (c_full * (col_tiles - 1) + c_last) / (double) col_tiles;
         return avg * per_item * (double) ((items + G - 1) / G);
     }
@@ -900,41 +944,50 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
     tc_plan p;
     p.batches   = P.mode == MM_PLAIN ? P.ne12 * P.ne13 : 1;
     p.n         = P.mode == MM_PLAIN ? P.ne11 : n_pos;
-    p.row_tiles = (P.m + TC_M - 1) / TC_M;
-    if (M) {                 // every matrix padded to whole tiles (must match tc_args::rt_end)
-        p.row_tiles = 0;
-        for (int j = 0; j < M->n_mats; ++j) p.row_tiles += (M->m[j] + TC_M - 1) / TC_M;
-    }
+    auto row_tiles_of = [&](int tm) {
+        if (!M) return (P.m + tm - 1) / tm;
+        int64_t rt = 0;              // every matrix padded to whole tiles (must match tc_args::rt_end)
+        for (int j = 0; j < M->n_mats; ++j) rt += (M->m[j] + tm - 1) / tm;
+        return rt;
+    };
     const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : 36));
     const int forced = ctx->tc_nt >= 192 ? 192 : (ctx->tc_nt >= 128 ? 128 : (ctx->tc_nt > 0 ? 64 : 0));
     p.split_k = 1;
+    p.pair = false;
     if (P.mode == MM_PLAIN) {
-        // tile width and split K by the estimated critical path.  ctx->tc_split_k: 0 = never, 1 = auto (long K only: the second
-        // half of a tile is added through a turnstile, which pays off when the K loop is long), 2 / 4 = forced
+        // tile width, CTA pairing and split K by the estimated critical path.  ctx->tc_split_k: 0 = never, 1 = auto (long K only: the
+        // later parts of a tile are added through a turnstile, which pays off when the K loop is long), 2 / 4 = forced;
+        // ctx->tc_pair: 0 = never, 1 = auto, 2 = always
         const int64_t stages = P.k / TC_KS;
         double best = 0.0;
         p.nt = 0;
-        for (const int nt : {192, 128, 64}) {
-            if (forced && nt != forced) continue;
-            if (!forced && nt > 64 && p.n <= nt - 64) continue;      // a narrower width already covers n with one tile
-            for (const int sk : {1, 2, 4}) {
-                if (sk > 1) {
-                    if (ctx->tc_split_k == 0 || P.n_peers > 0 || (P.k / 256) % sk != 0) continue;
-                    if (ctx->tc_split_k == 1 && (sk > 2 || P.k < 8192)) continue;
-                    if (ctx->tc_split_k > 1 && sk != ctx->tc_split_k) continue;
-                } else if (ctx->tc_split_k > 1 && (P.k / 256) % ctx->tc_split_k == 0 && P.n_peers == 0) continue;
-                double t = tc_makespan(p.row_tiles, p.n, p.batches, nt, sk, stages, ctx->sm_count, raw_stage_bytes);
-                if (sk > 1) t *= 1.05;                                // the turnstile and the reductions are not free
-                if (p.nt == 0 || t < best) { best = t; p.nt = nt; p.split_k = sk; }
+        for (const int pair : {0, 1}) {
+            if ((pair && ctx->tc_pair == 0) || (!pair && ctx->tc_pair == 2)) continue;
+            const int64_t rts = row_tiles_of(pair ? 2 * TC_M : TC_M);
+            const int units = pair ? ctx->sm_count / 2 : ctx->sm_count;
+            for (const int nt : {192, 128, 64}) {
+                if (forced && nt != forced) continue;
+                if (!forced && nt > 64 && p.n <= nt - 64) continue;      // a narrower width already covers n with one tile
+                for (const int sk : {1, 2, 4}) {
+                    if (sk > 1) {
+                        if (pair || ctx->tc_split_k == 0 || P.n_peers > 0 || (P.k / 256) % sk != 0) continue;
+                        if (ctx->tc_split_k == 1 && (sk > 2 || P.k < 8192)) continue;
+                        if (ctx->tc_split_k > 1 && sk != ctx->tc_split_k) continue;
+                    } else if (!pair && ctx->tc_split_k > 1 && (P.k / 256) % ctx->tc_split_k == 0 && P.n_peers == 0) continue;
+                    double t = tc_makespan(rts, p.n, p.batches, nt, sk, stages, units, raw_stage_bytes, pair != 0);
+                    if (sk > 1) t *= 1.05;                                // the turnstile and the reductions are not free
+                    if (p.nt == 0 || t < best) { best = t; p.nt = nt; p.split_k = sk; p.pair = pair != 0; }
+                }
             }
         }
-        if (p.nt == 0) p.nt = forced ? forced : 192;
+        if (p.nt == 0) { p.nt = forced ? forced : 192; p.pair = ctx->tc_pair == 2; }
     } else {
         // MUL_MAT_ID: the positions per expert are only known on the device; take the width that holds an average expert's share
         // with some margin in one tile (a tile costs what its valid columns cost)
         const int64_t avg = n_pos / (P.n_expert > 0 ? P.n_expert : 1);
         p.nt = forced ? forced : (avg <= 48 ? 64 : (avg <= 100 ? 128 : 192));
     }
+    p.row_tiles = row_tiles_of(p.pair ? 2 * TC_M : TC_M);
     p.col_tiles = P.mode == MM_PLAIN ? (p.n + p.nt - 1) / p.nt : (n_pos + p.nt - 1) / p.nt + P.n_expert;
     p.n_tiles   = p.row_tiles * p.col_tiles * p.batches;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
@@ -943,7 +996,7 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
     p.off_yc   = p.off_sc + up((size_t) n_pos * 4);
     p.off_sync = p.off_yc + up((size_t) n_pos * 4);
     // (room for the turnstiles of the narrowest tiling: the scratch is reserved before options may change the plan)
-    const int64_t max_tiles = p.row_tiles * (P.mode == MM_PLAIN ? (p.n + 63) / 64 : (n_pos + 63) / 64 + P.n_expert) * p.batches;
+    const int64_t max_tiles = row_tiles_of(TC_M) * (P.mode == MM_PLAIN ? (p.n + 63) / 64 : (n_pos + 63) / 64 + P.n_expert) * p.batches;
     p.total    = p.off_sync + up((size_t) max_tiles * 4 * sizeof(int32_t));
     return p;
 }
@@ -981,7 +1034,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     CUtensorMap tmb;
     const cuuint64_t gdim[2]    = {(cuuint64_t) P.k, (cuuint64_t) n_pos};
     const cuuint64_t gstride[1] = {(cuuint64_t) P.k * sizeof(__half)};
-    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) TC_B_BOX};
+    const cuuint32_t box[2]     = {(cuuint32_t) TC_KS, (cuuint32_t) (pl.pair ? TC_B_BOX_P : TC_B_BOX)};
     const cuuint32_t estr[2]    = {1, 1};
     const CUresult cr = get_encode()(&tmb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, Xh, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1015,11 +1068,12 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     a.Y = P.Y; a.colscale = sc; a.ycol = P.mode == MM_PLAIN ? nullptr : yc;
     a.mode = P.mode; a.n_expert = P.n_expert; a.expert_bounds = P.expert_bounds;
     a.n_mats = M ? M->n_mats : 1;
+    const int tm = pl.pair ? 2 * TC_M : TC_M;
     if (M) {
         int rt = 0;
         for (int j = 0; j < 3; ++j) {
             const int jj = j < M->n_mats ? j : M->n_mats - 1;
-            if (j < M->n_mats) rt += (int) ((M->m[j] + TC_M - 1) / TC_M);
+            if (j < M->n_mats) rt += (int) ((M->m[j] + tm - 1) / tm);
             a.rt_end[j] = rt; a.m_j[j] = (int) M->m[jj]; a.Y_j[j] = M->Y[jj];
         }
     }
@@ -1034,11 +1088,12 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
     for (int p = 0; p < P.n_peers; ++p) a.peer_Y[p] = P.peer_Y[p];
     const int64_t items = pl.n_tiles * a.split_k;
     a.grid = (int) (items < ctx->sm_count ? items : ctx->sm_count);
+    if (pl.pair) { const int64_t cl = ctx->sm_count / 2; a.grid = 2 * (int) (items < cl ? items : cl); }
     if (a.split_k > 1) {
         a.tile_sync = (int32_t *) (ws + pl.off_sync);
         B200_CUDA_TRY(cudaMemsetAsync(a.tile_sync, 0, (size_t) pl.n_tiles * 4 * sizeof(int32_t), ctx->stream));
     }
-    return launch_type(ctx, type, tmw, tmb, a);
+    return pl.pair ? launch_type<true>(ctx, type, tmw, tmb, a) : launch_type<false>(ctx, type, tmw, tmb, a);
 }
 
 // several weight matrices x the same activations (caller checked: same type / k / row size, MM_PLAIN without batch dims)
@@ -1054,7 +1109,7 @@ int b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const 
     int64_t padded = 0;
     for (int j = 0; j < n_mats; ++j) {
         M.W[j] = (const uint8_t *) a[j]->data; M.m[j] = a[j]->ne[1]; M.Y[j] = (float *) d[j]->data;
-        padded += (a[j]->ne[1] + TC_M - 1) / TC_M * TC_M;
+        padded += (a[j]->ne[1] + 2 * TC_M - 1) / (2 * TC_M) * (2 * TC_M);      // whole 256-row tiles: valid for single CTAs and for pairs
     }
     P.m = padded;
     if (!b200_tc_supported(ctx, a[0]->type, P)) return B200_E_UNSUPPORTED;

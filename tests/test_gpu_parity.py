@@ -260,6 +260,36 @@ def test_tc_gemm_llama_shape_linearity_and_tiles(pkg, gpu_ctx, name):
     assert torch.equal(Y[:, :256], Y[:, 256:512]) and torch.equal(Y[:, :256], Y[:, 3840:])      # W repeats every 256 rows
 
 
+@pytest.mark.parametrize("name", TC_TYPES)
+@pytest.mark.parametrize("m,k,n", [(1000, 4096, 77), (4096, 4096, 512), (2048, 8192, 200)])
+def test_tc_gemm_tilings_give_the_same_bits(pkg, gpu_ctx, orc, name, m, k, n):
+    """the sum over K of an output element is formed in the same order whatever the tiling: every tile width (64 / 128 / 192 columns, the
+    last tile of a row narrower), and CTA pairs on 256-row tiles (cta_group::2, option tc_pair = 2), must give the bits of the default
+    plan; split K re-associates the two halves (fp32 rounding only).  Sampled rows against the oracle."""
+    import torch
+    t = TYPES[name]
+    if t == TYPES["q6_K"] and k % 2048:
+        pytest.skip("Q6_K takes the tensor-core path only for k % 2048 == 0")
+    rng = np.random.default_rng(zlib.crc32(repr((name, m, k, n)).encode()))
+    Wn = np.tile(random_blocks(t, 250, k, rng), ((m + 249) // 250, 1))[:m]
+    W = dev(Wn)
+    Xn = rng.standard_normal((n, k)).astype(np.float32)
+    X = dev(Xn)
+    gpu_ctx.set_option("tc_split_k", 0)
+    try:
+        base = pkg.mul_mat(gpu_ctx, t, W, X)
+        rows = np.sort(rng.choice(m, 48, replace=False))
+        assert nmse(oracle_mul_mat(orc, t, np.ascontiguousarray(Wn[rows]), Xn), base.cpu().numpy()[:, rows]) <= NMSE_TOL
+        for nt in (64, 128, 192):
+            for pair in (0, 2):
+                gpu_ctx.set_option("tc_nt", nt); gpu_ctx.set_option("tc_pair", pair)
+                assert torch.equal(pkg.mul_mat(gpu_ctx, t, W, X), base), (nt, pair)
+        gpu_ctx.set_option("tc_nt", 0); gpu_ctx.set_option("tc_pair", 0); gpu_ctx.set_option("tc_split_k", 2)
+        assert nmse(base.cpu().numpy(), pkg.mul_mat(gpu_ctx, t, W, X).cpu().numpy()) <= 1e-10
+    finally:
+        gpu_ctx.set_option("tc_nt", 0); gpu_ctx.set_option("tc_pair", 0); gpu_ctx.set_option("tc_split_k", 1)
+
+
 # ---- (4) MUL_MAT_ID --------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", list(TYPES))
 def test_mul_mat_id_golden_strided_ids(pkg, gpu_ctx, name):

@@ -1,32 +1,41 @@
-"""GPU tool: tcgen05 GEMM with single CTAs vs CTA pairs (cta_group::2): agreement and speed on the Llama-3-8B prefill shapes."""
+"""GPU tool: tcgen05 prefill GEMM, CTA pairs (cta_group::2, option tc_pair = 2) against single CTAs: same bits? time per shape (CUDA graph)."""
 import sys
 from pathlib import Path
-import numpy as np
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 import torch
-ROOT = Path(__file__).resolve().parents[1]; sys.path.insert(0, str(ROOT))
 from __graft_entry__ import load_package
-from tests.util import nmse, random_blocks
+import bench
 pkg = load_package()
-ctx = pkg.Context(0, stream="torch")
-rng = np.random.default_rng(1)
-TYPES = {"q4_K": 12, "q8_0": 8, "q4_0": 2}
-for name, t in TYPES.items():
-    for m, k, n in ((4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (128256, 4096, 512), (2048, 1024, 300)):
-        W = torch.from_numpy(random_blocks(t, 256, k, rng)).cuda().repeat((m + 255) // 256, 1)[:m].contiguous()
+stream = torch.cuda.Stream()
+ctx = pkg.Context(0, stream=stream.cuda_stream)
+gen = torch.Generator(device="cuda"); gen.manual_seed(1)
+shapes = [(1024, 4096, 512), (4096, 4096, 512), (14336, 4096, 512), (4096, 14336, 512), (128256, 4096, 512), (4096, 4096, 100), (1000, 4096, 77)]
+if len(sys.argv) > 1 and sys.argv[1] == "small":
+    shapes = [(4096, 4096, 512), (1000, 4096, 77)]
+for tname, t, make in (("q4_K", 12, bench.device_random_q4k), ("q8_0", 8, bench.device_random_q8_0)):
+    for (m, k, n) in shapes:
+        copies = 1 if m > 100000 else 3
+        Ws = [make(torch, m, k, gen) for _ in range(copies)]
         X = torch.randn((n, k), device="cuda")
-        ys, row = [], []
+        out = {}
+        line = f"{tname} {m}x{k}x{n}:"
         for pair in (0, 2):
             ctx.set_option("tc_pair", pair)
             Y = torch.empty((n, m), device="cuda")
-            for _ in range(3):
-                pkg.mul_mat(ctx, t, W, X, out=Y)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            iters = 20 if m < 100000 else 4
-            e0.record()
-            for _ in range(iters):
-                pkg.mul_mat(ctx, t, W, X, out=Y)
-            e1.record(); torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / iters
-            row.append(f"pair={pair}: {ms * 1e3:7.1f}us {2.0 * m * n * k / ms / 1e9:6.0f}TF")
-            ys.append(Y.cpu().numpy())
-        print(f"{name} {m}x{k}x{n}: " + " | ".join(row) + f" | nmse(pair, single) = {nmse(ys[0], ys[1]):.2e}", flush=True)
+            with torch.cuda.stream(stream):
+                for i in range(3): pkg.mul_mat(ctx, t, Ws[0], X, out=Y)
+                stream.synchronize()
+                out[pair] = Y.clone()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    for i in range(12): pkg.mul_mat(ctx, t, Ws[i % copies], X, out=Y)
+                g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream); g.replay(); e1.record(stream); stream.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / 12
+            line += f"  pair={pair} {us:7.1f} us ({2.0 * m * k * n / us * 1e-6:5.0f} TF)"
+        same = torch.equal(out[0], out[2])
+        line += f"  same bits: {same}" + ("" if same else f"  max diff {float((out[0] - out[2]).abs().max()):.3e} of {float(out[0].abs().max()):.3e}")
+        print(line, flush=True)
+        del Ws
+ctx.set_option("tc_pair", 0)
