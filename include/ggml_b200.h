@@ -57,12 +57,15 @@ enum {
 /* enum ggml_type values this path understands (ggml/include/ggml.h:389-432) */
 enum {
     B200_TYPE_F32  = 0,
+    B200_TYPE_F16  = 1,      /* graph ops only (KV cache, masks); MUL_MAT weights of this type go to b200_mul_mat_f */
     B200_TYPE_Q4_0 = 2,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
     B200_TYPE_Q4_K = 12,
     B200_TYPE_Q6_K = 14,
     B200_TYPE_I32  = 26,
+    B200_TYPE_I64  = 27,     /* SET_ROWS indices */
+    B200_TYPE_BF16 = 30,     /* graph ops only */
 };
 
 /* A ggml tensor as the kernels see it: ne[] in elements, nb[] in bytes, ne[0] contiguous
@@ -295,6 +298,56 @@ B200_API int  b200_rowsplit_mul_mat_main(b200_rowsplit * rs, b200_ctx * main_ctx
                                          const int64_t * row_lo, const int64_t * row_hi, const b200_tensor * src1, const b200_tensor * dst);
 B200_API int  b200_rowsplit_synchronize(b200_rowsplit * rs);
 B200_API b200_ctx * b200_rowsplit_ctx(b200_rowsplit * rs, int idx);
+
+
+/* ---- the other ops of a Llama graph ---------------------------------------------------------
+ * So that a cgraph stays on the device between its MUL_MATs.  Each call restates the reference's CPU forward function of the op
+ * (ggml/src/ggml-cpu/ops.cpp, binary-ops.cpp, unary-ops.cpp; the exact lines are cited in csrc/ops.cu) on device tensors with
+ * ggml's shapes, byte strides and broadcasting rules, queued on the context's stream.  F32 data unless said otherwise; a form a
+ * function does not implement returns B200_E_UNSUPPORTED (the shell's supports_op() answers false for it, ggml then runs the node on
+ * another backend). */
+enum { B200_OP_ADD = 0, B200_OP_SUB = 1, B200_OP_MUL = 2, B200_OP_DIV = 3 };
+/* enum ggml_glu_op (ggml/include/ggml.h:616-625) */
+enum { B200_GLU_REGLU = 0, B200_GLU_GEGLU = 1, B200_GLU_SWIGLU = 2, B200_GLU_SWIGLU_OAI = 3, B200_GLU_GEGLU_ERF = 4, B200_GLU_GEGLU_QUICK = 5 };
+/* enum ggml_unary_op (ggml/include/ggml.h:589-614), the members implemented here */
+enum { B200_UNARY_ABS = 0, B200_UNARY_SGN = 1, B200_UNARY_NEG = 2, B200_UNARY_STEP = 3, B200_UNARY_TANH = 4, B200_UNARY_RELU = 6,
+       B200_UNARY_SIGMOID = 7, B200_UNARY_GELU = 8, B200_UNARY_GELU_QUICK = 9, B200_UNARY_SILU = 10, B200_UNARY_EXP = 13, B200_UNARY_GELU_ERF = 16 };
+/* dst = src0 (op) src1, src1 repeated into src0's shape (ggml_can_repeat); any strides */
+B200_API int b200_op_binary(b200_ctx * ctx, int op, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+/* GGML_OP_ADD_ID: dst[:, i1, i2] = src0[:, i1, i2] + src1[:, ids[i1, i2]] (expert biases of MUL_MAT_ID) */
+B200_API int b200_op_add_id(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * ids, const b200_tensor * dst);
+/* GGML_OP_GLU: dst = act(x) * g; src1 != NULL: x = src0, g = src1 (ggml_glu_split); src1 == NULL: the two halves of src0's rows
+ * (`swapped` exchanges them).  alpha / limit: SWIGLU_OAI only. */
+B200_API int b200_op_glu(b200_ctx * ctx, int glu_op, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst,
+                         int swapped, float alpha, float limit);
+B200_API int b200_op_unary(b200_ctx * ctx, int unary_op, const b200_tensor * src0, const b200_tensor * dst);      /* contiguous tensors */
+B200_API int b200_op_unary_supported(int unary_op);
+B200_API int b200_op_scale(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst, float scale, float bias);   /* dst = src0 * scale + bias */
+B200_API int b200_op_rms_norm(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst, float eps);
+/* GGML_OP_ROPE, modes normal (0) and NeoX (2), F32 or F16 rows; op_params = the node's 15 int32 parameter words */
+B200_API int b200_op_rope(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * pos, const b200_tensor * freq_factors /* or NULL */,
+                          const b200_tensor * dst, const int32_t * op_params);
+/* GGML_OP_SOFT_MAX: softmax(src0 * scale + slope(head) * mask) over ne0, mask F16 or F32 broadcast over heads / batches, optional sinks */
+B200_API int b200_op_soft_max(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * mask /* or NULL */, const b200_tensor * sinks /* or NULL */,
+                              const b200_tensor * dst, float scale, float max_bias);
+/* GGML_OP_CPY / CONT / DUP between F32 / F16 / BF16 tensors with the same number of elements, any strides */
+B200_API int b200_op_cpy(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst);
+/* GGML_OP_GET_ROWS: rows of an F32 / F16 / BF16 / Q4_0 / Q8_0 / Q4_K / Q6_K matrix by I32 index -> F32 (token embeddings) */
+B200_API int b200_op_get_rows(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * idx, const b200_tensor * dst);
+/* GGML_OP_SET_ROWS: F32 rows scattered by I64 / I32 index into an F32 / F16 / BF16 tensor (KV-cache store) */
+B200_API int b200_op_set_rows(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * idx, const b200_tensor * dst);
+/* MUL_MAT with F32 / F16 / BF16 src0 (attention: K.q, V.p), src0 rows contiguous, batch broadcast like b200_mul_mat */
+B200_API int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+B200_API int b200_mul_mat_f_supported(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+/* N2 — MUL_MAT(+ bias)(+ gate MUL_MAT (+ bias) + GLU) for one activation column per batch in ONE launch (reference:
+ * ggml_cuda_should_fuse_mul_mat_vec_q, ggml/src/ggml-cuda/ggml-cuda.cu:2499-2535, kernel mmvq.cu:440-477):
+ *   gate == NULL: dst = up x + bias_up
+ *   gate != NULL: dst = glu(gate x + bias_gate, up x + bias_up)        (act on the gate product, as ggml_glu_split(gate, up))
+ * up / gate: quantized matrices of one type and shape, x: F32 with ne[1] == 1, biases: F32 shaped like dst or NULL. */
+B200_API int b200_mul_mat_fused(b200_ctx * ctx, const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x,
+                                const b200_tensor * bias_up, const b200_tensor * bias_gate, int glu_op, const b200_tensor * dst);
+B200_API int b200_mul_mat_fused_supported(const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x,
+                                          const b200_tensor * bias_up, const b200_tensor * bias_gate, int glu_op, const b200_tensor * dst);
 
 #ifdef __cplusplus
 }

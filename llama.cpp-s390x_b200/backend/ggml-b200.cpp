@@ -51,6 +51,8 @@ struct b200_backend_ctx {
     std::string name;
     b200_ctx *  ctx;
     long        n_graphs = 0, n_mul_mat = 0, n_mul_mat_id = 0, n_fused_groups = 0;      // GGML_B200_STATS=1 prints them on free
+    long        n_extra_ops = 0, n_fused_mm = 0;
+    bool        fuse = true;               // GGML_B200_FUSE=0: MUL_MAT + bias / gate + GLU run as separate nodes
     void *      copy_event = nullptr;      // orders cpy_tensor_async after this backend's queued work
     b200_rowsplit * rs = nullptr;          // row-split driver of the split buffer type this backend last computed with
     const void *    rs_key = nullptr;
@@ -394,8 +396,8 @@ const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ct
 void backend_free(ggml_backend_t backend) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     if (const char * e = getenv("GGML_B200_STATS"); e && *e == '1') {
-        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld\n", bctx->n_graphs, bctx->n_mul_mat,
-                bctx->n_mul_mat_id, bctx->n_fused_groups);
+        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld other_ops=%ld fused_mul_mat=%ld\n", bctx->n_graphs,
+                bctx->n_mul_mat, bctx->n_mul_mat_id, bctx->n_fused_groups, bctx->n_extra_ops, bctx->n_fused_mm);
     }
     if (bctx->copy_event) b200_event_destroy(bctx->device, bctx->copy_event);
     if (bctx->rs) b200_rowsplit_destroy(bctx->rs);
@@ -418,6 +420,129 @@ void backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * tensor
 
 bool is_view_op(ggml_op op) {
     return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE;
+}
+
+// ---- the other ops of a Llama graph: which forms the kernels take, and their dispatch ----------------
+bool is_f32(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32; }
+bool is_float_type(ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16 || t == GGML_TYPE_BF16; }
+bool is_quant_weight(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K; }
+
+bool extra_op_supported(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1], * c = op->src[2];
+    switch (op->op) {
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
+            return is_f32(a) && is_f32(b) && is_f32(op) && ggml_can_repeat(b, a) && ggml_are_same_shape(a, op);
+        case GGML_OP_ADD_ID:
+            return is_f32(a) && is_f32(b) && is_f32(op) && c && c->type == GGML_TYPE_I32 && a->nb[0] == 4 && b->nb[0] == 4 && op->nb[0] == 4;
+        case GGML_OP_GLU:
+            return is_f32(a) && is_f32(op) && (!b || (is_f32(b) && ggml_is_contiguous_1(b))) && ggml_is_contiguous_1(a) && ggml_is_contiguous_1(op);
+        case GGML_OP_UNARY:
+            return is_f32(a) && is_f32(op) && ggml_is_contiguous(a) && ggml_is_contiguous(op) && b200_op_unary_supported((int) ggml_get_unary_op(op));
+        case GGML_OP_SCALE:
+            return is_f32(a) && is_f32(op) && ggml_is_contiguous(a) && ggml_is_contiguous(op);
+        case GGML_OP_RMS_NORM:
+            return is_f32(a) && is_f32(op) && a->nb[0] == 4 && op->nb[0] == 4;
+        case GGML_OP_ROPE: {
+            const int mode = ((const int32_t *) op->op_params)[2];
+            if (mode != GGML_ROPE_TYPE_NORMAL && mode != GGML_ROPE_TYPE_NEOX) return false;
+            if (!a || (a->type != GGML_TYPE_F32 && a->type != GGML_TYPE_F16) || op->type != a->type || !b || b->type != GGML_TYPE_I32) return false;
+            if (c && c->type != GGML_TYPE_F32) return false;
+            return a->nb[0] == ggml_type_size(a->type) && op->nb[0] == ggml_type_size(a->type) && (a->ne[0] % 2) == 0;
+        }
+        case GGML_OP_SOFT_MAX:
+            return is_f32(a) && is_f32(op) && a->nb[0] == 4 && ggml_is_contiguous(op) &&
+                   (!b || ((b->type == GGML_TYPE_F16 || b->type == GGML_TYPE_F32) && b->nb[0] == ggml_type_size(b->type))) && (!c || is_f32(c));
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP:
+            return a && is_float_type(a->type) && is_float_type(op->type) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_GET_ROWS:
+            return a && (is_float_type(a->type) || is_quant_weight(a->type)) && b && b->type == GGML_TYPE_I32 && is_f32(op) && op->nb[0] == 4;
+        case GGML_OP_SET_ROWS:
+            return is_f32(a) && a->nb[0] == 4 && b && (b->type == GGML_TYPE_I64 || b->type == GGML_TYPE_I32) && is_float_type(op->type);
+        default:
+            return false;
+    }
+}
+
+int run_extra_op(b200_backend_ctx * bctx, const ggml_tensor * node) {
+    b200_ctx * ctx = bctx->ctx;
+    const b200_tensor d = to_b200(node);
+    const b200_tensor a = node->src[0] ? to_b200(node->src[0]) : b200_tensor{};
+    const b200_tensor b = node->src[1] ? to_b200(node->src[1]) : b200_tensor{};
+    const b200_tensor c = node->src[2] ? to_b200(node->src[2]) : b200_tensor{};
+    const float * fp = (const float *) node->op_params;
+    switch (node->op) {
+        case GGML_OP_ADD:      return b200_op_binary(ctx, B200_OP_ADD, &a, &b, &d);
+        case GGML_OP_SUB:      return b200_op_binary(ctx, B200_OP_SUB, &a, &b, &d);
+        case GGML_OP_MUL:      return b200_op_binary(ctx, B200_OP_MUL, &a, &b, &d);
+        case GGML_OP_DIV:      return b200_op_binary(ctx, B200_OP_DIV, &a, &b, &d);
+        case GGML_OP_ADD_ID:   return b200_op_add_id(ctx, &a, &b, &c, &d);
+        case GGML_OP_GLU:      return b200_op_glu(ctx, (int) ggml_get_glu_op(node), &a, node->src[1] ? &b : nullptr, &d, ggml_get_op_params_i32(node, 1),
+                                                  ggml_get_op_params_f32(node, 2), ggml_get_op_params_f32(node, 3));
+        case GGML_OP_UNARY:    return b200_op_unary(ctx, (int) ggml_get_unary_op(node), &a, &d);
+        case GGML_OP_SCALE:    return b200_op_scale(ctx, &a, &d, fp[0], fp[1]);
+        case GGML_OP_RMS_NORM: return b200_op_rms_norm(ctx, &a, &d, fp[0]);
+        case GGML_OP_ROPE:     return b200_op_rope(ctx, &a, &b, node->src[2] ? &c : nullptr, &d, (const int32_t *) node->op_params);
+        case GGML_OP_SOFT_MAX: return b200_op_soft_max(ctx, &a, node->src[1] ? &b : nullptr, node->src[2] ? &c : nullptr, &d, fp[0], fp[1]);
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP:
+                               return b200_op_cpy(ctx, &a, &d);
+        case GGML_OP_GET_ROWS: return b200_op_get_rows(ctx, &a, &b, &d);
+        case GGML_OP_SET_ROWS: return b200_op_set_rows(ctx, &a, &b, &d);
+        default:               return B200_E_UNSUPPORTED;
+    }
+}
+
+// N2 (reference: ggml_cuda_should_fuse_mul_mat_vec_q, ggml-cuda.cu:2499-2535): the nodes starting at `i` are
+//   up = MUL_MAT(Wu, x) [, ADD(up, bias)] , gate = MUL_MAT(Wg, x) [, ADD(gate, bias)] , GLU(gate, up)        -> one launch
+//   y  = MUL_MAT(W, x) , ADD(y, bias)                                                                           -> one launch
+// with one activation column per batch, quantized weights, and every intermediate used by the next node of the pattern only.
+// Returns the number of nodes consumed (0: no fusion), the arguments in `f`.
+struct fused_mm { const ggml_tensor * up, * gate, * x, * bias_up, * bias_gate, * out; int glu_op; };
+
+bool bias_of(const ggml_tensor * add, const ggml_tensor * mm, const ggml_tensor ** bias) {
+    if (add->op != GGML_OP_ADD) return false;
+    const ggml_tensor * other = add->src[0] == mm ? add->src[1] : (add->src[1] == mm ? add->src[0] : nullptr);
+    if (!other || add->src[0] != mm) return false;               // (the kernel adds into the product: keep src0 = product, as llama.cpp builds it)
+    if (!is_f32(other) || !ggml_are_same_shape(other, mm) || other->nb[0] != 4) return false;
+    *bias = other;
+    return true;
+}
+
+int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f) {
+    const ggml_tensor * n0 = cgraph->nodes[i];
+    if (n0->op != GGML_OP_MUL_MAT || !is_quant_weight(n0->src[0]->type) || n0->ne[1] != 1 || split_src0(n0)) return 0;
+    f = {};
+    f.up = n0->src[0]; f.x = n0->src[1];
+    int j = i + 1;
+    const ggml_tensor * up_out = n0;
+    auto single_use = [&](int idx) { return ggml_node_has_n_uses(cgraph, idx, 1) && (cgraph->nodes[idx]->flags & GGML_TENSOR_FLAG_OUTPUT) == 0; };
+    if (j < cgraph->n_nodes && single_use(i) && bias_of(cgraph->nodes[j], n0, &f.bias_up)) { up_out = cgraph->nodes[j]; ++j; }
+    const int after_up = j;
+    // gate product, its bias, the GLU
+    if (j < cgraph->n_nodes && single_use(j - 1)) {
+        const ggml_tensor * g0 = cgraph->nodes[j];
+        if (g0->op == GGML_OP_MUL_MAT && g0->src[1] == f.x && g0->src[0]->type == f.up->type && ggml_are_same_shape(g0->src[0], f.up) &&
+            ggml_are_same_stride(g0->src[0], f.up) && !split_src0(g0)) {
+            const ggml_tensor * gate_out = g0;
+            const ggml_tensor * bg = nullptr;
+            int k = j + 1;
+            if (k < cgraph->n_nodes && single_use(j) && bias_of(cgraph->nodes[k], g0, &bg)) { gate_out = cgraph->nodes[k]; ++k; }
+            if (k < cgraph->n_nodes && single_use(k - 1)) {
+                const ggml_tensor * glu = cgraph->nodes[k];
+                if (glu->op == GGML_OP_GLU && glu->src[0] == gate_out && glu->src[1] == up_out && ggml_get_glu_op(glu) != GGML_GLU_OP_SWIGLU_OAI) {
+                    f.gate = g0->src[0]; f.bias_gate = bg; f.glu_op = (int) ggml_get_glu_op(glu); f.out = glu;
+                    j = k + 1;
+                }
+            }
+        }
+    }
+    if (!f.gate) {
+        if (!f.bias_up) return 0;
+        f.out = up_out; j = after_up;
+    }
+    const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
+    const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{}, bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
+    if (!b200_mul_mat_fused_supported(&up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d)) return 0;
+    return j - i;
 }
 
 // graph_compute: every maximal run of MUL_MAT nodes (view ops in between need no work) goes to the kernels as ONE list,
@@ -451,8 +576,33 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
         ggml_tensor * node = cgraph->nodes[i];
         if (ggml_is_empty(node) || is_view_op(node->op)) continue;
         if ((node->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) continue;
+        if (bctx->fuse) {
+            fused_mm f;
+            const int used = try_fuse_mul_mat(cgraph, i, f);
+            if (used > 0) {
+                int rc = flush();
+                if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
+                const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
+                const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{};
+                const b200_tensor bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
+                rc = b200_mul_mat_fused(bctx->ctx, &up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d);
+                if (rc != B200_OK) return failed(rc, node);
+                bctx->n_fused_mm++;
+                i += used - 1;
+                continue;
+            }
+        }
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
+                if (!is_quant_weight(node->src[0]->type)) {          // attention products: float src0
+                    int rc = flush();
+                    if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
+                    const b200_tensor a = to_b200(node->src[0]), b = to_b200(node->src[1]), d = to_b200(node);
+                    rc = b200_mul_mat_f(bctx->ctx, &a, &b, &d);
+                    if (rc != B200_OK) return failed(rc, node);
+                    bctx->n_extra_ops++;
+                    break;
+                }
                 if (split_src0(node)) {
                     int rc = flush();
                     if (rc == B200_OK) rc = split_mul_mat(bctx, node);
@@ -470,8 +620,14 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
                 bctx->n_mul_mat_id++;
                 if (rc != B200_OK) return failed(rc, node);
             } break;
-            default:
-                GGML_ABORT("ggml-b200: op %s reached graph_compute but supports_op() rejects it", ggml_op_name(node->op));
+            default: {
+                if (!extra_op_supported(node)) GGML_ABORT("ggml-b200: op %s reached graph_compute but supports_op() rejects it", ggml_op_name(node->op));
+                int rc = flush();
+                if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
+                rc = run_extra_op(bctx, node);
+                if (rc != B200_OK) return failed(rc, node);
+                bctx->n_extra_ops++;
+            }
         }
     }
     const int rc = flush();
@@ -566,11 +722,13 @@ ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char * /*params
         GGML_LOG_ERROR("ggml-b200: cannot create a context on device %d: %s\n", dctx->device, b200_last_error());
         return nullptr;
     }
+    b200_backend_ctx * bctx = new b200_backend_ctx{dctx->device, dctx->name, ctx};
+    if (const char * e = getenv("GGML_B200_FUSE"); e && *e == '0') bctx->fuse = false;
     return new ggml_backend{
         /* .guid    = */ backend_guid(),
         /* .iface   = */ k_backend_iface,
         /* .device  = */ dev,
-        /* .context = */ new b200_backend_ctx{dctx->device, dctx->name, ctx},
+        /* .context = */ bctx,
     };
 }
 
@@ -582,6 +740,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
         case GGML_OP_MUL_MAT: {
             if (!op->src[0] || !op->src[1]) return false;
             const b200_tensor a = to_b200(op->src[0]), b = to_b200(op->src[1]), d = to_b200(op);
+            if (is_float_type(op->src[0]->type)) return !split_src0(op) && b200_mul_mat_f_supported(&a, &b, &d) != 0;
             if (split_src0(op) && (op->src[1]->ne[2] * op->src[1]->ne[3] != 1 || (op->ne[1] > 1 && op->nb[1] != (size_t) op->ne[0] * 4))) return false;
             return b200_mul_mat_supported(&a, &b, &d) != 0;
         }
@@ -592,7 +751,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
             return b200_mul_mat_id_supported(&a, &b, &ids, &d) != 0;
         }
         default:
-            return false;
+            return extra_op_supported(op);
     }
 }
 

@@ -14,6 +14,8 @@
 // kernels' host launchers (other TUs)
 int    b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles);
 int    b200_launch_gemv_q4k(b200_ctx * ctx, const mm_problem & P, int nc, int64_t tiles, bool late_wait);
+int    b200_launch_gemv_fused(b200_ctx * ctx, int type, const mm_problem & P, const uint8_t * Wg, const float * bias_up, const int64_t * bu_nb,
+                              const float * bias_gate, const int64_t * bg_nb, int glu_op, int64_t batches);
 size_t b200_gemv_q4k_smem(int nc, int64_t k);
 int    b200_gemv_mma_ok(const b200_ctx * ctx, int type, const mm_problem & P);
 int    b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & P, int64_t tiles, bool late_wait, int64_t live_tiles = 0);
@@ -361,6 +363,54 @@ int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, c
 }
 
 }  // extern "C"
+
+// ---- N2: MUL_MAT (+ bias) (+ gate MUL_MAT (+ bias) + GLU), one activation column per batch ---------------------------------------
+static const char * check_fused(const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x, const b200_tensor * bu, const b200_tensor * bg,
+                                int glu_op, const b200_tensor * d) {
+    if (const char * why = check_mul_mat(up, x, d)) return why;
+    if (x->ne[1] != 1) return "one activation column per batch";
+    if (x->ne[2] * x->ne[3] > 65535) return "too many batches";
+    if (gate) {
+        if (glu_op < B200_GLU_REGLU || glu_op > B200_GLU_GEGLU_QUICK || glu_op == B200_GLU_SWIGLU_OAI) return "unsupported GLU op";
+        if (gate->type != up->type) return "gate and up must have one type";
+        for (int i = 0; i < 4; ++i) if (gate->ne[i] != up->ne[i] || gate->nb[i] != up->nb[i]) return "gate and up must have one shape and layout";
+    } else if (bg) return "gate bias without a gate";
+    for (const b200_tensor * b : {bu, bg}) {
+        if (!b) continue;
+        if (b->type != B200_TYPE_F32 || b->nb[0] != 4) return "bias must be f32 with nb[0] == 4";
+        for (int i = 0; i < 4; ++i) if (b->ne[i] != d->ne[i]) return "bias must be shaped like dst";
+    }
+    return nullptr;
+}
+
+extern "C" int b200_mul_mat_fused_supported(const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x, const b200_tensor * bias_up,
+                                            const b200_tensor * bias_gate, int glu_op, const b200_tensor * dst) {
+    return up && x && dst && check_fused(up, gate, x, bias_up, bias_gate, glu_op, dst) == nullptr;
+}
+
+extern "C" int b200_mul_mat_fused(b200_ctx * ctx, const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x, const b200_tensor * bias_up,
+                                  const b200_tensor * bias_gate, int glu_op, const b200_tensor * d) {
+    if (!ctx || !up || !x || !d) { b200_set_error("mul_mat_fused: NULL argument"); return B200_E_ARG; }
+    if (const char * why = check_fused(up, gate, x, bias_up, bias_gate, glu_op, d)) { b200_set_error("mul_mat_fused: %s", why); return B200_E_UNSUPPORTED; }
+    const int64_t batches = x->ne[2] * x->ne[3];
+    if (up->ne[1] == 0 || batches == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    mm_problem P = {};
+    P.W = (const uint8_t *) up->data; P.nb01 = up->nb[1]; P.nb02 = up->nb[2]; P.nb03 = up->nb[3];
+    P.m = up->ne[1]; P.k = up->ne[0];
+    P.X = (const float *) x->data; P.nb11 = x->nb[1]; P.nb12 = x->nb[2]; P.nb13 = x->nb[3];
+    P.ne11 = 1; P.ne12 = x->ne[2]; P.ne13 = x->ne[3];
+    P.r2 = x->ne[2] / up->ne[2]; P.r3 = x->ne[3] / up->ne[3];
+    P.Y = (float *) d->data;
+    P.mode = MM_PLAIN;
+    pending_push(ctx, d, true);
+    ctx->n_pend = 16;            // the biases may come from kernels the tracker does not know; nothing is deferred around this launch
+    const int rc = quantize_into_ws(ctx, x, 0, &P.act, nullptr);
+    if (rc) return rc;
+    return b200_launch_gemv_fused(ctx, up->type, P, gate ? (const uint8_t *) gate->data : nullptr, bias_up ? (const float *) bias_up->data : nullptr,
+                                  bias_up ? &bias_up->nb[2] : nullptr, bias_gate ? (const float *) bias_gate->data : nullptr,
+                                  bias_gate ? &bias_gate->nb[2] : nullptr, glu_op, batches);
+}
 
 // MUL_MAT with the row-split all-gather fused into the store: results also go to peer_Y[p][col*peer_m + peer_row0 + row]
 int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,

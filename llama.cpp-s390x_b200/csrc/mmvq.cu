@@ -17,6 +17,7 @@
 //                   in registers, one fragment of software prefetch, warp-shuffle reduction.
 #include "mm_problem.cuh"
 #include "quantize.cuh"
+#include "ops.cuh"
 
 // ------------------------------------------------------------------------------------------------------------------
 // generic kernel
@@ -179,6 +180,53 @@ gemv_generic(const mm_problem P) {
     for (int c = 0; c < NC; ++c) {
         const float s = warp_sum(acc[c]);
         if (lane == 0 && c < C.nc) mm_store(P, C.y[c], row, s);
+    }
+}
+
+// N2 — MUL_MAT (+ bias) (+ gate MUL_MAT (+ bias) + GLU) for one activation column per batch in one launch (the reference fuses the same
+// pattern into its mul_mat_vec_q kernel: ggml-cuda/mmvq.cu:440-477, chosen by ggml_cuda_should_fuse_mul_mat_vec_q ggml-cuda.cu:2499-2535).
+// One warp per output row walks the row of the up matrix and, if there is a gate, the same row of the gate matrix against ONE
+// fetch of the quantized activations; the epilogue adds the biases and applies the activation, so neither product goes to memory.
+struct mm_fuse {
+    const uint8_t * Wg;                   // gate matrix (same type, shape and strides as P.W) or NULL
+    const float * bias_up, * bias_gate;   // f32 [m, 1, ne12, ne13] or NULL
+    int64_t bu_nb2, bu_nb3, bg_nb2, bg_nb3;
+    int glu_op;
+};
+
+template <int TYPE>
+__global__ void __launch_bounds__(GENERIC_WARPS * 32)
+gemv_fused(const mm_problem P, const mm_fuse F) {
+    mm_cols<1> C;
+    if (!mm_resolve<1>(P, blockIdx.y, C)) return;
+    const int     lane = threadIdx.x & 31;
+    const int64_t row  = (int64_t) blockIdx.x * GENERIC_WARPS + (threadIdx.x >> 5);
+    if (row >= P.m) return;                                   // whole warp leaves together
+    const uint8_t * urow = C.W + row * P.nb01;
+    const uint8_t * grow = F.Wg ? F.Wg + (C.W - P.W) + row * P.nb01 : nullptr;
+    const int64_t   nu   = P.k >> 5;
+    float au = 0.0f, ag = 0.0f;
+    for (int64_t ib = lane; ib < nu; ib += 32) {
+        const act_unit u = load_act(P.act, C.plane_col[0], ib);
+        w_unit<TYPE> w;
+        w.load(urow, ib);
+        au += w.dot(u);
+        if (grow) {
+            w_unit<TYPE> g;
+            g.load(grow, ib);
+            ag += g.dot(u);
+        }
+    }
+    au = warp_sum(au);
+    if (grow) ag = warp_sum(ag);
+    if (lane == 0) {
+        const int64_t batch = blockIdx.y, i12 = batch % P.ne12, i13 = batch / P.ne12;
+        if (F.bias_up) au += *reinterpret_cast<const float *>(reinterpret_cast<const char *>(F.bias_up) + row * 4 + i12 * F.bu_nb2 + i13 * F.bu_nb3);
+        if (grow) {
+            if (F.bias_gate) ag += *reinterpret_cast<const float *>(reinterpret_cast<const char *>(F.bias_gate) + row * 4 + i12 * F.bg_nb2 + i13 * F.bg_nb3);
+            au = glu_value(F.glu_op, ag, au, 0.0f, 0.0f);
+        }
+        C.y[0][row] = au;
     }
 }
 
@@ -588,6 +636,25 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
 // ---- host entry points used by mul_mat.cu -------------------------------------------------------------------------
 
 // pre-quantized activations in P.act; nc = columns per tile (1..8); tiles = gridDim.y
+int b200_launch_gemv_fused(b200_ctx * ctx, int type, const mm_problem & P, const uint8_t * Wg, const float * bias_up, const int64_t * bu_nb,
+                           const float * bias_gate, const int64_t * bg_nb, int glu_op, int64_t batches) {
+    mm_fuse F = {};
+    F.Wg = Wg; F.bias_up = bias_up; F.bias_gate = bias_gate; F.glu_op = glu_op;
+    if (bias_up)   { F.bu_nb2 = bu_nb[0]; F.bu_nb3 = bu_nb[1]; }
+    if (bias_gate) { F.bg_nb2 = bg_nb[0]; F.bg_nb3 = bg_nb[1]; }
+    const dim3 grid((unsigned) ((P.m + GENERIC_WARPS - 1) / GENERIC_WARPS), (unsigned) batches);
+    switch (type) {
+        case B200_TYPE_Q4_0: gemv_fused<B200_TYPE_Q4_0><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q8_0: gemv_fused<B200_TYPE_Q8_0><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q4_K: gemv_fused<B200_TYPE_Q4_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q6_K: gemv_fused<B200_TYPE_Q6_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        default: b200_set_error("fused GEMV: unsupported weight type %d", type); return B200_E_UNSUPPORTED;
+    }
+    B200_CUDA_TRY(cudaGetLastError());
+    ctx->launches++;
+    return B200_OK;
+}
+
 int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int nc, int64_t tiles) {
     if (tiles <= 0 || P.m <= 0) return B200_OK;
     if (tiles > 65535) { b200_set_error("gemv: %lld column tiles exceed gridDim.y", (long long) tiles); return B200_E_ARG; }

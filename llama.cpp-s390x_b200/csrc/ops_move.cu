@@ -1,0 +1,197 @@
+// ops_move.cu — CPY / CONT / DUP, GET_ROWS (float and the four quantized weight types), SET_ROWS and the float MUL_MAT of attention
+// (see ops.cu for the reference functions each one restates).
+#include <cuda_bf16.h>
+#include <math.h>
+
+#include "ops.cuh"
+
+namespace {
+
+__device__ __forceinline__ float load_elem(const char * p, const int type) {
+    switch (type) {
+        case B200_TYPE_F32:  return *(const float *) p;
+        case B200_TYPE_F16:  return __half2float(*(const __half *) p);
+        default:             return __bfloat162float(*(const __nv_bfloat16 *) p);
+    }
+}
+__device__ __forceinline__ void store_elem(char * p, const int type, const float v) {
+    switch (type) {
+        case B200_TYPE_F32:  *(float *) p = v; break;
+        case B200_TYPE_F16:  *(__half *) p = __float2half_rn(v); break;
+        default:             *(__nv_bfloat16 *) p = __float2bfloat16_rn(v); break;
+    }
+}
+
+__device__ __forceinline__ float to_float(const float v) { return v; }
+__device__ __forceinline__ float to_float(const __half v) { return __half2float(v); }
+__device__ __forceinline__ float to_float(const __nv_bfloat16 v) { return __bfloat162float(v); }
+
+// ---- CPY: element i of src (in src's index order) goes to element i of dst (in dst's index order) -------------------------------
+__global__ void __launch_bounds__(OPS_THREADS) cpy_kernel(const tview a, const int ta, const tview d, const int td, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t a0, a1, a2, a3, d0, d1, d2, d3;
+        split4(i, a.ne, a0, a1, a2, a3);
+        split4(i, d.ne, d0, d1, d2, d3);
+        const float v = load_elem(a.p + a0 * a.nb[0] + a1 * a.nb[1] + a2 * a.nb[2] + a3 * a.nb[3], ta);
+        store_elem(d.p + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3], td, v);
+    }
+}
+
+// ---- one element of a row of any type GET_ROWS reads (dequantize_row_* of ggml-quants.c, element by element) -------------------
+__device__ __forceinline__ float row_elem(const uint8_t * row, const int type, const int64_t i) {
+    switch (type) {
+        case B200_TYPE_F32: return ((const float *) row)[i];
+        case B200_TYPE_F16: return __half2float(((const __half *) row)[i]);
+        case B200_TYPE_BF16: return __bfloat162float(((const __nv_bfloat16 *) row)[i]);
+        case B200_TYPE_Q4_0: {                                  // ggml-quants.c:314-332
+            const uint8_t * b = row + (i >> 5) * SZ_Q4_0;
+            const int j = (int) (i & 31);
+            const int q = j < 16 ? (b[2 + j] & 0xF) : (b[2 + j - 16] >> 4);
+            return (float) (q - 8) * ld_half(b);
+        }
+        case B200_TYPE_Q8_0: {                                  // ggml-quants.c:392-406
+            const uint8_t * b = row + (i >> 5) * SZ_Q8_0;
+            return (float) (int8_t) b[2 + (i & 31)] * ld_half(b);
+        }
+        case B200_TYPE_Q4_K: {                                  // ggml-quants.c:1467-1489
+            const uint8_t * b = row + (i >> 8) * SZ_Q4_K;
+            const int e = (int) (i & 255), j = e >> 5, l = e & 31;       // sub-block j, element l
+            const float d = ld_half(b), dmin = ld_half(b + 2);
+            const uint8_t * sc = b + 4;
+            int s, m;
+            if (j < 4) { s = sc[j] & 63; m = sc[j + 4] & 63; }
+            else       { s = (sc[j + 4] & 0xF) | ((sc[j - 4] >> 6) << 4); m = (sc[j + 4] >> 4) | ((sc[j] >> 6) << 4); }
+            const uint8_t qb = b[16 + 32 * (j >> 1) + l];
+            const int q = (j & 1) ? (qb >> 4) : (qb & 0xF);
+            return d * (float) s * (float) q - dmin * (float) m;
+        }
+        default: {                                               // Q6_K, ggml-quants.c:1877-1906
+            const uint8_t * b = row + (i >> 8) * SZ_Q6_K;
+            const int e = (int) (i & 255), n = e >> 7, r = (e & 127) >> 5, l = e & 31;
+            const uint8_t ql = b[64 * n + 32 * (r & 1) + l], qh = b[128 + 32 * n + l];
+            const int q = (int) (((r >> 1) ? (ql >> 4) : (ql & 0xF)) | (((qh >> (2 * r)) & 3) << 4)) - 32;
+            const int8_t sc = (int8_t) b[192 + 8 * n + 2 * r + l / 16];
+            return ld_half(b + 208) * (float) sc * (float) q;
+        }
+    }
+}
+
+// dst[i0, i10, i11, i12] = src0[i0, idx[i10, i11, i12], i11, i12]
+__global__ void __launch_bounds__(OPS_THREADS) get_rows_kernel(const tview a, const int ta, const tview idx, const tview d, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t i0, i10, i11, i12;
+        split4(i, d.ne, i0, i10, i11, i12);
+        const int64_t r = *(const int32_t *) (idx.p + i10 * idx.nb[0] + i11 * idx.nb[1] + i12 * idx.nb[2]);
+        float v = 0.0f;
+        if (r >= 0 && r < a.ne[1]) v = row_elem((const uint8_t *) (a.p + r * a.nb[1] + i11 * a.nb[2] + i12 * a.nb[3]), ta, i0);
+        *(float *) (d.p + i0 * 4 + i10 * d.nb[1] + i11 * d.nb[2] + i12 * d.nb[3]) = v;
+    }
+}
+
+// dst[i0, idx[i, i02 % ne11, i03 % ne12], i02, i03] = src0[i0, i, i02, i03]
+template <typename IDX>
+__global__ void __launch_bounds__(OPS_THREADS) set_rows_kernel(const tview a, const tview idx, const tview d, const int td, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t i0, i1, i2, i3;
+        split4(i, a.ne, i0, i1, i2, i3);
+        const int64_t r = (int64_t) *(const IDX *) (idx.p + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
+        if (r < 0 || r >= d.ne[1]) continue;
+        const float v = *(const float *) (a.p + i0 * 4 + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+        store_elem(d.p + i0 * d.nb[0] + r * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3], td, v);
+    }
+}
+
+// ---- float MUL_MAT: dst[i0, i1, i2, i3] = sum_k src0[k, i0, i2 / r2, i3 / r3] * src1[k, i1, i2, i3]; one warp per output element ------
+// (the attention products of a decode step: rows of 64-128 values against thousands of keys — HBM / L2 streaming, no reuse to tile for)
+template <typename T>
+__global__ void __launch_bounds__(OPS_THREADS) mul_mat_f_kernel(const tview a, const tview b, const tview d, const int64_t r2, const int64_t r3,
+                                                                const int64_t n_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t) gridDim.x * (OPS_THREADS / 32);
+    for (int64_t o = (int64_t) blockIdx.x * (OPS_THREADS / 32) + (threadIdx.x >> 5); o < n_out; o += warps) {
+        int64_t i0, i1, i2, i3;
+        split4(o, d.ne, i0, i1, i2, i3);
+        const T *     w = (const T *) (a.p + i0 * a.nb[1] + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3]);
+        const float * x = (const float *) (b.p + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]);
+        float s = 0.0f;
+        for (int64_t k = lane; k < a.ne[0]; k += 32) s += to_float(w[k]) * x[k];
+        s = warp_sum(s);
+        if (lane == 0) *(float *) (d.p + i0 * 4 + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = s;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+static bool cpy_type_ok(int t) { return t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_BF16; }
+
+int b200_op_cpy(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d) {
+    if (!ctx || !a || !d) { b200_set_error("b200_op_cpy: null argument"); return B200_E_ARG; }
+    if (!cpy_type_ok(a->type) || !cpy_type_ok(d->type) || nelem(a) != nelem(d)) {
+        b200_set_error("b200_op_cpy: f32 / f16 / bf16 tensors with the same number of elements"); return B200_E_UNSUPPORTED;
+    }
+    const int64_t n = nelem(a);
+    if (n == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    cpy_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), a->type, view_of(d), d->type, n);
+    return finish(ctx);
+}
+
+int b200_op_get_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * idx, const b200_tensor * d) {
+    if (!ctx || !a || !idx || !d) { b200_set_error("b200_op_get_rows: null argument"); return B200_E_ARG; }
+    const bool type_ok = cpy_type_ok(a->type) || a->type == B200_TYPE_Q4_0 || a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_K || a->type == B200_TYPE_Q6_K;
+    if (!type_ok || idx->type != B200_TYPE_I32 || d->type != B200_TYPE_F32 || d->nb[0] != 4 || d->ne[0] != a->ne[0] ||
+        d->ne[1] != idx->ne[0] || d->ne[2] != idx->ne[1] || d->ne[3] != idx->ne[2] || a->ne[0] % b200_blck_size(a->type) != 0) {
+        b200_set_error("b200_op_get_rows: f32 / f16 / bf16 / q4_0 / q8_0 / q4_K / q6_K rows, i32 indices, f32 result"); return B200_E_UNSUPPORTED;
+    }
+    const int64_t n = nelem(d);
+    if (n == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    get_rows_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), a->type, view_of(idx), view_of(d), n);
+    return finish(ctx);
+}
+
+int b200_op_set_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * idx, const b200_tensor * d) {
+    if (!ctx || !a || !idx || !d) { b200_set_error("b200_op_set_rows: null argument"); return B200_E_ARG; }
+    if (a->type != B200_TYPE_F32 || a->nb[0] != 4 || (idx->type != B200_TYPE_I64 && idx->type != B200_TYPE_I32) || !cpy_type_ok(d->type) ||
+        d->ne[0] != a->ne[0] || d->ne[2] != a->ne[2] || d->ne[3] != a->ne[3] || idx->ne[0] != a->ne[1] || idx->ne[1] <= 0 || idx->ne[2] <= 0 ||
+        a->ne[2] % idx->ne[1] != 0 || a->ne[3] % idx->ne[2] != 0) {
+        b200_set_error("b200_op_set_rows: f32 rows, i64 / i32 indices, f32 / f16 / bf16 destination"); return B200_E_UNSUPPORTED;
+    }
+    const int64_t n = nelem(a);
+    if (n == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int g = grid_for(n, ctx->sm_count);
+    if (idx->type == B200_TYPE_I64) set_rows_kernel<int64_t><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(idx), view_of(d), d->type, n);
+    else                            set_rows_kernel<int32_t><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(idx), view_of(d), d->type, n);
+    return finish(ctx);
+}
+
+int b200_mul_mat_f_supported(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    if (!a || !b || !d) return 0;
+    if (!cpy_type_ok(a->type) || b->type != B200_TYPE_F32 || d->type != B200_TYPE_F32) return 0;
+    if (a->nb[0] != (a->type == B200_TYPE_F32 ? 4 : 2) || b->nb[0] != 4 || d->nb[0] != 4) return 0;
+    if (a->ne[0] != b->ne[0] || d->ne[0] != a->ne[1] || d->ne[1] != b->ne[1] || d->ne[2] != b->ne[2] || d->ne[3] != b->ne[3]) return 0;
+    if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] != 0 || b->ne[3] % a->ne[3] != 0) return 0;
+    return 1;
+}
+
+int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    if (!ctx) { b200_set_error("b200_mul_mat_f: null context"); return B200_E_ARG; }
+    if (!b200_mul_mat_f_supported(a, b, d)) { b200_set_error("b200_mul_mat_f: f32 / f16 / bf16 src0 rows x f32 src1 rows -> f32"); return B200_E_UNSUPPORTED; }
+    const int64_t n_out = nelem(d);
+    if (n_out == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t blocks = (n_out + OPS_THREADS / 32 - 1) / (OPS_THREADS / 32), cap = (int64_t) ctx->sm_count * 16;
+    const int g = (int) (blocks < cap ? blocks : cap);
+    const int64_t r2 = b->ne[2] / a->ne[2], r3 = b->ne[3] / a->ne[3];
+    switch (a->type) {
+        case B200_TYPE_F32: mul_mat_f_kernel<float><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+        case B200_TYPE_F16: mul_mat_f_kernel<__half><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+        default:            mul_mat_f_kernel<__nv_bfloat16><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+    }
+    return finish(ctx);
+}
+
+}  // extern "C"
