@@ -314,6 +314,8 @@ enum { B200_UNARY_ABS = 0, B200_UNARY_SGN = 1, B200_UNARY_NEG = 2, B200_UNARY_ST
        B200_UNARY_SIGMOID = 7, B200_UNARY_GELU = 8, B200_UNARY_GELU_QUICK = 9, B200_UNARY_SILU = 10, B200_UNARY_EXP = 13, B200_UNARY_GELU_ERF = 16 };
 /* dst = src0 (op) src1, src1 repeated into src0's shape (ggml_can_repeat); any strides */
 B200_API int b200_op_binary(b200_ctx * ctx, int op, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * dst);
+/* GGML_OP_REPEAT: dst = src0 tiled into dst's shape */
+B200_API int b200_op_repeat(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst);
 /* GGML_OP_ADD_ID: dst[:, i1, i2] = src0[:, i1, i2] + src1[:, ids[i1, i2]] (expert biases of MUL_MAT_ID) */
 B200_API int b200_op_add_id(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * ids, const b200_tensor * dst);
 /* GGML_OP_GLU: dst = act(x) * g; src1 != NULL: x = src0, g = src1 (ggml_glu_split); src1 == NULL: the two halves of src0's rows

@@ -427,11 +427,29 @@ bool is_f32(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32; }
 bool is_float_type(ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16 || t == GGML_TYPE_BF16; }
 bool is_quant_weight(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K; }
 
+// GGML_B200_OPS=mul_mat: answer supports_op() for MUL_MAT / MUL_MAT_ID only (the round-1 behaviour: every other node of a graph runs
+// on another backend, the scheduler copies activations across — kept so that split structure stays tested)
+bool only_mul_mat() {
+    static const bool v = [] { const char * e = getenv("GGML_B200_OPS"); return e && !strcmp(e, "mul_mat"); }();
+    return v;
+}
+
+// GGML_B200_NO_OP=ADD,ROPE,...: decline single ops (bisecting a graph difference)
+bool op_disabled(const ggml_tensor * op) {
+    static const std::string list = [] { const char * e = getenv("GGML_B200_NO_OP"); return std::string(e ? e : ""); }();
+    if (list.empty()) return false;
+    const std::string name = std::string(",") + ggml_op_name(op->op) + ",";
+    return (std::string(",") + list + ",").find(name) != std::string::npos;
+}
+
 bool extra_op_supported(const ggml_tensor * op) {
+    if (only_mul_mat() || op_disabled(op)) return false;
     const ggml_tensor * a = op->src[0], * b = op->src[1], * c = op->src[2];
     switch (op->op) {
         case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
             return is_f32(a) && is_f32(b) && is_f32(op) && ggml_can_repeat(b, a) && ggml_are_same_shape(a, op);
+        case GGML_OP_REPEAT:
+            return is_f32(a) && is_f32(op) && ggml_can_repeat(a, op);
         case GGML_OP_ADD_ID:
             return is_f32(a) && is_f32(b) && is_f32(op) && c && c->type == GGML_TYPE_I32 && a->nb[0] == 4 && b->nb[0] == 4 && op->nb[0] == 4;
         case GGML_OP_GLU:
@@ -465,6 +483,19 @@ bool extra_op_supported(const ggml_tensor * op) {
 
 int run_extra_op(b200_backend_ctx * bctx, const ggml_tensor * node) {
     b200_ctx * ctx = bctx->ctx;
+    static const bool sync_ops = [] { const char * e = getenv("GGML_B200_SYNC_OPS"); return e && *e == '1'; }();      // debugging aid
+    if (sync_ops) b200_ctx_synchronize(ctx);
+    static const bool trace_ops = [] { const char * e = getenv("GGML_B200_TRACE_OPS"); return e && *e == '1'; }();    // debugging aid
+    if (trace_ops) {
+        fprintf(stderr, "ggml-b200 op %s %s dst %p ne [%ld %ld %ld %ld] nb [%zu %zu %zu %zu]", ggml_op_name(node->op), node->name, node->data,
+                (long) node->ne[0], (long) node->ne[1], (long) node->ne[2], (long) node->ne[3], node->nb[0], node->nb[1], node->nb[2], node->nb[3]);
+        for (int j = 0; j < 3 && node->src[j]; ++j) {
+            const ggml_tensor * t = node->src[j];
+            fprintf(stderr, " | src%d %s %p ne [%ld %ld %ld %ld] nb [%zu %zu %zu %zu]", j, t->name, t->data, (long) t->ne[0], (long) t->ne[1], (long) t->ne[2],
+                    (long) t->ne[3], t->nb[0], t->nb[1], t->nb[2], t->nb[3]);
+        }
+        fprintf(stderr, "\n");
+    }
     const b200_tensor d = to_b200(node);
     const b200_tensor a = node->src[0] ? to_b200(node->src[0]) : b200_tensor{};
     const b200_tensor b = node->src[1] ? to_b200(node->src[1]) : b200_tensor{};
@@ -475,6 +506,7 @@ int run_extra_op(b200_backend_ctx * bctx, const ggml_tensor * node) {
         case GGML_OP_SUB:      return b200_op_binary(ctx, B200_OP_SUB, &a, &b, &d);
         case GGML_OP_MUL:      return b200_op_binary(ctx, B200_OP_MUL, &a, &b, &d);
         case GGML_OP_DIV:      return b200_op_binary(ctx, B200_OP_DIV, &a, &b, &d);
+        case GGML_OP_REPEAT:   return b200_op_repeat(ctx, &a, &d);
         case GGML_OP_ADD_ID:   return b200_op_add_id(ctx, &a, &b, &c, &d);
         case GGML_OP_GLU:      return b200_op_glu(ctx, (int) ggml_get_glu_op(node), &a, node->src[1] ? &b : nullptr, &d, ggml_get_op_params_i32(node, 1),
                                                   ggml_get_op_params_f32(node, 2), ggml_get_op_params_f32(node, 3));
@@ -508,37 +540,43 @@ bool bias_of(const ggml_tensor * add, const ggml_tensor * mm, const ggml_tensor 
 }
 
 int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f) {
+    if (only_mul_mat()) return 0;
     const ggml_tensor * n0 = cgraph->nodes[i];
     if (n0->op != GGML_OP_MUL_MAT || !is_quant_weight(n0->src[0]->type) || n0->ne[1] != 1 || split_src0(n0)) return 0;
     f = {};
-    f.up = n0->src[0]; f.x = n0->src[1];
-    int j = i + 1;
-    const ggml_tensor * up_out = n0;
     auto single_use = [&](int idx) { return ggml_node_has_n_uses(cgraph, idx, 1) && (cgraph->nodes[idx]->flags & GGML_TENSOR_FLAG_OUTPUT) == 0; };
-    if (j < cgraph->n_nodes && single_use(i) && bias_of(cgraph->nodes[j], n0, &f.bias_up)) { up_out = cgraph->nodes[j]; ++j; }
-    const int after_up = j;
-    // gate product, its bias, the GLU
+    // first product (+ bias)
+    int j = i + 1;
+    const ggml_tensor * out1 = n0, * bias1 = nullptr;
+    if (j < cgraph->n_nodes && single_use(i) && bias_of(cgraph->nodes[j], n0, &bias1)) { out1 = cgraph->nodes[j]; ++j; }
+    const int after_first = j;
+    // second product against the same activations (+ bias), then the GLU of the two (llama.cpp's build_ffn computes up first, other graphs
+    // gate first: the GLU's src0 says which one is the gate)
     if (j < cgraph->n_nodes && single_use(j - 1)) {
-        const ggml_tensor * g0 = cgraph->nodes[j];
-        if (g0->op == GGML_OP_MUL_MAT && g0->src[1] == f.x && g0->src[0]->type == f.up->type && ggml_are_same_shape(g0->src[0], f.up) &&
-            ggml_are_same_stride(g0->src[0], f.up) && !split_src0(g0)) {
-            const ggml_tensor * gate_out = g0;
-            const ggml_tensor * bg = nullptr;
+        const ggml_tensor * m1 = cgraph->nodes[j];
+        if (m1->op == GGML_OP_MUL_MAT && m1->src[1] == n0->src[1] && m1->src[0]->type == n0->src[0]->type && ggml_are_same_shape(m1->src[0], n0->src[0]) &&
+            ggml_are_same_stride(m1->src[0], n0->src[0]) && !split_src0(m1)) {
+            const ggml_tensor * out2 = m1, * bias2 = nullptr;
             int k = j + 1;
-            if (k < cgraph->n_nodes && single_use(j) && bias_of(cgraph->nodes[k], g0, &bg)) { gate_out = cgraph->nodes[k]; ++k; }
+            if (k < cgraph->n_nodes && single_use(j) && bias_of(cgraph->nodes[k], m1, &bias2)) { out2 = cgraph->nodes[k]; ++k; }
             if (k < cgraph->n_nodes && single_use(k - 1)) {
                 const ggml_tensor * glu = cgraph->nodes[k];
-                if (glu->op == GGML_OP_GLU && glu->src[0] == gate_out && glu->src[1] == up_out && ggml_get_glu_op(glu) != GGML_GLU_OP_SWIGLU_OAI) {
-                    f.gate = g0->src[0]; f.bias_gate = bg; f.glu_op = (int) ggml_get_glu_op(glu); f.out = glu;
-                    j = k + 1;
+                if (glu->op == GGML_OP_GLU && ggml_get_glu_op(glu) != GGML_GLU_OP_SWIGLU_OAI && glu->src[1] != nullptr) {
+                    if (glu->src[0] == out2 && glu->src[1] == out1) {
+                        f.up = n0->src[0]; f.bias_up = bias1; f.gate = m1->src[0]; f.bias_gate = bias2;
+                    } else if (glu->src[0] == out1 && glu->src[1] == out2) {
+                        f.up = m1->src[0]; f.bias_up = bias2; f.gate = n0->src[0]; f.bias_gate = bias1;
+                    }
+                    if (f.gate) { f.glu_op = (int) ggml_get_glu_op(glu); f.out = glu; j = k + 1; }
                 }
             }
         }
     }
     if (!f.gate) {
-        if (!f.bias_up) return 0;
-        f.out = up_out; j = after_up;
+        if (!bias1) return 0;
+        f.up = n0->src[0]; f.bias_up = bias1; f.out = out1; j = after_first;
     }
+    f.x = n0->src[1];
     const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
     const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{}, bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
     if (!b200_mul_mat_fused_supported(&up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d)) return 0;
@@ -740,7 +778,7 @@ bool device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
         case GGML_OP_MUL_MAT: {
             if (!op->src[0] || !op->src[1]) return false;
             const b200_tensor a = to_b200(op->src[0]), b = to_b200(op->src[1]), d = to_b200(op);
-            if (is_float_type(op->src[0]->type)) return !split_src0(op) && b200_mul_mat_f_supported(&a, &b, &d) != 0;
+            if (is_float_type(op->src[0]->type)) return !only_mul_mat() && !split_src0(op) && b200_mul_mat_f_supported(&a, &b, &d) != 0;
             if (split_src0(op) && (op->src[1]->ne[2] * op->src[1]->ne[3] != 1 || (op->ne[1] > 1 && op->nb[1] != (size_t) op->ne[0] * 4))) return false;
             return b200_mul_mat_supported(&a, &b, &d) != 0;
         }

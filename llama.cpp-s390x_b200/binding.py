@@ -23,6 +23,9 @@ EXPORTS = [
     "b200_event_record", "b200_event_wait", "b200_event_synchronize", "b200_rowsplit_create", "b200_rowsplit_destroy", "b200_rowsplit_n_dev",
     "b200_rowsplit_rows", "b200_rowsplit_upload", "b200_rowsplit_weights_free", "b200_rowsplit_mul_mat", "b200_rowsplit_mul_mat_main",
     "b200_rowsplit_synchronize", "b200_rowsplit_ctx",
+    "b200_op_binary", "b200_op_repeat", "b200_op_add_id", "b200_op_glu", "b200_op_unary", "b200_op_unary_supported", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope",
+    "b200_op_soft_max", "b200_op_cpy", "b200_op_get_rows", "b200_op_set_rows", "b200_mul_mat_f", "b200_mul_mat_f_supported", "b200_mul_mat_fused",
+    "b200_mul_mat_fused_supported",
 ]
 
 
@@ -76,6 +79,14 @@ def lib() -> C.CDLL:
     sig("b200_quantize_row_q8_1", i32, [vp, vp, i64, vp, i64, i64])
     sig("b200_mul_mat", i32, [vp, T, T, T]); sig("b200_mul_mat_supported", i32, [T, T, T])
     sig("b200_mul_mat_noalloc", i32, [vp, T, T, T])
+    f32 = C.c_float
+    sig("b200_op_binary", i32, [vp, i32, T, T, T]); sig("b200_op_repeat", i32, [vp, T, T]); sig("b200_op_add_id", i32, [vp, T, T, T, T])
+    sig("b200_op_glu", i32, [vp, i32, T, T, T, i32, f32, f32]); sig("b200_op_unary", i32, [vp, i32, T, T]); sig("b200_op_unary_supported", i32, [i32])
+    sig("b200_op_scale", i32, [vp, T, T, f32, f32]); sig("b200_op_rms_norm", i32, [vp, T, T, f32])
+    sig("b200_op_rope", i32, [vp, T, T, T, T, C.POINTER(i32)]); sig("b200_op_soft_max", i32, [vp, T, T, T, T, f32, f32])
+    sig("b200_op_cpy", i32, [vp, T, T]); sig("b200_op_get_rows", i32, [vp, T, T, T]); sig("b200_op_set_rows", i32, [vp, T, T, T])
+    sig("b200_mul_mat_f", i32, [vp, T, T, T]); sig("b200_mul_mat_f_supported", i32, [T, T, T])
+    sig("b200_mul_mat_fused", i32, [vp, T, T, T, T, T, i32, T]); sig("b200_mul_mat_fused_supported", i32, [T, T, T, T, T, i32, T])
     sig("b200_mul_mat_id", i32, [vp, T, T, T, T]); sig("b200_mul_mat_id_supported", i32, [T, T, T, T])
     sig("b200_mm_ids", i32, [vp, vp, i64, i32, i32, i64, vp, vp])
     sig("b200_weights_upload", i32, [vp, i32, vp, i64, i64, C.POINTER(vp)]); sig("b200_weights_free", None, [vp, vp])

@@ -6,6 +6,7 @@
 //
 // Each entry point restates the semantics of the reference's CPU forward function (file:line under /root/reference/ggml/src):
 //   b200_op_binary    ggml_compute_forward_{add,sub,mul,div}      ggml-cpu/binary-ops.cpp (broadcast: ggml.c ggml_can_repeat)
+//   b200_op_repeat    ggml_compute_forward_repeat_f32              ggml-cpu/ops.cpp
 //   b200_op_add_id    ggml_compute_forward_add_id_f32             ggml-cpu/ops.cpp:703-752
 //   b200_op_glu       ggml_compute_forward_{reglu,geglu,swiglu,swiglu_oai,geglu_erf,geglu_quick}   ggml-cpu/ops.cpp:3133-3345
 //   b200_op_unary     ggml_compute_forward_unary                   ggml-cpu/unary-ops.cpp, formulas ggml-cpu/vec.h:981-1070
@@ -36,6 +37,16 @@ __global__ void __launch_bounds__(OPS_THREADS) bin_kernel(const tview a, const t
         float r;
         if (OP == B200_OP_ADD) r = x + y; else if (OP == B200_OP_SUB) r = x - y; else if (OP == B200_OP_MUL) r = x * y; else r = x / y;
         *(float *) (d.p + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = r;
+    }
+}
+
+// ---- REPEAT: dst = src0 tiled -------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(OPS_THREADS) repeat_kernel(const tview a, const tview d, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t i0, i1, i2, i3;
+        split4(i, d.ne, i0, i1, i2, i3);
+        *(float *) (d.p + i0 * d.nb[0] + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) =
+            *(const float *) (a.p + (i0 % a.ne[0]) * a.nb[0] + (i1 % a.ne[1]) * a.nb[1] + (i2 % a.ne[2]) * a.nb[2] + (i3 % a.ne[3]) * a.nb[3]);
     }
 }
 
@@ -109,6 +120,17 @@ int b200_op_binary(b200_ctx * ctx, int op, const b200_tensor * a, const b200_ten
         case B200_OP_DIV: bin_kernel<B200_OP_DIV><<<g, OPS_THREADS, 0, ctx->stream>>>(va, vb, vd, n); break;
         default: b200_set_error("b200_op_binary: unknown op %d", op); return B200_E_ARG;
     }
+    return finish(ctx);
+}
+
+int b200_op_repeat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d) {
+    if (!ctx || !a || !d) { b200_set_error("b200_op_repeat: null argument"); return B200_E_ARG; }
+    if (a->type != B200_TYPE_F32 || d->type != B200_TYPE_F32) { b200_set_error("b200_op_repeat: f32 tensors"); return B200_E_UNSUPPORTED; }
+    for (int i = 0; i < 4; ++i) if (a->ne[i] <= 0 || d->ne[i] % a->ne[i] != 0) { b200_set_error("b200_op_repeat: src0 cannot be repeated into dst"); return B200_E_ARG; }
+    const int64_t n = nelem(d);
+    if (n == 0) return B200_OK;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    repeat_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), n);
     return finish(ctx);
 }
 

@@ -63,7 +63,7 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
             else       { s = (sc[j + 4] & 0xF) | ((sc[j - 4] >> 6) << 4); m = (sc[j + 4] >> 4) | ((sc[j] >> 6) << 4); }
             const uint8_t qb = b[16 + 32 * (j >> 1) + l];
             const int q = (j & 1) ? (qb >> 4) : (qb & 0xF);
-            return d * (float) s * (float) q - dmin * (float) m;
+            return __fsub_rn(__fmul_rn(__fmul_rn(d, (float) s), (float) q), __fmul_rn(dmin, (float) m));      // no FMA contraction: the bits of dequantize_row_q4_K
         }
         default: {                                               // Q6_K, ggml-quants.c:1877-1906
             const uint8_t * b = row + (i >> 8) * SZ_Q6_K;

@@ -92,6 +92,72 @@ def mul_mat_multi(ctx: Context, wtype: int, ws, x, outs=None):
     return outs
 
 
+def mul_mat_fused(ctx: Context, wtype: int, w_up, x, w_gate=None, bias_up=None, bias_gate=None, glu_op: int = 2, out=None):
+    """N2: out = w_up x (+ bias_up), or glu(w_gate x (+ bias_gate), w_up x (+ bias_up)), one activation column per batch, ONE launch
+    (b200_mul_mat_fused; glu_op: enum ggml_glu_op, 2 = SWIGLU)"""
+    import torch
+    k = x.shape[-1]
+    if out is None:
+        out = torch.empty(tuple(x.shape[:-1]) + (w_up.shape[-2],), dtype=torch.float32, device=x.device)
+    a = _desc(w_up, wtype, k_elems=k)
+    g = _desc(w_gate, wtype, k_elems=k) if w_gate is not None else None
+    bu = _desc(bias_up, F32) if bias_up is not None else None
+    bg = _desc(bias_gate, F32) if bias_gate is not None else None
+    b, d = _desc(x, F32), _desc(out, F32)
+    ref = lambda t: C.byref(t) if t is not None else None
+    check(lib().b200_mul_mat_fused(ctx.handle, C.byref(a), ref(g), C.byref(b), ref(bu), ref(bg), glu_op, C.byref(d)), "b200_mul_mat_fused")
+    return out
+
+
+_TORCH_TYPES = {"torch.float32": 0, "torch.float16": 1, "torch.bfloat16": 30, "torch.int32": 26, "torch.int64": 27}
+
+
+def _fdesc(t):
+    return _desc(t, _TORCH_TYPES[str(t.dtype)])
+
+
+def graph_op(ctx: Context, name: str, *tensors, **params):
+    """The other graph ops of the C ABI on torch tensors (ggml shapes: torch (ne3, ne2, ne1, ne0)).  name in {"add","sub","mul","div",
+    "add_id","glu","unary","scale","rms_norm","rope","soft_max","cpy","get_rows","set_rows","mul_mat_f"}; the LAST tensor is the destination,
+    None stands for an absent optional source."""
+    L = lib()
+    d = [C.byref(_fdesc(t)) if t is not None else None for t in tensors]
+    h = ctx.handle
+    if name in ("add", "sub", "mul", "div"):
+        rc = L.b200_op_binary(h, ("add", "sub", "mul", "div").index(name), *d)
+    elif name == "add_id":
+        rc = L.b200_op_add_id(h, *d)
+    elif name == "glu":
+        rc = L.b200_op_glu(h, params["op"], d[0], d[1], d[2], params.get("swapped", 0), params.get("alpha", 0.0), params.get("limit", 0.0))
+    elif name == "unary":
+        rc = L.b200_op_unary(h, params["op"], *d)
+    elif name == "scale":
+        rc = L.b200_op_scale(h, d[0], d[1], params["scale"], params.get("bias", 0.0))
+    elif name == "rms_norm":
+        rc = L.b200_op_rms_norm(h, d[0], d[1], params["eps"])
+    elif name == "rope":
+        import struct
+        words = [0, params["n_dims"], params.get("mode", 0), 0, params.get("n_ctx_orig", 0)]
+        words += [struct.unpack("<i", struct.pack("<f", params.get(k_, dv)))[0] for k_, dv in (("freq_base", 10000.0), ("freq_scale", 1.0), ("ext_factor", 0.0),
+                                                                                             ("attn_factor", 1.0), ("beta_fast", 32.0), ("beta_slow", 1.0))]
+        words += [0, 0, 0, 0]
+        rc = L.b200_op_rope(h, d[0], d[1], d[2], d[3], (C.c_int32 * 15)(*words))
+    elif name == "soft_max":
+        rc = L.b200_op_soft_max(h, d[0], d[1], d[2], d[3], params.get("scale", 1.0), params.get("max_bias", 0.0))
+    elif name == "cpy":
+        rc = L.b200_op_cpy(h, *d)
+    elif name == "get_rows":
+        rc = L.b200_op_get_rows(h, *d)
+    elif name == "set_rows":
+        rc = L.b200_op_set_rows(h, *d)
+    elif name == "mul_mat_f":
+        rc = L.b200_mul_mat_f(h, *d)
+    else:
+        raise ValueError(name)
+    check(rc, "b200 graph op " + name)
+    return tensors[-1]
+
+
 class MatmulBatch:
     """A prepared list of matmuls for b200_mul_mat_batch: d[i] = ws[i] x xs[i], executed as if in list order.  The descriptor
     arrays are built once, run() is one C-ABI call (what the backend shell does for the MUL_MAT nodes of a cgraph)."""

@@ -125,9 +125,11 @@ result run(std::vector<ggml_backend_t> backends, ggml_backend_t weight_backend, 
     graph G = build_graph(M, n_tokens);
     ggml_backend_sched_t sched = ggml_backend_sched_new(backends.data(), nullptr, (int) backends.size(), 4096, false, true);
     if (!ggml_backend_sched_alloc_graph(sched, G.gf)) { fprintf(stderr, "sched alloc failed\n"); exit(1); }
-    ggml_backend_tensor_set(G.inp, x.data(), 0, x.size() * sizeof(float));
     result R;
     for (int rep = 0; rep < 2; ++rep) {        // twice: the second pass re-uses every buffer (stale data would show)
+        // the input is set before EVERY pass, as llama.cpp does: ggml-alloc may hand an input's memory to a later node of the graph
+        // once the input has been consumed (seen with the REPEAT node of this graph on the CPU backend), so it does not survive a pass
+        ggml_backend_tensor_set(G.inp, x.data(), 0, x.size() * sizeof(float));
         if (ggml_backend_sched_graph_compute(sched, G.gf) != GGML_STATUS_SUCCESS) { fprintf(stderr, "graph compute failed\n"); exit(1); }
     }
     R.n_splits = ggml_backend_sched_get_n_splits(sched);
@@ -179,6 +181,9 @@ int main(int argc, char ** argv) {
     const result got = run({ gpu, cpu }, gpu, type, n_tokens, n_layers, blobs, x);
 
     const double e_out = nmse(ref.out, got.out), e_kv = nmse(ref.kv, got.kv);
+    if (getenv("GRAPH_CHECK_DEBUG")) {
+        for (size_t i = 0; i < 6 && i < ref.kv.size(); ++i) printf("kv[%zu] ref %g got %g | out ref %g got %g\n", i, ref.kv[i], got.kv[i], ref.out[i], got.out[i]);
+    }
     bool finite = true;
     for (float v : got.out) finite = finite && std::isfinite(v);
     printf("graph_check type=%s n_tokens=%d n_layers=%d splits_cpu=%d splits_b200=%d nmse_out=%.3e nmse_kv=%.3e finite=%d\n",
@@ -188,7 +193,11 @@ int main(int argc, char ** argv) {
     // every single MUL_MAT is within NMSE 5e-4 of the CPU backend (test-backend-ops); the CPU quantizes Q4_K / Q6_K activations
     // to Q8_K and this backend to Q8_1, so along a chain of 4 dependent matmuls per layer the differences add up
     const double tol = 5e-4 * 4 * n_layers;
-    const bool ok = finite && e_out <= tol && e_kv <= tol && got.n_splits > 1;
+    // GGML_B200_OPS=mul_mat: only the MUL_MATs run on the plug-in, so the scheduler must have cut the graph into many splits;
+    // default: the plug-in takes every op of this graph and the whole graph is one split
+    const char * ops_env = getenv("GGML_B200_OPS");
+    const bool mm_only = ops_env && !strcmp(ops_env, "mul_mat");
+    const bool ok = finite && e_out <= tol && e_kv <= tol && (mm_only ? got.n_splits > 1 : got.n_splits <= 2);
     printf(ok ? "OK\n" : "FAIL\n");
     return ok ? 0 : 1;
 }

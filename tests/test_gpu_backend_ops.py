@@ -49,21 +49,53 @@ def test_backend_ops_support_listing():
 GRAPH_CHECK = refenv.REF_DIR / "graph_check"
 
 
+# the other ops of a Llama graph and the fused MUL_MAT patterns (N2): op filter -> least number of cases that must RUN
+EXTRA_OPS = {
+    "ADD": 40, "SUB": 40, "MUL": 40, "DIV": 40, "ADD_ID": 30, "SCALE": 4, "RMS_NORM": 20, "ROPE": 150, "SOFT_MAX": 150, "CPY": 50, "CONT": 20, "DUP": 6,
+    "GET_ROWS": 30, "SET_ROWS": 50, "SILU": 2, "GELU": 2, "RELU": 2, "SIGMOID": 2, "TANH": 2, "SWIGLU": 12, "GEGLU": 12, "REGLU": 12, "GEGLU_ERF": 12,
+    "GEGLU_QUICK": 12, "SWIGLU_OAI": 8,
+    # whole-graph cases of the harness (run_whole_graph): the plug-in computes every node, fused where its shell fuses
+    "MUL_MAT_VEC_FUSION": 100, "MUL_MAT_ID_FUSION": 6, "RMS_NORM_MUL_ADD": 30, "ADD_RMS_NORM": 25, "RMS_NORM_MUL_ROPE": 70, "ROPE_SET_ROWS": 24,
+}
+
+
+@pytest.mark.parametrize("op", sorted(EXTRA_OPS))
+def test_backend_ops_llama_graph_ops(op):
+    """unmodified test-backend-ops, op by op: everything supports_op() accepts must match the reference's CPU backend (the harness' own
+    per-op NMSE limits), and at least the listed number of cases must have run rather than been declined"""
+    rc, out = run_harness("test", "-b", "B2000", "-o", op)
+    tail = "\n".join(out.splitlines()[-25:])
+    assert rc == 0 and "Backend B2000: OK" in out, tail
+    ran = [l for l in out.splitlines() if re.match(r"\s*" + op + r"\(", l) and l.rstrip().endswith("OK")]
+    assert len(ran) >= EXTRA_OPS[op], f"only {len(ran)} cases of {op} ran\n{tail}"
+    assert not [l for l in out.splitlines() if "FAIL" in l]
+
+
+@pytest.mark.parametrize("mode", ["on_device", "mul_mat_only"])
 @pytest.mark.parametrize("wtype,n_tokens", [("q4_K", 1), ("q4_K", 5), ("q4_K", 64), ("q8_0", 1), ("q8_0", 48), ("q4_0", 1), ("q4_0", 33), ("q6_K", 1), ("q6_K", 20)])
-def test_layer_graph_through_sched(wtype, n_tokens):
-    """oracle/graph_check.cpp: transformer-layer-shaped graphs scheduled by the reference's ggml_backend_sched over
-    {plug-in, CPU} (all MUL_MATs on the plug-in, everything else on the CPU) == the CPU backend alone; wq/wk/wv and
-    gate/up must have gone through the fused b200_mul_mat_multi path of graph_compute"""
+def test_layer_graph_through_sched(wtype, n_tokens, mode):
+    """oracle/graph_check.cpp: transformer-layer-shaped graphs scheduled by the reference's ggml_backend_sched over {plug-in, CPU} == the CPU
+    backend alone.  on_device: the plug-in takes every node (one split); at one token gate / up / SWIGLU go through b200_mul_mat_fused, wq / wk /
+    wv through one b200_mul_mat_batch.  mul_mat_only (GGML_B200_OPS=mul_mat, the round-1 behaviour): all MUL_MATs on the plug-in, everything
+    else on the CPU, the scheduler copying activations across; wq/wk/wv and gate/up each one batch."""
     if not GRAPH_CHECK.exists() or not PLUGIN.exists():
         pytest.skip("oracle/_ref/graph_check or libggml-b200.so not built (needs /root/reference at build time)")
-    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN), "GGML_B200_STATS": "1"})
-    p = subprocess.run([str(GRAPH_CHECK), wtype, str(n_tokens), "3"], env=env, capture_output=True, text=True, timeout=300)
+    extra = {"GGML_BACKEND_PATH": str(PLUGIN), "GGML_B200_STATS": "1"}
+    if mode == "mul_mat_only":
+        extra["GGML_B200_OPS"] = "mul_mat"
+    p = subprocess.run([str(GRAPH_CHECK), wtype, str(n_tokens), "3"], env=refenv.ref_env(extra), capture_output=True, text=True, timeout=300)
     out = p.stdout + p.stderr
     assert p.returncode == 0 and "OK" in p.stdout.splitlines()[-1], out[-2000:]
-    m = re.search(r"stats: graphs=(\d+) mul_mat=(\d+) mul_mat_id=(\d+) fused_groups=(\d+)", out)
+    m = re.search(r"stats: graphs=(\d+) mul_mat=(\d+) mul_mat_id=(\d+) fused_groups=(\d+) other_ops=(\d+) fused_mul_mat=(\d+)", out)
     assert m, out[-2000:]
-    # 3 layers x 7 matmuls x 2 passes; two fused groups per layer and pass
-    assert int(m.group(2)) == 3 * 7 * 2 and int(m.group(4)) == 3 * 2 * 2, m.group(0)
+    mul_mat, groups, other, fused = int(m.group(2)), int(m.group(4)), int(m.group(5)), int(m.group(6))
+    if mode == "mul_mat_only" or n_tokens > 1:
+        # 3 layers x 7 matmuls x 2 passes; two batched groups per layer and pass
+        assert mul_mat == 3 * 7 * 2 and groups == 3 * 2 * 2 and fused == 0, m.group(0)
+    else:
+        # one token: gate + up + SWIGLU is one fused launch per layer and pass, the other five matmuls go through the batch / single path
+        assert mul_mat == 3 * 5 * 2 and fused == 3 * 2 and groups == 3 * 2, m.group(0)
+    assert (other == 0) == (mode == "mul_mat_only"), m.group(0)
 
 
 SPLIT_CHECK = refenv.REF_DIR / "split_check"
