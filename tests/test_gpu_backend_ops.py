@@ -98,6 +98,23 @@ def test_layer_graph_through_sched(wtype, n_tokens, mode):
     assert (other == 0) == (mode == "mul_mat_only"), m.group(0)
 
 
+LLAMA_STEP = refenv.REF_DIR / "llama_step"
+
+
+@pytest.mark.parametrize("args", [("tiny", "1", "40"), ("tiny", "7", "33"), ("tiny", "64", "0"), ("1b", "1", "300"), ("1b", "33", "100")])
+def test_whole_llama_graph_on_the_plugin(args):
+    """oracle/llama_step.cpp: a Llama decoder graph as llama.cpp builds it without flash attention (GET_ROWS, RMS_NORM, MUL, quantized MUL_MAT,
+    ROPE, SET_ROWS / CPY into an F16 KV cache, F16 MUL_MAT over strided cache views with grouped-query broadcast, SOFT_MAX with mask, CONT, ADD,
+    SWIGLU) scheduled by the reference's ggml_backend_sched over {plug-in, CPU}: every node must run on the plug-in (ONE split) and the logits must
+    match the reference's CPU backend"""
+    if not LLAMA_STEP.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/llama_step or libggml-b200.so not built (needs /root/reference at build time)")
+    p = subprocess.run([str(LLAMA_STEP), *args, "2", "1"], env=refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN)}), capture_output=True, text=True, timeout=600)
+    out = p.stdout + p.stderr
+    assert p.returncode == 0 and p.stdout.strip().splitlines()[-1] == "OK", out[-2000:]
+    assert '"splits_b200": 1,' in out, out[-2000:]
+
+
 SPLIT_CHECK = refenv.REF_DIR / "split_check"
 
 
