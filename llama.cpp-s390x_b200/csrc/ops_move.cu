@@ -120,6 +120,52 @@ __global__ void __launch_bounds__(OPS_THREADS) mul_mat_f_kernel(const tview a, c
     }
 }
 
+// the same product for many activation columns (prefill attention: hundreds of query rows against hundreds of keys per head): a 64 x 64
+// output tile per CTA, K in steps of 16 through shared memory, 4 x 4 outputs per thread, fp32 accumulation
+constexpr int MMF_T = 64, MMF_K = 16;
+template <typename T>
+__global__ void __launch_bounds__(256) mul_mat_f_tiled_kernel(const tview a, const tview b, const tview d, const int64_t r2, const int64_t r3) {
+    __shared__ float sa[MMF_K][MMF_T + 1], sb[MMF_K][MMF_T + 1];
+    const int64_t batch = blockIdx.z, i2 = batch % d.ne[2], i3 = batch / d.ne[2];
+    const int64_t row0 = (int64_t) blockIdx.x * MMF_T, col0 = (int64_t) blockIdx.y * MMF_T;
+    const char * ap = a.p + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3];
+    const char * bp = b.p + i2 * b.nb[2] + i3 * b.nb[3];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;           // outputs rows 4 tx .. +3, columns 4 ty .. +3
+    const int lk = threadIdx.x & 15, lr = threadIdx.x >> 4;           // loader: element lk of rows lr, lr + 16, lr + 32, lr + 48
+    float acc[4][4] = {};
+    const int64_t K = a.ne[0];
+    for (int64_t k0 = 0; k0 < K; k0 += MMF_K) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t r = row0 + lr + 16 * j, c = col0 + lr + 16 * j, k = k0 + lk;
+            sa[lk][lr + 16 * j] = (r < a.ne[1] && k < K) ? to_float(((const T *) (ap + r * a.nb[1]))[k]) : 0.0f;
+            sb[lk][lr + 16 * j] = (c < b.ne[1] && k < K) ? ((const float *) (bp + c * b.nb[1]))[k] : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < MMF_K; ++k) {
+            float av[4], bv[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { av[j] = sa[k][4 * tx + j]; bv[j] = sb[k][4 * ty + j]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] += av[i] * bv[j];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int64_t c = col0 + 4 * ty + j;
+        if (c >= d.ne[1]) continue;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int64_t r = row0 + 4 * tx + i;
+            if (r < d.ne[0]) *(float *) (d.p + r * 4 + c * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = acc[i][j];
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -183,6 +229,16 @@ int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     const int64_t n_out = nelem(d);
     if (n_out == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t r2t = b->ne[2] / a->ne[2], r3t = b->ne[3] / a->ne[3];
+    if (b->ne[1] > 8 && d->ne[2] * d->ne[3] <= 65535) {            // many columns: the tiled kernel
+        const dim3 grid((unsigned) ((d->ne[0] + MMF_T - 1) / MMF_T), (unsigned) ((d->ne[1] + MMF_T - 1) / MMF_T), (unsigned) (d->ne[2] * d->ne[3]));
+        switch (a->type) {
+            case B200_TYPE_F32: mul_mat_f_tiled_kernel<float><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+            case B200_TYPE_F16: mul_mat_f_tiled_kernel<__half><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+            default:            mul_mat_f_tiled_kernel<__nv_bfloat16><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+        }
+        return finish(ctx);
+    }
     const int64_t blocks = (n_out + OPS_THREADS / 32 - 1) / (OPS_THREADS / 32), cap = (int64_t) ctx->sm_count * 16;
     const int g = (int) (blocks < cap ? blocks : cap);
     const int64_t r2 = b->ne[2] / a->ne[2], r3 = b->ne[3] / a->ne[3];
