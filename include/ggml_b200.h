@@ -300,6 +300,18 @@ B200_API int  b200_rowsplit_synchronize(b200_rowsplit * rs);
 B200_API b200_ctx * b200_rowsplit_ctx(b200_rowsplit * rs, int idx);
 
 
+/* ---- stream capture (reference: the CUDA-graph path of ggml_backend_cuda_graph_compute, ggml/src/ggml-cuda/ggml-cuda.cu:4457-4490) -------
+ * Between b200_capture_begin and b200_capture_end every entry point of this header RECORDS its work on the context's stream instead of
+ * running it; b200_capture_end returns a graph that b200_graph_launch replays with one call.  An entry point that would have to
+ * synchronize or reallocate a scratch buffer fails during capture and invalidates it (end then returns an error): run the same work
+ * eagerly once — that grows the buffers — and capture the next time.  A graph holds pointers into the context's scratch buffers and into
+ * every tensor it was recorded with; it is stale once b200_ctx_alloc_generation() has changed. */
+B200_API int      b200_capture_begin(b200_ctx * ctx);
+B200_API int      b200_capture_end(b200_ctx * ctx, void ** graph_out);
+B200_API int      b200_graph_launch(b200_ctx * ctx, void * graph);
+B200_API void     b200_graph_free(void * graph);
+B200_API uint64_t b200_ctx_alloc_generation(const b200_ctx * ctx);
+
 /* ---- the other ops of a Llama graph ---------------------------------------------------------
  * So that a cgraph stays on the device between its MUL_MATs.  Each call restates the reference's CPU forward function of the op
  * (ggml/src/ggml-cpu/ops.cpp, binary-ops.cpp, unary-ops.cpp; the exact lines are cited in csrc/ops.cu) on device tensors with

@@ -46,13 +46,19 @@ struct b200_device_ctx {
     ggml_backend_buffer_type buft;
 };
 
+struct graph_cache_entry { uint64_t key = 0; void * graph = nullptr; uint64_t alloc_gen = 0; int seen = 0; int capture_attempts = 0; bool failed = false; uint64_t stamp = 0; };
+
 struct b200_backend_ctx {
     int         device;
     std::string name;
     b200_ctx *  ctx;
     long        n_graphs = 0, n_mul_mat = 0, n_mul_mat_id = 0, n_fused_groups = 0;      // GGML_B200_STATS=1 prints them on free
     long        n_extra_ops = 0, n_fused_mm = 0;
-    bool        fuse = true;               // GGML_B200_FUSE=0: MUL_MAT + bias / gate + GLU run as separate nodes
+    int         fuse = 1;                  // GGML_B200_FUSE: 0 = MUL_MAT + bias / gate + GLU run as separate nodes, 1 = fused when it pays, 2 = always
+    bool        use_graphs = true;         // GGML_B200_GRAPHS=0: every graph_compute launches its kernels one by one
+    graph_cache_entry graphs[8];           // captured cgraphs, least recently used replaced
+    uint64_t    graph_clock = 0;
+    long        n_graph_captures = 0, n_graph_replays = 0;
     void *      copy_event = nullptr;      // orders cpy_tensor_async after this backend's queued work
     b200_rowsplit * rs = nullptr;          // row-split driver of the split buffer type this backend last computed with
     const void *    rs_key = nullptr;
@@ -396,9 +402,10 @@ const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ct
 void backend_free(ggml_backend_t backend) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     if (const char * e = getenv("GGML_B200_STATS"); e && *e == '1') {
-        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld other_ops=%ld fused_mul_mat=%ld\n", bctx->n_graphs,
-                bctx->n_mul_mat, bctx->n_mul_mat_id, bctx->n_fused_groups, bctx->n_extra_ops, bctx->n_fused_mm);
+        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld other_ops=%ld fused_mul_mat=%ld graph_captures=%ld graph_replays=%ld\n", bctx->n_graphs,
+                bctx->n_mul_mat, bctx->n_mul_mat_id, bctx->n_fused_groups, bctx->n_extra_ops, bctx->n_fused_mm, bctx->n_graph_captures, bctx->n_graph_replays);
     }
+    for (auto & c : bctx->graphs) if (c.graph) b200_graph_free(c.graph);
     if (bctx->copy_event) b200_event_destroy(bctx->device, bctx->copy_event);
     if (bctx->rs) b200_rowsplit_destroy(bctx->rs);
     b200_ctx_destroy(bctx->ctx);
@@ -539,7 +546,7 @@ bool bias_of(const ggml_tensor * add, const ggml_tensor * mm, const ggml_tensor 
     return true;
 }
 
-int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f) {
+int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f, int mode) {
     if (only_mul_mat()) return 0;
     const ggml_tensor * n0 = cgraph->nodes[i];
     if (n0->op != GGML_OP_MUL_MAT || !is_quant_weight(n0->src[0]->type) || n0->ne[1] != 1 || split_src0(n0)) return 0;
@@ -580,6 +587,10 @@ int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f) {
     const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
     const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{}, bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
     if (!b200_mul_mat_fused_supported(&up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d)) return 0;
+    // The fused launch walks the rows with the generic one-warp-per-row GEMV; the unfused path has the fast kernels (0.9 of the HBM peak on
+    // Q4_K).  Measured on the Llama-3-8B decode graph (oracle/llama_step, 1 token, 512 past): everything fused 4.12 ms / step, nothing fused
+    // 3.76 ms — so by default only matrices small enough for the saved launches to outweigh the slower rows are fused.
+    if (mode == 1 && (ggml_nbytes(f.up) + (f.gate ? ggml_nbytes(f.gate) : 0)) > ((size_t) 8 << 20)) return 0;
     return j - i;
 }
 
@@ -588,9 +599,7 @@ int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f) {
 // address ranges), runs of Q4_K decode matmuls become one persistent launch, nodes that share their activations (wq / wk / wv,
 // ffn_gate / ffn_up of a llama graph) share one quantization of them.  The reference's CUDA backend reaches the same end by
 // capturing the whole cgraph into a CUDA graph (ggml-cuda.cu:4457-4490).
-ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
-    b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
-    bctx->n_graphs++;
+ggml_status graph_compute_eager(b200_backend_ctx * bctx, ggml_cgraph * cgraph) {
     std::vector<b200_tensor> ta, tb, td;
     std::vector<const b200_tensor *> pa, pb, pd;
     auto flush = [&]() -> int {
@@ -616,7 +625,7 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
         if ((node->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) continue;
         if (bctx->fuse) {
             fused_mm f;
-            const int used = try_fuse_mul_mat(cgraph, i, f);
+            const int used = try_fuse_mul_mat(cgraph, i, f, bctx->fuse);
             if (used > 0) {
                 int rc = flush();
                 if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
@@ -670,6 +679,92 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
     }
     const int rc = flush();
     if (rc != B200_OK) return failed(rc, last_mm ? last_mm : cgraph->nodes[0]);
+    return GGML_STATUS_SUCCESS;
+}
+
+// CUDA-graph replay of a whole cgraph (reference: ggml-cuda.cu:3287 graph properties, :4457-4490 capture / update / launch).  A cgraph is
+// identified by a hash over every node's op, type, shape, strides, parameters and data pointers (sources included): llama.cpp rebuilds the same
+// graph for every decoded token until the KV-cache view grows past its padding, so a decode step is one cudaGraphLaunch instead of ~600
+// kernel launches.  First sight of a key: eager (this also grows the scratch buffers); second sight: capture + launch; later: launch.
+
+
+uint64_t graph_key(const ggml_cgraph * cgraph) {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void * p, size_t n) { const uint8_t * b = (const uint8_t *) p; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } };
+    auto mix_tensor = [&](const ggml_tensor * t) {
+        mix(&t->type, sizeof(t->type)); mix(t->ne, sizeof(t->ne)); mix(t->nb, sizeof(t->nb)); mix(&t->data, sizeof(t->data));
+    };
+    mix(&cgraph->n_nodes, sizeof(cgraph->n_nodes));
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        const ggml_tensor * n = cgraph->nodes[i];
+        mix(&n->op, sizeof(n->op)); mix(&n->flags, sizeof(n->flags)); mix(n->op_params, sizeof(n->op_params));
+        mix_tensor(n);
+        for (int j = 0; j < GGML_MAX_SRC; ++j) {
+            if (!n->src[j]) { const int z = -1; mix(&z, sizeof(z)); continue; }
+            mix_tensor(n->src[j]);
+        }
+    }
+    return h;
+}
+
+bool graph_capturable(const ggml_cgraph * cgraph) {
+    int work = 0;
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        const ggml_tensor * n = cgraph->nodes[i];
+        if (is_view_op(n->op) || ggml_is_empty(n)) continue;
+        if (n->op == GGML_OP_MUL_MAT && split_src0(n)) return false;        // several devices and their events: stays eager
+        if (n->op == GGML_OP_MUL_MAT_ID) return false;                       // (its routing tables are sized on the host per call)
+        ++work;
+    }
+    return work >= 8;                                                        // short graphs gain nothing
+}
+
+ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
+    bctx->n_graphs++;
+    if (!bctx->use_graphs || !graph_capturable(cgraph)) return graph_compute_eager(bctx, cgraph);
+    const uint64_t key = graph_key(cgraph);
+    graph_cache_entry * e = nullptr, * oldest = &bctx->graphs[0];
+    for (auto & c : bctx->graphs) {
+        if (c.key == key && c.seen > 0) { e = &c; break; }
+        if (c.stamp < oldest->stamp) oldest = &c;
+    }
+    if (!e) {
+        e = oldest;
+        if (e->graph) b200_graph_free(e->graph);
+        *e = graph_cache_entry{};
+        e->key = key;
+    }
+    e->stamp = ++bctx->graph_clock;
+    e->seen++;
+    const uint64_t gen = b200_ctx_alloc_generation(bctx->ctx);
+    if (e->graph && e->alloc_gen != gen) { b200_graph_free(e->graph); e->graph = nullptr; }       // a scratch buffer moved since the capture
+    if (e->graph) {
+        if (b200_graph_launch(bctx->ctx, e->graph) == B200_OK) { bctx->n_graph_replays++; return GGML_STATUS_SUCCESS; }
+        GGML_LOG_ERROR("ggml-b200: graph launch failed (%s), running eagerly\n", b200_last_error());
+        b200_graph_free(e->graph); e->graph = nullptr; e->failed = true;
+    }
+    if (e->seen < 2 || e->failed) return graph_compute_eager(bctx, cgraph);
+    // second sight of this graph: record it
+    const long s_mm = bctx->n_mul_mat, s_id = bctx->n_mul_mat_id, s_fg = bctx->n_fused_groups, s_ops = bctx->n_extra_ops, s_fm = bctx->n_fused_mm;
+    if (b200_capture_begin(bctx->ctx) != B200_OK) { e->failed = true; return graph_compute_eager(bctx, cgraph); }
+    const ggml_status st = graph_compute_eager(bctx, cgraph);
+    void * g = nullptr;
+    const int rc = b200_capture_end(bctx->ctx, &g);
+    if (st != GGML_STATUS_SUCCESS || rc != B200_OK || !g) {
+        // (typically a scratch buffer that had to grow: the eager run below grows it, the next sight of the graph captures)
+        if (g) b200_graph_free(g);
+        bctx->n_mul_mat = s_mm; bctx->n_mul_mat_id = s_id; bctx->n_fused_groups = s_fg; bctx->n_extra_ops = s_ops; bctx->n_fused_mm = s_fm;
+        if (++e->capture_attempts >= 3) e->failed = true;
+        e->seen = 1;
+        return graph_compute_eager(bctx, cgraph);
+    }
+    e->graph = g; e->alloc_gen = b200_ctx_alloc_generation(bctx->ctx);
+    bctx->n_graph_captures++;
+    if (b200_graph_launch(bctx->ctx, e->graph) != B200_OK) {
+        GGML_LOG_ERROR("ggml-b200: graph launch failed (%s)\n", b200_last_error());
+        return GGML_STATUS_FAILED;
+    }
     return GGML_STATUS_SUCCESS;
 }
 
@@ -761,7 +856,8 @@ ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char * /*params
         return nullptr;
     }
     b200_backend_ctx * bctx = new b200_backend_ctx{dctx->device, dctx->name, ctx};
-    if (const char * e = getenv("GGML_B200_FUSE"); e && *e == '0') bctx->fuse = false;
+    if (const char * e = getenv("GGML_B200_FUSE")) bctx->fuse = atoi(e);
+    if (const char * e = getenv("GGML_B200_GRAPHS"); e && *e == '0') bctx->use_graphs = false;
     return new ggml_backend{
         /* .guid    = */ backend_guid(),
         /* .iface   = */ k_backend_iface,

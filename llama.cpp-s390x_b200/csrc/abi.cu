@@ -217,6 +217,7 @@ int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes) {
     // the scratch may still be read by kernels in flight on this stream
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     if (ctx->ws) { cudaFree(ctx->ws); ctx->ws = nullptr; ctx->ws_size = 0; }
+    ctx->alloc_gen++;
     const size_t want = (nbytes + (size_t) (1 << 20) - 1) & ~((size_t) (1 << 20) - 1);
     cudaError_t err = cudaMalloc(&ctx->ws, want);
     if (err != cudaSuccess) {
@@ -606,6 +607,64 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
 }
 
 // ---- raw memory -----------------------------------------------------------------------------------------------------
+// ---- stream capture of a whole graph_compute (reference: ggml_backend_cuda_graph_compute's CUDA-graph path, ggml-cuda.cu:4457-4490) --------
+// Everything the entry points of this library queue on the context's stream between begin and end is recorded instead of executed; an entry
+// point that would have to synchronize or reallocate (a scratch buffer that must grow) fails, which invalidates the capture — the caller
+// ends it, runs the work eagerly (which grows the buffers) and captures the next time.  A captured graph holds pointers into the
+// context's scratch buffers: b200_ctx_alloc_generation() changes whenever one of them moves, graphs captured before that are stale.
+struct b200_graph { cudaGraphExec_t exec; int64_t n_launches; int device; };
+
+int b200_capture_begin(b200_ctx * ctx) {
+    if (!ctx) { b200_set_error("capture_begin: ctx is NULL"); return B200_E_ARG; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+    ctx->capture_launches0 = ctx->launches;
+    return B200_OK;
+}
+
+int b200_capture_end(b200_ctx * ctx, void ** graph_out) {
+    if (!ctx || !graph_out) { b200_set_error("capture_end: NULL argument"); return B200_E_ARG; }
+    *graph_out = nullptr;
+    cudaGraph_t g = nullptr;
+    const cudaError_t err = cudaStreamEndCapture(ctx->stream, &g);
+    const int64_t n = ctx->launches - ctx->capture_launches0;
+    ctx->launches = ctx->capture_launches0;                    // nothing ran
+    ctx->n_pend = 16;
+    if (err != cudaSuccess || !g) {
+        cudaGetLastError();
+        if (g) cudaGraphDestroy(g);
+        b200_set_error("stream capture failed: %s", cudaGetErrorString(err));
+        return B200_E_CUDA;
+    }
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ierr = cudaGraphInstantiate(&exec, g, 0);
+    cudaGraphDestroy(g);
+    if (ierr != cudaSuccess) { cudaGetLastError(); b200_set_error("cudaGraphInstantiate failed: %s", cudaGetErrorString(ierr)); return B200_E_CUDA; }
+    *graph_out = new b200_graph{exec, n, ctx->device};
+    return B200_OK;
+}
+
+int b200_graph_launch(b200_ctx * ctx, void * graph) {
+    if (!ctx || !graph) { b200_set_error("graph_launch: NULL argument"); return B200_E_ARG; }
+    b200_graph * g = (b200_graph *) graph;
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->n_launches;
+    ctx->n_pend = 16;
+    return B200_OK;
+}
+
+void b200_graph_free(void * graph) {
+    if (!graph) return;
+    b200_graph * g = (b200_graph *) graph;
+    device_guard guard;
+    cudaSetDevice(g->device);
+    cudaGraphExecDestroy(g->exec);
+    delete g;
+}
+
+uint64_t b200_ctx_alloc_generation(const b200_ctx * ctx) { return ctx ? ctx->alloc_gen : 0; }
+
 int b200_malloc(int device, size_t nbytes, void ** out) {
     if (!out) return B200_E_ARG;
     *out = nullptr;
@@ -743,6 +802,7 @@ static int grow(b200_ctx * ctx, void ** buf, size_t * have, size_t want) {
     if (want <= *have) return B200_OK;
     B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
     if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
+    ctx->alloc_gen++;
     cudaError_t err = cudaMalloc(buf, want);
     if (err != cudaSuccess) { cudaGetLastError(); b200_set_error("staging allocation failed: %s", cudaGetErrorString(err)); return B200_E_ALLOC; }
     *have = want;
@@ -852,6 +912,7 @@ static int stream_images(b200_ctx * ctx, sq_params & P) {
     if (total > ctx->sq_img_cap) {
         B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
         if (ctx->sq_img) { cudaFree(ctx->sq_img); ctx->sq_img = nullptr; ctx->sq_img_cap = 0; }
+        ctx->alloc_gen++;
         const size_t want = total < ((size_t) 4 << 20) ? ((size_t) 4 << 20) : total;
         if (cudaMalloc((void **) &ctx->sq_img, want) != cudaSuccess) { cudaGetLastError(); b200_set_error("mul_mat_batch: activation image allocation failed"); return B200_E_ALLOC; }
         ctx->sq_img_cap = want;
@@ -947,6 +1008,7 @@ static int stream_run(b200_ctx * ctx, int n, const b200_tensor * const * a, cons
         // grow-only; like the scratch of the other paths this needs one un-captured call before a CUDA-graph capture
         B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
         if (ctx->sq_ll) { cudaFree(ctx->sq_ll); ctx->sq_ll = nullptr; ctx->sq_ll_cap = 0; }
+        ctx->alloc_gen++;
         const size_t want = ll_entries < ((size_t) 1 << 20) ? ((size_t) 1 << 20) : ll_entries;
         if (cudaMalloc((void **) &ctx->sq_ll, want * 8) != cudaSuccess) { cudaGetLastError(); b200_set_error("mul_mat_batch: exchange buffer allocation failed"); return B200_E_ALLOC; }
         B200_CUDA_TRY(cudaMemsetAsync(ctx->sq_ll, 0, want * 8, ctx->stream));

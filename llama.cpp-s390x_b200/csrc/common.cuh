@@ -76,6 +76,8 @@ struct b200_ctx {
     void *       dev_x;   size_t dev_x_size;
     void *       dev_y;   size_t dev_y_size;
     int64_t      launches;
+    uint64_t     alloc_gen;       // bumped whenever a device buffer kernels were given pointers into is reallocated (captured graphs go stale)
+    int64_t      capture_launches0; // ctx->launches when the running stream capture began
     // options
     int          force_generic;   // 1: never use the specialised GEMV kernels
     int          use_tc;          // 1: n > max_gemv_cols goes to the tcgen05 GEMM (when the shape allows)

@@ -16,10 +16,10 @@ PLUGIN = ROOT / "llama.cpp-s390x_b200" / "libggml-b200.so"
 HARNESS = refenv.REF_DIR / "test-backend-ops"
 
 
-def run_harness(*args, timeout=900):
+def run_harness(*args, timeout=900, extra_env=None):
     if not HARNESS.exists() or not PLUGIN.exists():
         pytest.skip("oracle/_ref/test-backend-ops or libggml-b200.so not built (needs /root/reference at build time)")
-    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN)})
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN), **(extra_env or {})})
     p = subprocess.run([str(HARNESS), *args], env=env, capture_output=True, text=True, timeout=timeout)
     out = re.sub(r"\x1b\[[0-9;]*m", "", p.stdout + p.stderr)
     return p.returncode, out
@@ -63,7 +63,7 @@ EXTRA_OPS = {
 def test_backend_ops_llama_graph_ops(op):
     """unmodified test-backend-ops, op by op: everything supports_op() accepts must match the reference's CPU backend (the harness' own
     per-op NMSE limits), and at least the listed number of cases must have run rather than been declined"""
-    rc, out = run_harness("test", "-b", "B2000", "-o", op)
+    rc, out = run_harness("test", "-b", "B2000", "-o", op, extra_env={"GGML_B200_FUSE": "2"})       # (2: fuse whatever the pattern allows)
     tail = "\n".join(out.splitlines()[-25:])
     assert rc == 0 and "Backend B2000: OK" in out, tail
     ran = [l for l in out.splitlines() if re.match(r"\s*" + op + r"\(", l) and l.rstrip().endswith("OK")]
