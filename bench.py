@@ -590,6 +590,11 @@ def run_gpu(args):
             out["moe"] = moe
         if big:
             out["llama3_70b"] = big
+        if world == 1 and not args.no_extras and not args.no_e2e:
+            torch.cuda.empty_cache()
+            wg = whole_graph_bench()
+            if wg:
+                out["whole_graph"] = wg
         if world == 1 and args.cpu_seconds > 0:
             out["cpu_baseline"] = cpu_baseline(seconds=args.cpu_seconds)
         print(json.dumps(out), flush=True)
@@ -791,6 +796,33 @@ def plugin_e2e(args):
     except (OSError, ValueError, subprocess.TimeoutExpired) as exc:
         sys.stderr.write(f"e2e_plugin: {exc}\n")
         return None
+
+
+def whole_graph_bench():
+    """a whole Llama-3-8B decoder graph (GET_ROWS, RMS_NORM, quantized MUL_MAT, ROPE, F16 KV-cache store, attention
+    products over the cache, SOFT_MAX, SWIGLU, residuals, output head) scheduled by the reference's ggml_backend_sched on the plug-in — every
+    node on the device, one split, CUDA-graph replay — against the same graph on the reference's CPU backend (oracle/_ref/llama_step, our
+    oracle/llama_step.cpp hosted by the unmodified libggml).  Host-timed per step: inputs set from host memory, logits read back."""
+    from oracle import refenv
+    exe = refenv.REF_DIR / "llama_step"
+    plugin = ROOT / "llama.cpp-s390x_b200" / "libggml-b200.so"
+    if not exe.exists() or not plugin.exists():
+        return None
+    env = refenv.ref_env({"GGML_BACKEND_PATH": str(plugin)})
+    res = {"harness": "oracle/llama_step.cpp (test infrastructure) -> ggml_backend_sched -> libggml-b200.so; weights: random valid Q4_K blocks, Q6_K head"}
+    for key, argv in (("decode_1_token_512_past", ["8b", "1", "512", "30", "2"]), ("prefill_512_tokens", ["8b", "512", "0", "5", "0"])):
+        try:
+            p = subprocess.run([str(exe), *argv], env=env, capture_output=True, text=True, timeout=900)
+            line = [l for l in p.stdout.splitlines() if l.startswith("{")]
+            if p.returncode != 0 or not line:
+                sys.stderr.write("llama_step failed: " + (p.stdout + p.stderr)[-1000:] + "\n")
+                continue
+            j = json.loads(line[-1])
+            res[key] = {k: j[k] for k in ("n_layer", "n_tokens", "n_past", "splits_b200", "ms_per_step_b200", "tok_per_s_b200", "ms_per_step_cpu",
+                                         "tok_per_s_cpu", "nmse_logits")}
+        except (OSError, ValueError, subprocess.TimeoutExpired) as exc:
+            sys.stderr.write(f"llama_step: {exc}\n")
+    return res if len(res) > 1 else None
 
 
 def decode_batch_bench(torch, pkg, ctx, stream, ops, ns=(2, 4, 8)):
