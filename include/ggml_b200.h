@@ -300,6 +300,18 @@ B200_API int  b200_rowsplit_synchronize(b200_rowsplit * rs);
 B200_API b200_ctx * b200_rowsplit_ctx(b200_rowsplit * rs, int idx);
 
 
+/* ---- all-reduce between the contexts of one process ---------------------------------------------------
+ * What the shell answers "ggml_backend_comm_init / _free / _allreduce_tensor" with (typedefs ggml/include/ggml-backend.h:205-208; the
+ * meta / tensor-parallel backend is the caller, ggml-backend-meta.cpp:1522-1553; reference: ggml-cuda.cu:1184-1312).  data[i] is
+ * participant i's packed F32 tensor of ne elements (16-byte aligned) on ctxs[i]'s device; afterwards every participant holds the
+ * element-wise sum, bit-identical everywhere (summed in participant order).  zero[i] != 0 (or zero == NULL: none): participant i
+ * contributes zeros.  Peer memory over NVLink + events, no library collective; asynchronous on every participant's stream. */
+typedef struct b200_comm b200_comm;
+B200_API int  b200_comm_create(b200_ctx * const * ctxs, int n, b200_comm ** out);       /* n <= 8; enables peer access between the devices */
+B200_API void b200_comm_destroy(b200_comm * comm);
+B200_API int  b200_comm_size(const b200_comm * comm);
+B200_API int  b200_comm_allreduce(b200_comm * comm, void * const * data, const int * zero, int64_t ne);
+
 /* ---- stream capture (reference: the CUDA-graph path of ggml_backend_cuda_graph_compute, ggml/src/ggml-cuda/ggml-cuda.cu:4457-4490) -------
  * Between b200_capture_begin and b200_capture_end every entry point of this header RECORDS its work on the context's stream instead of
  * running it; b200_capture_end returns a graph that b200_graph_launch replays with one call.  An entry point that would have to

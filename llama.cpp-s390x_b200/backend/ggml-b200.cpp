@@ -985,8 +985,58 @@ ggml_backend_feature * get_features(ggml_backend_reg_t) {
     return features;
 }
 
+// ---- ggml_backend_comm_{init, free, allreduce_tensor} (ggml-backend.h:205-208; reference ggml-cuda.cu:1184-1430): the all-reduce of the
+// meta / tensor-parallel backend.  All backends must be B200 backends; a tensor that cannot be reduced here (type, layout) returns
+// false and the meta backend uses its generic path for that call, like the reference's per-call fallback.
+struct b200_comm_ctx { b200_comm * comm; std::vector<ggml_backend_t> backends; };
+
+void * comm_init(ggml_backend_t * backends, size_t n_backends) {
+    if (!backends || n_backends == 0 || n_backends > 8) return nullptr;
+    std::vector<b200_ctx *> ctxs;
+    for (size_t i = 0; i < n_backends; ++i) {
+        if (!backend_is_b200(backends[i])) return nullptr;
+        ctxs.push_back(((b200_backend_ctx *) backends[i]->context)->ctx);
+    }
+    b200_comm * comm = nullptr;
+    if (b200_comm_create(ctxs.data(), (int) n_backends, &comm) != B200_OK) {
+        GGML_LOG_ERROR("ggml-b200: comm_init failed: %s\n", b200_last_error());
+        return nullptr;
+    }
+    return new b200_comm_ctx{comm, std::vector<ggml_backend_t>(backends, backends + n_backends)};
+}
+
+void comm_free(void * comm_ctx) {
+    b200_comm_ctx * c = (b200_comm_ctx *) comm_ctx;
+    if (!c) return;
+    b200_comm_destroy(c->comm);
+    delete c;
+}
+
+bool comm_allreduce_tensor(void * comm_ctx, ggml_tensor ** tensors) {
+    b200_comm_ctx * c = (b200_comm_ctx *) comm_ctx;
+    if (!c || !tensors || !tensors[0]) return false;
+    const size_t n = c->backends.size();
+    const int64_t ne = ggml_nelements(tensors[0]);
+    if (ne == 0) return true;
+    void * data[8]; int zero[8];
+    for (size_t i = 0; i < n; ++i) {
+        const ggml_tensor * t = tensors[i];
+        if (!t || t->type != GGML_TYPE_F32 || ggml_nelements(t) != ne || !ggml_is_contiguously_allocated(t) || ((uintptr_t) t->data & 15)) return false;
+        data[i] = t->data;
+        zero[i] = (t->flags & GGML_TENSOR_FLAG_COMPUTE) == 0;         // not computed on this backend: contributes zeros (ggml-cuda.cu:1205-1211)
+    }
+    if (b200_comm_allreduce(c->comm, data, zero, ne) != B200_OK) {
+        GGML_LOG_ERROR("ggml-b200: allreduce failed: %s\n", b200_last_error());
+        return false;
+    }
+    return true;
+}
+
 void * reg_get_proc_address(ggml_backend_reg_t, const char * name) {
     if (strcmp(name, "ggml_backend_get_features") == 0) return (void *) get_features;
+    if (strcmp(name, "ggml_backend_comm_init") == 0) return (void *) comm_init;                          // ggml_backend_comm_init_t
+    if (strcmp(name, "ggml_backend_comm_free") == 0) return (void *) comm_free;                          // ggml_backend_comm_free_t
+    if (strcmp(name, "ggml_backend_comm_allreduce_tensor") == 0) return (void *) comm_allreduce_tensor;  // ggml_backend_comm_allreduce_tensor_t
     if (strcmp(name, "ggml_backend_split_buffer_type") == 0) return (void *) split_buffer_type;      // ggml_backend_split_buffer_type_t
     return nullptr;
 }

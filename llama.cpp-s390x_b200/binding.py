@@ -23,7 +23,7 @@ EXPORTS = [
     "b200_event_record", "b200_event_wait", "b200_event_synchronize", "b200_rowsplit_create", "b200_rowsplit_destroy", "b200_rowsplit_n_dev",
     "b200_rowsplit_rows", "b200_rowsplit_upload", "b200_rowsplit_weights_free", "b200_rowsplit_mul_mat", "b200_rowsplit_mul_mat_main",
     "b200_rowsplit_synchronize", "b200_rowsplit_ctx",
-    "b200_capture_begin", "b200_capture_end", "b200_graph_launch", "b200_graph_free", "b200_ctx_alloc_generation",
+    "b200_comm_create", "b200_comm_destroy", "b200_comm_size", "b200_comm_allreduce", "b200_capture_begin", "b200_capture_end", "b200_graph_launch", "b200_graph_free", "b200_ctx_alloc_generation",
     "b200_op_binary", "b200_op_repeat", "b200_op_add_id", "b200_op_glu", "b200_op_unary", "b200_op_unary_supported", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope",
     "b200_op_soft_max", "b200_op_cpy", "b200_op_get_rows", "b200_op_set_rows", "b200_mul_mat_f", "b200_mul_mat_f_supported", "b200_mul_mat_fused",
     "b200_mul_mat_fused_supported",
@@ -81,7 +81,7 @@ def lib() -> C.CDLL:
     sig("b200_mul_mat", i32, [vp, T, T, T]); sig("b200_mul_mat_supported", i32, [T, T, T])
     sig("b200_mul_mat_noalloc", i32, [vp, T, T, T])
     f32 = C.c_float
-    sig("b200_capture_begin", i32, [vp]); sig("b200_capture_end", i32, [vp, C.POINTER(vp)]); sig("b200_graph_launch", i32, [vp, vp])
+    sig("b200_comm_create", "b200_comm_destroy", "b200_comm_size", "b200_comm_allreduce", "b200_capture_begin", i32, [vp]); sig("b200_capture_end", i32, [vp, C.POINTER(vp)]); sig("b200_graph_launch", i32, [vp, vp])
     sig("b200_graph_free", None, [vp]); sig("b200_ctx_alloc_generation", C.c_uint64, [vp])
     sig("b200_op_binary", i32, [vp, i32, T, T, T]); sig("b200_op_repeat", i32, [vp, T, T]); sig("b200_op_add_id", i32, [vp, T, T, T, T])
     sig("b200_op_glu", i32, [vp, i32, T, T, T, i32, f32, f32]); sig("b200_op_unary", i32, [vp, i32, T, T]); sig("b200_op_unary_supported", i32, [i32])

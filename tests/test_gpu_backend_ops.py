@@ -98,6 +98,20 @@ def test_layer_graph_through_sched(wtype, n_tokens, mode):
     assert (other == 0) == (mode == "mul_mat_only"), m.group(0)
 
 
+COMM_CHECK = refenv.REF_DIR / "comm_check"
+
+
+@pytest.mark.parametrize("args", [("2", "4096"), ("2", "1000003"), ("3", "65536", "1"), ("4", "262147"), ("8", "4096", "5"), ("1", "777")])
+def test_comm_allreduce_through_the_registry(args):
+    """oracle/comm_check.cpp: ggml_backend_comm_init / _allreduce_tensor / _free obtained from the plug-in's registry the way the reference's
+    meta (tensor-parallel) backend does: every participant ends with the bit-exact participant-order sum, a tensor
+    that was not computed contributes zeros, an F16 tensor is declined.  With one GPU the participants are backends of the same device."""
+    if not COMM_CHECK.exists() or not PLUGIN.exists():
+        pytest.skip("oracle/_ref/comm_check or libggml-b200.so not built (needs /root/reference at build time)")
+    p = subprocess.run([str(COMM_CHECK), *args], env=refenv.ref_env({"GGML_BACKEND_PATH": str(PLUGIN)}), capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and p.stdout.strip().splitlines()[-1] == "OK", (p.stdout + p.stderr)[-2000:]
+
+
 LLAMA_STEP = refenv.REF_DIR / "llama_step"
 
 
