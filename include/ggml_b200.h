@@ -59,9 +59,13 @@ enum {
     B200_TYPE_F32  = 0,
     B200_TYPE_F16  = 1,      /* graph ops only (KV cache, masks); MUL_MAT weights of this type go to b200_mul_mat_f */
     B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q4_1 = 3,      /* Q4_1 / Q5_0 / Q5_1 / Q5_K: the generic GEMV family, GET_ROWS; no tensor-core path yet */
+    B200_TYPE_Q5_0 = 6,
+    B200_TYPE_Q5_1 = 7,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
     B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,
     B200_TYPE_I32  = 26,
     B200_TYPE_I64  = 27,     /* SET_ROWS indices */

@@ -432,7 +432,10 @@ bool is_view_op(ggml_op op) {
 // ---- the other ops of a Llama graph: which forms the kernels take, and their dispatch ----------------
 bool is_f32(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32; }
 bool is_float_type(ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16 || t == GGML_TYPE_BF16; }
-bool is_quant_weight(ggml_type t) { return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K; }
+bool is_quant_weight(ggml_type t) {
+    return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K ||
+           t == GGML_TYPE_Q4_1 || t == GGML_TYPE_Q5_0 || t == GGML_TYPE_Q5_1 || t == GGML_TYPE_Q5_K;           // (N4: generic GEMV family)
+}
 
 // GGML_B200_OPS=mul_mat: answer supports_op() for MUL_MAT / MUL_MAT_ID only (the round-1 behaviour: every other node of a graph runs
 // on another backend, the scheduler copies activations across — kept so that split structure stays tested)

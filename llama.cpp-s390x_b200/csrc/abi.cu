@@ -231,7 +231,8 @@ int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes) {
 
 // ---- validation -----------------------------------------------------------------------------------------------------
 static bool is_weight_type(int t) {
-    return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K;
+    return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K ||
+           t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q5_K;       // (these four: generic GEMV family only)
 }
 
 static bool f32_contiguous(const b200_tensor * t) {
@@ -240,7 +241,7 @@ static bool f32_contiguous(const b200_tensor * t) {
 
 static const char * check_mul_mat(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
     if (!a || !b || !d) return "NULL tensor";
-    if (!is_weight_type(a->type)) return "src0 type is not Q4_0/Q8_0/Q4_K/Q6_K";
+    if (!is_weight_type(a->type)) return "src0 type is not one of Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q8_0 / Q4_K / Q5_K / Q6_K";
     if (b->type != B200_TYPE_F32 || d->type != B200_TYPE_F32) return "src1/dst must be F32";
     const int64_t k = a->ne[0];
     if (k <= 0 || k % b200_blck(a->type) != 0) return "ne00 is not a whole number of blocks";

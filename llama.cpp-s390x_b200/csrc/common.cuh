@@ -27,15 +27,20 @@
 #define SZ_Q8_1  36
 #define SZ_Q4_K  144
 #define SZ_Q6_K  210
+#define SZ_Q4_1  20
+#define SZ_Q5_0  22
+#define SZ_Q5_1  24
+#define SZ_Q5_K  176
 
 __host__ __device__ constexpr int b200_blck(int type) {
-    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K) ? QK_K
-         : (type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q8_1) ? QK_SMALL
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K) ? QK_K
+         : (type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q8_1 || type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1) ? QK_SMALL
          : (type == B200_TYPE_F32 || type == B200_TYPE_I32 || type == B200_TYPE_F16 || type == B200_TYPE_BF16 || type == B200_TYPE_I64) ? 1 : 0;
 }
 __host__ __device__ constexpr int b200_tsize(int type) {
     return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : type == B200_TYPE_Q8_1 ? SZ_Q8_1
          : type == B200_TYPE_Q4_K ? SZ_Q4_K : type == B200_TYPE_Q6_K ? SZ_Q6_K
+         : type == B200_TYPE_Q4_1 ? SZ_Q4_1 : type == B200_TYPE_Q5_0 ? SZ_Q5_0 : type == B200_TYPE_Q5_1 ? SZ_Q5_1 : type == B200_TYPE_Q5_K ? SZ_Q5_K
          : (type == B200_TYPE_F32 || type == B200_TYPE_I32) ? 4 : (type == B200_TYPE_F16 || type == B200_TYPE_BF16) ? 2 : type == B200_TYPE_I64 ? 8 : 0;
 }
 

@@ -152,6 +152,81 @@ template <> struct w_unit<B200_TYPE_Q6_K> {
     }
 };
 
+// N4 — Q4_1 / Q5_0 / Q5_1 / Q5_K (ggml-common.h:191-239, 330-346; dequantize_row_* ggml-quants.c:417-490, 1669-1697): the same per-block algebra
+// with a block minimum (x = d q + m: the minimum meets the activations' block sum s) and / or a fifth bit (bit e of qh belongs to element e;
+// Q5_K: bit j of qh[l] belongs to sub-block j).
+__device__ __forceinline__ uint32_t spread4(const uint32_t h4) {          // bits 0..3 -> bit 4 of bytes 0..3
+    return ((h4 & 1u) << 4) | ((h4 & 2u) << 11) | ((h4 & 4u) << 18) | ((h4 & 8u) << 25);
+}
+
+template <> struct w_unit<B200_TYPE_Q4_1> {
+    int lo[4], hi[4]; float d, m;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint8_t * bp = row + ib * SZ_Q4_1;
+        d = ld_half(bp); m = ld_half(bp + 2);
+        uint32_t q[4];
+        ldw_b2<4>(bp + 4, q);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { lo[i] = q[i] & 0x0F0F0F0Fu; hi[i] = (q[i] >> 4) & 0x0F0F0F0Fu; }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sumi = __dp4a(lo[i], u.a[i], sumi); sumi = __dp4a(hi[i], u.a[i + 4], sumi); }
+        return d * u.d * (float) sumi + m * u.s;
+    }
+};
+
+template <int TYPE> struct w_unit_q5 {          // Q5_0 (TYPE = Q5_0: offset 16, no minimum) and Q5_1 (minimum)
+    int v[8]; float d, m;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        constexpr int SZ = TYPE == B200_TYPE_Q5_0 ? SZ_Q5_0 : SZ_Q5_1, OFF = TYPE == B200_TYPE_Q5_0 ? 2 : 4;
+        const uint8_t * bp = row + ib * SZ;
+        d = ld_half(bp); m = TYPE == B200_TYPE_Q5_0 ? 0.0f : ld_half(bp + 2);
+        uint32_t w[5];
+        ldw_b2<5>(bp + OFF, w);                  // qh, then the 16 nibble bytes
+        const uint32_t qh = w[0];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            v[i]     = (int) ((w[i + 1] & 0x0F0F0F0Fu)        | spread4((qh >> (4 * i)) & 0xFu));
+            v[i + 4] = (int) (((w[i + 1] >> 4) & 0x0F0F0F0Fu) | spread4((qh >> (16 + 4 * i)) & 0xFu));
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sumi = __dp4a(v[i], u.a[i], sumi);
+        return TYPE == B200_TYPE_Q5_0 ? d * (u.d * (float) sumi - 16.0f * u.s) : d * u.d * (float) sumi + m * u.s;
+    }
+};
+template <> struct w_unit<B200_TYPE_Q5_0> : w_unit_q5<B200_TYPE_Q5_0> {};
+template <> struct w_unit<B200_TYPE_Q5_1> : w_unit_q5<B200_TYPE_Q5_1> {};
+
+template <> struct w_unit<B200_TYPE_Q5_K> {
+    int v[8]; float dsc, dmn;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7);
+        const uint32_t * bp = reinterpret_cast<const uint32_t *>(row + sb * SZ_Q5_K);     // 176-byte blocks: 4-byte aligned
+        const float2 dm = __half22float2(*reinterpret_cast<const half2 *>(bp));
+        int sc, mn;
+        q4k_scale_min(j, __ldg(bp + 1), __ldg(bp + 2), __ldg(bp + 3), sc, mn);
+        dsc = dm.x * (float) sc;
+        dmn = dm.y * (float) mn;
+        const uint32_t * qh = bp + 4;                  // 32 bytes: bit j of byte l = fifth bit of element l of sub-block j
+        const uint32_t * q  = bp + 12 + 8 * (j >> 1);  // 32 bytes: the nibbles of sub-blocks 2c (low) and 2c + 1 (high)
+        const int sh = 4 * (j & 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = (int) (((__ldg(q + i) >> sh) & 0x0F0F0F0Fu) | (((__ldg(qh + i) >> j) & 0x01010101u) << 4));
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0, sum8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { sumi = __dp4a(v[i], u.a[i], sumi); sum8 = __dp4a(0x01010101, u.a[i], sum8); }
+        return u.d * (dsc * (float) sumi - dmn * (float) sum8);
+    }
+};
+
 constexpr int GENERIC_WARPS = 4;
 
 template <int TYPE, int NC>
@@ -648,6 +723,10 @@ int b200_launch_gemv_fused(b200_ctx * ctx, int type, const mm_problem & P, const
         case B200_TYPE_Q8_0: gemv_fused<B200_TYPE_Q8_0><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         case B200_TYPE_Q4_K: gemv_fused<B200_TYPE_Q4_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         case B200_TYPE_Q6_K: gemv_fused<B200_TYPE_Q6_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q4_1: gemv_fused<B200_TYPE_Q4_1><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q5_0: gemv_fused<B200_TYPE_Q5_0><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q5_1: gemv_fused<B200_TYPE_Q5_1><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q5_K: gemv_fused<B200_TYPE_Q5_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         default: b200_set_error("fused GEMV: unsupported weight type %d", type); return B200_E_UNSUPPORTED;
     }
     B200_CUDA_TRY(cudaGetLastError());
@@ -663,6 +742,10 @@ int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int
         case B200_TYPE_Q8_0: return launch_generic_t<B200_TYPE_Q8_0>(ctx, P, nc, tiles);
         case B200_TYPE_Q4_K: return launch_generic_t<B200_TYPE_Q4_K>(ctx, P, nc, tiles);
         case B200_TYPE_Q6_K: return launch_generic_t<B200_TYPE_Q6_K>(ctx, P, nc, tiles);
+        case B200_TYPE_Q4_1: return launch_generic_t<B200_TYPE_Q4_1>(ctx, P, nc, tiles);
+        case B200_TYPE_Q5_0: return launch_generic_t<B200_TYPE_Q5_0>(ctx, P, nc, tiles);
+        case B200_TYPE_Q5_1: return launch_generic_t<B200_TYPE_Q5_1>(ctx, P, nc, tiles);
+        case B200_TYPE_Q5_K: return launch_generic_t<B200_TYPE_Q5_K>(ctx, P, nc, tiles);
     }
     b200_set_error("gemv: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;

@@ -53,6 +53,34 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
             const uint8_t * b = row + (i >> 5) * SZ_Q8_0;
             return (float) (int8_t) b[2 + (i & 31)] * ld_half(b);
         }
+        case B200_TYPE_Q4_1: {                                  // ggml-quants.c:417-436
+            const uint8_t * b = row + (i >> 5) * SZ_Q4_1;
+            const int j = (int) (i & 31);
+            const int q = j < 16 ? (b[4 + j] & 0xF) : (b[4 + j - 16] >> 4);
+            return __fadd_rn(__fmul_rn((float) q, ld_half(b)), ld_half(b + 2));
+        }
+        case B200_TYPE_Q5_0: case B200_TYPE_Q5_1: {             // ggml-quants.c:438-490
+            const bool one = type == B200_TYPE_Q5_1;
+            const uint8_t * b = row + (i >> 5) * (one ? SZ_Q5_1 : SZ_Q5_0);
+            const uint8_t * qhp = b + (one ? 4 : 2);
+            const uint32_t qh = (uint32_t) qhp[0] | ((uint32_t) qhp[1] << 8) | ((uint32_t) qhp[2] << 16) | ((uint32_t) qhp[3] << 24);
+            const int j = (int) (i & 31);
+            const int nib = j < 16 ? (qhp[4 + j] & 0xF) : (qhp[4 + j - 16] >> 4);
+            const int q = nib | (int) (((qh >> j) & 1u) << 4);
+            return one ? __fadd_rn(__fmul_rn((float) q, ld_half(b)), ld_half(b + 2)) : (float) (q - 16) * ld_half(b);
+        }
+        case B200_TYPE_Q5_K: {                                  // ggml-quants.c:1669-1697
+            const uint8_t * b = row + (i >> 8) * SZ_Q5_K;
+            const int e = (int) (i & 255), j = e >> 5, l = e & 31;
+            const float d = ld_half(b), dmin = ld_half(b + 2);
+            const uint8_t * sc = b + 4;
+            int s, m;
+            if (j < 4) { s = sc[j] & 63; m = sc[j + 4] & 63; }
+            else       { s = (sc[j + 4] & 0xF) | ((sc[j - 4] >> 6) << 4); m = (sc[j + 4] >> 4) | ((sc[j] >> 6) << 4); }
+            const uint8_t qb = b[48 + 32 * (j >> 1) + l];
+            const int q = ((j & 1) ? (qb >> 4) : (qb & 0xF)) + (((b[16 + l] >> j) & 1) ? 16 : 0);
+            return __fsub_rn(__fmul_rn(__fmul_rn(d, (float) s), (float) q), __fmul_rn(dmin, (float) m));
+        }
         case B200_TYPE_Q4_K: {                                  // ggml-quants.c:1467-1489
             const uint8_t * b = row + (i >> 8) * SZ_Q4_K;
             const int e = (int) (i & 255), j = e >> 5, l = e & 31;       // sub-block j, element l
@@ -186,7 +214,8 @@ int b200_op_cpy(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d) {
 
 int b200_op_get_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * idx, const b200_tensor * d) {
     if (!ctx || !a || !idx || !d) { b200_set_error("b200_op_get_rows: null argument"); return B200_E_ARG; }
-    const bool type_ok = cpy_type_ok(a->type) || a->type == B200_TYPE_Q4_0 || a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_K || a->type == B200_TYPE_Q6_K;
+    const bool type_ok = cpy_type_ok(a->type) || a->type == B200_TYPE_Q4_0 || a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_K || a->type == B200_TYPE_Q6_K ||
+                         a->type == B200_TYPE_Q4_1 || a->type == B200_TYPE_Q5_0 || a->type == B200_TYPE_Q5_1 || a->type == B200_TYPE_Q5_K;
     if (!type_ok || idx->type != B200_TYPE_I32 || d->type != B200_TYPE_F32 || d->nb[0] != 4 || d->ne[0] != a->ne[0] ||
         d->ne[1] != idx->ne[0] || d->ne[2] != idx->ne[1] || d->ne[3] != idx->ne[2] || a->ne[0] % b200_blck_size(a->type) != 0) {
         b200_set_error("b200_op_get_rows: f32 / f16 / bf16 / q4_0 / q8_0 / q4_K / q6_K rows, i32 indices, f32 result"); return B200_E_UNSUPPORTED;

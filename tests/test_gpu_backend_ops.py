@@ -41,6 +41,16 @@ def test_backend_ops(op):
     assert not failed, failed[:5]
 
 
+def test_backend_ops_more_weight_types():
+    """Q4_1 / Q5_0 / Q5_1 / Q5_K weights (generic GEMV family) through the unmodified harness — every MUL_MAT case of
+    those types with F32 activations must run and match the CPU backend"""
+    rc, out = run_harness("test", "-b", "B2000", "-o", "MUL_MAT")
+    assert rc == 0 and "Backend B2000: OK" in out, "\n".join(out.splitlines()[-25:])
+    for t, least in (("q4_1", 40), ("q5_0", 10), ("q5_1", 10), ("q5_K", 10)):
+        ran = [l for l in out.splitlines() if re.search(r"type_a=" + t + r",type_b=f32", l) and l.rstrip().endswith("OK")]
+        assert len(ran) >= least, f"only {len(ran)} {t} cases ran"
+
+
 def test_backend_ops_support_listing():
     rc, out = run_harness("support", "-b", "B2000", "-o", "MUL_MAT")
     assert rc == 0 and "B2000" in out
