@@ -81,7 +81,9 @@ def lib() -> C.CDLL:
     sig("b200_mul_mat", i32, [vp, T, T, T]); sig("b200_mul_mat_supported", i32, [T, T, T])
     sig("b200_mul_mat_noalloc", i32, [vp, T, T, T])
     f32 = C.c_float
-    sig("b200_comm_create", "b200_comm_destroy", "b200_comm_size", "b200_comm_allreduce", "b200_capture_begin", i32, [vp]); sig("b200_capture_end", i32, [vp, C.POINTER(vp)]); sig("b200_graph_launch", i32, [vp, vp])
+    sig("b200_comm_create", i32, [C.POINTER(vp), i32, C.POINTER(vp)]); sig("b200_comm_destroy", None, [vp]); sig("b200_comm_size", i32, [vp])
+    sig("b200_comm_allreduce", i32, [vp, C.POINTER(vp), C.POINTER(i32), i64])
+    sig("b200_capture_begin", i32, [vp]); sig("b200_capture_end", i32, [vp, C.POINTER(vp)]); sig("b200_graph_launch", i32, [vp, vp])
     sig("b200_graph_free", None, [vp]); sig("b200_ctx_alloc_generation", C.c_uint64, [vp])
     sig("b200_op_binary", i32, [vp, i32, T, T, T]); sig("b200_op_repeat", i32, [vp, T, T]); sig("b200_op_add_id", i32, [vp, T, T, T, T])
     sig("b200_op_glu", i32, [vp, i32, T, T, T, i32, f32, f32]); sig("b200_op_unary", i32, [vp, i32, T, T]); sig("b200_op_unary_supported", i32, [i32])
