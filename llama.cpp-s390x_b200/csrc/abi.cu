@@ -115,7 +115,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     }
     ctx->force_generic = env_int("GGML_B200_FORCE_GENERIC", 0);
     ctx->use_tc        = env_int("GGML_B200_USE_TC", 1);
-    ctx->tc_pair       = env_int("GGML_B200_TC_PAIR", 0);
+    ctx->tc_pair       = env_int("GGML_B200_TC_PAIR", 1);
     ctx->max_gemv_cols = env_int("GGML_B200_MAX_GEMV_COLS", 8);
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);

@@ -58,7 +58,7 @@ static_assert((TC_A_SLOTS & (TC_A_SLOTS - 1)) == 0, "A ring slots are taken from
 // RAW_ROW: bytes per row and raw slot — 144 (Q4_K: 1 super-block, Q4_0: 8 blocks, Q8_0: 4 blocks + pad) or 224 (Q6_K: one 210-byte
 // super-block + pad; the wider raw ring is paid for with one activation slot and one raw slot)
 template <int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
-    static constexpr int B_SLOTS   = RAW_ROW > TC_RAW_ROW ? 5 : 6;
+    static constexpr int B_SLOTS   = RAW_ROW > TC_RAW_ROW ? 4 : 6;           // an even number: stages travel in pairs
     static constexpr int RAW_SLOTS = RAW_ROW > TC_RAW_ROW ? 3 : 4;
     static constexpr int RAW_BYTES = TC_M * RAW_ROW;
     static constexpr int SMEM      = B_SLOTS * TC_B_BYTES + RAW_SLOTS * RAW_BYTES + 1024 /*alignment slack*/ + 512 /*barriers*/;
@@ -507,8 +507,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
         if (lane == 0) {
             tc::tma_prefetch_desc(&tmW);
             tc::tma_prefetch_desc(&tmB);
-            for (int s = 0; s < BS; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
-            for (int s = 0; s < AS; ++s) { tc::mbar_init(bAFull + 8 * s, 4 * NC); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 4 converter warps (one group) per CTA / commit
+            // Operands travel to the MMA warp in PAIRS of 64-K stages (one barrier round trip and one pair of commits per 128 K: the issue
+            // loop's fixed cost per stage is what an MMA-issue warp among 15 busy warps cannot hide, ncu: the converters spent 41 % of their
+            // time waiting for A slots).  Barrier s of a ring stands for slots 2 s and 2 s + 1.
+            for (int s = 0; s < BS / 2; ++s) { tc::mbar_init(bBFull + 8 * s, 1); tc::mbar_init(bBEmpty + 8 * s, 1); }   // expect_tx / commit
+            for (int s = 0; s < AS / 2; ++s) { tc::mbar_init(bAFull + 8 * s, 8 * NC); tc::mbar_init(bAEmpty + 8 * s, 1); }   // 2 stages x 4 converter warps per CTA / commit
             for (int s = 0; s < RS; ++s) { tc::mbar_init(bRFull + 8 * s, 1); tc::mbar_init(bREmpty + 8 * s, 4 * SPR); }   // expect_tx / 4 converter warps per stage of the slot
             for (int i = 0; i < 2; ++i)  { tc::mbar_init(bAccFull + 8 * i, 1); tc::mbar_init(bAccEmpty + 8 * i, 4 * NC); } // commit / 4 epilogue warps per CTA
             tc::mbar_fence_init();
@@ -553,7 +556,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             for (int lt = first; lt < nst; lt += TC_CONV_GROUPS) {
                 const uint32_t g = gs + (uint32_t) lt;
                 const int it = sg.k0 + lt, sub = lt & (SPR - 1), sbi = it / SPR;
-                const int as = (int) (g & (AS - 1));
+                const int as = (int) (g & (AS - 1)), ap = as >> 1;            // TMEM slot of the stage, barrier of its pair
                 const uint32_t a_ph = (g / AS) & 1u;
                 const uint32_t slotc = g / SPR;
                 const int rs = (int) (slotc % RS);
@@ -578,7 +581,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                     v[4 * s1[c]] = o1[c].x; v[4 * s1[c] + 1] = o1[c].y; v[4 * s1[c] + 2] = o1[c].z; v[4 * s1[c] + 3] = o1[c].w;
                 }
                 if (tid == 0) TC_TRACE(7, (int) g);
-                tc::mbar_wait(bAEmpty + 8 * as, a_ph ^ 1, 40);
+                tc::mbar_wait(bAEmpty + 8 * ap, a_ph ^ 1, 40);
                 tc::tc_fence_after();
                 if (tid == 0) TC_TRACE(2, (int) g);
                 tc::tmem_st32(ta + (uint32_t) (as * TC_A_COLS), v);
@@ -586,7 +589,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 tc::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if (PAIR) tc::mbar_arrive_cluster(rAFull + 8 * as); else tc::mbar_arrive(bAFull + 8 * as);
+                    if (PAIR) tc::mbar_arrive_cluster(rAFull + 8 * ap); else tc::mbar_arrive(bAFull + 8 * ap);
                     tc::mbar_arrive(bREmpty + 8 * rs);
                     if (warp == 0) TC_TRACE(3, (int) g);
                     if (warp == 7) TC_TRACE(5, (int) g);
@@ -608,24 +611,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             const int n16 = (t.nvalid + 15) & ~15, half = n16 >> 1;
             const int nbox = PAIR ? (half + TC_B_BOX_P - 1) / TC_B_BOX_P : (t.nvalid + TC_B_BOX - 1) / TC_B_BOX;
             const int col0 = t.pos0 + (PAIR ? (int) cta_rank * half : 0);
-            for (int it = sg.k0; it < sg.k1; ++it) {
+            for (int it = sg.k0; it < sg.k1; it += 2) {                   // (segments are whole pairs of stages: k is a multiple of 128)
                 tc::mbar_wait(bBEmpty + 8 * bs, b_ph ^ 1, 100);
                 if (lane == 0) TC_TRACE(4, tg);
-                ++tg;
+                tg += 2;
                 if (tc::elect_one()) {
                     if (PAIR) {
                         // both halves of the activation tile report to the leader's barrier (it expects the bytes of both)
-                        if (cta_rank == 0) tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (2 * nbox * TC_B_BOX_P_BYTES));
-                        for (int j = 0; j < nbox; ++j)
-                            tc::tma_load_2d_2cta(sB + bs * TC_B_BYTES + j * TC_B_BOX_P_BYTES, &tmB, rBFull + 8 * bs, it * TC_KS, col0 + j * TC_B_BOX_P);
+                        if (cta_rank == 0) tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (4 * nbox * TC_B_BOX_P_BYTES));
+                        for (int h = 0; h < 2; ++h)
+                            for (int j = 0; j < nbox; ++j)
+                                tc::tma_load_2d_2cta(sB + (2 * bs + h) * TC_B_BYTES + j * TC_B_BOX_P_BYTES, &tmB, rBFull + 8 * bs, (it + h) * TC_KS, col0 + j * TC_B_BOX_P);
                     } else {
-                        tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (nbox * TC_B_BOX_BYTES));
-                        for (int j = 0; j < nbox; ++j)
-                            tc::tma_load_2d(sB + bs * TC_B_BYTES + j * TC_B_BOX_BYTES, &tmB, bBFull + 8 * bs, it * TC_KS, col0 + j * TC_B_BOX);
+                        tc::mbar_arrive_expect_tx(bBFull + 8 * bs, (uint32_t) (2 * nbox * TC_B_BOX_BYTES));
+                        for (int h = 0; h < 2; ++h)
+                            for (int j = 0; j < nbox; ++j)
+                                tc::tma_load_2d(sB + (2 * bs + h) * TC_B_BYTES + j * TC_B_BOX_BYTES, &tmB, bBFull + 8 * bs, (it + h) * TC_KS, col0 + j * TC_B_BOX);
                     }
                 }
                 __syncwarp();
-                if (++bs == BS) { bs = 0; b_ph ^= 1; }
+                if (++bs == BS / 2) { bs = 0; b_ph ^= 1; }
             }
         }
     } else if (warp == TC_W_RAW) {
@@ -668,7 +673,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
             tc::tc_fence_after();
             const uint32_t d_tmem = tmem + acc * TC_NT_MAX;
             const uint32_t idesc = idesc0 | ((uint32_t) ((sg.t.nvalid + 15) >> 4) << 18);      // N = valid columns rounded up to 16 (N >> 3 at bit 17)
-            for (int it = sg.k0; it < sg.k1; ++it) {
+            for (int it = sg.k0; it < sg.k1; it += 2) {                   // a pair of stages per round trip
                 {   // both operands are normally there: probe the two barriers back to back, wait only for what is missing
                     const bool okA = tc::mbar_try_wait(bAFull + 8 * as, a_ph), okB = tc::mbar_try_wait(bBFull + 8 * bs, b_ph);
                     if (!okA) tc::mbar_wait(bAFull + 8 * as, a_ph);
@@ -678,19 +683,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 TC_PHASE(4, lane == 0 && tg == 0);
                 tc::tc_fence_after();
                 if (lane == 0) TC_TRACE(8, tg);
-                const uint32_t da = ta0 + (uint32_t) (as * TC_A_COLS);
-                const uint64_t db = db0 + (uint64_t) (bs * (TC_B_BYTES >> 4));
+                const uint32_t da = ta0 + (uint32_t) (2 * as * TC_A_COLS);
+                const uint64_t db = db0 + (uint64_t) (2 * bs * (TC_B_BYTES >> 4));
                 if (tc::elect_one()) {
                     TC_TRACE(9, tg);
                     if (PAIR) {
 #pragma unroll
-                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts_2cta(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                        for (int kk = 0; kk < 2 * TC_KS / 16; ++kk)
+                            tc::umma_f16_ts_2cta(d_tmem, da + 8 * kk, db + (uint64_t) ((kk >> 2) * (TC_B_BYTES >> 4) + 2 * (kk & 3)), idesc, (uint32_t) (it > sg.k0 || kk > 0));
                         TC_TRACE(10, tg);
                         tc::tc_commit2_mc(bAEmpty + 8 * as, 3);
                         tc::tc_commit2_mc(bBEmpty + 8 * bs, 3);
                     } else {
 #pragma unroll
-                        for (int kk = 0; kk < TC_KS / 16; ++kk) tc::umma_f16_ts(d_tmem, da + 8 * kk, db + 2 * kk, idesc, (uint32_t) (it > sg.k0 || kk > 0));
+                        for (int kk = 0; kk < 2 * TC_KS / 16; ++kk)
+                            tc::umma_f16_ts(d_tmem, da + 8 * kk, db + (uint64_t) ((kk >> 2) * (TC_B_BYTES >> 4) + 2 * (kk & 3)), idesc, (uint32_t) (it > sg.k0 || kk > 0));
                         TC_TRACE(10, tg);
                         tc::tc_commit(bAEmpty + 8 * as);
                         tc::tc_commit(bBEmpty + 8 * bs);
@@ -699,9 +706,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mmq_tc_f16_kernel(const __grid_
                 }
                 __syncwarp();
                 if (lane == 0) TC_TRACE(1, tg);
-                ++tg;
-                if (++as == AS) { as = 0; a_ph ^= 1; }
-                if (++bs == BS) { bs = 0; b_ph ^= 1; }
+                tg += 2;
+                if (++as == AS / 2) { as = 0; a_ph ^= 1; }
+                if (++bs == BS / 2) { bs = 0; b_ph ^= 1; }
             }
             if (tc::elect_one()) { if (PAIR) tc::tc_commit2_mc(bAccFull + 8 * acc, 3); else tc::tc_commit(bAccFull + 8 * acc); }
             __syncwarp();
@@ -964,6 +971,11 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
         for (const int pair : {0, 1}) {
             if ((pair && ctx->tc_pair == 0) || (!pair && ctx->tc_pair == 2)) continue;
             const int64_t rts = row_tiles_of(pair ? 2 * TC_M : TC_M);
+            // auto: pairs where they measure faster — matrices with at least two waves of 256-row tiles (14336 x 4096 x 512: 60.6 vs 62.3 us,
+            // 128256 x 4096: 449 vs 477 us; shorter grids lose 3-5 % to the cluster launch and the remote barrier hops); never with the
+            // fused row-split stores
+            if (pair && ctx->tc_pair == 1 && (P.n_peers > 0 || rts * ((p.n + 191) / 192) * p.batches < (int64_t) ctx->sm_count)) continue;
+            if (!pair && ctx->tc_pair == 1 && P.n_peers == 0 && row_tiles_of(2 * TC_M) * ((p.n + 191) / 192) * p.batches >= (int64_t) ctx->sm_count) continue;
             const int units = pair ? ctx->sm_count / 2 : ctx->sm_count;
             for (const int nt : {192, 128, 64}) {
                 if (forced && nt != forced) continue;

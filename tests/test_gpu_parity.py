@@ -287,7 +287,7 @@ def test_tc_gemm_tilings_give_the_same_bits(pkg, gpu_ctx, orc, name, m, k, n):
         gpu_ctx.set_option("tc_nt", 0); gpu_ctx.set_option("tc_pair", 0); gpu_ctx.set_option("tc_split_k", 2)
         assert nmse(base.cpu().numpy(), pkg.mul_mat(gpu_ctx, t, W, X).cpu().numpy()) <= 1e-10
     finally:
-        gpu_ctx.set_option("tc_nt", 0); gpu_ctx.set_option("tc_pair", 0); gpu_ctx.set_option("tc_split_k", 1)
+        gpu_ctx.set_option("tc_nt", 0); gpu_ctx.set_option("tc_pair", 1); gpu_ctx.set_option("tc_split_k", 1)
 
 
 # ---- (4) MUL_MAT_ID --------------------------------------------------------------------------------------------------------

@@ -38,4 +38,4 @@ for tname, t, make in (("q4_K", 12, bench.device_random_q4k), ("q8_0", 8, bench.
         line += f"  same bits: {same}" + ("" if same else f"  max diff {float((out[0] - out[2]).abs().max()):.3e} of {float(out[0].abs().max()):.3e}")
         print(line, flush=True)
         del Ws
-ctx.set_option("tc_pair", 0)
+ctx.set_option("tc_pair", 1)
