@@ -15,6 +15,8 @@
 //                   swizzled shared memory (no separate launch, no q8 round trip through HBM), weights streamed with
 //                   coalesced 128-bit no-allocate loads (4 lanes per 144-byte superblock), d/dmin/6-bit scales applied
 //                   in registers, one fragment of software prefetch, warp-shuffle reduction.
+#include <atomic>
+
 #include "mm_problem.cuh"
 #include "quantize.cuh"
 #include "ops.cuh"
@@ -673,7 +675,7 @@ int launch_q4k_t(b200_ctx * ctx, const mm_problem & P, int64_t tiles, size_t sme
         return B200_E_UNSUPPORTED;
     }
     auto kern = gemv_q4k<NC, NWARPS, MINB, NBUF, VARIANT>;
-    static bool attr_done[16] = {};            // per device
+    static std::atomic<bool> attr_done[16];   // per device (several backends of one device may launch from different threads)
     if (!attr_done[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
         attr_done[ctx->device & 15] = true;

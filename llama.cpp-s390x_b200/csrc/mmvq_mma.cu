@@ -31,6 +31,8 @@
 //     for every KS, grid size and row sharding (the row-split parity property), and never depends on timing.
 #include <cuda.h>
 #include <cstdio>
+#include <atomic>
+
 #include "mm_problem.cuh"
 #include "quantize.cuh"
 #include "tc_ptx.cuh"
@@ -688,7 +690,7 @@ static int mma_quant_launch_t(b200_ctx * ctx, const mm_problem & P, int ncol, ui
 
 template <int TYPE>
 static int mma_launch_t(b200_ctx * ctx, const cudaLaunchConfig_t & cfg, const CUtensorMap & tmw, const mm_problem & P, const mma_args & A) {
-    static bool attr_done[16] = {};
+    static std::atomic<bool> attr_done[16];   // per device (several backends of one device may launch from different threads)
     if (!attr_done[ctx->device & 15]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(gemv_q4k_mma<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ctx->smem_optin));
         attr_done[ctx->device & 15] = true;

@@ -1,3 +1,4 @@
+#include <atomic>
 // mmvq_stream.cu — the decode path as ONE persistent kernel per list of matmuls ("job table").
 //
 // Why: a decoder-layer GEMV at n = 1 streams 2-33 MB, i.e. 0.4-5 us of HBM time; launched one kernel per matmul, every one of them
@@ -594,7 +595,7 @@ int b200_launch_gemv_stream(b200_ctx * ctx, sq_params & P) {
     const int  mode  = !multi ? 0 : P.emu_stride ? 2 : 1;
     auto kern = mode == 0 ? gemv_q4k_stream<0> : mode == 1 ? gemv_q4k_stream<1> : gemv_q4k_stream<2>;
     static std::mutex attr_mutex;
-    static bool attr_done[3][64] = {};         // per variant and device
+    static std::atomic<bool> attr_done[3][64];   // per variant and device (several backends of one device may launch from different threads)
     {
         std::lock_guard<std::mutex> lock(attr_mutex);
         if (!attr_done[mode][ctx->device & 63]) {
