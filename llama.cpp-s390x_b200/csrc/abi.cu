@@ -116,6 +116,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->force_generic = env_int("GGML_B200_FORCE_GENERIC", 0);
     ctx->use_tc        = env_int("GGML_B200_USE_TC", 1);
     ctx->tc_pair       = env_int("GGML_B200_TC_PAIR", 1);
+    ctx->gather_push   = env_int("GGML_B200_GATHER_PUSH", 1);
     ctx->max_gemv_cols = env_int("GGML_B200_MAX_GEMV_COLS", 8);
     ctx->pdl           = env_int("GGML_B200_PDL", 1);
     ctx->fuse_quant    = env_int("GGML_B200_FUSE_QUANT", 1);
@@ -179,6 +180,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     if      (!strcmp(name, "force_generic")) slot = &ctx->force_generic;
     else if (!strcmp(name, "use_tc"))        slot = &ctx->use_tc;
     else if (!strcmp(name, "tc_pair"))       slot = &ctx->tc_pair;
+    else if (!strcmp(name, "gather_push"))   slot = &ctx->gather_push;
     else if (!strcmp(name, "max_gemv_cols")) slot = &ctx->max_gemv_cols;
     else if (!strcmp(name, "pdl"))           slot = &ctx->pdl;
     else if (!strcmp(name, "fuse_quant"))    slot = &ctx->fuse_quant;
@@ -810,11 +812,54 @@ static int grow(b200_ctx * ctx, void ** buf, size_t * have, size_t want) {
     return B200_OK;
 }
 
+// prefill row split: this rank's [n][rows] block goes into rows [row0, row0 + rows) of every rank's [n][dst_m] output with 16-byte stores
+// (NVLink peer mappings).  Round 1 stored from the GEMM epilogue, one 4-byte lane store per value and peer, which made the step slower with
+// every GPU added (10.0 -> 20.0 ms at N = 8); a separate pass moves the same bytes at link speed and leaves the GEMM as fast as unsplit.
+struct push_dst { float * p[B200_MAX_PEERS]; };
+
+__global__ void __launch_bounds__(256) push_shard_kernel(const float * __restrict__ ysh, const int64_t rows, const int64_t n, const push_dst D,
+                                                         const int64_t dst_m, const int64_t row0, const int vec) {
+    float * dst = D.p[blockIdx.y];
+    if (vec) {
+        const int64_t r4 = rows >> 2, total = r4 * n;
+        for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+            const int64_t col = i / r4, r = (i - col * r4) << 2;
+            const uint4 v = *reinterpret_cast<const uint4 *>(ysh + col * rows + r);
+            *reinterpret_cast<uint4 *>(dst + col * dst_m + row0 + r) = v;
+        }
+    } else {
+        const int64_t total = rows * n;
+        for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+            const int64_t col = i / rows, r = i - col * rows;
+            dst[col * dst_m + row0 + r] = ysh[i];
+        }
+    }
+}
+
 int b200_mul_mat_gather(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d_shard,
                         int n_dst, float * const * dst, int64_t dst_m, int64_t dst_row0) {
     if (!ctx || !b || n_dst < 1 || !dst) { b200_set_error("mul_mat_gather: bad argument"); return B200_E_ARG; }
-    // n <= 8: GEMV family; n > 8: tcgen05 GEMM (both store to the peers from their epilogues); completion is the caller's barrier
+    // n <= 8: GEMV family, results stored to the peers from the epilogue; n > 8: tcgen05 GEMM into the shard, then one pass that pushes the
+    // shard to every rank (option gather_push = 0: from the GEMM epilogue as in round 1); completion is the caller's barrier
     if (b->ne[2] * b->ne[3] != 1) { b200_set_error("mul_mat_gather: no batch dims"); return B200_E_UNSUPPORTED; }
+    if (n_dst > B200_MAX_PEERS) { b200_set_error("mul_mat_gather: too many destinations"); return B200_E_ARG; }
+    if (b->ne[1] > ctx->max_gemv_cols && ctx->gather_push && d_shard && a) {
+        int rc = b200_mul_mat_ex(ctx, a, b, d_shard, 0, nullptr, 0, 0);
+        if (rc) return rc;
+        const int64_t rows = a->ne[1], n = b->ne[1];
+        if (rows > 0 && n > 0) {
+            push_dst D = {};
+            bool aligned = ((uintptr_t) d_shard->data & 15) == 0 && rows % 4 == 0 && dst_m % 4 == 0 && dst_row0 % 4 == 0;
+            for (int p = 0; p < n_dst; ++p) { D.p[p] = dst[p]; aligned = aligned && ((uintptr_t) dst[p] & 15) == 0; }
+            const int64_t work = aligned ? (rows / 4) * n : rows * n, blocks = (work + 255) / 256, cap = (int64_t) ctx->sm_count * 8;
+            const dim3 grid((unsigned) (blocks < cap ? blocks : cap), (unsigned) n_dst);
+            push_shard_kernel<<<grid, 256, 0, ctx->stream>>>((const float *) d_shard->data, rows, n, D, dst_m, dst_row0, aligned ? 1 : 0);
+            B200_CUDA_TRY(cudaGetLastError());
+            ctx->launches++;
+        }
+        ctx->n_pend = 16;
+        return B200_OK;
+    }
     const int rc = b200_mul_mat_ex(ctx, a, b, d_shard, n_dst, dst, dst_m, dst_row0);
     // The in-flight write tracker knows d_shard only; the same kernel also wrote this rank's rows of the full-height outputs
     // (dst[p] through peer mappings), and other ranks write the rest.  A later GEMV that reads such a vector must not defer its

@@ -90,6 +90,7 @@ struct b200_ctx {
     int          pdl;             // programmatic dependent launch for back-to-back GEMVs
     int          fuse_quant;      // 1: GEMV quantizes activations in its prologue (no separate launch)
     int          tc_pdl;         // tcgen05 GEMM: programmatic dependent launch of the conversion kernel and the GEMM
+    int          gather_push;    // b200_mul_mat_gather at n > 8: 1 = GEMM into the shard + one pass of 16-byte peer stores (default), 0 = stores from the GEMM epilogue
     int          tc_pair;        // tcgen05 GEMM: CTA pairs (cta_group::2) on 256-row tiles: 0 never, 1 auto (two or more waves of tiles; default), 2 always
     int          tc_split_k;     // tcgen05 GEMM: split long-K matrices with few tiles along K (0 never, 1 auto, 2/4 forced)
     // fused row-split all-gather, one process per GPU (b200_gather_sync_init)
