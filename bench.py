@@ -1073,7 +1073,7 @@ def run_reference(args):
         return
     cb = cpu_baseline(seconds=max(8.0, min(60.0, 6.0 * (args.steps + args.warmup))))
     out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", args.gpus)),
-           "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "strong",
            "vs_baseline": None, "dtype": "int8 dot x fp32 scales (ggml-cpu Q4_K x Q8_K)", "data": "synthetic",
            "config": {"workload": "Llama-3-8B Q4_K decode step: 225 MUL_MATs at n=1 (bounded per-shape sample, extrapolated)"},
            "cpu_baseline": cb,
