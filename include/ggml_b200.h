@@ -374,6 +374,10 @@ B200_API int b200_mul_mat_f_supported(const b200_tensor * src0, const b200_tenso
  *   gate == NULL: dst = up x + bias_up
  *   gate != NULL: dst = glu(gate x + bias_gate, up x + bias_up)        (act on the gate product, as ggml_glu_split(gate, up))
  * up / gate: quantized matrices of one type and shape, x: F32 with ne[1] == 1, biases: F32 shaped like dst or NULL. */
+/* dst = src0 x src1 + addend in the store of the fast GEMV kernels (n <= 8; addend: contiguous F32 shaped like dst — a bias, or the residual
+ * stream; dst may be the addend's memory, not src1's).  What the shell uses for MUL_MAT + ADD at any matrix size. */
+B200_API int b200_mul_mat_add(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * addend, const b200_tensor * dst);
+B200_API int b200_mul_mat_add_supported(const b200_tensor * src0, const b200_tensor * src1, const b200_tensor * addend, const b200_tensor * dst);
 B200_API int b200_mul_mat_fused(b200_ctx * ctx, const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x,
                                 const b200_tensor * bias_up, const b200_tensor * bias_gate, int glu_op, const b200_tensor * dst);
 B200_API int b200_mul_mat_fused_supported(const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x,

@@ -15,4 +15,4 @@ from .binding import (  # noqa: F401
     B200Error, Context, F32, HostMM, I32, Q4_0, Q4_K, Q6_K, Q8_0, Q8_1, WEIGHT_TYPES, blck_size, build_native, check, lib, lib_path,
     row_size, type_size,
 )
-from .ops import MatmulBatch, MatmulBatchGather, stream_comm_init, gather_ll_init, mul_mat_batch, mm_ids, mul_mat, mul_mat_gather, mul_mat_gather_ll, mul_mat_id, mul_mat_multi, mul_mat_fused, graph_op, mul_mat_noalloc, quantize_row_q8_1, row_shard  # noqa: F401
+from .ops import MatmulBatch, MatmulBatchGather, stream_comm_init, gather_ll_init, mul_mat_batch, mm_ids, mul_mat, mul_mat_gather, mul_mat_gather_ll, mul_mat_id, mul_mat_multi, mul_mat_fused, mul_mat_add, graph_op, mul_mat_noalloc, quantize_row_q8_1, row_shard  # noqa: F401

@@ -538,7 +538,7 @@ int run_extra_op(b200_backend_ctx * bctx, const ggml_tensor * node) {
 //   y  = MUL_MAT(W, x) , ADD(y, bias)                                                                           -> one launch
 // with one activation column per batch, quantized weights, and every intermediate used by the next node of the pattern only.
 // Returns the number of nodes consumed (0: no fusion), the arguments in `f`.
-struct fused_mm { const ggml_tensor * up, * gate, * x, * bias_up, * bias_gate, * out; int glu_op; };
+struct fused_mm { const ggml_tensor * up, * gate, * x, * bias_up, * bias_gate, * out; int glu_op; bool add_only; };
 
 bool bias_of(const ggml_tensor * add, const ggml_tensor * mm, const ggml_tensor ** bias) {
     if (add->op != GGML_OP_ADD) return false;
@@ -552,7 +552,7 @@ bool bias_of(const ggml_tensor * add, const ggml_tensor * mm, const ggml_tensor 
 int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f, int mode) {
     if (only_mul_mat()) return 0;
     const ggml_tensor * n0 = cgraph->nodes[i];
-    if (n0->op != GGML_OP_MUL_MAT || !is_quant_weight(n0->src[0]->type) || n0->ne[1] != 1 || split_src0(n0)) return 0;
+    if (n0->op != GGML_OP_MUL_MAT || !is_quant_weight(n0->src[0]->type) || n0->ne[1] > 8 || split_src0(n0)) return 0;
     f = {};
     auto single_use = [&](int idx) { return ggml_node_has_n_uses(cgraph, idx, 1) && (cgraph->nodes[idx]->flags & GGML_TENSOR_FLAG_OUTPUT) == 0; };
     // first product (+ bias)
@@ -562,7 +562,7 @@ int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f, int mode) 
     const int after_first = j;
     // second product against the same activations (+ bias), then the GLU of the two (llama.cpp's build_ffn computes up first, other graphs
     // gate first: the GLU's src0 says which one is the gate)
-    if (j < cgraph->n_nodes && single_use(j - 1)) {
+    if (n0->ne[1] == 1 && j < cgraph->n_nodes && single_use(j - 1)) {
         const ggml_tensor * m1 = cgraph->nodes[j];
         if (m1->op == GGML_OP_MUL_MAT && m1->src[1] == n0->src[1] && m1->src[0]->type == n0->src[0]->type && ggml_are_same_shape(m1->src[0], n0->src[0]) &&
             ggml_are_same_stride(m1->src[0], n0->src[0]) && !split_src0(m1)) {
@@ -589,6 +589,9 @@ int try_fuse_mul_mat(const ggml_cgraph * cgraph, int i, fused_mm & f, int mode) 
     f.x = n0->src[1];
     const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
     const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{}, bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
+    // MUL_MAT + ADD alone: the addend goes into the store of the fast GEMV kernels (any matrix size, up to 8 columns)
+    if (!f.gate && b200_mul_mat_add_supported(&up, &x, &bu, &d)) { f.add_only = true; return j - i; }
+    if (n0->ne[1] != 1) return 0;
     if (!b200_mul_mat_fused_supported(&up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d)) return 0;
     // The fused launch walks the rows with the generic one-warp-per-row GEMV; the unfused path has the fast kernels (0.9 of the HBM peak on
     // Q4_K).  Measured on the Llama-3-8B decode graph (oracle/llama_step, 1 token, 512 past): everything fused 4.12 ms / step, nothing fused
@@ -635,7 +638,8 @@ ggml_status graph_compute_eager(b200_backend_ctx * bctx, ggml_cgraph * cgraph) {
                 const b200_tensor up = to_b200(f.up), x = to_b200(f.x), d = to_b200(f.out);
                 const b200_tensor gt = f.gate ? to_b200(f.gate) : b200_tensor{}, bu = f.bias_up ? to_b200(f.bias_up) : b200_tensor{};
                 const b200_tensor bg = f.bias_gate ? to_b200(f.bias_gate) : b200_tensor{};
-                rc = b200_mul_mat_fused(bctx->ctx, &up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d);
+                rc = f.add_only ? b200_mul_mat_add(bctx->ctx, &up, &x, &bu, &d)
+                                : b200_mul_mat_fused(bctx->ctx, &up, f.gate ? &gt : nullptr, &x, f.bias_up ? &bu : nullptr, f.bias_gate ? &bg : nullptr, f.glu_op, &d);
                 if (rc != B200_OK) return failed(rc, node);
                 bctx->n_fused_mm++;
                 i += used - 1;

@@ -25,7 +25,7 @@ EXPORTS = [
     "b200_rowsplit_synchronize", "b200_rowsplit_ctx",
     "b200_comm_create", "b200_comm_destroy", "b200_comm_size", "b200_comm_allreduce", "b200_capture_begin", "b200_capture_end", "b200_graph_launch", "b200_graph_free", "b200_ctx_alloc_generation",
     "b200_op_binary", "b200_op_repeat", "b200_op_add_id", "b200_op_glu", "b200_op_unary", "b200_op_unary_supported", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope",
-    "b200_op_soft_max", "b200_op_cpy", "b200_op_get_rows", "b200_op_set_rows", "b200_mul_mat_f", "b200_mul_mat_f_supported", "b200_mul_mat_fused",
+    "b200_op_soft_max", "b200_op_cpy", "b200_op_get_rows", "b200_op_set_rows", "b200_mul_mat_f", "b200_mul_mat_f_supported", "b200_mul_mat_add", "b200_mul_mat_add_supported", "b200_mul_mat_fused",
     "b200_mul_mat_fused_supported",
 ]
 
@@ -91,6 +91,7 @@ def lib() -> C.CDLL:
     sig("b200_op_rope", i32, [vp, T, T, T, T, C.POINTER(i32)]); sig("b200_op_soft_max", i32, [vp, T, T, T, T, f32, f32])
     sig("b200_op_cpy", i32, [vp, T, T]); sig("b200_op_get_rows", i32, [vp, T, T, T]); sig("b200_op_set_rows", i32, [vp, T, T, T])
     sig("b200_mul_mat_f", i32, [vp, T, T, T]); sig("b200_mul_mat_f_supported", i32, [T, T, T])
+    sig("b200_mul_mat_add", i32, [vp, T, T, T, T]); sig("b200_mul_mat_add_supported", i32, [T, T, T, T])
     sig("b200_mul_mat_fused", i32, [vp, T, T, T, T, T, i32, T]); sig("b200_mul_mat_fused_supported", i32, [T, T, T, T, T, i32, T])
     sig("b200_mul_mat_id", i32, [vp, T, T, T, T]); sig("b200_mul_mat_id_supported", i32, [T, T, T, T])
     sig("b200_mm_ids", i32, [vp, vp, i64, i32, i32, i64, vp, vp])

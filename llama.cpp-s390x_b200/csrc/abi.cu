@@ -27,7 +27,7 @@ int    b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * buf, int64_t cap, uin
 int    b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d);
 size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
-                       int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
+                       int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0, const float * bias = nullptr);
 
 // ---- errors ---------------------------------------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -368,6 +368,29 @@ int b200_mul_mat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, c
 
 }  // extern "C"
 
+// MUL_MAT + ADD in the store of the fast GEMV kernels (n <= 8): dst = src0 x src1 + addend, addend shaped like dst (a bias repeated by the
+// caller, or the residual stream).  dst may be the addend's own memory (each element is read and written by one thread); it must not
+// overlap src1.
+extern "C" int b200_mul_mat_add_supported(const b200_tensor * a, const b200_tensor * b, const b200_tensor * addend, const b200_tensor * d) {
+    if (!a || !b || !addend || !d || check_mul_mat(a, b, d)) return 0;
+    if (b->ne[1] > 8 || b->ne[2] * b->ne[3] > 65535) return 0;
+    if (addend->type != B200_TYPE_F32 || !f32_contiguous(addend)) return 0;
+    for (int i = 0; i < 4; ++i) if (addend->ne[i] != d->ne[i]) return 0;
+    const char * xl, * xh, * dl, * dh;
+    tensor_extent(b, &xl, &xh); tensor_extent(d, &dl, &dh);
+    return !(xl < dh && dl < xh);
+}
+
+extern "C" int b200_mul_mat_add(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * addend, const b200_tensor * d) {
+    if (!ctx) { b200_set_error("mul_mat_add: ctx is NULL"); return B200_E_ARG; }
+    if (!b200_mul_mat_add_supported(a, b, addend, d) || b->ne[1] > ctx->max_gemv_cols) {
+        b200_set_error("mul_mat_add: quantized src0, n <= 8, a contiguous F32 addend shaped like dst, dst not overlapping src1"); return B200_E_UNSUPPORTED;
+    }
+    const int rc = b200_mul_mat_ex(ctx, a, b, d, 0, nullptr, 0, 0, (const float *) addend->data);
+    ctx->n_pend = 16;          // the addend may come from a kernel the write tracker does not know
+    return rc;
+}
+
 // ---- N2: MUL_MAT (+ bias) (+ gate MUL_MAT (+ bias) + GLU), one activation column per batch ---------------------------------------
 static const char * check_fused(const b200_tensor * up, const b200_tensor * gate, const b200_tensor * x, const b200_tensor * bu, const b200_tensor * bg,
                                 int glu_op, const b200_tensor * d) {
@@ -418,7 +441,7 @@ extern "C" int b200_mul_mat_fused(b200_ctx * ctx, const b200_tensor * up, const 
 
 // MUL_MAT with the row-split all-gather fused into the store: results also go to peer_Y[p][col*peer_m + peer_row0 + row]
 int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
-                    int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0) {
+                    int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0, const float * bias) {
     if (!ctx) { b200_set_error("mul_mat: ctx is NULL"); return B200_E_ARG; }
     if (n_peers < 0 || n_peers > B200_MAX_PEERS) { b200_set_error("mul_mat: n_peers out of range"); return B200_E_ARG; }
     if (const char * why = check_mul_mat(a, b, d)) { b200_set_error("mul_mat: %s", why); return B200_E_ARG; }
@@ -434,6 +457,8 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
     P.ne11 = n; P.ne12 = b->ne[2]; P.ne13 = b->ne[3];
     P.r2 = b->ne[2] / a->ne[2]; P.r3 = b->ne[3] / a->ne[3];
     P.Y = (float *) d->data;
+    P.bias = bias;
+    if (bias && n > ctx->max_gemv_cols) { b200_set_error("mul_mat: an addend is taken by the GEMV kernels only (n <= %d)", ctx->max_gemv_cols); return B200_E_UNSUPPORTED; }
     P.mode = MM_PLAIN;
     P.n_peers = n_peers; P.peer_m = peer_m; P.peer_row0 = peer_row0;
     for (int p = 0; p < n_peers; ++p) P.peer_Y[p] = peer_Y[p];
@@ -482,6 +507,7 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
                     P2 = P;
                     P2.X    = reinterpret_cast<const float *>(reinterpret_cast<const char *>(P.X) + c0 * P.nb11);
                     P2.Y    = P.Y + c0 * m;
+                    P2.bias = P.bias ? P.bias + c0 * m : nullptr;
                     P2.ne11 = n - c0 < 4 ? n - c0 : 4;
                     const int rc = b200_launch_gemv_mma(ctx, a->type, P2, 1, late && c0 == 0);
                     if (rc) return rc;

@@ -23,6 +23,9 @@ struct mm_problem {
     int64_t r2, r3;        // broadcast ratios ne12/ne02, ne13/ne03
     // output: contiguous f32, column stride m
     float * Y;
+    // optional addend laid out like Y (a bias or the residual stream): y = W x + bias, added where the result is stored (per-launch GEMV
+    // kernels only; single matrix)
+    const float * bias;
     // MUL_MAT_ID
     int            mode;
     const int32_t *ids;          // [n_used, n_tokens] with row stride ids_ne_stride (in int32 elements)
@@ -66,7 +69,8 @@ struct mm_problem {
 
 
 // store one result (row, plane-order column index `ycol` = (Y column pointer - P.Y) / m) locally and to the peers
-__device__ __forceinline__ void mm_store(const mm_problem & P, float * ycol_ptr, const int64_t row, const float v) {
+__device__ __forceinline__ void mm_store(const mm_problem & P, float * ycol_ptr, const int64_t row, float v) {
+    if (P.bias) v += P.bias[(ycol_ptr - P.Y) + row];
     ycol_ptr[row] = v;
     if (P.n_peers > 0) {
         const int64_t col = (ycol_ptr - P.Y) / P.m;

@@ -18,7 +18,7 @@
 #include <cstring>
 
 int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b, const b200_tensor * d,
-                    int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0);
+                    int n_peers, float * const * peer_Y, int64_t peer_m, int64_t peer_row0, const float * bias = nullptr);
 
 namespace {
 

@@ -109,6 +109,16 @@ def mul_mat_fused(ctx: Context, wtype: int, w_up, x, w_gate=None, bias_up=None, 
     return out
 
 
+def mul_mat_add(ctx: Context, wtype: int, w, x, addend, out=None):
+    """out = w x + addend through the fast GEMV kernels (b200_mul_mat_add; n <= 8; out may be the addend itself)"""
+    import torch
+    if out is None:
+        out = torch.empty(tuple(x.shape[:-1]) + (w.shape[-2],), dtype=torch.float32, device=x.device)
+    a, b, c, d = _desc(w, wtype, k_elems=x.shape[-1]), _desc(x, F32), _desc(addend, F32), _desc(out, F32)
+    check(lib().b200_mul_mat_add(ctx.handle, C.byref(a), C.byref(b), C.byref(c), C.byref(d)), "b200_mul_mat_add")
+    return out
+
+
 _TORCH_TYPES = {"torch.float32": 0, "torch.float16": 1, "torch.bfloat16": 30, "torch.int32": 26, "torch.int64": 27}
 
 

@@ -151,3 +151,27 @@ def test_fused_gate_up_glu_equals_separate_calls(pkg, gpu_ctx, orc, name, glu):
     # bias only
     only = pkg.mul_mat_fused(gpu_ctx, t, Wud, Xd, bias_up=bud)
     assert torch.equal(only, up_b)
+
+
+@pytest.mark.parametrize("n", [1, 3, 8])
+@pytest.mark.parametrize("name,m,k", [("q4_K", 4096, 14336), ("q4_K", 1000, 4096), ("q8_0", 4096, 4096), ("q6_K", 2048, 4096), ("q4_0", 4096, 4096), ("q5_K", 512, 2048)])
+def test_mul_mat_add_equals_mul_mat_then_add(pkg, gpu_ctx, name, m, k, n):
+    """b200_mul_mat_add (the addend goes into the store of the fast GEMV kernels) == b200_mul_mat followed by the ADD, bit for bit, also
+    when the result overwrites the addend (the residual stream in place)"""
+    import torch
+    from tests.util import TYPES as T2
+    t = {**T2, "q5_K": 13}[name]
+    rng = np.random.default_rng(zlib.crc32(repr((name, m, k, n)).encode()))
+    if name == "q5_K":
+        W = torch.randint(0, 256, (m, k // 256 * 176), dtype=torch.uint8, device="cuda")
+        W.view(m, k // 256, 176)[:, :, 0:4] = torch.tensor([0x00, 0x1c, 0x00, 0x1c], dtype=torch.uint8, device="cuda")      # d = dmin = 2^-8
+    else:
+        W = dev(random_blocks(t, m, k, rng))
+    X = torch.randn((n, k), device="cuda")
+    R = torch.randn((n, m), device="cuda")
+    want = pkg.mul_mat(gpu_ctx, t, W, X) + R
+    got = pkg.mul_mat_add(gpu_ctx, t, W, X, R)
+    assert torch.equal(got, want)
+    R2 = R.clone()
+    pkg.mul_mat_add(gpu_ctx, t, W, X, R2, out=R2)
+    assert torch.equal(R2, want)
