@@ -354,6 +354,8 @@ B200_API int b200_op_unary(b200_ctx * ctx, int unary_op, const b200_tensor * src
 B200_API int b200_op_unary_supported(int unary_op);
 B200_API int b200_op_scale(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst, float scale, float bias);   /* dst = src0 * scale + bias */
 B200_API int b200_op_rms_norm(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * dst, float eps);
+/* RMS_NORM followed by MUL with a weight repeated into src0's shape, in one pass: dst = (src0 / rms) * weight (the shell fuses the two nodes) */
+B200_API int b200_op_rms_norm_mul(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * weight, const b200_tensor * dst, float eps);
 /* GGML_OP_ROPE, modes normal (0) and NeoX (2), F32 or F16 rows; op_params = the node's 15 int32 parameter words */
 B200_API int b200_op_rope(b200_ctx * ctx, const b200_tensor * src0, const b200_tensor * pos, const b200_tensor * freq_factors /* or NULL */,
                           const b200_tensor * dst, const int32_t * op_params);

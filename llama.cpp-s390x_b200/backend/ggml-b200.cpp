@@ -646,6 +646,28 @@ ggml_status graph_compute_eager(b200_backend_ctx * bctx, ggml_cgraph * cgraph) {
                 continue;
             }
         }
+        // RMS_NORM followed by MUL with the norm weight (every norm of a Llama graph): one pass (reference: ggml_cuda_can_fuse of
+        // {RMS_NORM, MUL}, ggml-cuda.cu)
+        static const bool no_fuse_norm = [] { const char * e = getenv("GGML_B200_NO_FUSE_NORM"); return e && *e == '1'; }();
+        if (bctx->fuse && !no_fuse_norm && node->op == GGML_OP_RMS_NORM && i + 1 < cgraph->n_nodes && extra_op_supported(node)) {
+            const ggml_tensor * mul = cgraph->nodes[i + 1];
+            if (mul->op == GGML_OP_MUL && ggml_node_has_n_uses(cgraph, i, 1) && (node->flags & GGML_TENSOR_FLAG_OUTPUT) == 0 && extra_op_supported(mul) &&
+                (mul->src[0] == node || mul->src[1] == node)) {
+                const ggml_tensor * wt = mul->src[0] == node ? mul->src[1] : mul->src[0];
+                const char * xl = (const char *) node->src[0]->data, * dl = (const char *) mul->data;
+                const bool clash = xl != dl && xl < dl + ggml_nbytes(mul) && dl < xl + ggml_nbytes(node->src[0]);     // (the same rows in place are fine)
+                if (wt != node && !clash && ggml_are_same_shape(mul, node) && ggml_can_repeat(wt, node) && mul->nb[0] == 4) {
+                    int rc = flush();
+                    if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
+                    const b200_tensor a = to_b200(node->src[0]), w = to_b200(wt), d = to_b200(mul);
+                    rc = b200_op_rms_norm_mul(bctx->ctx, &a, &w, &d, ((const float *) node->op_params)[0]);
+                    if (rc != B200_OK) return failed(rc, node);
+                    bctx->n_extra_ops++;
+                    ++i;
+                    continue;
+                }
+            }
+        }
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
                 if (!is_quant_weight(node->src[0]->type)) {          // attention products: float src0

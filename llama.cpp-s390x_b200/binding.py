@@ -24,7 +24,7 @@ EXPORTS = [
     "b200_rowsplit_rows", "b200_rowsplit_upload", "b200_rowsplit_weights_free", "b200_rowsplit_mul_mat", "b200_rowsplit_mul_mat_main",
     "b200_rowsplit_synchronize", "b200_rowsplit_ctx",
     "b200_comm_create", "b200_comm_destroy", "b200_comm_size", "b200_comm_allreduce", "b200_capture_begin", "b200_capture_end", "b200_graph_launch", "b200_graph_free", "b200_ctx_alloc_generation",
-    "b200_op_binary", "b200_op_repeat", "b200_op_add_id", "b200_op_glu", "b200_op_unary", "b200_op_unary_supported", "b200_op_scale", "b200_op_rms_norm", "b200_op_rope",
+    "b200_op_binary", "b200_op_repeat", "b200_op_add_id", "b200_op_glu", "b200_op_unary", "b200_op_unary_supported", "b200_op_scale", "b200_op_rms_norm", "b200_op_rms_norm_mul", "b200_op_rope",
     "b200_op_soft_max", "b200_op_cpy", "b200_op_get_rows", "b200_op_set_rows", "b200_mul_mat_f", "b200_mul_mat_f_supported", "b200_mul_mat_add", "b200_mul_mat_add_supported", "b200_mul_mat_fused",
     "b200_mul_mat_fused_supported",
 ]
@@ -87,7 +87,7 @@ def lib() -> C.CDLL:
     sig("b200_graph_free", None, [vp]); sig("b200_ctx_alloc_generation", C.c_uint64, [vp])
     sig("b200_op_binary", i32, [vp, i32, T, T, T]); sig("b200_op_repeat", i32, [vp, T, T]); sig("b200_op_add_id", i32, [vp, T, T, T, T])
     sig("b200_op_glu", i32, [vp, i32, T, T, T, i32, f32, f32]); sig("b200_op_unary", i32, [vp, i32, T, T]); sig("b200_op_unary_supported", i32, [i32])
-    sig("b200_op_scale", i32, [vp, T, T, f32, f32]); sig("b200_op_rms_norm", i32, [vp, T, T, f32])
+    sig("b200_op_scale", i32, [vp, T, T, f32, f32]); sig("b200_op_rms_norm", i32, [vp, T, T, f32]); sig("b200_op_rms_norm_mul", i32, [vp, T, T, T, f32])
     sig("b200_op_rope", i32, [vp, T, T, T, T, C.POINTER(i32)]); sig("b200_op_soft_max", i32, [vp, T, T, T, T, f32, f32])
     sig("b200_op_cpy", i32, [vp, T, T]); sig("b200_op_get_rows", i32, [vp, T, T, T]); sig("b200_op_set_rows", i32, [vp, T, T, T])
     sig("b200_mul_mat_f", i32, [vp, T, T, T]); sig("b200_mul_mat_f_supported", i32, [T, T, T])

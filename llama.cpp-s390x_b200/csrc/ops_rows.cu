@@ -30,7 +30,8 @@ __device__ __forceinline__ float block_max(float v, float * red) {
 }
 
 // ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row -------------------------------------------------------------
-__global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, const tview d, const float eps) {
+// (w.p != NULL: the product with a weight tensor repeated into x's shape — RMS_NORM followed by MUL, as every norm of a Llama graph is)
+__global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, const tview w, const tview d, const float eps) {
     __shared__ float red[OPS_THREADS / 32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
@@ -41,7 +42,56 @@ __global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, co
     for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) { const float v = x[i]; s += v * v; }
     s = block_sum(s, red);
     const float scale = 1.0f / sqrtf(s / (float) n + eps);
-    for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) y[i] = x[i] * scale;
+    if (w.p) {
+        const char * wr = w.p + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3];
+        if (w.ne[0] == n && w.nb[0] == 4) {           // the usual case: one weight per channel (no 64-bit modulo per element)
+            const float * wf = (const float *) wr;
+            for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) y[i] = (x[i] * scale) * wf[i];
+        } else {
+            for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) y[i] = (x[i] * scale) * *(const float *) (wr + (i % w.ne[0]) * w.nb[0]);
+        }
+    } else {
+        for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) y[i] = x[i] * scale;
+    }
+}
+
+// the same for rows of float4s (16-byte aligned rows, one weight per channel): 1024 threads, the first two float4 of every thread stay in
+// registers between the two passes — a 4096-value row is ONE load per thread, against a 16-deep serial load chain per thread in the kernel
+// above (a decode step normalises single rows: the latency of that chain is the kernel)
+constexpr int RMS_VEC_THREADS = 1024;
+__global__ void __launch_bounds__(RMS_VEC_THREADS) rms_norm_vec_kernel(const tview a, const tview w, const tview d, const float eps) {
+    __shared__ float red[RMS_VEC_THREADS / 32];
+    const int64_t r = blockIdx.x;
+    const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
+    const float4 * x = (const float4 *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    float4 *       y = (float4 *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const float4 * wf = w.p ? (const float4 *) (w.p + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]) : nullptr;
+    const int64_t n4 = a.ne[0] >> 2;
+    const int tid = threadIdx.x;
+    float4 keep[2];
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const int64_t i = tid + (int64_t) j * RMS_VEC_THREADS;
+        keep[j] = i < n4 ? x[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        s += keep[j].x * keep[j].x + keep[j].y * keep[j].y + keep[j].z * keep[j].z + keep[j].w * keep[j].w;
+    }
+    for (int64_t i = tid + 2 * RMS_VEC_THREADS; i < n4; i += RMS_VEC_THREADS) { const float4 v = x[i]; s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    s = warp_sum(s);
+    if ((tid & 31) == 0) red[tid >> 5] = s;
+    __syncthreads();
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < RMS_VEC_THREADS / 32; ++k) t += red[k];
+    const float scale = 1.0f / sqrtf(t / (float) a.ne[0] + eps);
+    auto emit = [&](const int64_t i, float4 v) {
+        v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+        if (wf) { const float4 g = wf[i]; v.x *= g.x; v.y *= g.y; v.z *= g.z; v.w *= g.w; }
+        y[i] = v;
+    };
+#pragma unroll
+    for (int j = 0; j < 2; ++j) { const int64_t i = tid + (int64_t) j * RMS_VEC_THREADS; if (i < n4) emit(i, keep[j]); }
+    for (int64_t i = tid + 2 * RMS_VEC_THREADS; i < n4; i += RMS_VEC_THREADS) emit(i, x[i]);
 }
 
 // ---- ROPE (normal and NeoX pair layouts, YaRN, frequency factors) ------------------------------------------------------------
@@ -139,8 +189,14 @@ __global__ void __launch_bounds__(OPS_THREADS) soft_max_kernel(const tview a, co
 
 extern "C" {
 
-int b200_op_rms_norm(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d, float eps) {
+int b200_op_rms_norm(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d, float eps) { return b200_op_rms_norm_mul(ctx, a, nullptr, d, eps); }
+
+int b200_op_rms_norm_mul(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * w, const b200_tensor * d, float eps) {
     if (!ctx || !a || !d) { b200_set_error("b200_op_rms_norm: null argument"); return B200_E_ARG; }
+    if (w) {
+        if (w->type != B200_TYPE_F32) { b200_set_error("b200_op_rms_norm_mul: f32 weight"); return B200_E_UNSUPPORTED; }
+        for (int i = 0; i < 4; ++i) if (w->ne[i] <= 0 || a->ne[i] % w->ne[i] != 0) { b200_set_error("b200_op_rms_norm_mul: the weight cannot be repeated into src0"); return B200_E_ARG; }
+    }
     if (a->type != B200_TYPE_F32 || d->type != B200_TYPE_F32 || a->nb[0] != 4 || d->nb[0] != 4 || !same_shape(a, d)) {
         b200_set_error("b200_op_rms_norm: f32 rows with nb[0] == 4"); return B200_E_UNSUPPORTED;
     }
@@ -148,7 +204,12 @@ int b200_op_rms_norm(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * 
     if (rows == 0 || a->ne[0] == 0) return B200_OK;
     if (rows >= ((int64_t) 1 << 31)) { b200_set_error("b200_op_rms_norm: too many rows"); return B200_E_UNSUPPORTED; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    rms_norm_kernel<<<(unsigned) rows, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), eps);
+    tview vw = {};
+    if (w) vw = view_of(w);
+    auto al16 = [](const b200_tensor * t) { return (((uintptr_t) t->data | (uintptr_t) t->nb[1] | (uintptr_t) t->nb[2] | (uintptr_t) t->nb[3]) & 15) == 0; };
+    const bool vec = a->ne[0] % 4 == 0 && a->ne[0] >= 1024 && al16(a) && al16(d) && (!w || (w->ne[0] == a->ne[0] && w->nb[0] == 4 && al16(w)));
+    if (vec) rms_norm_vec_kernel<<<(unsigned) rows, RMS_VEC_THREADS, 0, ctx->stream>>>(view_of(a), vw, view_of(d), eps);
+    else     rms_norm_kernel<<<(unsigned) rows, OPS_THREADS, 0, ctx->stream>>>(view_of(a), vw, view_of(d), eps);
     return finish(ctx);
 }
 
