@@ -55,6 +55,7 @@ struct b200_backend_ctx {
     long        n_graphs = 0, n_mul_mat = 0, n_mul_mat_id = 0, n_fused_groups = 0;      // GGML_B200_STATS=1 prints them on free
     long        n_extra_ops = 0, n_fused_mm = 0;
     int         fuse = 1;                  // GGML_B200_FUSE: 0 = MUL_MAT + bias / gate + GLU run as separate nodes, 1 = fused when it pays, 2 = always
+    bool        reorder = true;            // GGML_B200_REORDER=0: graph_optimize leaves the node order alone
     bool        use_graphs = true;         // GGML_B200_GRAPHS=0: every graph_compute launches its kernels one by one
     graph_cache_entry graphs[8];           // captured cgraphs, least recently used replaced
     uint64_t    graph_clock = 0;
@@ -660,7 +661,7 @@ ggml_status graph_compute_eager(b200_backend_ctx * bctx, ggml_cgraph * cgraph) {
                     int rc = flush();
                     if (rc != B200_OK) return failed(rc, last_mm ? last_mm : node);
                     const b200_tensor a = to_b200(node->src[0]), w = to_b200(wt), d = to_b200(mul);
-                    rc = b200_op_rms_norm_mul(bctx->ctx, &a, &w, &d, ((const float *) node->op_params)[0]);
+                    rc = b200_op_rms_norm_mul(bctx->ctx, &a, &w, &d, ggml_get_op_params_f32(node, 0));
                     if (rc != B200_OK) return failed(rc, node);
                     bctx->n_extra_ops++;
                     ++i;
@@ -825,6 +826,33 @@ bool backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend
     return true;
 }
 
+// graph_optimize (called by ggml_backend_sched on every split before allocation): quantized MUL_MATs that share their activations are moved
+// next to each other — llama.cpp emits wq, ROPE(q), wk, ROPE(k), wv …, and only adjacent MUL_MAT nodes reach the kernels as one list
+// (b200_mul_mat_batch: one quantization of the activations, one launch for q / k / v).  A moved node depends on nothing but its weight and
+// the shared activations, which are complete before the first MUL_MAT of the group, so the order stays a valid one.
+void backend_graph_optimize(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
+    if (!bctx->reorder || only_mul_mat()) return;
+    auto groupable = [](const ggml_tensor * t) {
+        return t->op == GGML_OP_MUL_MAT && t->src[0] && t->src[1] && is_quant_weight(t->src[0]->type) && !split_src0(t) && t->src[0]->op == GGML_OP_NONE;
+    };
+    for (int i = 0; i < cgraph->n_nodes; ++i) {
+        ggml_tensor * first = cgraph->nodes[i];
+        if (!groupable(first)) continue;
+        int ins = i + 1, members = 1;
+        for (int j = i + 1; j < cgraph->n_nodes && j <= i + 32 && members < 3; ++j) {
+            ggml_tensor * t = cgraph->nodes[j];
+            if (!groupable(t) || t->src[1] != first->src[1] || t->src[0]->type != first->src[0]->type) continue;
+            if (j != ins) {                      // rotate nodes[ins .. j] right by one
+                for (int k = j; k > ins; --k) cgraph->nodes[k] = cgraph->nodes[k - 1];
+                cgraph->nodes[ins] = t;
+            }
+            ++ins; ++members;
+        }
+        i = ins - 1;
+    }
+}
+
 const ggml_backend_i k_backend_iface = {
     /* .get_name            = */ backend_get_name,
     /* .free                = */ backend_free,
@@ -841,7 +869,7 @@ const ggml_backend_i k_backend_iface = {
     /* .graph_compute       = */ backend_graph_compute,
     /* .event_record        = */ backend_event_record,
     /* .event_wait          = */ backend_event_wait,
-    /* .graph_optimize      = */ nullptr,
+    /* .graph_optimize      = */ backend_graph_optimize,
 };
 
 bool backend_is_b200(ggml_backend_t backend) { return backend && backend->iface.get_name == backend_get_name; }
@@ -887,6 +915,7 @@ ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char * /*params
     b200_backend_ctx * bctx = new b200_backend_ctx{dctx->device, dctx->name, ctx};
     if (const char * e = getenv("GGML_B200_FUSE")) bctx->fuse = atoi(e);
     if (const char * e = getenv("GGML_B200_GRAPHS"); e && *e == '0') bctx->use_graphs = false;
+    if (const char * e = getenv("GGML_B200_REORDER"); e && *e == '0') bctx->reorder = false;
     return new ggml_backend{
         /* .guid    = */ backend_guid(),
         /* .iface   = */ k_backend_iface,
