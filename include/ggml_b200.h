@@ -59,17 +59,23 @@ enum {
     B200_TYPE_F32  = 0,
     B200_TYPE_F16  = 1,      /* graph ops only (KV cache, masks); MUL_MAT weights of this type go to b200_mul_mat_f */
     B200_TYPE_Q4_0 = 2,
-    B200_TYPE_Q4_1 = 3,      /* Q4_1 / Q5_0 / Q5_1 / Q5_K: the generic GEMV family, GET_ROWS; no tensor-core path yet */
+    B200_TYPE_Q4_1 = 3,      /* Q4_1 / Q5_0 / Q5_1: the generic GEMV family, GET_ROWS; no tensor-core path (Q5_K has one) */
     B200_TYPE_Q5_0 = 6,
     B200_TYPE_Q5_1 = 7,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q2_K = 10,     /* Q2_K / Q3_K / IQ4_NL / IQ4_XS / MXFP4 / NVFP4 (N4): the generic GEMV family and GET_ROWS */
+    B200_TYPE_Q3_K = 11,
     B200_TYPE_Q4_K = 12,
     B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,
+    B200_TYPE_IQ4_NL = 20,
+    B200_TYPE_IQ4_XS = 23,
     B200_TYPE_I32  = 26,
     B200_TYPE_I64  = 27,     /* SET_ROWS indices */
     B200_TYPE_BF16 = 30,     /* graph ops only */
+    B200_TYPE_MXFP4 = 39,    /* 17-byte blocks: rows are only byte-aligned */
+    B200_TYPE_NVFP4 = 40,    /* 64 values: four UE4M3 scales + 32 bytes of e2m1 nibbles */
 };
 
 /* A ggml tensor as the kernels see it: ne[] in elements, nb[] in bytes, ne[0] contiguous

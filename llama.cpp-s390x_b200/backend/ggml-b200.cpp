@@ -435,7 +435,8 @@ bool is_f32(const ggml_tensor * t) { return t && t->type == GGML_TYPE_F32; }
 bool is_float_type(ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16 || t == GGML_TYPE_BF16; }
 bool is_quant_weight(ggml_type t) {
     return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K ||
-           t == GGML_TYPE_Q4_1 || t == GGML_TYPE_Q5_0 || t == GGML_TYPE_Q5_1 || t == GGML_TYPE_Q5_K;           // (N4: generic GEMV family)
+           t == GGML_TYPE_Q4_1 || t == GGML_TYPE_Q5_0 || t == GGML_TYPE_Q5_1 || t == GGML_TYPE_Q5_K ||           // (N4: generic GEMV family; Q5_K also tcgen05)
+           t == GGML_TYPE_Q2_K || t == GGML_TYPE_Q3_K || t == GGML_TYPE_IQ4_NL || t == GGML_TYPE_IQ4_XS || t == GGML_TYPE_MXFP4 || t == GGML_TYPE_NVFP4;
 }
 
 // GGML_B200_OPS=mul_mat: answer supports_op() for MUL_MAT / MUL_MAT_ID only (the round-1 behaviour: every other node of a graph runs

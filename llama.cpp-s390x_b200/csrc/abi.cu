@@ -234,8 +234,11 @@ int b200_ctx_reserve(b200_ctx * ctx, size_t nbytes) {
 // ---- validation -----------------------------------------------------------------------------------------------------
 static bool is_weight_type(int t) {
     return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q6_K ||
-           t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q5_K;       // (these four: generic GEMV family only)
+           t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q5_K ||       // (Q5_K: generic GEMV + tcgen05 GEMM)
+           t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K || t == B200_TYPE_IQ4_NL || t == B200_TYPE_IQ4_XS || t == B200_TYPE_MXFP4 ||
+           t == B200_TYPE_NVFP4;                                                                                                       // (generic GEMV family only)
 }
+static int64_t weight_align(int t) { return t == B200_TYPE_MXFP4 ? 1 : 2; }        // 17-byte MXFP4 blocks: rows are only byte-aligned
 
 static bool f32_contiguous(const b200_tensor * t) {
     return t->nb[0] == 4 && t->nb[1] == t->ne[0] * 4 && t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
@@ -243,7 +246,7 @@ static bool f32_contiguous(const b200_tensor * t) {
 
 static const char * check_mul_mat(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
     if (!a || !b || !d) return "NULL tensor";
-    if (!is_weight_type(a->type)) return "src0 type is not one of Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q8_0 / Q4_K / Q5_K / Q6_K";
+    if (!is_weight_type(a->type)) return "src0 type is not one of Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q8_0 / Q2_K / Q3_K / Q4_K / Q5_K / Q6_K / IQ4_NL / IQ4_XS / MXFP4 / NVFP4";
     if (b->type != B200_TYPE_F32 || d->type != B200_TYPE_F32) return "src1/dst must be F32";
     const int64_t k = a->ne[0];
     if (k <= 0 || k % b200_blck(a->type) != 0) return "ne00 is not a whole number of blocks";
@@ -251,7 +254,7 @@ static const char * check_mul_mat(const b200_tensor * a, const b200_tensor * b, 
     if (d->ne[0] != a->ne[1] || d->ne[1] != b->ne[1] || d->ne[2] != b->ne[2] || d->ne[3] != b->ne[3]) return "dst shape mismatch";
     if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] != 0 || b->ne[3] % a->ne[3] != 0) return "batch dims do not broadcast";
     if (a->nb[0] != (int64_t) b200_tsize(a->type)) return "src0 is transposed/permuted in dim 0";
-    if (a->nb[1] % 2 != 0 || a->nb[2] % 2 != 0 || a->nb[3] % 2 != 0) return "src0 strides not 2-byte aligned";
+    if (a->nb[1] % weight_align(a->type) != 0 || a->nb[2] % weight_align(a->type) != 0 || a->nb[3] % weight_align(a->type) != 0) return "src0 strides not 2-byte aligned";
     if (b->nb[0] != 4) return "src1 is not contiguous in dim 0";
     if (b->nb[1] % 4 != 0 || b->nb[2] % 4 != 0 || b->nb[3] % 4 != 0) return "src1 strides not 4-byte aligned";
     if (!f32_contiguous(d)) return "dst is not contiguous";
@@ -261,7 +264,7 @@ static const char * check_mul_mat(const b200_tensor * a, const b200_tensor * b, 
 
 static const char * check_mul_mat_id(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * c) {
     if (!as || !b || !ids || !c) return "NULL tensor";
-    if (!is_weight_type(as->type)) return "as type is not Q4_0/Q8_0/Q4_K/Q6_K";
+    if (!is_weight_type(as->type)) return "as type is not a supported weight type";
     if (b->type != B200_TYPE_F32 || c->type != B200_TYPE_F32 || ids->type != B200_TYPE_I32) return "b/c must be F32 and ids I32";
     const int64_t k = as->ne[0];
     if (k <= 0 || k % b200_blck(as->type) != 0) return "ne00 is not a whole number of blocks";
@@ -271,7 +274,7 @@ static const char * check_mul_mat_id(const b200_tensor * as, const b200_tensor *
     if (b->ne[2] != n_tokens) return "b->ne[2] != n_tokens";
     if (b->ne[1] <= 0 || n_used % b->ne[1] != 0) return "n_used is not a multiple of b->ne[1]";   // ggml.c:3305
     if (c->ne[0] != as->ne[1] || c->ne[1] != n_used || c->ne[2] != n_tokens) return "c shape mismatch";
-    if (as->nb[0] != (int64_t) b200_tsize(as->type) || as->nb[1] % 2 != 0 || as->nb[2] % 2 != 0) return "as strides";
+    if (as->nb[0] != (int64_t) b200_tsize(as->type) || as->nb[1] % weight_align(as->type) != 0 || as->nb[2] % weight_align(as->type) != 0) return "as strides";
     if (b->nb[0] != 4 || b->nb[1] % 4 != 0 || b->nb[2] % 4 != 0) return "b strides";
     if (ids->nb[0] != 4 || ids->nb[1] % 4 != 0) return "ids strides";
     if (!f32_contiguous(c)) return "c is not contiguous";

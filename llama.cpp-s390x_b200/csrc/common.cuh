@@ -31,16 +31,25 @@
 #define SZ_Q5_0  22
 #define SZ_Q5_1  24
 #define SZ_Q5_K  176
+#define SZ_Q2_K  84
+#define SZ_Q3_K  110
+#define SZ_IQ4_NL 18
+#define SZ_IQ4_XS 136
+#define SZ_MXFP4 17
+#define SZ_NVFP4 36
 
 __host__ __device__ constexpr int b200_blck(int type) {
-    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K) ? QK_K
-         : (type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q8_1 || type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1) ? QK_SMALL
+    return (type == B200_TYPE_Q4_K || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K || type == B200_TYPE_IQ4_XS) ? QK_K
+         : (type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q8_1 || type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 ||
+            type == B200_TYPE_IQ4_NL || type == B200_TYPE_MXFP4) ? QK_SMALL
+         : type == B200_TYPE_NVFP4 ? 64
          : (type == B200_TYPE_F32 || type == B200_TYPE_I32 || type == B200_TYPE_F16 || type == B200_TYPE_BF16 || type == B200_TYPE_I64) ? 1 : 0;
 }
 __host__ __device__ constexpr int b200_tsize(int type) {
     return type == B200_TYPE_Q4_0 ? SZ_Q4_0 : type == B200_TYPE_Q8_0 ? SZ_Q8_0 : type == B200_TYPE_Q8_1 ? SZ_Q8_1
          : type == B200_TYPE_Q4_K ? SZ_Q4_K : type == B200_TYPE_Q6_K ? SZ_Q6_K
          : type == B200_TYPE_Q4_1 ? SZ_Q4_1 : type == B200_TYPE_Q5_0 ? SZ_Q5_0 : type == B200_TYPE_Q5_1 ? SZ_Q5_1 : type == B200_TYPE_Q5_K ? SZ_Q5_K
+         : type == B200_TYPE_Q2_K ? SZ_Q2_K : type == B200_TYPE_Q3_K ? SZ_Q3_K : type == B200_TYPE_IQ4_NL ? SZ_IQ4_NL : type == B200_TYPE_IQ4_XS ? SZ_IQ4_XS : type == B200_TYPE_MXFP4 ? SZ_MXFP4 : type == B200_TYPE_NVFP4 ? SZ_NVFP4
          : (type == B200_TYPE_F32 || type == B200_TYPE_I32) ? 4 : (type == B200_TYPE_F16 || type == B200_TYPE_BF16) ? 2 : type == B200_TYPE_I64 ? 8 : 0;
 }
 

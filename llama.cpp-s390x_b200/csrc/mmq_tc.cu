@@ -74,6 +74,8 @@ template <int TYPE> __device__ __forceinline__ uint32_t raw_skew(const int i) {
 }
 template <int TYPE> struct raw_row        { static constexpr int value = TC_RAW_ROW; };
 template <> struct raw_row<B200_TYPE_Q6_K> { static constexpr int value = 224; };
+template <> struct raw_row<B200_TYPE_Q5_K> { static constexpr int value = SZ_Q5_K; };       // 176: a whole number of 16-byte units, no skew
+constexpr int raw_row_of(const int type) { return type == B200_TYPE_Q6_K ? 224 : (type == B200_TYPE_Q5_K ? SZ_Q5_K : TC_RAW_ROW); }
 
 struct tc_args {
     const uint8_t * W;
@@ -251,6 +253,50 @@ template <> struct w_frag<B200_TYPE_Q4_K> {
             hi[2 * j + 1] = h2_bits(__hfma2(__hfma2(d, sixteenth, m64), s_hi, nb_hi));
         }
         // half 0 stores slots (0,1,4,5), half 1 stores (6,7,2,3): every 8-lane STS phase hits 8 distinct bank groups
+        const uint4 l0 = make_uint4(lo[0], lo[1], lo[2], lo[3]), l1 = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        const uint4 h0 = make_uint4(hi[0], hi[1], hi[2], hi[3]), h1 = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        out[0] = h ? h0 : l0; slot[0] = h ? 6 : 0;
+        out[1] = h ? h1 : l1; slot[1] = h ? 7 : 1;
+        out[2] = h ? l0 : h0; slot[2] = h ? 2 : 4;
+        out[3] = h ? l1 : h1; slot[3] = h ? 3 : 5;
+    }
+};
+
+// Q5_K (ggml-common.h:330-346, dequantize_row_q5_K ggml-quants.c:1669-1697): Q4_K's layout with 32 bytes qh between the scales and the
+// nibbles — bit j of qh[l] is the fifth bit of element l of sub-block j.  Same stage / half / slot assignment as Q4_K.
+template <> struct w_frag<B200_TYPE_Q5_K> {
+    uint4 hdr, q, qh;
+    __device__ __forceinline__ void load(const uint32_t row, const int sub, const int h) {
+        hdr = lds_u4(row);
+        qh  = lds_u4(row + 16 + 16 * h);
+        q   = lds_u4(row + 48 + 32 * sub + 16 * h);
+    }
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) {
+        f0.hdr = lds_u4(row); f1.hdr = f0.hdr;
+        f0.qh = lds_u4(row + 16); f1.qh = lds_u4(row + 32);
+        f0.q = lds_u4(row + 48 + 32 * sub); f1.q = lds_u4(row + 48 + 32 * sub + 16);
+    }
+    __device__ __forceinline__ void convert(const int sub, const int h, const uint32_t k6400, uint4 (&out)[4], int (&slot)[4]) const {
+        (void) k6400;
+        const int g = sub;
+        int sc0, mn0, sc1, mn1;
+        q4k_scale_min(2 * g,     hdr.y, hdr.z, hdr.w, sc0, mn0);
+        q4k_scale_min(2 * g + 1, hdr.y, hdr.z, hdr.w, sc1, mn1);
+        const float2 dm = __half22float2(bits_h2(hdr.x));
+        const __half2 s_lo = h2_const(dm.x * (float) sc0), nb_lo = h2_const(-dm.y * (float) mn0);
+        const __half2 s_hi = h2_const(dm.x * (float) sc1), nb_hi = h2_const(-dm.y * (float) mn1);
+        const __half2 k1024 = h2_const(1024.0f);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w}, hw[4] = {qh.x, qh.y, qh.z, qh.w};
+        uint32_t lo[8], hi[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t ql = (w[j] & 0x0F0F0F0Fu)        | (((hw[j] >> (2 * g)) & 0x01010101u) << 4);          // 4 x (0..31)
+            const uint32_t qu = ((w[j] >> 4) & 0x0F0F0F0Fu) | (((hw[j] >> (2 * g + 1)) & 0x01010101u) << 4);
+            lo[2 * j]     = h2_bits(__hfma2(__hsub2(bits_h2(__byte_perm(ql, 0x64646464u, 0x4240)), k1024), s_lo, nb_lo));
+            lo[2 * j + 1] = h2_bits(__hfma2(__hsub2(bits_h2(__byte_perm(ql, 0x64646464u, 0x4341)), k1024), s_lo, nb_lo));
+            hi[2 * j]     = h2_bits(__hfma2(__hsub2(bits_h2(__byte_perm(qu, 0x64646464u, 0x4240)), k1024), s_hi, nb_hi));
+            hi[2 * j + 1] = h2_bits(__hfma2(__hsub2(bits_h2(__byte_perm(qu, 0x64646464u, 0x4341)), k1024), s_hi, nb_hi));
+        }
         const uint4 l0 = make_uint4(lo[0], lo[1], lo[2], lo[3]), l1 = make_uint4(lo[4], lo[5], lo[6], lo[7]);
         const uint4 h0 = make_uint4(hi[0], hi[1], hi[2], hi[3]), h1 = make_uint4(hi[4], hi[5], hi[6], hi[7]);
         out[0] = h ? h0 : l0; slot[0] = h ? 6 : 0;
@@ -835,7 +881,7 @@ encode_tiled_fn get_encode() {
     return fn;
 }
 
-bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K; }
+bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K; }
 
 template <int TYPE, bool PAIR>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
@@ -877,6 +923,7 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtenso
         case B200_TYPE_Q4_0: return launch_one<B200_TYPE_Q4_0, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_Q5_K: return launch_one<B200_TYPE_Q5_K, PAIR>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -957,7 +1004,7 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
         for (int j = 0; j < M->n_mats; ++j) rt += (M->m[j] + tm - 1) / tm;
         return rt;
     };
-    const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : 36));
+    const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : (type == B200_TYPE_Q5_K ? 44 : 36)));
     const int forced = ctx->tc_nt >= 192 ? 192 : (ctx->tc_nt >= 128 ? 128 : (ctx->tc_nt > 0 ? 64 : 0));
     p.split_k = 1;
     p.pair = false;
@@ -1063,7 +1110,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
         const int64_t rows = M ? M->m[jj] : P.m;
         const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) rows, (cuuint64_t) (M ? 1 : nmat)};
         const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (!M && nmat > 1 ? P.nb02 : P.nb01 * rows)};
-        const cuuint32_t wbox[3]    = {(cuuint32_t) (type == B200_TYPE_Q6_K ? raw_row<B200_TYPE_Q6_K>::value : TC_RAW_ROW) / 2, (cuuint32_t) TC_M, 1};
+        const cuuint32_t wbox[3]    = {(cuuint32_t) raw_row_of(type) / 2, (cuuint32_t) TC_M, 1};
         const cuuint32_t westr[3]   = {1, 1, 1};
         const CUresult wr = get_encode()(&tmw[j], CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void *) base, wdim, wstride, wbox, westr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1072,7 +1119,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
 
     tc_args a = {};
     a.ne02 = (int) ne02;
-    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : TC_RAW_ROW)) / 2;
+    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : (type == B200_TYPE_Q5_K ? SZ_Q5_K : TC_RAW_ROW))) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
     a.nt = pl.nt; a.col_tiles = (int) pl.col_tiles; a.k6400 = 0x64006400u;

@@ -229,6 +229,178 @@ template <> struct w_unit<B200_TYPE_Q5_K> {
     }
 };
 
+// N4 — Q2_K / Q3_K / IQ4_NL / IQ4_XS / MXFP4 (ggml-common.h:204-209, 288-311, 437-450; dequantize_row_* ggml-quants.c:507-525, 899-930, 1243-1290,
+// 2649-2688).  Unit ib of a K-quant row = elements [32 j, 32 j + 32) of super-block ib / 8 with j = ib % 8: 128-half n = j / 4, two-bit field
+// r = j % 4 of the 32 bytes qs[32 n ..], and two 16-element scales (2 j, 2 j + 1).
+template <> struct w_unit<B200_TYPE_Q2_K> {
+    int v[8]; float d0, d1, m0, m1;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7), n = j >> 2, r = j & 3;
+        const uint32_t * bp = reinterpret_cast<const uint32_t *>(row + sb * SZ_Q2_K);     // 84-byte blocks: 4-byte aligned
+        const uint32_t sc = (__ldg(bp + 2 * n + (r >> 1)) >> (16 * (r & 1))) & 0xFFFFu;    // scales[8 n + 2 r], [.. + 1]: low nibble scale, high nibble minimum
+        const float2 dm = __half22float2(*reinterpret_cast<const half2 *>(bp + 20));
+        d0 = dm.x * (float) (sc & 0xF);        m0 = dm.y * (float) ((sc >> 4) & 0xF);
+        d1 = dm.x * (float) ((sc >> 8) & 0xF); m1 = dm.y * (float) (sc >> 12);
+        const uint32_t * q = bp + 4 + 8 * n;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = (int) ((__ldg(q + i) >> (2 * r)) & 0x03030303u);
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int s0 = 0, s1 = 0, a0 = 0, a1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            s0 = __dp4a(v[i], u.a[i], s0);         a0 = __dp4a(0x01010101, u.a[i], a0);
+            s1 = __dp4a(v[i + 4], u.a[i + 4], s1); a1 = __dp4a(0x01010101, u.a[i + 4], a1);
+        }
+        return u.d * (d0 * (float) s0 + d1 * (float) s1 - m0 * (float) a0 - m1 * (float) a1);
+    }
+};
+
+template <> struct w_unit<B200_TYPE_Q3_K> {
+    int v[8]; float d0, d1;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7), n = j >> 2, r = j & 3;
+        const uint8_t * bp = row + sb * SZ_Q3_K;                                          // 110-byte blocks: 2-byte aligned only
+        uint32_t hw[8], lw[8];
+        ldw_b2<8>(bp, hw);                       // hmask: bit j of byte l = third bit of element l of unit j (set: 0, clear: -4)
+        ldw_b2<8>(bp + 32 + 32 * n, lw);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = (int) __vsubss4(((lw[i] >> (2 * r)) & 0x03030303u) | (((hw[i] >> j) & 0x01010101u) << 2), 0x04040404u);
+        // sixteen 6-bit scales in 12 bytes: low nibbles of bytes 0..7 = scales 0..7, high nibbles = scales 8..15, bytes 8..11 hold the top two bits
+        const uint8_t * raw = bp + 96;
+        const int is = 2 * j, sh = 2 * (is >> 2);
+        const int b0 = __ldg(raw + (is & 7)), b1 = __ldg(raw + (is & 7) + 1);
+        const int l0 = j < 4 ? (b0 & 0xF) : (b0 >> 4), l1 = j < 4 ? (b1 & 0xF) : (b1 >> 4);
+        const int h0 = (__ldg(raw + 8 + (is & 3)) >> sh) & 3, h1 = (__ldg(raw + 9 + (is & 3)) >> sh) & 3;
+        const float d = ld_half(bp + 108);
+        d0 = d * (float) ((l0 | (h0 << 4)) - 32);
+        d1 = d * (float) ((l1 | (h1 << 4)) - 32);
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int s0 = 0, s1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { s0 = __dp4a(v[i], u.a[i], s0); s1 = __dp4a(v[i + 4], u.a[i + 4], s1); }
+        return u.d * (d0 * (float) s0 + d1 * (float) s1);
+    }
+};
+
+// sixteen int8 code-book values (t0..t3 = entries 0-3, 4-7, 8-11, 12-15) looked up for the four 4-bit indices in the bytes of x
+__host__ __device__ constexpr uint32_t pack_s8(int a, int b, int c, int d) {
+    return (uint32_t) (a & 0xFF) | ((uint32_t) (b & 0xFF) << 8) | ((uint32_t) (c & 0xFF) << 16) | ((uint32_t) (d & 0xFF) << 24);
+}
+__device__ __forceinline__ int tab16(const uint32_t x, const uint32_t t0, const uint32_t t1, const uint32_t t2, const uint32_t t3) {
+    const uint32_t y   = x & 0x07070707u;
+    const uint32_t sel = __byte_perm(y | (y >> 4), 0u, 0x4420);            // the four 3-bit indices as PRMT selector nibbles
+    const uint32_t lo  = __byte_perm(t0, t1, sel), hi = __byte_perm(t2, t3, sel);
+    const uint32_t top = ((x >> 3) & 0x01010101u) * 0xFFu;                  // 0xFF where the index is 8..15
+    return (int) ((hi & top) | (lo & ~top));
+}
+// kvalues_iq4nl / kvalues_mxfp4 (ggml-common.h:1110-1118)
+#define IQ4NL_TAB pack_s8(-127, -104, -83, -65), pack_s8(-49, -35, -22, -10), pack_s8(1, 13, 25, 38), pack_s8(53, 69, 89, 113)
+#define MXFP4_TAB pack_s8(0, 1, 2, 3), pack_s8(4, 6, 8, 12), pack_s8(0, -1, -2, -3), pack_s8(-4, -6, -8, -12)
+
+template <> struct w_unit<B200_TYPE_IQ4_NL> {
+    int lo[4], hi[4]; float d;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint8_t * bp = row + ib * SZ_IQ4_NL;
+        d = ld_half(bp);
+        uint32_t q[4];
+        ldw_b2<4>(bp + 2, q);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { lo[i] = tab16(q[i] & 0x0F0F0F0Fu, IQ4NL_TAB); hi[i] = tab16((q[i] >> 4) & 0x0F0F0F0Fu, IQ4NL_TAB); }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sumi = __dp4a(lo[i], u.a[i], sumi); sumi = __dp4a(hi[i], u.a[i + 4], sumi); }
+        return d * u.d * (float) sumi;
+    }
+};
+
+template <> struct w_unit<B200_TYPE_IQ4_XS> {
+    int lo[4], hi[4]; float d;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const int64_t sb = ib >> 3;
+        const int     j  = (int) (ib & 7);
+        const uint32_t * bp = reinterpret_cast<const uint32_t *>(row + sb * SZ_IQ4_XS);   // 136-byte blocks: 8-byte aligned
+        const uint32_t w0 = __ldg(bp), sl = __ldg(bp + 1);                                // d | scales_h << 16, scales_l[4]
+        const int ls = (int) (((sl >> (4 * j)) & 0xFu) | ((((w0 >> 16) >> (2 * j)) & 3u) << 4));
+        d = __half2float(__ushort_as_half((unsigned short) (w0 & 0xFFFFu))) * (float) (ls - 32);
+        const uint32_t * q = bp + 2 + 4 * j;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t w = __ldg(q + i);
+            lo[i] = tab16(w & 0x0F0F0F0Fu, IQ4NL_TAB); hi[i] = tab16((w >> 4) & 0x0F0F0F0Fu, IQ4NL_TAB);
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sumi = __dp4a(lo[i], u.a[i], sumi); sumi = __dp4a(hi[i], u.a[i + 4], sumi); }
+        return d * u.d * (float) sumi;
+    }
+};
+
+// half of 2^(e - 127) (the code book holds the e2m1 values doubled; ggml-impl.h:477-495)
+__device__ __forceinline__ float e8m0_half(const uint32_t e) { return __uint_as_float(e < 2 ? 0x00200000u << e : (e - 1) << 23); }
+
+template <> struct w_unit<B200_TYPE_MXFP4> {
+    int lo[4], hi[4]; float d;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint8_t * bp = row + ib * SZ_MXFP4;                                         // 17-byte blocks: no alignment at all
+        const uint32_t * a = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(bp) & ~(uintptr_t) 3);
+        const uint32_t  sh = ((uint32_t) reinterpret_cast<uintptr_t>(bp) & 3u) * 8u;
+        uint32_t w[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) w[i] = __ldg(a + i);                                   // (up to 7 bytes past the block: rows are padded)
+        d = e8m0_half(__funnelshift_r(w[0], w[1], sh) & 0xFFu);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t q = __funnelshift_r(__funnelshift_r(w[i], w[i + 1], sh), __funnelshift_r(w[i + 1], w[i + 2], sh), 8);
+            lo[i] = tab16(q & 0x0F0F0F0Fu, MXFP4_TAB); hi[i] = tab16((q >> 4) & 0x0F0F0F0Fu, MXFP4_TAB);
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int sumi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { sumi = __dp4a(lo[i], u.a[i], sumi); sumi = __dp4a(hi[i], u.a[i + 4], sumi); }
+        return d * u.d * (float) sumi;
+    }
+};
+
+// UE4M3 scale (unsigned, bias 7, 3 mantissa bits), halved like the code book is doubled (ggml-impl.h:500-516)
+__device__ __forceinline__ float ue4m3_half(const uint32_t x) {
+    if (x == 0 || x == 0x7F) return 0.0f;
+    const uint32_t e = (x >> 3) & 0xFu, man = x & 7u;
+    return e == 0 ? (float) man * 0.0009765625f /* 2^-10 */ : __uint_as_float(((e + 119u) << 23) | (man << 20));
+}
+
+// NVFP4 (ggml-common.h:211-217, dequantize_row_nvfp4 ggml-quants.c:527-550): unit ib = sub-blocks 2 h, 2 h + 1 of block ib / 2 (h = ib % 2); a
+// sub-block's 8 bytes hold elements 0..7 in their low nibbles and 8..15 in their high nibbles
+template <> struct w_unit<B200_TYPE_NVFP4> {
+    int v[8]; float d0, d1;
+    __device__ __forceinline__ void load(const uint8_t * row, int64_t ib) {
+        const uint32_t * bp = reinterpret_cast<const uint32_t *>(row + (ib >> 1) * SZ_NVFP4);   // 36-byte blocks: 4-byte aligned
+        const int h = (int) (ib & 1);
+        const uint32_t sc = __ldg(bp) >> (16 * h);
+        d0 = ue4m3_half(sc & 0xFFu); d1 = ue4m3_half((sc >> 8) & 0xFFu);
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t w0 = __ldg(bp + 1 + 4 * h + 2 * s), w1 = __ldg(bp + 2 + 4 * h + 2 * s);
+            v[4 * s]     = tab16(w0 & 0x0F0F0F0Fu, MXFP4_TAB);        v[4 * s + 1] = tab16(w1 & 0x0F0F0F0Fu, MXFP4_TAB);
+            v[4 * s + 2] = tab16((w0 >> 4) & 0x0F0F0F0Fu, MXFP4_TAB); v[4 * s + 3] = tab16((w1 >> 4) & 0x0F0F0F0Fu, MXFP4_TAB);
+        }
+    }
+    __device__ __forceinline__ float dot(const act_unit & u) const {
+        int s0 = 0, s1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { s0 = __dp4a(v[i], u.a[i], s0); s1 = __dp4a(v[i + 4], u.a[i + 4], s1); }
+        return u.d * (d0 * (float) s0 + d1 * (float) s1);
+    }
+};
+
 constexpr int GENERIC_WARPS = 4;
 
 template <int TYPE, int NC>
@@ -729,6 +901,12 @@ int b200_launch_gemv_fused(b200_ctx * ctx, int type, const mm_problem & P, const
         case B200_TYPE_Q5_0: gemv_fused<B200_TYPE_Q5_0><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         case B200_TYPE_Q5_1: gemv_fused<B200_TYPE_Q5_1><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         case B200_TYPE_Q5_K: gemv_fused<B200_TYPE_Q5_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q2_K: gemv_fused<B200_TYPE_Q2_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_Q3_K: gemv_fused<B200_TYPE_Q3_K><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_IQ4_NL: gemv_fused<B200_TYPE_IQ4_NL><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_IQ4_XS: gemv_fused<B200_TYPE_IQ4_XS><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_MXFP4: gemv_fused<B200_TYPE_MXFP4><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
+        case B200_TYPE_NVFP4: gemv_fused<B200_TYPE_NVFP4><<<grid, GENERIC_WARPS * 32, 0, ctx->stream>>>(P, F); break;
         default: b200_set_error("fused GEMV: unsupported weight type %d", type); return B200_E_UNSUPPORTED;
     }
     B200_CUDA_TRY(cudaGetLastError());
@@ -748,6 +926,12 @@ int b200_launch_gemv_generic(b200_ctx * ctx, int type, const mm_problem & P, int
         case B200_TYPE_Q5_0: return launch_generic_t<B200_TYPE_Q5_0>(ctx, P, nc, tiles);
         case B200_TYPE_Q5_1: return launch_generic_t<B200_TYPE_Q5_1>(ctx, P, nc, tiles);
         case B200_TYPE_Q5_K: return launch_generic_t<B200_TYPE_Q5_K>(ctx, P, nc, tiles);
+        case B200_TYPE_Q2_K: return launch_generic_t<B200_TYPE_Q2_K>(ctx, P, nc, tiles);
+        case B200_TYPE_Q3_K: return launch_generic_t<B200_TYPE_Q3_K>(ctx, P, nc, tiles);
+        case B200_TYPE_IQ4_NL: return launch_generic_t<B200_TYPE_IQ4_NL>(ctx, P, nc, tiles);
+        case B200_TYPE_IQ4_XS: return launch_generic_t<B200_TYPE_IQ4_XS>(ctx, P, nc, tiles);
+        case B200_TYPE_MXFP4: return launch_generic_t<B200_TYPE_MXFP4>(ctx, P, nc, tiles);
+        case B200_TYPE_NVFP4: return launch_generic_t<B200_TYPE_NVFP4>(ctx, P, nc, tiles);
     }
     b200_set_error("gemv: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;

@@ -81,6 +81,53 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
             const int q = ((j & 1) ? (qb >> 4) : (qb & 0xF)) + (((b[16 + l] >> j) & 1) ? 16 : 0);
             return __fsub_rn(__fmul_rn(__fmul_rn(d, (float) s), (float) q), __fmul_rn(dmin, (float) m));
         }
+        case B200_TYPE_Q2_K: {                                  // ggml-quants.c:899-930
+            const uint8_t * b = row + (i >> 8) * SZ_Q2_K;
+            const int e = (int) (i & 255), j = e >> 5, l = e & 31, n = j >> 2, r = j & 3;
+            const uint8_t sc = b[8 * n + 2 * r + (l >> 4)];
+            const int q = (b[16 + 32 * n + l] >> (2 * r)) & 3;
+            return __fsub_rn(__fmul_rn(__fmul_rn(ld_half(b + 80), (float) (sc & 0xF)), (float) q), __fmul_rn(ld_half(b + 82), (float) (sc >> 4)));
+        }
+        case B200_TYPE_Q3_K: {                                  // ggml-quants.c:1243-1290
+            const uint8_t * b = row + (i >> 8) * SZ_Q3_K;
+            const int e = (int) (i & 255), j = e >> 5, l = e & 31, n = j >> 2, r = j & 3, is = 2 * j + (l >> 4);
+            const uint8_t * raw = b + 96;
+            const int sc = (is < 8 ? (raw[is] & 0xF) : (raw[is - 8] >> 4)) | (((raw[8 + (is & 3)] >> (2 * (is >> 2))) & 3) << 4);
+            const int q = ((b[32 + 32 * n + l] >> (2 * r)) & 3) - (((b[l] >> j) & 1) ? 0 : 4);
+            return __fmul_rn(__fmul_rn(ld_half(b + 108), (float) (sc - 32)), (float) q);
+        }
+        case B200_TYPE_IQ4_NL: case B200_TYPE_IQ4_XS: case B200_TYPE_MXFP4: {   // ggml-quants.c:2649-2688, 507-525
+            const int tab_nl[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+            const int tab_mx[16] = {0, 1, 2, 3, 4, 6, 8, 12, 0, -1, -2, -3, -4, -6, -8, -12};
+            const int l = (int) (i & 31);
+            if (type == B200_TYPE_IQ4_XS) {
+                const uint8_t * b = row + (i >> 8) * SZ_IQ4_XS;
+                const int ib = (int) (i & 255) >> 5;
+                const int sh = b[2] | (b[3] << 8);
+                const int ls = ((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4);
+                const uint8_t qb = b[8 + 16 * ib + (l & 15)];
+                return __fmul_rn(__fmul_rn(ld_half(b), (float) (ls - 32)), (float) tab_nl[l < 16 ? (qb & 0xF) : (qb >> 4)]);
+            }
+            if (type == B200_TYPE_IQ4_NL) {
+                const uint8_t * b = row + (i >> 5) * SZ_IQ4_NL;
+                const uint8_t qb = b[2 + (l & 15)];
+                return __fmul_rn(ld_half(b), (float) tab_nl[l < 16 ? (qb & 0xF) : (qb >> 4)]);
+            }
+            const uint8_t * b = row + (i >> 5) * SZ_MXFP4;
+            const uint32_t e8 = b[0];
+            const uint8_t qb = b[1 + (l & 15)];
+            return __fmul_rn((float) tab_mx[l < 16 ? (qb & 0xF) : (qb >> 4)], __uint_as_float(e8 < 2 ? 0x00200000u << e8 : (e8 - 1) << 23));
+        }
+        case B200_TYPE_NVFP4: {                                 // ggml-quants.c:527-550
+            const int tab_mx[16] = {0, 1, 2, 3, 4, 6, 8, 12, 0, -1, -2, -3, -4, -6, -8, -12};
+            const uint8_t * b = row + (i >> 6) * SZ_NVFP4;
+            const int e = (int) (i & 63), s = e >> 4, j = e & 15;
+            const uint32_t x = b[s];
+            const uint32_t ex = (x >> 3) & 0xFu, man = x & 7u;
+            const float d = (x == 0 || x == 0x7F) ? 0.0f : (ex == 0 ? (float) man * 0.0009765625f : __uint_as_float(((ex + 119u) << 23) | (man << 20)));
+            const uint8_t qb = b[4 + 8 * s + (j & 7)];
+            return __fmul_rn((float) tab_mx[j < 8 ? (qb & 0xF) : (qb >> 4)], d);
+        }
         case B200_TYPE_Q4_K: {                                  // ggml-quants.c:1467-1489
             const uint8_t * b = row + (i >> 8) * SZ_Q4_K;
             const int e = (int) (i & 255), j = e >> 5, l = e & 31;       // sub-block j, element l
@@ -215,7 +262,9 @@ int b200_op_cpy(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d) {
 int b200_op_get_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * idx, const b200_tensor * d) {
     if (!ctx || !a || !idx || !d) { b200_set_error("b200_op_get_rows: null argument"); return B200_E_ARG; }
     const bool type_ok = cpy_type_ok(a->type) || a->type == B200_TYPE_Q4_0 || a->type == B200_TYPE_Q8_0 || a->type == B200_TYPE_Q4_K || a->type == B200_TYPE_Q6_K ||
-                         a->type == B200_TYPE_Q4_1 || a->type == B200_TYPE_Q5_0 || a->type == B200_TYPE_Q5_1 || a->type == B200_TYPE_Q5_K;
+                         a->type == B200_TYPE_Q4_1 || a->type == B200_TYPE_Q5_0 || a->type == B200_TYPE_Q5_1 || a->type == B200_TYPE_Q5_K ||
+                         a->type == B200_TYPE_Q2_K || a->type == B200_TYPE_Q3_K || a->type == B200_TYPE_IQ4_NL || a->type == B200_TYPE_IQ4_XS || a->type == B200_TYPE_MXFP4 ||
+                         a->type == B200_TYPE_NVFP4;
     if (!type_ok || idx->type != B200_TYPE_I32 || d->type != B200_TYPE_F32 || d->nb[0] != 4 || d->ne[0] != a->ne[0] ||
         d->ne[1] != idx->ne[0] || d->ne[2] != idx->ne[1] || d->ne[3] != idx->ne[2] || a->ne[0] % b200_blck_size(a->type) != 0) {
         b200_set_error("b200_op_get_rows: f32 / f16 / bf16 / q4_0 / q8_0 / q4_K / q6_K rows, i32 indices, f32 result"); return B200_E_UNSUPPORTED;

@@ -58,8 +58,10 @@ def test_supports_op_validation_needs_no_device(pkg):
     assert L.b200_mul_mat_supported(C.byref(a), C.byref(f16), C.byref(d)) == 0
     q5 = _t(pkg, 13, (k, m, 1, 1), (176, 176 * 16, 176 * 16 * m, 176 * 16 * m))        # Q5_K weights: the generic GEMV family (round 2, N4)
     assert L.b200_mul_mat_supported(C.byref(q5), C.byref(b), C.byref(d)) == 1
-    q2 = _t(pkg, 10, (k, m, 1, 1), (84, 84 * 16, 0, 0))                        # Q2_K weights are not on this path
-    assert L.b200_mul_mat_supported(C.byref(q2), C.byref(b), C.byref(d)) == 0
+    q2 = _t(pkg, 10, (k, m, 1, 1), (84, 84 * 16, 84 * 16 * m, 84 * 16 * m))    # Q2_K weights: generic GEMV family (N4)
+    assert L.b200_mul_mat_supported(C.byref(q2), C.byref(b), C.byref(d)) == 1
+    iq2 = _t(pkg, 16, (k, m, 1, 1), (66, 66 * 16, 66 * 16 * m, 66 * 16 * m))   # IQ2_XXS (grid code books) is not on this path
+    assert L.b200_mul_mat_supported(C.byref(iq2), C.byref(b), C.byref(d)) == 0
     perm = _t(pkg, pkg.F32, (m, n, 1, 1), (4 * n, 4, 4 * m * n, 4 * m * n))    # transposed dst
     assert L.b200_mul_mat_supported(C.byref(a), C.byref(b), C.byref(perm)) == 0
     ids = _t(pkg, pkg.I32, (2, 5, 1, 1), (4, 32, 160, 160))                    # strided view rows

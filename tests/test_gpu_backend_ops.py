@@ -42,11 +42,11 @@ def test_backend_ops(op):
 
 
 def test_backend_ops_more_weight_types():
-    """Q4_1 / Q5_0 / Q5_1 / Q5_K weights (generic GEMV family) through the unmodified harness — every MUL_MAT case of
+    """Q4_1 / Q5_0 / Q5_1 / Q5_K / Q2_K / Q3_K / IQ4_NL / IQ4_XS / MXFP4 / NVFP4 weights through the unmodified harness — every MUL_MAT case of
     those types with F32 activations must run and match the CPU backend"""
     rc, out = run_harness("test", "-b", "B2000", "-o", "MUL_MAT")
     assert rc == 0 and "Backend B2000: OK" in out, "\n".join(out.splitlines()[-25:])
-    for t, least in (("q4_1", 40), ("q5_0", 10), ("q5_1", 10), ("q5_K", 10)):
+    for t, least in (("q4_1", 40), ("q5_0", 10), ("q5_1", 10), ("q5_K", 10), ("q2_K", 10), ("q3_K", 10), ("iq4_nl", 10), ("iq4_xs", 10), ("mxfp4", 40), ("nvfp4", 40)):
         ran = [l for l in out.splitlines() if re.search(r"type_a=" + t + r",type_b=f32", l) and l.rstrip().endswith("OK")]
         assert len(ran) >= least, f"only {len(ran)} {t} cases ran"
 
