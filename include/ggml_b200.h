@@ -274,6 +274,8 @@ B200_API int  b200_host_free(void * ptr);
 /* Events on a context's stream (ggml_backend_cuda_event_record / _wait, ggml-cuda.cu:4498-4520; device event_new / _free /
  * _synchronize, :5430-5460).  An event is created for a device and may be waited for by any context of any device. */
 B200_API int  b200_event_create(int device, void ** event_out);
+B200_API int  b200_event_create_timed(int device, void ** event_out);                 /* keeps its time stamp (the plug-in times a graph run eagerly and replayed) */
+B200_API int  b200_event_elapsed_ms(void * start, void * stop, float * ms);           /* device time between two timed events; waits for `stop` */
 B200_API int  b200_event_destroy(int device, void * event);
 B200_API int  b200_event_record(b200_ctx * ctx, void * event);        /* after everything queued on ctx's stream so far      */
 B200_API int  b200_event_wait(b200_ctx * ctx, void * event);          /* ctx's stream waits (device side) for the event      */

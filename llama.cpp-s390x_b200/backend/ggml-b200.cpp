@@ -21,6 +21,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -46,7 +47,14 @@ struct b200_device_ctx {
     ggml_backend_buffer_type buft;
 };
 
-struct graph_cache_entry { uint64_t key = 0; void * graph = nullptr; uint64_t alloc_gen = 0; int seen = 0; int capture_attempts = 0; bool failed = false; uint64_t stamp = 0; };
+struct graph_cache_entry {
+    uint64_t key = 0; void * graph = nullptr; uint64_t alloc_gen = 0; int seen = 0; int capture_attempts = 0; bool failed = false; uint64_t stamp = 0;
+    // eager launches or replay, whichever is faster for THIS graph on THIS host (GGML_B200_GRAPHS=1): two timed runs of each, then decided
+    int   mode = 0;                         // 0 = still measuring, 1 = eager, 2 = replay
+    int   eager_runs = 0, replay_runs = 0;  // timed runs started
+    int   timing = 0;                       // a timed run is in flight: 1 = eager, 2 = replay
+    float t_eager = 1e30f, t_replay = 1e30f;
+};
 
 struct b200_backend_ctx {
     int         device;
@@ -56,7 +64,10 @@ struct b200_backend_ctx {
     long        n_extra_ops = 0, n_fused_mm = 0;
     int         fuse = 1;                  // GGML_B200_FUSE: 0 = MUL_MAT + bias / gate + GLU run as separate nodes, 1 = fused when it pays, 2 = always
     bool        reorder = true;            // GGML_B200_REORDER=0: graph_optimize leaves the node order alone
-    bool        use_graphs = true;         // GGML_B200_GRAPHS=0: every graph_compute launches its kernels one by one
+    int         use_graphs = 1;            // GGML_B200_GRAPHS: 0 = every graph_compute launches its kernels one by one, 2 = a graph seen twice is captured
+                                           // and replayed, 1 (default) = both are timed for every graph and the faster one is kept
+    void *      t0 = nullptr, * t1 = nullptr;          // timed events of the run being measured
+    long        n_graphs_eager_kept = 0, n_graphs_replay_kept = 0;
     graph_cache_entry graphs[8];           // captured cgraphs, least recently used replaced
     uint64_t    graph_clock = 0;
     long        n_graph_captures = 0, n_graph_replays = 0;
@@ -403,9 +414,13 @@ const char * backend_get_name(ggml_backend_t backend) { return ((b200_backend_ct
 void backend_free(ggml_backend_t backend) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     if (const char * e = getenv("GGML_B200_STATS"); e && *e == '1') {
-        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld other_ops=%ld fused_mul_mat=%ld graph_captures=%ld graph_replays=%ld\n", bctx->n_graphs,
-                bctx->n_mul_mat, bctx->n_mul_mat_id, bctx->n_fused_groups, bctx->n_extra_ops, bctx->n_fused_mm, bctx->n_graph_captures, bctx->n_graph_replays);
+        fprintf(stderr, "ggml-b200 stats: graphs=%ld mul_mat=%ld mul_mat_id=%ld fused_groups=%ld other_ops=%ld fused_mul_mat=%ld graph_captures=%ld graph_replays=%ld kept_eager=%ld kept_replay=%ld\n", bctx->n_graphs,
+                bctx->n_mul_mat, bctx->n_mul_mat_id, bctx->n_fused_groups, bctx->n_extra_ops, bctx->n_fused_mm, bctx->n_graph_captures, bctx->n_graph_replays,
+                bctx->n_graphs_eager_kept, bctx->n_graphs_replay_kept);
+        for (const auto & c : bctx->graphs) if (c.mode) fprintf(stderr, "ggml-b200 stats: graph %016llx: eager %.3f ms, replay %.3f ms -> %s\n", (unsigned long long) c.key, c.t_eager, c.t_replay, c.mode == 1 ? "eager" : "replay");
     }
+    if (bctx->t0) b200_event_destroy(bctx->device, bctx->t0);
+    if (bctx->t1) b200_event_destroy(bctx->device, bctx->t1);
     for (auto & c : bctx->graphs) if (c.graph) b200_graph_free(c.graph);
     if (bctx->copy_event) b200_event_destroy(bctx->device, bctx->copy_event);
     if (bctx->rs) b200_rowsplit_destroy(bctx->rs);
@@ -719,19 +734,26 @@ ggml_status graph_compute_eager(b200_backend_ctx * bctx, ggml_cgraph * cgraph) {
 // kernel launches.  First sight of a key: eager (this also grows the scratch buffers); second sight: capture + launch; later: launch.
 
 
+// (hashed 8 bytes at a time: a byte-wise FNV over the ~560 KB that describe a Llama-3-8B decode graph took 0.5 ms of every step — host time
+//  in front of the first launch)
 uint64_t graph_key(const ggml_cgraph * cgraph) {
     uint64_t h = 1469598103934665603ull;
-    auto mix = [&](const void * p, size_t n) { const uint8_t * b = (const uint8_t *) p; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } };
-    auto mix_tensor = [&](const ggml_tensor * t) {
-        mix(&t->type, sizeof(t->type)); mix(t->ne, sizeof(t->ne)); mix(t->nb, sizeof(t->nb)); mix(&t->data, sizeof(t->data));
+    auto mix64 = [&](uint64_t w) { h = (h ^ w) * 0x9E3779B97F4A7C15ull; h ^= h >> 29; };
+    auto mix_words = [&](const void * p, size_t n) {           // n is a multiple of 8 for every field hashed this way
+        const char * b = (const char *) p;
+        for (size_t i = 0; i < n; i += 8) { uint64_t w; memcpy(&w, b + i, 8); mix64(w); }
     };
-    mix(&cgraph->n_nodes, sizeof(cgraph->n_nodes));
+    auto mix_tensor = [&](const ggml_tensor * t) {
+        mix64((uint64_t) t->type); mix_words(t->ne, sizeof(t->ne)); mix_words(t->nb, sizeof(t->nb)); mix64((uint64_t) (uintptr_t) t->data);
+    };
+    static_assert(sizeof(((ggml_tensor *) nullptr)->op_params) % 8 == 0 && sizeof(((ggml_tensor *) nullptr)->ne) % 8 == 0, "hashed in 8-byte words");
+    mix64((uint64_t) cgraph->n_nodes);
     for (int i = 0; i < cgraph->n_nodes; ++i) {
         const ggml_tensor * n = cgraph->nodes[i];
-        mix(&n->op, sizeof(n->op)); mix(&n->flags, sizeof(n->flags)); mix(n->op_params, sizeof(n->op_params));
+        mix64(((uint64_t) n->op << 32) | (uint32_t) n->flags); mix_words(n->op_params, sizeof(n->op_params));
         mix_tensor(n);
         for (int j = 0; j < GGML_MAX_SRC; ++j) {
-            if (!n->src[j]) { const int z = -1; mix(&z, sizeof(z)); continue; }
+            if (!n->src[j]) { mix64(~0ull); continue; }
             mix_tensor(n->src[j]);
         }
     }
@@ -750,12 +772,31 @@ bool graph_capturable(const ggml_cgraph * cgraph) {
     return work >= 8;                                                        // short graphs gain nothing
 }
 
+// Eager launches or CUDA-graph replay?  Measured on B200 (Llama-3-8B decode graph, ~520 launches): replay 2.92 ms, eager 2.72 ms — with
+// programmatic dependent launch on every kernel the stream feeds the GPU faster than a graph's kernel-to-kernel dependencies resolve, as long
+// as the host keeps up (here ~5 us per launch are available); a single MUL_MAT (test-backend-ops perf) is the other way round.  So neither
+// is assumed: a graph is run eagerly twice and replayed twice under device timers, and the faster way is kept for that graph.
+static void graph_collect_timing(b200_backend_ctx * bctx, graph_cache_entry * e) {
+    if (!e->timing) return;
+    float ms = 0.0f;
+    if (b200_event_elapsed_ms(bctx->t0, bctx->t1, &ms) == B200_OK) {
+        if (e->timing == 1) e->t_eager = std::min(e->t_eager, ms); else e->t_replay = std::min(e->t_replay, ms);
+    }
+    e->timing = 0;
+}
+
+static bool graph_timer_start(b200_backend_ctx * bctx) {
+    if (!bctx->t0 && (b200_event_create_timed(bctx->device, &bctx->t0) != B200_OK || b200_event_create_timed(bctx->device, &bctx->t1) != B200_OK)) return false;
+    return b200_event_record(bctx->ctx, bctx->t0) == B200_OK;
+}
+
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     bctx->n_graphs++;
     if (!bctx->use_graphs || !graph_capturable(cgraph)) return graph_compute_eager(bctx, cgraph);
     const uint64_t key = graph_key(cgraph);
     graph_cache_entry * e = nullptr, * oldest = &bctx->graphs[0];
+    for (auto & c : bctx->graphs) if (c.timing) graph_collect_timing(bctx, &c);      // (one pair of timer events: a measurement is read before the next one starts)
     for (auto & c : bctx->graphs) {
         if (c.key == key && c.seen > 0) { e = &c; break; }
         if (c.stamp < oldest->stamp) oldest = &c;
@@ -768,15 +809,37 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
     }
     e->stamp = ++bctx->graph_clock;
     e->seen++;
+    const bool tune = bctx->use_graphs == 1;
+    if (tune && e->mode == 0 && e->eager_runs >= 2 && e->replay_runs >= 2) {
+        e->mode = e->t_replay <= e->t_eager ? 2 : 1;
+        if (e->mode == 1) { bctx->n_graphs_eager_kept++; if (e->graph) { b200_graph_free(e->graph); e->graph = nullptr; } }
+        else bctx->n_graphs_replay_kept++;
+    }
+    if (tune && (e->mode == 1 || e->failed)) return graph_compute_eager(bctx, cgraph);
+    if (tune && e->mode == 0 && e->seen >= 2 && e->eager_runs < 2) {            // second and third sight: eager, timed
+        const bool timed = graph_timer_start(bctx);
+        const ggml_status st = graph_compute_eager(bctx, cgraph);
+        if (timed && b200_event_record(bctx->ctx, bctx->t1) == B200_OK) e->timing = 1;
+        e->eager_runs++;
+        return st;
+    }
     const uint64_t gen = b200_ctx_alloc_generation(bctx->ctx);
     if (e->graph && e->alloc_gen != gen) { b200_graph_free(e->graph); e->graph = nullptr; }       // a scratch buffer moved since the capture
     if (e->graph) {
-        if (b200_graph_launch(bctx->ctx, e->graph) == B200_OK) { bctx->n_graph_replays++; return GGML_STATUS_SUCCESS; }
+        const bool timed = tune && e->mode == 0 && e->replay_runs < 2 && graph_timer_start(bctx);
+        if (b200_graph_launch(bctx->ctx, e->graph) == B200_OK) {
+            bctx->n_graph_replays++;
+            if (tune && e->mode == 0 && e->replay_runs < 2) {
+                if (timed && b200_event_record(bctx->ctx, bctx->t1) == B200_OK) e->timing = 2;
+                e->replay_runs++;
+            }
+            return GGML_STATUS_SUCCESS;
+        }
         GGML_LOG_ERROR("ggml-b200: graph launch failed (%s), running eagerly\n", b200_last_error());
         b200_graph_free(e->graph); e->graph = nullptr; e->failed = true;
     }
     if (e->seen < 2 || e->failed) return graph_compute_eager(bctx, cgraph);
-    // second sight of this graph: record it
+    // seen before (and, when tuning, timed eagerly): record it
     const long s_mm = bctx->n_mul_mat, s_id = bctx->n_mul_mat_id, s_fg = bctx->n_fused_groups, s_ops = bctx->n_extra_ops, s_fm = bctx->n_fused_mm;
     if (b200_capture_begin(bctx->ctx) != B200_OK) { e->failed = true; return graph_compute_eager(bctx, cgraph); }
     const ggml_status st = graph_compute_eager(bctx, cgraph);
@@ -787,7 +850,7 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) 
         if (g) b200_graph_free(g);
         bctx->n_mul_mat = s_mm; bctx->n_mul_mat_id = s_id; bctx->n_fused_groups = s_fg; bctx->n_extra_ops = s_ops; bctx->n_fused_mm = s_fm;
         if (++e->capture_attempts >= 3) e->failed = true;
-        e->seen = 1;
+        if (!tune) e->seen = 1;
         return graph_compute_eager(bctx, cgraph);
     }
     e->graph = g; e->alloc_gen = b200_ctx_alloc_generation(bctx->ctx);
@@ -915,7 +978,7 @@ ggml_backend_t device_init_backend(ggml_backend_dev_t dev, const char * /*params
     }
     b200_backend_ctx * bctx = new b200_backend_ctx{dctx->device, dctx->name, ctx};
     if (const char * e = getenv("GGML_B200_FUSE")) bctx->fuse = atoi(e);
-    if (const char * e = getenv("GGML_B200_GRAPHS"); e && *e == '0') bctx->use_graphs = false;
+    if (const char * e = getenv("GGML_B200_GRAPHS"); e && *e >= '0' && *e <= '2') bctx->use_graphs = *e - '0';
     if (const char * e = getenv("GGML_B200_REORDER"); e && *e == '0') bctx->reorder = false;
     return new ggml_backend{
         /* .guid    = */ backend_guid(),

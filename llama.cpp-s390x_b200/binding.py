@@ -19,7 +19,7 @@ EXPORTS = [
     "b200_mul_mat_noalloc",
     "b200_mul_mat_id", "b200_mul_mat_id_supported", "b200_mm_ids", "b200_weights_upload", "b200_weights_free",
     "b200_mul_mat_host", "b200_mul_mat_host_batch", "b200_mul_mat_gather", "b200_gather_sync_init", "b200_mul_mat_multi", "b200_mul_mat_batch", "b200_stream_comm_init", "b200_mul_mat_batch_gather", "b200_gather_ll_init", "b200_mul_mat_gather_ll", "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d",
-    "b200_memset", "b200_memcpy_async", "b200_host_malloc", "b200_host_free", "b200_event_create", "b200_event_destroy",
+    "b200_memset", "b200_memcpy_async", "b200_host_malloc", "b200_host_free", "b200_event_create", "b200_event_destroy", "b200_event_create_timed", "b200_event_elapsed_ms",
     "b200_event_record", "b200_event_wait", "b200_event_synchronize", "b200_rowsplit_create", "b200_rowsplit_destroy", "b200_rowsplit_n_dev",
     "b200_rowsplit_rows", "b200_rowsplit_upload", "b200_rowsplit_weights_free", "b200_rowsplit_mul_mat", "b200_rowsplit_mul_mat_main",
     "b200_rowsplit_synchronize", "b200_rowsplit_ctx",
@@ -111,6 +111,7 @@ def lib() -> C.CDLL:
     sig("b200_memset", i32, [vp, vp, i32, sz]); sig("b200_memcpy_async", i32, [vp, vp, vp, sz, i32])
     sig("b200_host_malloc", i32, [sz, C.POINTER(vp)]); sig("b200_host_free", i32, [vp])
     sig("b200_event_create", i32, [i32, C.POINTER(vp)]); sig("b200_event_destroy", i32, [i32, vp])
+    sig("b200_event_create_timed", i32, [i32, C.POINTER(vp)]); sig("b200_event_elapsed_ms", i32, [vp, vp, C.POINTER(C.c_float)])
     sig("b200_event_record", i32, [vp, vp]); sig("b200_event_wait", i32, [vp, vp]); sig("b200_event_synchronize", i32, [vp])
     sig("b200_rowsplit_create", i32, [C.POINTER(i32), i32, C.POINTER(C.c_float), C.POINTER(vp)])
     sig("b200_rowsplit_destroy", None, [vp]); sig("b200_rowsplit_n_dev", i32, [vp])

@@ -125,6 +125,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->gemv_rpw      = env_int("GGML_B200_GEMV_RPW", 1);
     ctx->gemv_rpw_max_m = env_int("GGML_B200_GEMV_RPW_MAX_M", 4096);
     ctx->tc_pdl        = env_int("GGML_B200_TC_PDL", 0);
+    ctx->ops_pdl       = env_int("GGML_B200_OPS_PDL", 1);
     ctx->use_mma       = env_int("GGML_B200_USE_MMA", 1);
     ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
     ctx->mma_ch        = env_int("GGML_B200_MMA_CH", 0);
@@ -189,6 +190,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "gemv_rpw"))      slot = &ctx->gemv_rpw;
     else if (!strcmp(name, "gemv_rpw_max_m")) slot = &ctx->gemv_rpw_max_m;
     else if (!strcmp(name, "tc_pdl"))        slot = &ctx->tc_pdl;
+    else if (!strcmp(name, "ops_pdl"))       slot = &ctx->ops_pdl;
     else if (!strcmp(name, "use_mma"))       slot = &ctx->use_mma;
     else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;
     else if (!strcmp(name, "mma_ch"))        slot = &ctx->mma_ch;
@@ -783,6 +785,24 @@ int b200_event_create(int device, void ** out) {
     cudaEvent_t ev;
     B200_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     *out = (void *) ev;
+    return B200_OK;
+}
+
+// an event that keeps its time stamp, and the device time between two of them (waits for `stop`)
+int b200_event_create_timed(int device, void ** out) {
+    if (!out) return B200_E_ARG;
+    *out = nullptr;
+    B200_CUDA_TRY(cudaSetDevice(device));
+    cudaEvent_t ev;
+    B200_CUDA_TRY(cudaEventCreate(&ev));
+    *out = (void *) ev;
+    return B200_OK;
+}
+
+int b200_event_elapsed_ms(void * start, void * stop, float * ms) {
+    if (!start || !stop || !ms) return B200_E_ARG;
+    B200_CUDA_TRY(cudaEventSynchronize((cudaEvent_t) stop));
+    B200_CUDA_TRY(cudaEventElapsedTime(ms, (cudaEvent_t) start, (cudaEvent_t) stop));
     return B200_OK;
 }
 

@@ -29,6 +29,7 @@ namespace {
 // ---- binary ops with broadcast ------------------------------------------------------------------------------------------
 template <int OP>
 __global__ void __launch_bounds__(OPS_THREADS) bin_kernel(const tview a, const tview b, const tview d, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t i0, i1, i2, i3;
         split4(i, d.ne, i0, i1, i2, i3);
@@ -42,6 +43,7 @@ __global__ void __launch_bounds__(OPS_THREADS) bin_kernel(const tview a, const t
 
 // ---- REPEAT: dst = src0 tiled -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(OPS_THREADS) repeat_kernel(const tview a, const tview d, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t i0, i1, i2, i3;
         split4(i, d.ne, i0, i1, i2, i3);
@@ -52,6 +54,7 @@ __global__ void __launch_bounds__(OPS_THREADS) repeat_kernel(const tview a, cons
 
 // ---- ADD_ID: dst[:, i1, i2] = a[:, i1, i2] + b[:, ids[i1, i2]] -----------------------------------------------------------
 __global__ void __launch_bounds__(OPS_THREADS) add_id_kernel(const tview a, const tview b, const tview ids, const tview d, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t i0, i1, i2, i3;
         split4(i, d.ne, i0, i1, i2, i3);
@@ -65,6 +68,7 @@ __global__ void __launch_bounds__(OPS_THREADS) add_id_kernel(const tview a, cons
 // rows: x row r at xp + r * xs, gate row at gp + r * gs, nc values per row
 __global__ void __launch_bounds__(OPS_THREADS) glu_kernel(const char * xp, const int64_t xs, const char * gp, const int64_t gs, char * dp, const int64_t ds,
                                                           const int64_t nc, const int64_t n, const int op, const float alpha, const float limit) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const int64_t r = i / nc, c = i - r * nc;
         const float x = ((const float *) (xp + r * xs))[c], g = ((const float *) (gp + r * gs))[c];
@@ -73,6 +77,7 @@ __global__ void __launch_bounds__(OPS_THREADS) glu_kernel(const char * xp, const
 }
 
 __global__ void __launch_bounds__(OPS_THREADS) unary_kernel(const float * __restrict__ x, float * __restrict__ y, const int64_t n, const int op) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const float v = x[i];
         float r;
@@ -95,6 +100,7 @@ __global__ void __launch_bounds__(OPS_THREADS) unary_kernel(const float * __rest
 }
 
 __global__ void __launch_bounds__(OPS_THREADS) scale_kernel(const float * __restrict__ x, float * __restrict__ y, const int64_t n, const float s, const float b) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) y[i] = x[i] * s + b;
 }
 
@@ -114,10 +120,10 @@ int b200_op_binary(b200_ctx * ctx, int op, const b200_tensor * a, const b200_ten
     const int g = grid_for(n, ctx->sm_count);
     const tview va = view_of(a), vb = view_of(b), vd = view_of(d);
     switch (op) {
-        case B200_OP_ADD: bin_kernel<B200_OP_ADD><<<g, OPS_THREADS, 0, ctx->stream>>>(va, vb, vd, n); break;
-        case B200_OP_SUB: bin_kernel<B200_OP_SUB><<<g, OPS_THREADS, 0, ctx->stream>>>(va, vb, vd, n); break;
-        case B200_OP_MUL: bin_kernel<B200_OP_MUL><<<g, OPS_THREADS, 0, ctx->stream>>>(va, vb, vd, n); break;
-        case B200_OP_DIV: bin_kernel<B200_OP_DIV><<<g, OPS_THREADS, 0, ctx->stream>>>(va, vb, vd, n); break;
+        case B200_OP_ADD: OPS_LAUNCH(ctx, bin_kernel<B200_OP_ADD>, g, OPS_THREADS, va, vb, vd, n); break;
+        case B200_OP_SUB: OPS_LAUNCH(ctx, bin_kernel<B200_OP_SUB>, g, OPS_THREADS, va, vb, vd, n); break;
+        case B200_OP_MUL: OPS_LAUNCH(ctx, bin_kernel<B200_OP_MUL>, g, OPS_THREADS, va, vb, vd, n); break;
+        case B200_OP_DIV: OPS_LAUNCH(ctx, bin_kernel<B200_OP_DIV>, g, OPS_THREADS, va, vb, vd, n); break;
         default: b200_set_error("b200_op_binary: unknown op %d", op); return B200_E_ARG;
     }
     return finish(ctx);
@@ -130,7 +136,7 @@ int b200_op_repeat(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d)
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    repeat_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), n);
+    OPS_LAUNCH(ctx, repeat_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, view_of(a), view_of(d), n);
     return finish(ctx);
 }
 
@@ -143,7 +149,7 @@ int b200_op_add_id(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    add_id_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(ids), view_of(d), n);
+    OPS_LAUNCH(ctx, add_id_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, view_of(a), view_of(b), view_of(ids), view_of(d), n);
     return finish(ctx);
 }
 
@@ -161,7 +167,7 @@ int b200_op_glu(b200_ctx * ctx, int glu_op, const b200_tensor * a, const b200_te
     const char * xp = (const char *) a->data, * gp = b ? (const char *) b->data : (const char *) a->data;
     if (!b) { xp += swapped ? nc * 4 : 0; gp += swapped ? 0 : nc * 4; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    glu_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(xp, a->nb[1], gp, b ? b->nb[1] : a->nb[1], (char *) d->data, d->nb[1], nc, n,
+    OPS_LAUNCH(ctx, glu_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, xp, a->nb[1], gp, b ? b->nb[1] : a->nb[1], (char *) d->data, d->nb[1], nc, n,
                                                                              glu_op, alpha, limit);
     return finish(ctx);
 }
@@ -175,7 +181,7 @@ int b200_op_unary(b200_ctx * ctx, int unary_op, const b200_tensor * a, const b20
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    unary_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>((const float *) a->data, (float *) d->data, n, unary_op);
+    OPS_LAUNCH(ctx, unary_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, (const float *) a->data, (float *) d->data, n, unary_op);
     return finish(ctx);
 }
 
@@ -197,7 +203,7 @@ int b200_op_scale(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d, 
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    scale_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>((const float *) a->data, (float *) d->data, n, scale, bias);
+    OPS_LAUNCH(ctx, scale_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, (const float *) a->data, (float *) d->data, n, scale, bias);
     return finish(ctx);
 }
 

@@ -40,6 +40,29 @@ inline int grid_for(int64_t n, int sm_count) {
     return (int) (blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
 
+// Every kernel of these files starts with pdl_enter() and is launched with the programmatic-serialization attribute (ctx->pdl and
+// ctx->ops_pdl): it may become resident while its predecessor in the stream is still running, waits there until that grid has completed
+// and its writes are visible (griddepcontrol.wait), and at once lets ITS successor do the same — the launch latency of a chain of
+// small kernels overlaps their execution, and a GEMV that follows starts streaming its weights before the small kernels are done
+// (the GEMVs fetch weights ahead of their own wait, mmvq.cu).  Every kernel waits before it touches memory, so "my predecessor is
+// complete" implies "everything before it is complete".  Without the attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+template <typename... KA, typename... A>
+inline cudaError_t ops_launch(b200_ctx * ctx, void (*kern)(KA...), const dim3 grid, const dim3 block, A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl && ctx->ops_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);
+}
+#define OPS_LAUNCH(ctx, kern, grid, block, ...) do { B200_CUDA_TRY(ops_launch(ctx, kern, dim3(grid), dim3(block), __VA_ARGS__)); } while (0)
+
 inline int finish(b200_ctx * ctx) {
     B200_CUDA_TRY(cudaGetLastError());
     ctx->launches++;

@@ -28,6 +28,7 @@ __device__ __forceinline__ float to_float(const __nv_bfloat16 v) { return __bflo
 
 // ---- CPY: element i of src (in src's index order) goes to element i of dst (in dst's index order) -------------------------------
 __global__ void __launch_bounds__(OPS_THREADS) cpy_kernel(const tview a, const int ta, const tview d, const int td, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t a0, a1, a2, a3, d0, d1, d2, d3;
         split4(i, a.ne, a0, a1, a2, a3);
@@ -153,6 +154,7 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
 
 // dst[i0, i10, i11, i12] = src0[i0, idx[i10, i11, i12], i11, i12]
 __global__ void __launch_bounds__(OPS_THREADS) get_rows_kernel(const tview a, const int ta, const tview idx, const tview d, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t i0, i10, i11, i12;
         split4(i, d.ne, i0, i10, i11, i12);
@@ -166,6 +168,7 @@ __global__ void __launch_bounds__(OPS_THREADS) get_rows_kernel(const tview a, co
 // dst[i0, idx[i, i02 % ne11, i03 % ne12], i02, i03] = src0[i0, i, i02, i03]
 template <typename IDX>
 __global__ void __launch_bounds__(OPS_THREADS) set_rows_kernel(const tview a, const tview idx, const tview d, const int td, const int64_t n) {
+    pdl_enter();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t i0, i1, i2, i3;
         split4(i, a.ne, i0, i1, i2, i3);
@@ -181,6 +184,7 @@ __global__ void __launch_bounds__(OPS_THREADS) set_rows_kernel(const tview a, co
 template <typename T>
 __global__ void __launch_bounds__(OPS_THREADS) mul_mat_f_kernel(const tview a, const tview b, const tview d, const int64_t r2, const int64_t r3,
                                                                 const int64_t n_out) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t) gridDim.x * (OPS_THREADS / 32);
     for (int64_t o = (int64_t) blockIdx.x * (OPS_THREADS / 32) + (threadIdx.x >> 5); o < n_out; o += warps) {
@@ -200,6 +204,7 @@ __global__ void __launch_bounds__(OPS_THREADS) mul_mat_f_kernel(const tview a, c
 constexpr int MMF_T = 64, MMF_K = 16;
 template <typename T>
 __global__ void __launch_bounds__(256) mul_mat_f_tiled_kernel(const tview a, const tview b, const tview d, const int64_t r2, const int64_t r3) {
+    pdl_enter();
     __shared__ float sa[MMF_K][MMF_T + 1], sb[MMF_K][MMF_T + 1];
     const int64_t batch = blockIdx.z, i2 = batch % d.ne[2], i3 = batch / d.ne[2];
     const int64_t row0 = (int64_t) blockIdx.x * MMF_T, col0 = (int64_t) blockIdx.y * MMF_T;
@@ -255,7 +260,7 @@ int b200_op_cpy(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * d) {
     const int64_t n = nelem(a);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    cpy_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), a->type, view_of(d), d->type, n);
+    OPS_LAUNCH(ctx, cpy_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, view_of(a), a->type, view_of(d), d->type, n);
     return finish(ctx);
 }
 
@@ -272,7 +277,7 @@ int b200_op_get_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * 
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    get_rows_kernel<<<grid_for(n, ctx->sm_count), OPS_THREADS, 0, ctx->stream>>>(view_of(a), a->type, view_of(idx), view_of(d), n);
+    OPS_LAUNCH(ctx, get_rows_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, view_of(a), a->type, view_of(idx), view_of(d), n);
     return finish(ctx);
 }
 
@@ -287,8 +292,8 @@ int b200_op_set_rows(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * 
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     const int g = grid_for(n, ctx->sm_count);
-    if (idx->type == B200_TYPE_I64) set_rows_kernel<int64_t><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(idx), view_of(d), d->type, n);
-    else                            set_rows_kernel<int32_t><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(idx), view_of(d), d->type, n);
+    if (idx->type == B200_TYPE_I64) OPS_LAUNCH(ctx, set_rows_kernel<int64_t>, g, OPS_THREADS, view_of(a), view_of(idx), view_of(d), d->type, n);
+    else                            OPS_LAUNCH(ctx, set_rows_kernel<int32_t>, g, OPS_THREADS, view_of(a), view_of(idx), view_of(d), d->type, n);
     return finish(ctx);
 }
 
@@ -311,9 +316,9 @@ int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     if (b->ne[1] > 8 && d->ne[2] * d->ne[3] <= 65535) {            // many columns: the tiled kernel
         const dim3 grid((unsigned) ((d->ne[0] + MMF_T - 1) / MMF_T), (unsigned) ((d->ne[1] + MMF_T - 1) / MMF_T), (unsigned) (d->ne[2] * d->ne[3]));
         switch (a->type) {
-            case B200_TYPE_F32: mul_mat_f_tiled_kernel<float><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
-            case B200_TYPE_F16: mul_mat_f_tiled_kernel<__half><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
-            default:            mul_mat_f_tiled_kernel<__nv_bfloat16><<<grid, 256, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+            case B200_TYPE_F32: OPS_LAUNCH(ctx, mul_mat_f_tiled_kernel<float>, grid, 256, view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+            case B200_TYPE_F16: OPS_LAUNCH(ctx, mul_mat_f_tiled_kernel<__half>, grid, 256, view_of(a), view_of(b), view_of(d), r2t, r3t); break;
+            default:            OPS_LAUNCH(ctx, mul_mat_f_tiled_kernel<__nv_bfloat16>, grid, 256, view_of(a), view_of(b), view_of(d), r2t, r3t); break;
         }
         return finish(ctx);
     }
@@ -321,9 +326,9 @@ int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     const int g = (int) (blocks < cap ? blocks : cap);
     const int64_t r2 = b->ne[2] / a->ne[2], r3 = b->ne[3] / a->ne[3];
     switch (a->type) {
-        case B200_TYPE_F32: mul_mat_f_kernel<float><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
-        case B200_TYPE_F16: mul_mat_f_kernel<__half><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
-        default:            mul_mat_f_kernel<__nv_bfloat16><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+        case B200_TYPE_F32: OPS_LAUNCH(ctx, mul_mat_f_kernel<float>, g, OPS_THREADS, view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+        case B200_TYPE_F16: OPS_LAUNCH(ctx, mul_mat_f_kernel<__half>, g, OPS_THREADS, view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
+        default:            OPS_LAUNCH(ctx, mul_mat_f_kernel<__nv_bfloat16>, g, OPS_THREADS, view_of(a), view_of(b), view_of(d), r2, r3, n_out); break;
     }
     return finish(ctx);
 }

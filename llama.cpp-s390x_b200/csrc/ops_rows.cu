@@ -32,6 +32,7 @@ __device__ __forceinline__ float block_max(float v, float * red) {
 // ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row -------------------------------------------------------------
 // (w.p != NULL: the product with a weight tensor repeated into x's shape — RMS_NORM followed by MUL, as every norm of a Llama graph is)
 __global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, const tview w, const tview d, const float eps) {
+    pdl_enter();
     __shared__ float red[OPS_THREADS / 32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, co
 // above (a decode step normalises single rows: the latency of that chain is the kernel)
 constexpr int RMS_VEC_THREADS = 1024;
 __global__ void __launch_bounds__(RMS_VEC_THREADS) rms_norm_vec_kernel(const tview a, const tview w, const tview d, const float eps) {
+    pdl_enter();
     __shared__ float red[RMS_VEC_THREADS / 32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
@@ -112,6 +114,7 @@ template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return
 // one thread per pair of a row; rows = (i1 head, i2 position, i3 batch)
 template <typename T>
 __global__ void __launch_bounds__(OPS_THREADS) rope_kernel(const tview a, const tview d, const rope_args R, const int64_t n) {
+    pdl_enter();
     const int64_t half0 = a.ne[0] / 2;
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const int64_t pr = i % half0;
@@ -152,6 +155,7 @@ struct softmax_args {
 };
 
 __global__ void __launch_bounds__(OPS_THREADS) soft_max_kernel(const tview a, const tview d, const softmax_args S) {
+    pdl_enter();
     __shared__ float red[OPS_THREADS / 32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
@@ -208,8 +212,8 @@ int b200_op_rms_norm_mul(b200_ctx * ctx, const b200_tensor * a, const b200_tenso
     if (w) vw = view_of(w);
     auto al16 = [](const b200_tensor * t) { return (((uintptr_t) t->data | (uintptr_t) t->nb[1] | (uintptr_t) t->nb[2] | (uintptr_t) t->nb[3]) & 15) == 0; };
     const bool vec = a->ne[0] % 4 == 0 && a->ne[0] >= 1024 && al16(a) && al16(d) && (!w || (w->ne[0] == a->ne[0] && w->nb[0] == 4 && al16(w)));
-    if (vec) rms_norm_vec_kernel<<<(unsigned) rows, RMS_VEC_THREADS, 0, ctx->stream>>>(view_of(a), vw, view_of(d), eps);
-    else     rms_norm_kernel<<<(unsigned) rows, OPS_THREADS, 0, ctx->stream>>>(view_of(a), vw, view_of(d), eps);
+    if (vec) OPS_LAUNCH(ctx, rms_norm_vec_kernel, (unsigned) rows, RMS_VEC_THREADS, view_of(a), vw, view_of(d), eps);
+    else     OPS_LAUNCH(ctx, rms_norm_kernel, (unsigned) rows, OPS_THREADS, view_of(a), vw, view_of(d), eps);
     return finish(ctx);
 }
 
@@ -243,8 +247,8 @@ int b200_op_rope(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * pos,
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     const int g = grid_for(n, ctx->sm_count);
-    if (a->type == B200_TYPE_F32) rope_kernel<float><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), R, n);
-    else                          rope_kernel<__half><<<g, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), R, n);
+    if (a->type == B200_TYPE_F32) OPS_LAUNCH(ctx, rope_kernel<float>, g, OPS_THREADS, view_of(a), view_of(d), R, n);
+    else                          OPS_LAUNCH(ctx, rope_kernel<__half>, g, OPS_THREADS, view_of(a), view_of(d), R, n);
     return finish(ctx);
 }
 
@@ -272,7 +276,7 @@ int b200_op_soft_max(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * 
     }
     S.sinks = sinks ? (const float *) sinks->data : nullptr;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    soft_max_kernel<<<(unsigned) rows, OPS_THREADS, 0, ctx->stream>>>(view_of(a), view_of(d), S);
+    OPS_LAUNCH(ctx, soft_max_kernel, (unsigned) rows, OPS_THREADS, view_of(a), view_of(d), S);
     return finish(ctx);
 }
 
