@@ -22,6 +22,7 @@ int    b200_launch_gemv_mma(b200_ctx * ctx, int type, const mm_problem & P, int6
 int    b200_launch_mm_ids(b200_ctx * ctx, const int32_t * ids, int64_t ids_stride, int n_expert, int n_used, int64_t n_tokens,
                           int32_t * ids_src1, int32_t * expert_bounds);
 int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
+int    b200_launch_dequant_f16(b200_ctx * ctx, int type, const uint8_t * W, int64_t nb01, int64_t rows, int64_t k, void * out);
 int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
 int    b200_launch_ll_unpack(b200_ctx * ctx, const uint2 * buf, int64_t cap, uint32_t * state, int n_mats, const int64_t * m_full, float * const * Y);
 int    b200_mul_mat_multi_tc(b200_ctx * ctx, int n_mats, const b200_tensor * const * a, const b200_tensor * b, const b200_tensor * const * d);
@@ -126,6 +127,7 @@ int b200_ctx_create(int device, void * stream, b200_ctx ** out) {
     ctx->gemv_rpw_max_m = env_int("GGML_B200_GEMV_RPW_MAX_M", 4096);
     ctx->tc_pdl        = env_int("GGML_B200_TC_PDL", 0);
     ctx->ops_pdl       = env_int("GGML_B200_OPS_PDL", 1);
+    ctx->tc_dequant    = env_int("GGML_B200_TC_DEQUANT", 1);
     ctx->use_mma       = env_int("GGML_B200_USE_MMA", 1);
     ctx->mma_ks        = env_int("GGML_B200_MMA_KS", 0);
     ctx->mma_ch        = env_int("GGML_B200_MMA_CH", 0);
@@ -191,6 +193,7 @@ int b200_ctx_set_option(b200_ctx * ctx, const char * name, int value) {
     else if (!strcmp(name, "gemv_rpw_max_m")) slot = &ctx->gemv_rpw_max_m;
     else if (!strcmp(name, "tc_pdl"))        slot = &ctx->tc_pdl;
     else if (!strcmp(name, "ops_pdl"))       slot = &ctx->ops_pdl;
+    else if (!strcmp(name, "tc_dequant"))    slot = &ctx->tc_dequant;
     else if (!strcmp(name, "use_mma"))       slot = &ctx->use_mma;
     else if (!strcmp(name, "mma_ks"))        slot = &ctx->mma_ks;
     else if (!strcmp(name, "mma_ch"))        slot = &ctx->mma_ch;
@@ -534,6 +537,22 @@ int b200_mul_mat_ex(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b
         if (rc) return rc;
         return b200_launch_gemm_tc(ctx, a->type, P, n * batches, 0);
     }
+    // a weight type the tcgen05 GEMM has no converter for (Q4_1, Q5_0 / Q5_1, Q2_K, Q3_K, IQ4_NL / XS, MXFP4, NVFP4) and three or more column
+    // tiles of the generic GEMV: dequantize the matrix into fp16 scratch (one pass over the blocks, 2 bytes per weight written) and run the
+    // tensor-core GEMM on that — the GEMV tiles would walk the blocks ceil(n / 8) times with dp4a
+    if (n_peers == 0 && batches == 1 && n >= 17 && ctx->use_tc && ctx->tc_dequant && !ctx->force_generic && a->type != B200_TYPE_F16) {
+        mm_problem PF = P;
+        PF.W = nullptr; PF.nb01 = P.k * 2; PF.nb02 = PF.nb03 = PF.nb01 * P.m;
+        if (b200_tc_supported(ctx, B200_TYPE_F16, PF)) {
+            const size_t wbytes = ((size_t) P.m * (size_t) P.k * 2 + 1023) / 1024 * 1024;
+            int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, PF, n, wbytes));
+            if (rc) return rc;
+            PF.W = (const uint8_t *) ctx->ws;
+            rc = b200_launch_dequant_f16(ctx, a->type, P.W, P.nb01, P.m, P.k, ctx->ws);
+            if (rc) return rc;
+            return b200_launch_gemm_tc(ctx, B200_TYPE_F16, PF, n, wbytes);
+        }
+    }
     int rc = quantize_into_ws(ctx, b, 0, &P.act, nullptr);
     if (rc) return rc;
     const int64_t tiles = batches * ((n + 7) / 8);
@@ -627,6 +646,26 @@ int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * 
         if (rc) return rc;
         P.ids_src1 = ids_src1; P.expert_bounds = bounds;
         return b200_launch_gemm_tc(ctx, as->type, P, n_pairs, extra_bytes);
+    }
+    if (ctx->use_tc && ctx->tc_dequant && !ctx->force_generic && n_pairs >= 8 * (int64_t) n_expert && as->nb[2] == as->nb[1] * as->ne[1]) {
+        // (as above: every expert's matrix -> fp16 scratch, then the grouped tensor-core GEMM; worth it from ~8 positions per expert on)
+        mm_problem PF = P;
+        PF.W = nullptr; PF.nb01 = k * 2; PF.nb02 = PF.nb03 = PF.nb01 * P.m;
+        if (b200_tc_supported(ctx, B200_TYPE_F16, PF)) {
+            const size_t off_w  = (extra_bytes + 1023) / 1024 * 1024;
+            const size_t wbytes = ((size_t) n_expert * (size_t) P.m * (size_t) k * 2 + 1023) / 1024 * 1024;
+            int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, PF, n_pairs, off_w + wbytes));
+            if (rc) return rc;
+            int32_t * ids_src1 = (int32_t *) ctx->ws;
+            int32_t * bounds   = ids_src1 + n_pairs;
+            rc = b200_launch_mm_ids(ctx, P.ids, P.ids_stride, n_expert, n_used, n_tokens, ids_src1, bounds);
+            if (rc) return rc;
+            PF.ids_src1 = ids_src1; PF.expert_bounds = bounds;
+            PF.W = (const uint8_t *) ctx->ws + off_w;
+            rc = b200_launch_dequant_f16(ctx, as->type, P.W, P.nb01, (int64_t) n_expert * P.m, k, (void *) PF.W);
+            if (rc) return rc;
+            return b200_launch_gemm_tc(ctx, B200_TYPE_F16, PF, n_pairs, off_w + wbytes);
+        }
     }
     int rc = quantize_into_ws(ctx, b, extra_bytes, &P.act, &extra);
     if (rc) return rc;

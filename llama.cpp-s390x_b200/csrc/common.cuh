@@ -118,6 +118,7 @@ struct b200_ctx {
     // byte ranges written by kernels that may still be in flight behind a deferred dependency wait (see abi.cu)
     const char * pend_lo[16];
     const char * pend_hi[16];
+    int          tc_dequant;   // weight types without a tcgen05 converter: dequantize to fp16 scratch + tensor-core GEMM at n >= 17 (GGML_B200_TC_DEQUANT, default 1)
     int          ops_pdl;      // the graph-op kernels (ops*.cu) take part in programmatic dependent launch (GGML_B200_OPS_PDL, default 1)
     int          n_pend;
     int          defer_wait;      // 1: allow the deferred dependency wait

@@ -68,6 +68,7 @@ template <int RAW_ROW = TC_RAW_ROW> struct tc_cfg {
 // K elements covered by one raw slot (144 bytes per row)
 template <int TYPE> struct raw_k          { static constexpr int value = 256; };
 template <> struct raw_k<B200_TYPE_Q8_0>  { static constexpr int value = 128; };
+template <> struct raw_k<B200_TYPE_F16>   { static constexpr int value = 64; };        // fp16 "weights" (see w_frag<F16>): one stage per slot
 // bytes by which raw slot i of a row is fetched early so that the TMA source address is 16-byte aligned
 template <int TYPE> __device__ __forceinline__ uint32_t raw_skew(const int i) {
     return TYPE == B200_TYPE_Q8_0 ? 8u * (uint32_t) (i & 1) : (TYPE == B200_TYPE_Q6_K ? 2u * (uint32_t) (i & 7) : 0u);
@@ -75,7 +76,9 @@ template <int TYPE> __device__ __forceinline__ uint32_t raw_skew(const int i) {
 template <int TYPE> struct raw_row        { static constexpr int value = TC_RAW_ROW; };
 template <> struct raw_row<B200_TYPE_Q6_K> { static constexpr int value = 224; };
 template <> struct raw_row<B200_TYPE_Q5_K> { static constexpr int value = SZ_Q5_K; };       // 176: a whole number of 16-byte units, no skew
-constexpr int raw_row_of(const int type) { return type == B200_TYPE_Q6_K ? 224 : (type == B200_TYPE_Q5_K ? SZ_Q5_K : TC_RAW_ROW); }
+template <> struct raw_row<B200_TYPE_F16>  { static constexpr int value = 2 * TC_KS; };    // 128: the 64 halves of a stage
+constexpr int raw_row_of(const int type) { return type == B200_TYPE_Q6_K ? 224 : (type == B200_TYPE_Q5_K ? SZ_Q5_K : (type == B200_TYPE_F16 ? 2 * TC_KS : TC_RAW_ROW)); }
+constexpr int raw_k_of(const int type)   { return type == B200_TYPE_Q8_0 ? 128 : (type == B200_TYPE_F16 ? 64 : 256); }
 
 struct tc_args {
     const uint8_t * W;
@@ -303,6 +306,26 @@ template <> struct w_frag<B200_TYPE_Q5_K> {
         out[1] = h ? h1 : l1; slot[1] = h ? 7 : 1;
         out[2] = h ? l0 : h0; slot[2] = h ? 2 : 4;
         out[3] = h ? l1 : h1; slot[3] = h ? 3 : 5;
+    }
+};
+
+// F16: the row already holds fp16 values in natural K order — weight types without a converter of their own are dequantized into an fp16
+// scratch matrix first (abi.cu: b200_launch_dequant_f16) and then take this path.  Thread half h owns K elements [32 h, 32 h + 32); every
+// group of four goes out in the activations' (0, 2, 1, 3) order.
+template <> struct w_frag<B200_TYPE_F16> {
+    uint4 q[4];
+    __device__ __forceinline__ void load(const uint32_t row, const int, const int h) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) q[c] = lds_u4(row + 64 * h + 16 * c);
+    }
+    static __device__ __forceinline__ void load_row(w_frag & f0, w_frag & f1, const uint32_t row, const int sub) { f0.load(row, sub, 0); f1.load(row, sub, 1); }
+    __device__ __forceinline__ void convert(const int, const int h, const uint32_t, uint4 (&out)[4], int (&slot)[4]) const {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            out[c] = make_uint4(__byte_perm(q[c].x, q[c].y, 0x5410), __byte_perm(q[c].x, q[c].y, 0x7632),
+                                __byte_perm(q[c].z, q[c].w, 0x5410), __byte_perm(q[c].z, q[c].w, 0x7632));
+            slot[c] = 4 * h + c;
+        }
     }
 };
 
@@ -881,7 +904,7 @@ encode_tiled_fn get_encode() {
     return fn;
 }
 
-bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K; }
+bool tc_type_ok(int type) { return type == B200_TYPE_Q4_K || type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q6_K || type == B200_TYPE_Q5_K || type == B200_TYPE_F16; }
 
 template <int TYPE, bool PAIR>
 int launch_one(b200_ctx * ctx, const CUtensorMap * tmw, const CUtensorMap & tm, const tc_args & a) {
@@ -924,6 +947,7 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtenso
         case B200_TYPE_Q8_0: return launch_one<B200_TYPE_Q8_0, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q6_K: return launch_one<B200_TYPE_Q6_K, PAIR>(ctx, tmw, tm, a);
         case B200_TYPE_Q5_K: return launch_one<B200_TYPE_Q5_K, PAIR>(ctx, tmw, tm, a);
+        case B200_TYPE_F16:  return launch_one<B200_TYPE_F16, PAIR>(ctx, tmw, tm, a);
     }
     b200_set_error("tcgen05 GEMM: unsupported weight type %d", type);
     return B200_E_UNSUPPORTED;
@@ -933,7 +957,7 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtenso
 
 int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (!tc_type_ok(type) || !get_encode()) return 0;
-    const int rawk = type == B200_TYPE_Q8_0 ? raw_k<B200_TYPE_Q8_0>::value : 256;
+    const int rawk = type == B200_TYPE_Q8_0 ? raw_k<B200_TYPE_Q8_0>::value : 256;      // (fp16 rows too: segments are whole multiples of 256)
     if (P.k % rawk != 0 || P.k > (1 << 24) || P.m > (1 << 30)) return 0;
     // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
     const uintptr_t bits = (uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03;
@@ -1004,7 +1028,7 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
         for (int j = 0; j < M->n_mats; ++j) rt += (M->m[j] + tm - 1) / tm;
         return rt;
     };
-    const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : (type == B200_TYPE_Q5_K ? 44 : 36)));
+    const int raw_stage_bytes = TC_M * (type == B200_TYPE_Q8_0 ? 68 : (type == B200_TYPE_Q6_K ? 56 : (type == B200_TYPE_Q5_K ? 44 : (type == B200_TYPE_F16 ? 128 : 36))));
     const int forced = ctx->tc_nt >= 192 ? 192 : (ctx->tc_nt >= 128 ? 128 : (ctx->tc_nt > 0 ? 64 : 0));
     p.split_k = 1;
     p.pair = false;
@@ -1119,7 +1143,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
 
     tc_args a = {};
     a.ne02 = (int) ne02;
-    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : (type == B200_TYPE_Q5_K ? SZ_Q5_K : TC_RAW_ROW))) / 2;
+    a.raw_step = (type == B200_TYPE_Q8_0 ? 4 * SZ_Q8_0 : (type == B200_TYPE_Q6_K ? SZ_Q6_K : (type == B200_TYPE_Q5_K ? SZ_Q5_K : (type == B200_TYPE_F16 ? 2 * TC_KS : TC_RAW_ROW)))) / 2;
     a.W = P.W; a.nb01 = P.nb01; a.nb02 = P.nb02; a.nb03 = P.nb03;
     a.m = (int) P.m; a.k = (int) P.k; a.n = (int) n;
     a.nt = pl.nt; a.col_tiles = (int) pl.col_tiles; a.k6400 = 0x64006400u;

@@ -38,6 +38,19 @@ __global__ void __launch_bounds__(OPS_THREADS) cpy_kernel(const tview a, const i
     }
 }
 
+// the 4-bit code books kvalues_iq4nl / kvalues_mxfp4 (ggml-common.h:1110-1118) as bytes of two 64-bit constants (an indexed local array
+// would live in local memory)
+__device__ __forceinline__ int tab_iq4nl(const int i) {
+    // -127, -104, -83, -65, -49, -35, -22, -10 | 1, 13, 25, 38, 53, 69, 89, 113
+    const unsigned long long lo = 0xF6EADDCFBFAD9881ull, hi = 0x7159453526190D01ull;
+    return (int) (int8_t) (((i & 8) ? hi : lo) >> (8 * (i & 7)));
+}
+__device__ __forceinline__ int tab_mxfp4(const int i) {
+    // 0, 1, 2, 3, 4, 6, 8, 12 | 0, -1, -2, -3, -4, -6, -8, -12
+    const unsigned long long lo = 0x0C08060403020100ull, hi = 0xF4F8FAFCFDFEFF00ull;
+    return (int) (int8_t) (((i & 8) ? hi : lo) >> (8 * (i & 7)));
+}
+
 // ---- one element of a row of any type GET_ROWS reads (dequantize_row_* of ggml-quants.c, element by element) -------------------
 __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, const int64_t i) {
     switch (type) {
@@ -98,8 +111,6 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
             return __fmul_rn(__fmul_rn(ld_half(b + 108), (float) (sc - 32)), (float) q);
         }
         case B200_TYPE_IQ4_NL: case B200_TYPE_IQ4_XS: case B200_TYPE_MXFP4: {   // ggml-quants.c:2649-2688, 507-525
-            const int tab_nl[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
-            const int tab_mx[16] = {0, 1, 2, 3, 4, 6, 8, 12, 0, -1, -2, -3, -4, -6, -8, -12};
             const int l = (int) (i & 31);
             if (type == B200_TYPE_IQ4_XS) {
                 const uint8_t * b = row + (i >> 8) * SZ_IQ4_XS;
@@ -107,27 +118,26 @@ __device__ __forceinline__ float row_elem(const uint8_t * row, const int type, c
                 const int sh = b[2] | (b[3] << 8);
                 const int ls = ((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4);
                 const uint8_t qb = b[8 + 16 * ib + (l & 15)];
-                return __fmul_rn(__fmul_rn(ld_half(b), (float) (ls - 32)), (float) tab_nl[l < 16 ? (qb & 0xF) : (qb >> 4)]);
+                return __fmul_rn(__fmul_rn(ld_half(b), (float) (ls - 32)), (float) tab_iq4nl(l < 16 ? (qb & 0xF) : (qb >> 4)));
             }
             if (type == B200_TYPE_IQ4_NL) {
                 const uint8_t * b = row + (i >> 5) * SZ_IQ4_NL;
                 const uint8_t qb = b[2 + (l & 15)];
-                return __fmul_rn(ld_half(b), (float) tab_nl[l < 16 ? (qb & 0xF) : (qb >> 4)]);
+                return __fmul_rn(ld_half(b), (float) tab_iq4nl(l < 16 ? (qb & 0xF) : (qb >> 4)));
             }
             const uint8_t * b = row + (i >> 5) * SZ_MXFP4;
             const uint32_t e8 = b[0];
             const uint8_t qb = b[1 + (l & 15)];
-            return __fmul_rn((float) tab_mx[l < 16 ? (qb & 0xF) : (qb >> 4)], __uint_as_float(e8 < 2 ? 0x00200000u << e8 : (e8 - 1) << 23));
+            return __fmul_rn((float) tab_mxfp4(l < 16 ? (qb & 0xF) : (qb >> 4)), __uint_as_float(e8 < 2 ? 0x00200000u << e8 : (e8 - 1) << 23));
         }
         case B200_TYPE_NVFP4: {                                 // ggml-quants.c:527-550
-            const int tab_mx[16] = {0, 1, 2, 3, 4, 6, 8, 12, 0, -1, -2, -3, -4, -6, -8, -12};
             const uint8_t * b = row + (i >> 6) * SZ_NVFP4;
             const int e = (int) (i & 63), s = e >> 4, j = e & 15;
             const uint32_t x = b[s];
             const uint32_t ex = (x >> 3) & 0xFu, man = x & 7u;
             const float d = (x == 0 || x == 0x7F) ? 0.0f : (ex == 0 ? (float) man * 0.0009765625f : __uint_as_float(((ex + 119u) << 23) | (man << 20)));
             const uint8_t qb = b[4 + 8 * s + (j & 7)];
-            return __fmul_rn((float) tab_mx[j < 8 ? (qb & 0xF) : (qb >> 4)], d);
+            return __fmul_rn((float) tab_mxfp4(j < 8 ? (qb & 0xF) : (qb >> 4)), d);
         }
         case B200_TYPE_Q4_K: {                                  // ggml-quants.c:1467-1489
             const uint8_t * b = row + (i >> 8) * SZ_Q4_K;
@@ -246,7 +256,30 @@ __global__ void __launch_bounds__(256) mul_mat_f_tiled_kernel(const tview a, con
     }
 }
 
+// rows of any quantized type -> fp16, natural order (the prefill route of the weight types the tcgen05 GEMM has no converter for: abi.cu).
+// One thread per 8 consecutive elements (always inside one block) and one 16-byte store.
+__global__ void __launch_bounds__(OPS_THREADS) dequant_f16_kernel(const uint8_t * __restrict__ W, const int type, const int64_t nb01, const int64_t k8,
+                                                                  const int64_t n8, __half * __restrict__ out) {
+    pdl_enter();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t r = i / k8, c = (i - r * k8) * 8;
+        const uint8_t * row = W + r * nb01;
+        __half2 h[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(row_elem(row, type, c + 2 * j), row_elem(row, type, c + 2 * j + 1));
+        *reinterpret_cast<uint4 *>(out + i * 8) = *reinterpret_cast<const uint4 *>(h);
+    }
+}
+
 }  // namespace
+
+// rows x k elements of `type` at W (row stride nb01 bytes) -> out[rows][k] fp16; k a multiple of 8, out 16-byte aligned
+int b200_launch_dequant_f16(b200_ctx * ctx, int type, const uint8_t * W, int64_t nb01, int64_t rows, int64_t k, void * out) {
+    const int64_t n8 = rows * (k / 8);
+    if (n8 <= 0) return B200_OK;
+    OPS_LAUNCH(ctx, dequant_f16_kernel, grid_for(n8, ctx->sm_count), OPS_THREADS, W, type, nb01, k / 8, n8, (__half *) out);
+    return finish(ctx);
+}
 
 extern "C" {
 

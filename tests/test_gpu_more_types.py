@@ -89,6 +89,34 @@ def test_q5k_prefill_gemm_on_the_tensor_cores(pkg, gpu_ctx, ref, n):
     assert torch.equal(pair, got) and torch.equal(single, got)
 
 
+@pytest.mark.parametrize("n", [17, 130])
+@pytest.mark.parametrize("name", sorted(set(MORE) - {"q5_K"}))
+def test_prefill_of_types_without_a_converter(pkg, gpu_ctx, ref, name, n):
+    """n >= 17: the matrix is dequantized into fp16 scratch and multiplied by the tcgen05 GEMM (three launches) instead of ceil(n / 8)
+    column tiles of the generic GEMV; both against ggml-cpu"""
+    if ref is None:
+        pytest.skip("oracle/_ref did not travel")
+    import torch
+    t = MORE[name][0]
+    m, k = 700, 2048
+    rng = np.random.default_rng(zlib.crc32(repr((name, n, "tc")).encode()))
+    W = quantize(ref, name, m, k, rng)
+    X = rng.standard_normal((n, k)).astype(np.float32)
+    want = ref_mul_mat(ref, t, W, X)
+    Wd, Xd = dev(W), dev(X)
+    l0 = gpu_ctx.launches
+    got = pkg.mul_mat(gpu_ctx, t, Wd, Xd)
+    torch.cuda.synchronize()
+    assert gpu_ctx.launches - l0 == 3                            # dequantize, activations -> fp16, GEMM
+    assert nmse(want, got.cpu().numpy()) <= NMSE_TOL
+    try:
+        gpu_ctx.set_option("tc_dequant", 0)
+        tiles = pkg.mul_mat(gpu_ctx, t, Wd, Xd)
+    finally:
+        gpu_ctx.set_option("tc_dequant", 1)
+    assert nmse(want, tiles.cpu().numpy()) <= NMSE_TOL
+
+
 @pytest.mark.parametrize("name", sorted(MORE))
 def test_get_rows_more_types(pkg, gpu_ctx, ref, name):
     if ref is None:
@@ -121,7 +149,7 @@ def test_mul_mat_id_more_types(pkg, gpu_ctx, ref, name):
     import torch
     t = MORE[name][0]
     n_expert, n_used, m, k = 8, 2, 96, 512
-    for n_tokens in (1, 37):
+    for n_tokens in (1, 37, 80):                                 # (80: 160 pairs, the experts' matrices go through fp16 scratch to the tcgen05 GEMM)
         rng = np.random.default_rng(zlib.crc32(repr((name, n_tokens)).encode()))
         AS = np.stack([quantize(ref, name, m, k, rng) for _ in range(n_expert)])
         B = rng.standard_normal((n_tokens, 1, k)).astype(np.float32)
