@@ -4,6 +4,12 @@
 #include <math.h>
 
 #include "ops.cuh"
+#include "mm_problem.cuh"
+
+int    b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P);
+size_t b200_gemm_tc_scratch(const b200_ctx * ctx, const mm_problem & P, int64_t n_pos, size_t ws_used);
+int    b200_launch_gemm_tc(b200_ctx * ctx, int type, const mm_problem & P, int64_t n_pos, size_t ws_used);
+int    b200_ctx_reserve(b200_ctx * ctx, size_t bytes);
 
 namespace {
 
@@ -25,6 +31,21 @@ __device__ __forceinline__ void store_elem(char * p, const int type, const float
 __device__ __forceinline__ float to_float(const float v) { return v; }
 __device__ __forceinline__ float to_float(const __half v) { return __half2float(v); }
 __device__ __forceinline__ float to_float(const __nv_bfloat16 v) { return __bfloat162float(v); }
+
+// four consecutive elements from an address aligned to their size
+__device__ __forceinline__ void load4(const float * p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4 *>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4(const __half * p, float (&v)[4]) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(p);
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&t.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&t.y));
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+__device__ __forceinline__ void load4(const __nv_bfloat16 * p, float (&v)[4]) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(p);
+    v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xFFFF0000u); v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xFFFF0000u);
+}
 
 // ---- CPY: element i of src (in src's index order) goes to element i of dst (in dst's index order) -------------------------------
 __global__ void __launch_bounds__(OPS_THREADS) cpy_kernel(const tview a, const int ta, const tview d, const int td, const int64_t n) {
@@ -203,7 +224,21 @@ __global__ void __launch_bounds__(OPS_THREADS) mul_mat_f_kernel(const tview a, c
         const T *     w = (const T *) (a.p + i0 * a.nb[1] + (i2 / r2) * a.nb[2] + (i3 / r3) * a.nb[3]);
         const float * x = (const float *) (b.p + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]);
         float s = 0.0f;
-        for (int64_t k = lane; k < a.ne[0]; k += 32) s += to_float(w[k]) * x[k];
+        const int64_t K = a.ne[0];
+        int64_t k_done = 0;
+        // four elements per lane and step where the row starts allow it (a decode step's K.q and V.p: 128 / n_kv elements per row — the
+        // scalar loop was a chain of 2-byte loads)
+        if (((uintptr_t) w % (4 * sizeof(T))) == 0 && ((uintptr_t) x & 15) == 0) {
+            const int64_t K4 = K & ~(int64_t) 3;
+            for (int64_t k = 4 * lane; k < K4; k += 128) {
+                float wv[4];
+                load4(w + k, wv);
+                const float4 xv = *reinterpret_cast<const float4 *>(x + k);
+                s += wv[0] * xv.x + wv[1] * xv.y + wv[2] * xv.z + wv[3] * xv.w;
+            }
+            k_done = K4;
+        }
+        for (int64_t k = k_done + lane; k < K; k += 32) s += to_float(w[k]) * x[k];
         s = warp_sum(s);
         if (lane == 0) *(float *) (d.p + i0 * 4 + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = s;
     }
@@ -346,6 +381,23 @@ int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     if (n_out == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     const int64_t r2t = b->ne[2] / a->ne[2], r3t = b->ne[3] / a->ne[3];
+    // many columns against a plain fp16 matrix (the weights of an F16 model): the tcgen05 GEMM reads the rows as they are (w_frag<F16>,
+    // mmq_tc.cu); src1 goes to normalised fp16 like for the quantized types (ggml-cpu converts src1 to fp16 for this product as well)
+    if (a->type == B200_TYPE_F16 && b->ne[1] >= 17 && ctx->use_tc && !ctx->force_generic && a->ne[2] * a->ne[3] == 1 && b->ne[2] * b->ne[3] == 1 &&
+        a->nb[0] == 2 && b->nb[0] == 4 && d->nb[0] == 4 && d->nb[1] == d->ne[0] * 4) {
+        mm_problem P = {};
+        P.W = (const uint8_t *) a->data; P.nb01 = a->nb[1]; P.nb02 = P.nb03 = a->nb[1] * a->ne[1];
+        P.m = a->ne[1]; P.k = a->ne[0];
+        P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = P.nb13 = b->nb[1] * b->ne[1];
+        P.ne11 = b->ne[1]; P.ne12 = 1; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+        P.Y = (float *) d->data; P.mode = MM_PLAIN;
+        if (b200_tc_supported(ctx, B200_TYPE_F16, P)) {
+            const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, b->ne[1], 0));
+            if (rc) return rc;
+            ctx->n_pend = 16;
+            return b200_launch_gemm_tc(ctx, B200_TYPE_F16, P, b->ne[1], 0);
+        }
+    }
     if (b->ne[1] > 8 && d->ne[2] * d->ne[3] <= 65535) {            // many columns: the tiled kernel
         const dim3 grid((unsigned) ((d->ne[0] + MMF_T - 1) / MMF_T), (unsigned) ((d->ne[1] + MMF_T - 1) / MMF_T), (unsigned) (d->ne[2] * d->ne[3]));
         switch (a->type) {

@@ -96,6 +96,29 @@ def test_kv_store_and_attention_products(pkg, gpu_ctx):
     assert nmse(want.cpu().numpy(), kq[0, :, 0].cpu().numpy()) <= 1e-10
 
 
+@pytest.mark.parametrize("n", [17, 512])
+def test_f16_weights_prefill_on_the_tensor_cores(pkg, gpu_ctx, n):
+    """MUL_MAT with a plain fp16 matrix and many columns: the tcgen05 GEMM reads the fp16 rows as they are (two launches), against the
+    SIMT tile kernel (use_tc = 0) and the f64 product"""
+    import torch
+    g = torch.Generator(device="cuda"); g.manual_seed(n)
+    m, k = 1000, 2048
+    W = (torch.randn((1, 1, m, k), device="cuda", generator=g) * 0.05).half()
+    X = torch.randn((1, 1, n, k), device="cuda", generator=g)
+    l0 = gpu_ctx.launches
+    got = pkg.graph_op(gpu_ctx, "mul_mat_f", W, X, torch.empty((1, 1, n, m), device="cuda"))
+    torch.cuda.synchronize()
+    assert gpu_ctx.launches - l0 == 2
+    want = X[0, 0].double() @ W[0, 0].double().T
+    assert nmse(want.cpu().numpy(), got[0, 0].cpu().numpy()) <= 1e-6
+    try:
+        gpu_ctx.set_option("use_tc", 0)
+        simt = pkg.graph_op(gpu_ctx, "mul_mat_f", W, X, torch.empty((1, 1, n, m), device="cuda"))
+    finally:
+        gpu_ctx.set_option("use_tc", 1)
+    assert nmse(want.cpu().numpy(), simt[0, 0].cpu().numpy()) <= 1e-10
+
+
 @pytest.mark.parametrize("name", ["f32", "q4_K", "q6_K", "q8_0", "q4_0"])
 def test_get_rows_token_embeddings(pkg, gpu_ctx, orc, name):
     import torch
