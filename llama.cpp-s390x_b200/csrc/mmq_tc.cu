@@ -957,7 +957,8 @@ int launch_type(b200_ctx * ctx, int type, const CUtensorMap * tmw, const CUtenso
 
 int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (!tc_type_ok(type) || !get_encode()) return 0;
-    const int rawk = type == B200_TYPE_Q8_0 ? raw_k<B200_TYPE_Q8_0>::value : 256;      // (fp16 rows too: segments are whole multiples of 256)
+    // (fp16 rows: one stage per raw slot, stages travel in pairs — 128; an attention head's K rows are 128 long)
+    const int rawk = (type == B200_TYPE_Q8_0 || type == B200_TYPE_F16) ? 128 : 256;
     if (P.k % rawk != 0 || P.k > (1 << 24) || P.m > (1 << 30)) return 0;
     // TMA over the raw blocks: base and strides 16-byte aligned, the matrices of all batches / experts equally spaced
     const uintptr_t bits = (uintptr_t) P.W | (uintptr_t) P.nb01 | (uintptr_t) P.nb02 | (uintptr_t) P.nb03;
@@ -965,7 +966,9 @@ int b200_tc_supported(const b200_ctx * ctx, int type, const mm_problem & P) {
     if (P.mode == MM_PLAIN) {
         const int64_t ne02 = P.ne12 / P.r2, ne03 = P.ne13 / P.r3;
         if (ne03 > 1 && P.nb03 != P.nb02 * ne02) return 0;
-        if (ne02 * ne03 > 1 && P.nb02 < P.nb01 * P.m) return 0;
+        // (quantized weights: batches are whole matrices one after the other; fp16 matrices may be strided views — the heads of a KV cache
+        //  interleave row by row — which the tensor map's strides express as they are)
+        if (type != B200_TYPE_F16 && ne02 * ne03 > 1 && P.nb02 < P.nb01 * P.m) return 0;
     } else if (P.n_expert > 1 && P.nb02 < P.nb01 * P.m) return 0;
     if (((uintptr_t) P.X | (uintptr_t) P.nb11 | (uintptr_t) P.nb12 | (uintptr_t) P.nb13) & 15) return 0;
     if (P.mode == MM_ID_PAIRS) return 0;
@@ -1053,10 +1056,10 @@ static tc_plan make_plan(const b200_ctx * ctx, int type, const mm_problem & P, i
                 if (!forced && nt > 64 && p.n <= nt - 64) continue;      // a narrower width already covers n with one tile
                 for (const int sk : {1, 2, 4}) {
                     if (sk > 1) {
-                        if (pair || ctx->tc_split_k == 0 || P.n_peers > 0 || (P.k / 256) % sk != 0) continue;
+                        if (pair || ctx->tc_split_k == 0 || P.n_peers > 0 || P.k % (256 * sk) != 0) continue;
                         if (ctx->tc_split_k == 1 && (sk > 2 || P.k < 8192)) continue;
                         if (ctx->tc_split_k > 1 && sk != ctx->tc_split_k) continue;
-                    } else if (!pair && ctx->tc_split_k > 1 && (P.k / 256) % ctx->tc_split_k == 0 && P.n_peers == 0) continue;
+                    } else if (!pair && ctx->tc_split_k > 1 && P.k % (256 * ctx->tc_split_k) == 0 && P.n_peers == 0) continue;
                     double t = tc_makespan(rts, p.n, p.batches, nt, sk, stages, units, raw_stage_bytes, pair != 0);
                     if (sk > 1) t *= 1.05;                                // the turnstile and the reductions are not free
                     if (p.nt == 0 || t < best) { best = t; p.nt = nt; p.split_k = sk; p.pair = pair != 0; }
@@ -1132,7 +1135,7 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
         if (j > 0 && jj == 0) { tmw[j] = tmw[0]; continue; }
         const void *  base = M ? (const void *) M->W[jj] : (const void *) P.W;
         const int64_t rows = M ? M->m[jj] : P.m;
-        const cuuint64_t wdim[3]    = {(cuuint64_t) P.nb01 / 2, (cuuint64_t) rows, (cuuint64_t) (M ? 1 : nmat)};
+        const cuuint64_t wdim[3]    = {(cuuint64_t) (type == B200_TYPE_F16 ? P.k : P.nb01 / 2), (cuuint64_t) rows, (cuuint64_t) (M ? 1 : nmat)};
         const cuuint64_t wstride[2] = {(cuuint64_t) P.nb01, (cuuint64_t) (!M && nmat > 1 ? P.nb02 : P.nb01 * rows)};
         const cuuint32_t wbox[3]    = {(cuuint32_t) raw_row_of(type) / 2, (cuuint32_t) TC_M, 1};
         const cuuint32_t westr[3]   = {1, 1, 1};

@@ -381,21 +381,23 @@ int b200_mul_mat_f(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * b,
     if (n_out == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     const int64_t r2t = b->ne[2] / a->ne[2], r3t = b->ne[3] / a->ne[3];
-    // many columns against a plain fp16 matrix (the weights of an F16 model): the tcgen05 GEMM reads the rows as they are (w_frag<F16>,
-    // mmq_tc.cu); src1 goes to normalised fp16 like for the quantized types (ggml-cpu converts src1 to fp16 for this product as well)
-    if (a->type == B200_TYPE_F16 && b->ne[1] >= 17 && ctx->use_tc && !ctx->force_generic && a->ne[2] * a->ne[3] == 1 && b->ne[2] * b->ne[3] == 1 &&
-        a->nb[0] == 2 && b->nb[0] == 4 && d->nb[0] == 4 && d->nb[1] == d->ne[0] * 4) {
+    // many columns against fp16 rows — the weights of an F16 model, or K / V of a KV cache at prompt time (a batch of strided views with
+    // grouped-query broadcast): the tcgen05 GEMM reads the rows as they are through its tensor map (w_frag<F16>, mmq_tc.cu); src1 goes to
+    // normalised fp16 like for the quantized types (ggml-cpu converts src1 to fp16 for this product as well)
+    if (a->type == B200_TYPE_F16 && b->ne[1] >= 17 && ctx->use_tc && !ctx->force_generic && a->ne[3] == 1 && b->ne[3] == 1 &&
+        a->nb[0] == 2 && b->nb[0] == 4 && contiguous(d, 4)) {
         mm_problem P = {};
-        P.W = (const uint8_t *) a->data; P.nb01 = a->nb[1]; P.nb02 = P.nb03 = a->nb[1] * a->ne[1];
+        P.W = (const uint8_t *) a->data; P.nb01 = a->nb[1]; P.nb02 = a->ne[2] > 1 ? a->nb[2] : a->nb[1] * a->ne[1]; P.nb03 = P.nb02 * a->ne[2];
         P.m = a->ne[1]; P.k = a->ne[0];
-        P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = P.nb13 = b->nb[1] * b->ne[1];
-        P.ne11 = b->ne[1]; P.ne12 = 1; P.ne13 = 1; P.r2 = 1; P.r3 = 1;
+        P.X = (const float *) b->data; P.nb11 = b->nb[1]; P.nb12 = b->ne[2] > 1 ? b->nb[2] : b->nb[1] * b->ne[1]; P.nb13 = P.nb12 * b->ne[2];
+        P.ne11 = b->ne[1]; P.ne12 = b->ne[2]; P.ne13 = 1; P.r2 = r2t; P.r3 = 1;
         P.Y = (float *) d->data; P.mode = MM_PLAIN;
-        if (b200_tc_supported(ctx, B200_TYPE_F16, P)) {
-            const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, b->ne[1], 0));
+        const int64_t n_pos = b->ne[1] * b->ne[2];
+        if (n_pos < ((int64_t) 1 << 24) && b200_tc_supported(ctx, B200_TYPE_F16, P)) {
+            const int rc = b200_ctx_reserve(ctx, b200_gemm_tc_scratch(ctx, P, n_pos, 0));
             if (rc) return rc;
             ctx->n_pend = 16;
-            return b200_launch_gemm_tc(ctx, B200_TYPE_F16, P, b->ne[1], 0);
+            return b200_launch_gemm_tc(ctx, B200_TYPE_F16, P, n_pos, 0);
         }
     }
     if (b->ne[1] > 8 && d->ne[2] * d->ne[3] <= 65535) {            // many columns: the tiled kernel

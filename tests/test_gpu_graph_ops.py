@@ -119,6 +119,34 @@ def test_f16_weights_prefill_on_the_tensor_cores(pkg, gpu_ctx, n):
     assert nmse(want.cpu().numpy(), simt[0, 0].cpu().numpy()) <= 1e-10
 
 
+def test_prompt_attention_products_on_the_tensor_cores(pkg, gpu_ctx):
+    """K.q and V.p of a 512-token prompt (Llama-3-8B: 32 heads over 8 KV heads, head size 128): K and V^T are strided fp16 views of the cache,
+    q is a permuted f32 view; the tcgen05 GEMM takes them as a batch (2 launches each) — against the SIMT tile kernel and torch"""
+    import torch
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    n_tok, n_kv, hd, n_head_kv, n_head, n_ctx = 512, 512, 128, 8, 32, 1024
+    kc = (torch.randn((n_ctx, n_head_kv * hd), device="cuda", generator=g)).half()              # K cache: one row per position
+    vc = (torch.randn((n_head_kv * hd, n_ctx), device="cuda", generator=g)).half()              # V cache, transposed: one row per channel
+    k_view = kc[:n_kv].view(n_kv, n_head_kv, hd).permute(1, 0, 2).unsqueeze(0)                   # ggml [hd, n_kv, n_head_kv]
+    v_view = vc.view(n_head_kv, hd, n_ctx)[:, :, :n_kv].unsqueeze(0)                             # ggml [n_kv, hd, n_head_kv]
+    q = torch.randn((n_tok, n_head, hd), device="cuda", generator=g).permute(1, 0, 2).unsqueeze(0)      # ggml [hd, n_tok, n_head], strided
+    p_ = torch.softmax(torch.randn((1, n_head, n_tok, n_kv), device="cuda", generator=g), dim=-1)
+    rep = n_head // n_head_kv
+    for a, b, m, want in ((k_view, q, n_kv, torch.einsum("hkd,htd->htk", k_view[0].double().repeat_interleave(rep, dim=0), q[0].double())),
+                          (v_view, p_, hd, torch.einsum("hdk,htk->htd", v_view[0].double().repeat_interleave(rep, dim=0), p_[0].double()))):
+        l0 = gpu_ctx.launches
+        got = pkg.graph_op(gpu_ctx, "mul_mat_f", a, b, torch.empty((1, n_head, n_tok, m), device="cuda"))
+        torch.cuda.synchronize()
+        assert gpu_ctx.launches - l0 == 2
+        assert nmse(want.cpu().numpy(), got[0].cpu().numpy()) <= 1e-6
+        try:
+            gpu_ctx.set_option("use_tc", 0)
+            simt = pkg.graph_op(gpu_ctx, "mul_mat_f", a, b, torch.empty((1, n_head, n_tok, m), device="cuda"))
+        finally:
+            gpu_ctx.set_option("use_tc", 1)
+        assert nmse(want.cpu().numpy(), simt[0].cpu().numpy()) <= 1e-10
+
+
 @pytest.mark.parametrize("name", ["f32", "q4_K", "q6_K", "q8_0", "q4_0"])
 def test_get_rows_token_embeddings(pkg, gpu_ctx, orc, name):
     import torch
