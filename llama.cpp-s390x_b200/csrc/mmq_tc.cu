@@ -190,6 +190,63 @@ __global__ void __launch_bounds__(256) tc_act_f16_kernel(const mm_problem P, __h
     for (int i = threadIdx.x + 256 * KEEP; i < k4; i += 256) emit(i, __ldg(reinterpret_cast<const float4 *>(x) + i));
 }
 
+// the same for short columns (k <= 1024: the q rows and the score rows of prompt-time attention, tens of thousands of positions): one warp
+// per position, eight positions per CTA, the column in registers, no block-wide synchronisation
+__global__ void __launch_bounds__(256) tc_act_f16_warp_kernel(const mm_problem P, __half * __restrict__ Xh, float * __restrict__ colscale,
+                                                              int32_t * __restrict__ ycol, const int64_t n_pos) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int lane = threadIdx.x & 31;
+    const int64_t p = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (p >= n_pos) return;
+    const float * x;
+    if (P.mode == MM_PLAIN) {
+        const int64_t batch = p / P.ne11, i11 = p - batch * P.ne11;
+        const int64_t i12 = batch % P.ne12, i13 = batch / P.ne12;
+        x = reinterpret_cast<const float *>(reinterpret_cast<const char *>(P.X) + i11 * P.nb11 + i12 * P.nb12 + i13 * P.nb13);
+    } else {
+        const int     pair  = __ldg(P.ids_src1 + p);
+        const int64_t token = pair / P.n_used;
+        const int64_t i11   = (pair - token * P.n_used) % P.ne11;
+        x = reinterpret_cast<const float *>(reinterpret_cast<const char *>(P.X) + i11 * P.nb11 + token * P.nb12);
+        if (lane == 0) ycol[p] = pair;
+    }
+    const int k4 = (int) (P.k / 4);                       // <= 256: at most 8 float4 per lane
+    float4 keep[8];
+    float amax = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int i = lane + 32 * j;
+        keep[j] = i < k4 ? __ldg(reinterpret_cast<const float4 *>(x) + i) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(keep[j].x), fabsf(keep[j].y)), fmaxf(fabsf(keep[j].z), fabsf(keep[j].w))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    int e = 0;
+    float up = 1.0f, down = 1.0f;
+    if (amax > 0.0f && amax < INFINITY) {                 // (as in tc_act_f16_kernel)
+        frexpf(amax, &e);
+        int s = 15 - e;
+        s = s > 126 ? 126 : (s < -126 ? -126 : s);
+        up   = ldexpf(1.0f, s);
+        down = ldexpf(1.0f, -s);
+    }
+    if (lane == 0) colscale[p] = down;
+    uint2 * out = reinterpret_cast<uint2 *>(Xh + p * P.k);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int i = lane + 32 * j;
+        if (i < k4) {
+            const __half2 a = __floats2half2_rn(keep[j].x * up, keep[j].z * up);      // order (0, 2, 1, 3)
+            const __half2 b = __floats2half2_rn(keep[j].y * up, keep[j].w * up);
+            uint2 o;
+            o.x = *reinterpret_cast<const uint32_t *>(&a);
+            o.y = *reinterpret_cast<const uint32_t *>(&b);
+            out[i] = o;
+        }
+    }
+}
+
 // ---- weight fragments: what one converter thread handles for one stage (64 K elements of its row, its half of them) ------
 __device__ __forceinline__ uint32_t lds_u32(const uint32_t a) {
     uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v;
@@ -1107,12 +1164,14 @@ static int launch_gemm_tc_core(b200_ctx * ctx, int type, const mm_problem & P, i
 
     {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned) n_pos); cfg.blockDim = dim3(256); cfg.stream = ctx->stream;
+        const bool warp_per_pos = P.k <= 1024 && n_pos >= 1024;
+        cfg.gridDim = dim3((unsigned) (warp_per_pos ? (n_pos + 7) / 8 : n_pos)); cfg.blockDim = dim3(256); cfg.stream = ctx->stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = (ctx->pdl && ctx->tc_pdl) ? 1 : 0;
-        B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, tc_act_f16_kernel, P, Xh, sc, yc));
+        if (warp_per_pos) B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, tc_act_f16_warp_kernel, P, Xh, sc, yc, n_pos));
+        else              B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, tc_act_f16_kernel, P, Xh, sc, yc));
     }
     ctx->launches++;
 

@@ -41,6 +41,21 @@ __global__ void __launch_bounds__(OPS_THREADS) bin_kernel(const tview a, const t
     }
 }
 
+// same-shape, contiguous, 16-byte aligned operands (the residual adds of a prompt: 8 MB each): four elements per thread, no index arithmetic
+template <int OP>
+__global__ void __launch_bounds__(OPS_THREADS) bin_vec_kernel(const float4 * a, const float4 * b, float4 * d, const int64_t n4) {          // (d may be a or b: in-place adds)
+    pdl_enter();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        const float4 x = a[i], y = b[i];
+        float4 r;
+        if (OP == B200_OP_ADD)      r = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+        else if (OP == B200_OP_SUB) r = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
+        else if (OP == B200_OP_MUL) r = make_float4(x.x * y.x, x.y * y.y, x.z * y.z, x.w * y.w);
+        else                        r = make_float4(x.x / y.x, x.y / y.y, x.z / y.z, x.w / y.w);
+        d[i] = r;
+    }
+}
+
 // ---- REPEAT: dst = src0 tiled -------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(OPS_THREADS) repeat_kernel(const tview a, const tview d, const int64_t n) {
     pdl_enter();
@@ -73,6 +88,18 @@ __global__ void __launch_bounds__(OPS_THREADS) glu_kernel(const char * xp, const
         const int64_t r = i / nc, c = i - r * nc;
         const float x = ((const float *) (xp + r * xs))[c], g = ((const float *) (gp + r * gs))[c];
         ((float *) (dp + r * ds))[c] = glu_value(op, x, g, alpha, limit);
+    }
+}
+
+// the same with four values per thread (rows a multiple of 4 long, 16-byte aligned)
+__global__ void __launch_bounds__(OPS_THREADS) glu_vec_kernel(const char * xp, const int64_t xs, const char * gp, const int64_t gs, char * dp, const int64_t ds,
+                                                              const int64_t nc4, const int64_t n4, const int op, const float alpha, const float limit) {
+    pdl_enter();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t r = i / nc4, c = i - r * nc4;
+        const float4 x = ((const float4 *) (xp + r * xs))[c], g = ((const float4 *) (gp + r * gs))[c];
+        ((float4 *) (dp + r * ds))[c] = make_float4(glu_value(op, x.x, g.x, alpha, limit), glu_value(op, x.y, g.y, alpha, limit),
+                                                    glu_value(op, x.z, g.z, alpha, limit), glu_value(op, x.w, g.w, alpha, limit));
     }
 }
 
@@ -117,6 +144,19 @@ int b200_op_binary(b200_ctx * ctx, int op, const b200_tensor * a, const b200_ten
     const int64_t n = nelem(d);
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    if (op >= B200_OP_ADD && op <= B200_OP_DIV && same_shape(a, b) && contiguous(a, 4) && contiguous(b, 4) && contiguous(d, 4) && n % 4 == 0 &&
+        (((uintptr_t) a->data | (uintptr_t) b->data | (uintptr_t) d->data) & 15) == 0) {
+        const float4 * pa = (const float4 *) a->data, * pb = (const float4 *) b->data;
+        float4 * pd = (float4 *) d->data;
+        const int gv = grid_for(n / 4, ctx->sm_count);
+        switch (op) {
+            case B200_OP_ADD: OPS_LAUNCH(ctx, bin_vec_kernel<B200_OP_ADD>, gv, OPS_THREADS, pa, pb, pd, n / 4); break;
+            case B200_OP_SUB: OPS_LAUNCH(ctx, bin_vec_kernel<B200_OP_SUB>, gv, OPS_THREADS, pa, pb, pd, n / 4); break;
+            case B200_OP_MUL: OPS_LAUNCH(ctx, bin_vec_kernel<B200_OP_MUL>, gv, OPS_THREADS, pa, pb, pd, n / 4); break;
+            default:          OPS_LAUNCH(ctx, bin_vec_kernel<B200_OP_DIV>, gv, OPS_THREADS, pa, pb, pd, n / 4); break;
+        }
+        return finish(ctx);
+    }
     const int g = grid_for(n, ctx->sm_count);
     const tview va = view_of(a), vb = view_of(b), vd = view_of(d);
     switch (op) {
@@ -167,8 +207,12 @@ int b200_op_glu(b200_ctx * ctx, int glu_op, const b200_tensor * a, const b200_te
     const char * xp = (const char *) a->data, * gp = b ? (const char *) b->data : (const char *) a->data;
     if (!b) { xp += swapped ? nc * 4 : 0; gp += swapped ? 0 : nc * 4; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    OPS_LAUNCH(ctx, glu_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, xp, a->nb[1], gp, b ? b->nb[1] : a->nb[1], (char *) d->data, d->nb[1], nc, n,
-                                                                             glu_op, alpha, limit);
+    const int64_t gs = b ? b->nb[1] : a->nb[1];
+    if (nc % 4 == 0 && (((uintptr_t) xp | (uintptr_t) gp | (uintptr_t) d->data | (uintptr_t) a->nb[1] | (uintptr_t) gs | (uintptr_t) d->nb[1]) & 15) == 0) {
+        OPS_LAUNCH(ctx, glu_vec_kernel, grid_for(n / 4, ctx->sm_count), OPS_THREADS, xp, a->nb[1], gp, gs, (char *) d->data, d->nb[1], nc / 4, n / 4, glu_op, alpha, limit);
+        return finish(ctx);
+    }
+    OPS_LAUNCH(ctx, glu_kernel, grid_for(n, ctx->sm_count), OPS_THREADS, xp, a->nb[1], gp, gs, (char *) d->data, d->nb[1], nc, n, glu_op, alpha, limit);
     return finish(ctx);
 }
 

@@ -189,6 +189,56 @@ __global__ void __launch_bounds__(OPS_THREADS) soft_max_kernel(const tview a, co
     for (int64_t i = threadIdx.x; i < n; i += OPS_THREADS) y[i] *= inv;
 }
 
+// rows of up to 32 * NPL values (the attention scores of a prompt: 16 384 rows of 512): one warp per row, the row stays in registers
+// between the three steps — one read, one write, no block-wide synchronisation.  Same arithmetic as soft_max_kernel.
+constexpr int SMW_ROWS = OPS_THREADS / 32;
+template <int NPL>
+__global__ void __launch_bounds__(OPS_THREADS) soft_max_warp_kernel(const tview a, const tview d, const softmax_args S, const int64_t rows) {
+    pdl_enter();
+    const int lane = threadIdx.x & 31;
+    const int64_t r = (int64_t) blockIdx.x * SMW_ROWS + (threadIdx.x >> 5);
+    if (r >= rows) return;                                      // (whole warps leave; nothing block-wide follows)
+    const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
+    const float * x = (const float *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    float *       y = (float *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const int n = (int) a.ne[0];
+    float slope = 1.0f;
+    if (S.max_bias > 0.0f) {
+        const uint32_t h = (uint32_t) i2;
+        slope = h < S.n_head_log2 ? powf(S.m0, (float) (h + 1)) : powf(S.m1, (float) (2 * (h - S.n_head_log2) + 1));
+    }
+    const char * mrow = S.mask ? S.mask + i1 * S.mnb1 + (i2 % S.mne2) * S.mnb2 + (i3 % S.mne3) * S.mnb3 : nullptr;
+    float v[NPL];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+        const int i = lane + 32 * j;
+        float t = -INFINITY;
+        if (i < n) {
+            t = x[i] * S.scale;
+            if (mrow) t += slope * (S.mask_f16 ? __half2float(((const __half *) mrow)[i]) : ((const float *) mrow)[i]);
+        }
+        v[j] = t;
+        mx = fmaxf(mx, t);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (S.sinks) mx = fmaxf(mx, S.sinks[i2]);
+    float sum = 0.0f;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+        const float e = lane + 32 * j < n ? expf(v[j] - mx) : 0.0f;
+        v[j] = e;
+        sum += e;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (S.sinks) sum += expf(S.sinks[i2] - mx);
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) if (lane + 32 * j < n) y[lane + 32 * j] = v[j] * inv;
+}
+
 }  // namespace
 
 extern "C" {
@@ -276,6 +326,12 @@ int b200_op_soft_max(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * 
     }
     S.sinks = sinks ? (const float *) sinks->data : nullptr;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    if (rows >= 64 && a->ne[0] <= 32 * 32) {                   // many short rows: a warp per row
+        const unsigned g = (unsigned) ((rows + SMW_ROWS - 1) / SMW_ROWS);
+        if (a->ne[0] <= 32 * 8) OPS_LAUNCH(ctx, soft_max_warp_kernel<8>, g, OPS_THREADS, view_of(a), view_of(d), S, rows);
+        else                    OPS_LAUNCH(ctx, soft_max_warp_kernel<32>, g, OPS_THREADS, view_of(a), view_of(d), S, rows);
+        return finish(ctx);
+    }
     OPS_LAUNCH(ctx, soft_max_kernel, (unsigned) rows, OPS_THREADS, view_of(a), view_of(d), S);
     return finish(ctx);
 }
