@@ -907,6 +907,14 @@ void backend_graph_optimize(ggml_backend_t backend, ggml_cgraph * cgraph) {
         for (int j = i + 1; j < cgraph->n_nodes && j <= i + 32 && members < 3; ++j) {
             ggml_tensor * t = cgraph->nodes[j];
             if (!groupable(t) || t->src[1] != first->src[1] || t->src[0]->type != first->src[0]->type) continue;
+            // (an op between the two that works in place on the shared activations — a node that is a view of their buffer — pins the order)
+            bool pinned = false;
+            const ggml_tensor * xroot = first->src[1]->view_src ? first->src[1]->view_src : first->src[1];
+            for (int k = ins; k < j && !pinned; ++k) {
+                const ggml_tensor * m = cgraph->nodes[k];
+                pinned = !is_view_op(m->op) && m->view_src && (m->view_src == xroot || m->view_src == first->src[1]);
+            }
+            if (pinned) break;
             if (j != ins) {                      // rotate nodes[ins .. j] right by one
                 for (int k = j; k > ins; --k) cgraph->nodes[k] = cgraph->nodes[k - 1];
                 cgraph->nodes[ins] = t;
