@@ -4,7 +4,7 @@ reading before GPU time is spent.  Test infrastructure only."""
 import numpy as np, struct, sys
 sys.path.insert(0,'/root/repo')
 from oracle import refenv
-ref = refenv.load_ref()
+ref = refenv.load_ref()          # None when oracle/_ref was not built
 M32=0xFFFFFFFF
 def f16(b0,b1): return float(np.frombuffer(bytes([b0,b1]),dtype=np.float16)[0])
 def word(b,off): return int.from_bytes(bytes(b[off:off+4]),'little')
@@ -91,9 +91,10 @@ def unit_nvfp4(row,ib):
         for x in v: out+=[(d0 if s==0 else d1)*q for q in s8x4(x)]
     return out
 TYPES={"q2_K":(10,256,84,unit_q2k),"q3_K":(11,256,110,unit_q3k),"iq4_nl":(20,32,18,unit_iq4nl),"iq4_xs":(23,256,136,unit_iq4xs),"mxfp4":(39,32,17,unit_mxfp4),"nvfp4":(40,64,36,unit_nvfp4)}
-rng=np.random.default_rng(1)
-for name,(t,bs,sz,fn) in TYPES.items():
-    k=1024
+def check(name, k=1024, seed=1):
+    """max |emulated - dequantize_row| / max |dequantize_row| for one row of gaussian weights quantized by the reference"""
+    t,bs,sz,fn=TYPES[name]
+    rng=np.random.default_rng(seed)
     wf=(rng.standard_normal((2,k))*0.05).astype(np.float32)
     W=np.zeros((2,k//bs*sz),np.uint8)
     ref.ref_quantize_chunk(t,refenv.ptr(wf),refenv.ptr(W),2,k)
@@ -101,5 +102,9 @@ for name,(t,bs,sz,fn) in TYPES.items():
     assert ref.ref_dequantize_row(t,refenv.ptr(np.ascontiguousarray(W[1])),refenv.ptr(want),k)==0
     row=[int(x) for x in W[1]]
     got=np.array(sum([fn(row,ib) for ib in range(k//32)],[]),np.float64)
-    err=np.abs(got-want).max()/np.abs(want).max()
-    print(name,"max rel err",err, "nonzero", np.count_nonzero(want))
+    return float(np.abs(got-want).max()/np.abs(want).max()), int(np.count_nonzero(want))
+
+if __name__=="__main__":
+    for name in TYPES:
+        err,nz=check(name)
+        print(name,"max rel err",err,"nonzero",nz)
