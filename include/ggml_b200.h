@@ -114,7 +114,9 @@ B200_API int   b200_ctx_synchronize(b200_ctx * ctx);
 B200_API int64_t b200_ctx_launch_count(const b200_ctx * ctx);
 /* tuning knobs (also read once from the GGML_B200_* environment): name in
  * {"force_generic","use_tc","max_gemv_cols","pdl","fuse_quant","defer_wait","gemv_cfg","use_mma","mma_min_n","mma_ks","mma_ch",
- *  "tc_pair","tc_nt","tc_split_k","gather_push","noop","use_stream","stream_min_jobs","stream_stages"}; returns the previous value or B200_E_ARG */
+ *  "mma_prequant","tc_pair","tc_nt","tc_split_k","tc_pdl","tc_dequant" (weight types without a tcgen05 converter go through an fp16 scratch
+ *  copy at n >= 17),"ops_pdl" (programmatic dependent launch on the graph-op kernels),"gather_push","noop","use_stream","stream_min_jobs",
+ *  "stream_stages","stream_ll","stream_grid","stream_chain","stream_trace","gemv_rpw","gemv_rpw_max_m"}; returns the previous value or B200_E_ARG */
 B200_API int   b200_ctx_set_option(b200_ctx * ctx, const char * name, int value);
 
 /* ---- (1) activation quantizer ------------------------------------------------------------------- */
