@@ -894,9 +894,14 @@ bool backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend
 // next to each other — llama.cpp emits wq, ROPE(q), wk, ROPE(k), wv …, and only adjacent MUL_MAT nodes reach the kernels as one list
 // (b200_mul_mat_batch: one quantization of the activations, one launch for q / k / v).  A moved node depends on nothing but its weight and
 // the shared activations, which are complete before the first MUL_MAT of the group, so the order stays a valid one.
+void reorder_shared_activation_mul_mats(ggml_cgraph * cgraph);
 void backend_graph_optimize(ggml_backend_t backend, ggml_cgraph * cgraph) {
     b200_backend_ctx * bctx = (b200_backend_ctx *) backend->context;
     if (!bctx->reorder || only_mul_mat()) return;
+    reorder_shared_activation_mul_mats(cgraph);
+}
+
+void reorder_shared_activation_mul_mats(ggml_cgraph * cgraph) {
     auto groupable = [](const ggml_tensor * t) {
         return t->op == GGML_OP_MUL_MAT && t->src[0] && t->src[1] && is_quant_weight(t->src[0]->type) && !split_src0(t) && t->src[0]->op == GGML_OP_NONE;
     };
@@ -1216,6 +1221,13 @@ ggml_backend_reg_t ggml_backend_b200_reg(void) {
 }
 
 static int ggml_backend_b200_score(void) { return b200_device_count() > 0 ? 100 : 0; }
+
+// the node reordering of graph_optimize on its own (needs no device): oracle/reorder_check.cpp checks on the CPU that the new order is still
+// a valid one and that q / k / v and gate / up end up adjacent
+extern "C" {
+GGML_BACKEND_API void ggml_backend_b200_reorder_graph(ggml_cgraph * cgraph);
+void ggml_backend_b200_reorder_graph(ggml_cgraph * cgraph) { reorder_shared_activation_mul_mats(cgraph); }
+}
 
 GGML_BACKEND_DL_IMPL(ggml_backend_b200_reg)
 GGML_BACKEND_DL_SCORE_IMPL(ggml_backend_b200_score)
