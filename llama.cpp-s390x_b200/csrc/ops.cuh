@@ -71,6 +71,15 @@ inline int finish(b200_ctx * ctx) {
 }
 
 __device__ __forceinline__ void split4(int64_t i, const int64_t (&ne)[4], int64_t & i0, int64_t & i1, int64_t & i2, int64_t & i3) {
+    if (((((uint64_t) i) | (uint64_t) ne[0] | (uint64_t) ne[1] | (uint64_t) ne[2]) >> 32) == 0) {      // (the usual case: 32-bit divisions)
+        uint32_t r = (uint32_t) i;
+        const uint32_t n0 = (uint32_t) ne[0], n1 = (uint32_t) ne[1], n2 = (uint32_t) ne[2];
+        i0 = r % n0; r /= n0;
+        i1 = r % n1; r /= n1;
+        i2 = r % n2;
+        i3 = r / n2;
+        return;
+    }
     i0 = i % ne[0]; i /= ne[0];
     i1 = i % ne[1]; i /= ne[1];
     i2 = i % ne[2];

@@ -59,10 +59,13 @@ __global__ void __launch_bounds__(OPS_THREADS) rms_norm_kernel(const tview a, co
 // the same for rows of float4s (16-byte aligned rows, one weight per channel): 1024 threads, the first two float4 of every thread stay in
 // registers between the two passes — a 4096-value row is ONE load per thread, against a 16-deep serial load chain per thread in the kernel
 // above (a decode step normalises single rows: the latency of that chain is the kernel)
+// Many rows at once (a prompt: 512 rows of 4096) take 256 threads per row and four float4 in registers instead: more rows in flight per SM
+// and an 8-warp instead of a 32-warp reduction.
 constexpr int RMS_VEC_THREADS = 1024;
-__global__ void __launch_bounds__(RMS_VEC_THREADS) rms_norm_vec_kernel(const tview a, const tview w, const tview d, const float eps) {
+template <int THREADS, int KEEP>
+__global__ void __launch_bounds__(THREADS) rms_norm_vec_kernel(const tview a, const tview w, const tview d, const float eps) {
     pdl_enter();
-    __shared__ float red[RMS_VEC_THREADS / 32];
+    __shared__ float red[THREADS / 32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % a.ne[1], i2 = (r / a.ne[1]) % a.ne[2], i3 = r / (a.ne[1] * a.ne[2]);
     const float4 * x = (const float4 *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
@@ -70,21 +73,21 @@ __global__ void __launch_bounds__(RMS_VEC_THREADS) rms_norm_vec_kernel(const tvi
     const float4 * wf = w.p ? (const float4 *) (w.p + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]) : nullptr;
     const int64_t n4 = a.ne[0] >> 2;
     const int tid = threadIdx.x;
-    float4 keep[2];
+    float4 keep[KEEP];
     float s = 0.0f;
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const int64_t i = tid + (int64_t) j * RMS_VEC_THREADS;
+    for (int j = 0; j < KEEP; ++j) {
+        const int64_t i = tid + (int64_t) j * THREADS;
         keep[j] = i < n4 ? x[i] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         s += keep[j].x * keep[j].x + keep[j].y * keep[j].y + keep[j].z * keep[j].z + keep[j].w * keep[j].w;
     }
-    for (int64_t i = tid + 2 * RMS_VEC_THREADS; i < n4; i += RMS_VEC_THREADS) { const float4 v = x[i]; s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
+    for (int64_t i = tid + (int64_t) KEEP * THREADS; i < n4; i += THREADS) { const float4 v = x[i]; s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w; }
     s = warp_sum(s);
     if ((tid & 31) == 0) red[tid >> 5] = s;
     __syncthreads();
     float t = 0.0f;
 #pragma unroll
-    for (int k = 0; k < RMS_VEC_THREADS / 32; ++k) t += red[k];
+    for (int k = 0; k < THREADS / 32; ++k) t += red[k];
     const float scale = 1.0f / sqrtf(t / (float) a.ne[0] + eps);
     auto emit = [&](const int64_t i, float4 v) {
         v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
@@ -92,8 +95,8 @@ __global__ void __launch_bounds__(RMS_VEC_THREADS) rms_norm_vec_kernel(const tvi
         y[i] = v;
     };
 #pragma unroll
-    for (int j = 0; j < 2; ++j) { const int64_t i = tid + (int64_t) j * RMS_VEC_THREADS; if (i < n4) emit(i, keep[j]); }
-    for (int64_t i = tid + 2 * RMS_VEC_THREADS; i < n4; i += RMS_VEC_THREADS) emit(i, x[i]);
+    for (int j = 0; j < KEEP; ++j) { const int64_t i = tid + (int64_t) j * THREADS; if (i < n4) emit(i, keep[j]); }
+    for (int64_t i = tid + (int64_t) KEEP * THREADS; i < n4; i += THREADS) emit(i, x[i]);
 }
 
 // ---- ROPE (normal and NeoX pair layouts, YaRN, frequency factors) ------------------------------------------------------------
@@ -112,15 +115,18 @@ template <> __device__ __forceinline__ float from_f32<float>(float v) { return v
 template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
 
 // one thread per pair of a row; rows = (i1 head, i2 position, i3 batch)
-template <typename T>
+template <typename T, typename IDX>
 __global__ void __launch_bounds__(OPS_THREADS) rope_kernel(const tview a, const tview d, const rope_args R, const int64_t n) {
     pdl_enter();
     const int64_t half0 = a.ne[0] / 2;
+    // (IDX = uint32_t whenever the pair count fits: the 64-bit divisions of the index split were most of this kernel's instructions)
+    const IDX h0 = (IDX) half0, ne1 = (IDX) a.ne[1], ne2 = (IDX) a.ne[2];
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
-        const int64_t pr = i % half0;
-        int64_t r = i / half0;
-        const int64_t i1 = r % a.ne[1]; r /= a.ne[1];
-        const int64_t i2 = r % a.ne[2], i3 = r / a.ne[2];
+        const IDX ii = (IDX) i;
+        const int64_t pr = (int64_t) (ii % h0);
+        IDX r = ii / h0;
+        const int64_t i1 = (int64_t) (r % ne1); r /= ne1;
+        const int64_t i2 = (int64_t) (r % ne2), i3 = (int64_t) (r / ne2);
         const T * src = (const T *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
         T *       dst = (T *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
         const int64_t i0 = 2 * pr;                      // index into the (cos, sin) sequence
@@ -262,7 +268,8 @@ int b200_op_rms_norm_mul(b200_ctx * ctx, const b200_tensor * a, const b200_tenso
     if (w) vw = view_of(w);
     auto al16 = [](const b200_tensor * t) { return (((uintptr_t) t->data | (uintptr_t) t->nb[1] | (uintptr_t) t->nb[2] | (uintptr_t) t->nb[3]) & 15) == 0; };
     const bool vec = a->ne[0] % 4 == 0 && a->ne[0] >= 1024 && al16(a) && al16(d) && (!w || (w->ne[0] == a->ne[0] && w->nb[0] == 4 && al16(w)));
-    if (vec) OPS_LAUNCH(ctx, rms_norm_vec_kernel, (unsigned) rows, RMS_VEC_THREADS, view_of(a), vw, view_of(d), eps);
+    if (vec && rows >= 64) OPS_LAUNCH(ctx, (rms_norm_vec_kernel<256, 4>), (unsigned) rows, 256, view_of(a), vw, view_of(d), eps);
+    else if (vec) OPS_LAUNCH(ctx, (rms_norm_vec_kernel<RMS_VEC_THREADS, 2>), (unsigned) rows, RMS_VEC_THREADS, view_of(a), vw, view_of(d), eps);
     else     OPS_LAUNCH(ctx, rms_norm_kernel, (unsigned) rows, OPS_THREADS, view_of(a), vw, view_of(d), eps);
     return finish(ctx);
 }
@@ -297,8 +304,14 @@ int b200_op_rope(b200_ctx * ctx, const b200_tensor * a, const b200_tensor * pos,
     if (n == 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     const int g = grid_for(n, ctx->sm_count);
-    if (a->type == B200_TYPE_F32) OPS_LAUNCH(ctx, rope_kernel<float>, g, OPS_THREADS, view_of(a), view_of(d), R, n);
-    else                          OPS_LAUNCH(ctx, rope_kernel<__half>, g, OPS_THREADS, view_of(a), view_of(d), R, n);
+    const bool small = n < ((int64_t) 1 << 31);
+    if (a->type == B200_TYPE_F32) {
+        if (small) OPS_LAUNCH(ctx, (rope_kernel<float, uint32_t>), g, OPS_THREADS, view_of(a), view_of(d), R, n);
+        else       OPS_LAUNCH(ctx, (rope_kernel<float, int64_t>), g, OPS_THREADS, view_of(a), view_of(d), R, n);
+    } else {
+        if (small) OPS_LAUNCH(ctx, (rope_kernel<__half, uint32_t>), g, OPS_THREADS, view_of(a), view_of(d), R, n);
+        else       OPS_LAUNCH(ctx, (rope_kernel<__half, int64_t>), g, OPS_THREADS, view_of(a), view_of(d), R, n);
+    }
     return finish(ctx);
 }
 
