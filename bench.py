@@ -787,7 +787,7 @@ def plugin_e2e(args):
         return None
     env = refenv.ref_env({"GGML_BACKEND_PATH": str(plugin)})
     try:
-        p = subprocess.run([str(exe), "70b" if MODEL.endswith("70B") else "8b", str(max(5, min(args.steps, 50))), str(max(3, args.warmup))],
+        p = subprocess.run([str(exe), "70b" if MODEL.endswith("70B") else "8b", str(max(5, min(args.steps, 50))), str(max(8, args.warmup))],      # (>= 8 untimed steps: the plug-in times a graph eagerly and replayed over its first 7 sights)
                            env=env, capture_output=True, text=True, timeout=600)
         if p.returncode != 0:
             sys.stderr.write("e2e_plugin failed: " + (p.stdout + p.stderr)[-1000:] + "\n")
