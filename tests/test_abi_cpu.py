@@ -89,3 +89,28 @@ def test_backend_plugin_exports():
     out = subprocess.run(["nm", "-D", "--defined-only", str(so)], capture_output=True, text=True, check=True).stdout
     for sym in ("ggml_backend_init", "ggml_backend_score", "ggml_backend_b200_reg"):
         assert re.search(rf"\bT {sym}\b", out), sym
+
+
+# enum ggml_type -> (block elements, block bytes) of every quantized weight type the path takes (ggml-common.h)
+WEIGHT_FORMATS = {2: (32, 18), 3: (32, 20), 6: (32, 22), 7: (32, 24), 8: (32, 34), 10: (256, 84), 11: (256, 110), 12: (256, 144), 13: (256, 176),
+                  14: (256, 210), 20: (32, 18), 23: (256, 136), 39: (32, 17), 40: (64, 36)}
+
+
+@pytest.mark.parametrize("t", sorted(WEIGHT_FORMATS))
+def test_weight_type_geometry_and_validation(pkg, t):
+    """block geometry as the reference defines it, and b200_mul_mat_supported's stride rules per type (no device needed): whole blocks
+    per row, 2-byte aligned rows — except MXFP4, whose 17-byte blocks make rows of any byte alignment legal"""
+    L = pkg.lib()
+    bs, sz = WEIGHT_FORMATS[t]
+    assert (pkg.blck_size(t), pkg.type_size(t)) == (bs, sz)
+    k, m, n = 3 * 256, 5, 2                                   # 3 super-blocks / 12 or 24 small blocks per row
+    rs = pkg.row_size(t, k)
+    assert rs == k // bs * sz
+    a = _t(pkg, t, (k, m, 1, 1), (sz, rs, rs * m, rs * m))
+    b = _t(pkg, pkg.F32, (k, n, 1, 1), (4, 4 * k, 4 * k * n, 4 * k * n))
+    d = _t(pkg, pkg.F32, (m, n, 1, 1), (4, 4 * m, 4 * m * n, 4 * m * n))
+    assert L.b200_mul_mat_supported(C.byref(a), C.byref(b), C.byref(d)) == 1
+    short = _t(pkg, t, (k - bs // 2, m, 1, 1), (sz, rs, rs * m, rs * m))            # not a whole number of blocks
+    assert L.b200_mul_mat_supported(C.byref(short), C.byref(b), C.byref(d)) == 0
+    odd = _t(pkg, t, (k, m, 1, 1), (sz, rs + 1, (rs + 1) * m, (rs + 1) * m))       # rows one byte further apart
+    assert L.b200_mul_mat_supported(C.byref(odd), C.byref(b), C.byref(d)) == (1 if t == 39 or (rs + 1) % 2 == 0 else 0)
